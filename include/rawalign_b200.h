@@ -1,0 +1,204 @@
+/*
+ * rawalign_b200.h -- C ABI of the B200 (sm_100a) hot path of RawAlign.
+ *
+ * The reference (CMU-SAFARI/RawAlign) has no plugin interface; the boundary is the two call
+ * sites inside its per-read map loop:
+ *
+ *   float* detect_events(void *km, uint32_t s_len, const float* sig,
+ *                        const ri_mapopt_t *opt, uint32_t *n);            src/revent.h:22, called rmap.cpp:551
+ *   void   align_chain(ri_chain_t&, const ri_idx_t*, const float* read_events, uint32_t, uint32_t,
+ *                      const ri_mapopt_t*, bool cigar, float min_score);   src/rmap.cpp:181, called :517, :716
+ *       -> float      DTW_global(a, a_len, b, b_len, exclude_last)                              src/dtw.hpp:21
+ *       -> float      DTW_global_slantedbanded_antidiagonalwise(a, a_len, b, b_len, R, excl)    src/dtw.hpp:25
+ *       -> dtw_result DTW_global_tb(a, a_len, b, b_len, exclude_last)                           src/dtw.hpp:28
+ *
+ * Each entry point below is the *batched* form of one of those calls: a batch of signal chunks,
+ * a batch of (read-event span, reference-signal span) pairs, or a batch of chains.  All pointers
+ * are plain host pointers unless the name ends in _dev.  Every function returns 0 on success or a
+ * negative RA_E* code; the message is available from ra_last_error().  The library never calls
+ * exit() and never frees or retains caller memory (except the reference-signal mirror, which is
+ * copied to the device in ra_ref_load).  There is no CPU fallback: without a CUDA device
+ * ra_init fails with RA_ENODEV.
+ */
+#ifndef RAWALIGN_B200_H
+#define RAWALIGN_B200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RA_OK        0
+#define RA_ENODEV   -1   /* no CUDA device / wrong architecture */
+#define RA_ECUDA    -2   /* a CUDA runtime call failed */
+#define RA_EINVAL   -3   /* bad argument */
+#define RA_ENOMEM   -4   /* host or device allocation failed */
+#define RA_EUNSUP   -5   /* combination the reference itself aborts on (rmap.cpp:223-225, :301-304) */
+
+/* same numeric values as roptions.h:20-26 */
+#define RA_DTW_BORDER_CONSTRAINT_GLOBAL 0
+#define RA_DTW_BORDER_CONSTRAINT_SPARSE 1
+#define RA_DTW_BORDER_CONSTRAINT_LOCAL  2
+#define RA_DTW_FILL_METHOD_FULL   0
+#define RA_DTW_FILL_METHOD_BANDED 1
+
+/* Sentinels of the reference: dtw.cpp uses 1e10 for "outside the band", rmap.cpp:207,266 uses
+ * -1e10 for "chain dropped by early termination". */
+#define RA_DTW_INF        1e10f
+#define RA_SCORE_DROPPED -1e10f
+
+/* The hot-path fields of ri_mapopt_t (roptions.h:39-87), same names, same defaults
+ * (roptions.c:37-53).  fp_contract selects which build of revent.c is mirrored: 1 = the
+ * reference Makefile's -O3 -march=native on an FMA host (GCC contracts revent.c:30, :61 twice and
+ * :180 into fused multiply-adds), 0 = the same source built with -ffp-contract=off. */
+typedef struct ra_mapopt_s {
+	uint32_t window_length1;      /* 3 */
+	uint32_t window_length2;      /* 6 */
+	float    threshold1;          /* 4.30265f */
+	float    threshold2;          /* 2.57058f */
+	float    peak_height;         /* 1.0f */
+	uint32_t dtw_border_constraint; /* RA_DTW_BORDER_CONSTRAINT_SPARSE */
+	uint32_t dtw_fill_method;     /* RA_DTW_FILL_METHOD_BANDED */
+	float    dtw_band_radius_frac;/* 0.10f */
+	float    dtw_match_bonus;     /* 0.4f */
+	float    dtw_min_score;       /* 20.0f */
+	uint32_t fp_contract;         /* 1 */
+	uint32_t reserved;
+} ra_mapopt_t;
+
+/* One DTW problem = one call of DTW_global / DTW_global_slantedbanded_antidiagonalwise /
+ * DTW_global_tb made by align_chain (rmap.cpp:211,215,221,273,277,284).  a = read-event span,
+ * b = reference expected-signal span, both as float offsets into the two arenas passed with the
+ * batch.  band_radius is the R align_chain computes (rmap.cpp:214,276) BEFORE the slant
+ * extension of dtw.cpp:298-300; band_radius < 0 selects the full matrix (DTW_global). */
+typedef struct ra_dtw_item_s {
+	uint64_t a_off;
+	uint64_t b_off;
+	uint32_t a_len;
+	uint32_t b_len;
+	int32_t  band_radius;
+	uint32_t exclude_last;
+} ra_dtw_item_t;
+
+/* ri_anchor_t, rmap.h:22-28 */
+typedef struct ra_anchor_s {
+	uint32_t target_position;
+	uint32_t query_position;
+} ra_anchor_t;
+
+/* What align_chain reads from ri_chain_t (rmap.h:30-46) plus where the chain's read and
+ * reference arrays live in the batch arenas.  Chains of one read must be contiguous and in the
+ * order the reference evaluates them (descending chaining_score, rmap.cpp:512): the running
+ * best_found_alignment threshold of rmap.cpp:515-524 is replayed per group. */
+typedef struct ra_chain_s {
+	uint64_t anchor_off;   /* first anchor of this chain in the anchors array (anchors[0] = chain END, rmap.cpp:194-196) */
+	uint32_t n_anchors;
+	uint32_t group;        /* chains with equal consecutive group ids share one best_found_alignment */
+	uint64_t read_off;     /* float offset of the read's event array (p->events[read_id].values) in the read arena */
+	uint64_t ref_off;      /* float offset of forward_signals[ref] / reverse_signals[ref] in the reference arena */
+} ra_chain_t;
+
+typedef struct ra_ctx ra_ctx;
+
+/* ---- lifetime ------------------------------------------------------------------------------- */
+int         ra_init(int device, ra_ctx **out);
+void        ra_destroy(ra_ctx *ctx);
+const char *ra_last_error(void);
+/* ri_mapopt_init, roptions.c:5-61 (hot-path subset) */
+void        ra_mapopt_init(ra_mapopt_t *opt);
+int         ra_set_opt(ra_ctx *ctx, const ra_mapopt_t *opt);
+/* number of kernels this context has launched since creation (bench.py's gpu_launches) */
+uint64_t    ra_launch_count(const ra_ctx *ctx);
+
+/* ---- reference-signal mirror ---------------------------------------------------------------- */
+/* Copies ri_idx_t::forward_signals / reverse_signals (rawindex.h:32-33) into one device arena:
+ * [fwd(0) | rev(0) | fwd(1) | rev(1) ...].  arena_off receives 2*n_seq float offsets (fwd, rev per
+ * sequence) to be used as ra_chain_t::ref_off / ra_dtw_item_t::b_off. */
+int ra_ref_load(ra_ctx *ctx, uint32_t n_seq, const float *const *fwd, const float *const *rev,
+                const uint32_t *len, uint64_t *arena_off);
+/* Same, from one already concatenated host array (n_floats values). */
+int ra_ref_load_flat(ra_ctx *ctx, const float *ref, uint64_t n_floats);
+/* Device pointer / size of the mirror (for NCCL broadcast by the multi-GPU driver). */
+int ra_ref_device(ra_ctx *ctx, float **dev_ptr, uint64_t *n_floats);
+/* Allocate the mirror without filling it (non-root ranks before the broadcast). */
+int ra_ref_alloc(ra_ctx *ctx, uint64_t n_floats);
+
+/* ---- K1: event detection, batched detect_events (revent.c:190-210) ---------------------------- */
+/* chunk c is sig[chunk_off[c] .. chunk_off[c]+chunk_len[c]).  Output is CSR: events of chunk c are
+ * ev_out[ev_off[c] .. ev_off[c+1]); ev_off has n_chunks+1 entries.  A chunk in which the reference
+ * finds no peak yields zero events (detect_events returns NULL and leaves *n at 0, revent.c:205-206).
+ * ev_cap is the capacity of ev_out in floats; RA_EINVAL if it is too small (sum chunk_len is
+ * always enough). */
+int ra_detect_events_batch(ra_ctx *ctx, const float *sig, uint64_t n_sig,
+                           const uint64_t *chunk_off, const uint32_t *chunk_len, uint32_t n_chunks,
+                           float *ev_out, uint64_t ev_cap, uint64_t *ev_off);
+/* Device-resident form: every pointer is a device pointer; runs on the context stream and
+ * returns after the stream is synchronised. total_events (host) receives ev_off[n_chunks]. */
+int ra_detect_events_batch_dev(ra_ctx *ctx, const float *sig_dev,
+                               const uint64_t *chunk_off_dev, const uint32_t *chunk_len_dev,
+                               uint32_t n_chunks, uint32_t max_chunk_len,
+                               float *ev_out_dev, uint64_t ev_cap, uint64_t *ev_off_dev,
+                               uint64_t *total_events);
+
+/* ---- K2/K3: DTW cost, batched DTW_global / DTW_global_slantedbanded_antidiagonalwise ---------- */
+/* a_arena = read events, b_arena = reference signal; b_arena == NULL uses the mirror of
+ * ra_ref_load.  cost_out[k] is bit-identical to the reference call for item k. */
+int ra_dtw_batch(ra_ctx *ctx, const float *a_arena, uint64_t n_a, const float *b_arena, uint64_t n_b,
+                 const ra_dtw_item_t *items, uint32_t n_items, float *cost_out);
+int ra_dtw_batch_dev(ra_ctx *ctx, const float *a_arena_dev, const float *b_arena_dev,
+                     const ra_dtw_item_t *items_dev, const ra_dtw_item_t *items_host,
+                     uint32_t n_items, float *cost_out_dev);
+/* Exact number of DP cells the reference evaluates for one item (the GCUPS numerator):
+ * |cell set| of dtw.cpp:273-520 for band_radius >= 0, a_len*b_len otherwise. */
+uint64_t ra_dtw_cells(uint32_t a_len, uint32_t b_len, int32_t band_radius);
+
+/* ---- K4: DTW with traceback, batched DTW_global_tb (dtw.cpp:595-667) --------------------------- */
+/* Always the full matrix (the reference has no banded traceback, rmap.cpp:223-225,284).
+ * Path of item k is path_i/path_j[path_off[k] .. path_off[k+1]) in forward order, i indexing a
+ * (read events) and j indexing b (reference), both relative to the item's spans; the third field
+ * of alignment_element, |a[i]-b[j]|, is written to path_diff when it is non-NULL.
+ * path_cap = capacity of the three path arrays; sum(a_len+b_len-1) is always enough. */
+int ra_dtw_tb_batch(ra_ctx *ctx, const float *a_arena, uint64_t n_a, const float *b_arena, uint64_t n_b,
+                    const ra_dtw_item_t *items, uint32_t n_items, float *cost_out,
+                    uint32_t *path_i, uint32_t *path_j, float *path_diff, uint64_t path_cap,
+                    uint64_t *path_off);
+
+/* ---- chain level: batched align_chain + the evaluation loop of gen_chains ---------------------- */
+/* For every chain: slices the sub-problems exactly as align_chain does for the border constraint
+ * and fill method in the context options (rmap.cpp:192-300), evaluates all of them on the GPU in
+ * one batch, then replays on the host, in the reference's order and float arithmetic, the early
+ * termination against min_score (rmap.cpp:205-209, :265-268), the cost accumulation (:279-280) and
+ * alignment_score = n_aligned*bonus - cost (:306).
+ * min_score_mode 0: every chain is scored against the given min_score[k] (NULL = -1e10, the
+ *                   default argument of align_chain);
+ * min_score_mode 1: the running best_found_alignment of rmap.cpp:515-524 is replayed per group
+ *                   (starts at 0.0f, raised by chains with score >= dtw_min_score).
+ * alignment_score[k] receives chain.alignment_score; keep[k] (optional) receives
+ * alignment_score >= dtw_min_score (rmap.cpp:518). cells_issued / cells_useful (optional) receive
+ * the DP cells the GPU evaluated and the cells the reference would have evaluated. */
+int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
+                          const float *ref_arena, uint64_t n_ref,
+                          const ra_anchor_t *anchors, uint64_t n_anchors,
+                          const ra_chain_t *chains, uint32_t n_chains,
+                          int min_score_mode, const float *min_score,
+                          float *alignment_score, uint8_t *keep,
+                          uint64_t *cells_issued, uint64_t *cells_useful);
+
+/* cigar=true form of align_chain (rmap.cpp:218-235, :282-299) for one batch of chains: the
+ * concatenated alignment with anchor offsets applied exactly as the reference does (including
+ * the quirks listed in SURVEY.md A.4: sparse ignores exclude_last_element and always uses the
+ * full matrix; global offsets only the last element, n times).  RA_EUNSUP for global+banded. */
+int ra_align_chains_cigar_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
+                                const float *ref_arena, uint64_t n_ref,
+                                const ra_anchor_t *anchors, uint64_t n_anchors,
+                                const ra_chain_t *chains, uint32_t n_chains,
+                                float *alignment_score, float *dtw_cost,
+                                uint64_t *path_i, uint64_t *path_j, float *path_diff, uint64_t path_cap,
+                                uint64_t *path_off);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RAWALIGN_B200_H */
