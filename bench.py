@@ -1,0 +1,407 @@
+#!/usr/bin/env python
+"""bench.py -- RawAlign hot path (event detection + DTW chain evaluation) on B200.
+
+  python bench.py --gpus N --steps K --warmup W            our arm (CUDA, through the C ABI)
+  python bench.py --impl reference --gpus N --steps K ...  the reference's own CPU code for the path
+                                                           (oracle/_ref when built, else the oracle port)
+
+Workload (BASELINE.json configs[1], synthetic): 5 Mb random reference, pore-model-simulated R9.4 reads,
+sparse border, banded=0.1.  One step = one pass of the hot path over one batch of reads per GPU:
+K1 (event detection) over every 4000-sample chunk of the batch, then the DTW evaluation of every
+candidate chain of every chunk round (chains grow with the number of chunks seen and are recomputed
+from scratch each round, as rmap.cpp does).  Weak scaling: every rank gets its own batch (reads are
+independent; no data-path collective).  See DESIGN.md "Measurement".
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+REF_BASES = 5_000_000
+MAX_CHUNKS = 8
+CHAINS_PER_ROUND = 3
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------
+# workload
+# ------------------------------------------------------------------------------------------------------
+def build_reference():
+    from rawalign_b200 import synth
+    ref = synth.random_reference(REF_BASES, seed=1)
+    mm, _ = synth.pore_model()
+    fwd = synth.seq_to_sig(ref, mm, 0); rev = synth.seq_to_sig(ref, mm, 1)
+    return ref, np.concatenate([fwd, rev])          # arena: [strand0 | strand1]
+
+
+def build_reads(ref, n_reads, seed):
+    from rawalign_b200 import synth
+    reads = synth.simulate_reads(ref, n_reads, seed=seed, max_chunks=MAX_CHUNKS)
+    coff, clen, crid = synth.chunk_table(reads.read_off, reads.read_len, max_chunks=MAX_CHUNKS)
+    return reads, coff, clen, crid
+
+
+def build_chains(ev_off, crid, n_reads, ref_len, seed):
+    """Chains of every chunk round of every read.  Round c of a read sees the events of chunks 0..c
+    (they are contiguous in the CSR event arena because chunks of a read are consecutive)."""
+    from rawalign_b200 import synth
+    per_chunk = np.diff(ev_off.astype(np.int64))
+    first_chunk = np.searchsorted(crid, np.arange(n_reads), "left")
+    last_chunk = np.searchsorted(crid, np.arange(n_reads), "right")
+    anchors, chains = [], []
+    a_base = 0
+    for rnd in range(MAX_CHUNKS):
+        has = (last_chunk - first_chunk) > rnd
+        n_ev = np.zeros(n_reads, np.int64)
+        for r in np.nonzero(has)[0]:
+            n_ev[r] = per_chunk[first_chunk[r]:first_chunk[r] + rnd + 1].sum()
+        a, c = synth.synth_chains(n_ev, ev_off[first_chunk.clip(max=len(ev_off) - 2)], ref_len, seed=seed * 100 + rnd,
+                                  chains_per_read=CHAINS_PER_ROUND)
+        if len(c):
+            c = c.copy(); c["anchor_off"] += a_base; c["group"] = c["group"] * MAX_CHUNKS + rnd
+            a_base += len(a); anchors.append(a); chains.append(c)
+    return np.concatenate(anchors), np.concatenate(chains)
+
+
+def chains_to_items(anchors, chains, frac=0.1, return_chain_of=False):
+    """Sub-problems of sparse-border align_chain (rmap.cpp:248-281), vectorised; test/bench helper."""
+    from rawalign_b200 import ITEM_DTYPE
+    n_parts = chains["n_anchors"].astype(np.int64) - 1
+    tot = int(n_parts.sum())
+    chain_of = np.repeat(np.arange(len(chains)), n_parts)
+    first = np.concatenate(([0], np.cumsum(n_parts)[:-1]))
+    p = np.arange(tot) - first[chain_of]
+    parts = n_parts[chain_of]
+    s_idx = chains["anchor_off"].astype(np.int64)[chain_of] + parts - p
+    s = anchors[s_idx]; e = anchors[s_idx - 1]
+    it = np.zeros(tot, ITEM_DTYPE)
+    it["a_off"] = chains["read_off"][chain_of] + s["query_position"]
+    it["b_off"] = chains["ref_off"][chain_of] + s["target_position"]
+    it["a_len"] = e["query_position"] - s["query_position"] + 1
+    it["b_len"] = e["target_position"] - s["target_position"] + 1
+    it["band_radius"] = np.maximum(1, (it["a_len"].astype(np.float32) * np.float32(frac)).astype(np.int32))
+    it["exclude_last"] = (p != parts - 1)
+    if return_chain_of:
+        return it, chain_of
+    return it
+
+
+def item_cells(items):
+    """Exact DP cells per item (GCUPS numerator) -- closed form for the shapes that dominate, C ABI otherwise."""
+    import rawalign_b200 as ra
+    key = (items["a_len"].astype(np.uint64) << np.uint64(40)) | (items["b_len"].astype(np.uint64) << np.uint64(16)) | items["band_radius"].astype(np.uint64)
+    uniq, inv = np.unique(key, return_inverse=True)
+    cells = np.array([ra.Context.dtw_cells(int(k >> np.uint64(40)), int((k >> np.uint64(16)) & np.uint64(0xFFFFFF)), int(k & np.uint64(0xFFFF))) for k in uniq], np.int64)
+    return cells[inv]
+
+
+# ------------------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index = index; self.rows = []; self._stop = False; self.t = None
+
+    def start(self):
+        def run():
+            while not self._stop:
+                try:
+                    out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                         capture_output=True, text=True, timeout=5).stdout.strip()
+                    if out:
+                        self.rows.append([x.strip() for x in out.split(",")])
+                except Exception:
+                    pass
+                time.sleep(0.1)
+        self.t = threading.Thread(target=run, daemon=True); self.t.start()
+
+    def stop(self):
+        self._stop = True
+        if self.t:
+            self.t.join(timeout=6)
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows for i in range(4) if len(r) > 2 + i and r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------------
+# CPU legs
+# ------------------------------------------------------------------------------------------------------
+def cpu_backend():
+    from oracle import Oracle, Reference
+    if Reference.available(True):
+        return Reference(True), "reference"
+    return Oracle(), "port"
+
+
+def cpu_step(be, sig, coff, clen, anchors, chains, ref_arena, n_threads, ev_cache=None):
+    """One pass of the hot path on the host for the given reads: detect_events per chunk, then every
+    sub-DTW of every chain (the reference evaluates them one by one inside align_chain)."""
+    from concurrent.futures import ThreadPoolExecutor
+    t0 = time.perf_counter()
+    n = len(coff)
+    bounds = np.linspace(0, n, n_threads + 1).astype(int)
+
+    def ev_job(k):
+        lo, hi = bounds[k], bounds[k + 1]
+        if hi <= lo:
+            return np.zeros(0, np.float32), np.zeros(1, np.uint64)
+        return be.detect_events_batch(sig, coff[lo:hi], clen[lo:hi])
+    with ThreadPoolExecutor(n_threads) as ex:
+        parts = list(ex.map(ev_job, range(n_threads)))
+    ev = np.concatenate([p[0] for p in parts])
+    t1 = time.perf_counter()
+    items = chains_to_items(anchors, chains)
+    ib = np.linspace(0, len(items), n_threads + 1).astype(int)
+
+    def dtw_job(k):
+        return be.dtw_batch(ev, ref_arena, items[ib[k]:ib[k + 1]])
+    with ThreadPoolExecutor(n_threads) as ex:
+        costs = list(ex.map(dtw_job, range(n_threads)))
+    t2 = time.perf_counter()
+    return t2 - t0, t1 - t0, t2 - t1, len(ev), np.concatenate(costs)
+
+
+def subset_reads(n_sub, crid, coff, clen, anchors, chains):
+    """The first n_sub reads of the batch (chunks and chains), anchors re-based."""
+    cm = crid < n_sub
+    ch = chains[(chains["group"] // MAX_CHUNKS) < n_sub]
+    return coff[cm], clen[cm], anchors, ch
+
+
+# ------------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--reads-per-gpu", type=int, default=int(os.environ.get("RA_BENCH_READS", 1024)))
+    ap.add_argument("--cpu-sample-reads", type=int, default=32)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1)); local = int(os.environ.get("LOCAL_RANK", 0))
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = max(args.warmup, 3)
+    config = {"workload": "C2: 5 Mb synthetic reference, simulated R9.4 reads, sparse border, banded=0.1",
+              "reads_per_gpu": args.reads_per_gpu, "max_chunks_per_read": MAX_CHUNKS, "chains_per_round": CHAINS_PER_ROUND,
+              "l2_policy": "inputs larger than L2 (signal batch >> 126 MB)"}
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        return run_reference_arm(args, config)
+
+    import torch
+    import torch.distributed as dist
+    import rawalign_b200 as ra
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback in the product path); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+
+    t_setup = time.time()
+    ref_seq, ref_arena = build_reference()
+    reads, coff, clen, crid = build_reads(ref_seq, args.reads_per_gpu, seed=2 + rank)
+    ctx = ra.Context(local)
+    # reference mirror: rank 0 loads, everyone else receives it by one NCCL broadcast
+    ctx.ref_alloc(len(ref_arena))
+    ptr, nfl = ctx.ref_device()
+    if world > 1:
+        ref_t = torch.from_numpy(ref_arena).to(dev) if rank == 0 else torch.empty(len(ref_arena), dtype=torch.float32, device=dev)
+        dist.broadcast(ref_t, 0)
+        _copy_dev(ptr, ref_t)          # device-to-device into the context's mirror
+        del ref_t
+    else:
+        ctx.ref_load_flat(ref_arena)
+
+    n_chunks = len(coff)
+    sig_pinned = torch.from_numpy(reads.sig).pin_memory()
+    coff_p = torch.from_numpy(coff.view(np.int64)).pin_memory(); clen_p = torch.from_numpy(clen.view(np.int32)).pin_memory()
+    sig_d = sig_pinned.to(dev); coff_d = coff_p.to(dev); clen_d = clen_p.to(dev)
+    ev_cap = int(clen.sum())
+    ev_d = torch.empty(ev_cap // 2 + 16, dtype=torch.float32, device=dev)
+    evoff_d = torch.empty(n_chunks + 1, dtype=torch.int64, device=dev)
+    torch.cuda.synchronize()
+    n_events = ctx.detect_events_batch_dev(sig_d.data_ptr(), coff_d.data_ptr(), clen_d.data_ptr(), n_chunks, int(clen.max()),
+                                           ev_d.data_ptr(), ev_d.numel(), evoff_d.data_ptr())
+    ev_off = evoff_d.cpu().numpy().view(np.uint64)
+    anchors, chains = build_chains(ev_off, crid, args.reads_per_gpu, REF_BASES - 6, seed=3 + rank)
+    items, chain_of = chains_to_items(anchors, chains, return_chain_of=True)
+    cells = int(item_cells(items).sum())
+    items_p = torch.from_numpy(items.view(np.uint8).reshape(-1)).pin_memory()
+    items_d = items_p.to(dev)
+    cost_d = torch.empty(len(items), dtype=torch.float32, device=dev)
+    n_samples = int(clen.sum())
+    log(f"[rank {rank}] setup {time.time() - t_setup:.1f}s: reads={args.reads_per_gpu} chunks={n_chunks} samples={n_samples} "
+        f"events={n_events} chains={len(chains)} sub-DTWs={len(items)} cells={cells}")
+
+    def step_device():
+        ctx.detect_events_batch_dev(sig_d.data_ptr(), coff_d.data_ptr(), clen_d.data_ptr(), n_chunks, int(clen.max()),
+                                    ev_d.data_ptr(), ev_d.numel(), evoff_d.data_ptr())
+        ctx.dtw_batch_dev(ev_d.data_ptr(), None, items_d.data_ptr(), items, cost_d.data_ptr())
+
+    ev_host = np.empty(ev_cap, np.float32); evoff_host = np.empty(n_chunks + 1, np.uint64)
+    score_holder = {}
+
+    def step_e2e():
+        ev, off = ctx.detect_events_batch(sig_pinned.numpy(), coff, clen, ev_host, evoff_host)
+        s, keep, _, _ = ctx.align_chains_batch(ev, None, anchors, chains, min_score_mode=1)
+        score_holder["s"] = s
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- device-resident timing ----
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    sampler = ClockSampler(local); sampler.start()
+    l0 = ctx.launch_count
+    t0 = time.perf_counter()
+    ev_ms, dtw_ms, scan_ms = [], [], []
+    for _ in range(args.steps):
+        ta = time.perf_counter()
+        ctx.detect_events_batch_dev(sig_d.data_ptr(), coff_d.data_ptr(), clen_d.data_ptr(), n_chunks, int(clen.max()),
+                                    ev_d.data_ptr(), ev_d.numel(), evoff_d.data_ptr())
+        tb = time.perf_counter()
+        ctx.dtw_batch_dev(ev_d.data_ptr(), None, items_d.data_ptr(), items, cost_d.data_ptr())
+        tc = time.perf_counter()
+        tm = ctx.last_timing()
+        ev_ms.append(tm[1]); dtw_ms.append(tm[2]); scan_ms.append(tm[0])
+    barrier()
+    dt = time.perf_counter() - t0
+    launches = ctx.launch_count - l0
+    clocks = sampler.stop()
+    # ---- end-to-end timing (host buffers, copies inside) ----
+    for _ in range(2):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    barrier()
+    dt_e2e = time.perf_counter() - t0
+
+    tt = torch.tensor([dt, dt_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    dt, dt_e2e = float(tt[0]), float(tt[1])
+    tot = torch.tensor([args.reads_per_gpu, cells, n_samples, n_events], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tot)
+    reads_all, cells_all, samples_all, events_all = [float(x) for x in tot]
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0)); peak_src = "measured" if peaks else "fallback"
+        ms_step = dt / args.steps * 1e3
+        k1_ms = float(np.median(scan_ms)); k1_all_ms = float(np.median(ev_ms)); k2_ms = float(np.median(dtw_ms))
+        k1_bytes = 4.0 * n_samples + 4.0 * n_events + 8.0 * n_chunks
+        sm_clk = (clocks.get("sm_mhz") or 1965.0) * 1e6
+        alu_peak_gcups = 148 * 128 * 1965.0e6 / 4 / 1e9
+        out = {
+            "metric": "reads_per_s", "value": reads_all * args.steps / dt, "unit": "reads/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+            "dtw_gcups": cells / (k2_ms * 1e-3) / 1e9, "hot_path_gcups": cells_all * args.steps / dt / 1e9,
+            "stages_ms": {"events_scan_kernel": k1_ms, "events_all_kernels": k1_all_ms, "dtw_kernels": k2_ms,
+                          "timing": "CUDA events on the library stream"},
+            "e2e": {"value": reads_all * args.steps / dt_e2e, "unit": "reads/s", "ms_per_step": dt_e2e / args.steps * 1e3,
+                    "h2d_bytes_per_step": int(reads.sig.nbytes + coff.nbytes + clen.nbytes + anchors.nbytes + chains.nbytes),
+                    "d2h_bytes_per_step": int(4 * n_events + 8 * (n_chunks + 1) + 4 * len(chains))},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"kernel": "k_events_scan", "bound": "hbm", "achieved": k1_bytes / (k1_ms * 1e-3) / 1e9, "peak": hbm_peak,
+                         "unit": "GB/s", "frac": k1_bytes / (k1_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None, "peak_source": peak_src},
+            "roofline_dtw": {"kernel": "k_dtw", "bound": "alu", "achieved": cells / (k2_ms * 1e-3) / 1e9, "peak": alu_peak_gcups,
+                             "unit": "GCUPS", "frac": cells / (k2_ms * 1e-3) / 1e9 / alu_peak_gcups,
+                             "peak_source": "148 SMs x 128 lanes x 1.965 GHz / 4 ops per cell"},
+        }
+        if not args.no_cpu_baseline:
+            be, kind = cpu_backend()
+            nsub = min(args.cpu_sample_reads, args.reads_per_gpu)
+            c_off, c_len, a_sub, ch_sub = subset_reads(nsub, crid, coff, clen, anchors, chains)
+            # chains reference events by arena offset of the full batch: CPU leg recomputes events for the subset, whose
+            # chunks are the first ones of the batch, so offsets agree
+            t_cpu, t_ev, t_dtw, n_ev_cpu, costs = cpu_step(be, reads.sig, c_off, c_len, a_sub, ch_sub, ref_arena, 1)
+            out["cpu_baseline"] = {"value": nsub / t_cpu, "unit": "reads/s", "cores": 1, "kind": kind,
+                                   "sample": f"first {nsub} reads of the batch, one pass, single thread (events {t_ev:.2f}s + dtw {t_dtw:.2f}s)"}
+            # parity spot check of the timed configuration: GPU costs of the subset == CPU costs
+            sub_mask = ((chains["group"] // MAX_CHUNKS) < nsub)[chain_of]
+            got = cost_d.cpu().numpy()[sub_mask]
+            out["cpu_baseline"]["parity_bit_exact"] = bool(np.array_equal(got.view(np.uint32), costs.view(np.uint32)))
+        print(json.dumps(out), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def _copy_dev(dst_ptr, src_tensor):
+    import torch
+    n = src_tensor.numel()
+    # wrap the context's mirror as a tensor via the CUDA array interface
+    class _W:
+        pass
+    w = _W(); w.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (dst_ptr, False), "version": 2}
+    torch.as_tensor(w, device=src_tensor.device).copy_(src_tensor)
+    torch.cuda.synchronize()
+
+
+def run_reference_arm(args, config):
+    """The reference's own CPU implementation of the path on all host threads; each step is a bounded sample."""
+    be, kind = cpu_backend()
+    n_threads = os.cpu_count() or 1
+    nsub = max(n_threads, min(args.reads_per_gpu, int(os.environ.get("RA_REF_SAMPLE_READS", 4 * n_threads))))
+    ref_seq, ref_arena = build_reference()
+    reads, coff, clen, crid = build_reads(ref_seq, nsub, seed=2)
+    # events of the sample are needed to place the chains (same generator as the GPU arm)
+    ev, ev_off = be.detect_events_batch(reads.sig, coff, clen)
+    anchors, chains = build_chains(ev_off, crid, nsub, REF_BASES - 6, seed=3)
+    for _ in range(min(args.warmup, 1)):
+        cpu_step(be, reads.sig, coff, clen, anchors, chains, ref_arena, n_threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        t_cpu, t_ev, t_dtw, _, _ = cpu_step(be, reads.sig, coff, clen, anchors, chains, ref_arena, n_threads)
+    dt = time.perf_counter() - t0
+    val = nsub * args.steps / dt
+    out = {"impl": "reference", "metric": "reads_per_s", "value": val, "unit": "reads/s", "n_gpus": args.gpus, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "f32", "data": "synthetic", "config": dict(config, reads_per_step=nsub),
+           "cpu_baseline": {"value": val, "unit": "reads/s", "cores": n_threads, "kind": kind,
+                            "sample": f"{nsub} reads per step (same generator and shape as the GPU arm), {n_threads} threads"},
+           "e2e": {"value": val, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out), flush=True)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

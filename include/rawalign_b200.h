@@ -111,6 +111,9 @@ void        ra_mapopt_init(ra_mapopt_t *opt);
 int         ra_set_opt(ra_ctx *ctx, const ra_mapopt_t *opt);
 /* number of kernels this context has launched since creation (bench.py's gpu_launches) */
 uint64_t    ra_launch_count(const ra_ctx *ctx);
+/* Device time of the most recent event-detection and DTW batches, measured with CUDA events on the
+ * context's own stream: the detector kernel alone, all K1 kernels, all DTW kernels (milliseconds). */
+int         ra_last_timing(ra_ctx *ctx, float *events_scan_ms, float *events_total_ms, float *dtw_ms);
 
 /* ---- reference-signal mirror ---------------------------------------------------------------- */
 /* Copies ri_idx_t::forward_signals / reverse_signals (rawindex.h:32-33) into one device arena:

@@ -1,0 +1,648 @@
+// api.cu -- the C ABI of include/rawalign_b200.h: context, device arenas, host<->device staging,
+// and the host-side replay of align_chain's control flow (src/rmap.cpp:181-313, :515-524).
+#include "ra_common.cuh"
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <vector>
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char *fmt, ...)
+{
+	va_list ap; va_start(ap, fmt);
+	vsnprintf(g_err, sizeof(g_err), fmt, ap);
+	va_end(ap);
+	return code;
+}
+
+#define RA_CUDA(call)                                                                                   \
+	do {                                                                                                \
+		cudaError_t e__ = (call);                                                                       \
+		if (e__ != cudaSuccess) return fail(RA_ECUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+	} while (0)
+
+// grow-only device buffer
+struct DevBuf {
+	void *p = nullptr;
+	size_t cap = 0;
+	int reserve(size_t bytes)
+	{
+		if (bytes <= cap) return RA_OK;
+		if (p) { cudaFree(p); p = nullptr; cap = 0; }
+		size_t want = bytes + bytes / 4 + 256;
+		cudaError_t e = cudaMalloc(&p, want);
+		if (e != cudaSuccess) { p = nullptr; cap = 0; (void)cudaGetLastError(); return fail(RA_ENOMEM, "cudaMalloc(%zu) failed: %s", want, cudaGetErrorString(e)); }
+		cap = want;
+		return RA_OK;
+	}
+	void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+	template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+} // namespace
+
+struct ra_ctx {
+	int device = 0;
+	int n_sm = 0;
+	cudaStream_t stream = nullptr;
+	ra_mapopt_t opt;
+	uint64_t launches = 0;
+	cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // K1 start / after scan / end, DTW start / end
+	bool timed_k1 = false, timed_dtw = false;
+	// reference mirror
+	DevBuf ref; uint64_t ref_n = 0;
+	// events
+	DevBuf sig, chunk_off, chunk_len, raw, nev, stat, ev_off, ev_out;
+	// dtw
+	DevBuf a_arena, b_arena, items, cost, counter, ring, order;
+	// traceback
+	DevBuf dirs, dir_off, slot_off, slot_i, slot_j, slot_d, path_len, path_off, out_i, out_j, out_d;
+};
+
+namespace {
+
+uint32_t events_raw_stride(const ra_mapopt_t &o, uint32_t max_len)
+{
+	// a detector emits at i >= peak_pos + w/2 + 1 and can only start its next peak at a later sample,
+	// so peaks of one detector are >= w/2 + 2 apart
+	const uint32_t s1 = o.window_length1 / 2 + 2, s2 = o.window_length2 / 2 + 2;
+	return max_len / s1 + max_len / s2 + 4;
+}
+
+int events_dev(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_dev, const uint32_t *chunk_len_dev,
+               uint32_t n_chunks, uint32_t max_chunk_len, float *ev_out_dev, uint64_t ev_cap, uint64_t *ev_off_dev,
+               uint64_t *total_events)
+{
+	const ra_mapopt_t &o = ctx->opt;
+	if (!ra::events_windows_supported(o.window_length1, o.window_length2))
+		return fail(RA_EUNSUP, "event detector windows (%u,%u) have no compiled kernel (built: (3,6) DNA, (7,14) RNA)",
+		            o.window_length1, o.window_length2);
+	if (n_chunks == 0) { if (total_events) *total_events = 0; uint64_t z = 0; RA_CUDA(cudaMemcpyAsync(ev_off_dev, &z, 8, cudaMemcpyHostToDevice, ctx->stream)); RA_CUDA(cudaStreamSynchronize(ctx->stream)); return RA_OK; }
+	const uint32_t stride = events_raw_stride(o, max_chunk_len);
+	int rc;
+	if ((rc = ctx->raw.reserve((size_t)n_chunks * stride * sizeof(float)))) return rc;
+	if ((rc = ctx->nev.reserve((size_t)n_chunks * sizeof(uint32_t)))) return rc;
+	if ((rc = ctx->stat.reserve((size_t)n_chunks * sizeof(ra::EvChunkStat)))) return rc;
+	ra::EvParams p = { o.window_length1, o.window_length2, o.threshold1, o.threshold2, o.peak_height };
+	RA_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
+	RA_CUDA(ra::launch_events_scan(sig_dev, chunk_off_dev, chunk_len_dev, n_chunks, p, (int)o.fp_contract,
+	                               ctx->raw.as<float>(), stride, ctx->nev.as<uint32_t>(), ctx->stat.as<ra::EvChunkStat>(), ctx->stream));
+	RA_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
+	RA_CUDA(ra::launch_exclusive_scan_u32(ctx->nev.as<uint32_t>(), ev_off_dev, n_chunks, ctx->stream));
+	RA_CUDA(ra::launch_events_normalise(ctx->raw.as<float>(), stride, ctx->nev.as<uint32_t>(), ctx->stat.as<ra::EvChunkStat>(),
+	                                    ev_off_dev, n_chunks, ev_out_dev, ev_cap, ctx->stream));
+	RA_CUDA(cudaEventRecord(ctx->ev[2], ctx->stream));
+	ctx->timed_k1 = true;
+	ctx->launches += 3;
+	uint64_t tot = 0;
+	RA_CUDA(cudaMemcpyAsync(&tot, ev_off_dev + n_chunks, sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+	RA_CUDA(cudaStreamSynchronize(ctx->stream));
+	if (total_events) *total_events = tot;
+	if (tot > ev_cap) return fail(RA_EINVAL, "ev_out capacity %llu < %llu events", (unsigned long long)ev_cap, (unsigned long long)tot);
+	return RA_OK;
+}
+
+// width (in floats) of the widest anti-diagonal of one item, as the generic kernel sees it
+uint32_t item_width(const ra_dtw_item_t &it, bool tb)
+{
+	uint32_t n = std::max(it.a_len, it.b_len), m = std::min(it.a_len, it.b_len);
+	if (tb) return it.b_len;
+	if (it.band_radius < 0) return m;
+	if (n == 0) return 0;
+	const uint32_t extra = ((n - m) * (uint32_t)it.band_radius + n - 1u) / n;
+	return (uint32_t)it.band_radius + extra + 1u;
+}
+
+// Launches the cost kernels for items already on the device. items_host is used for sizing only.
+int dtw_dev(ra_ctx *ctx, const float *a_dev, const float *b_dev, const ra_dtw_item_t *items_dev,
+            const ra_dtw_item_t *items_host, uint32_t n_items, float *cost_dev)
+{
+	if (n_items == 0) return RA_OK;
+	int rc;
+	uint32_t maxw = 0;
+	for (uint32_t k = 0; k < n_items; ++k) maxw = std::max(maxw, item_width(items_host[k], false));
+	ra::DtwLaunch L; memset(&L, 0, sizeof(L));
+	L.a_arena = a_dev; L.b_arena = b_dev; L.items = items_dev; L.n_items = n_items; L.cost = cost_dev;
+	if ((rc = ctx->counter.reserve(64))) return rc;
+	L.work_counter = ctx->counter.as<uint32_t>();
+	if (maxw > ra::dtw_generic_smem_ring_cap()) {
+		uint32_t cap = 1; while (cap < maxw) cap <<= 1;
+		const size_t warps = (size_t)ctx->n_sm * 4 * 4;
+		if ((rc = ctx->ring.reserve(warps * 3 * cap * sizeof(float)))) return rc;
+		L.ring_scratch = ctx->ring.as<float>(); L.ring_cap = cap;
+	}
+	int nl = 0;
+	RA_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
+	RA_CUDA(ra::launch_dtw_generic(L, false, ctx->n_sm, ctx->stream, &nl));
+	RA_CUDA(cudaEventRecord(ctx->ev[4], ctx->stream));
+	ctx->timed_dtw = true;
+	ctx->launches += nl;
+	return RA_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+const char *ra_last_error(void) { return g_err; }
+
+void ra_mapopt_init(ra_mapopt_t *o)
+{
+	memset(o, 0, sizeof(*o));
+	o->window_length1 = 3; o->window_length2 = 6;                 // roptions.c:49-50
+	o->threshold1 = 4.30265f; o->threshold2 = 2.57058f;           // :51-52
+	o->peak_height = 1.0f;                                        // :53
+	o->dtw_border_constraint = RA_DTW_BORDER_CONSTRAINT_SPARSE;   // :37
+	o->dtw_fill_method = RA_DTW_FILL_METHOD_BANDED;               // :38
+	o->dtw_band_radius_frac = 0.10f;                              // :39
+	o->dtw_match_bonus = 0.4f;                                    // :40
+	o->dtw_min_score = 20.0f;                                     // :41
+	o->fp_contract = 1;
+}
+
+int ra_init(int device, ra_ctx **out)
+{
+	if (!out) return fail(RA_EINVAL, "out is NULL");
+	*out = nullptr;
+	int n = 0;
+	cudaError_t e = cudaGetDeviceCount(&n);
+	if (e != cudaSuccess || n == 0) { (void)cudaGetLastError(); return fail(RA_ENODEV, "no CUDA device (%s); this library has no CPU fallback", e != cudaSuccess ? cudaGetErrorString(e) : "count=0"); }
+	if (device < 0 || device >= n) return fail(RA_EINVAL, "device %d out of range [0,%d)", device, n);
+	cudaDeviceProp prop;
+	RA_CUDA(cudaGetDeviceProperties(&prop, device));
+	if (prop.major < 10) return fail(RA_ENODEV, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+	RA_CUDA(cudaSetDevice(device));
+	ra_ctx *ctx = new (std::nothrow) ra_ctx();
+	if (!ctx) return fail(RA_ENOMEM, "out of host memory");
+	ctx->device = device; ctx->n_sm = prop.multiProcessorCount;
+	ra_mapopt_init(&ctx->opt);
+	e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+	if (e != cudaSuccess) { delete ctx; return fail(RA_ECUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); }
+	for (int k = 0; k < 5; ++k) {
+		e = cudaEventCreate(&ctx->ev[k]);
+		if (e != cudaSuccess) { delete ctx; return fail(RA_ECUDA, "cudaEventCreate: %s", cudaGetErrorString(e)); }
+	}
+	*out = ctx;
+	return RA_OK;
+}
+
+void ra_destroy(ra_ctx *ctx)
+{
+	if (!ctx) return;
+	cudaSetDevice(ctx->device);
+	cudaStreamSynchronize(ctx->stream);
+	DevBuf *bufs[] = { &ctx->ref, &ctx->sig, &ctx->chunk_off, &ctx->chunk_len, &ctx->raw, &ctx->nev, &ctx->stat, &ctx->ev_off,
+	                   &ctx->ev_out, &ctx->a_arena, &ctx->b_arena, &ctx->items, &ctx->cost, &ctx->counter, &ctx->ring, &ctx->order,
+	                   &ctx->dirs, &ctx->dir_off, &ctx->slot_off, &ctx->slot_i, &ctx->slot_j, &ctx->slot_d, &ctx->path_len,
+	                   &ctx->path_off, &ctx->out_i, &ctx->out_j, &ctx->out_d };
+	for (DevBuf *b : bufs) b->release();
+	for (int k = 0; k < 5; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
+	cudaStreamDestroy(ctx->stream);
+	delete ctx;
+}
+
+int ra_set_opt(ra_ctx *ctx, const ra_mapopt_t *opt)
+{
+	if (!ctx || !opt) return fail(RA_EINVAL, "NULL argument");
+	if (opt->dtw_border_constraint > RA_DTW_BORDER_CONSTRAINT_LOCAL) return fail(RA_EINVAL, "invalid border constraint %u", opt->dtw_border_constraint);
+	if (opt->dtw_fill_method > RA_DTW_FILL_METHOD_BANDED) return fail(RA_EINVAL, "invalid fill method %u", opt->dtw_fill_method);
+	ctx->opt = *opt;
+	return RA_OK;
+}
+
+uint64_t ra_launch_count(const ra_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int ra_last_timing(ra_ctx *ctx, float *events_scan_ms, float *events_total_ms, float *dtw_ms)
+{
+	if (!ctx) return fail(RA_EINVAL, "NULL ctx");
+	RA_CUDA(cudaSetDevice(ctx->device));
+	RA_CUDA(cudaStreamSynchronize(ctx->stream));
+	float a = 0.f, b = 0.f, c = 0.f;
+	if (ctx->timed_k1) { RA_CUDA(cudaEventElapsedTime(&a, ctx->ev[0], ctx->ev[1])); RA_CUDA(cudaEventElapsedTime(&b, ctx->ev[0], ctx->ev[2])); }
+	if (ctx->timed_dtw) RA_CUDA(cudaEventElapsedTime(&c, ctx->ev[3], ctx->ev[4]));
+	if (events_scan_ms) *events_scan_ms = a;
+	if (events_total_ms) *events_total_ms = b;
+	if (dtw_ms) *dtw_ms = c;
+	return RA_OK;
+}
+
+/* ---- reference mirror ---------------------------------------------------------------------------- */
+
+int ra_ref_alloc(ra_ctx *ctx, uint64_t n_floats)
+{
+	if (!ctx) return fail(RA_EINVAL, "NULL ctx");
+	RA_CUDA(cudaSetDevice(ctx->device));
+	int rc = ctx->ref.reserve((size_t)std::max<uint64_t>(n_floats, 1) * sizeof(float));
+	if (rc) return rc;
+	ctx->ref_n = n_floats;
+	return RA_OK;
+}
+
+int ra_ref_load_flat(ra_ctx *ctx, const float *ref, uint64_t n_floats)
+{
+	if (!ctx || (!ref && n_floats)) return fail(RA_EINVAL, "NULL argument");
+	int rc = ra_ref_alloc(ctx, n_floats);
+	if (rc) return rc;
+	RA_CUDA(cudaMemcpyAsync(ctx->ref.p, ref, (size_t)n_floats * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	RA_CUDA(cudaStreamSynchronize(ctx->stream));
+	return RA_OK;
+}
+
+int ra_ref_load(ra_ctx *ctx, uint32_t n_seq, const float *const *fwd, const float *const *rev, const uint32_t *len,
+                uint64_t *arena_off)
+{
+	if (!ctx || !fwd || !rev || !len || !arena_off) return fail(RA_EINVAL, "NULL argument");
+	uint64_t tot = 0;
+	for (uint32_t s = 0; s < n_seq; ++s) { arena_off[2 * s] = tot; tot += len[s]; arena_off[2 * s + 1] = tot; tot += len[s]; }
+	int rc = ra_ref_alloc(ctx, tot);
+	if (rc) return rc;
+	for (uint32_t s = 0; s < n_seq; ++s) {
+		RA_CUDA(cudaMemcpyAsync(ctx->ref.as<float>() + arena_off[2 * s], fwd[s], (size_t)len[s] * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+		RA_CUDA(cudaMemcpyAsync(ctx->ref.as<float>() + arena_off[2 * s + 1], rev[s], (size_t)len[s] * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	}
+	RA_CUDA(cudaStreamSynchronize(ctx->stream));
+	return RA_OK;
+}
+
+int ra_ref_device(ra_ctx *ctx, float **dev_ptr, uint64_t *n_floats)
+{
+	if (!ctx || !dev_ptr || !n_floats) return fail(RA_EINVAL, "NULL argument");
+	*dev_ptr = ctx->ref.as<float>(); *n_floats = ctx->ref_n;
+	return RA_OK;
+}
+
+/* ---- K1 ------------------------------------------------------------------------------------------ */
+
+int ra_detect_events_batch_dev(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_dev,
+                               const uint32_t *chunk_len_dev, uint32_t n_chunks, uint32_t max_chunk_len,
+                               float *ev_out_dev, uint64_t ev_cap, uint64_t *ev_off_dev, uint64_t *total_events)
+{
+	if (!ctx || !ev_off_dev || (n_chunks && (!sig_dev || !chunk_off_dev || !chunk_len_dev || !ev_out_dev)))
+		return fail(RA_EINVAL, "NULL argument");
+	RA_CUDA(cudaSetDevice(ctx->device));
+	return events_dev(ctx, sig_dev, chunk_off_dev, chunk_len_dev, n_chunks, max_chunk_len, ev_out_dev, ev_cap, ev_off_dev, total_events);
+}
+
+int ra_detect_events_batch(ra_ctx *ctx, const float *sig, uint64_t n_sig, const uint64_t *chunk_off,
+                           const uint32_t *chunk_len, uint32_t n_chunks, float *ev_out, uint64_t ev_cap, uint64_t *ev_off)
+{
+	if (!ctx || !ev_off || (n_chunks && (!sig || !chunk_off || !chunk_len || !ev_out))) return fail(RA_EINVAL, "NULL argument");
+	RA_CUDA(cudaSetDevice(ctx->device));
+	uint32_t max_len = 0; uint64_t sum_len = 0;
+	for (uint32_t c = 0; c < n_chunks; ++c) {
+		if (chunk_off[c] + chunk_len[c] > n_sig) return fail(RA_EINVAL, "chunk %u exceeds the signal array", c);
+		max_len = std::max(max_len, chunk_len[c]); sum_len += chunk_len[c];
+	}
+	int rc;
+	if ((rc = ctx->sig.reserve((size_t)std::max<uint64_t>(n_sig, 4) * sizeof(float)))) return rc;
+	if ((rc = ctx->chunk_off.reserve((size_t)(n_chunks + 1) * sizeof(uint64_t)))) return rc;
+	if ((rc = ctx->chunk_len.reserve((size_t)(n_chunks + 1) * sizeof(uint32_t)))) return rc;
+	if ((rc = ctx->ev_off.reserve((size_t)(n_chunks + 1) * sizeof(uint64_t)))) return rc;
+	const uint64_t dev_cap = std::min<uint64_t>(ev_cap, (uint64_t)n_chunks * events_raw_stride(ctx->opt, max_len));
+	if ((rc = ctx->ev_out.reserve((size_t)std::max<uint64_t>(dev_cap, 1) * sizeof(float)))) return rc;
+	if (n_chunks) {
+		RA_CUDA(cudaMemcpyAsync(ctx->sig.p, sig, (size_t)n_sig * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+		RA_CUDA(cudaMemcpyAsync(ctx->chunk_off.p, chunk_off, (size_t)n_chunks * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
+		RA_CUDA(cudaMemcpyAsync(ctx->chunk_len.p, chunk_len, (size_t)n_chunks * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+	}
+	uint64_t total = 0;
+	rc = events_dev(ctx, ctx->sig.as<float>(), ctx->chunk_off.as<uint64_t>(), ctx->chunk_len.as<uint32_t>(), n_chunks, max_len,
+	                ctx->ev_out.as<float>(), dev_cap, ctx->ev_off.as<uint64_t>(), &total);
+	if (rc) return rc;
+	RA_CUDA(cudaMemcpyAsync(ev_off, ctx->ev_off.p, (size_t)(n_chunks + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+	if (total) RA_CUDA(cudaMemcpyAsync(ev_out, ctx->ev_out.p, (size_t)total * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+	RA_CUDA(cudaStreamSynchronize(ctx->stream));
+	return RA_OK;
+}
+
+/* ---- K2 / K3 ------------------------------------------------------------------------------------- */
+
+uint64_t ra_dtw_cells(uint32_t a_len, uint32_t b_len, int32_t band_radius)
+{
+	if (band_radius < 0) return (uint64_t)a_len * b_len;
+	if (a_len == 0 || b_len == 0) return 0;
+	const int64_t n = std::max(a_len, b_len), m = std::min(a_len, b_len);
+	const uint32_t extra = (((uint32_t)n - (uint32_t)m) * (uint32_t)band_radius + (uint32_t)n - 1u) / (uint32_t)n;   // dtw.cpp:298
+	const int64_t R = (int64_t)band_radius + (int64_t)extra;
+	const int64_t P = R + (R % 2 == 0 ? 1 : 0), S = R + (R % 2 == 1 ? 1 : 0);
+	auto count = [&](int64_t start_i, int64_t start_j, int64_t len) -> uint64_t {
+		int64_t o0 = std::max<int64_t>(std::max<int64_t>(0, start_i - (n - 1)), -start_j);                              // :365, :419
+		int64_t o1 = std::min<int64_t>(std::min<int64_t>(len, start_i + 1), m - start_j);                               // :366, :420
+		return o1 > o0 ? (uint64_t)(o1 - o0) : 0;
+	};
+	uint64_t cells = 1;
+	int64_t r = 0;
+	for (int64_t c = 1; c < n; ++c) {
+		if ((r + 1) * n <= m * c) { ++r; cells += count(c + S / 2 - 1, r - S / 2, S); }
+		cells += count(c + P / 2, r - P / 2, P);
+	}
+	return cells;
+}
+
+int ra_dtw_batch_dev(ra_ctx *ctx, const float *a_arena_dev, const float *b_arena_dev, const ra_dtw_item_t *items_dev,
+                     const ra_dtw_item_t *items_host, uint32_t n_items, float *cost_out_dev)
+{
+	if (!ctx || (n_items && (!a_arena_dev || !items_dev || !items_host || !cost_out_dev))) return fail(RA_EINVAL, "NULL argument");
+	RA_CUDA(cudaSetDevice(ctx->device));
+	const float *b = b_arena_dev ? b_arena_dev : ctx->ref.as<float>();
+	if (n_items && !b) return fail(RA_EINVAL, "no reference arena: pass b_arena or call ra_ref_load first");
+	int rc = dtw_dev(ctx, a_arena_dev, b, items_dev, items_host, n_items, cost_out_dev);
+	if (rc) return rc;
+	RA_CUDA(cudaStreamSynchronize(ctx->stream));
+	return RA_OK;
+}
+
+static int check_items(const ra_dtw_item_t *items, uint32_t n_items, uint64_t n_a, uint64_t n_b)
+{
+	for (uint32_t k = 0; k < n_items; ++k) {
+		const ra_dtw_item_t &it = items[k];
+		if (it.a_len == 0 || it.b_len == 0) return fail(RA_EINVAL, "item %u has an empty span (the reference asserts a_length > 0 && b_length > 0)", k);
+		if (it.a_off + it.a_len > n_a) return fail(RA_EINVAL, "item %u: read span exceeds the read arena", k);
+		if (it.b_off + it.b_len > n_b) return fail(RA_EINVAL, "item %u: reference span exceeds the reference arena", k);
+		if (it.a_len > 0x3fffffffu || it.b_len > 0x3fffffffu) return fail(RA_EINVAL, "item %u: span too long", k);
+	}
+	return RA_OK;
+}
+
+int ra_dtw_batch(ra_ctx *ctx, const float *a_arena, uint64_t n_a, const float *b_arena, uint64_t n_b,
+                 const ra_dtw_item_t *items, uint32_t n_items, float *cost_out)
+{
+	if (!ctx || (n_items && (!a_arena || !items || !cost_out))) return fail(RA_EINVAL, "NULL argument");
+	RA_CUDA(cudaSetDevice(ctx->device));
+	if (n_items == 0) return RA_OK;
+	if (!b_arena && !ctx->ref.p) return fail(RA_EINVAL, "no reference arena: pass b_arena or call ra_ref_load first");
+	int rc = check_items(items, n_items, n_a, b_arena ? n_b : ctx->ref_n);
+	if (rc) return rc;
+	if ((rc = ctx->a_arena.reserve((size_t)n_a * sizeof(float)))) return rc;
+	if ((rc = ctx->items.reserve((size_t)n_items * sizeof(ra_dtw_item_t)))) return rc;
+	if ((rc = ctx->cost.reserve((size_t)n_items * sizeof(float)))) return rc;
+	RA_CUDA(cudaMemcpyAsync(ctx->a_arena.p, a_arena, (size_t)n_a * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	const float *b_dev = ctx->ref.as<float>();
+	if (b_arena) {
+		if ((rc = ctx->b_arena.reserve((size_t)n_b * sizeof(float)))) return rc;
+		RA_CUDA(cudaMemcpyAsync(ctx->b_arena.p, b_arena, (size_t)n_b * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+		b_dev = ctx->b_arena.as<float>();
+	}
+	RA_CUDA(cudaMemcpyAsync(ctx->items.p, items, (size_t)n_items * sizeof(ra_dtw_item_t), cudaMemcpyHostToDevice, ctx->stream));
+	if ((rc = dtw_dev(ctx, ctx->a_arena.as<float>(), b_dev, ctx->items.as<ra_dtw_item_t>(), items, n_items, ctx->cost.as<float>()))) return rc;
+	RA_CUDA(cudaMemcpyAsync(cost_out, ctx->cost.p, (size_t)n_items * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+	RA_CUDA(cudaStreamSynchronize(ctx->stream));
+	return RA_OK;
+}
+
+/* ---- K4 ------------------------------------------------------------------------------------------ */
+
+int ra_dtw_tb_batch(ra_ctx *ctx, const float *a_arena, uint64_t n_a, const float *b_arena, uint64_t n_b,
+                    const ra_dtw_item_t *items, uint32_t n_items, float *cost_out, uint32_t *path_i, uint32_t *path_j,
+                    float *path_diff, uint64_t path_cap, uint64_t *path_off)
+{
+	if (!ctx || !path_off || (n_items && (!a_arena || !items || !cost_out || !path_i || !path_j))) return fail(RA_EINVAL, "NULL argument");
+	RA_CUDA(cudaSetDevice(ctx->device));
+	path_off[0] = 0;
+	if (n_items == 0) return RA_OK;
+	if (!b_arena && !ctx->ref.p) return fail(RA_EINVAL, "no reference arena: pass b_arena or call ra_ref_load first");
+	int rc = check_items(items, n_items, n_a, b_arena ? n_b : ctx->ref_n);
+	if (rc) return rc;
+	// per-item direction matrix (diagonal-major, 16 cells per word, 128-byte aligned) and path slot
+	std::vector<uint64_t> dir_off(n_items + 1), slot_off(n_items + 1);
+	uint64_t dwords = 0, slots = 0; uint32_t maxw = 0;
+	for (uint32_t k = 0; k < n_items; ++k) {
+		const ra_dtw_item_t &it = items[k];
+		dir_off[k] = dwords; slot_off[k] = slots;
+		const uint64_t stride = ((uint64_t)it.b_len + 15) >> 4;
+		dwords += (((uint64_t)it.a_len + it.b_len - 1) * stride + 31) & ~(uint64_t)31;
+		slots += (uint64_t)it.a_len + it.b_len - 1;
+		maxw = std::max(maxw, it.b_len);
+	}
+	dir_off[n_items] = dwords; slot_off[n_items] = slots;
+	if ((rc = ctx->a_arena.reserve((size_t)n_a * sizeof(float)))) return rc;
+	if ((rc = ctx->items.reserve((size_t)n_items * sizeof(ra_dtw_item_t)))) return rc;
+	if ((rc = ctx->cost.reserve((size_t)n_items * sizeof(float)))) return rc;
+	if ((rc = ctx->dirs.reserve((size_t)dwords * 4))) return rc;
+	if ((rc = ctx->dir_off.reserve((size_t)(n_items + 1) * 8))) return rc;
+	if ((rc = ctx->slot_off.reserve((size_t)(n_items + 1) * 8))) return rc;
+	if ((rc = ctx->slot_i.reserve((size_t)slots * 4))) return rc;
+	if ((rc = ctx->slot_j.reserve((size_t)slots * 4))) return rc;
+	if (path_diff && (rc = ctx->slot_d.reserve((size_t)slots * 4))) return rc;
+	if ((rc = ctx->path_len.reserve((size_t)n_items * 4))) return rc;
+	if ((rc = ctx->path_off.reserve((size_t)(n_items + 1) * 8))) return rc;
+	if ((rc = ctx->out_i.reserve((size_t)slots * 4))) return rc;
+	if ((rc = ctx->out_j.reserve((size_t)slots * 4))) return rc;
+	if (path_diff && (rc = ctx->out_d.reserve((size_t)slots * 4))) return rc;
+	if ((rc = ctx->counter.reserve(64))) return rc;
+	RA_CUDA(cudaMemcpyAsync(ctx->a_arena.p, a_arena, (size_t)n_a * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	const float *b_dev = ctx->ref.as<float>();
+	if (b_arena) {
+		if ((rc = ctx->b_arena.reserve((size_t)n_b * sizeof(float)))) return rc;
+		RA_CUDA(cudaMemcpyAsync(ctx->b_arena.p, b_arena, (size_t)n_b * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+		b_dev = ctx->b_arena.as<float>();
+	}
+	RA_CUDA(cudaMemcpyAsync(ctx->items.p, items, (size_t)n_items * sizeof(ra_dtw_item_t), cudaMemcpyHostToDevice, ctx->stream));
+	RA_CUDA(cudaMemcpyAsync(ctx->dir_off.p, dir_off.data(), (size_t)(n_items + 1) * 8, cudaMemcpyHostToDevice, ctx->stream));
+	RA_CUDA(cudaMemcpyAsync(ctx->slot_off.p, slot_off.data(), (size_t)(n_items + 1) * 8, cudaMemcpyHostToDevice, ctx->stream));
+
+	ra::DtwLaunch L; memset(&L, 0, sizeof(L));
+	L.a_arena = ctx->a_arena.as<float>(); L.b_arena = b_dev; L.items = ctx->items.as<ra_dtw_item_t>(); L.n_items = n_items;
+	L.cost = ctx->cost.as<float>(); L.work_counter = ctx->counter.as<uint32_t>();
+	if (maxw > ra::dtw_generic_smem_ring_cap()) {
+		uint32_t cap = 1; while (cap < maxw) cap <<= 1;
+		const size_t warps = (size_t)ctx->n_sm * 4 * 4;
+		if ((rc = ctx->ring.reserve(warps * 3 * cap * sizeof(float)))) return rc;
+		L.ring_scratch = ctx->ring.as<float>(); L.ring_cap = cap;
+	}
+	L.dirs = ctx->dirs.as<uint32_t>(); L.dir_off = ctx->dir_off.as<uint64_t>();
+	L.path_i = ctx->slot_i.as<uint32_t>(); L.path_j = ctx->slot_j.as<uint32_t>();
+	L.path_diff = path_diff ? ctx->slot_d.as<float>() : nullptr;
+	L.slot_off = ctx->slot_off.as<uint64_t>(); L.path_len = ctx->path_len.as<uint32_t>();
+	int nl = 0;
+	RA_CUDA(ra::launch_dtw_generic(L, true, ctx->n_sm, ctx->stream, &nl));
+	RA_CUDA(ra::launch_exclusive_scan_u32(ctx->path_len.as<uint32_t>(), ctx->path_off.as<uint64_t>(), n_items, ctx->stream));
+	RA_CUDA(ra::launch_path_compact(ctx->slot_i.as<uint32_t>(), ctx->slot_j.as<uint32_t>(), L.path_diff, ctx->slot_off.as<uint64_t>(),
+	                                ctx->items.as<ra_dtw_item_t>(), ctx->path_len.as<uint32_t>(), ctx->path_off.as<uint64_t>(), n_items,
+	                                ctx->out_i.as<uint32_t>(), ctx->out_j.as<uint32_t>(), path_diff ? ctx->out_d.as<float>() : nullptr, ctx->stream));
+	ctx->launches += nl + 2;
+	RA_CUDA(cudaMemcpyAsync(path_off, ctx->path_off.p, (size_t)(n_items + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+	RA_CUDA(cudaMemcpyAsync(cost_out, ctx->cost.p, (size_t)n_items * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	RA_CUDA(cudaStreamSynchronize(ctx->stream));
+	const uint64_t total = path_off[n_items];
+	if (total > path_cap) return fail(RA_EINVAL, "path capacity %llu < %llu", (unsigned long long)path_cap, (unsigned long long)total);
+	if (total) {
+		RA_CUDA(cudaMemcpyAsync(path_i, ctx->out_i.p, (size_t)total * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		RA_CUDA(cudaMemcpyAsync(path_j, ctx->out_j.p, (size_t)total * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		if (path_diff) RA_CUDA(cudaMemcpyAsync(path_diff, ctx->out_d.p, (size_t)total * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		RA_CUDA(cudaStreamSynchronize(ctx->stream));
+	}
+	return RA_OK;
+}
+
+/* ---- chain level --------------------------------------------------------------------------------- */
+
+// The sub-problems align_chain would issue for one chain (rmap.cpp:192-300), in the reference's order.
+static int chain_items(const ra_mapopt_t &o, const ra_anchor_t *anc, const ra_chain_t &ch, bool cigar,
+                       std::vector<ra_dtw_item_t> &items)
+{
+	if (ch.n_anchors == 0) return fail(RA_EINVAL, "chain without anchors");
+	const bool banded = (o.dtw_fill_method == RA_DTW_FILL_METHOD_BANDED);
+	auto push = [&](const ra_anchor_t &s, const ra_anchor_t &e, bool excl) {
+		ra_dtw_item_t it;
+		it.a_off = ch.read_off + s.query_position;                  // rmap.cpp:201, :259
+		it.b_off = ch.ref_off + s.target_position;                  // :198, :256
+		it.a_len = e.query_position - s.query_position + 1;         // :202, :260
+		it.b_len = e.target_position - s.target_position + 1;       // :199, :257
+		if (cigar || !banded) it.band_radius = -1;                  // DTW_global / DTW_global_tb
+		else it.band_radius = std::max(1, (int)((float)it.a_len * o.dtw_band_radius_frac));   // :214, :276
+		it.exclude_last = excl ? 1u : 0u;
+		items.push_back(it);
+	};
+	if (o.dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_GLOBAL) {
+		if (cigar && banded) return fail(RA_EUNSUP, "global border + banded fill + cigar is not implemented by the reference (rmap.cpp:223-225 asserts)");
+		push(anc[ch.n_anchors - 1], anc[0], false);
+	} else if (o.dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_SPARSE) {
+		const uint32_t parts = ch.n_anchors - 1;
+		for (uint32_t p = 0; p < parts; ++p)
+			push(anc[parts - p], anc[parts - p - 1], cigar ? false : (p != parts - 1));     // :270; cigar ignores it (:283-284)
+	} else {
+		return fail(RA_EUNSUP, "invalid border constraint (the reference exits at rmap.cpp:301-304)");
+	}
+	return RA_OK;
+}
+
+static inline float chain_score(const ra_mapopt_t &o, uint32_t n_aligned, float cost)
+{
+	// rmap.cpp:306; the reference build (-O3, -ffp-contract=fast default of GNU C++) fuses it
+	if (o.fp_contract) return fmaf((float)n_aligned, o.dtw_match_bonus, -cost);
+	volatile float prod = (float)n_aligned * o.dtw_match_bonus;
+	return prod - cost;
+}
+
+int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read, const float *ref_arena, uint64_t n_ref,
+                          const ra_anchor_t *anchors, uint64_t n_anchors, const ra_chain_t *chains, uint32_t n_chains,
+                          int min_score_mode, const float *min_score, float *alignment_score, uint8_t *keep,
+                          uint64_t *cells_issued, uint64_t *cells_useful)
+{
+	if (!ctx || (n_chains && (!read_arena || !anchors || !chains || !alignment_score))) return fail(RA_EINVAL, "NULL argument");
+	const ra_mapopt_t &o = ctx->opt;
+	std::vector<ra_dtw_item_t> items;
+	std::vector<uint64_t> first(n_chains + 1);
+	items.reserve((size_t)n_anchors);
+	for (uint32_t k = 0; k < n_chains; ++k) {
+		first[k] = items.size();
+		if (chains[k].anchor_off + chains[k].n_anchors > n_anchors) return fail(RA_EINVAL, "chain %u: anchors out of range", k);
+		int rc = chain_items(o, anchors + chains[k].anchor_off, chains[k], false, items);
+		if (rc) return rc;
+	}
+	first[n_chains] = items.size();
+	if (items.size() > 0xffffffffull) return fail(RA_EINVAL, "too many sub-problems in one batch");
+	std::vector<float> cost(items.size());
+	int rc = ra_dtw_batch(ctx, read_arena, n_read, ref_arena, n_ref, items.data(), (uint32_t)items.size(), cost.data());
+	if (rc) return rc;
+
+	uint64_t issued = 0, useful = 0;
+	const bool want_cells = cells_issued || cells_useful;
+	float best = 0.0f; uint32_t cur_group = 0; bool have_group = false;
+	for (uint32_t k = 0; k < n_chains; ++k) {
+		const ra_chain_t &ch = chains[k];
+		const ra_anchor_t *anc = anchors + ch.anchor_off;
+		if (min_score_mode == 1 && (!have_group || ch.group != cur_group)) { best = 0.0f; cur_group = ch.group; have_group = true; }   // rmap.cpp:515
+		const float ms = (min_score_mode == 1) ? best : (min_score ? min_score[k] : RA_SCORE_DROPPED);
+		float score;
+		const uint64_t f = first[k], l = first[k + 1];
+		if (want_cells) for (uint64_t q = f; q < l; ++q) issued += ra_dtw_cells(items[q].a_len, items[q].b_len, items[q].band_radius);
+		if (o.dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_GLOBAL) {
+			const uint32_t read_size = items[f].a_len;
+			const float max_attainable = (float)read_size * o.dtw_match_bonus;                 // :205
+			if (max_attainable < ms) score = RA_SCORE_DROPPED;                               // :206-209
+			else {
+				score = chain_score(o, read_size, cost[f]);                                  // :236, :306
+				if (want_cells) useful += ra_dtw_cells(items[f].a_len, items[f].b_len, items[f].band_radius);
+			}
+		} else {
+			const uint32_t chain_read_size = anc[0].query_position - anc[ch.n_anchors - 1].query_position + 1;   // :245
+			float cur_max = (float)chain_read_size * o.dtw_match_bonus;                      // :246
+			float dtw_cost = 0.0f; uint32_t n_aligned = 0; bool dropped = false;
+			for (uint64_t q = f; q < l; ++q) {
+				if (cur_max < ms) { dropped = true; break; }                                 // :265-268
+				dtw_cost += cost[q];                                                         // :279
+				cur_max -= cost[q];                                                          // :280
+				n_aligned += items[q].a_len;                                                 // :292
+				if (want_cells) useful += ra_dtw_cells(items[q].a_len, items[q].b_len, items[q].band_radius);
+			}
+			score = dropped ? RA_SCORE_DROPPED : chain_score(o, n_aligned, dtw_cost);
+		}
+		alignment_score[k] = score;
+		const bool kp = score >= o.dtw_min_score;                                            // :518
+		if (keep) keep[k] = kp ? 1 : 0;
+		if (min_score_mode == 1 && kp && score > best) best = score;                         // :519-521
+	}
+	if (cells_issued) *cells_issued = issued;
+	if (cells_useful) *cells_useful = useful;
+	return RA_OK;
+}
+
+int ra_align_chains_cigar_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read, const float *ref_arena, uint64_t n_ref,
+                                const ra_anchor_t *anchors, uint64_t n_anchors, const ra_chain_t *chains, uint32_t n_chains,
+                                float *alignment_score, float *dtw_cost_out, uint64_t *path_i, uint64_t *path_j, float *path_diff,
+                                uint64_t path_cap, uint64_t *path_off)
+{
+	if (!ctx || !path_off || (n_chains && (!read_arena || !anchors || !chains || !alignment_score || !path_i || !path_j)))
+		return fail(RA_EINVAL, "NULL argument");
+	const ra_mapopt_t &o = ctx->opt;
+	std::vector<ra_dtw_item_t> items;
+	std::vector<uint64_t> first(n_chains + 1);
+	for (uint32_t k = 0; k < n_chains; ++k) {
+		first[k] = items.size();
+		if (chains[k].anchor_off + chains[k].n_anchors > n_anchors) return fail(RA_EINVAL, "chain %u: anchors out of range", k);
+		int rc = chain_items(o, anchors + chains[k].anchor_off, chains[k], true, items);
+		if (rc) return rc;
+	}
+	first[n_chains] = items.size();
+	uint64_t cap = 0;
+	for (const ra_dtw_item_t &it : items) cap += (uint64_t)it.a_len + it.b_len - 1;
+	std::vector<float> cost(items.size()), pd(path_diff ? cap : 0);
+	std::vector<uint32_t> pi(cap), pj(cap);
+	std::vector<uint64_t> poff(items.size() + 1);
+	int rc = ra_dtw_tb_batch(ctx, read_arena, n_read, ref_arena, n_ref, items.data(), (uint32_t)items.size(), cost.data(),
+	                         pi.data(), pj.data(), path_diff ? pd.data() : nullptr, cap, poff.data());
+	if (rc) return rc;
+	uint64_t w = 0;
+	for (uint32_t k = 0; k < n_chains; ++k) {
+		const ra_chain_t &ch = chains[k];
+		const ra_anchor_t *anc = anchors + ch.anchor_off;
+		path_off[k] = w;
+		float dtw_cost = 0.0f; uint32_t n_aligned = 0;
+		const uint64_t f = first[k], l = first[k + 1];
+		for (uint64_t q = f; q < l; ++q) {
+			const uint64_t len = poff[q + 1] - poff[q];
+			if (w + len > path_cap) return fail(RA_EINVAL, "path capacity %llu too small", (unsigned long long)path_cap);
+			// start anchor of this part: global -> anchors[n-1]; sparse part p -> anchors[parts-p]
+			const ra_anchor_t &s = (o.dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_GLOBAL) ? anc[ch.n_anchors - 1]
+			                                                                                    : anc[(ch.n_anchors - 1) - (q - f)];
+			for (uint64_t t = 0; t < len; ++t) {
+				uint64_t pi64 = pi[poff[q] + t], pj64 = pj[poff[q] + t];
+				if (o.dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_SPARSE) { pi64 += s.query_position; pj64 += s.target_position; } // :287-288
+				path_i[w + t] = pi64; path_j[w + t] = pj64;
+				if (path_diff) path_diff[w + t] = pd[poff[q] + t];
+			}
+			if (o.dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_GLOBAL && len) {
+				// rmap.cpp:230-233: the loop shifts alignment.back() once per element
+				path_i[w + len - 1] += len * (uint64_t)s.query_position;
+				path_j[w + len - 1] += len * (uint64_t)s.target_position;
+			}
+			w += len;
+			dtw_cost += cost[q];                                                             // :226, :290
+			n_aligned += items[q].a_len;                                                     // :236, :292
+		}
+		if (dtw_cost_out) dtw_cost_out[k] = dtw_cost;
+		alignment_score[k] = chain_score(o, n_aligned, dtw_cost);                            // :306
+	}
+	path_off[n_chains] = w;
+	return RA_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,243 @@
+// dtw.cu -- K2/K3/K4 generic path: one warp per DTW problem, anti-diagonal wavefront.
+//
+// Semantics (bit-identical to the reference for every schedule, because each cell is
+// min(min(top,left),topleft) + |a-b| -- min is exact, one rounding per cell):
+//   banded : the cell set of DTW_global_slantedbanded_antidiagonalwise, src/dtw.cpp:273-520
+//            (closed form in oracle/ra_oracle.c:ora_dtw_banded and DESIGN.md), out-of-set = 1e10f;
+//   full   : DTW_global, src/dtw.cpp:37-66 (whole rectangle);
+//   tb     : DTW_global_tb, src/dtw.cpp:595-667 -- full rectangle, 2-bit direction per cell packed
+//            16 cells per 32-bit word in HBM, then the tie rule of :629-653 walked on the device.
+//
+// This is the shape-agnostic kernel: lanes stride over the rows of one anti-diagonal, three rolling
+// anti-diagonals live in a per-warp shared-memory ring (or in an HBM/L2 ring when a band is wider than
+// the ring), warps pull problems from a global work counter.  The register-resident small-band kernels
+// in dtw_small.cu take the sparse anchor-to-anchor problems; everything they do not cover lands here.
+#include "ra_common.cuh"
+
+namespace ra {
+
+constexpr int kWarpsPerCta = 4;
+constexpr uint32_t kSmemRingCap = 1024;          // floats per anti-diagonal ring in shared memory
+constexpr float kInf = 1e10f;
+
+uint32_t dtw_generic_smem_ring_cap() { return kSmemRingCap; }
+
+// Enumerates the anti-diagonals of one problem in order; warp-uniform.
+struct DiagIter {
+	int n, m, P, S;
+	bool full;
+	int c, r, d;
+	bool pending_primary;
+	int lo, hi;       // rows (index into the shorter sequence) of the current diagonal, clipped; lo > hi = empty
+
+	__device__ __forceinline__ void set_range(int start_i, int start_j, int len)
+	{
+		// cells (start_i - o, start_j + o), o in [o0, o1)   dtw.cpp:365-366, :419-420
+		int o0 = max(max(0, start_i - (n - 1)), -start_j);
+		int o1 = min(min(len, start_i + 1), m - start_j);
+		lo = start_j + o0; hi = start_j + o1 - 1;
+		d = start_i + start_j;
+	}
+	__device__ __forceinline__ void init(int n_, int m_, int band_radius)
+	{
+		n = n_; m = m_;
+		full = band_radius < 0;
+		if (!full) {
+			// dtw.cpp:298-302 (32-bit unsigned arithmetic in the reference)
+			const uint32_t extra = (((uint32_t)n - (uint32_t)m) * (uint32_t)band_radius + (uint32_t)n - 1u) / (uint32_t)n;
+			const int R = band_radius + (int)extra;
+			P = R + ((R % 2 == 0) ? 1 : 0);
+			S = R + ((R % 2 == 1) ? 1 : 0);
+		} else { P = S = 0; }
+		c = 0; r = 0; d = 0; lo = 0; hi = 0; pending_primary = false;   // iteration 0: the corner cell only (:317-347)
+	}
+	__device__ __forceinline__ bool next()
+	{
+		if (full) {
+			if (++d > n + m - 2) return false;
+			lo = max(0, d - (n - 1)); hi = min(m - 1, d);
+			return true;
+		}
+		if (pending_primary) { pending_primary = false; set_range(c + P / 2, r - P / 2, P); return true; }
+		if (++c >= n) return false;
+		if ((int64_t)(r + 1) * (int64_t)n <= (int64_t)m * (int64_t)c) {   // :352-359
+			++r; pending_primary = true;
+			set_range(c + S / 2 - 1, r - S / 2, S);                        // secondary, :362-366
+			return true;
+		}
+		set_range(c + P / 2, r - P / 2, P);                                // primary, :416-420
+		return true;
+	}
+	__device__ __forceinline__ int max_width() const { return full ? m : max(P, S); }
+};
+
+template <bool TB>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+k_dtw_generic(DtwLaunch L)
+{
+	extern __shared__ float smem_ring[];           // [kWarpsPerCta][3][kSmemRingCap]
+	const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+	const uint32_t gwarp = blockIdx.x * kWarpsPerCta + wid;
+	float *const my_smem = smem_ring + (size_t)wid * 3 * kSmemRingCap;
+	float *const my_gmem = L.ring_scratch ? L.ring_scratch + (size_t)gwarp * 3 * L.ring_cap : nullptr;
+
+	for (;;) {
+		uint32_t slot = 0;
+		if (lane == 0) slot = atomicAdd(L.work_counter, 1u);
+		slot = __shfl_sync(0xffffffffu, slot, 0);
+		if (slot >= L.n_items) break;
+		const uint32_t k = L.order ? L.order[slot] : slot;
+		const ra_dtw_item_t it = L.items[k];
+		const float *A = L.a_arena + it.a_off, *B = L.b_arena + it.b_off;
+		int n = (int)it.a_len, m = (int)it.b_len;
+		int band = TB ? -1 : it.band_radius;
+		if (!TB && n < m) { const float *t = A; A = B; B = t; int tl = n; n = m; m = tl; }   // dtw.cpp:284-292 (harmless for full)
+		if (n == 0 || m == 0) { if (lane == 0) { L.cost[k] = kInf; if (TB) L.path_len[k] = 0; } continue; }
+
+		DiagIter di; di.init(n, m, band);
+		const int width = di.max_width();
+		uint32_t cap = 1; while ((int)cap < width) cap <<= 1;
+		float *ring = (cap <= kSmemRingCap) ? my_smem : my_gmem;
+		if (cap <= kSmemRingCap) cap = kSmemRingCap;
+		else cap = L.ring_cap;
+		const uint32_t mask = cap - 1;
+		float *r0 = ring, *r1 = ring + cap, *r2 = ring + 2 * (size_t)cap;
+		int lo1 = 0, hi1 = -1, lo2 = 0, hi2 = -1;
+
+		uint32_t *dirs = nullptr; uint32_t dstride = 0;
+		if (TB) { dirs = L.dirs + L.dir_off[k]; dstride = ((uint32_t)m + 15u) >> 4; }
+
+		// diagonal 0: the corner
+		if (lane == 0) r0[0] = fabsf(__ldg(A) - __ldg(B));
+		__syncwarp();
+		int lo0 = 0, hi0 = 0;
+
+		while (true) {
+			// rotate r2 <- r1 <- r0 <- old r2
+			float *t = r2; r2 = r1; r1 = r0; r0 = t;
+			lo2 = lo1; hi2 = hi1; lo1 = lo0; hi1 = hi0;
+			if (!di.next()) break;
+			lo0 = di.lo; hi0 = di.hi;
+			const int d = di.d;
+			for (int jb = lo0 & ~31; jb <= hi0; jb += 32) {
+				const int j = jb + lane;
+				const bool act = (j >= lo0) && (j <= hi0);
+				uint32_t code = 0;
+				if (act) {
+					const int i = d - j;
+					// (i, j-1) and (i-1, j) on diagonal d-1; (i-1, j-1) on diagonal d-2
+					const float top = (j - 1 >= lo1 && j - 1 <= hi1) ? r1[(uint32_t)(j - 1) & mask] : kInf;
+					const float left = (j >= lo1 && j <= hi1) ? r1[(uint32_t)j & mask] : kInf;
+					const float tl = (j - 1 >= lo2 && j - 1 <= hi2) ? r2[(uint32_t)(j - 1) & mask] : kInf;
+					const float v = fminf(fminf(top, left), tl) + fabsf(__ldg(A + i) - __ldg(B + j));
+					r0[(uint32_t)j & mask] = v;
+					if (TB) {
+						// dtw.cpp:636-653 with left = dp[i-1][j], top = dp[i][j-1], topleft = dp[i-1][j-1]
+						if (left < fminf(top, tl)) code = 1u;           // i--
+						else if (top < fminf(left, tl)) code = 2u;      // j--
+						else code = 0u;                                 // i--, j--
+					}
+				}
+				if (TB) {
+					const uint32_t bits = act ? (code << (2 * (j & 15))) : 0u;
+					const uint32_t w_lo = __reduce_or_sync(0xffffffffu, lane < 16 ? bits : 0u);
+					const uint32_t w_hi = __reduce_or_sync(0xffffffffu, lane >= 16 ? bits : 0u);
+					const uint32_t wbase = (uint32_t)jb >> 4;
+					if (lane == 0 && wbase < dstride) dirs[(size_t)d * dstride + wbase] = w_lo;
+					if (lane == 16 && wbase + 1 < dstride) dirs[(size_t)d * dstride + wbase + 1] = w_hi;
+				}
+			}
+			__syncwarp();
+		}
+		// after the final rotation the last diagonal is r1
+		if (lane == 0) {
+			float res = r1[(uint32_t)(m - 1) & mask];
+			if (it.exclude_last) res -= fabsf(__ldg(A + n - 1) - __ldg(B + m - 1));   // dtw.cpp:514-516 / :60-62
+			L.cost[k] = res;
+		}
+		if (TB) {
+			__syncwarp();
+			if (lane == 0) {
+				// dtw.cpp:616-654; written back-to-front so the slot ends in forward order
+				const uint64_t so = L.slot_off[k];
+				const uint32_t capk = (uint32_t)n + (uint32_t)m - 1u;
+				uint32_t i = (uint32_t)n - 1u, j = (uint32_t)m - 1u, w = capk, len = 0;
+				for (;;) {
+					--w; ++len;
+					L.path_i[so + w] = i; L.path_j[so + w] = j;
+					if (L.path_diff) L.path_diff[so + w] = fabsf(__ldg(A + i) - __ldg(B + j));
+					if (i == 0 && j == 0) break;
+					if (i == 0) --j;
+					else if (j == 0) --i;
+					else {
+						const uint32_t word = __ldcg(dirs + (size_t)(i + j) * dstride + (j >> 4));   // L2 read: other lanes wrote it
+						const uint32_t code = (word >> (2 * (j & 15))) & 3u;
+						if (code == 1u) --i;
+						else if (code == 2u) --j;
+						else { --i; --j; }
+					}
+				}
+				L.path_len[k] = it.exclude_last ? len - 1u : len;         // dtw.cpp:659-663 drops the final element
+			}
+		}
+		__syncwarp();
+	}
+}
+
+// Copies each item's path from its (end-aligned) slot to the CSR output.
+__global__ void __launch_bounds__(256)
+k_path_compact(const uint32_t *__restrict__ slot_i, const uint32_t *__restrict__ slot_j, const float *__restrict__ slot_d,
+               const uint64_t *__restrict__ slot_off, const ra_dtw_item_t *__restrict__ items,
+               const uint32_t *__restrict__ path_len, const uint64_t *__restrict__ path_off, uint32_t n_items,
+               uint32_t *__restrict__ out_i, uint32_t *__restrict__ out_j, float *__restrict__ out_d)
+{
+	const uint32_t k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const int lane = threadIdx.x & 31;
+	if (k >= n_items) return;
+	const uint32_t len = path_len[k];
+	const uint32_t full_len = len + (items[k].exclude_last ? 1u : 0u);   // the slot still holds the dropped final element
+	const uint32_t capk = items[k].a_len + items[k].b_len - 1u;
+	const uint64_t src = slot_off[k] + (capk - full_len);
+	const uint64_t dst = path_off[k];
+	for (uint32_t t = lane; t < len; t += 32) {
+		out_i[dst + t] = slot_i[src + t];
+		out_j[dst + t] = slot_j[src + t];
+		if (out_d) out_d[dst + t] = slot_d[src + t];
+	}
+}
+
+cudaError_t launch_dtw_generic(const DtwLaunch &L, bool traceback, int n_sm, cudaStream_t s, int *n_launches)
+{
+	if (L.n_items == 0) return cudaSuccess;
+	cudaError_t e = cudaMemsetAsync(L.work_counter, 0, sizeof(uint32_t), s);
+	if (e != cudaSuccess) return e;
+	const size_t smem = (size_t)kWarpsPerCta * 3 * kSmemRingCap * sizeof(float);
+	static bool attr_done = false;
+	if (!attr_done) {
+		cudaFuncSetAttribute(k_dtw_generic<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		cudaFuncSetAttribute(k_dtw_generic<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		attr_done = true;
+	}
+	// persistent grid: 4 CTAs of 4 warps per SM (shared-memory bound), never more warps than problems
+	uint32_t ctas = (uint32_t)n_sm * 4u;
+	const uint32_t need = (L.n_items + kWarpsPerCta - 1) / kWarpsPerCta;
+	if (ctas > need) ctas = need;
+	if (traceback) k_dtw_generic<true><<<ctas, kWarpsPerCta * 32, smem, s>>>(L);
+	else k_dtw_generic<false><<<ctas, kWarpsPerCta * 32, smem, s>>>(L);
+	if (n_launches) *n_launches += 1;
+	return cudaGetLastError();
+}
+
+cudaError_t launch_path_compact(const uint32_t *slot_i, const uint32_t *slot_j, const float *slot_d,
+                                const uint64_t *slot_off, const ra_dtw_item_t *items, const uint32_t *path_len,
+                                const uint64_t *path_off, uint32_t n_items, uint32_t *out_i, uint32_t *out_j,
+                                float *out_d, cudaStream_t s)
+{
+	if (n_items == 0) return cudaSuccess;
+	const int threads = 256;
+	const unsigned blocks = (unsigned)(((uint64_t)n_items * 32 + threads - 1) / threads);
+	k_path_compact<<<blocks, threads, 0, s>>>(slot_i, slot_j, slot_d, slot_off, items, path_len, path_off, n_items, out_i, out_j, out_d);
+	return cudaGetLastError();
+}
+
+} // namespace ra

@@ -1,0 +1,289 @@
+"""GPU (-m gpu): the CUDA path through the C ABI against the oracle and the committed reference
+fixtures.  Everything is asserted BIT-EXACT (integer compare of the float bit patterns)."""
+import numpy as np
+import pytest
+
+from conftest import bits, unpack
+
+pytestmark = pytest.mark.gpu
+
+
+def _items(ra, a_lens, b_lens, R, ex):
+    a_off = np.concatenate(([0], np.cumsum(a_lens)[:-1])); b_off = np.concatenate(([0], np.cumsum(b_lens)[:-1]))
+    return ra.make_items(a_off, b_off, a_lens, b_lens, R, ex)
+
+
+def test_extension_is_loaded(ctx):
+    import os
+    import rawalign_b200 as ra
+    maps = open("/proc/self/maps").read()
+    assert os.path.basename(ra.LIB_PATH) in maps, "native library not loaded"
+
+
+# ---- K1 ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("contract,key", [(1, "ev_fma"), (0, "ev_nofma")])
+def test_events_golden(ctx, event_golden, contract, key):
+    import rawalign_b200 as ra
+    g = event_golden
+    opt = ra.ri_mapopt_init(); opt.fp_contract = contract
+    ctx.set_opt(opt)
+    try:
+        n = len(g["sig_off"]) - 1
+        # pad every chunk start to 16 bytes and also run an unaligned layout
+        for pad in (4, 1):
+            lens = np.diff(g["sig_off"]).astype(np.uint32)
+            starts = np.zeros(n, np.uint64); pos = 3 if pad == 1 else 0
+            for k in range(n):
+                starts[k] = pos; pos += int(lens[k]); pos = (pos + pad - 1) // pad * pad
+            sig = np.zeros(pos + 8, np.float32)
+            for k in range(n):
+                sig[int(starts[k]):int(starts[k]) + int(lens[k])] = unpack(g["sig"], g["sig_off"], k)
+            ev, off = ctx.detect_events_batch(sig, starts, lens)
+            assert np.array_equal(off.astype(np.int64), g[key + "_off"]), "event counts differ"
+            assert np.array_equal(bits(ev), bits(g[key])), "event values differ"
+    finally:
+        ctx.set_opt(ra.ri_mapopt_init())
+
+
+def test_events_vs_oracle_simulated_reads(ctx, oracle):
+    from rawalign_b200 import synth
+    ref = synth.random_reference(200_000, seed=1)
+    reads = synth.simulate_reads(ref, 96, seed=21, max_chunks=8)
+    coff, clen, _ = synth.chunk_table(reads.read_off, reads.read_len, max_chunks=8)
+    ev, off = ctx.detect_events_batch(reads.sig, coff, clen)
+    ev_o, off_o = oracle.detect_events_batch(reads.sig, coff, clen)
+    assert np.array_equal(off, off_o)
+    assert np.array_equal(bits(ev), bits(ev_o))
+    per_chunk = np.diff(off.astype(np.int64))
+    assert per_chunk[clen == 4000].mean() > 300       # pore-model-like signal: ~400-600 events per 4000 samples
+
+
+def test_events_single_call_and_empty(ctx, oracle):
+    rng = np.random.default_rng(4)
+    s = np.clip(rng.normal(90, 13, 4000), 31, 199).astype(np.float32)
+    assert np.array_equal(bits(ctx.detect_events(s)), bits(oracle.detect_events(s)))
+    assert len(ctx.detect_events(np.full(7, 80.0, np.float32))) == 0
+    ev, off = ctx.detect_events_batch(np.zeros(4, np.float32), np.zeros(0, np.uint64), np.zeros(0, np.uint32))
+    assert len(ev) == 0 and off[0] == 0
+
+
+def test_events_unsupported_windows_fail_loudly(ctx):
+    import rawalign_b200 as ra
+    opt = ra.ri_mapopt_init(); opt.window_length1 = 4; opt.window_length2 = 9
+    ctx.set_opt(opt)
+    try:
+        with pytest.raises(ra.RawAlignError) as e:
+            ctx.detect_events(np.zeros(100, np.float32))
+        assert e.value.code == -5
+    finally:
+        ctx.set_opt(ra.ri_mapopt_init())
+
+
+# ---- K2 / K3 ------------------------------------------------------------------------------------------
+def test_dtw_golden_banded_and_full(ctx, dtw_golden):
+    import rawalign_b200 as ra
+    g = dtw_golden
+    n = len(g["band_radius"])
+    a_len = np.diff(g["a_off"]); b_len = np.diff(g["b_off"])
+    it = ra.make_items(g["a_off"][:-1], g["b_off"][:-1], a_len, b_len, g["band_radius"], g["exclude_last"])
+    cost = ctx.dtw_batch(g["a"], g["b"], it)
+    assert np.array_equal(bits(cost), bits(g["banded_cost"]))
+    it["band_radius"] = -1
+    cost = ctx.dtw_batch(g["a"], g["b"], it)
+    assert np.array_equal(bits(cost), bits(g["full_cost"]))
+    assert n > 1000
+
+
+def test_dtw_vs_oracle_random_and_wide(ctx, oracle):
+    import rawalign_b200 as ra
+    rng = np.random.default_rng(31)
+    shapes = [(int(rng.integers(1, 700)), int(rng.integers(1, 700)), int(rng.integers(0, 80))) for _ in range(300)]
+    shapes += [(5000, 5200, 500), (12000, 11000, 1200), (2, 9000, 1), (9000, 3, 900), (3000, 3000, -1), (1, 1, 1), (1, 1, -1)]
+    a_lens = np.array([s[0] for s in shapes]); b_lens = np.array([s[1] for s in shapes])
+    R = np.array([s[2] for s in shapes]); ex = rng.integers(0, 2, len(shapes))
+    A = rng.normal(0, 1, int(a_lens.sum())).astype(np.float32); B = rng.normal(0, 1, int(b_lens.sum())).astype(np.float32)
+    it = _items(ra, a_lens, b_lens, R, ex)
+    cost = ctx.dtw_batch(A, B, it)
+    want = oracle.dtw_batch(A, B, it)
+    assert np.array_equal(bits(cost), bits(want))
+
+
+def test_dtw_sparse_like_stream(ctx, oracle):
+    """1e5 tiny anchor-to-anchor problems (a_len, b_len ~ 2+Geom(0.2), R = 1), overlapping spans."""
+    import rawalign_b200 as ra
+    rng = np.random.default_rng(32)
+    n = 100_000
+    a_lens = 1 + rng.geometric(0.2, n); b_lens = 1 + rng.geometric(0.2, n)
+    A = rng.normal(0, 1, 50_000).astype(np.float32); B = rng.normal(0, 1, 80_000).astype(np.float32)
+    a_off = rng.integers(0, len(A) - a_lens.max(), n); b_off = rng.integers(0, len(B) - b_lens.max(), n)
+    it = ra.make_items(a_off, b_off, a_lens, b_lens, np.maximum(1, (a_lens * 0.1).astype(int)), rng.integers(0, 2, n))
+    cost = ctx.dtw_batch(A, B, it)
+    assert np.array_equal(bits(cost), bits(oracle.dtw_batch(A, B, it)))
+
+
+def test_dtw_properties_at_full_size(ctx):
+    """Size-independent properties on a batch too large for the oracle: identical spans cost 0;
+    a band that covers the matrix equals the full matrix; cost is symmetric in (a, b)."""
+    import rawalign_b200 as ra
+    rng = np.random.default_rng(33)
+    n = 4000
+    a_lens = rng.integers(300, 900, n); b_lens = rng.integers(300, 900, n)
+    A = rng.normal(0, 1, int(a_lens.sum())).astype(np.float32); B = rng.normal(0, 1, int(b_lens.sum())).astype(np.float32)
+    it = _items(ra, a_lens, b_lens, 2 * np.maximum(a_lens, b_lens), np.zeros(n, int))
+    wide = ctx.dtw_batch(A, B, it)
+    it["band_radius"] = -1
+    full = ctx.dtw_batch(A, B, it)
+    assert np.array_equal(bits(wide), bits(full))
+    sw = it.copy(); sw["a_off"], sw["b_off"] = it["b_off"], it["a_off"]; sw["a_len"], sw["b_len"] = it["b_len"], it["a_len"]
+    assert np.array_equal(bits(ctx.dtw_batch(B, A, sw)), bits(full))
+    same = ra.make_items(it["a_off"], it["a_off"], a_lens, a_lens, np.maximum(1, (a_lens * 0.1).astype(int)), np.zeros(n, int))
+    assert np.all(ctx.dtw_batch(A, A, same) == 0.0)
+
+
+def test_dtw_rejects_bad_items(ctx):
+    import rawalign_b200 as ra
+    A = np.zeros(10, np.float32)
+    with pytest.raises(ra.RawAlignError):
+        ctx.dtw_batch(A, A, ra.make_items([0], [0], [0], [5], [1], [0]))
+    with pytest.raises(ra.RawAlignError):
+        ctx.dtw_batch(A, A, ra.make_items([8], [0], [5], [5], [1], [0]))
+    with pytest.raises(ValueError):
+        ctx.DTW_global_slantedbanded_antidiagonalwise(A, A, -1)
+
+
+def test_reference_named_single_calls(ctx, oracle):
+    rng = np.random.default_rng(34)
+    a = rng.normal(size=120).astype(np.float32); b = rng.normal(size=100).astype(np.float32)
+    assert bits(ctx.DTW_global(a, b)) == bits(oracle.dtw_global(a, b))
+    assert bits(ctx.DTW_global(a, b, True)) == bits(oracle.dtw_global(a, b, True))
+    assert bits(ctx.DTW_global_slantedbanded_antidiagonalwise(a, b, 12)) == bits(oracle.dtw_banded(a, b, 12))
+    c, pi, pj, pd = ctx.DTW_global_tb(a, b)
+    c2, i2, j2, d2 = oracle.dtw_global_tb(a, b)
+    assert bits(c) == bits(c2) and np.array_equal(pi, i2) and np.array_equal(pj, j2) and np.array_equal(bits(pd), bits(d2))
+
+
+# ---- K4 -----------------------------------------------------------------------------------------------
+def test_traceback_golden(ctx, dtw_golden):
+    import rawalign_b200 as ra
+    g = dtw_golden
+    idx = g["tb_idx"]
+    a_len = np.diff(g["a_off"])[idx]; b_len = np.diff(g["b_off"])[idx]
+    it = ra.make_items(g["a_off"][:-1][idx], g["b_off"][:-1][idx], a_len, b_len, -np.ones(len(idx), int), g["exclude_last"][idx])
+    cost, pi, pj, pd, off = ctx.dtw_tb_batch(g["a"], g["b"], it)
+    assert np.array_equal(bits(cost), bits(g["tb_cost"]))
+    assert np.array_equal(off.astype(np.int64), g["tb_off"])
+    assert np.array_equal(pi, g["tb_i"]) and np.array_equal(pj, g["tb_j"])
+    assert np.array_equal(bits(pd), bits(g["tb_diff"]))
+
+
+def test_traceback_large_and_ties(ctx, oracle):
+    import rawalign_b200 as ra
+    rng = np.random.default_rng(35)
+    # quantised values create many exact ties: the tie rule (diagonal wins, dtw.cpp:636-653) must match
+    shapes = [(1500, 1400), (700, 2100), (33, 17), (1, 40), (40, 1), (1, 1), (260, 260)]
+    a_lens = np.array([s[0] for s in shapes]); b_lens = np.array([s[1] for s in shapes])
+    A = (rng.integers(-3, 4, int(a_lens.sum())) * 0.5).astype(np.float32); B = (rng.integers(-3, 4, int(b_lens.sum())) * 0.5).astype(np.float32)
+    it = _items(ra, a_lens, b_lens, -np.ones(len(shapes), int), np.array([0, 0, 1, 0, 1, 0, 0]))
+    cost, pi, pj, pd, off = ctx.dtw_tb_batch(A, B, it)
+    for k in range(len(shapes)):
+        a = A[int(it["a_off"][k]):int(it["a_off"][k]) + a_lens[k]]; b = B[int(it["b_off"][k]):int(it["b_off"][k]) + b_lens[k]]
+        c2, i2, j2, d2 = oracle.dtw_global_tb(a, b, bool(it["exclude_last"][k]))
+        s, e = int(off[k]), int(off[k + 1])
+        assert bits(cost[k]) == bits(c2), k
+        assert np.array_equal(pi[s:e], i2) and np.array_equal(pj[s:e], j2), k
+        assert np.array_equal(bits(pd[s:e]), bits(d2)), k
+
+
+# ---- chain level --------------------------------------------------------------------------------------
+def _workload(n_reads=40, seed=41):
+    from rawalign_b200 import synth
+    rng = np.random.default_rng(seed)
+    n_ev = rng.integers(100, 2500, n_reads)
+    ev_off = np.concatenate(([0], np.cumsum(n_ev)))
+    read = rng.normal(0, 1, int(ev_off[-1])).astype(np.float32)
+    ref = rng.normal(0, 1, 200_000).astype(np.float32)
+    anchors, chains = synth.synth_chains(n_ev, ev_off[:-1], len(ref), seed=seed + 1, chains_per_read=4)
+    # make the first chain of each read a true match so scores pass dtw_min_score and the running threshold bites
+    for g in np.unique(chains["group"]):
+        ch = chains[chains["group"] == g][0]
+        a = anchors[int(ch["anchor_off"]):int(ch["anchor_off"]) + int(ch["n_anchors"])]
+        q0, q1 = int(a["query_position"][-1]), int(a["query_position"][0])
+        t0, t1 = int(a["target_position"][-1]), int(a["target_position"][0])
+        seg = read[int(ch["read_off"]) + q0:int(ch["read_off"]) + q1 + 1]
+        ref[t0:t1 + 1] = np.interp(np.linspace(0, len(seg) - 1, t1 - t0 + 1), np.arange(len(seg)), seg) + rng.normal(0, 0.1, t1 - t0 + 1)
+    return read, ref.astype(np.float32), anchors, chains
+
+
+@pytest.mark.parametrize("border,fill", [(1, 1), (1, 0), (0, 1), (0, 0)])
+def test_align_chains_batch_vs_oracle(ctx, oracle, border, fill):
+    import rawalign_b200 as ra
+    from oracle import DtwOpt
+    read, ref, anchors, chains = _workload()
+    opt = ra.ri_mapopt_init(); opt.dtw_border_constraint = border; opt.dtw_fill_method = fill
+    ctx.set_opt(opt)
+    try:
+        score, keep, issued, useful = ctx.align_chains_batch(read, ref, anchors, chains, min_score_mode=1)
+    finally:
+        ctx.set_opt(ra.ri_mapopt_init())
+    oo = DtwOpt(border, fill, 0.10, 0.4, 20.0)
+    best, grp, useful_o, dropped = 0.0, None, 0, 0
+    for k, ch in enumerate(chains):
+        if grp != ch["group"]:
+            best, grp = 0.0, ch["group"]
+        a = anchors[int(ch["anchor_off"]):int(ch["anchor_off"]) + int(ch["n_anchors"])]
+        s, cells = oracle.align_chain(a, read[int(ch["read_off"]):], ref, oo, min_score=best, score_fma=1, return_cells=True)
+        useful_o += cells
+        assert bits(score[k]) == bits(s), (k, score[k], s)
+        assert bool(keep[k]) == bool(s >= np.float32(20.0))
+        dropped += s == np.float32(-1e10)
+        if s >= np.float32(20.0) and s > best:
+            best = float(s)
+    assert useful == useful_o and issued >= useful
+    assert keep.sum() >= len(np.unique(chains["group"])) // 2
+    if border == 1:
+        assert dropped > 0, "the early-termination replay was never exercised"
+
+
+def test_align_chain_cigar_vs_oracle(ctx, oracle):
+    import rawalign_b200 as ra
+    read, ref, anchors, chains = _workload(n_reads=6, seed=43)
+    chains = chains[::4]
+    for border in (1, 0):
+        opt = ra.ri_mapopt_init(); opt.dtw_border_constraint = border; opt.dtw_fill_method = 0
+        ctx.set_opt(opt)
+        try:
+            score, cost, pi, pj, pd, off = ctx.align_chains_cigar_batch(read, ref, anchors, chains)
+        finally:
+            ctx.set_opt(ra.ri_mapopt_init())
+        for k, ch in enumerate(chains):
+            a = anchors[int(ch["anchor_off"]):int(ch["anchor_off"]) + int(ch["n_anchors"])]
+            rd = read[int(ch["read_off"]):]
+            wi, wj, wd, c_tot, n_al = [], [], [], np.float32(0), 0
+            if border == 1:                                  # rmap.cpp:282-292
+                parts = len(a) - 1
+                for p in range(parts):
+                    s, e = a[parts - p], a[parts - p - 1]
+                    c, i2, j2, d2 = oracle.dtw_global_tb(rd[s["query_position"]:e["query_position"] + 1], ref[s["target_position"]:e["target_position"] + 1])
+                    wi.append(i2.astype(np.uint64) + int(s["query_position"])); wj.append(j2.astype(np.uint64) + int(s["target_position"])); wd.append(d2)
+                    c_tot = np.float32(c_tot + c); n_al += int(e["query_position"]) - int(s["query_position"]) + 1
+            else:                                            # rmap.cpp:218-235 (offset applied to back() only, n times)
+                s, e = a[-1], a[0]
+                c, i2, j2, d2 = oracle.dtw_global_tb(rd[s["query_position"]:e["query_position"] + 1], ref[s["target_position"]:e["target_position"] + 1])
+                i2 = i2.astype(np.uint64); j2 = j2.astype(np.uint64)
+                i2[-1] += len(i2) * int(s["query_position"]); j2[-1] += len(j2) * int(s["target_position"])
+                wi, wj, wd = [i2], [j2], [d2]; c_tot = c; n_al = int(e["query_position"]) - int(s["query_position"]) + 1
+            wi, wj, wd = np.concatenate(wi), np.concatenate(wj), np.concatenate(wd)
+            s0, e0 = int(off[k]), int(off[k + 1])
+            assert np.array_equal(pi[s0:e0], wi) and np.array_equal(pj[s0:e0], wj) and np.array_equal(bits(pd[s0:e0]), bits(wd))
+            assert bits(cost[k]) == bits(c_tot)
+            # fused n*bonus - cost (rmap.cpp:306 as built): the float64 product of two float32 is exact
+            want = np.float32(np.float64(np.float32(n_al)) * np.float64(np.float32(0.4)) - np.float64(c_tot))
+            assert bits(score[k]) == bits(want)
+    opt = ra.ri_mapopt_init(); opt.dtw_border_constraint = 0; opt.dtw_fill_method = 1
+    ctx.set_opt(opt)
+    try:
+        with pytest.raises(ra.RawAlignError) as e:
+            ctx.align_chains_cigar_batch(read, ref, anchors, chains)
+        assert e.value.code == -5
+    finally:
+        ctx.set_opt(ra.ri_mapopt_init())
