@@ -54,25 +54,46 @@ def build_reads(ref, n_reads, seed):
     return reads, coff, clen, crid
 
 
-def build_chains(ev_off, crid, n_reads, ref_len, seed):
-    """Chains of every chunk round of every read.  Round c of a read sees the events of chunks 0..c
-    (they are contiguous in the CSR event arena because chunks of a read are consecutive)."""
-    from rawalign_b200 import synth
+def build_chains(ev_off, ev_pos, coff, crid, reads, n_reads, ref_len, seed):
+    """Chains of every chunk round of every read.  Round c of a read sees the events of chunks 0..c (contiguous in
+    the CSR event arena because chunks of a read are consecutive).  Per round: the true chain (anchors placed from the
+    simulator's ground truth, as exact seed hits would be) followed by CHAINS_PER_ROUND-1 decoys at random positions,
+    i.e. the reference's evaluation order, best chaining score first."""
+    from rawalign_b200 import CHAIN_DTYPE, synth
+    rng = np.random.default_rng(seed)
     per_chunk = np.diff(ev_off.astype(np.int64))
     first_chunk = np.searchsorted(crid, np.arange(n_reads), "left")
     last_chunk = np.searchsorted(crid, np.arange(n_reads), "right")
+    half = ref_len + 6 - 5                                  # strand-1 signal follows strand-0 in the arena (len = bases-5 each)
     anchors, chains = [], []
     a_base = 0
     for rnd in range(MAX_CHUNKS):
-        has = (last_chunk - first_chunk) > rnd
-        n_ev = np.zeros(n_reads, np.int64)
-        for r in np.nonzero(has)[0]:
-            n_ev[r] = per_chunk[first_chunk[r]:first_chunk[r] + rnd + 1].sum()
-        a, c = synth.synth_chains(n_ev, ev_off[first_chunk.clip(max=len(ev_off) - 2)], ref_len, seed=seed * 100 + rnd,
-                                  chains_per_read=CHAINS_PER_ROUND)
-        if len(c):
-            c = c.copy(); c["anchor_off"] += a_base; c["group"] = c["group"] * MAX_CHUNKS + rnd
-            a_base += len(a); anchors.append(a); chains.append(c)
+        for r in range(n_reads):
+            nch = last_chunk[r] - first_chunk[r]
+            if nch <= rnd:
+                continue
+            c0 = first_chunk[r]
+            e0 = int(ev_off[c0]); e1 = int(ev_off[c0 + rnd + 1])
+            ne = e1 - e0
+            if ne < 60:
+                continue
+            # sample position of every event within the read
+            chunk_of = np.repeat(np.arange(rnd + 1), per_chunk[c0:c0 + rnd + 1])
+            spos = ev_pos[e0:e1].astype(np.int64) + chunk_of * synth.CHUNK_SIZE
+            ref_off = 0 if reads.strand[r] == 0 else half
+            grp = []
+            a = synth.truth_chain(spos, reads.base_start[r], int(reads.ref_start[r]), rng)
+            if a is not None:
+                grp.append((a, ref_off))
+            da, dc = synth.synth_chains(np.array([ne]), np.array([e0], np.uint64), ref_len - 8, seed=int(rng.integers(1 << 30)),
+                                        chains_per_read=CHAINS_PER_ROUND)
+            for ch in dc[1:]:
+                grp.append((da[int(ch["anchor_off"]):int(ch["anchor_off"]) + int(ch["n_anchors"])], int(rng.integers(0, 2)) * half))
+            for a, roff in grp:
+                ch = np.zeros(1, CHAIN_DTYPE)
+                ch["anchor_off"] = a_base; ch["n_anchors"] = len(a); ch["group"] = r * MAX_CHUNKS + rnd
+                ch["read_off"] = e0; ch["ref_off"] = roff
+                anchors.append(a); chains.append(ch); a_base += len(a)
     return np.concatenate(anchors), np.concatenate(chains)
 
 
@@ -239,35 +260,47 @@ def main():
     sig_pinned = torch.from_numpy(reads.sig).pin_memory()
     coff_p = torch.from_numpy(coff.view(np.int64)).pin_memory(); clen_p = torch.from_numpy(clen.view(np.int32)).pin_memory()
     sig_d = sig_pinned.to(dev); coff_d = coff_p.to(dev); clen_d = clen_p.to(dev)
-    ev_cap = int(clen.sum())
-    ev_d = torch.empty(ev_cap // 2 + 16, dtype=torch.float32, device=dev)
+    ev_cap = int(clen.sum()) // 2 + n_chunks + 16
+    ev_d = torch.empty(ev_cap, dtype=torch.float32, device=dev)
     evoff_d = torch.empty(n_chunks + 1, dtype=torch.int64, device=dev)
+    max_len = int(clen.max())
     torch.cuda.synchronize()
-    n_events = ctx.detect_events_batch_dev(sig_d.data_ptr(), coff_d.data_ptr(), clen_d.data_ptr(), n_chunks, int(clen.max()),
+
+    def k1_dev():
+        return ctx.detect_events_batch_dev(sig_d.data_ptr(), coff_d.data_ptr(), clen_d.data_ptr(), n_chunks, max_len,
                                            ev_d.data_ptr(), ev_d.numel(), evoff_d.data_ptr())
+    n_events = k1_dev()
     ev_off = evoff_d.cpu().numpy().view(np.uint64)
-    anchors, chains = build_chains(ev_off, crid, args.reads_per_gpu, REF_BASES - 6, seed=3 + rank)
-    items, chain_of = chains_to_items(anchors, chains, return_chain_of=True)
-    cells = int(item_cells(items).sum())
-    items_p = torch.from_numpy(items.view(np.uint8).reshape(-1)).pin_memory()
-    items_d = items_p.to(dev)
-    cost_d = torch.empty(len(items), dtype=torch.float32, device=dev)
+    ev_pos = ctx.last_event_positions(n_events)
+    anchors, chains = build_chains(ev_off, ev_pos, coff, crid, reads, args.reads_per_gpu, REF_BASES - 6, seed=3 + rank)
+    gfirst = np.concatenate((np.nonzero(np.concatenate(([True], chains["group"][1:] != chains["group"][:-1])))[0], [len(chains)])).astype(np.uint32)
+    n_groups = len(gfirst) - 1
+    # pinned host copies (the e2e path copies from these every step) and device-resident copies (the `value` path)
+    anchors_p = torch.from_numpy(anchors.view(np.uint8).reshape(-1)).pin_memory()
+    chains_p = torch.from_numpy(chains.view(np.uint8).reshape(-1)).pin_memory()
+    anchors_d = anchors_p.to(dev); chains_d = chains_p.to(dev); gfirst_d = torch.from_numpy(gfirst.view(np.int32)).to(dev)
+    score_d = torch.empty(len(chains), dtype=torch.float32, device=dev); keep_d = torch.empty(len(chains), dtype=torch.uint8, device=dev)
+    anchors_h = anchors_p.numpy().view(anchors.dtype); chains_h = chains_p.numpy().view(chains.dtype)
+    n_parts = int((chains["n_anchors"].astype(np.int64) - 1).sum())
     n_samples = int(clen.sum())
+
+    def k2_dev():
+        return ctx.align_chains_batch_dev(ev_d.data_ptr(), None, anchors_d.data_ptr(), chains_d.data_ptr(), gfirst_d.data_ptr(),
+                                          n_groups, score_d.data_ptr(), keep_d.data_ptr(), min_score_mode=1)
+    cells_issued, cells_useful = k2_dev()
     log(f"[rank {rank}] setup {time.time() - t_setup:.1f}s: reads={args.reads_per_gpu} chunks={n_chunks} samples={n_samples} "
-        f"events={n_events} chains={len(chains)} sub-DTWs={len(items)} cells={cells}")
+        f"events={n_events} chains={len(chains)} groups={n_groups} sub-DTWs={n_parts} cells issued={cells_issued} useful={cells_useful}")
 
-    def step_device():
-        ctx.detect_events_batch_dev(sig_d.data_ptr(), coff_d.data_ptr(), clen_d.data_ptr(), n_chunks, int(clen.max()),
-                                    ev_d.data_ptr(), ev_d.numel(), evoff_d.data_ptr())
-        ctx.dtw_batch_dev(ev_d.data_ptr(), None, items_d.data_ptr(), items, cost_d.data_ptr())
-
-    ev_host = np.empty(ev_cap, np.float32); evoff_host = np.empty(n_chunks + 1, np.uint64)
-    score_holder = {}
+    ev_host = torch.empty(ev_cap, dtype=torch.float32).pin_memory().numpy(); evoff_host = np.empty(n_chunks + 1, np.uint64)
+    sig_h = sig_pinned.numpy()
+    e2e_out = {}
 
     def step_e2e():
-        ev, off = ctx.detect_events_batch(sig_pinned.numpy(), coff, clen, ev_host, evoff_host)
-        s, keep, _, _ = ctx.align_chains_batch(ev, None, anchors, chains, min_score_mode=1)
-        score_holder["s"] = s
+        # host signal -> device, K1, events back to the host (the map loop seeds from them), anchors/chains -> device,
+        # chain evaluation against the events that stayed on the device, scores back
+        ev, off = ctx.detect_events_batch(sig_h, coff, clen, ev_host, evoff_host)
+        s, keep, _, _ = ctx.align_chains_batch(None, None, anchors_h, chains_h, min_score_mode=1)
+        e2e_out["score"] = s; e2e_out["n_ev"] = len(ev)
 
     def barrier():
         torch.cuda.synchronize()
@@ -277,21 +310,16 @@ def main():
 
     # ---- device-resident timing ----
     for _ in range(args.warmup):
-        step_device()
+        k1_dev(); k2_dev()
     barrier()
     sampler = ClockSampler(local); sampler.start()
     l0 = ctx.launch_count
     t0 = time.perf_counter()
-    ev_ms, dtw_ms, scan_ms = [], [], []
+    ev_ms, dtw_ms, det_ms = [], [], []
     for _ in range(args.steps):
-        ta = time.perf_counter()
-        ctx.detect_events_batch_dev(sig_d.data_ptr(), coff_d.data_ptr(), clen_d.data_ptr(), n_chunks, int(clen.max()),
-                                    ev_d.data_ptr(), ev_d.numel(), evoff_d.data_ptr())
-        tb = time.perf_counter()
-        ctx.dtw_batch_dev(ev_d.data_ptr(), None, items_d.data_ptr(), items, cost_d.data_ptr())
-        tc = time.perf_counter()
+        k1_dev(); k2_dev()
         tm = ctx.last_timing()
-        ev_ms.append(tm[1]); dtw_ms.append(tm[2]); scan_ms.append(tm[0])
+        det_ms.append(tm[0]); ev_ms.append(tm[1]); dtw_ms.append(tm[2])
     barrier()
     dt = time.perf_counter() - t0
     launches = ctx.launch_count - l0
@@ -310,7 +338,7 @@ def main():
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     dt, dt_e2e = float(tt[0]), float(tt[1])
-    tot = torch.tensor([args.reads_per_gpu, cells, n_samples, n_events], dtype=torch.float64, device=dev)
+    tot = torch.tensor([args.reads_per_gpu, cells_issued, n_samples, n_events], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tot)
     reads_all, cells_all, samples_all, events_all = [float(x) for x in tot]
@@ -321,48 +349,69 @@ def main():
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
-        hbm_peak = float(peaks.get("hbm_gbs", 6650.0)); peak_src = "measured" if peaks else "fallback"
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0)); peak_src = "measured (MEASURED_PEAKS.json)" if peaks else "fallback"
         ms_step = dt / args.steps * 1e3
-        k1_ms = float(np.median(scan_ms)); k1_all_ms = float(np.median(ev_ms)); k2_ms = float(np.median(dtw_ms))
-        k1_bytes = 4.0 * n_samples + 4.0 * n_events + 8.0 * n_chunks
-        sm_clk = (clocks.get("sm_mhz") or 1965.0) * 1e6
+        k1_ms = float(np.median(ev_ms)); k2_ms = float(np.median(dtw_ms))
+        k1_bytes = 4.0 * n_samples + 4.0 * n_events + 8.0 * n_chunks + 12.0 * n_chunks
         alu_peak_gcups = 148 * 128 * 1965.0e6 / 4 / 1e9
         out = {
             "metric": "reads_per_s", "value": reads_all * args.steps / dt, "unit": "reads/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
-            "dtw_gcups": cells / (k2_ms * 1e-3) / 1e9, "hot_path_gcups": cells_all * args.steps / dt / 1e9,
-            "stages_ms": {"events_scan_kernel": k1_ms, "events_all_kernels": k1_all_ms, "dtw_kernels": k2_ms,
-                          "timing": "CUDA events on the library stream"},
+            "dtw_gcups": cells_issued / (k2_ms * 1e-3) / 1e9, "hot_path_gcups": cells_all * args.steps / dt / 1e9,
+            "cells_per_step": {"issued": cells_issued, "useful": cells_useful},
+            "stages_ms": {"events_5_kernels": k1_ms, "events_detect_3_kernels": float(np.median(det_ms)), "chain_dtw_kernel": k2_ms,
+                          "timing": "CUDA events on the library stream, median over the timed steps"},
             "e2e": {"value": reads_all * args.steps / dt_e2e, "unit": "reads/s", "ms_per_step": dt_e2e / args.steps * 1e3,
-                    "h2d_bytes_per_step": int(reads.sig.nbytes + coff.nbytes + clen.nbytes + anchors.nbytes + chains.nbytes),
-                    "d2h_bytes_per_step": int(4 * n_events + 8 * (n_chunks + 1) + 4 * len(chains))},
+                    "h2d_bytes_per_step": int(reads.sig.nbytes + coff.nbytes + clen.nbytes + anchors.nbytes + chains.nbytes + gfirst.nbytes),
+                    "d2h_bytes_per_step": int(4 * n_events + 8 * (n_chunks + 1) + 5 * len(chains))},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"kernel": "k_events_scan", "bound": "hbm", "achieved": k1_bytes / (k1_ms * 1e-3) / 1e9, "peak": hbm_peak,
-                         "unit": "GB/s", "frac": k1_bytes / (k1_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None, "peak_source": peak_src},
-            "roofline_dtw": {"kernel": "k_dtw", "bound": "alu", "achieved": cells / (k2_ms * 1e-3) / 1e9, "peak": alu_peak_gcups,
-                             "unit": "GCUPS", "frac": cells / (k2_ms * 1e-3) / 1e9 / alu_peak_gcups,
-                             "peak_source": "148 SMs x 128 lanes x 1.965 GHz / 4 ops per cell"},
+            "roofline": {"kernel": "K1 event detection (k_prefix+k_tstat+k_peaks+k_scan+k_finish)", "bound": "hbm",
+                         "achieved": k1_bytes / (k1_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": k1_bytes / (k1_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes": "4 B/sample in + 4 B/event out + 20 B/chunk of tables"},
+            "roofline_dtw": {"kernel": "k_chain_eval", "bound": "alu", "achieved": cells_issued / (k2_ms * 1e-3) / 1e9, "peak": alu_peak_gcups,
+                             "unit": "GCUPS", "frac": cells_issued / (k2_ms * 1e-3) / 1e9 / alu_peak_gcups,
+                             "peak_source": "148 SMs x 128 fp32 lanes x 1.965 GHz / 4 lane-ops per cell (SURVEY 8d)"},
         }
         if not args.no_cpu_baseline:
             be, kind = cpu_backend()
             nsub = min(args.cpu_sample_reads, args.reads_per_gpu)
             c_off, c_len, a_sub, ch_sub = subset_reads(nsub, crid, coff, clen, anchors, chains)
-            # chains reference events by arena offset of the full batch: CPU leg recomputes events for the subset, whose
-            # chunks are the first ones of the batch, so offsets agree
+            # chains address events by their offset in the batch's event arena; the subset's chunks are the first chunks of
+            # the batch, so the CPU leg's events land at the same offsets
             t_cpu, t_ev, t_dtw, n_ev_cpu, costs = cpu_step(be, reads.sig, c_off, c_len, a_sub, ch_sub, ref_arena, 1)
             out["cpu_baseline"] = {"value": nsub / t_cpu, "unit": "reads/s", "cores": 1, "kind": kind,
                                    "sample": f"first {nsub} reads of the batch, one pass, single thread (events {t_ev:.2f}s + dtw {t_dtw:.2f}s)"}
-            # parity spot check of the timed configuration: GPU costs of the subset == CPU costs
-            sub_mask = ((chains["group"] // MAX_CHUNKS) < nsub)[chain_of]
-            got = cost_d.cpu().numpy()[sub_mask]
-            out["cpu_baseline"]["parity_bit_exact"] = bool(np.array_equal(got.view(np.uint32), costs.view(np.uint32)))
+            # parity spot check of the timed configuration: GPU chain scores of the sample == the oracle's align_chain replay
+            out["cpu_baseline"]["parity_bit_exact"] = bool(parity_check(ch_sub, anchors, ev_d, n_events, ref_arena, score_d, chains))
         print(json.dumps(out), flush=True)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def parity_check(ch_sub, anchors, ev_d, n_events, ref_arena, score_d, chains):
+    from oracle import DtwOpt, Oracle
+    orc = Oracle()
+    ev = ev_d[:n_events].cpu().numpy()
+    score = score_d.cpu().numpy()
+    sel = np.nonzero((chains["group"] // MAX_CHUNKS) < 4)[0]          # chains of the first 4 reads, all rounds
+    oo = DtwOpt.default()
+    best, grp = 0.0, None
+    for k in sel:
+        ch = chains[k]
+        if grp != ch["group"]:
+            best, grp = 0.0, ch["group"]
+        a = anchors[int(ch["anchor_off"]):int(ch["anchor_off"]) + int(ch["n_anchors"])]
+        s = orc.align_chain(a, ev[int(ch["read_off"]):], ref_arena, oo, min_score=best, score_fma=1)
+        if np.float32(s).view(np.uint32) != score[k].view(np.uint32):
+            return False
+        if s >= 20.0 and s > best:
+            best = float(s)
+    return True
 
 
 def _copy_dev(dst_ptr, src_tensor):
@@ -385,7 +434,16 @@ def run_reference_arm(args, config):
     reads, coff, clen, crid = build_reads(ref_seq, nsub, seed=2)
     # events of the sample are needed to place the chains (same generator as the GPU arm)
     ev, ev_off = be.detect_events_batch(reads.sig, coff, clen)
-    anchors, chains = build_chains(ev_off, crid, nsub, REF_BASES - 6, seed=3)
+    # event start samples (for ground-truth anchor placement) from the oracle's peak list: event k starts at peaks[k-1]
+    from oracle import Oracle
+    orc = Oracle()
+    ev_pos = np.zeros(len(ev), np.uint32)
+    for c in range(len(coff)):
+        _, peaks = orc.detect_events(reads.sig[int(coff[c]):int(coff[c]) + int(clen[c])], return_peaks=True)
+        n = int(ev_off[c + 1] - ev_off[c])
+        if n > 1:
+            ev_pos[int(ev_off[c]) + 1:int(ev_off[c]) + n] = peaks[:n - 1]
+    anchors, chains = build_chains(ev_off, ev_pos, coff, crid, reads, nsub, REF_BASES - 6, seed=3)
     for _ in range(min(args.warmup, 1)):
         cpu_step(be, reads.sig, coff, clen, anchors, chains, ref_arena, n_threads)
     t0 = time.perf_counter()

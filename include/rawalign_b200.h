@@ -145,6 +145,11 @@ int ra_detect_events_batch_dev(ra_ctx *ctx, const float *sig_dev,
                                float *ev_out_dev, uint64_t ev_cap, uint64_t *ev_off_dev,
                                uint64_t *total_events);
 
+/* Extension (not in the reference's interface): the first sample, relative to its chunk, of every event
+ * of the most recent event-detection call, in the same CSR order as ev_out.  Used by the synthetic
+ * workload generator to place ground-truth anchors; the map loop does not need it. */
+int ra_last_event_positions(ra_ctx *ctx, uint32_t *pos_out, uint64_t cap);
+
 /* ---- K2/K3: DTW cost, batched DTW_global / DTW_global_slantedbanded_antidiagonalwise ---------- */
 /* a_arena = read events, b_arena = reference signal; b_arena == NULL uses the mirror of
  * ra_ref_load.  cost_out[k] is bit-identical to the reference call for item k. */
@@ -180,7 +185,9 @@ int ra_dtw_tb_batch(ra_ctx *ctx, const float *a_arena, uint64_t n_a, const float
  *                   (starts at 0.0f, raised by chains with score >= dtw_min_score).
  * alignment_score[k] receives chain.alignment_score; keep[k] (optional) receives
  * alignment_score >= dtw_min_score (rmap.cpp:518). cells_issued / cells_useful (optional) receive
- * the DP cells the GPU evaluated and the cells the reference would have evaluated. */
+ * the DP cells the GPU evaluated and the cells the reference would have evaluated.
+ * The slicing, the DTW and the replay all run in one kernel (csrc/chains.cu); 8 bytes per anchor and
+ * 32 per chain go to the device, 5 bytes per chain come back. */
 int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
                           const float *ref_arena, uint64_t n_ref,
                           const ra_anchor_t *anchors, uint64_t n_anchors,
@@ -188,6 +195,17 @@ int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
                           int min_score_mode, const float *min_score,
                           float *alignment_score, uint8_t *keep,
                           uint64_t *cells_issued, uint64_t *cells_useful);
+
+/* read_arena == NULL uses the events the last ra_detect_events_batch left on the device (offsets in
+ * ra_chain_t::read_off are then offsets into that call's ev_out): the map loop needs the events on the
+ * host for seeding, the device keeps its copy for DTW.
+ *
+ * Device-resident form: all pointers are device pointers; group_first has n_groups+1 chain indices
+ * (first chain of every group, then n_chains). read/ref NULL = resident events / reference mirror. */
+int ra_align_chains_batch_dev(ra_ctx *ctx, const float *read_arena_dev, const float *ref_arena_dev,
+                              const ra_anchor_t *anchors_dev, const ra_chain_t *chains_dev, const uint32_t *group_first_dev,
+                              uint32_t n_groups, int min_score_mode, const float *min_score_dev,
+                              float *alignment_score_dev, uint8_t *keep_dev, uint64_t *cells_issued, uint64_t *cells_useful);
 
 /* cigar=true form of align_chain (rmap.cpp:218-235, :282-299) for one batch of chains: the
  * concatenated alignment with anchor offsets applied exactly as the reference does (including

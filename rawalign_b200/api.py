@@ -142,6 +142,12 @@ class Context:
                                                  ev_out_ptr, ev_cap, ev_off_ptr, C.byref(tot)))
         return int(tot.value)
 
+    def last_event_positions(self, n_events: int) -> np.ndarray:
+        """First sample (relative to its chunk) of every event of the last detect_events call."""
+        pos = np.empty(max(int(n_events), 1), np.uint32)
+        check(self._L.ra_last_event_positions(self._h, pos.ctypes.data, pos.size))
+        return pos[:int(n_events)]
+
     # ---- K2 / K3 ---------------------------------------------------------------------------------
     def dtw_batch(self, a_arena, b_arena, items: np.ndarray, cost_out: Optional[np.ndarray] = None) -> np.ndarray:
         a_arena = _f32(a_arena)
@@ -205,18 +211,27 @@ class Context:
                            min_score_mode: int = 1, min_score: Optional[np.ndarray] = None):
         """Batched align_chain(cigar=false) + the evaluation loop of gen_chains (rmap.cpp:515-524).
         Returns (alignment_score, keep, cells_issued, cells_useful)."""
-        read_arena = _f32(read_arena)
+        read_arena = None if read_arena is None else _f32(read_arena)   # None: events resident from detect_events_batch
         ref_arena = None if ref_arena is None else _f32(ref_arena)
         anchors = np.ascontiguousarray(anchors, dtype=ANCHOR_DTYPE)
         chains = np.ascontiguousarray(chains, dtype=CHAIN_DTYPE)
         ms = None if min_score is None else _f32(min_score)
         score = np.empty(len(chains), np.float32); keep = np.empty(len(chains), np.uint8)
         ci = C.c_uint64(0); cu = C.c_uint64(0)
-        check(self._L.ra_align_chains_batch(self._h, read_arena.ctypes.data, read_arena.size, _ptr(ref_arena),
+        check(self._L.ra_align_chains_batch(self._h, _ptr(read_arena), 0 if read_arena is None else read_arena.size, _ptr(ref_arena),
                                             0 if ref_arena is None else ref_arena.size, anchors.ctypes.data, len(anchors),
                                             chains.ctypes.data, len(chains), int(min_score_mode), _ptr(ms),
                                             score.ctypes.data, keep.ctypes.data, C.byref(ci), C.byref(cu)))
         return score, keep.astype(bool), int(ci.value), int(cu.value)
+
+    def align_chains_batch_dev(self, read_ptr, ref_ptr, anchors_ptr: int, chains_ptr: int, group_first_ptr: int,
+                               n_groups: int, score_ptr: int, keep_ptr: Optional[int] = None, min_score_mode: int = 1,
+                               min_score_ptr: Optional[int] = None):
+        """Device-resident chain evaluation; returns (cells_issued, cells_useful)."""
+        ci = C.c_uint64(0); cu = C.c_uint64(0)
+        check(self._L.ra_align_chains_batch_dev(self._h, read_ptr, ref_ptr, anchors_ptr, chains_ptr, group_first_ptr, int(n_groups),
+                                                int(min_score_mode), min_score_ptr, score_ptr, keep_ptr, C.byref(ci), C.byref(cu)))
+        return int(ci.value), int(cu.value)
 
     def align_chain(self, anchors, read_events, ref_events, cigar: bool = False, min_score: float = -1e10):
         """align_chain(chain, ri, read_events, ..., opt, cigar, min_score) for one chain (rmap.cpp:181).

@@ -58,22 +58,20 @@ struct ra_ctx {
 	// reference mirror
 	DevBuf ref; uint64_t ref_n = 0;
 	// events
-	DevBuf sig, chunk_off, chunk_len, raw, nev, stat, ev_off, ev_out;
+	DevBuf sig, chunk_off, chunk_len, raw, nev, ev_off, ev_out, ev_pos;
+	uint64_t last_events = 0;
 	// dtw
 	DevBuf a_arena, b_arena, items, cost, counter, ring, order;
+	// chains
+	DevBuf anchors, chains, group_first, min_score, score, keep, cells, chain_ring;
+	uint64_t resident_events = 0;      // events left on the device by the last ra_detect_events_batch
 	// traceback
 	DevBuf dirs, dir_off, slot_off, slot_i, slot_j, slot_d, path_len, path_off, out_i, out_j, out_d;
 };
 
 namespace {
 
-uint32_t events_raw_stride(const ra_mapopt_t &o, uint32_t max_len)
-{
-	// a detector emits at i >= peak_pos + w/2 + 1 and can only start its next peak at a later sample,
-	// so peaks of one detector are >= w/2 + 2 apart
-	const uint32_t s1 = o.window_length1 / 2 + 2, s2 = o.window_length2 / 2 + 2;
-	return max_len / s1 + max_len / s2 + 4;
-}
+constexpr uint32_t kEventSubBatch = 32768;   // chunks per launch group: bounds the scratch arena (~2.4 GB at 4000 samples)
 
 int events_dev(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_dev, const uint32_t *chunk_len_dev,
                uint32_t n_chunks, uint32_t max_chunk_len, float *ev_out_dev, uint64_t ev_cap, uint64_t *ev_off_dev,
@@ -81,29 +79,31 @@ int events_dev(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_dev,
 {
 	const ra_mapopt_t &o = ctx->opt;
 	if (!ra::events_windows_supported(o.window_length1, o.window_length2))
-		return fail(RA_EUNSUP, "event detector windows (%u,%u) have no compiled kernel (built: (3,6) DNA, (7,14) RNA)",
-		            o.window_length1, o.window_length2);
+		return fail(RA_EUNSUP, "event detector windows (%u,%u) are not supported", o.window_length1, o.window_length2);
 	if (n_chunks == 0) { if (total_events) *total_events = 0; uint64_t z = 0; RA_CUDA(cudaMemcpyAsync(ev_off_dev, &z, 8, cudaMemcpyHostToDevice, ctx->stream)); RA_CUDA(cudaStreamSynchronize(ctx->stream)); return RA_OK; }
-	const uint32_t stride = events_raw_stride(o, max_chunk_len);
-	int rc;
-	if ((rc = ctx->raw.reserve((size_t)n_chunks * stride * sizeof(float)))) return rc;
-	if ((rc = ctx->nev.reserve((size_t)n_chunks * sizeof(uint32_t)))) return rc;
-	if ((rc = ctx->stat.reserve((size_t)n_chunks * sizeof(ra::EvChunkStat)))) return rc;
 	ra::EvParams p = { o.window_length1, o.window_length2, o.threshold1, o.threshold2, o.peak_height };
+	ra::EvScratch lay; ra::events_scratch_layout(max_chunk_len, p, &lay);
+	const uint32_t sub = std::min(n_chunks, kEventSubBatch);
+	int rc;
+	if ((rc = ctx->raw.reserve((size_t)sub * lay.floats_per_chunk * sizeof(float)))) return rc;
+	if ((rc = ctx->nev.reserve((size_t)sub * sizeof(uint32_t)))) return rc;
+	if ((rc = ctx->ev_pos.reserve((size_t)std::max<uint64_t>(ev_cap, 1) * sizeof(uint32_t)))) return rc;
 	RA_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
-	RA_CUDA(ra::launch_events_scan(sig_dev, chunk_off_dev, chunk_len_dev, n_chunks, p, (int)o.fp_contract,
-	                               ctx->raw.as<float>(), stride, ctx->nev.as<uint32_t>(), ctx->stat.as<ra::EvChunkStat>(), ctx->stream));
-	RA_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
-	RA_CUDA(ra::launch_exclusive_scan_u32(ctx->nev.as<uint32_t>(), ev_off_dev, n_chunks, ctx->stream));
-	RA_CUDA(ra::launch_events_normalise(ctx->raw.as<float>(), stride, ctx->nev.as<uint32_t>(), ctx->stat.as<ra::EvChunkStat>(),
-	                                    ev_off_dev, n_chunks, ev_out_dev, ev_cap, ctx->stream));
+	for (uint32_t s0 = 0; s0 < n_chunks; s0 += sub) {
+		const uint32_t n = std::min(sub, n_chunks - s0);
+		const bool last = (s0 + n == n_chunks);
+		RA_CUDA(ra::launch_events(sig_dev, chunk_off_dev + s0, chunk_len_dev + s0, n, max_chunk_len, p, (int)o.fp_contract,
+		                          ctx->raw.as<float>(), ctx->nev.as<uint32_t>(), ev_off_dev + s0, s0 != 0, ev_out_dev, ev_cap,
+		                          ctx->ev_pos.as<uint32_t>(), ctx->stream, last ? ctx->ev[1] : nullptr));
+		ctx->launches += ra::kEventKernels;
+	}
 	RA_CUDA(cudaEventRecord(ctx->ev[2], ctx->stream));
 	ctx->timed_k1 = true;
-	ctx->launches += 3;
 	uint64_t tot = 0;
 	RA_CUDA(cudaMemcpyAsync(&tot, ev_off_dev + n_chunks, sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
 	RA_CUDA(cudaStreamSynchronize(ctx->stream));
 	if (total_events) *total_events = tot;
+	ctx->last_events = tot;
 	if (tot > ev_cap) return fail(RA_EINVAL, "ev_out capacity %llu < %llu events", (unsigned long long)ev_cap, (unsigned long long)tot);
 	return RA_OK;
 }
@@ -144,6 +144,59 @@ int dtw_dev(ra_ctx *ctx, const float *a_dev, const float *b_dev, const ra_dtw_it
 	ctx->timed_dtw = true;
 	ctx->launches += nl;
 	return RA_OK;
+}
+
+// Runs the chain kernel on device-resident inputs; retries once with a larger HBM ring when a part
+// was wider than the rings available.
+int chains_dev(ra_ctx *ctx, const float *read_dev, const float *ref_dev, const ra_anchor_t *anchors_dev,
+               const ra_chain_t *chains_dev_p, const uint32_t *group_first_dev, uint32_t n_groups, int min_score_mode,
+               const float *min_score_dev, float *score_dev, uint8_t *keep_dev, uint64_t *cells_host /* [2] or null */)
+{
+	if (n_groups == 0) { if (cells_host) cells_host[0] = cells_host[1] = 0; return RA_OK; }
+	const ra_mapopt_t &o = ctx->opt;
+	if (o.dtw_border_constraint != RA_DTW_BORDER_CONSTRAINT_GLOBAL && o.dtw_border_constraint != RA_DTW_BORDER_CONSTRAINT_SPARSE)
+		return fail(RA_EUNSUP, "invalid border constraint (the reference exits at rmap.cpp:301-304)");
+	int rc;
+	if ((rc = ctx->counter.reserve(64))) return rc;
+	if ((rc = ctx->cells.reserve(64))) return rc;
+	const size_t warps = (size_t)ctx->n_sm * ra::kChainCtasPerSm * 4;
+	uint32_t ring_cap = ctx->chain_ring.cap ? (uint32_t)(ctx->chain_ring.cap / (warps * 3 * sizeof(float))) : 0;
+	{ uint32_t c = 1; while (c * 2 <= ring_cap) c *= 2; ring_cap = ring_cap ? c : 0; }
+	for (int attempt = 0; attempt < 2; ++attempt) {
+		ra::ChainLaunch L; memset(&L, 0, sizeof(L));
+		L.read_arena = read_dev; L.ref_arena = ref_dev; L.anchors = anchors_dev; L.chains = chains_dev_p;
+		L.group_first = group_first_dev; L.n_groups = n_groups;
+		L.border = o.dtw_border_constraint; L.fill = o.dtw_fill_method; L.fp_contract = o.fp_contract;
+		L.band_frac = o.dtw_band_radius_frac; L.match_bonus = o.dtw_match_bonus; L.min_dtw_score = o.dtw_min_score;
+		L.min_score_mode = min_score_mode; L.min_score = min_score_dev; L.score = score_dev; L.keep = keep_dev;
+		L.work_counter = ctx->counter.as<uint32_t>(); L.need_cap = ctx->counter.as<uint32_t>() + 4;
+		L.cells = ctx->cells.as<uint64_t>();
+		L.ring_scratch = ring_cap ? ctx->chain_ring.as<float>() : nullptr; L.ring_cap = ring_cap;
+		RA_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
+		RA_CUDA(ra::launch_chain_eval(L, ctx->n_sm, ctx->stream));
+		RA_CUDA(cudaEventRecord(ctx->ev[4], ctx->stream));
+		ctx->timed_dtw = true;
+		ctx->launches += 1;
+		uint32_t need = 0;
+		RA_CUDA(cudaMemcpyAsync(&need, L.need_cap, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+		uint64_t cells[2] = {0, 0};
+		RA_CUDA(cudaMemcpyAsync(cells, L.cells, sizeof(cells), cudaMemcpyDeviceToHost, ctx->stream));
+		RA_CUDA(cudaStreamSynchronize(ctx->stream));
+		if (need == 0) { if (cells_host) { cells_host[0] = cells[0]; cells_host[1] = cells[1]; } return RA_OK; }
+		if (attempt == 1) break;
+		if ((rc = ctx->chain_ring.reserve(warps * 3 * (size_t)need * sizeof(float)))) return rc;
+		ring_cap = need;
+	}
+	return fail(RA_ECUDA, "chain kernel could not obtain a wide enough ring");
+}
+
+// group_first[g] = index of the first chain of group g (groups are runs of equal ra_chain_t::group); n_groups+1 entries.
+void group_boundaries(const ra_chain_t *chains, uint32_t n_chains, int min_score_mode, std::vector<uint32_t> &gf)
+{
+	gf.clear();
+	for (uint32_t k = 0; k < n_chains; ++k)
+		if (k == 0 || min_score_mode != 1 || chains[k].group != chains[k - 1].group) gf.push_back(k);
+	gf.push_back(n_chains);
 }
 
 } // namespace
@@ -197,8 +250,8 @@ void ra_destroy(ra_ctx *ctx)
 	if (!ctx) return;
 	cudaSetDevice(ctx->device);
 	cudaStreamSynchronize(ctx->stream);
-	DevBuf *bufs[] = { &ctx->ref, &ctx->sig, &ctx->chunk_off, &ctx->chunk_len, &ctx->raw, &ctx->nev, &ctx->stat, &ctx->ev_off,
-	                   &ctx->ev_out, &ctx->a_arena, &ctx->b_arena, &ctx->items, &ctx->cost, &ctx->counter, &ctx->ring, &ctx->order,
+	DevBuf *bufs[] = { &ctx->ref, &ctx->sig, &ctx->chunk_off, &ctx->chunk_len, &ctx->raw, &ctx->nev, &ctx->ev_pos, &ctx->ev_off,
+	                   &ctx->ev_out, &ctx->a_arena, &ctx->b_arena, &ctx->items, &ctx->cost, &ctx->counter, &ctx->ring, &ctx->order, &ctx->anchors, &ctx->chains, &ctx->group_first, &ctx->min_score, &ctx->score, &ctx->keep, &ctx->cells, &ctx->chain_ring,
 	                   &ctx->dirs, &ctx->dir_off, &ctx->slot_off, &ctx->slot_i, &ctx->slot_j, &ctx->slot_d, &ctx->path_len,
 	                   &ctx->path_off, &ctx->out_i, &ctx->out_j, &ctx->out_d };
 	for (DevBuf *b : bufs) b->release();
@@ -304,7 +357,7 @@ int ra_detect_events_batch(ra_ctx *ctx, const float *sig, uint64_t n_sig, const 
 	if ((rc = ctx->chunk_off.reserve((size_t)(n_chunks + 1) * sizeof(uint64_t)))) return rc;
 	if ((rc = ctx->chunk_len.reserve((size_t)(n_chunks + 1) * sizeof(uint32_t)))) return rc;
 	if ((rc = ctx->ev_off.reserve((size_t)(n_chunks + 1) * sizeof(uint64_t)))) return rc;
-	const uint64_t dev_cap = std::min<uint64_t>(ev_cap, (uint64_t)n_chunks * events_raw_stride(ctx->opt, max_len));
+	const uint64_t dev_cap = std::min<uint64_t>(ev_cap, sum_len / 2 + n_chunks + 16);   // peaks are >= 3 samples apart per detector: < 0.54 events per sample
 	if ((rc = ctx->ev_out.reserve((size_t)std::max<uint64_t>(dev_cap, 1) * sizeof(float)))) return rc;
 	if (n_chunks) {
 		RA_CUDA(cudaMemcpyAsync(ctx->sig.p, sig, (size_t)n_sig * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
@@ -315,8 +368,19 @@ int ra_detect_events_batch(ra_ctx *ctx, const float *sig, uint64_t n_sig, const 
 	rc = events_dev(ctx, ctx->sig.as<float>(), ctx->chunk_off.as<uint64_t>(), ctx->chunk_len.as<uint32_t>(), n_chunks, max_len,
 	                ctx->ev_out.as<float>(), dev_cap, ctx->ev_off.as<uint64_t>(), &total);
 	if (rc) return rc;
+	ctx->resident_events = total;
 	RA_CUDA(cudaMemcpyAsync(ev_off, ctx->ev_off.p, (size_t)(n_chunks + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
 	if (total) RA_CUDA(cudaMemcpyAsync(ev_out, ctx->ev_out.p, (size_t)total * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+	RA_CUDA(cudaStreamSynchronize(ctx->stream));
+	return RA_OK;
+}
+
+int ra_last_event_positions(ra_ctx *ctx, uint32_t *pos_out, uint64_t cap)
+{
+	if (!ctx || !pos_out) return fail(RA_EINVAL, "NULL argument");
+	RA_CUDA(cudaSetDevice(ctx->device));
+	if (cap < ctx->last_events) return fail(RA_EINVAL, "capacity %llu < %llu events", (unsigned long long)cap, (unsigned long long)ctx->last_events);
+	if (ctx->last_events) RA_CUDA(cudaMemcpyAsync(pos_out, ctx->ev_pos.p, (size_t)ctx->last_events * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
 	RA_CUDA(cudaStreamSynchronize(ctx->stream));
 	return RA_OK;
 }
@@ -526,62 +590,76 @@ int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
                           int min_score_mode, const float *min_score, float *alignment_score, uint8_t *keep,
                           uint64_t *cells_issued, uint64_t *cells_useful)
 {
-	if (!ctx || (n_chains && (!read_arena || !anchors || !chains || !alignment_score))) return fail(RA_EINVAL, "NULL argument");
-	const ra_mapopt_t &o = ctx->opt;
-	std::vector<ra_dtw_item_t> items;
-	std::vector<uint64_t> first(n_chains + 1);
-	items.reserve((size_t)n_anchors);
-	for (uint32_t k = 0; k < n_chains; ++k) {
-		first[k] = items.size();
-		if (chains[k].anchor_off + chains[k].n_anchors > n_anchors) return fail(RA_EINVAL, "chain %u: anchors out of range", k);
-		int rc = chain_items(o, anchors + chains[k].anchor_off, chains[k], false, items);
-		if (rc) return rc;
-	}
-	first[n_chains] = items.size();
-	if (items.size() > 0xffffffffull) return fail(RA_EINVAL, "too many sub-problems in one batch");
-	std::vector<float> cost(items.size());
-	int rc = ra_dtw_batch(ctx, read_arena, n_read, ref_arena, n_ref, items.data(), (uint32_t)items.size(), cost.data());
-	if (rc) return rc;
-
-	uint64_t issued = 0, useful = 0;
-	const bool want_cells = cells_issued || cells_useful;
-	float best = 0.0f; uint32_t cur_group = 0; bool have_group = false;
-	for (uint32_t k = 0; k < n_chains; ++k) {
+	if (!ctx || (n_chains && (!anchors || !chains || !alignment_score))) return fail(RA_EINVAL, "NULL argument");
+	RA_CUDA(cudaSetDevice(ctx->device));
+	if (n_chains == 0) { if (cells_issued) *cells_issued = 0; if (cells_useful) *cells_useful = 0; return RA_OK; }
+	if (!read_arena && !ctx->resident_events) return fail(RA_EINVAL, "read_arena is NULL and no events are resident on the device");
+	if (!ref_arena && !ctx->ref.p) return fail(RA_EINVAL, "no reference arena: pass ref_arena or call ra_ref_load first");
+	const uint64_t nr = read_arena ? n_read : ctx->resident_events, nf = ref_arena ? n_ref : ctx->ref_n;
+	for (uint32_t k = 0; k < n_chains; ++k) {          // bounds: the kernel trusts these
 		const ra_chain_t &ch = chains[k];
-		const ra_anchor_t *anc = anchors + ch.anchor_off;
-		if (min_score_mode == 1 && (!have_group || ch.group != cur_group)) { best = 0.0f; cur_group = ch.group; have_group = true; }   // rmap.cpp:515
-		const float ms = (min_score_mode == 1) ? best : (min_score ? min_score[k] : RA_SCORE_DROPPED);
-		float score;
-		const uint64_t f = first[k], l = first[k + 1];
-		if (want_cells) for (uint64_t q = f; q < l; ++q) issued += ra_dtw_cells(items[q].a_len, items[q].b_len, items[q].band_radius);
-		if (o.dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_GLOBAL) {
-			const uint32_t read_size = items[f].a_len;
-			const float max_attainable = (float)read_size * o.dtw_match_bonus;                 // :205
-			if (max_attainable < ms) score = RA_SCORE_DROPPED;                               // :206-209
-			else {
-				score = chain_score(o, read_size, cost[f]);                                  // :236, :306
-				if (want_cells) useful += ra_dtw_cells(items[f].a_len, items[f].b_len, items[f].band_radius);
-			}
-		} else {
-			const uint32_t chain_read_size = anc[0].query_position - anc[ch.n_anchors - 1].query_position + 1;   // :245
-			float cur_max = (float)chain_read_size * o.dtw_match_bonus;                      // :246
-			float dtw_cost = 0.0f; uint32_t n_aligned = 0; bool dropped = false;
-			for (uint64_t q = f; q < l; ++q) {
-				if (cur_max < ms) { dropped = true; break; }                                 // :265-268
-				dtw_cost += cost[q];                                                         // :279
-				cur_max -= cost[q];                                                          // :280
-				n_aligned += items[q].a_len;                                                 // :292
-				if (want_cells) useful += ra_dtw_cells(items[q].a_len, items[q].b_len, items[q].band_radius);
-			}
-			score = dropped ? RA_SCORE_DROPPED : chain_score(o, n_aligned, dtw_cost);
-		}
-		alignment_score[k] = score;
-		const bool kp = score >= o.dtw_min_score;                                            // :518
-		if (keep) keep[k] = kp ? 1 : 0;
-		if (min_score_mode == 1 && kp && score > best) best = score;                         // :519-521
+		if (ch.n_anchors < 1 || ch.anchor_off + ch.n_anchors > n_anchors) return fail(RA_EINVAL, "chain %u: anchors out of range", k);
+		const ra_anchor_t &s = anchors[ch.anchor_off + ch.n_anchors - 1], &e = anchors[ch.anchor_off];
+		if (e.query_position < s.query_position || e.target_position < s.target_position) return fail(RA_EINVAL, "chain %u: anchors[0] must be the chain end", k);
+		if (ch.read_off + e.query_position >= nr) return fail(RA_EINVAL, "chain %u: read span exceeds the read arena", k);
+		if (ch.ref_off + e.target_position >= nf) return fail(RA_EINVAL, "chain %u: reference span exceeds the reference arena", k);
 	}
-	if (cells_issued) *cells_issued = issued;
-	if (cells_useful) *cells_useful = useful;
+	std::vector<uint32_t> gf;
+	group_boundaries(chains, n_chains, min_score_mode, gf);
+	int rc;
+	const float *read_dev = ctx->ev_out.as<float>();
+	if (read_arena) {
+		if ((rc = ctx->a_arena.reserve((size_t)n_read * sizeof(float)))) return rc;
+		RA_CUDA(cudaMemcpyAsync(ctx->a_arena.p, read_arena, (size_t)n_read * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+		read_dev = ctx->a_arena.as<float>();
+	}
+	const float *ref_dev = ctx->ref.as<float>();
+	if (ref_arena) {
+		if ((rc = ctx->b_arena.reserve((size_t)n_ref * sizeof(float)))) return rc;
+		RA_CUDA(cudaMemcpyAsync(ctx->b_arena.p, ref_arena, (size_t)n_ref * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+		ref_dev = ctx->b_arena.as<float>();
+	}
+	if ((rc = ctx->anchors.reserve((size_t)n_anchors * sizeof(ra_anchor_t)))) return rc;
+	if ((rc = ctx->chains.reserve((size_t)n_chains * sizeof(ra_chain_t)))) return rc;
+	if ((rc = ctx->group_first.reserve(gf.size() * sizeof(uint32_t)))) return rc;
+	if ((rc = ctx->score.reserve((size_t)n_chains * sizeof(float)))) return rc;
+	if ((rc = ctx->keep.reserve((size_t)n_chains))) return rc;
+	RA_CUDA(cudaMemcpyAsync(ctx->anchors.p, anchors, (size_t)n_anchors * sizeof(ra_anchor_t), cudaMemcpyHostToDevice, ctx->stream));
+	RA_CUDA(cudaMemcpyAsync(ctx->chains.p, chains, (size_t)n_chains * sizeof(ra_chain_t), cudaMemcpyHostToDevice, ctx->stream));
+	RA_CUDA(cudaMemcpyAsync(ctx->group_first.p, gf.data(), gf.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+	const float *ms_dev = nullptr;
+	if (min_score_mode != 1 && min_score) {
+		if ((rc = ctx->min_score.reserve((size_t)n_chains * sizeof(float)))) return rc;
+		RA_CUDA(cudaMemcpyAsync(ctx->min_score.p, min_score, (size_t)n_chains * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+		ms_dev = ctx->min_score.as<float>();
+	}
+	uint64_t cells[2] = {0, 0};
+	if ((rc = chains_dev(ctx, read_dev, ref_dev, ctx->anchors.as<ra_anchor_t>(), ctx->chains.as<ra_chain_t>(), ctx->group_first.as<uint32_t>(),
+	                     (uint32_t)gf.size() - 1, min_score_mode, ms_dev, ctx->score.as<float>(), ctx->keep.as<uint8_t>(), cells))) return rc;
+	RA_CUDA(cudaMemcpyAsync(alignment_score, ctx->score.p, (size_t)n_chains * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+	if (keep) RA_CUDA(cudaMemcpyAsync(keep, ctx->keep.p, (size_t)n_chains, cudaMemcpyDeviceToHost, ctx->stream));
+	RA_CUDA(cudaStreamSynchronize(ctx->stream));
+	if (cells_issued) *cells_issued = cells[0];
+	if (cells_useful) *cells_useful = cells[1];
+	return RA_OK;
+}
+
+int ra_align_chains_batch_dev(ra_ctx *ctx, const float *read_arena_dev, const float *ref_arena_dev,
+                              const ra_anchor_t *anchors_dev, const ra_chain_t *chains_dev_p, const uint32_t *group_first_dev,
+                              uint32_t n_groups, int min_score_mode, const float *min_score_dev,
+                              float *alignment_score_dev, uint8_t *keep_dev, uint64_t *cells_issued, uint64_t *cells_useful)
+{
+	if (!ctx || (n_groups && (!anchors_dev || !chains_dev_p || !group_first_dev || !alignment_score_dev))) return fail(RA_EINVAL, "NULL argument");
+	RA_CUDA(cudaSetDevice(ctx->device));
+	const float *read_dev = read_arena_dev ? read_arena_dev : ctx->ev_out.as<float>();
+	const float *ref_dev = ref_arena_dev ? ref_arena_dev : ctx->ref.as<float>();
+	if (n_groups && (!read_dev || !ref_dev)) return fail(RA_EINVAL, "no read or reference arena on the device");
+	uint64_t cells[2] = {0, 0};
+	int rc = chains_dev(ctx, read_dev, ref_dev, anchors_dev, chains_dev_p, group_first_dev, n_groups, min_score_mode, min_score_dev,
+	                    alignment_score_dev, keep_dev, cells);
+	if (rc) return rc;
+	if (cells_issued) *cells_issued = cells[0];
+	if (cells_useful) *cells_useful = cells[1];
 	return RA_OK;
 }
 

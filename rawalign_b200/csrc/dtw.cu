@@ -12,64 +12,14 @@
 // anti-diagonals live in a per-warp shared-memory ring (or in an HBM/L2 ring when a band is wider than
 // the ring), warps pull problems from a global work counter.  The register-resident small-band kernels
 // in dtw_small.cu take the sparse anchor-to-anchor problems; everything they do not cover lands here.
-#include "ra_common.cuh"
+#include "dtw_core.cuh"
 
 namespace ra {
 
 constexpr int kWarpsPerCta = 4;
 constexpr uint32_t kSmemRingCap = 1024;          // floats per anti-diagonal ring in shared memory
-constexpr float kInf = 1e10f;
 
 uint32_t dtw_generic_smem_ring_cap() { return kSmemRingCap; }
-
-// Enumerates the anti-diagonals of one problem in order; warp-uniform.
-struct DiagIter {
-	int n, m, P, S;
-	bool full;
-	int c, r, d;
-	bool pending_primary;
-	int lo, hi;       // rows (index into the shorter sequence) of the current diagonal, clipped; lo > hi = empty
-
-	__device__ __forceinline__ void set_range(int start_i, int start_j, int len)
-	{
-		// cells (start_i - o, start_j + o), o in [o0, o1)   dtw.cpp:365-366, :419-420
-		int o0 = max(max(0, start_i - (n - 1)), -start_j);
-		int o1 = min(min(len, start_i + 1), m - start_j);
-		lo = start_j + o0; hi = start_j + o1 - 1;
-		d = start_i + start_j;
-	}
-	__device__ __forceinline__ void init(int n_, int m_, int band_radius)
-	{
-		n = n_; m = m_;
-		full = band_radius < 0;
-		if (!full) {
-			// dtw.cpp:298-302 (32-bit unsigned arithmetic in the reference)
-			const uint32_t extra = (((uint32_t)n - (uint32_t)m) * (uint32_t)band_radius + (uint32_t)n - 1u) / (uint32_t)n;
-			const int R = band_radius + (int)extra;
-			P = R + ((R % 2 == 0) ? 1 : 0);
-			S = R + ((R % 2 == 1) ? 1 : 0);
-		} else { P = S = 0; }
-		c = 0; r = 0; d = 0; lo = 0; hi = 0; pending_primary = false;   // iteration 0: the corner cell only (:317-347)
-	}
-	__device__ __forceinline__ bool next()
-	{
-		if (full) {
-			if (++d > n + m - 2) return false;
-			lo = max(0, d - (n - 1)); hi = min(m - 1, d);
-			return true;
-		}
-		if (pending_primary) { pending_primary = false; set_range(c + P / 2, r - P / 2, P); return true; }
-		if (++c >= n) return false;
-		if ((int64_t)(r + 1) * (int64_t)n <= (int64_t)m * (int64_t)c) {   // :352-359
-			++r; pending_primary = true;
-			set_range(c + S / 2 - 1, r - S / 2, S);                        // secondary, :362-366
-			return true;
-		}
-		set_range(c + P / 2, r - P / 2, P);                                // primary, :416-420
-		return true;
-	}
-	__device__ __forceinline__ int max_width() const { return full ? m : max(P, S); }
-};
 
 template <bool TB>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)

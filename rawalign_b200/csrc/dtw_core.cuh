@@ -1,0 +1,142 @@
+// dtw_core.cuh -- device-side DTW building blocks shared by the item kernels (dtw.cu) and the chain
+// kernel (chains.cu).
+//
+// Semantics (bit-identical to the reference for every schedule, because each cell is
+// min(min(top,left),topleft) + |a-b| -- min is exact, one rounding per cell):
+//   banded : the cell set of DTW_global_slantedbanded_antidiagonalwise, src/dtw.cpp:273-520
+//            (closed form in oracle/ra_oracle.c:ora_dtw_banded and DESIGN.md), out-of-set = 1e10f;
+//   full   : DTW_global, src/dtw.cpp:37-66 (whole rectangle).
+#pragma once
+#include "ra_common.cuh"
+
+namespace ra {
+
+constexpr float kInf = 1e10f;
+
+// Enumerates the anti-diagonals of one problem in order.  n >= m for banded problems (the caller
+// swaps, dtw.cpp:284-292); rows j index the shorter sequence.
+struct DiagIter {
+	int n, m, P, S;
+	bool full;
+	int c, r, d;
+	bool pending_primary;
+	int lo, hi;       // rows of the current diagonal, clipped to the matrix; lo > hi = empty
+
+	__device__ __forceinline__ void set_range(int start_i, int start_j, int len)
+	{
+		// cells (start_i - o, start_j + o), o in [o0, o1)   dtw.cpp:365-366, :419-420
+		const int o0 = max(max(0, start_i - (n - 1)), -start_j);
+		const int o1 = min(min(len, start_i + 1), m - start_j);
+		lo = start_j + o0; hi = start_j + o1 - 1;
+		d = start_i + start_j;
+	}
+	__device__ __forceinline__ void init(int n_, int m_, int band_radius)
+	{
+		n = n_; m = m_;
+		full = band_radius < 0;
+		if (!full) {
+			// dtw.cpp:298-302 (32-bit unsigned arithmetic in the reference)
+			const uint32_t extra = (((uint32_t)n - (uint32_t)m) * (uint32_t)band_radius + (uint32_t)n - 1u) / (uint32_t)n;
+			const int R = band_radius + (int)extra;
+			P = R + ((R % 2 == 0) ? 1 : 0);
+			S = R + ((R % 2 == 1) ? 1 : 0);
+		} else { P = S = 0; }
+		c = 0; r = 0; d = 0; lo = 0; hi = 0; pending_primary = false;   // iteration 0: the corner cell only (:317-347)
+	}
+	__device__ __forceinline__ bool next()
+	{
+		if (full) {
+			if (++d > n + m - 2) return false;
+			lo = max(0, d - (n - 1)); hi = min(m - 1, d);
+			return true;
+		}
+		if (pending_primary) { pending_primary = false; set_range(c + P / 2, r - P / 2, P); return true; }
+		if (++c >= n) return false;
+		if ((int64_t)(r + 1) * (int64_t)n <= (int64_t)m * (int64_t)c) {   // :352-359
+			++r; pending_primary = true;
+			set_range(c + S / 2 - 1, r - S / 2, S);                        // secondary, :362-366
+			return true;
+		}
+		set_range(c + P / 2, r - P / 2, P);                                // primary, :416-420
+		return true;
+	}
+	__device__ __forceinline__ int max_width() const { return full ? m : max(P, S); }
+};
+
+__device__ __forceinline__ int band_width_of(int n, int m, int band_radius)
+{
+	if (band_radius < 0) return m;
+	const uint32_t extra = (((uint32_t)n - (uint32_t)m) * (uint32_t)band_radius + (uint32_t)n - 1u) / (uint32_t)n;
+	return band_radius + (int)extra + 1;
+}
+
+// Warp-cooperative cost of one problem: lanes stride over the rows of each anti-diagonal; three rolling
+// diagonals in `ring` (3*cap floats, cap a power of two >= the widest diagonal; shared or global memory).
+// A is the longer sequence (n >= m) for banded problems.  Returns dp(n-1, m-1) in every lane and adds the
+// number of evaluated cells to *cells (lane-uniform).
+__device__ __forceinline__ float warp_dtw_cost(const float *__restrict__ A, int n, const float *__restrict__ B, int m,
+                                               int band, float *ring, uint32_t cap, int lane, uint64_t *cells)
+{
+	DiagIter di; di.init(n, m, band);
+	const uint32_t mask = cap - 1;
+	float *r0 = ring, *r1 = ring + cap, *r2 = ring + 2 * (size_t)cap;
+	int lo1 = 0, hi1 = -1, lo2 = 0, hi2 = -1;
+	if (lane == 0) r0[0] = fabsf(__ldg(A) - __ldg(B));
+	__syncwarp();
+	int lo0 = 0, hi0 = 0;
+	uint64_t cnt = 1;
+	for (;;) {
+		float *t = r2; r2 = r1; r1 = r0; r0 = t;
+		lo2 = lo1; hi2 = hi1; lo1 = lo0; hi1 = hi0;
+		if (!di.next()) break;
+		lo0 = di.lo; hi0 = di.hi;
+		const int d = di.d;
+		if (hi0 >= lo0) cnt += (uint64_t)(hi0 - lo0 + 1);
+		for (int j = lo0 + lane; j <= hi0; j += 32) {
+			const int i = d - j;
+			// (i, j-1) and (i-1, j) on diagonal d-1; (i-1, j-1) on diagonal d-2
+			const float top = (j - 1 >= lo1 && j - 1 <= hi1) ? r1[(uint32_t)(j - 1) & mask] : kInf;
+			const float left = (j >= lo1 && j <= hi1) ? r1[(uint32_t)j & mask] : kInf;
+			const float tl = (j - 1 >= lo2 && j - 1 <= hi2) ? r2[(uint32_t)(j - 1) & mask] : kInf;
+			r0[(uint32_t)j & mask] = fminf(fminf(top, left), tl) + fabsf(__ldg(A + i) - __ldg(B + j));
+		}
+		__syncwarp();
+	}
+	if (cells) *cells += cnt;
+	const float res = r1[(uint32_t)(m - 1) & mask];      // after the final rotation the last diagonal is r1
+	__syncwarp();
+	return res;
+}
+
+// Lane-private cost of one SMALL problem (widest diagonal <= kLaneRing): the three rolling diagonals
+// live in shared memory, interleaved across the warp ([slot][lane], bank-conflict free).
+constexpr int kLaneRing = 8;
+__device__ __forceinline__ float lane_dtw_cost(const float *__restrict__ A, int n, const float *__restrict__ B, int m,
+                                               int band, float *ring_lane /* + slot*32 */, uint32_t *cells)
+{
+	DiagIter di; di.init(n, m, band);
+	constexpr uint32_t mask = kLaneRing - 1;
+	int o0 = 0, o1 = kLaneRing, o2 = 2 * kLaneRing;      // slot offsets of the current / previous / before-previous diagonal
+	int lo1 = 0, hi1 = -1, lo2 = 0, hi2 = -1, lo0 = 0, hi0 = 0;
+	ring_lane[(o0 + 0) * 32] = fabsf(__ldg(A) - __ldg(B));
+	uint32_t cnt = 1;
+	for (;;) {
+		const int t = o2; o2 = o1; o1 = o0; o0 = t;
+		lo2 = lo1; hi2 = hi1; lo1 = lo0; hi1 = hi0;
+		if (!di.next()) break;
+		lo0 = di.lo; hi0 = di.hi;
+		const int d = di.d;
+		for (int j = lo0; j <= hi0; ++j) {
+			const int i = d - j;
+			const float top = (j - 1 >= lo1 && j - 1 <= hi1) ? ring_lane[(o1 + ((uint32_t)(j - 1) & mask)) * 32] : kInf;
+			const float left = (j >= lo1 && j <= hi1) ? ring_lane[(o1 + ((uint32_t)j & mask)) * 32] : kInf;
+			const float tl = (j - 1 >= lo2 && j - 1 <= hi2) ? ring_lane[(o2 + ((uint32_t)(j - 1) & mask)) * 32] : kInf;
+			ring_lane[(o0 + ((uint32_t)j & mask)) * 32] = fminf(fminf(top, left), tl) + fabsf(__ldg(A + i) - __ldg(B + j));
+			++cnt;
+		}
+	}
+	if (cells) *cells += cnt;
+	return ring_lane[(o1 + ((uint32_t)(m - 1) & mask)) * 32];
+}
+
+} // namespace ra

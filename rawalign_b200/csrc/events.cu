@@ -1,14 +1,21 @@
 // events.cu -- K1: batched event detection, bit-identical to detect_events() of the reference
 // (src/revent.c:190-210; arithmetic of :22-32, :34-75, :77-138, :140-188).
 //
-// Parallelism: the reference's prefix sums are *sequential* fp32 accumulations and its peak
-// detector is a sequential two-detector state machine, so bit-exactness forces one sequential
-// scan per chunk.  One thread owns one chunk and fuses all four reference passes into a single
-// sweep: it keeps the last 2*W2+1 prefix values in a register ring (the t-statistic at position
-// p needs prefix[p-w], prefix[p], prefix[p+w] only), steps both detectors W2 samples behind the
-// scan head, and turns every emitted peak into an event mean on the fly.  Parallelism comes from
-// the batch: >= 1e5 chunks in flight.  Each thread streams its own chunk with 16-byte loads
-// (float4); the 32 B sector a lane touches is reused from L1 on its next load.
+// What the reference semantics force: prefix_sum / prefix_sum_square are *sequential* fp32
+// accumulations (rounding depends on the order), and the peak detector is a sequential two-detector
+// state machine.  Everything else (the two t-statistic tracks, the per-event means, the
+// normalisation) is position-independent.  So the chunk is processed by five kernels that each use
+// the parallelism their stage has:
+//
+//   k_prefix   one thread per chunk      sequential fp32 scan, float4 in / float4 out       revent.c:22-32
+//   k_tstat    one thread per sample     both windows, fully parallel, coalesced            revent.c:34-75
+//   k_peaks    one thread per chunk      the two-detector FSM over the t-stat tracks        revent.c:77-138
+//   k_scan     one CTA                   CSR offsets from the per-chunk event counts
+//   k_finish   one warp per chunk        event means (parallel), fp64 sum/sum2 in array
+//                                        order (lane 0), z-normalise (parallel), CSR write  revent.c:140-188
+//
+// Intermediates (prefix sums, t-stat tracks, peak lists) live in an HBM scratch arena that the
+// 126 MB L2 mostly absorbs for sub-batches of a few thousand chunks.
 //
 // Compiled with -fmad=false: every fused multiply-add below is spelled out and exists only where
 // the reference *build* has one (GCC -O3 on an FMA host contracts revent.c:30, :61 twice, :180),
@@ -18,10 +25,60 @@
 
 namespace ra {
 
-template <int W2> struct RingSize { static constexpr int value = (2 * W2 + 1 <= 16) ? 16 : ((2 * W2 + 1 <= 32) ? 32 : 64); };
+// ---------------------------------------------------------------------------------------------------
+// k_prefix: ps[0]=pss[0]=0; ps[i+1]=ps[i]+x[i]; pss[i+1]=pss[i]+x[i]*x[i]  (fused when CONTRACT)
+// Layout per chunk: ps[0..len] at ps_base + chunk*pstride (pstride % 4 == 0).
+// ---------------------------------------------------------------------------------------------------
+template <bool CONTRACT>
+__global__ void __launch_bounds__(64)
+k_prefix(const float *__restrict__ sig, const uint64_t *__restrict__ chunk_off, const uint32_t *__restrict__ chunk_len,
+         uint32_t n_chunks, float *__restrict__ ps_base, float *__restrict__ pss_base, uint32_t pstride)
+{
+	const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+	if (c >= n_chunks) return;
+	const uint32_t len = chunk_len[c];
+	const float *__restrict__ x = sig + chunk_off[c];
+	float *__restrict__ ps = ps_base + (size_t)c * pstride;
+	float *__restrict__ pss = pss_base + (size_t)c * pstride;
+	float s = 0.0f, q = 0.0f;
+	// outputs are written as float4 at positions [4k .. 4k+3]; position 0 holds the leading zero, so
+	// the vector written at step k is {P(4k), P(4k+1), P(4k+2), P(4k+3)} with P(0)=0
+	float s0 = 0.0f, q0 = 0.0f;      // P(4k) carried from the previous group
+	const bool vec = ((reinterpret_cast<uintptr_t>(x) & 15u) == 0);
+	uint32_t t = 0;
+	if (vec) {
+		constexpr int G = 4;         // float4 loads in flight per thread
+		for (; t + 4 * G <= len; t += 4 * G) {
+			float4 v[G];
+#pragma unroll
+			for (int g = 0; g < G; ++g) v[g] = __ldcs(reinterpret_cast<const float4 *>(x + t) + g);
+#pragma unroll
+			for (int g = 0; g < G; ++g) {
+				float4 a, b;
+				a.x = s0; b.x = q0;
+				s = __fadd_rn(s, v[g].x); q = CONTRACT ? __fmaf_rn(v[g].x, v[g].x, q) : __fadd_rn(q, __fmul_rn(v[g].x, v[g].x)); a.y = s; b.y = q;
+				s = __fadd_rn(s, v[g].y); q = CONTRACT ? __fmaf_rn(v[g].y, v[g].y, q) : __fadd_rn(q, __fmul_rn(v[g].y, v[g].y)); a.z = s; b.z = q;
+				s = __fadd_rn(s, v[g].z); q = CONTRACT ? __fmaf_rn(v[g].z, v[g].z, q) : __fadd_rn(q, __fmul_rn(v[g].z, v[g].z)); a.w = s; b.w = q;
+				s = __fadd_rn(s, v[g].w); q = CONTRACT ? __fmaf_rn(v[g].w, v[g].w, q) : __fadd_rn(q, __fmul_rn(v[g].w, v[g].w)); s0 = s; q0 = q;
+				*reinterpret_cast<float4 *>(ps + t + 4 * g) = a;
+				*reinterpret_cast<float4 *>(pss + t + 4 * g) = b;
+			}
+		}
+	}
+	// tail / unaligned path: scalar
+	ps[t] = s; pss[t] = q;
+	for (; t < len; ++t) {
+		const float xv = __ldg(x + t);
+		s = __fadd_rn(s, xv);
+		q = CONTRACT ? __fmaf_rn(xv, xv, q) : __fadd_rn(q, __fmul_rn(xv, xv));
+		ps[t + 1] = s; pss[t + 1] = q;
+	}
+}
 
-// t-statistic of revent.c:50-69 for one window, from prefix values around position p.
+// ---------------------------------------------------------------------------------------------------
+// t-statistic of revent.c:50-69 for one window, from prefix values around position p:
 //   s_m = ps[p-w], s_0 = ps[p], s_p = ps[p+w]  (same for the squares)
+// ---------------------------------------------------------------------------------------------------
 template <bool CONTRACT>
 __device__ __forceinline__ float tstat_point(float s_m, float s_0, float s_p, float q_m, float q_0, float q_p, float wf)
 {
@@ -52,160 +109,113 @@ __device__ __forceinline__ float tstat_point(float s_m, float s_0, float s_p, fl
 	return __double2float_rn(__ddiv_rn(fabs((double)delta_mean), __dsqrt_rn((double)vw)));
 }
 
+// One thread per (chunk, position).  Grid: x = position tiles, y = chunk.
+template <bool CONTRACT>
+__global__ void __launch_bounds__(256)
+k_tstat(const uint32_t *__restrict__ chunk_len, const float *__restrict__ ps_base, const float *__restrict__ pss_base,
+        uint32_t pstride, float *__restrict__ t1_base, float *__restrict__ t2_base, uint32_t tstride, uint32_t w1, uint32_t w2)
+{
+	const uint32_t c = blockIdx.y;
+	const uint32_t len = chunk_len[c];
+	const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+	if (p >= len) return;
+	const float *__restrict__ ps = ps_base + (size_t)c * pstride;
+	const float *__restrict__ pss = pss_base + (size_t)c * pstride;
+	float v1 = 0.0f, v2 = 0.0f;
+	const float s_0 = __ldg(ps + p), q_0 = __ldg(pss + p);
+	if (len >= 2u * w1 && w1 >= 2u && p >= w1 && p + w1 <= len)          // :46, :50
+		v1 = tstat_point<CONTRACT>(__ldg(ps + p - w1), s_0, __ldg(ps + p + w1), __ldg(pss + p - w1), q_0, __ldg(pss + p + w1), (float)w1);
+	if (len >= 2u * w2 && w2 >= 2u && p >= w2 && p + w2 <= len)
+		v2 = tstat_point<CONTRACT>(__ldg(ps + p - w2), s_0, __ldg(ps + p + w2), __ldg(pss + p - w2), q_0, __ldg(pss + p + w2), (float)w2);
+	t1_base[(size_t)c * tstride + p] = v1;
+	t2_base[(size_t)c * tstride + p] = v2;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// k_peaks: gen_peaks, revent.c:77-138
+// ---------------------------------------------------------------------------------------------------
 struct Detector {
 	uint32_t masked_to;
 	int peak_pos;
 	float peak_value;
 	int valid_peak;
-	float peak_ps;     // prefix_sum[peak_pos], captured when peak_pos is assigned (gen_events needs it later)
 };
-
-struct EventAcc {
-	float l_ps, l_peak;         // revent.c:155
-	double sum, sum2;           // :143
-	uint32_t n_peaks;
-	uint32_t pend_pos; float pend_ps;   // the most recent peak; becomes an event only when another peak follows
-	float *out;                 // raw (un-normalised) events of this chunk
-};
-
-// gen_events consumes peaks[0 .. n_ev-2] in emission order and closes the last event at s_len
-// (revent.c:160-172): the final peak of a chunk never bounds an event.  n_ev == n_peaks because the
-// filter of :145-147 (0 < peaks[i] < s_len) always holds: position 0 is never examined
-// (masked_to(0) >= 0, :91) and positions are < s_len by construction.
-__device__ __forceinline__ void emit_peak(EventAcc &E, uint32_t pos, float ps_at)
-{
-	if (E.n_peaks > 0) {
-		const float e = __fdiv_rn(__fsub_rn(E.pend_ps, E.l_ps), __fsub_rn(__uint2float_rn(E.pend_pos), E.l_peak)); // :162
-		E.out[E.n_peaks - 1] = e;
-		E.sum = __dadd_rn(E.sum, (double)e);                      // :163
-		E.sum2 = __dadd_rn(E.sum2, (double)__fmul_rn(e, e));      // :164 (float product, then widened)
-		E.l_ps = E.pend_ps;                                       // :165
-		E.l_peak = __uint2float_rn(E.pend_pos);                   // :166
-	}
-	E.pend_pos = pos; E.pend_ps = ps_at;
-	E.n_peaks++;
-}
 
 // One detector step, revent.c:89-133.  SHORT selects the masking side effect of :113-120.
 template <bool SHORT>
-__device__ __forceinline__ void detector_step(Detector &d, Detector &long_d, uint32_t i, float v, float ps_i,
-                                              float threshold, uint32_t window_length, float peak_height, EventAcc &E)
+__device__ __forceinline__ void detector_step(Detector &d, Detector &long_d, uint32_t i, float v, float threshold,
+                                              uint32_t window_length, float peak_height, uint32_t *__restrict__ peaks, uint32_t &n_peaks)
 {
-	if (d.masked_to >= i) return;                                 // :91
+	if (d.masked_to >= i) return;                                 // :91 (unsigned compare: i = 0 is always skipped)
 	if (d.peak_pos == -1) {                                       // :94
 		if (v < d.peak_value) d.peak_value = v;
-		else if (__fsub_rn(v, d.peak_value) > peak_height) { d.peak_value = v; d.peak_pos = (int)i; d.peak_ps = ps_i; }
+		else if (__fsub_rn(v, d.peak_value) > peak_height) { d.peak_value = v; d.peak_pos = (int)i; }
 	} else {
-		if (v > d.peak_value) { d.peak_value = v; d.peak_pos = (int)i; d.peak_ps = ps_i; }   // :107-111
+		if (v > d.peak_value) { d.peak_value = v; d.peak_pos = (int)i; }   // :107-111
 		if (SHORT && d.peak_value > threshold) {                  // :113-120
 			long_d.masked_to = (uint32_t)d.peak_pos + window_length;
 			long_d.peak_pos = -1; long_d.peak_value = FLT_MAX; long_d.valid_peak = 0;
 		}
 		if (__fsub_rn(d.peak_value, v) > peak_height && d.peak_value > threshold) d.valid_peak = 1; // :122
 		if (d.valid_peak && (i - (uint32_t)d.peak_pos) > window_length / 2) {                         // :126
-			emit_peak(E, (uint32_t)d.peak_pos, d.peak_ps);
+			peaks[n_peaks++] = (uint32_t)d.peak_pos;              // :128
 			d.peak_pos = -1; d.peak_value = v; d.valid_peak = 0;
 		}
 	}
 }
 
-template <int W1, int W2, bool CONTRACT>
-__global__ void __launch_bounds__(128)
-k_events_scan(const float *__restrict__ sig, const uint64_t *__restrict__ chunk_off,
-              const uint32_t *__restrict__ chunk_len, uint32_t n_chunks, EvParams prm,
-              float *__restrict__ raw, uint32_t raw_stride, uint32_t *__restrict__ n_ev_out,
-              EvChunkStat *__restrict__ stat_out)
+__global__ void __launch_bounds__(32)
+k_peaks(const uint32_t *__restrict__ chunk_len, uint32_t n_chunks, const float *__restrict__ t1_base,
+        const float *__restrict__ t2_base, uint32_t tstride, EvParams prm, uint32_t *__restrict__ peaks_base,
+        uint32_t peak_stride, uint32_t *__restrict__ n_peaks_out)
 {
-	constexpr int RING = RingSize<W2>::value;
-	constexpr int MASK = RING - 1;
 	const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
 	if (c >= n_chunks) return;
-	const uint32_t s_len = chunk_len[c];
-	const float *__restrict__ x = sig + chunk_off[c];
-	const bool vec_ok = ((reinterpret_cast<uintptr_t>(x) & 15u) == 0);
-
-	float rs[RING], rq[RING];                                    // prefix_sum / prefix_sum_square ring, index = position & MASK
-#pragma unroll
-	for (int k = 0; k < RING; ++k) { rs[k] = 0.0f; rq[k] = 0.0f; }
-	float ps = 0.0f, pss = 0.0f;                                 // :26-27
-
-	Detector sd = { 0u, -1, FLT_MAX, 0, 0.0f };                   // :198-202
-	Detector ld = { 0u, -1, FLT_MAX, 0, 0.0f };
-	EventAcc E;
-	E.l_ps = 0.0f; E.l_peak = 0.0f; E.sum = 0.0; E.sum2 = 0.0; E.n_peaks = 0; E.pend_pos = 0; E.pend_ps = 0.0f;
-	E.out = raw + (size_t)c * raw_stride;
-
-	const bool t1_on = (s_len >= 2u * W1) && (W1 >= 2);           // :46
-	const bool t2_on = (s_len >= 2u * W2) && (W2 >= 2);
-	const float w1f = (float)W1, w2f = (float)W2;
-
-	// iteration t: (A) extend the prefix sums to position t+1, (B) step the detectors at p = t+1-W2
-	const uint32_t t_end = s_len + (uint32_t)W2 - 1u;             // last t has p = s_len-1
-	for (uint32_t t0 = 0; t0 < t_end; t0 += RING) {
-		float xin[RING];
-		if (vec_ok && t0 + RING <= s_len) {
-#pragma unroll
-			for (int k = 0; k < RING / 4; ++k) {
-				const float4 v = __ldg(reinterpret_cast<const float4 *>(x + t0) + k);
-				xin[4 * k] = v.x; xin[4 * k + 1] = v.y; xin[4 * k + 2] = v.z; xin[4 * k + 3] = v.w;
-			}
-		} else {
-#pragma unroll
-			for (int k = 0; k < RING; ++k) xin[k] = (t0 + k < s_len) ? __ldg(x + t0 + k) : 0.0f;
-		}
-#pragma unroll
-		for (int u = 0; u < RING; ++u) {
-			const uint32_t t = t0 + u;                             // t & MASK == u  (t0 is a multiple of RING)
-			if (t >= t_end) break;
-			if (t < s_len) {                                       // (A) revent.c:28-31
-				const float xv = xin[u];
-				ps = __fadd_rn(ps, xv);
-				pss = CONTRACT ? __fmaf_rn(xv, xv, pss) : __fadd_rn(pss, __fmul_rn(xv, xv));
-				rs[(u + 1) & MASK] = ps; rq[(u + 1) & MASK] = pss;
-			}
-			if (t + 1u >= (uint32_t)W2) {                          // (B)
-				const uint32_t p = t + 1u - (uint32_t)W2;          // position & MASK == (u + 1 - W2) & MASK
-				constexpr int dummy = 0; (void)dummy;
-				const int ip = (u + 1 - W2) & MASK;
-				const float s_0 = rs[ip], q_0 = rq[ip];
-				float v1 = 0.0f, v2 = 0.0f;
-				if (t1_on && p >= (uint32_t)W1 && p + (uint32_t)W1 <= s_len)
-					v1 = tstat_point<CONTRACT>(rs[(ip - W1) & MASK], s_0, rs[(ip + W1) & MASK],
-					                           rq[(ip - W1) & MASK], q_0, rq[(ip + W1) & MASK], w1f);
-				if (t2_on && p >= (uint32_t)W2 && p + (uint32_t)W2 <= s_len)
-					v2 = tstat_point<CONTRACT>(rs[(ip - W2) & MASK], s_0, rs[(ip + W2) & MASK],
-					                           rq[(ip - W2) & MASK], q_0, rq[(ip + W2) & MASK], w2f);
-				detector_step<true>(sd, ld, p, v1, s_0, prm.thr1, (uint32_t)W1, prm.peak_height, E);
-				detector_step<false>(ld, ld, p, v2, s_0, prm.thr2, (uint32_t)W2, prm.peak_height, E);
-			}
+	const uint32_t len = chunk_len[c];
+	const float *__restrict__ t1 = t1_base + (size_t)c * tstride;
+	const float *__restrict__ t2 = t2_base + (size_t)c * tstride;
+	uint32_t *__restrict__ peaks = peaks_base + (size_t)c * peak_stride;
+	Detector sd = { 0u, -1, FLT_MAX, 0 };                          // :198-202
+	Detector ld = { 0u, -1, FLT_MAX, 0 };
+	uint32_t n_peaks = 0;
+	uint32_t i = 0;
+	// tstride % 4 == 0 and the tracks are 16-byte aligned: stream them as float4, two groups ahead
+	const uint32_t len4 = len & ~3u;
+	if (len4 >= 8) {
+		float4 a = __ldcs(reinterpret_cast<const float4 *>(t1)), b = __ldcs(reinterpret_cast<const float4 *>(t2));
+		float4 a1 = __ldcs(reinterpret_cast<const float4 *>(t1 + 4)), b1 = __ldcs(reinterpret_cast<const float4 *>(t2 + 4));
+		for (; i < len4; i += 4) {
+			float4 a2 = a1, b2 = b1;
+			if (i + 8 < len4) { a2 = __ldcs(reinterpret_cast<const float4 *>(t1 + i + 8)); b2 = __ldcs(reinterpret_cast<const float4 *>(t2 + i + 8)); }
+			detector_step<true>(sd, ld, i, a.x, prm.thr1, prm.w1, prm.peak_height, peaks, n_peaks);
+			detector_step<false>(ld, ld, i, b.x, prm.thr2, prm.w2, prm.peak_height, peaks, n_peaks);
+			detector_step<true>(sd, ld, i + 1, a.y, prm.thr1, prm.w1, prm.peak_height, peaks, n_peaks);
+			detector_step<false>(ld, ld, i + 1, b.y, prm.thr2, prm.w2, prm.peak_height, peaks, n_peaks);
+			detector_step<true>(sd, ld, i + 2, a.z, prm.thr1, prm.w1, prm.peak_height, peaks, n_peaks);
+			detector_step<false>(ld, ld, i + 2, b.z, prm.thr2, prm.w2, prm.peak_height, peaks, n_peaks);
+			detector_step<true>(sd, ld, i + 3, a.w, prm.thr1, prm.w1, prm.peak_height, peaks, n_peaks);
+			detector_step<false>(ld, ld, i + 3, b.w, prm.thr2, prm.w2, prm.peak_height, peaks, n_peaks);
+			a = a1; b = b1; a1 = a2; b1 = b2;
 		}
 	}
-
-	uint32_t n_ev = 0;
-	double mean = 0.0, stdv = 1.0;
-	if (E.n_peaks > 0) {                                          // :206
-		n_ev = E.n_peaks;
-		const float e = __fdiv_rn(__fsub_rn(ps, E.l_ps), __fsub_rn(__uint2float_rn(s_len), E.l_peak)); // :172 (ps == prefix_sum[s_len])
-		E.out[n_ev - 1] = e;
-		E.sum = __dadd_rn(E.sum, (double)e);
-		E.sum2 = __dadd_rn(E.sum2, (double)__fmul_rn(e, e));
-		mean = __ddiv_rn(E.sum, (double)n_ev);                     // :179
-		const double q = __ddiv_rn(E.sum2, (double)n_ev);
-		const double var = CONTRACT ? __fma_rn(-mean, mean, q) : __dsub_rn(q, __dmul_rn(mean, mean)); // :180
-		stdv = __dsqrt_rn(var);
+	for (; i < len; ++i) {
+		detector_step<true>(sd, ld, i, __ldg(t1 + i), prm.thr1, prm.w1, prm.peak_height, peaks, n_peaks);
+		detector_step<false>(ld, ld, i, __ldg(t2 + i), prm.thr2, prm.w2, prm.peak_height, peaks, n_peaks);
 	}
-	n_ev_out[c] = n_ev;
-	stat_out[c].mean = mean; stat_out[c].stdv = stdv;
+	n_peaks_out[c] = n_peaks;      // == number of events (see k_finish)
 }
 
+// ---------------------------------------------------------------------------------------------------
 // Exclusive prefix sum of per-chunk event counts -> CSR offsets (single CTA; n is the number of
-// chunks of one batch, the scan is a few microseconds of plumbing next to the detector).
-__global__ void __launch_bounds__(1024) k_exclusive_scan_u32(const uint32_t *__restrict__ in, uint64_t *__restrict__ out, uint32_t n)
+// chunks of one sub-batch).  With chained != 0 the scan continues from out[0] (the total the
+// previous sub-batch left there).
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) k_exclusive_scan_u32(const uint32_t *__restrict__ in, uint64_t *__restrict__ out, uint32_t n, int chained)
 {
 	__shared__ uint64_t warp_tot[32];
 	__shared__ uint64_t carry_s, block_tot;
 	const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-	if (threadIdx.x == 0) carry_s = 0;
+	if (threadIdx.x == 0) carry_s = chained ? out[0] : 0;
 	__syncthreads();
 	for (uint32_t base = 0; base < n; base += blockDim.x) {
 		const uint32_t idx = base + threadIdx.x;
@@ -231,60 +241,109 @@ __global__ void __launch_bounds__(1024) k_exclusive_scan_u32(const uint32_t *__r
 	if (threadIdx.x == 0) out[n] = carry_s;
 }
 
-// (ev - mean) / std_dev of revent.c:182-184, written to the CSR output; one warp per chunk.
-__global__ void __launch_bounds__(256)
-k_events_normalise(const float *__restrict__ raw, uint32_t raw_stride, const uint32_t *__restrict__ n_ev,
-                   const EvChunkStat *__restrict__ stat, const uint64_t *__restrict__ ev_off, uint32_t n_chunks,
-                   float *__restrict__ ev_out, uint64_t ev_cap)
+// ---------------------------------------------------------------------------------------------------
+// k_finish: gen_events, revent.c:140-188.  One warp per chunk.
+//
+// gen_events consumes peaks[0 .. n_ev-2] in emission order and closes the last event at s_len
+// (:160-172): the final peak of a chunk never bounds an event.  n_ev == n_peaks because the filter
+// of :145-147 (0 < peaks[i] < s_len) always holds: position 0 is never examined (masked_to(0) >= 0,
+// :91) and positions are < s_len by construction.
+// ---------------------------------------------------------------------------------------------------
+template <bool CONTRACT>
+__global__ void __launch_bounds__(128)
+k_finish(const uint32_t *__restrict__ chunk_len, uint32_t n_chunks, const float *__restrict__ ps_base, uint32_t pstride,
+         const uint32_t *__restrict__ peaks_base, uint32_t peak_stride, const uint32_t *__restrict__ n_peaks_in,
+         const uint64_t *__restrict__ ev_off, float *__restrict__ ev_out, uint64_t ev_cap, float *__restrict__ raw_base,
+         uint32_t *__restrict__ ev_pos)
 {
-	const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const uint32_t c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
 	const int lane = threadIdx.x & 31;
-	if (warp >= n_chunks) return;
-	const uint32_t n = n_ev[warp];
-	if (n == 0) return;
-	const double mean = stat[warp].mean, sd = stat[warp].stdv;
-	const float *__restrict__ r = raw + (size_t)warp * raw_stride;
-	const uint64_t off = ev_off[warp];
-	for (uint32_t k = lane; k < n; k += 32)
-		if (off + k < ev_cap)
-			ev_out[off + k] = __double2float_rn(__ddiv_rn(__dsub_rn((double)r[k], mean), sd));
+	if (c >= n_chunks) return;
+	const uint32_t n_ev = n_peaks_in[c];
+	if (n_ev == 0) return;                                         // detect_events returns NULL, *n untouched (:205-206)
+	const uint32_t len = chunk_len[c];
+	const float *__restrict__ ps = ps_base + (size_t)c * pstride;
+	const uint32_t *__restrict__ peaks = peaks_base + (size_t)c * peak_stride;
+	float *__restrict__ raw = raw_base + (size_t)c * peak_stride;  // un-normalised means (scratch, L2-resident)
+	// event k: (ps[end_k] - ps[start_k]) / ((float)end_k - (float)start_k), end_k = peaks[k] (k < n_ev-1) or len,
+	// start_k = peaks[k-1] or 0                                   :160-172
+	for (uint32_t k = lane; k < n_ev; k += 32) {
+		const uint32_t e_pos = (k + 1 < n_ev) ? peaks[k] : len;
+		const uint32_t s_pos = (k > 0) ? peaks[k - 1] : 0u;
+		const float l_ps = (k > 0) ? __ldg(ps + s_pos) : 0.0f;
+		const float l_peak = (k > 0) ? __uint2float_rn(s_pos) : 0.0f;
+		raw[k] = __fdiv_rn(__fsub_rn(__ldg(ps + e_pos), l_ps), __fsub_rn(__uint2float_rn(e_pos), l_peak));
+	}
+	__syncwarp();
+	// sum / sum2 in array order, fp64 (:163-164, :173-174); lanes fetch 32 values at a time, lane 0 accumulates
+	double sum = 0.0, sum2 = 0.0;
+	for (uint32_t base = 0; base < n_ev; base += 32) {
+		const float mine = (base + lane < n_ev) ? raw[base + lane] : 0.0f;
+		const uint32_t cnt = min(32u, n_ev - base);
+		for (uint32_t t = 0; t < cnt; ++t) {
+			const float e = __shfl_sync(0xffffffffu, mine, (int)t);
+			sum = __dadd_rn(sum, (double)e);
+			sum2 = __dadd_rn(sum2, (double)__fmul_rn(e, e));       // float product, then widened (:164)
+		}
+	}
+	const double mean = __ddiv_rn(sum, (double)n_ev);              // :179
+	const double q = __ddiv_rn(sum2, (double)n_ev);
+	const double var = CONTRACT ? __fma_rn(-mean, mean, q) : __dsub_rn(q, __dmul_rn(mean, mean));   // :180
+	const double sd = __dsqrt_rn(var);
+	const uint64_t off = ev_off[c];
+	for (uint32_t k = lane; k < n_ev; k += 32)
+		if (off + k < ev_cap) {
+			ev_out[off + k] = __double2float_rn(__ddiv_rn(__dsub_rn((double)raw[k], mean), sd));        // :183
+			if (ev_pos) ev_pos[off + k] = (k > 0) ? peaks[k - 1] : 0u;   // first sample of the event (not part of the reference's output)
+		}
 }
 
-bool events_windows_supported(uint32_t w1, uint32_t w2) { return (w1 == 3 && w2 == 6) || (w1 == 7 && w2 == 14); }
+// ---------------------------------------------------------------------------------------------------
+bool events_windows_supported(uint32_t w1, uint32_t w2) { return w1 >= 1 && w2 >= 1 && w1 < 4096 && w2 < 4096; }
 
-cudaError_t launch_events_scan(const float *sig, const uint64_t *chunk_off, const uint32_t *chunk_len,
-                               uint32_t n_chunks, const EvParams &p, int contract, float *raw,
-                               uint32_t raw_stride, uint32_t *n_ev, EvChunkStat *stat, cudaStream_t s)
+void events_scratch_layout(uint32_t max_len, const EvParams &p, EvScratch *s)
+{
+	s->pstride = ((max_len + 1 + 3) & ~3u) + 4;
+	s->tstride = ((max_len + 3) & ~3u) + 4;
+	// a detector emits at i >= peak_pos + w/2 + 1 and can only start its next peak at a later sample,
+	// so peaks of one detector are >= w/2 + 2 apart
+	s->peak_stride = max_len / (p.w1 / 2 + 2) + max_len / (p.w2 / 2 + 2) + 4;
+	s->floats_per_chunk = 2 * (size_t)s->pstride + 2 * (size_t)s->tstride + 2 * (size_t)s->peak_stride;
+}
+
+cudaError_t launch_events(const float *sig, const uint64_t *chunk_off, const uint32_t *chunk_len, uint32_t n_chunks,
+                          uint32_t max_len, const EvParams &p, int contract, float *scratch, uint32_t *n_ev,
+                          uint64_t *ev_off, int chained, float *ev_out, uint64_t ev_cap, uint32_t *ev_pos, cudaStream_t s,
+                          cudaEvent_t after_detect)
 {
 	if (n_chunks == 0) return cudaSuccess;
-	const int threads = 128;
-	const unsigned blocks = (n_chunks + threads - 1) / threads;
-#define RA_EV_LAUNCH(W1, W2)                                                                                       \
-	do {                                                                                                           \
-		if (contract) k_events_scan<W1, W2, true><<<blocks, threads, 0, s>>>(sig, chunk_off, chunk_len, n_chunks, p, raw, raw_stride, n_ev, stat); \
-		else k_events_scan<W1, W2, false><<<blocks, threads, 0, s>>>(sig, chunk_off, chunk_len, n_chunks, p, raw, raw_stride, n_ev, stat);         \
-	} while (0)
-	if (p.w1 == 3 && p.w2 == 6) RA_EV_LAUNCH(3, 6);
-	else if (p.w1 == 7 && p.w2 == 14) RA_EV_LAUNCH(7, 14);
-	else return cudaErrorInvalidValue;
-#undef RA_EV_LAUNCH
+	EvScratch L; events_scratch_layout(max_len, p, &L);
+	float *ps = scratch;
+	float *pss = ps + (size_t)n_chunks * L.pstride;
+	float *t1 = pss + (size_t)n_chunks * L.pstride;
+	float *t2 = t1 + (size_t)n_chunks * L.tstride;
+	uint32_t *peaks = reinterpret_cast<uint32_t *>(t2 + (size_t)n_chunks * L.tstride);
+	float *raw = reinterpret_cast<float *>(peaks + (size_t)n_chunks * L.peak_stride);
+	const dim3 tgrid((max_len + 255) / 256, n_chunks);
+	if (contract) {
+		k_prefix<true><<<(n_chunks + 63) / 64, 64, 0, s>>>(sig, chunk_off, chunk_len, n_chunks, ps, pss, L.pstride);
+		k_tstat<true><<<tgrid, 256, 0, s>>>(chunk_len, ps, pss, L.pstride, t1, t2, L.tstride, p.w1, p.w2);
+	} else {
+		k_prefix<false><<<(n_chunks + 63) / 64, 64, 0, s>>>(sig, chunk_off, chunk_len, n_chunks, ps, pss, L.pstride);
+		k_tstat<false><<<tgrid, 256, 0, s>>>(chunk_len, ps, pss, L.pstride, t1, t2, L.tstride, p.w1, p.w2);
+	}
+	k_peaks<<<(n_chunks + 31) / 32, 32, 0, s>>>(chunk_len, n_chunks, t1, t2, L.tstride, p, peaks, L.peak_stride, n_ev);
+	if (after_detect) cudaEventRecord(after_detect, s);
+	k_exclusive_scan_u32<<<1, 1024, 0, s>>>(n_ev, ev_off, n_chunks, chained);
+	const unsigned fblocks = (unsigned)(((uint64_t)n_chunks * 32 + 127) / 128);
+	if (contract) k_finish<true><<<fblocks, 128, 0, s>>>(chunk_len, n_chunks, ps, L.pstride, peaks, L.peak_stride, n_ev, ev_off, ev_out, ev_cap, raw, ev_pos);
+	else k_finish<false><<<fblocks, 128, 0, s>>>(chunk_len, n_chunks, ps, L.pstride, peaks, L.peak_stride, n_ev, ev_off, ev_out, ev_cap, raw, ev_pos);
 	return cudaGetLastError();
 }
 
 cudaError_t launch_exclusive_scan_u32(const uint32_t *in, uint64_t *out, uint32_t n, cudaStream_t s)
 {
-	k_exclusive_scan_u32<<<1, 1024, 0, s>>>(in, out, n);
-	return cudaGetLastError();
-}
-
-cudaError_t launch_events_normalise(const float *raw, uint32_t raw_stride, const uint32_t *n_ev,
-                                    const EvChunkStat *stat, const uint64_t *ev_off, uint32_t n_chunks,
-                                    float *ev_out, uint64_t ev_cap, cudaStream_t s)
-{
-	if (n_chunks == 0) return cudaSuccess;
-	const int threads = 256;
-	const unsigned blocks = (unsigned)(((uint64_t)n_chunks * 32 + threads - 1) / threads);
-	k_events_normalise<<<blocks, threads, 0, s>>>(raw, raw_stride, n_ev, stat, ev_off, n_chunks, ev_out, ev_cap);
+	k_exclusive_scan_u32<<<1, 1024, 0, s>>>(in, out, n, 0);
 	return cudaGetLastError();
 }
 

@@ -12,21 +12,23 @@ struct EvParams {
 	float thr1, thr2, peak_height;
 };
 
-// Per-chunk result of the scan kernel, consumed by the normalise/compact kernel.
-struct EvChunkStat {
-	double mean, stdv;
+// Scratch layout of one sub-batch of the event pipeline (all strides in floats, multiples of 4).
+struct EvScratch {
+	uint32_t pstride, tstride, peak_stride;
+	size_t floats_per_chunk;
 };
 
 // ---- launchers (events.cu) ---------------------------------------------------------------------
-// raw: [n_chunks][raw_stride] floats of un-normalised event means; n_ev: events per chunk.
-cudaError_t launch_events_scan(const float *sig, const uint64_t *chunk_off, const uint32_t *chunk_len,
-                               uint32_t n_chunks, const EvParams &p, int contract, float *raw,
-                               uint32_t raw_stride, uint32_t *n_ev, EvChunkStat *stat, cudaStream_t s);
+void events_scratch_layout(uint32_t max_len, const EvParams &p, EvScratch *s);
+// Runs the five K1 kernels for n_chunks chunks.  scratch holds n_chunks * floats_per_chunk floats.
+// ev_off: n_chunks+1 CSR offsets; with chained != 0 the scan continues from the value already in ev_off[0].
+cudaError_t launch_events(const float *sig, const uint64_t *chunk_off, const uint32_t *chunk_len, uint32_t n_chunks,
+                          uint32_t max_len, const EvParams &p, int contract, float *scratch, uint32_t *n_ev,
+                          uint64_t *ev_off, int chained, float *ev_out, uint64_t ev_cap, uint32_t *ev_pos, cudaStream_t s,
+                          cudaEvent_t after_detect);
 cudaError_t launch_exclusive_scan_u32(const uint32_t *in, uint64_t *out, uint32_t n, cudaStream_t s);
-cudaError_t launch_events_normalise(const float *raw, uint32_t raw_stride, const uint32_t *n_ev,
-                                    const EvChunkStat *stat, const uint64_t *ev_off, uint32_t n_chunks,
-                                    float *ev_out, uint64_t ev_cap, cudaStream_t s);
 bool events_windows_supported(uint32_t w1, uint32_t w2);
+constexpr int kEventKernels = 5;
 
 // ---- launchers (dtw.cu) ------------------------------------------------------------------------
 struct DtwLaunch {
@@ -52,5 +54,27 @@ cudaError_t launch_path_compact(const uint32_t *slot_i, const uint32_t *slot_j, 
                                 const uint64_t *path_off, uint32_t n_items, uint32_t *out_i, uint32_t *out_j,
                                 float *out_d, cudaStream_t s);
 uint32_t dtw_generic_smem_ring_cap();
+
+// ---- launcher (chains.cu) ----------------------------------------------------------------------
+struct ChainLaunch {
+	const float *read_arena, *ref_arena;
+	const ra_anchor_t *anchors;
+	const ra_chain_t *chains;
+	const uint32_t *group_first;     // n_groups + 1 chain indices
+	uint32_t n_groups;
+	uint32_t border, fill, fp_contract;
+	float band_frac, match_bonus, min_dtw_score;
+	int min_score_mode;
+	const float *min_score;          // per chain, mode 0; may be null
+	float *score;
+	uint8_t *keep;                   // may be null
+	uint32_t *work_counter;
+	float *ring_scratch;             // HBM rings for parts wider than the shared-memory ring; may be null
+	uint32_t ring_cap;
+	uint64_t *cells;                 // [issued, useful]; may be null
+	uint32_t *need_cap;              // receives the ring capacity a skipped part needed (0 = none skipped)
+};
+constexpr int kChainCtasPerSm = 6;
+cudaError_t launch_chain_eval(const ChainLaunch &L, int n_sm, cudaStream_t s);
 
 } // namespace ra

@@ -56,6 +56,7 @@ class Reads:
     ref_start: np.ndarray    # int64 first base on the sampled strand's coordinate
     strand: np.ndarray       # uint8
     n_bases: np.ndarray
+    base_start: list         # per read: first sample of every base (int64), truth for anchor placement
 
 
 def simulate_reads(ref: np.ndarray, n_reads: int, seed: int = 2, mean_len: float = 8000.0, max_chunks: int = MAX_NUM_CHUNK,
@@ -73,14 +74,14 @@ def simulate_reads(ref: np.ndarray, n_reads: int, seed: int = 2, mean_len: float
     nb = np.minimum(nb, max_bases)
     strand = rng.integers(0, 2, n_reads).astype(np.uint8)
     start = (rng.random(n_reads) * (L - K + 1 - nb)).astype(np.int64)
-    sigs, lens = [], []
+    sigs, lens, bstarts = [], [], []
     for r in range(n_reads):
         ranks = (fwd_rank if strand[r] == 0 else rev_rank)[start[r]:start[r] + nb[r]]
         dwell = 1 + rng.poisson(7.9, nb[r])
         lv = np.repeat(mm[ranks], dwell); sd = np.repeat(ms[ranks], dwell)
         s = lv + rng.normal(0.0, 1.0, len(lv)) * sd
         s = np.clip(s, 31.0, 199.0).astype(np.float32)[: max_chunks * CHUNK_SIZE]
-        sigs.append(s); lens.append(len(s))
+        sigs.append(s); lens.append(len(s)); bstarts.append(np.concatenate(([0], np.cumsum(dwell)[:-1])))
     lens = np.array(lens, np.uint32)
     padded = (lens.astype(np.int64) + 3) // 4 * 4
     off = np.zeros(n_reads + 1, np.uint64)
@@ -88,7 +89,7 @@ def simulate_reads(ref: np.ndarray, n_reads: int, seed: int = 2, mean_len: float
     sig = np.zeros(int(off[-1]), np.float32)
     for r in range(n_reads):
         sig[int(off[r]):int(off[r]) + lens[r]] = sigs[r]
-    return Reads(sig, off, lens, start, strand, nb)
+    return Reads(sig, off, lens, start, strand, nb, bstarts)
 
 
 def chunk_table(read_off: np.ndarray, read_len: np.ndarray, chunk_size: int = CHUNK_SIZE, max_chunks: int = MAX_NUM_CHUNK):
@@ -139,3 +140,30 @@ def synth_chains(n_read_events: np.ndarray, read_ev_off: np.ndarray, ref_len: in
     if not chains:
         return np.zeros(0, ANCHOR_DTYPE), np.zeros(0, CHAIN_DTYPE)
     return np.concatenate(anchors), np.concatenate(chains)
+
+
+def truth_chain(ev_sample_pos: np.ndarray, base_start: np.ndarray, ref_start: int, rng, gap_p: float = 0.2):
+    """Anchors of the chain a perfect seeder would produce: read events q (2+Geom(gap_p) apart) paired with the
+    reference k-mer position of the base being sequenced when event q starts.  Positions strictly increase in
+    both coordinates (rmap.cpp:456-465); returned right-to-left like traceback_chains."""
+    ne = len(ev_sample_pos)
+    if ne < 12:
+        return None
+    gaps = 1 + rng.geometric(gap_p, size=ne)
+    q = np.cumsum(gaps); q = q[q < ne - 1]
+    if len(q) < 2:
+        return None
+    base = np.searchsorted(base_start, ev_sample_pos[q], "right") - 1
+    t = ref_start + base
+    keep = np.concatenate(([True], np.diff(t) > 0))
+    # drop anchors whose target does not advance past the last kept one
+    last = -1; sel = []
+    for k in range(len(q)):
+        if t[k] > last:
+            sel.append(k); last = t[k]
+    q = q[sel]; t = t[sel]
+    if len(q) < 2:
+        return None
+    a = np.zeros(len(q), ANCHOR_DTYPE)
+    a["query_position"] = q[::-1]; a["target_position"] = t[::-1]
+    return a

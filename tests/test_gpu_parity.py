@@ -67,16 +67,40 @@ def test_events_single_call_and_empty(ctx, oracle):
     assert len(ev) == 0 and off[0] == 0
 
 
-def test_events_unsupported_windows_fail_loudly(ctx):
+@pytest.mark.parametrize("w1,w2,t1,t2", [(7, 14, 2.5, 9.0), (4, 9, 3.0, 2.0), (2, 5, 4.0, 2.5), (1, 6, 4.3, 2.6)])
+def test_events_other_windows(ctx, oracle, w1, w2, t1, t2):
+    """Detector windows are run-time options (RNA uses 7/14, roptions.c:56-60); w < 2 silences a track (revent.c:46)."""
     import rawalign_b200 as ra
-    opt = ra.ri_mapopt_init(); opt.window_length1 = 4; opt.window_length2 = 9
+    from oracle import EvOpt
+    from oracle.gen_golden import sim_signal
+    rng = np.random.default_rng(50 + w1)
+    lens = np.array([4000, 4000, 1234, 27, 13, 4000], np.uint32)
+    offs = np.zeros(len(lens), np.uint64); offs[1:] = np.cumsum((lens[:-1] + 3) // 4 * 4)
+    sig = np.zeros(int(offs[-1]) + 4000, np.float32)
+    for k in range(len(lens)):
+        sig[int(offs[k]):int(offs[k]) + lens[k]] = sim_signal(int(lens[k]) + 40, rng)[:lens[k]]
+    opt = ra.ri_mapopt_init(); opt.window_length1 = w1; opt.window_length2 = w2; opt.threshold1 = t1; opt.threshold2 = t2
     ctx.set_opt(opt)
     try:
-        with pytest.raises(ra.RawAlignError) as e:
-            ctx.detect_events(np.zeros(100, np.float32))
-        assert e.value.code == -5
+        ev, off = ctx.detect_events_batch(sig, offs, lens)
     finally:
         ctx.set_opt(ra.ri_mapopt_init())
+    ev_o, off_o = oracle.detect_events_batch(sig, offs, lens, EvOpt(w1, w2, t1, t2, 1.0))
+    assert np.array_equal(off, off_o) and np.array_equal(bits(ev), bits(ev_o))
+
+
+def test_events_many_chunks_sub_batched(ctx, oracle):
+    """More chunks than one launch group (32768): the CSR scan must chain across sub-batches."""
+    rng = np.random.default_rng(77)
+    n = 40_000
+    lens = rng.integers(40, 120, n).astype(np.uint32)
+    offs = np.zeros(n, np.uint64); offs[1:] = np.cumsum((lens[:-1] + 3) // 4 * 4)
+    lv = np.repeat(rng.normal(90, 13, (int(offs[-1]) + 200) // 8 + 2), 8)[: int(offs[-1]) + 128]
+    sig = np.clip(lv + rng.normal(0, 2, len(lv)), 31, 199).astype(np.float32)
+    ev, off = ctx.detect_events_batch(sig, offs, lens)
+    ev_o, off_o = oracle.detect_events_batch(sig, offs, lens)
+    assert np.array_equal(off, off_o) and np.array_equal(bits(ev), bits(ev_o))
+    assert off[-1] > n
 
 
 # ---- K2 / K3 ------------------------------------------------------------------------------------------
@@ -207,10 +231,12 @@ def _workload(n_reads=40, seed=41):
     for g in np.unique(chains["group"]):
         ch = chains[chains["group"] == g][0]
         a = anchors[int(ch["anchor_off"]):int(ch["anchor_off"]) + int(ch["n_anchors"])]
-        q0, q1 = int(a["query_position"][-1]), int(a["query_position"][0])
-        t0, t1 = int(a["target_position"][-1]), int(a["target_position"][0])
-        seg = read[int(ch["read_off"]) + q0:int(ch["read_off"]) + q1 + 1]
-        ref[t0:t1 + 1] = np.interp(np.linspace(0, len(seg) - 1, t1 - t0 + 1), np.arange(len(seg)), seg) + rng.normal(0, 0.1, t1 - t0 + 1)
+        rd = read[int(ch["read_off"]):]
+        for p in range(len(a) - 1, 0, -1):                   # anchor-to-anchor: the reference span is the read span, resampled
+            qs, qe = int(a["query_position"][p]), int(a["query_position"][p - 1])
+            ts, te = int(a["target_position"][p]), int(a["target_position"][p - 1])
+            seg = rd[qs:qe + 1]
+            ref[ts:te + 1] = np.interp(np.linspace(0, len(seg) - 1, te - ts + 1), np.arange(len(seg)), seg) + rng.normal(0, 0.05, te - ts + 1)
     return read, ref.astype(np.float32), anchors, chains
 
 
