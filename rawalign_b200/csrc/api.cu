@@ -64,6 +64,7 @@ struct ra_ctx {
 	DevBuf a_arena, b_arena, items, cost, counter, ring, order;
 	// chains
 	DevBuf anchors, chains, group_first, min_score, score, keep, cells, chain_ring;
+	DevBuf sp_nparts, sp_ntiles, sp_pbase, sp_tbase, sp_tchain, sp_cost, sp_pcells, sp_best;   // sparse-border plan (chains_sparse.cu)
 	uint64_t resident_events = 0;      // events left on the device by the last ra_detect_events_batch
 	// traceback
 	DevBuf dirs, dir_off, slot_off, slot_i, slot_j, slot_d, path_len, path_off, out_i, out_j, out_d;
@@ -146,11 +147,54 @@ int dtw_dev(ra_ctx *ctx, const float *a_dev, const float *b_dev, const ra_dtw_it
 	return RA_OK;
 }
 
+// Sparse border: plan (which chains, how many parts / tiles), flat part-cost kernel, replay -- once for
+// min_score_mode 0, twice (first chain of every group, then the rest) for the running threshold.
+int sparse_pipeline(ra_ctx *ctx, const ra::ChainLaunch &L, uint32_t n_chains)
+{
+	int rc;
+	if (n_chains == 0) {
+		RA_CUDA(cudaMemcpyAsync(&n_chains, L.group_first + L.n_groups, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+		RA_CUDA(cudaStreamSynchronize(ctx->stream));
+		if (n_chains == 0) return RA_OK;
+	}
+	if ((rc = ctx->sp_nparts.reserve((size_t)n_chains * 4))) return rc;
+	if ((rc = ctx->sp_ntiles.reserve((size_t)n_chains * 4))) return rc;
+	if ((rc = ctx->sp_pbase.reserve((size_t)(n_chains + 1) * 8))) return rc;
+	if ((rc = ctx->sp_tbase.reserve((size_t)(n_chains + 1) * 8))) return rc;
+	if ((rc = ctx->sp_best.reserve((size_t)L.n_groups * 4))) return rc;
+	RA_CUDA(cudaMemsetAsync(L.cells, 0, 2 * sizeof(uint64_t), ctx->stream));
+	RA_CUDA(cudaMemsetAsync(L.need_cap, 0, sizeof(uint32_t), ctx->stream));
+	ra::SparsePlan P; memset(&P, 0, sizeof(P));
+	P.n_chains = n_chains;
+	P.n_parts = ctx->sp_nparts.as<uint32_t>(); P.n_tiles = ctx->sp_ntiles.as<uint32_t>();
+	P.part_base = ctx->sp_pbase.as<uint64_t>(); P.tile_base = ctx->sp_tbase.as<uint64_t>();
+	P.best = ctx->sp_best.as<float>();
+	const int first = (L.min_score_mode == 1) ? 1 : 0, last = (L.min_score_mode == 1) ? 2 : 0;
+	for (int phase = first; phase <= last; ++phase) {
+		RA_CUDA(ra::launch_sparse_prep(L, P, phase, ctx->stream));
+		RA_CUDA(ra::launch_exclusive_scan_u32(P.n_parts, P.part_base, n_chains, ctx->stream));
+		RA_CUDA(ra::launch_exclusive_scan_u32(P.n_tiles, P.tile_base, n_chains, ctx->stream));
+		uint64_t tot[2] = {0, 0};
+		RA_CUDA(cudaMemcpyAsync(&tot[0], P.part_base + n_chains, 8, cudaMemcpyDeviceToHost, ctx->stream));
+		RA_CUDA(cudaMemcpyAsync(&tot[1], P.tile_base + n_chains, 8, cudaMemcpyDeviceToHost, ctx->stream));
+		RA_CUDA(cudaStreamSynchronize(ctx->stream));
+		if (tot[1] >= 0xffffffffull) return fail(RA_EINVAL, "too many part tiles in one batch (%llu)", (unsigned long long)tot[1]);
+		if ((rc = ctx->sp_tchain.reserve((size_t)(tot[1] + 1) * 4))) return rc;
+		if ((rc = ctx->sp_cost.reserve((size_t)(tot[0] + 1) * 4))) return rc;
+		if ((rc = ctx->sp_pcells.reserve((size_t)(tot[0] + 1) * 4))) return rc;
+		P.tile_chain = ctx->sp_tchain.as<uint32_t>(); P.part_cost = ctx->sp_cost.as<float>(); P.part_cells = ctx->sp_pcells.as<uint32_t>();
+		RA_CUDA(ra::launch_sparse_eval(L, P, phase, ctx->n_sm, ctx->stream));
+		ctx->launches += ra::kSparseKernelsPerPhase;
+	}
+	return RA_OK;
+}
+
 // Runs the chain kernel on device-resident inputs; retries once with a larger HBM ring when a part
 // was wider than the rings available.
 int chains_dev(ra_ctx *ctx, const float *read_dev, const float *ref_dev, const ra_anchor_t *anchors_dev,
                const ra_chain_t *chains_dev_p, const uint32_t *group_first_dev, uint32_t n_groups, int min_score_mode,
-               const float *min_score_dev, float *score_dev, uint8_t *keep_dev, uint64_t *cells_host /* [2] or null */)
+               const float *min_score_dev, float *score_dev, uint8_t *keep_dev, uint64_t *cells_host /* [2] or null */,
+               uint32_t n_chains /* 0 = read group_first[n_groups] back */)
 {
 	if (n_groups == 0) { if (cells_host) cells_host[0] = cells_host[1] = 0; return RA_OK; }
 	const ra_mapopt_t &o = ctx->opt;
@@ -173,10 +217,14 @@ int chains_dev(ra_ctx *ctx, const float *read_dev, const float *ref_dev, const r
 		L.cells = ctx->cells.as<uint64_t>();
 		L.ring_scratch = ring_cap ? ctx->chain_ring.as<float>() : nullptr; L.ring_cap = ring_cap;
 		RA_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
-		RA_CUDA(ra::launch_chain_eval(L, ctx->n_sm, ctx->stream));
+		if (o.dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_SPARSE) {
+			if ((rc = sparse_pipeline(ctx, L, n_chains))) return rc;
+		} else {
+			RA_CUDA(ra::launch_chain_eval(L, ctx->n_sm, ctx->stream));
+			ctx->launches += 1;
+		}
 		RA_CUDA(cudaEventRecord(ctx->ev[4], ctx->stream));
 		ctx->timed_dtw = true;
-		ctx->launches += 1;
 		uint32_t need = 0;
 		RA_CUDA(cudaMemcpyAsync(&need, L.need_cap, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
 		uint64_t cells[2] = {0, 0};
@@ -251,7 +299,7 @@ void ra_destroy(ra_ctx *ctx)
 	cudaSetDevice(ctx->device);
 	cudaStreamSynchronize(ctx->stream);
 	DevBuf *bufs[] = { &ctx->ref, &ctx->sig, &ctx->chunk_off, &ctx->chunk_len, &ctx->raw, &ctx->nev, &ctx->ev_pos, &ctx->ev_off,
-	                   &ctx->ev_out, &ctx->a_arena, &ctx->b_arena, &ctx->items, &ctx->cost, &ctx->counter, &ctx->ring, &ctx->order, &ctx->anchors, &ctx->chains, &ctx->group_first, &ctx->min_score, &ctx->score, &ctx->keep, &ctx->cells, &ctx->chain_ring,
+	                   &ctx->ev_out, &ctx->a_arena, &ctx->b_arena, &ctx->items, &ctx->cost, &ctx->counter, &ctx->ring, &ctx->order, &ctx->anchors, &ctx->chains, &ctx->group_first, &ctx->min_score, &ctx->score, &ctx->keep, &ctx->cells, &ctx->chain_ring, &ctx->sp_nparts, &ctx->sp_ntiles, &ctx->sp_pbase, &ctx->sp_tbase, &ctx->sp_tchain, &ctx->sp_cost, &ctx->sp_pcells, &ctx->sp_best,
 	                   &ctx->dirs, &ctx->dir_off, &ctx->slot_off, &ctx->slot_i, &ctx->slot_j, &ctx->slot_d, &ctx->path_len,
 	                   &ctx->path_off, &ctx->out_i, &ctx->out_j, &ctx->out_d };
 	for (DevBuf *b : bufs) b->release();
@@ -635,7 +683,7 @@ int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
 	}
 	uint64_t cells[2] = {0, 0};
 	if ((rc = chains_dev(ctx, read_dev, ref_dev, ctx->anchors.as<ra_anchor_t>(), ctx->chains.as<ra_chain_t>(), ctx->group_first.as<uint32_t>(),
-	                     (uint32_t)gf.size() - 1, min_score_mode, ms_dev, ctx->score.as<float>(), ctx->keep.as<uint8_t>(), cells))) return rc;
+	                     (uint32_t)gf.size() - 1, min_score_mode, ms_dev, ctx->score.as<float>(), ctx->keep.as<uint8_t>(), cells, n_chains))) return rc;
 	RA_CUDA(cudaMemcpyAsync(alignment_score, ctx->score.p, (size_t)n_chains * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
 	if (keep) RA_CUDA(cudaMemcpyAsync(keep, ctx->keep.p, (size_t)n_chains, cudaMemcpyDeviceToHost, ctx->stream));
 	RA_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -656,7 +704,7 @@ int ra_align_chains_batch_dev(ra_ctx *ctx, const float *read_arena_dev, const fl
 	if (n_groups && (!read_dev || !ref_dev)) return fail(RA_EINVAL, "no read or reference arena on the device");
 	uint64_t cells[2] = {0, 0};
 	int rc = chains_dev(ctx, read_dev, ref_dev, anchors_dev, chains_dev_p, group_first_dev, n_groups, min_score_mode, min_score_dev,
-	                    alignment_score_dev, keep_dev, cells);
+	                    alignment_score_dev, keep_dev, cells, 0);
 	if (rc) return rc;
 	if (cells_issued) *cells_issued = cells[0];
 	if (cells_useful) *cells_useful = cells[1];

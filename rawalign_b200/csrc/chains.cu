@@ -46,7 +46,7 @@ __device__ __forceinline__ PartDesc make_part(const ChainLaunch &L, const ra_cha
 __global__ void __launch_bounds__(kChainWarps * 32)
 k_chain_eval(ChainLaunch L)
 {
-	__shared__ float lane_ring[kChainWarps][3 * kLaneRing * 32];
+	__shared__ float lane_ring[kChainWarps][2 * kNarrowRing * 32];   // [row ring | B ring], lane-interleaved
 	__shared__ float warp_ring[kChainWarps][3 * kWarpRingCap];
 	__shared__ float tile_cost[kChainWarps][kTile];
 	__shared__ uint32_t tile_alen[kChainWarps][kTile];
@@ -87,11 +87,10 @@ k_chain_eval(ChainLaunch L)
 					bool is_big = false;
 					if (base + lane < tn) {
 						const PartDesc d = make_part(L, ch, anc, parts, p);
-						const int width = band_width_of(d.n, d.m, d.band);
 						tile_alen[wid][base + lane] = d.a_len;
-						if (width <= kLaneRing) {
+						if (narrow_ok(d.n, d.m, d.band)) {
 							uint32_t cnt = 0;
-							float c = lane_dtw_cost(d.A, d.n, d.B, d.m, d.band, my_lane_ring, &cnt);
+							float c = thread_dtw_narrow(LdgLoader{d.A}, d.n, LdgLoader{d.B}, d.m, d.band, my_lane_ring, my_lane_ring + kNarrowRing * 32, &cnt);
 							if (d.excl) c -= fabsf(__ldg(d.A + d.n - 1) - __ldg(d.B + d.m - 1));   // dtw.cpp:514-516 / :60-62
 							tile_cost[wid][base + lane] = c;
 							tile_cells[wid][base + lane] = cnt;

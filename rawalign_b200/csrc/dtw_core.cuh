@@ -108,6 +108,153 @@ __device__ __forceinline__ float warp_dtw_cost(const float *__restrict__ A, int 
 	return res;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Row form of the banded cell set.  For A = longer sequence (index i, n entries), B = shorter
+// (index j, m entries), R' = slant-extended radius (dtw.cpp:298-300), odd = R' & 1,
+// h = odd ? (R'-1)/2 : R'/2, the cell set of dtw.cpp:273-520 is, row by row,
+//     jhi(i) = (i+h+odd > n-1) ? m-1 : min(m-1, floor(m*(i+h+odd)/n) + h)
+//     jlo(i) = (i-h-odd < 0)   ? 0   : max(0,   floor(m*(i-h-odd)/n) - h)
+// contiguous in every row and non-decreasing in i (tests/test_band_rows.py checks this closed form
+// against the anti-diagonal enumeration; tools/band_rows_check.py is the same check as a script).
+// Full matrix: jlo = 0, jhi = m-1.
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int slant_radius(int n, int m, int band_radius)
+{
+	const uint32_t extra = (((uint32_t)n - (uint32_t)m) * (uint32_t)band_radius + (uint32_t)n - 1u) / (uint32_t)n;
+	return band_radius + (int)extra;
+}
+
+// Thread-private cost of one NARROW problem: one row of A per step, the previous row and the B values
+// of the live columns in two lane-interleaved shared-memory rings of kNarrowRing entries
+// (ring[slot*32 + lane], bank-conflict free).  Requires 2*R'+4 <= kNarrowRing (band) or m+2 <= kNarrowRing (full).
+constexpr int kNarrowRing = 16;
+__device__ __forceinline__ bool narrow_ok(int n, int m, int band_radius)
+{
+	if (band_radius < 0) return m + 2 <= kNarrowRing;
+	return 2 * slant_radius(n, m, band_radius) + 4 <= kNarrowRing;
+}
+
+struct LdgLoader {          // operands straight from global memory (read-only path)
+	const float *__restrict__ p;
+	__device__ __forceinline__ float operator[](int k) const { return __ldg(p + k); }
+};
+struct SmemLoader {         // operands staged in shared memory by the CTA
+	const float *p;
+	__device__ __forceinline__ float operator[](int k) const { return p[k]; }
+};
+
+template <class LA, class LB>
+__device__ __forceinline__ float thread_dtw_narrow(const LA A, int n, const LB B, int m,
+                                                   int band_radius, float *row /* + lane */, float *bv /* + lane */, uint32_t *cells)
+{
+	constexpr uint32_t M = kNarrowRing - 1;
+	int h = 0, lead = 0;                 // lead = h + odd: how far the column trackers run ahead of / behind the row
+	const bool full = band_radius < 0;
+	if (!full) {
+		const int Rp = slant_radius(n, m, band_radius);
+		const int odd = Rp & 1;
+		h = odd ? (Rp - 1) / 2 : Rp / 2;
+		lead = h + odd;
+	}
+	// upper tracker: x_hi = i + lead, r_hi = floor(m*x_hi/n), e_hi = (m*x_hi) mod n
+	int r_hi = 0, e_hi = 0;
+	for (int s = 0; s < lead; ++s) { e_hi += m; if (e_hi >= n) { e_hi -= n; ++r_hi; } }
+	int r_lo = 0, e_lo = 0;              // lower tracker, valid once i - lead >= 0
+	int pjh = -1;                        // jhi of the previous row (columns <= pjh hold dp[i-1][.])
+	int pjl = 0;
+	float last = kInf;
+	uint32_t cnt = 0;
+	for (int i = 0; i < n; ++i) {
+		int jh = m - 1, jl = 0;
+		if (!full) {
+			if (i + lead <= n - 1) jh = min(m - 1, r_hi + h);
+			if (i - lead >= 0) jl = max(0, r_lo - h);
+		}
+		// columns entering the band: fetch B, no value from the previous row
+		for (int j = pjh + 1; j <= jh; ++j) { bv[((uint32_t)j & M) * 32] = B[j]; row[((uint32_t)j & M) * 32] = kInf; }
+		const float a_i = A[i];
+		// dp(i-1, jl-1): inside the previous row's range or outside the set; row 0 starts from 0 so that dp(0,0) = |A0-B0|
+		float diag = (i == 0) ? 0.0f : ((jl - 1 >= pjl) ? row[((uint32_t)(jl - 1) & M) * 32] : kInf);
+		float left = kInf;
+		for (int j = jl; j <= jh; ++j) {
+			const uint32_t s = ((uint32_t)j & M) * 32;
+			const float up = row[s];
+			const float v = fminf(fminf(left, up), diag) + fabsf(a_i - bv[s]);
+			row[s] = v; diag = up; left = v;
+		}
+		cnt += (uint32_t)(jh - jl + 1);
+		last = left;
+		pjh = jh; pjl = jl;
+		if (!full) {
+			e_hi += m; if (e_hi >= n) { e_hi -= n; ++r_hi; }
+			if (i - lead >= 0) { e_lo += m; if (e_lo >= n) { e_lo -= n; ++r_lo; } }
+		}
+	}
+	if (cells) *cells += cnt;
+	return last;                         // dp(n-1, m-1): jhi(n-1) = m-1 always
+}
+
+// Register-resident cost of one banded problem with R' <= 2 (every anchor gap below 20 events at
+// banded=0.1): a row holds at most kWin = 2R'+2 = 6 cells, so the previous row and the B values of the
+// live columns are kept in a 6-register window anchored at jlo(i).  The window slides by
+// jlo(i)-jlo(i-1) in {0,1} per row; every row executes the same straight-line code (no inner loop, no
+// shared-memory round trip on the DP chain), invalid slots carry 1e10f.
+constexpr int kWin = 6;
+__device__ __forceinline__ bool win6_ok(int n, int m, int band_radius)
+{
+	return band_radius >= 0 && slant_radius(n, m, band_radius) <= 2;
+}
+
+template <class LA, class LB>
+__device__ __forceinline__ float thread_dtw_win6(const LA A, int n, const LB B, int m, int band_radius, uint32_t *cells)
+{
+	const int Rp = slant_radius(n, m, band_radius);      // 1 or 2
+	const int odd = Rp & 1;
+	const int h = odd ? 0 : 1;                            // (R'-1)/2 = 0 for R'=1, R'/2 = 1 for R'=2
+	const int lead = 1;                                   // h + odd = 1 in both cases
+	int r_hi = 0, e_hi = m;                               // upper tracker at x = lead = 1: floor(m/n), m mod n  (m <= n)
+	if (e_hi >= n) { e_hi -= n; ++r_hi; }
+	int r_lo = 0, e_lo = 0;
+	float u[kWin], bw[kWin];
+#pragma unroll
+	for (int t = 0; t < kWin; ++t) { u[t] = kInf; bw[t] = B[min(t, m - 1)]; }
+	int pjl = 0, jl = 0, jh = 0;
+	uint32_t cnt = 0;
+#pragma unroll 1
+	for (int i = 0; i < n; ++i) {
+		jh = (i + lead <= n - 1) ? min(m - 1, r_hi + h) : m - 1;
+		jl = (i - lead >= 0) ? max(0, r_lo - h) : 0;
+		const float a_i = A[i];
+		float diag = kInf;
+		if (jl != pjl) {                                  // slide the windows by one column
+			diag = u[0];                                  // dp(i-1, jl-1)
+#pragma unroll
+			for (int t = 0; t < kWin - 1; ++t) { u[t] = u[t + 1]; bw[t] = bw[t + 1]; }
+			u[kWin - 1] = kInf; bw[kWin - 1] = B[min(jl + kWin - 1, m - 1)];
+		}
+		if (i == 0) diag = 0.0f;                          // dp(0,0) = |A0 - B0|
+		const int nvalid = jh - jl + 1;
+		float left = kInf;
+#pragma unroll
+		for (int t = 0; t < kWin; ++t) {
+			const float up = u[t];
+			const float v = fminf(fminf(left, up), diag) + fabsf(a_i - bw[t]);
+			u[t] = (t < nvalid) ? v : kInf;
+			diag = up; left = v;
+		}
+		cnt += (uint32_t)nvalid;
+		pjl = jl;
+		e_hi += m; if (e_hi >= n) { e_hi -= n; ++r_hi; }
+		if (i - lead >= 0) { e_lo += m; if (e_lo >= n) { e_lo -= n; ++r_lo; } }
+	}
+	if (cells) *cells += cnt;
+	const int t_last = (m - 1) - jl;                      // dp(n-1, m-1)
+	float res = u[0];
+#pragma unroll
+	for (int t = 1; t < kWin; ++t) res = (t_last == t) ? u[t] : res;
+	return res;
+}
+
 // Lane-private cost of one SMALL problem (widest diagonal <= kLaneRing): the three rolling diagonals
 // live in shared memory, interleaved across the warp ([slot][lane], bank-conflict free).
 constexpr int kLaneRing = 8;
