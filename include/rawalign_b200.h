@@ -203,8 +203,8 @@ int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
  * Device-resident form: all pointers are device pointers; group_first has n_groups+1 chain indices
  * (first chain of every group, then n_chains). read/ref NULL = resident events / reference mirror. */
 int ra_align_chains_batch_dev(ra_ctx *ctx, const float *read_arena_dev, const float *ref_arena_dev,
-                              const ra_anchor_t *anchors_dev, const ra_chain_t *chains_dev, const uint32_t *group_first_dev,
-                              uint32_t n_groups, int min_score_mode, const float *min_score_dev,
+                              const ra_anchor_t *anchors_dev, uint64_t n_anchors, const ra_chain_t *chains_dev, uint32_t n_chains,
+                              const uint32_t *group_first_dev, uint32_t n_groups, int min_score_mode, const float *min_score_dev,
                               float *alignment_score_dev, uint8_t *keep_dev, uint64_t *cells_issued, uint64_t *cells_useful);
 
 /* cigar=true form of align_chain (rmap.cpp:218-235, :282-299) for one batch of chains: the

@@ -68,7 +68,7 @@ def load() -> C.CDLL:
     L.ra_dtw_cells.argtypes = [u32, u32, C.c_int32]; L.ra_dtw_cells.restype = u64
     L.ra_dtw_tb_batch.argtypes = [vp, vp, u64, vp, u64, vp, u32, vp, vp, vp, vp, u64, vp]
     L.ra_align_chains_batch.argtypes = [vp, vp, u64, vp, u64, vp, u64, vp, u32, i32, vp, vp, vp, C.POINTER(u64), C.POINTER(u64)]
-    L.ra_align_chains_batch_dev.argtypes = [vp, vp, vp, vp, vp, vp, u32, i32, vp, vp, vp, C.POINTER(u64), C.POINTER(u64)]
+    L.ra_align_chains_batch_dev.argtypes = [vp, vp, vp, vp, u64, vp, u32, vp, u32, i32, vp, vp, vp, C.POINTER(u64), C.POINTER(u64)]
     L.ra_align_chains_cigar_batch.argtypes = [vp, vp, u64, vp, u64, vp, u64, vp, u32, vp, vp, vp, vp, vp, u64, vp]
     for name in ("ra_init", "ra_set_opt", "ra_last_timing", "ra_ref_load", "ra_ref_load_flat", "ra_ref_device", "ra_ref_alloc",
                  "ra_detect_events_batch", "ra_detect_events_batch_dev", "ra_last_event_positions", "ra_dtw_batch", "ra_dtw_batch_dev",

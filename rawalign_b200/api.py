@@ -208,9 +208,10 @@ class Context:
 
     # ---- chain level -----------------------------------------------------------------------------
     def align_chains_batch(self, read_arena, ref_arena, anchors: np.ndarray, chains: np.ndarray,
-                           min_score_mode: int = 1, min_score: Optional[np.ndarray] = None):
+                           min_score_mode: int = 1, min_score: Optional[np.ndarray] = None, count_cells: bool = True):
         """Batched align_chain(cigar=false) + the evaluation loop of gen_chains (rmap.cpp:515-524).
-        Returns (alignment_score, keep, cells_issued, cells_useful)."""
+        Returns (alignment_score, keep, cells_issued, cells_useful); the two cell counts are instrumentation
+        (GCUPS numerator) and are 0 when count_cells is False."""
         read_arena = None if read_arena is None else _f32(read_arena)   # None: events resident from detect_events_batch
         ref_arena = None if ref_arena is None else _f32(ref_arena)
         anchors = np.ascontiguousarray(anchors, dtype=ANCHOR_DTYPE)
@@ -221,16 +222,19 @@ class Context:
         check(self._L.ra_align_chains_batch(self._h, _ptr(read_arena), 0 if read_arena is None else read_arena.size, _ptr(ref_arena),
                                             0 if ref_arena is None else ref_arena.size, anchors.ctypes.data, len(anchors),
                                             chains.ctypes.data, len(chains), int(min_score_mode), _ptr(ms),
-                                            score.ctypes.data, keep.ctypes.data, C.byref(ci), C.byref(cu)))
+                                            score.ctypes.data, keep.ctypes.data, C.byref(ci) if count_cells else None,
+                                            C.byref(cu) if count_cells else None))
         return score, keep.astype(bool), int(ci.value), int(cu.value)
 
-    def align_chains_batch_dev(self, read_ptr, ref_ptr, anchors_ptr: int, chains_ptr: int, group_first_ptr: int,
-                               n_groups: int, score_ptr: int, keep_ptr: Optional[int] = None, min_score_mode: int = 1,
-                               min_score_ptr: Optional[int] = None):
-        """Device-resident chain evaluation; returns (cells_issued, cells_useful)."""
+    def align_chains_batch_dev(self, read_ptr, ref_ptr, anchors_ptr: int, n_anchors: int, chains_ptr: int, n_chains: int,
+                               group_first_ptr: int, n_groups: int, score_ptr: int, keep_ptr: Optional[int] = None, min_score_mode: int = 1,
+                               min_score_ptr: Optional[int] = None, count_cells: bool = True):
+        """Device-resident chain evaluation; returns (cells_issued, cells_useful) (0, 0 when count_cells is False)."""
         ci = C.c_uint64(0); cu = C.c_uint64(0)
-        check(self._L.ra_align_chains_batch_dev(self._h, read_ptr, ref_ptr, anchors_ptr, chains_ptr, group_first_ptr, int(n_groups),
-                                                int(min_score_mode), min_score_ptr, score_ptr, keep_ptr, C.byref(ci), C.byref(cu)))
+        check(self._L.ra_align_chains_batch_dev(self._h, read_ptr, ref_ptr, anchors_ptr, int(n_anchors), chains_ptr, int(n_chains),
+                                                group_first_ptr, int(n_groups),
+                                                int(min_score_mode), min_score_ptr, score_ptr, keep_ptr,
+                                                C.byref(ci) if count_cells else None, C.byref(cu) if count_cells else None))
         return int(ci.value), int(cu.value)
 
     def align_chain(self, anchors, read_events, ref_events, cigar: bool = False, min_score: float = -1e10):

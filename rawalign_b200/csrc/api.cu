@@ -147,42 +147,35 @@ int dtw_dev(ra_ctx *ctx, const float *a_dev, const float *b_dev, const ra_dtw_it
 	return RA_OK;
 }
 
-// Sparse border: plan (which chains, how many parts / tiles), flat part-cost kernel, replay -- once for
-// min_score_mode 0, twice (first chain of every group, then the rest) for the running threshold.
-int sparse_pipeline(ra_ctx *ctx, const ra::ChainLaunch &L, uint32_t n_chains)
+// Sparse border: plan (which chains, slots for their parts and tiles), flat part-cost kernel, replay -- once
+// for min_score_mode 0, twice (first chain of every group, then the rest) for the running threshold.  No host
+// synchronisation inside: capacities come from the anchor count (a chain of k anchors has k-1 parts).
+int sparse_pipeline(ra_ctx *ctx, const ra::ChainLaunch &L, uint32_t n_chains, uint64_t n_anchors)
 {
 	int rc;
-	if (n_chains == 0) {
-		RA_CUDA(cudaMemcpyAsync(&n_chains, L.group_first + L.n_groups, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
-		RA_CUDA(cudaStreamSynchronize(ctx->stream));
-		if (n_chains == 0) return RA_OK;
-	}
+	if (n_chains == 0) return RA_OK;
+	const uint64_t part_cap = n_anchors + 1, tile_cap = n_anchors / ra::kSparseTileParts + n_chains + 1;
+	if (tile_cap >= 0xffffffffull) return fail(RA_EINVAL, "too many part tiles in one batch (%llu)", (unsigned long long)tile_cap);
 	if ((rc = ctx->sp_nparts.reserve((size_t)n_chains * 4))) return rc;
-	if ((rc = ctx->sp_ntiles.reserve((size_t)n_chains * 4))) return rc;
-	if ((rc = ctx->sp_pbase.reserve((size_t)(n_chains + 1) * 8))) return rc;
-	if ((rc = ctx->sp_tbase.reserve((size_t)(n_chains + 1) * 8))) return rc;
+	if ((rc = ctx->sp_pbase.reserve((size_t)n_chains * 8))) return rc;
 	if ((rc = ctx->sp_best.reserve((size_t)L.n_groups * 4))) return rc;
-	RA_CUDA(cudaMemsetAsync(L.cells, 0, 2 * sizeof(uint64_t), ctx->stream));
+	if ((rc = ctx->sp_tchain.reserve((size_t)tile_cap * 4))) return rc;
+	if ((rc = ctx->sp_tbase.reserve((size_t)tile_cap * 4))) return rc;
+	if ((rc = ctx->sp_cost.reserve((size_t)part_cap * 4))) return rc;
+	if (L.cells && (rc = ctx->sp_pcells.reserve((size_t)part_cap * 4))) return rc;
+	if ((rc = ctx->sp_ntiles.reserve(64))) return rc;
+	if (L.cells) RA_CUDA(cudaMemsetAsync(L.cells, 0, 2 * sizeof(uint64_t), ctx->stream));
 	RA_CUDA(cudaMemsetAsync(L.need_cap, 0, sizeof(uint32_t), ctx->stream));
 	ra::SparsePlan P; memset(&P, 0, sizeof(P));
 	P.n_chains = n_chains;
-	P.n_parts = ctx->sp_nparts.as<uint32_t>(); P.n_tiles = ctx->sp_ntiles.as<uint32_t>();
-	P.part_base = ctx->sp_pbase.as<uint64_t>(); P.tile_base = ctx->sp_tbase.as<uint64_t>();
+	P.n_parts = ctx->sp_nparts.as<uint32_t>(); P.part_base = ctx->sp_pbase.as<uint64_t>();
+	P.tile_chain = ctx->sp_tchain.as<uint32_t>(); P.tile_t0 = ctx->sp_tbase.as<uint32_t>();
+	P.totals = ctx->sp_ntiles.as<unsigned long long>();
+	P.part_cost = ctx->sp_cost.as<float>(); P.part_cells = L.cells ? ctx->sp_pcells.as<uint32_t>() : nullptr;
 	P.best = ctx->sp_best.as<float>();
 	const int first = (L.min_score_mode == 1) ? 1 : 0, last = (L.min_score_mode == 1) ? 2 : 0;
 	for (int phase = first; phase <= last; ++phase) {
 		RA_CUDA(ra::launch_sparse_prep(L, P, phase, ctx->stream));
-		RA_CUDA(ra::launch_exclusive_scan_u32(P.n_parts, P.part_base, n_chains, ctx->stream));
-		RA_CUDA(ra::launch_exclusive_scan_u32(P.n_tiles, P.tile_base, n_chains, ctx->stream));
-		uint64_t tot[2] = {0, 0};
-		RA_CUDA(cudaMemcpyAsync(&tot[0], P.part_base + n_chains, 8, cudaMemcpyDeviceToHost, ctx->stream));
-		RA_CUDA(cudaMemcpyAsync(&tot[1], P.tile_base + n_chains, 8, cudaMemcpyDeviceToHost, ctx->stream));
-		RA_CUDA(cudaStreamSynchronize(ctx->stream));
-		if (tot[1] >= 0xffffffffull) return fail(RA_EINVAL, "too many part tiles in one batch (%llu)", (unsigned long long)tot[1]);
-		if ((rc = ctx->sp_tchain.reserve((size_t)(tot[1] + 1) * 4))) return rc;
-		if ((rc = ctx->sp_cost.reserve((size_t)(tot[0] + 1) * 4))) return rc;
-		if ((rc = ctx->sp_pcells.reserve((size_t)(tot[0] + 1) * 4))) return rc;
-		P.tile_chain = ctx->sp_tchain.as<uint32_t>(); P.part_cost = ctx->sp_cost.as<float>(); P.part_cells = ctx->sp_pcells.as<uint32_t>();
 		RA_CUDA(ra::launch_sparse_eval(L, P, phase, ctx->n_sm, ctx->stream));
 		ctx->launches += ra::kSparseKernelsPerPhase;
 	}
@@ -194,7 +187,7 @@ int sparse_pipeline(ra_ctx *ctx, const ra::ChainLaunch &L, uint32_t n_chains)
 int chains_dev(ra_ctx *ctx, const float *read_dev, const float *ref_dev, const ra_anchor_t *anchors_dev,
                const ra_chain_t *chains_dev_p, const uint32_t *group_first_dev, uint32_t n_groups, int min_score_mode,
                const float *min_score_dev, float *score_dev, uint8_t *keep_dev, uint64_t *cells_host /* [2] or null */,
-               uint32_t n_chains /* 0 = read group_first[n_groups] back */)
+               uint32_t n_chains, uint64_t n_anchors)
 {
 	if (n_groups == 0) { if (cells_host) cells_host[0] = cells_host[1] = 0; return RA_OK; }
 	const ra_mapopt_t &o = ctx->opt;
@@ -214,11 +207,11 @@ int chains_dev(ra_ctx *ctx, const float *read_dev, const float *ref_dev, const r
 		L.band_frac = o.dtw_band_radius_frac; L.match_bonus = o.dtw_match_bonus; L.min_dtw_score = o.dtw_min_score;
 		L.min_score_mode = min_score_mode; L.min_score = min_score_dev; L.score = score_dev; L.keep = keep_dev;
 		L.work_counter = ctx->counter.as<uint32_t>(); L.need_cap = ctx->counter.as<uint32_t>() + 4;
-		L.cells = ctx->cells.as<uint64_t>();
+		L.cells = cells_host ? ctx->cells.as<uint64_t>() : nullptr;      // cell counting is instrumentation: off unless asked for
 		L.ring_scratch = ring_cap ? ctx->chain_ring.as<float>() : nullptr; L.ring_cap = ring_cap;
 		RA_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
 		if (o.dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_SPARSE) {
-			if ((rc = sparse_pipeline(ctx, L, n_chains))) return rc;
+			if ((rc = sparse_pipeline(ctx, L, n_chains, n_anchors))) return rc;
 		} else {
 			RA_CUDA(ra::launch_chain_eval(L, ctx->n_sm, ctx->stream));
 			ctx->launches += 1;
@@ -228,7 +221,7 @@ int chains_dev(ra_ctx *ctx, const float *read_dev, const float *ref_dev, const r
 		uint32_t need = 0;
 		RA_CUDA(cudaMemcpyAsync(&need, L.need_cap, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
 		uint64_t cells[2] = {0, 0};
-		RA_CUDA(cudaMemcpyAsync(cells, L.cells, sizeof(cells), cudaMemcpyDeviceToHost, ctx->stream));
+		if (L.cells) RA_CUDA(cudaMemcpyAsync(cells, L.cells, sizeof(cells), cudaMemcpyDeviceToHost, ctx->stream));
 		RA_CUDA(cudaStreamSynchronize(ctx->stream));
 		if (need == 0) { if (cells_host) { cells_host[0] = cells[0]; cells_host[1] = cells[1]; } return RA_OK; }
 		if (attempt == 1) break;
@@ -683,7 +676,7 @@ int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
 	}
 	uint64_t cells[2] = {0, 0};
 	if ((rc = chains_dev(ctx, read_dev, ref_dev, ctx->anchors.as<ra_anchor_t>(), ctx->chains.as<ra_chain_t>(), ctx->group_first.as<uint32_t>(),
-	                     (uint32_t)gf.size() - 1, min_score_mode, ms_dev, ctx->score.as<float>(), ctx->keep.as<uint8_t>(), cells, n_chains))) return rc;
+	                     (uint32_t)gf.size() - 1, min_score_mode, ms_dev, ctx->score.as<float>(), ctx->keep.as<uint8_t>(), (cells_issued || cells_useful) ? cells : nullptr, n_chains, n_anchors))) return rc;
 	RA_CUDA(cudaMemcpyAsync(alignment_score, ctx->score.p, (size_t)n_chains * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
 	if (keep) RA_CUDA(cudaMemcpyAsync(keep, ctx->keep.p, (size_t)n_chains, cudaMemcpyDeviceToHost, ctx->stream));
 	RA_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -693,8 +686,8 @@ int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
 }
 
 int ra_align_chains_batch_dev(ra_ctx *ctx, const float *read_arena_dev, const float *ref_arena_dev,
-                              const ra_anchor_t *anchors_dev, const ra_chain_t *chains_dev_p, const uint32_t *group_first_dev,
-                              uint32_t n_groups, int min_score_mode, const float *min_score_dev,
+                              const ra_anchor_t *anchors_dev, uint64_t n_anchors, const ra_chain_t *chains_dev_p, uint32_t n_chains,
+                              const uint32_t *group_first_dev, uint32_t n_groups, int min_score_mode, const float *min_score_dev,
                               float *alignment_score_dev, uint8_t *keep_dev, uint64_t *cells_issued, uint64_t *cells_useful)
 {
 	if (!ctx || (n_groups && (!anchors_dev || !chains_dev_p || !group_first_dev || !alignment_score_dev))) return fail(RA_EINVAL, "NULL argument");
@@ -704,7 +697,7 @@ int ra_align_chains_batch_dev(ra_ctx *ctx, const float *read_arena_dev, const fl
 	if (n_groups && (!read_dev || !ref_dev)) return fail(RA_EINVAL, "no read or reference arena on the device");
 	uint64_t cells[2] = {0, 0};
 	int rc = chains_dev(ctx, read_dev, ref_dev, anchors_dev, chains_dev_p, group_first_dev, n_groups, min_score_mode, min_score_dev,
-	                    alignment_score_dev, keep_dev, cells, 0);
+	                    alignment_score_dev, keep_dev, (cells_issued || cells_useful) ? cells : nullptr, n_chains, n_anchors);
 	if (rc) return rc;
 	if (cells_issued) *cells_issued = cells[0];
 	if (cells_useful) *cells_useful = cells[1];

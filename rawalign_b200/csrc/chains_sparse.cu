@@ -8,14 +8,14 @@
 // is split into a flat, fully parallel part-cost kernel and a tiny replay kernel:
 //
 //   k_sp_prep    per group: which chains can still matter (their budget chain_read_span*bonus is not
-//                below the threshold known so far), parts / tiles per chain
-//   (scan x2)    part_base[], tile_base[]
-//   k_sp_tiles   tile -> chain table
+//                below the threshold known so far); slots for their parts and tiles are reserved with
+//                one atomicAdd per warp, the tile table is filled (no scan, no host round trip)
 //   k_sp_parts   one CTA per tile of up to 256 consecutive parts of one chain: descriptors from the
 //                anchors, the tile's read-event span and reference span staged in shared memory with
-//                coalesced loads, parts counting-sorted by height so the lanes of a warp run equally
-//                long, one part per thread (register-window row sweep for R' <= 2, shared-memory rings
-//                up to R' = 6, a whole warp for anything wider); cost and cell count per part to HBM
+//                coalesced loads, parts counting-sorted by evaluator class and height so the lanes of
+//                a warp run the same code equally long, one part per thread (register-resident
+//                anti-diagonal evaluator for R' <= 4, shared-memory rings up to R' = 6, a whole warp
+//                for anything wider); cost (and, when asked, cell count) per part to HBM
 //   k_sp_replay  one warp per group: the reference's serial float arithmetic in part order (every lane
 //                carries the same state, values broadcast by shuffle), alignment_score (:306), keep
 //                flag (:518), running best (:519-521)
@@ -48,47 +48,65 @@ __device__ __forceinline__ float chain_budget(const ChainLaunch &L, const ra_cha
 }
 
 // phase 0: min_score_mode 0 (every chain against its own min_score); phase 1 / 2: A / B of mode 1.
+// One thread per group decides which of its chains are evaluated in this phase, reserves their slots in
+// the part arrays and their tiles (one atomicAdd per warp), and fills the tile table.
+__device__ __forceinline__ bool chain_active(const ChainLaunch &L, const SparsePlan &P, int phase, uint32_t g, uint32_t k, uint32_t k0,
+                                             const ra_chain_t &ch)
+{
+	if (ch.n_anchors < 2) return false;
+	if (phase == 1) return k == k0;                                           // threshold 0.0f: decided by the replay
+	const float budget = chain_budget(L, ch);
+	if (phase == 0) return !(budget < (L.min_score ? L.min_score[k] : RA_SCORE_DROPPED));
+	return (k != k0) && !(budget < P.best[g]);
+}
+
 __global__ void __launch_bounds__(256)
 k_sp_prep(ChainLaunch L, SparsePlan P, int phase)
 {
 	const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-	if (g >= L.n_groups) return;
-	const uint32_t k0 = L.group_first[g], k1 = L.group_first[g + 1];
+	const int lane = threadIdx.x & 31;
+	uint32_t k0 = 0, k1 = 0;
+	if (g < L.n_groups) { k0 = L.group_first[g]; k1 = L.group_first[g + 1]; }
+	uint32_t my_parts = 0, my_tiles = 0;
 	for (uint32_t k = k0; k < k1; ++k) {
 		const ra_chain_t ch = L.chains[k];
-		const uint32_t parts = ch.n_anchors - 1u;
-		bool active = parts > 0;
-		if (active) {
-			const float budget = chain_budget(L, ch);
-			if (phase == 0) active = !(budget < (L.min_score ? L.min_score[k] : RA_SCORE_DROPPED));
-			else if (phase == 1) active = (k == k0);                       // threshold 0.0f: decided by the replay
-			else active = (k != k0) && !(budget < P.best[g]);
-		}
-		P.n_parts[k] = active ? parts : 0u;
-		P.n_tiles[k] = active ? (parts + kTileParts - 1) / kTileParts : 0u;
+		if (chain_active(L, P, phase, g, k, k0, ch)) { my_parts += ch.n_anchors - 1u; my_tiles += (ch.n_anchors - 1u + kTileParts - 1) / kTileParts; }
 	}
-}
-
-__global__ void __launch_bounds__(256)
-k_sp_tiles(uint32_t n_chains, SparsePlan P)
-{
-	const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-	if (k >= n_chains) return;
-	const uint64_t b = P.tile_base[k], e = P.tile_base[k + 1];
-	for (uint64_t t = b; t < e; ++t) P.tile_chain[t] = k;
+	uint32_t ip = my_parts, it = my_tiles;                                    // inclusive warp scans
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		const uint32_t yp = __shfl_up_sync(0xffffffffu, ip, o), yt = __shfl_up_sync(0xffffffffu, it, o);
+		if (lane >= o) { ip += yp; it += yt; }
+	}
+	unsigned long long bp = 0, bt = 0;
+	if (lane == 31) { bp = atomicAdd(P.totals, (unsigned long long)ip); bt = atomicAdd(P.totals + 1, (unsigned long long)it); }
+	bp = __shfl_sync(0xffffffffu, bp, 31); bt = __shfl_sync(0xffffffffu, bt, 31);
+	uint64_t pb = bp + ip - my_parts, tb = bt + it - my_tiles;
+	for (uint32_t k = k0; k < k1; ++k) {
+		const ra_chain_t ch = L.chains[k];
+		const bool active = chain_active(L, P, phase, g, k, k0, ch);
+		const uint32_t parts = active ? ch.n_anchors - 1u : 0u;
+		P.n_parts[k] = parts;
+		P.part_base[k] = pb;
+		for (uint32_t t0 = 0; t0 < parts; t0 += kTileParts) { P.tile_chain[tb] = k; P.tile_t0[tb] = t0; ++tb; }
+		pb += parts;
+	}
 }
 
 struct SpShared {
 	float sA[kStageCap];
 	float sB[kStageCap];
 	float rings[kSpWarps][2 * kNarrowRing * 32];
-	uint16_t a_rel[kTileParts], b_rel[kTileParts], a_len[kTileParts], b_len[kTileParts];
+	uint64_t desc[kTileParts];                   // a_rel:11 | b_rel:11 | a_len:12 | b_len:12 | R' (0 = ring path):4 | band+1:8
 	uint16_t order[kTileParts];                  // sorted narrow parts from the front, wide parts from the back
 	uint32_t hist[kKeyBins];
 	uint32_t n_big;
 	uint32_t tile;
 };
 
+constexpr int kDiagMaxRp = 4;                    // register evaluator instantiated for R' = 1..4
+
+template <bool COUNT>
 __global__ void __launch_bounds__(kSpThreads)
 k_sp_parts(ChainLaunch L, SparsePlan P)
 {
@@ -97,7 +115,7 @@ k_sp_parts(ChainLaunch L, SparsePlan P)
 	float *my_row = &sh.rings[wid][lane];
 	float *my_bv = my_row + kNarrowRing * 32;
 	float *my_gring = L.ring_scratch ? L.ring_scratch + (size_t)(blockIdx.x * kSpWarps + wid) * 3 * L.ring_cap : nullptr;
-	const uint64_t n_tiles = P.tile_base[P.n_chains];
+	const uint64_t n_tiles = P.totals[1];
 	uint64_t cells_issued = 0;
 
 	for (;;) {
@@ -114,7 +132,7 @@ k_sp_parts(ChainLaunch L, SparsePlan P)
 		const float *__restrict__ read = L.read_arena + ch.read_off;
 		const float *__restrict__ ref = L.ref_arena + ch.ref_off;
 		const uint32_t parts = ch.n_anchors - 1u;
-		const uint32_t t0 = (uint32_t)(tile - P.tile_base[k]) * kTileParts;
+		const uint32_t t0 = P.tile_t0[tile];
 		const uint32_t tn = min((uint32_t)kTileParts, parts - t0);
 		const uint64_t out0 = P.part_base[k] + t0;
 		// ---- 1. descriptors (sparse part p runs from anchors[parts-p] to anchors[parts-p-1], rmap.cpp:253-260) ----
@@ -132,10 +150,13 @@ k_sp_parts(ChainLaunch L, SparsePlan P)
 				const int band = part_band(L, al);
 				// staged = both spans of the part lie inside the tile's staging window
 				const bool staged = (pe.query_position - q0 < (uint32_t)kStageCap) && (pe.target_position - r0 < (uint32_t)kStageCap);
-				const bool narrow = staged && (win6_ok(n, m, band) || narrow_ok(n, m, band));
-				sh.a_rel[idx] = (uint16_t)(ps.query_position - q0); sh.b_rel[idx] = (uint16_t)(ps.target_position - r0);
-				sh.a_len[idx] = (uint16_t)min(al, 65535u); sh.b_len[idx] = (uint16_t)min(bl, 65535u);
-				if (narrow) { key[u] = min(n, kKeyBins - 1); atomicAdd(&sh.hist[key[u]], 1u); }
+				const int rp = band >= 0 ? slant_radius(n, m, band) : 0;
+				const bool diag = rp >= 1 && rp <= kDiagMaxRp;
+				const bool narrow = staged && al < 4096u && bl < 4096u && (diag || narrow_ok(n, m, band));
+				sh.desc[idx] = (uint64_t)(ps.query_position - q0) | ((uint64_t)(ps.target_position - r0) << 11) | ((uint64_t)(al & 4095u) << 22) |
+				               ((uint64_t)(bl & 4095u) << 34) | ((uint64_t)(diag ? rp : 0) << 46) | ((uint64_t)(uint32_t)((band + 1) & 255) << 50);
+				// sort key: evaluator class (R' = 1 | anything else) then height, so a warp runs one code path and equally long
+				if (narrow) { key[u] = min(n, kKeyBins / 2 - 1) + (rp == 1 ? 0 : kKeyBins / 2); atomicAdd(&sh.hist[key[u]], 1u); }
 				else { const uint32_t b = atomicAdd(&sh.n_big, 1u); sh.order[kTileParts - 1 - b] = (uint16_t)idx; }
 			}
 		}
@@ -169,18 +190,24 @@ k_sp_parts(ChainLaunch L, SparsePlan P)
 			const int pos = (u == 0) ? tid : (int)n_narrow - 1 - tid;
 			if (pos < 0 || pos >= (int)n_narrow || (u == 1 && pos < kSpThreads)) continue;
 			const uint32_t idx = sh.order[pos];
-			const uint32_t al = sh.a_len[idx], bl = sh.b_len[idx];
-			const float *a = sh.sA + sh.a_rel[idx], *b = sh.sB + sh.b_rel[idx];
-			const int band = part_band(L, al);
+			const uint64_t dsc = sh.desc[idx];
+			const uint32_t al = (uint32_t)(dsc >> 22) & 4095u, bl = (uint32_t)(dsc >> 34) & 4095u;
+			const float *a = sh.sA + ((uint32_t)dsc & 2047u), *b = sh.sB + ((uint32_t)(dsc >> 11) & 2047u);
 			const bool swap = al < bl;                                           // dtw.cpp:284-292: A is the longer sequence
 			const SmemLoader LA{swap ? b : a}, LB{swap ? a : b};
 			const int n = (int)(swap ? bl : al), m = (int)(swap ? al : bl);
 			uint32_t cnt = 0;
 			float c;
-			if (win6_ok(n, m, band)) c = thread_dtw_win6(LA, n, LB, m, band, &cnt);
-			else c = thread_dtw_narrow(LA, n, LB, m, band, my_row, my_bv, &cnt);
+			switch ((uint32_t)(dsc >> 46) & 15u) {
+			case 1: c = thread_dtw_diag<1, COUNT>(LA, n, LB, m, &cnt); break;
+			case 2: c = thread_dtw_diag<2, COUNT>(LA, n, LB, m, &cnt); break;
+			case 3: c = thread_dtw_diag<3, COUNT>(LA, n, LB, m, &cnt); break;
+			case 4: c = thread_dtw_diag<4, COUNT>(LA, n, LB, m, &cnt); break;
+			default: c = thread_dtw_narrow(LA, n, LB, m, (int)((uint32_t)(dsc >> 50) & 255u) - 1, my_row, my_bv, &cnt); break;
+			}
 			if (t0 + idx != parts - 1) c -= fabsf(a[al - 1] - b[bl - 1]);         // exclude_last: rmap.cpp:270, dtw.cpp:514-516
-			P.part_cost[out0 + idx] = c; P.part_cells[out0 + idx] = cnt;
+			P.part_cost[out0 + idx] = c;
+			if (COUNT) P.part_cells[out0 + idx] = cnt;
 			cells_issued += cnt;
 		}
 		// ---- 4b. wide parts: one warp each, operands from global memory ----
@@ -207,11 +234,11 @@ k_sp_parts(ChainLaunch L, SparsePlan P)
 				c = warp_dtw_cost(A, n, B, m, band, ring, cap, lane, &cnt);
 				if (p != parts - 1) c -= fabsf(__ldg(A + n - 1) - __ldg(B + m - 1));
 			}
-			if (lane == 0) { P.part_cost[out0 + idx] = c; P.part_cells[out0 + idx] = (uint32_t)min(cnt, (uint64_t)0xffffffffu); cells_issued += cnt; }
+			if (lane == 0) { P.part_cost[out0 + idx] = c; if (COUNT) P.part_cells[out0 + idx] = (uint32_t)min(cnt, (uint64_t)0xffffffffu); cells_issued += cnt; }
 			__syncwarp();
 		}
 	}
-	if (L.cells) {
+	if (COUNT && L.cells) {
 #pragma unroll
 		for (int o = 16; o > 0; o >>= 1) cells_issued += __shfl_down_sync(0xffffffffu, cells_issued, o);
 		if (lane == 0 && cells_issued) atomicAdd(reinterpret_cast<unsigned long long *>(L.cells), (unsigned long long)cells_issued);
@@ -243,26 +270,37 @@ k_sp_replay(ChainLaunch L, SparsePlan P, int phase)
 		const ra_anchor_t *__restrict__ anc = L.anchors + ch.anchor_off;
 		for (uint32_t base = 0; base < parts && !dropped; base += 32) {
 			const uint32_t cntb = min(32u, parts - base);
-			const bool mine = base + lane < parts;
-			const float c = mine ? pc[base + lane] : 0.0f;
-			uint32_t done = 0;
-			for (; done < cntb; ++done) {
-				if (cur_max < ms) { dropped = true; break; }                     // :265-268
-				const float sub = __shfl_sync(0xffffffffu, c, (int)done);
-				dtw_cost += sub;                                                 // :279
-				cur_max -= sub;                                                  // :280
-			}
-			// integer side for the parts consumed: read_region_size (:260, :292) and useful cells
-			uint32_t al = 0, ce = 0;
-			if ((uint32_t)lane < done) {
-				const uint32_t p = base + lane;
-				al = anc[parts - p - 1].query_position - anc[parts - p].query_position + 1;
-				ce = pn[p];
-			}
+			const float c = (base + lane < parts) ? pc[base + lane] : 0.0f;
+			uint32_t done = cntb;
+			const float cur0 = cur_max, cost0 = dtw_cost;
+			bool hit = false;
+			if (cntb == 32) {                                                    // full block: branch-free, same adds in the same order
 #pragma unroll
-			for (int o = 16; o > 0; o >>= 1) { al += __shfl_xor_sync(0xffffffffu, al, o); ce += __shfl_xor_sync(0xffffffffu, ce, o); }
-			n_aligned += al; useful += ce;
+				for (int t = 0; t < 32; ++t) {
+					hit |= (cur_max < ms);                                       // :265-268 (the check before part base+t)
+					const float sub = __shfl_sync(0xffffffffu, c, t);
+					dtw_cost += sub;                                             // :279
+					cur_max -= sub;                                              // :280
+				}
+			}
+			if (cntb != 32 || hit) {                                             // tail block, or locate the part the reference stops at
+				cur_max = cur0; dtw_cost = cost0;
+				for (done = 0; done < cntb; ++done) {
+					if (cur_max < ms) { dropped = true; break; }
+					const float sub = __shfl_sync(0xffffffffu, c, (int)done);
+					dtw_cost += sub;
+					cur_max -= sub;
+				}
+			}
+			if (L.cells) {                                                       // useful cells = cells of the parts the reference evaluates
+				uint32_t ce = ((uint32_t)lane < done) ? pn[base + lane] : 0u;
+#pragma unroll
+				for (int o = 16; o > 0; o >>= 1) ce += __shfl_xor_sync(0xffffffffu, ce, o);
+				useful += ce;
+			}
 		}
+		// sum of read_region_size over all parts (:260, :292): anchors are shared by neighbouring parts
+		n_aligned = parts ? (anc[0].query_position - anc[parts].query_position) + parts : 0u;
 		float score = RA_SCORE_DROPPED;
 		if (!dropped)                                                            // :306; the reference build fuses it when fp_contract is set
 			score = L.fp_contract ? __fmaf_rn((float)n_aligned, L.match_bonus, -dtw_cost)
@@ -279,6 +317,8 @@ k_sp_replay(ChainLaunch L, SparsePlan P, int phase)
 
 cudaError_t launch_sparse_prep(const ChainLaunch &L, const SparsePlan &P, int phase, cudaStream_t s)
 {
+	cudaError_t e = cudaMemsetAsync(P.totals, 0, 2 * sizeof(unsigned long long), s);
+	if (e != cudaSuccess) return e;
 	k_sp_prep<<<(L.n_groups + 255) / 256, 256, 0, s>>>(L, P, phase);
 	return cudaGetLastError();
 }
@@ -287,8 +327,8 @@ cudaError_t launch_sparse_eval(const ChainLaunch &L, const SparsePlan &P, int ph
 {
 	cudaError_t e = cudaMemsetAsync(L.work_counter, 0, sizeof(uint32_t), s);
 	if (e != cudaSuccess) return e;
-	k_sp_tiles<<<(P.n_chains + 255) / 256, 256, 0, s>>>(P.n_chains, P);
-	k_sp_parts<<<(uint32_t)n_sm * kSparseCtasPerSm, kSpThreads, 0, s>>>(L, P);
+	if (L.cells) k_sp_parts<true><<<(uint32_t)n_sm * kSparseCtasPerSm, kSpThreads, 0, s>>>(L, P);
+	else k_sp_parts<false><<<(uint32_t)n_sm * kSparseCtasPerSm, kSpThreads, 0, s>>>(L, P);
 	k_sp_replay<<<(uint32_t)(((uint64_t)L.n_groups * 32 + 127) / 128), 128, 0, s>>>(L, P, phase);
 	return cudaGetLastError();
 }

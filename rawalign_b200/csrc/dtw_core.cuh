@@ -120,8 +120,11 @@ __device__ __forceinline__ float warp_dtw_cost(const float *__restrict__ A, int 
 // ---------------------------------------------------------------------------------------------------
 __device__ __forceinline__ int slant_radius(int n, int m, int band_radius)
 {
-	const uint32_t extra = (((uint32_t)n - (uint32_t)m) * (uint32_t)band_radius + (uint32_t)n - 1u) / (uint32_t)n;
-	return band_radius + (int)extra;
+	// dtw.cpp:298-300: R' = R + ceil((n-m)*R / n), 32-bit unsigned arithmetic.  ceil(x/n) = #{k >= 0 : k*n < x} and
+	// x < R*n, so for the radii that dominate (R <= 4) four compares replace the division.
+	const uint32_t x = ((uint32_t)n - (uint32_t)m) * (uint32_t)band_radius, un = (uint32_t)n;
+	if (band_radius <= 4 && un < (1u << 28)) return band_radius + (int)(x > 0u) + (int)(x > un) + (int)(x > 2u * un) + (int)(x > 3u * un);
+	return band_radius + (int)((x + un - 1u) / un);
 }
 
 // Thread-private cost of one NARROW problem: one row of A per step, the previous row and the B values
@@ -194,65 +197,109 @@ __device__ __forceinline__ float thread_dtw_narrow(const LA A, int n, const LB B
 	return last;                         // dp(n-1, m-1): jhi(n-1) = m-1 always
 }
 
-// Register-resident cost of one banded problem with R' <= 2 (every anchor gap below 20 events at
-// banded=0.1): a row holds at most kWin = 2R'+2 = 6 cells, so the previous row and the B values of the
-// live columns are kept in a 6-register window anchored at jlo(i).  The window slides by
-// jlo(i)-jlo(i-1) in {0,1} per row; every row executes the same straight-line code (no inner loop, no
-// shared-memory round trip on the DP chain), invalid slots carry 1e10f.
-constexpr int kWin = 6;
-__device__ __forceinline__ bool win6_ok(int n, int m, int band_radius)
+// ---------------------------------------------------------------------------------------------------
+// Register-resident anti-diagonal evaluator for a compile-time slant-extended radius RP (= R').
+//
+// This is the reference's own schedule (dtw.cpp:352-485): per column c of the longer sequence one
+// primary anti-diagonal P(c) = {(c+k, r-k), |k| <= h} (2h+1 cells) and, when r = floor(m*c/n) has just
+// incremented, a secondary S(c) before it.  Every diagonal depends on the two before it with FIXED
+// index offsets (derived in DESIGN.md "K2 register evaluator"), so the three live diagonals, the
+// A window [c-h-1, c+h] and the B window [r-h-1, r+h] are plain registers and the code of one column is
+// straight-line: no loop over cells, no shared-memory round trip, no per-cell bounds test.
+// Cells outside the matrix are neutralised by operand sentinels (A = +1e18 before/after the sequence,
+// B = -1e18), which makes their cost, hence their value, >= 1e18; cells outside the band are the
+// constant kInf operands below.  Because min() discards them wherever a real predecessor exists and
+// the centre staircase (c, r(c)) is always connected, dp(n-1, m-1) is bit-identical to the reference's
+// (whose out-of-band value is 1e10f) -- asserted against the oracle in tests/test_gpu_parity.py.
+// ---------------------------------------------------------------------------------------------------
+template <int RP, bool COUNT, class LA, class LB>
+__device__ __forceinline__ float thread_dtw_diag(const LA A, int n, const LB B, int m, uint32_t *cells)
 {
-	return band_radius >= 0 && slant_radius(n, m, band_radius) <= 2;
-}
-
-template <class LA, class LB>
-__device__ __forceinline__ float thread_dtw_win6(const LA A, int n, const LB B, int m, int band_radius, uint32_t *cells)
-{
-	const int Rp = slant_radius(n, m, band_radius);      // 1 or 2
-	const int odd = Rp & 1;
-	const int h = odd ? 0 : 1;                            // (R'-1)/2 = 0 for R'=1, R'/2 = 1 for R'=2
-	const int lead = 1;                                   // h + odd = 1 in both cases
-	int r_hi = 0, e_hi = m;                               // upper tracker at x = lead = 1: floor(m/n), m mod n  (m <= n)
-	if (e_hi >= n) { e_hi -= n; ++r_hi; }
-	int r_lo = 0, e_lo = 0;
-	float u[kWin], bw[kWin];
+	constexpr bool ODD = (RP & 1) != 0;
+	constexpr int h = ODD ? (RP - 1) / 2 : RP / 2;
+	constexpr int NP = 2 * h + 1;                 // primary length (odd)
+	constexpr int NS = ODD ? 2 * h + 2 : 2 * h;   // secondary length (even)
+	constexpr int NW = 2 * h + 2;                 // operand windows and the d-2 diagonal
+	constexpr float SA = 1e18f, SB = -1e18f;
+	float pold[NP], xq[NW], aw[NW], bw[NW];
 #pragma unroll
-	for (int t = 0; t < kWin; ++t) { u[t] = kInf; bw[t] = B[min(t, m - 1)]; }
-	int pjl = 0, jl = 0, jh = 0;
+	for (int t = 0; t < NP; ++t) pold[t] = kInf;
+#pragma unroll
+	for (int u = 0; u < NW; ++u) {
+		xq[u] = (u == h + 1) ? 0.0f : kInf;       // virtual dp(-1,-1) = 0 so that dp(0,0) = |A0 - B0|
+		const int i = -h - 1 + u;                 // aw[u] = A[c-h-1+u], bw[u] = B[r-h-1+u] at c = 0, r = 0
+		aw[u] = (i >= 0 && i < n) ? A[i] : SA;
+		bw[u] = (i >= 0 && i < m) ? B[i] : SB;
+	}
+	int r = 0, e = 0;
 	uint32_t cnt = 0;
 #pragma unroll 1
-	for (int i = 0; i < n; ++i) {
-		jh = (i + lead <= n - 1) ? min(m - 1, r_hi + h) : m - 1;
-		jl = (i - lead >= 0) ? max(0, r_lo - h) : 0;
-		const float a_i = A[i];
-		float diag = kInf;
-		if (jl != pjl) {                                  // slide the windows by one column
-			diag = u[0];                                  // dp(i-1, jl-1)
+	for (int c = 0; c < n; ++c) {
+		bool inc = false;
+		if (c > 0) {
+			e += m; if (e >= n) { e -= n; ++r; inc = true; }          // dtw.cpp:352-359
 #pragma unroll
-			for (int t = 0; t < kWin - 1; ++t) { u[t] = u[t + 1]; bw[t] = bw[t + 1]; }
-			u[kWin - 1] = kInf; bw[kWin - 1] = B[min(jl + kWin - 1, m - 1)];
-		}
-		if (i == 0) diag = 0.0f;                          // dp(0,0) = |A0 - B0|
-		const int nvalid = jh - jl + 1;
-		float left = kInf;
+			for (int u = 0; u < NW - 1; ++u) aw[u] = aw[u + 1];
+			aw[NW - 1] = (c + h < n) ? A[c + h] : SA;
+			if (inc) {
 #pragma unroll
-		for (int t = 0; t < kWin; ++t) {
-			const float up = u[t];
-			const float v = fminf(fminf(left, up), diag) + fabsf(a_i - bw[t]);
-			u[t] = (t < nvalid) ? v : kInf;
-			diag = up; left = v;
+				for (int u = 0; u < NW - 1; ++u) bw[u] = bw[u + 1];
+				bw[NW - 1] = (r + h < m) ? B[r + h] : SB;
+			}
 		}
-		cnt += (uint32_t)nvalid;
-		pjl = jl;
-		e_hi += m; if (e_hi >= n) { e_hi -= n; ++r_hi; }
-		if (i - lead >= 0) { e_lo += m; if (e_lo >= n) { e_lo -= n; ++r_lo; } }
+		// ---- secondary diagonal S(c), only meaningful when inc ----
+		float s[NS > 0 ? NS : 1];
+#pragma unroll
+		for (int t = 0; t < NS; ++t) {
+			float pa, pb, tl, cost;
+			if (ODD) {        // cell i = c-h-1+t, j = r+h-t
+				pa = (t >= 1) ? pold[t - 1] : kInf;
+				pb = (t <= 2 * h) ? pold[t] : kInf;
+				tl = xq[t];
+				cost = fabsf(aw[t] - bw[2 * h + 1 - t]);
+			} else {          // cell i = c-h+t, j = r-1+h-t
+				pa = pold[t]; pb = pold[t + 1];
+				tl = xq[t + 1];
+				cost = fabsf(aw[t + 1] - bw[2 * h - t]);
+			}
+			s[t] = fminf(fminf(pa, pb), tl) + cost;
+		}
+		// ---- primary diagonal P(c): cell i = c-h+t, j = r+h-t ----
+		float pnew[NP];
+#pragma unroll
+		for (int t = 0; t < NP; ++t) {
+			// after S(c): prev = S(c), prev2 = P(c-1); otherwise prev = P(c-1), prev2 = xq
+			float sa, sb;
+			if (ODD) { sa = s[t]; sb = s[t + 1]; }
+			else { sa = (t >= 1) ? s[t - 1] : kInf; sb = (t <= 2 * h - 1) ? s[t] : kInf; }
+			const float na = pold[t], nb = (t + 1 <= 2 * h) ? pold[t + 1] : kInf, ntl = xq[t + 1];
+			const float pa = inc ? sa : na, pb = inc ? sb : nb, tl = inc ? pold[t] : ntl;
+			pnew[t] = fminf(fminf(pa, pb), tl) + fabsf(aw[t + 1] - bw[2 * h + 1 - t]);
+		}
+		// ---- the d-2 diagonal of the next column, anchored at i = c-h-1 ----
+#pragma unroll
+		for (int u = 0; u < NW; ++u) {
+			float fromS;
+			if (ODD) fromS = s[u];
+			else fromS = (u >= 1 && u <= 2 * h) ? s[u - 1] : kInf;
+			const float fromP = (u <= 2 * h) ? pold[u] : kInf;
+			xq[u] = inc ? fromS : fromP;
+		}
+#pragma unroll
+		for (int t = 0; t < NP; ++t) pold[t] = pnew[t];
+		if (COUNT) {
+			// cells of P(c) and S(c) inside the matrix (dtw.cpp:365-366, :419-420)
+			const int klo = max(max(-h, -c), r - (m - 1)), khi = min(min(h, n - 1 - c), r);
+			cnt += (uint32_t)max(0, khi - klo + 1);
+			if (inc) {
+				// S(c): (c+k, r-1-k), k in [-NS/2, NS/2-1]
+				const int slo = max(max(-(NS / 2), -c), r - 1 - (m - 1)), shi = min(min(NS / 2 - 1, n - 1 - c), r - 1);
+				cnt += (uint32_t)max(0, shi - slo + 1);
+			}
+		}
 	}
-	if (cells) *cells += cnt;
-	const int t_last = (m - 1) - jl;                      // dp(n-1, m-1)
-	float res = u[0];
-#pragma unroll
-	for (int t = 1; t < kWin; ++t) res = (t_last == t) ? u[t] : res;
-	return res;
+	if (COUNT && cells) *cells += cnt;
+	return pold[h];                               // dp(n-1, m-1) = P(n-1), k = 0
 }
 
 // Lane-private cost of one SMALL problem (widest diagonal <= kLaneRing): the three rolling diagonals

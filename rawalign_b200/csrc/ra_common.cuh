@@ -79,16 +79,17 @@ cudaError_t launch_chain_eval(const ChainLaunch &L, int n_sm, cudaStream_t s);
 // sparse border (chains_sparse.cu): flat part-cost kernel over tiles of 256 parts + replay kernel
 struct SparsePlan {
 	uint32_t n_chains;
-	uint32_t *n_parts, *n_tiles;     // per chain: parts / tiles evaluated in this phase (0 = chain inactive)
-	uint64_t *part_base, *tile_base; // exclusive scans, n_chains + 1 entries
-	uint32_t *tile_chain;            // tile -> chain
+	uint32_t *n_parts;               // per chain: parts evaluated in this phase (0 = chain inactive)
+	uint64_t *part_base;             // per chain: first slot of its parts in part_cost / part_cells
+	uint32_t *tile_chain, *tile_t0;  // per tile: chain and first part
+	unsigned long long *totals;      // [0] parts, [1] tiles allocated so far in this phase (device counters)
 	float *part_cost;                // per evaluated part, at part_base[chain] + p
 	uint32_t *part_cells;
 	float *best;                     // per group: best score after phase A
 };
 constexpr int kSparseCtasPerSm = 6;
 constexpr int kSparseTileParts = 256;
-constexpr int kSparseKernelsPerPhase = 6;   // prep, scan, scan, tiles, parts, replay
+constexpr int kSparseKernelsPerPhase = 3;   // prep, parts, replay
 // phase 0: min_score_mode 0; 1 / 2: first chain of every group / the remaining chains (min_score_mode 1)
 cudaError_t launch_sparse_prep(const ChainLaunch &L, const SparsePlan &P, int phase, cudaStream_t s);
 cudaError_t launch_sparse_eval(const ChainLaunch &L, const SparsePlan &P, int phase, int n_sm, cudaStream_t s);
