@@ -449,3 +449,31 @@ void ora_dtw_batch(const float *a_arena, const float *b_arena, const ora_item_t 
 			                         it->band_radius, (int)it->exclude_last, 0);
 	}
 }
+
+/* ================================================================================================
+ * Checker for the kernel's division-by-window shortcut (rawalign_b200/csrc/events_fused.cu):
+ *   rcp = RN(1/w); q0 = RN(x*rcp); r = fma(-q0, w, x); q = fma(r, rcp, q0)
+ * must equal the correctly rounded x / w that revent.c:59-61,69 performs.  Exhaustive over all 2^23
+ * mantissas at three exponents (the sequence is scale-invariant away from under/overflow; the kernel
+ * only takes the shortcut for 1e-30 <= |x| <= 1e30).  Returns the number of mismatches.
+ * ============================================================================================== */
+uint64_t ora_check_fastdiv(uint32_t w)
+{
+	const float wf = (float)w;
+	const float rcp = 1.0f / wf;
+	uint64_t bad = 0;
+	const float scales[3] = { 1.0f, 1048576.0f, 1.0f / 1048576.0f };
+	for (int s = 0; s < 3; ++s)
+		for (uint32_t mant = 0; mant < (1u << 23); ++mant) {
+			union { uint32_t u; float f; } v;
+			v.u = 0x3f800000u | mant;
+			const float x = v.f * scales[s];
+			const float q0 = x * rcp;
+			const float r = fmaf(-q0, wf, x);
+			const float q = fmaf(r, rcp, q0);
+			if (q != x / wf) ++bad;
+			const float qn = fmaf(fmaf(q0, wf, -x), rcp, -q0);   /* same sequence on -x */
+			if (qn != (-x) / wf) ++bad;
+		}
+	return bad;
+}

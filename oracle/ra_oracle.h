@@ -29,6 +29,7 @@ void ora_evaluate_chains(const ora_anchor_t *anchors, const uint64_t *anchor_off
                          const float *read, const float *const *ref_per_chain, const ora_dtwopt_t *opt,
                          int score_fma, float *alignment_score, uint8_t *keep, uint64_t *cells_out);
 void ora_dtw_batch(const float *a_arena, const float *b_arena, const ora_item_t *items, uint32_t n_items, float *cost);
+uint64_t ora_check_fastdiv(uint32_t w);
 
 #ifdef __cplusplus
 }

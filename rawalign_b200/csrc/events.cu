@@ -341,6 +341,12 @@ cudaError_t launch_events(const float *sig, const uint64_t *chunk_off, const uin
 	return cudaGetLastError();
 }
 
+cudaError_t launch_exclusive_scan_u32_chained(const uint32_t *in, uint64_t *out, uint32_t n, int chained, cudaStream_t s)
+{
+	k_exclusive_scan_u32<<<1, 1024, 0, s>>>(in, out, n, chained);
+	return cudaGetLastError();
+}
+
 cudaError_t launch_exclusive_scan_u32(const uint32_t *in, uint64_t *out, uint32_t n, cudaStream_t s)
 {
 	k_exclusive_scan_u32<<<1, 1024, 0, s>>>(in, out, n, 0);

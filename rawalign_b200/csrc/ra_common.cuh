@@ -27,7 +27,17 @@ cudaError_t launch_events(const float *sig, const uint64_t *chunk_off, const uin
                           uint64_t *ev_off, int chained, float *ev_out, uint64_t ev_cap, uint32_t *ev_pos, cudaStream_t s,
                           cudaEvent_t after_detect);
 cudaError_t launch_exclusive_scan_u32(const uint32_t *in, uint64_t *out, uint32_t n, cudaStream_t s);
+cudaError_t launch_exclusive_scan_u32_chained(const uint32_t *in, uint64_t *out, uint32_t n, int chained, cudaStream_t s);
 bool events_windows_supported(uint32_t w1, uint32_t w2);
+// ---- launchers (events_fused.cu): one pass over the signal; windows up to kFusedMaxWindow ----------
+constexpr uint32_t kFusedMaxWindow = 14;
+constexpr int kFusedEventKernels = 3;
+bool events_fused_supported(uint32_t w1, uint32_t w2);
+void events_fused_layout(uint32_t max_len, const EvParams &p, uint32_t *raw_stride, size_t *floats_per_chunk);
+cudaError_t launch_events_fused(const float *sig, const uint64_t *chunk_off, const uint32_t *chunk_len, uint32_t n_chunks,
+                                uint32_t max_len, const EvParams &p, int contract, float *scratch, uint32_t *n_ev,
+                                uint64_t *ev_off, int chained, float *ev_out, uint64_t ev_cap, uint32_t *ev_pos, int n_sm,
+                                cudaStream_t s, cudaEvent_t after_detect);
 constexpr int kEventKernels = 5;
 
 // ---- launchers (dtw.cu) ------------------------------------------------------------------------

@@ -21,11 +21,12 @@ def test_extension_is_loaded(ctx):
 
 
 # ---- K1 ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("unfused", [0, 1])
 @pytest.mark.parametrize("contract,key", [(1, "ev_fma"), (0, "ev_nofma")])
-def test_events_golden(ctx, event_golden, contract, key):
+def test_events_golden(ctx, event_golden, contract, key, unfused):
     import rawalign_b200 as ra
     g = event_golden
-    opt = ra.ri_mapopt_init(); opt.fp_contract = contract
+    opt = ra.ri_mapopt_init(); opt.fp_contract = contract; opt.reserved = unfused
     ctx.set_opt(opt)
     try:
         n = len(g["sig_off"]) - 1
