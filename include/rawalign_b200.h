@@ -65,8 +65,8 @@ typedef struct ra_mapopt_s {
 	float    dtw_match_bonus;     /* 0.4f */
 	float    dtw_min_score;       /* 20.0f */
 	uint32_t fp_contract;         /* 1 */
-	uint32_t reserved;            /* 0; bit 0 set = run event detection as the five-kernel pipeline instead of the fused
-	                                 kernel (test hook; it is also the path taken for windows > 14) */
+	uint32_t reserved;            /* 0 = default event-detection pipeline; test hooks: bit 0 = the earlier five-kernel form
+	                                 (also the path taken for windows > 14), bit 1 = the single-pass fused kernel */
 } ra_mapopt_t;
 
 /* One DTW problem = one call of DTW_global / DTW_global_slantedbanded_antidiagonalwise /

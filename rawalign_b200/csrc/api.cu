@@ -66,7 +66,8 @@ struct ra_ctx {
 	DevBuf anchors, chains, group_first, min_score, score, keep, cells, chain_ring;
 	DevBuf sp_nparts, sp_ntiles, sp_pbase, sp_tbase, sp_tchain, sp_cost, sp_pcells, sp_best;   // sparse-border plan (chains_sparse.cu)
 	uint64_t resident_events = 0;      // events left on the device by the last ra_detect_events_batch
-	bool force_unfused_events = false; // test hook: run the five-kernel K1 (also the path for windows > kFusedMaxWindow)
+	bool force_unfused_events = false; // test hook: run the five-kernel K1 v2 (also the path for windows > kFusedMaxWindow)
+	bool force_fused_events = false;   // test hook: run the single-pass K1 v3
 	bool want_ev_pos = true;           // keep the event start samples of the last K1 call (ra_last_event_positions)
 	// traceback
 	DevBuf dirs, dir_off, slot_off, slot_i, slot_j, slot_d, path_len, path_off, out_i, out_j, out_d;
@@ -85,10 +86,13 @@ int events_dev(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_dev,
 		return fail(RA_EUNSUP, "event detector windows (%u,%u) are not supported", o.window_length1, o.window_length2);
 	if (n_chunks == 0) { if (total_events) *total_events = 0; uint64_t z = 0; RA_CUDA(cudaMemcpyAsync(ev_off_dev, &z, 8, cudaMemcpyHostToDevice, ctx->stream)); RA_CUDA(cudaStreamSynchronize(ctx->stream)); return RA_OK; }
 	ra::EvParams p = { o.window_length1, o.window_length2, o.threshold1, o.threshold2, o.peak_height };
-	const bool fused = ra::events_fused_supported(o.window_length1, o.window_length2) && !ctx->force_unfused_events;
+	// K1 variants: v4 pipeline (default), v3 fused single pass (reserved bit 1), v2 five kernels (reserved bit 0 or windows > 14)
+	const bool pipe = ra::events_pipe_supported(o.window_length1, o.window_length2) && !ctx->force_unfused_events && !ctx->force_fused_events;
+	const bool fused = !pipe && ra::events_fused_supported(o.window_length1, o.window_length2) && !ctx->force_unfused_events;
 	ra::EvScratch lay; ra::events_scratch_layout(max_chunk_len, p, &lay);
 	size_t fpc = lay.floats_per_chunk;
 	if (fused) { uint32_t stride; ra::events_fused_layout(max_chunk_len, p, &stride, &fpc); }
+	if (pipe) { uint32_t stride, pstride; ra::events_pipe_layout(max_chunk_len, p, &stride, &pstride, &fpc); }
 	const uint32_t sub = std::min(n_chunks, kEventSubBatch);
 	int rc;
 	if ((rc = ctx->raw.reserve((size_t)sub * fpc * sizeof(float)))) return rc;
@@ -98,7 +102,12 @@ int events_dev(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_dev,
 	for (uint32_t s0 = 0; s0 < n_chunks; s0 += sub) {
 		const uint32_t n = std::min(sub, n_chunks - s0);
 		const bool last = (s0 + n == n_chunks);
-		if (fused) {
+		if (pipe) {
+			RA_CUDA(ra::launch_events_pipe(sig_dev, chunk_off_dev + s0, chunk_len_dev + s0, n, max_chunk_len, p, (int)o.fp_contract,
+			                               ctx->raw.as<float>(), ctx->nev.as<uint32_t>(), ev_off_dev + s0, s0 != 0, ev_out_dev, ev_cap,
+			                               ctx->want_ev_pos ? ctx->ev_pos.as<uint32_t>() : nullptr, ctx->stream, last ? ctx->ev[1] : nullptr));
+			ctx->launches += ra::kPipeEventKernels;
+		} else if (fused) {
 			RA_CUDA(ra::launch_events_fused(sig_dev, chunk_off_dev + s0, chunk_len_dev + s0, n, max_chunk_len, p, (int)o.fp_contract,
 			                                ctx->raw.as<float>(), ctx->nev.as<uint32_t>(), ev_off_dev + s0, s0 != 0, ev_out_dev, ev_cap,
 			                                ctx->want_ev_pos ? ctx->ev_pos.as<uint32_t>() : nullptr, ctx->n_sm, ctx->stream, last ? ctx->ev[1] : nullptr));
@@ -320,6 +329,7 @@ int ra_set_opt(ra_ctx *ctx, const ra_mapopt_t *opt)
 	if (opt->dtw_fill_method > RA_DTW_FILL_METHOD_BANDED) return fail(RA_EINVAL, "invalid fill method %u", opt->dtw_fill_method);
 	ctx->opt = *opt;
 	ctx->force_unfused_events = (opt->reserved & 1u) != 0;
+	ctx->force_fused_events = (opt->reserved & 2u) != 0;
 	return RA_OK;
 }
 

@@ -1,0 +1,489 @@
+// events_pipe.cu -- K1 v4: detect_events() (src/revent.c:190-210) for a batch of chunks as a pipeline of
+// kernels that each use exactly the parallelism their stage has.  Bit-identical to the reference build.
+//
+// What the reference's arithmetic forces to be sequential per chunk: the fp32 prefix sums (revent.c:22-32,
+// rounding depends on the order) and the two-detector peak state machine (:77-138).  ncu on the fused v3
+// kernel (profiles/r01_ncu_full_v3_summary.md) showed it issue-bound at 7.7 of 32 active lanes because those
+// sections ran on k = 3 lanes per warp.  Here every lane of a warp owns one chunk in the sequential stages
+// (32 chunks per warp, all lanes busy, nothing but the recurrence on the critical path), HBM latency is
+// hidden by a 4-stage cp.async ring of 32-sample x 32-chunk tiles in shared memory, and everything that is
+// position-independent runs in fully parallel kernels:
+//
+//   k_prefix_pipe  lane per chunk   ps/pss recurrences; tiles in by cp.async (16 B, coalesced 128 B rows),
+//                                   results out as 128-bit stores.  Row stride 36 floats: 16-byte aligned and
+//                                   conflict-free for lane-per-row LDS.128/STS.128.
+//   k_tstat_pipe   thread per sample both windows (:34-75).  mean2/e2 of position p equal mean1/e1 of position
+//                                   p+w (same expression, same operands), so every window mean is divided once
+//                                   and shared through shared memory: 3 instead of 5 divisions per window.
+//   k_fsm_pipe     lane per chunk   the detector state machine only: peak positions to a per-chunk list.  The
+//                                   event arithmetic (:140-188) is hoisted out of the recurrence.
+//   k_scan         one CTA          CSR offsets from the per-chunk peak counts (events.cu)
+//   k_finish_pipe  warp per chunk   event means in parallel (gather ps[peak]), fp64 sum/sum2 in emission order,
+//                                   z-normalisation, CSR write.
+//
+// HBM traffic per sample: 4 B in + 8 B ps/pss out, 8 B in + 8 B t-stats out, 8 B in = 36 B (scratch is
+// L2-absorbed only for small batches); per event 4 B peak + 4 B ps gather + 4-8 B out.
+//
+// Compiled with -fmad=false: fused multiply-adds exist only where the reference build has them (CONTRACT).
+#include "ra_common.cuh"
+#include <float.h>
+
+namespace ra {
+namespace evp {
+
+constexpr int kTile = 32;            // samples per tile per chunk
+constexpr int kRow = 36;             // shared-memory row stride (floats)
+constexpr int kStages = 4;
+constexpr int kTsBlock = 256;
+constexpr int kHalo = 16;            // >= kPipeMaxWindow
+
+__device__ __forceinline__ void cp_async16(float *smem_dst, const float *gsrc, int src_bytes)
+{
+	const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem_dst);
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(gsrc), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async4(float *smem_dst, const float *gsrc)
+{
+	const uint32_t s = (uint32_t)__cvta_generic_to_shared(smem_dst);
+	asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// Warp-cooperative load of one tile: rows r = 0..31 (chunk c0 + r), columns [base, base + 32) of a per-chunk array,
+// into dst[r * kRow + col].  Row r's samples start at rowp[r]; rowl[r] of them exist.  Pieces past the end of a
+// row are not loaded (consumers never read past rowl).
+template <bool ALIGNED>
+__device__ __forceinline__ void load_tile(float *dst, const float *const *rowp, const uint32_t *rowl, uint32_t base, int lane)
+{
+	const int piece = lane & 7;
+	const uint32_t p0 = base + 4u * (uint32_t)piece;
+#pragma unroll
+	for (int k = 0; k < 8; ++k) {
+		const int row = 4 * k + (lane >> 3);
+		const uint32_t len = rowl[row];
+		if (p0 < len) {
+			const float *g = rowp[row] + p0;
+			float *d = dst + row * kRow + 4 * piece;
+			const uint32_t n = min(4u, len - p0);
+			if (ALIGNED || (reinterpret_cast<uintptr_t>(g) & 15u) == 0) cp_async16(d, g, (int)(4u * n));
+			else
+				for (uint32_t e = 0; e < n; ++e) cp_async4(d + e, g + e);
+		}
+	}
+}
+
+// ---------------------------------------------------------------------------------------------------
+// k_prefix_pipe: psx[j] = ps[j+1], pssx[j] = pss[j+1] for j in [0, len)   (ps[0] = pss[0] = 0 is implicit)
+// ---------------------------------------------------------------------------------------------------
+template <bool CONTRACT>
+__global__ void __launch_bounds__(32)
+k_prefix_pipe(const float *__restrict__ sig, const uint64_t *__restrict__ chunk_off, const uint32_t *__restrict__ chunk_len,
+              uint32_t n_chunks, float *__restrict__ psx, float *__restrict__ pssx, uint32_t stride)
+{
+	__shared__ __align__(16) float in[kStages][32 * kRow];
+	__shared__ __align__(16) float outs[32 * kRow];
+	__shared__ __align__(16) float outq[32 * kRow];
+	__shared__ const float *rowp[32];
+	__shared__ uint32_t rowl[32];
+	const int lane = threadIdx.x;
+	const uint32_t c0 = blockIdx.x * 32u, c = c0 + (uint32_t)lane;
+	const uint32_t my_len = c < n_chunks ? chunk_len[c] : 0u;
+	rowp[lane] = c < n_chunks ? sig + chunk_off[c] : sig;
+	rowl[lane] = my_len;
+	uint32_t max_len = my_len;
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) max_len = max(max_len, __shfl_xor_sync(0xffffffffu, max_len, o));
+	__syncwarp();
+	const int n_tiles = (int)((max_len + kTile - 1) / kTile);
+#pragma unroll
+	for (int t = 0; t < kStages - 1; ++t) {
+		if (t < n_tiles) load_tile<false>(in[t], rowp, rowl, (uint32_t)t * kTile, lane);
+		cp_async_commit();
+	}
+	float s = 0.0f, q = 0.0f;                                         // revent.c:26-27
+	const int piece = lane & 7;
+	for (int t = 0; t < n_tiles; ++t) {
+		if (t + kStages - 1 < n_tiles) load_tile<false>(in[(t + kStages - 1) % kStages], rowp, rowl, (uint32_t)(t + kStages - 1) * kTile, lane);
+		cp_async_commit();
+		cp_async_wait<kStages - 1>();
+		__syncwarp();
+		const uint32_t base = (uint32_t)t * kTile;
+		if (base < my_len) {
+			const float *row = in[t % kStages] + lane * kRow;
+			const uint32_t cnt = min((uint32_t)kTile, my_len - base);
+#pragma unroll
+			for (int k = 0; k < 8; ++k) {
+				const float4 v = *reinterpret_cast<const float4 *>(row + 4 * k);
+				const float x[4] = { v.x, v.y, v.z, v.w };
+				float a[4], b[4];
+#pragma unroll
+				for (int e = 0; e < 4; ++e) {
+					if ((uint32_t)(4 * k + e) < cnt) {
+						s = __fadd_rn(s, x[e]);                                                                  // :29
+						q = CONTRACT ? __fmaf_rn(x[e], x[e], q) : __fadd_rn(q, __fmul_rn(x[e], x[e]));             // :30
+					}
+					a[e] = s; b[e] = q;
+				}
+				*reinterpret_cast<float4 *>(outs + lane * kRow + 4 * k) = make_float4(a[0], a[1], a[2], a[3]);
+				*reinterpret_cast<float4 *>(outq + lane * kRow + 4 * k) = make_float4(b[0], b[1], b[2], b[3]);
+			}
+		}
+		__syncwarp();
+		const uint32_t p0 = base + 4u * (uint32_t)piece;
+#pragma unroll
+		for (int k = 0; k < 8; ++k) {
+			const int row = 4 * k + (lane >> 3);
+			if (p0 < rowl[row]) {                                      // whole 16-byte piece: rows are padded to the stride
+				const size_t o = (size_t)(c0 + (uint32_t)row) * stride + p0;
+				*reinterpret_cast<float4 *>(psx + o) = *reinterpret_cast<const float4 *>(outs + row * kRow + 4 * piece);
+				*reinterpret_cast<float4 *>(pssx + o) = *reinterpret_cast<const float4 *>(outq + row * kRow + 4 * piece);
+			}
+		}
+		__syncwarp();
+	}
+}
+
+// ---------------------------------------------------------------------------------------------------
+// t-statistics
+// ---------------------------------------------------------------------------------------------------
+// x / wf, correctly rounded, for wf = a window length in [2, 32] (exhaustive check: tests/test_fastdiv.py)
+__device__ __forceinline__ float fdiv_w(float x, float wf, float rcp)
+{
+	const float ax = fabsf(x);
+	if ((ax >= 1e-30f && ax <= 1e30f) || ax == 0.0f) {
+		const float q0 = __fmul_rn(x, rcp);
+		const float r = __fmaf_rn(-q0, wf, x);
+		return __fmaf_rn(r, rcp, q0);
+	}
+	return __fdiv_rn(x, wf);
+}
+
+// revent.c:61-69 from the window means (mean1, mean2) and mean squares (e1, e2)
+template <bool CONTRACT>
+__device__ __forceinline__ float tstat_from_means(float mean1, float mean2, float e1, float e2, float wf, float rcp)
+{
+	float var;
+	if (CONTRACT) var = __fmaf_rn(-mean2, mean2, __fadd_rn(__fmaf_rn(-mean1, mean1, e1), e2));            // :61, two vfnmadd
+	else var = __fsub_rn(__fadd_rn(__fsub_rn(e1, __fmul_rn(mean1, mean1)), e2), __fmul_rn(mean2, mean2));
+	var = fmaxf(var, FLT_MIN);                                                                              // :63
+	const float dm = __fsub_rn(mean2, mean1);                                                               // :68
+	const float vw = fdiv_w(var, wf, rcp);
+	const float x = fabsf(dm);
+	// :69  (float)(fabs((double)dm) / sqrt((double)vw)).  y = x * rsqrt(vw) to ~2^-43 by one Newton step in fp64; the
+	// reference's doubly rounded quotient is within 2^-52 of the exact value, so both round to the same float unless y
+	// sits within 2^13 double ulps of a float rounding boundary -- then the exact path runs.
+	if (vw >= 1e-30f && vw <= 1e30f && x <= 1e30f) {
+		float r0f;
+		asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r0f) : "f"(vw));
+		const double r0 = (double)r0f, vd = (double)vw;
+		const double e = __fma_rn(-__dmul_rn(vd, r0), r0, 1.0);
+		const double r1 = __fma_rn(__dmul_rn(r0, 0.5), e, r0);
+		const double y = __dmul_rn((double)x, r1);
+		const uint32_t lo = (uint32_t)__double2loint(y);
+		const bool near_boundary = ((lo - (0x10000000u - 0x2000u)) & 0x1FFFFFFFu) < 0x4000u;
+		if (!near_boundary && (y >= 1e-37 || y == 0.0)) return __double2float_rn(y);
+	}
+	return __double2float_rn(__ddiv_rn((double)x, __dsqrt_rn((double)vw)));
+}
+
+// grid: x = tiles of kTsBlock positions, y = chunk.  kTsThreads = kTsBlock + 32: thread u owns position base + u for the
+// window means (the last 32 threads only serve the look-ahead of up to kPipeMaxWindow positions), threads < kTsBlock
+// then own one output position each.
+constexpr int kTsThreads = kTsBlock + 32;
+template <bool CONTRACT>
+__global__ void __launch_bounds__(kTsThreads)
+k_tstat_pipe(const uint32_t *__restrict__ chunk_len, const float *__restrict__ psx, const float *__restrict__ pssx, uint32_t stride,
+             float *__restrict__ t1, float *__restrict__ t2, uint32_t w1, uint32_t w2, float rcp1, float rcp2)
+{
+	__shared__ float sp[kTsThreads + kHalo], sq[kTsThreads + kHalo];  // ps[j], pss[j] for j = base - kHalo + t
+	__shared__ float M1[kTsThreads], E1[kTsThreads], M2[kTsThreads], E2[kTsThreads];
+	const uint32_t c = blockIdx.y;
+	const uint32_t len = chunk_len[c];
+	const int base = (int)(blockIdx.x * kTsBlock);
+	if ((uint32_t)base >= len) return;
+	const int u = threadIdx.x;
+	const float *__restrict__ prow = psx + (size_t)c * stride;
+	const float *__restrict__ qrow = pssx + (size_t)c * stride;
+	const int j = base + u;
+	{
+		const bool in = j >= 1 && j <= (int)len;                     // ps[0] = pss[0] = +0.0f (:26-27)
+		sp[u + kHalo] = in ? __ldg(prow + j - 1) : 0.0f;
+		sq[u + kHalo] = in ? __ldg(qrow + j - 1) : 0.0f;
+		if (u < kHalo) {
+			const int jh = base - kHalo + u;
+			const bool inh = jh >= 1;                                // jh < base < len
+			sp[u] = inh ? __ldg(prow + jh - 1) : 0.0f;
+			sq[u] = inh ? __ldg(qrow + jh - 1) : 0.0f;
+		}
+	}
+	__syncthreads();
+	const float w1f = (float)w1, w2f = (float)w2;
+	// window mean ending at j:  M(j) = (ps[j] - ps[j-w]) / w, j in [w, len].  At j == w the reference skips the
+	// subtraction (:53-56); ps[0] = +0.0f and x - 0.0f == x bit for bit.
+	if (j <= (int)len) {
+		const float s0 = sp[u + kHalo], q0 = sq[u + kHalo];
+		if (j >= (int)w1) {
+			M1[u] = fdiv_w(__fsub_rn(s0, sp[u + kHalo - (int)w1]), w1f, rcp1);
+			E1[u] = fdiv_w(__fsub_rn(q0, sq[u + kHalo - (int)w1]), w1f, rcp1);
+		}
+		if (j >= (int)w2) {
+			M2[u] = fdiv_w(__fsub_rn(s0, sp[u + kHalo - (int)w2]), w2f, rcp2);
+			E2[u] = fdiv_w(__fsub_rn(q0, sq[u + kHalo - (int)w2]), w2f, rcp2);
+		}
+	}
+	__syncthreads();
+	const uint32_t p = (uint32_t)j;
+	if (u >= kTsBlock || p >= len) return;
+	float v1 = 0.0f, v2 = 0.0f;
+	if (len >= 2u * w1 && w1 >= 2u && p >= w1 && p + w1 <= len)      // :46, :50
+		v1 = tstat_from_means<CONTRACT>(M1[u], M1[u + w1], E1[u], E1[u + w1], w1f, rcp1);
+	if (len >= 2u * w2 && w2 >= 2u && p >= w2 && p + w2 <= len)
+		v2 = tstat_from_means<CONTRACT>(M2[u], M2[u + w2], E2[u], E2[u + w2], w2f, rcp2);
+	t1[(size_t)c * stride + p] = v1;
+	t2[(size_t)c * stride + p] = v2;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// k_fsm_pipe: gen_peaks, revent.c:77-138
+// ---------------------------------------------------------------------------------------------------
+// One step of both detectors, revent.c:89-133, as straight-line predicated code (the lanes of a warp are in different
+// states at every step, so branches would serialise every path anyway; ncu on the branchy form: 116 warp
+// instructions per step at 14.5 active lanes).  Semantics, per detector, in the reference's order:
+//   masked_to >= i -> skip;  searching (pos == -1): v < pv -> pv = v, else v - pv > h -> pv = v, pos = i;
+//   tracking: v > pv -> pv = v, pos = i;  [short only] pv > thr -> mask + reset the long detector (:113-120);
+//   pv - v > h && pv > thr -> valid;  valid && i - pos > w/2 -> emit pos, pos = -1, pv = v, valid = 0.
+// The short detector is never masked (only the long one is, :116), so its masked_to stays 0: active iff i > 0.
+struct DetS { int pos; float pv; unsigned valid; };
+struct DetL { uint32_t masked_to; int pos; float pv; unsigned valid; };
+
+__device__ __forceinline__ void fsm_step(DetS &S, DetL &L, uint32_t i, float v1, float v2, float thr1, float thr2, float h,
+                                         uint32_t w1, uint32_t half1, uint32_t half2, uint32_t *__restrict__ peaks, uint32_t &n)
+{
+	// bitwise (&, |) on 0/1 flags instead of && / ||: no short-circuit evaluation, so nothing here needs a branch
+	// ---- short detector ----
+	{
+		const unsigned act = i > 0u;
+		const unsigned srch = S.pos < 0;
+		const unsigned lt = v1 < S.pv;
+		const unsigned rise = __fsub_rn(v1, S.pv) > h;
+		const unsigned gt = v1 > S.pv;
+		const unsigned setpos = act & ((srch & (lt ^ 1u) & rise) | ((srch ^ 1u) & gt));
+		const unsigned upd = act & ((srch & (lt | rise)) | ((srch ^ 1u) & gt));
+		const float pv = upd ? v1 : S.pv;
+		const int pos = setpos ? (int)i : S.pos;
+		const unsigned trk = act & (srch ^ 1u);
+		const unsigned over = pv > thr1;
+		const unsigned dom = trk & over;                                // :113-120
+		L.masked_to = dom ? (uint32_t)pos + w1 : L.masked_to;
+		L.pos = dom ? -1 : L.pos;
+		L.pv = dom ? FLT_MAX : L.pv;
+		L.valid = dom ? 0u : L.valid;
+		const unsigned valid = S.valid | (dom & (unsigned)(__fsub_rn(pv, v1) > h));     // :122
+		const unsigned emit = trk & valid & (unsigned)((i - (uint32_t)pos) > half1);    // :126
+		if (emit) peaks[n] = (uint32_t)pos;                          // :128
+		n += emit;
+		S.pos = emit ? -1 : pos; S.pv = emit ? v1 : pv; S.valid = emit ? 0u : valid;
+	}
+	// ---- long detector ----
+	{
+		const unsigned act = L.masked_to < i;
+		const unsigned srch = L.pos < 0;
+		const unsigned lt = v2 < L.pv;
+		const unsigned rise = __fsub_rn(v2, L.pv) > h;
+		const unsigned gt = v2 > L.pv;
+		const unsigned setpos = act & ((srch & (lt ^ 1u) & rise) | ((srch ^ 1u) & gt));
+		const unsigned upd = act & ((srch & (lt | rise)) | ((srch ^ 1u) & gt));
+		const float pv = upd ? v2 : L.pv;
+		const int pos = setpos ? (int)i : L.pos;
+		const unsigned trk = act & (srch ^ 1u);
+		const unsigned valid = L.valid | (trk & (unsigned)(pv > thr2) & (unsigned)(__fsub_rn(pv, v2) > h));
+		const unsigned emit = trk & valid & (unsigned)((i - (uint32_t)pos) > half2);
+		if (emit) peaks[n] = (uint32_t)pos;
+		n += emit;
+		L.pos = emit ? -1 : pos; L.pv = emit ? v2 : pv; L.valid = emit ? 0u : valid;
+	}
+}
+
+__global__ void __launch_bounds__(32)
+k_fsm_pipe(const uint32_t *__restrict__ chunk_len, uint32_t n_chunks, const float *__restrict__ t1, const float *__restrict__ t2,
+           uint32_t stride, EvParams prm, uint32_t *__restrict__ peaks_base, uint32_t peak_stride, uint32_t *__restrict__ n_peaks_out)
+{
+	__shared__ __align__(16) float s1[kStages][32 * kRow];
+	__shared__ __align__(16) float s2[kStages][32 * kRow];
+	__shared__ const float *rowp1[32];
+	__shared__ const float *rowp2[32];
+	__shared__ uint32_t rowl[32];
+	const int lane = threadIdx.x;
+	const uint32_t c0 = blockIdx.x * 32u, c = c0 + (uint32_t)lane;
+	const uint32_t my_len = c < n_chunks ? chunk_len[c] : 0u;
+	rowp1[lane] = t1 + (size_t)min(c, n_chunks - 1) * stride;
+	rowp2[lane] = t2 + (size_t)min(c, n_chunks - 1) * stride;
+	rowl[lane] = my_len;
+	uint32_t max_len = my_len;
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) max_len = max(max_len, __shfl_xor_sync(0xffffffffu, max_len, o));
+	__syncwarp();
+	const int n_tiles = (int)((max_len + kTile - 1) / kTile);
+#pragma unroll
+	for (int t = 0; t < kStages - 1; ++t) {
+		if (t < n_tiles) { load_tile<true>(s1[t], rowp1, rowl, (uint32_t)t * kTile, lane); load_tile<true>(s2[t], rowp2, rowl, (uint32_t)t * kTile, lane); }
+		cp_async_commit();
+	}
+	DetS sd = { -1, FLT_MAX, 0u };                                 // :198-202
+	DetL ld = { 0u, -1, FLT_MAX, 0u };
+	uint32_t n_peaks = 0;
+	uint32_t *__restrict__ peaks = peaks_base + (size_t)min(c, n_chunks - 1) * peak_stride;
+	const float thr1 = prm.thr1, thr2 = prm.thr2, ph = prm.peak_height;
+	const uint32_t w1 = prm.w1, half1 = prm.w1 / 2, half2 = prm.w2 / 2;
+	for (int t = 0; t < n_tiles; ++t) {
+		if (t + kStages - 1 < n_tiles) {
+			const int st = (t + kStages - 1) % kStages;
+			load_tile<true>(s1[st], rowp1, rowl, (uint32_t)(t + kStages - 1) * kTile, lane);
+			load_tile<true>(s2[st], rowp2, rowl, (uint32_t)(t + kStages - 1) * kTile, lane);
+		}
+		cp_async_commit();
+		cp_async_wait<kStages - 1>();
+		__syncwarp();
+		const uint32_t base = (uint32_t)t * kTile;
+		if (base < my_len) {
+			const float *r1 = s1[t % kStages] + lane * kRow, *r2 = s2[t % kStages] + lane * kRow;
+			const uint32_t cnt = min((uint32_t)kTile, my_len - base);
+			if (cnt == (uint32_t)kTile) {                               // full tile: no per-step guard
+#pragma unroll 2
+				for (int k = 0; k < 8; ++k) {
+					const float4 a = *reinterpret_cast<const float4 *>(r1 + 4 * k);
+					const float4 b = *reinterpret_cast<const float4 *>(r2 + 4 * k);
+					const uint32_t i = base + (uint32_t)(4 * k);
+					fsm_step(sd, ld, i, a.x, b.x, thr1, thr2, ph, w1, half1, half2, peaks, n_peaks);
+					fsm_step(sd, ld, i + 1u, a.y, b.y, thr1, thr2, ph, w1, half1, half2, peaks, n_peaks);
+					fsm_step(sd, ld, i + 2u, a.z, b.z, thr1, thr2, ph, w1, half1, half2, peaks, n_peaks);
+					fsm_step(sd, ld, i + 3u, a.w, b.w, thr1, thr2, ph, w1, half1, half2, peaks, n_peaks);
+				}
+			} else {
+#pragma unroll 1
+				for (uint32_t e = 0; e < cnt; ++e) fsm_step(sd, ld, base + e, r1[e], r2[e], thr1, thr2, ph, w1, half1, half2, peaks, n_peaks);
+			}
+		}
+		__syncwarp();
+	}
+	if (c < n_chunks) n_peaks_out[c] = n_peaks;                       // == number of events (see k_finish_pipe)
+}
+
+// ---------------------------------------------------------------------------------------------------
+// k_finish_pipe: gen_events, revent.c:140-188.  One warp per chunk.
+//
+// gen_events consumes peaks[0 .. n_ev-2] in emission order and closes the last event at s_len (:160-172): the final
+// peak of a chunk never bounds an event.  n_ev == n_peaks because the filter of :145-147 (0 < peaks[i] < s_len)
+// always holds: position 0 is never examined (masked_to(0) >= 0, :91) and positions are < s_len by construction.
+// ---------------------------------------------------------------------------------------------------
+template <bool CONTRACT>
+__global__ void __launch_bounds__(128)
+k_finish_pipe(const uint32_t *__restrict__ chunk_len, uint32_t n_chunks, const float *__restrict__ psx, uint32_t stride,
+              const uint32_t *__restrict__ peaks_base, uint32_t peak_stride, const uint32_t *__restrict__ n_peaks_in,
+              const uint64_t *__restrict__ ev_off, float *__restrict__ ev_out, uint64_t ev_cap, float *__restrict__ raw_base,
+              uint32_t *__restrict__ ev_pos)
+{
+	const uint32_t c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const int lane = threadIdx.x & 31;
+	if (c >= n_chunks) return;
+	const uint32_t n_ev = n_peaks_in[c];
+	if (n_ev == 0) return;                                            // detect_events returns NULL, *n untouched (:205-206)
+	const uint32_t len = chunk_len[c];
+	const float *__restrict__ ps1 = psx + (size_t)c * stride;         // ps[j] = ps1[j-1], j >= 1
+	const uint32_t *__restrict__ peaks = peaks_base + (size_t)c * peak_stride;
+	float *__restrict__ raw = raw_base + (size_t)c * peak_stride;
+	// event k: (ps[end_k] - ps[start_k]) / ((float)end_k - (float)start_k), end_k = peaks[k] (k < n_ev-1) or len,
+	// start_k = peaks[k-1] or 0                                      :160-172
+	double sum = 0.0, sum2 = 0.0;
+	for (uint32_t kb = 0; kb < n_ev; kb += 32) {
+		const uint32_t k = kb + (uint32_t)lane;
+		float ev = 0.0f;
+		if (k < n_ev) {
+			const uint32_t e_pos = (k + 1 < n_ev) ? peaks[k] : len;
+			const uint32_t s_pos = (k > 0) ? peaks[k - 1] : 0u;
+			const float l_ps = (s_pos > 0) ? __ldg(ps1 + s_pos - 1) : 0.0f;
+			const float e_ps = (e_pos > 0) ? __ldg(ps1 + e_pos - 1) : 0.0f;
+			ev = __fdiv_rn(__fsub_rn(e_ps, l_ps), __fsub_rn(__uint2float_rn(e_pos), __uint2float_rn(s_pos)));
+			raw[k] = ev;
+		}
+		// sum / sum2 in array order, fp64 (:163-164, :173-174): every lane carries the same accumulators
+		const uint32_t cnt = min(32u, n_ev - kb);
+		if (cnt == 32u) {
+#pragma unroll
+			for (int t = 0; t < 32; ++t) {
+				const float e = __shfl_sync(0xffffffffu, ev, t);
+				sum = __dadd_rn(sum, (double)e);
+				sum2 = __dadd_rn(sum2, (double)__fmul_rn(e, e));       // float product, then widened (:164)
+			}
+		} else {
+			for (uint32_t t = 0; t < cnt; ++t) {
+				const float e = __shfl_sync(0xffffffffu, ev, (int)t);
+				sum = __dadd_rn(sum, (double)e);
+				sum2 = __dadd_rn(sum2, (double)__fmul_rn(e, e));
+			}
+		}
+	}
+	const double mean = __ddiv_rn(sum, (double)n_ev);                  // :179
+	const double q = __ddiv_rn(sum2, (double)n_ev);
+	const double var = CONTRACT ? __fma_rn(-mean, mean, q) : __dsub_rn(q, __dmul_rn(mean, mean));   // :180
+	const double sd = __dsqrt_rn(var);
+	const uint64_t off = ev_off[c];
+	__syncwarp();
+	for (uint32_t k = lane; k < n_ev; k += 32)
+		if (off + k < ev_cap) {
+			ev_out[off + k] = __double2float_rn(__ddiv_rn(__dsub_rn((double)raw[k], mean), sd));           // :183
+			if (ev_pos) ev_pos[off + k] = (k > 0) ? peaks[k - 1] : 0u;   // first sample of the event (not part of the reference's output)
+		}
+}
+
+} // namespace evp
+
+bool events_pipe_supported(uint32_t w1, uint32_t w2) { return w1 >= 1 && w2 >= 1 && w1 <= kPipeMaxWindow && w2 <= kPipeMaxWindow; }
+
+void events_pipe_layout(uint32_t max_len, const EvParams &p, uint32_t *stride, uint32_t *peak_stride, size_t *floats_per_chunk)
+{
+	*stride = (max_len + 31u) & ~31u;
+	if (*stride == 0) *stride = 32;
+	// a detector emits at i >= peak_pos + w/2 + 1 and can only start its next peak at a later sample, so peaks of one
+	// detector are >= w/2 + 2 apart
+	*peak_stride = ((max_len / (p.w1 / 2 + 2) + max_len / (p.w2 / 2 + 2) + 4) + 3u) & ~3u;
+	*floats_per_chunk = 4 * (size_t)*stride + 2 * (size_t)*peak_stride;
+}
+
+cudaError_t launch_events_pipe(const float *sig, const uint64_t *chunk_off, const uint32_t *chunk_len, uint32_t n_chunks,
+                               uint32_t max_len, const EvParams &p, int contract, float *scratch, uint32_t *n_ev,
+                               uint64_t *ev_off, int chained, float *ev_out, uint64_t ev_cap, uint32_t *ev_pos, cudaStream_t s,
+                               cudaEvent_t after_detect)
+{
+	using namespace evp;
+	if (n_chunks == 0) return cudaSuccess;
+	uint32_t stride, pstride; size_t fpc;
+	events_pipe_layout(max_len, p, &stride, &pstride, &fpc);
+	float *psx = scratch;
+	float *pssx = psx + (size_t)n_chunks * stride;
+	float *t1 = pssx + (size_t)n_chunks * stride;
+	float *t2 = t1 + (size_t)n_chunks * stride;
+	uint32_t *peaks = reinterpret_cast<uint32_t *>(t2 + (size_t)n_chunks * stride);
+	float *raw = reinterpret_cast<float *>(peaks + (size_t)n_chunks * pstride);
+	const uint32_t lane_ctas = (n_chunks + 31u) / 32u;
+	const dim3 tgrid((max_len + kTsBlock - 1) / kTsBlock, n_chunks);
+	const float rcp1 = 1.0f / (float)p.w1, rcp2 = 1.0f / (float)p.w2;      // correctly rounded reciprocals (IEEE division on the host)
+	if (contract) {
+		k_prefix_pipe<true><<<lane_ctas, 32, 0, s>>>(sig, chunk_off, chunk_len, n_chunks, psx, pssx, stride);
+		k_tstat_pipe<true><<<tgrid, kTsThreads, 0, s>>>(chunk_len, psx, pssx, stride, t1, t2, p.w1, p.w2, rcp1, rcp2);
+	} else {
+		k_prefix_pipe<false><<<lane_ctas, 32, 0, s>>>(sig, chunk_off, chunk_len, n_chunks, psx, pssx, stride);
+		k_tstat_pipe<false><<<tgrid, kTsThreads, 0, s>>>(chunk_len, psx, pssx, stride, t1, t2, p.w1, p.w2, rcp1, rcp2);
+	}
+	k_fsm_pipe<<<lane_ctas, 32, 0, s>>>(chunk_len, n_chunks, t1, t2, stride, p, peaks, pstride, n_ev);
+	if (after_detect) cudaEventRecord(after_detect, s);
+	cudaError_t e = launch_exclusive_scan_u32_chained(n_ev, ev_off, n_chunks, chained, s);
+	if (e != cudaSuccess) return e;
+	const unsigned fblocks = (unsigned)(((uint64_t)n_chunks * 32 + 127) / 128);
+	if (contract) k_finish_pipe<true><<<fblocks, 128, 0, s>>>(chunk_len, n_chunks, psx, stride, peaks, pstride, n_ev, ev_off, ev_out, ev_cap, raw, ev_pos);
+	else k_finish_pipe<false><<<fblocks, 128, 0, s>>>(chunk_len, n_chunks, psx, stride, peaks, pstride, n_ev, ev_off, ev_out, ev_cap, raw, ev_pos);
+	return cudaGetLastError();
+}
+
+} // namespace ra

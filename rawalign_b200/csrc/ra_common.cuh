@@ -39,6 +39,15 @@ cudaError_t launch_events_fused(const float *sig, const uint64_t *chunk_off, con
                                 uint64_t *ev_off, int chained, float *ev_out, uint64_t ev_cap, uint32_t *ev_pos, int n_sm,
                                 cudaStream_t s, cudaEvent_t after_detect);
 constexpr int kEventKernels = 5;
+// ---- launchers (events_pipe.cu): K1 v4, the default -- lane-per-chunk cp.async pipelines + parallel t-stat ------
+constexpr uint32_t kPipeMaxWindow = 14;
+constexpr int kPipeEventKernels = 5;
+bool events_pipe_supported(uint32_t w1, uint32_t w2);
+void events_pipe_layout(uint32_t max_len, const EvParams &p, uint32_t *stride, uint32_t *peak_stride, size_t *floats_per_chunk);
+cudaError_t launch_events_pipe(const float *sig, const uint64_t *chunk_off, const uint32_t *chunk_len, uint32_t n_chunks,
+                               uint32_t max_len, const EvParams &p, int contract, float *scratch, uint32_t *n_ev,
+                               uint64_t *ev_off, int chained, float *ev_out, uint64_t ev_cap, uint32_t *ev_pos, cudaStream_t s,
+                               cudaEvent_t after_detect);
 
 // ---- launchers (dtw.cu) ------------------------------------------------------------------------
 struct DtwLaunch {

@@ -21,7 +21,7 @@ def test_extension_is_loaded(ctx):
 
 
 # ---- K1 ---------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("unfused", [0, 1])
+@pytest.mark.parametrize("unfused", [0, 1, 2])   # K1 variant: 0 = v4 pipeline (default), 1 = v2 five kernels, 2 = v3 fused
 @pytest.mark.parametrize("contract,key", [(1, "ev_fma"), (0, "ev_nofma")])
 def test_events_golden(ctx, event_golden, contract, key, unfused):
     import rawalign_b200 as ra
