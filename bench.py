@@ -215,7 +215,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--reads-per-gpu", type=int, default=int(os.environ.get("RA_BENCH_READS", 1024)))
+    ap.add_argument("--reads-per-gpu", type=int, default=int(os.environ.get("RA_BENCH_READS", 4096)))
     ap.add_argument("--cpu-sample-reads", type=int, default=32)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -223,7 +223,8 @@ def main():
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = max(args.warmup, 3)
     config = {"workload": "C2: 5 Mb synthetic reference, simulated R9.4 reads, sparse border, banded=0.1",
-              "reads_per_gpu": args.reads_per_gpu, "max_chunks_per_read": MAX_CHUNKS, "chains_per_round": CHAINS_PER_ROUND,
+              "reads_per_gpu": args.reads_per_gpu, "batch_note": "one batch ~ the reference's default mini-batch (-K 500M of signal, roptions.c:34)",
+              "max_chunks_per_read": MAX_CHUNKS, "chains_per_round": CHAINS_PER_ROUND,
               "l2_policy": "inputs larger than L2 (signal batch >> 126 MB)"}
 
     if args.impl == "reference":
@@ -284,16 +285,18 @@ def main():
     log(f"[rank {rank}] setup {time.time() - t_setup:.1f}s: reads={args.reads_per_gpu} chunks={n_chunks} samples={n_samples} "
         f"events={n_events} chains={len(chains)} groups={n_groups} sub-DTWs={n_parts} cells issued={cells_issued} useful={cells_useful}")
 
-    ev_host = torch.empty(ev_cap, dtype=torch.float32).pin_memory().numpy(); evoff_host = np.empty(n_chunks + 1, np.uint64)
-    sig_h = sig_pinned.numpy()
+    ev_host = torch.empty(ev_cap, dtype=torch.float32).pin_memory().numpy()
+    raw_h = torch.from_numpy(reads.raw).pin_memory().numpy()
+    raw_off = np.ascontiguousarray(reads.read_off[:-1]); raw_len = reads.read_len
     e2e_out = {}
 
     def step_e2e():
-        # host signal -> device, K1, events back to the host (the map loop seeds from them), anchors/chains -> device,
-        # chain evaluation against the events that stayed on the device, scores back
-        ev, off = ctx.detect_events_batch(sig_h, coff, clen, ev_host, evoff_host)
+        # int16 DAC samples (what a FAST5 holds) -> device in slices that overlap the kernels, decode + K1, events back to the
+        # host (the map loop seeds from them), anchors/chains -> device, chain evaluation against the events that stayed on the
+        # device, scores back
+        ev, off, lsig, first = ctx.detect_events_raw_batch(raw_h, raw_off, raw_len, reads.dac_offset, reads.dac_scale, 4000, MAX_CHUNKS, ev_host)
         s, keep, _, _ = ctx.align_chains_batch(None, None, anchors_h, chains_h, min_score_mode=1, count_cells=False)
-        e2e_out["score"] = s; e2e_out["n_ev"] = len(ev)
+        e2e_out["score"] = s; e2e_out["n_ev"] = len(ev); e2e_out["ev"] = ev
 
     def barrier():
         torch.cuda.synchronize()
@@ -356,11 +359,13 @@ def main():
             "stages_ms": {"events_all_kernels": k1_ms, "events_detect_kernel": float(np.median(det_ms)), "chain_dtw_kernels": k2_ms,
                           "timing": "CUDA events on the library stream, median over the timed steps"},
             "e2e": {"value": reads_all * args.steps / dt_e2e, "unit": "reads/s", "ms_per_step": dt_e2e / args.steps * 1e3,
-                    "h2d_bytes_per_step": int(reads.sig.nbytes + coff.nbytes + clen.nbytes + anchors.nbytes + chains.nbytes + gfirst.nbytes),
-                    "d2h_bytes_per_step": int(4 * n_events + 8 * (n_chunks + 1) + 5 * len(chains))},
+                    "h2d_bytes_per_step": int(reads.raw.nbytes + 20 * args.reads_per_gpu + coff.nbytes + clen.nbytes + anchors.nbytes + chains.nbytes + gfirst.nbytes),
+                    "d2h_bytes_per_step": int(4 * n_events + 8 * (n_chunks + 1) + 4 * args.reads_per_gpu + 5 * len(chains)),
+                    "input": "int16 DAC samples, decoded on the device (ra_detect_events_raw_batch); copies sliced to overlap the kernels",
+                    "events_equal_resident_path": bool(e2e_out["n_ev"] == n_events and np.array_equal(e2e_out["ev"][:4096], ev_d[:4096].cpu().numpy()))},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"kernel": "K1 event detection (k_events_fused + k_exclusive_scan_u32 + k_ev_normalise)", "bound": "hbm",
+            "roofline": {"kernel": "K1 event detection (k_prefix_pipe + k_tstat_pipe + k_fsm_pipe + k_exclusive_scan_u32 + k_finish_pipe)", "bound": "hbm",
                          "achieved": k1_bytes / (k1_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                          "frac": k1_bytes / (k1_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None, "peak_source": peak_src,
                          "algorithmic_bytes": "4 B/sample in + 4 B/event out + 20 B/chunk of tables"},
@@ -399,7 +404,7 @@ def parity_check(ch_sub, anchors, ev_d, n_events, ref_arena, score_d, chains):
         if grp != ch["group"]:
             best, grp = 0.0, ch["group"]
         a = anchors[int(ch["anchor_off"]):int(ch["anchor_off"]) + int(ch["n_anchors"])]
-        s = orc.align_chain(a, ev[int(ch["read_off"]):], ref_arena, oo, min_score=best, score_fma=1)
+        s = orc.align_chain(a, ev[int(ch["read_off"]):], ref_arena[int(ch["ref_off"]):], oo, min_score=best, score_fma=1)
         if np.float32(s).view(np.uint32) != score[k].view(np.uint32):
             return False
         if s >= 20.0 and s > best:

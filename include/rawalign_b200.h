@@ -146,6 +146,19 @@ int ra_detect_events_batch_dev(ra_ctx *ctx, const float *sig_dev,
                                float *ev_out_dev, uint64_t ev_cap, uint64_t *ev_off_dev,
                                uint64_t *total_events);
 
+/* Raw-signal form: the conversion loop of ri_read_sig (src/rsig.cpp:213-222) and the chunk loop of
+ * map_worker_for (src/rmap.cpp:684-689) moved to the device, so that the DAC samples cross the bus as int16.
+ * Read r is raw[raw_off[r] .. raw_off[r]+raw_len[r]) (reads in order, not overlapping; 16-byte aligned starts are fastest);
+ * offset[r] and scale[r] = range/digitisation are the float fields of ri_sig_t (rsig.h:16, rsig.cpp:215).
+ * pA = ((float)raw + offset) * scale is kept iff 30 < pA < 200 (rsig.cpp:219-220); l_sig[r] receives the number of kept
+ * samples (ri_sig_t::l_sig); the kept signal is cut into chunks of chunk_size samples, at most max_chunks per read.
+ * chunk_first has n_reads+1 entries: chunks of read r are [chunk_first[r], chunk_first[r+1]); events come back in the same CSR
+ * form as ra_detect_events_batch over those chunks (ev_off needs chunk_first[n_reads]+1 entries; sum over reads of
+ * min(max_chunks, ceil(raw_len/chunk_size)) + 1 is always enough).  Copies are sliced and overlap the kernels. */
+int ra_detect_events_raw_batch(ra_ctx *ctx, const int16_t *raw, uint64_t n_raw, const uint64_t *raw_off, const uint32_t *raw_len,
+                               const float *offset, const float *scale, uint32_t n_reads, uint32_t chunk_size, uint32_t max_chunks,
+                               uint32_t *l_sig, uint32_t *chunk_first, float *ev_out, uint64_t ev_cap, uint64_t *ev_off);
+
 /* Extension (not in the reference's interface): the first sample, relative to its chunk, of every event
  * of the most recent event-detection call, in the same CSR order as ev_out.  Used by the synthetic
  * workload generator to place ground-truth anchors; the map loop does not need it. */

@@ -90,6 +90,8 @@ class Oracle:
         L.ora_align_chain.argtypes = [C.c_void_p, C.c_uint32, _f32p, _f32p, C.POINTER(DtwOpt), C.c_float, C.c_int, C.POINTER(C.c_uint64)]
         L.ora_dtw_batch.restype = None
         L.ora_dtw_batch.argtypes = [_f32p, _f32p, C.c_void_p, C.c_uint32, _f32p]
+        L.ora_decode_raw.argtypes = [C.c_void_p, C.c_uint32, C.c_float, C.c_float, _f32p]
+        L.ora_decode_raw.restype = C.c_uint32
 
     def detect_events(self, sig, opt: EvOpt | None = None, contract: int = 1, return_peaks: bool = False):
         sig = _f32(sig)
@@ -112,6 +114,13 @@ class Oracle:
         off = np.empty(len(chunk_off) + 1, np.uint64)
         self.lib.ora_detect_events_batch(sig, chunk_off, chunk_len, len(chunk_off), C.byref(opt), contract, ev, off)
         return ev[:int(off[-1])].copy(), off
+
+    def decode_raw(self, raw, offset: float, scale: float) -> np.ndarray:
+        """ri_read_sig's conversion + (30,200) filter for one read (rsig.cpp:213-222)."""
+        raw = np.ascontiguousarray(raw, np.int16)
+        out = np.empty(len(raw) + 1, np.float32)
+        n = self.lib.ora_decode_raw(raw.ctypes.data, len(raw), float(offset), float(scale), out)
+        return out[:n].copy()
 
     def dtw_global(self, a, b, exclude_last=False):
         a, b = _f32(a), _f32(b)

@@ -477,3 +477,24 @@ uint64_t ora_check_fastdiv(uint32_t w)
 		}
 	return bad;
 }
+
+/* ==============================================================================================
+ * Raw-signal decode: the conversion loop of ri_read_sig, src/rsig.cpp:213-222.
+ *   float scale = s->ran/s->dig;                                         :215 (the caller passes it)
+ *   float original_sig = (discretized_sig[i] + s->offset) * scale;      :217  two fp32 roundings
+ *   if (original_sig > 30 && original_sig < 200) keep                    :218
+ * discretized_sig is the int16 Signal dataset read into floats (exact).  Returns l_sig.
+ * Parity note: ri_read_sig itself needs the HDF5 reader, which is not built here, so this restatement
+ * is not pinned against a compiled reference object (stated in DESIGN.md).
+ * ============================================================================================== */
+uint32_t ora_decode_raw(const int16_t *raw, uint32_t n, float offset, float scale, float *out)
+{
+	uint32_t l_sig = 0;
+	for (uint32_t i = 0; i < n; ++i) {
+		const float d = (float)raw[i];
+		const float t = d + offset;
+		const float pa = t * scale;
+		if (pa > 30 && pa < 200) out[l_sig++] = pa;
+	}
+	return l_sig;
+}

@@ -30,6 +30,7 @@ void ora_evaluate_chains(const ora_anchor_t *anchors, const uint64_t *anchor_off
                          int score_fma, float *alignment_score, uint8_t *keep, uint64_t *cells_out);
 void ora_dtw_batch(const float *a_arena, const float *b_arena, const ora_item_t *items, uint32_t n_items, float *cost);
 uint64_t ora_check_fastdiv(uint32_t w);
+uint32_t ora_decode_raw(const int16_t *raw, uint32_t n, float offset, float scale, float *out);
 
 #ifdef __cplusplus
 }

@@ -62,6 +62,7 @@ def load() -> C.CDLL:
     L.ra_ref_alloc.argtypes = [vp, u64]
     L.ra_detect_events_batch.argtypes = [vp, vp, u64, vp, vp, u32, vp, u64, vp]
     L.ra_detect_events_batch_dev.argtypes = [vp, vp, vp, vp, u32, u32, vp, u64, vp, C.POINTER(u64)]
+    L.ra_detect_events_raw_batch.argtypes = [vp, vp, u64, vp, vp, vp, vp, u32, u32, u32, vp, vp, vp, u64, vp]
     L.ra_last_event_positions.argtypes = [vp, vp, u64]
     L.ra_dtw_batch.argtypes = [vp, vp, u64, vp, u64, vp, u32, vp]
     L.ra_dtw_batch_dev.argtypes = [vp, vp, vp, vp, vp, u32, vp]
@@ -71,7 +72,7 @@ def load() -> C.CDLL:
     L.ra_align_chains_batch_dev.argtypes = [vp, vp, vp, vp, u64, vp, u32, vp, u32, i32, vp, vp, vp, C.POINTER(u64), C.POINTER(u64)]
     L.ra_align_chains_cigar_batch.argtypes = [vp, vp, u64, vp, u64, vp, u64, vp, u32, vp, vp, vp, vp, vp, u64, vp]
     for name in ("ra_init", "ra_set_opt", "ra_last_timing", "ra_ref_load", "ra_ref_load_flat", "ra_ref_device", "ra_ref_alloc",
-                 "ra_detect_events_batch", "ra_detect_events_batch_dev", "ra_last_event_positions", "ra_dtw_batch", "ra_dtw_batch_dev",
+                 "ra_detect_events_batch", "ra_detect_events_batch_dev", "ra_detect_events_raw_batch", "ra_last_event_positions", "ra_dtw_batch", "ra_dtw_batch_dev",
                  "ra_dtw_tb_batch", "ra_align_chains_batch", "ra_align_chains_batch_dev", "ra_align_chains_cigar_batch"):
         getattr(L, name).restype = C.c_int
     _lib = L
@@ -86,7 +87,7 @@ def check(rc: int) -> None:
 EXPORTED_SYMBOLS = [
     "ra_init", "ra_destroy", "ra_last_error", "ra_mapopt_init", "ra_set_opt", "ra_launch_count", "ra_last_timing",
     "ra_ref_load", "ra_ref_load_flat", "ra_ref_device", "ra_ref_alloc",
-    "ra_detect_events_batch", "ra_detect_events_batch_dev", "ra_last_event_positions",
+    "ra_detect_events_batch", "ra_detect_events_batch_dev", "ra_detect_events_raw_batch", "ra_last_event_positions",
     "ra_dtw_batch", "ra_dtw_batch_dev", "ra_dtw_cells", "ra_dtw_tb_batch",
     "ra_align_chains_batch", "ra_align_chains_batch_dev", "ra_align_chains_cigar_batch",
 ]

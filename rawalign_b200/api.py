@@ -128,6 +128,26 @@ class Context:
                                              chunk_len.ctypes.data, n, ev_out.ctypes.data, ev_out.size, ev_off.ctypes.data))
         return ev_out[:int(ev_off[n])], ev_off
 
+    def detect_events_raw_batch(self, raw, raw_off, raw_len, offset, scale, chunk_size: int = 4000, max_chunks: int = 30,
+                                ev_out: Optional[np.ndarray] = None):
+        """Raw-signal form: int16 DAC samples in; ri_read_sig's conversion + (30,200) filter (rsig.cpp:213-222), the chunk
+        loop of map_worker_for (rmap.cpp:684-689) and detect_events run on the device.
+        Returns (events, ev_off, l_sig, chunk_first)."""
+        raw = np.ascontiguousarray(raw, np.int16)
+        raw_off = np.ascontiguousarray(raw_off, np.uint64); raw_len = np.ascontiguousarray(raw_len, np.uint32)
+        offset = np.ascontiguousarray(offset, np.float32); scale = np.ascontiguousarray(scale, np.float32)
+        n = len(raw_len)
+        cap_chunks = int(np.minimum(max_chunks, (raw_len.astype(np.int64) + chunk_size - 1) // chunk_size).sum())
+        if ev_out is None:
+            ev_out = np.empty(max(int(raw_len.sum()) // 2 + cap_chunks + 16, 1), np.float32)
+        ev_off = np.zeros(cap_chunks + 1, np.uint64)
+        l_sig = np.zeros(n, np.uint32); chunk_first = np.zeros(n + 1, np.uint32)
+        check(self._L.ra_detect_events_raw_batch(self._h, raw.ctypes.data, raw.size, raw_off.ctypes.data, raw_len.ctypes.data,
+                                                 offset.ctypes.data, scale.ctypes.data, n, int(chunk_size), int(max_chunks),
+                                                 l_sig.ctypes.data, chunk_first.ctypes.data, ev_out.ctypes.data, ev_out.size, ev_off.ctypes.data))
+        nch = int(chunk_first[n])
+        return ev_out[:int(ev_off[nch])], ev_off[:nch + 1], l_sig, chunk_first
+
     def detect_events(self, sig) -> np.ndarray:
         """detect_events(km, s_len, sig, opt, &n) for one chunk (revent.h:22): the event array
         (empty where the reference returns NULL)."""

@@ -6,12 +6,22 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
+#include <ctime>
 #include <new>
 #include <vector>
 
 namespace {
 
 thread_local char g_err[512] = "";
+
+// RA_TRACE=1: host wall-clock marks of the sliced entry points on stderr (debugging aid)
+struct Trace {
+	bool on; double t0;
+	static double now() { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; }
+	Trace() : on(getenv("RA_TRACE") != nullptr), t0(now()) {}
+	void mark(const char *what, int k = -1) const { if (on) fprintf(stderr, "[ra trace] %8.3f ms  %s %d\n", now() - t0, what, k); }
+};
 
 int fail(int code, const char *fmt, ...)
 {
@@ -26,6 +36,9 @@ int fail(int code, const char *fmt, ...)
 		cudaError_t e__ = (call);                                                                       \
 		if (e__ != cudaSuccess) return fail(RA_ECUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
 	} while (0)
+
+constexpr int kMaxSlices = 8;
+constexpr int kSliceStreams = 4;      // with compute, h2d, d2h and aux: 8 streams = the default number of hardware queues (no false dependencies)         // host<->device copies of the e2e entry points are cut into slices that overlap the kernels
 
 // grow-only device buffer
 struct DevBuf {
@@ -45,12 +58,34 @@ struct DevBuf {
 	template <class T> T *as() const { return reinterpret_cast<T *>(p); }
 };
 
+// grow-only pinned host buffer (staging for the small tables that cross the bus inside the sliced entry points)
+struct PinBuf {
+	void *p = nullptr;
+	size_t cap = 0;
+	int reserve(size_t bytes)
+	{
+		if (bytes <= cap) return RA_OK;
+		if (p) { cudaFreeHost(p); p = nullptr; cap = 0; }
+		size_t want = bytes + bytes / 4 + 256;
+		cudaError_t e = cudaMallocHost(&p, want);
+		if (e != cudaSuccess) { p = nullptr; cap = 0; (void)cudaGetLastError(); return fail(RA_ENOMEM, "cudaMallocHost(%zu) failed: %s", want, cudaGetErrorString(e)); }
+		cap = want;
+		return RA_OK;
+	}
+	void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+	template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
 } // namespace
 
 struct ra_ctx {
 	int device = 0;
 	int n_sm = 0;
-	cudaStream_t stream = nullptr;
+	cudaStream_t stream = nullptr;       // compute
+	cudaStream_t h2d = nullptr, d2h = nullptr, aux = nullptr;   // copy engines and the decode kernel of the sliced e2e entry points
+	cudaStream_t slice_stream[kSliceStreams] = {};                // K1 of different slices runs concurrently (each slice is latency-bound)
+	cudaEvent_t slice_in[kMaxSlices] = {}, slice_done[kMaxSlices] = {}, slice_dec[kMaxSlices] = {}, slice_scan[kMaxSlices] = {};
+	bool slices_concurrent = false;
 	ra_mapopt_t opt;
 	uint64_t launches = 0;
 	cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // K1 start / after scan / end, DTW start / end
@@ -59,6 +94,8 @@ struct ra_ctx {
 	DevBuf ref; uint64_t ref_n = 0;
 	// events
 	DevBuf sig, chunk_off, chunk_len, raw, nev, ev_off, ev_out, ev_pos;
+	DevBuf raw16, rd_off, rd_len, rd_offset, rd_scale, rd_lsig;   // raw-signal decode (decode.cu)
+	PinBuf pin_off, pin_tab, pin_lsig;
 	uint64_t last_events = 0;
 	// dtw
 	DevBuf a_arena, b_arena, items, cost, counter, ring, order;
@@ -77,14 +114,19 @@ namespace {
 
 constexpr uint32_t kEventSubBatch = 32768;   // chunks per launch group: bounds the scratch arena (~2.4 GB at 4000 samples)
 
-int events_dev(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_dev, const uint32_t *chunk_len_dev,
-               uint32_t n_chunks, uint32_t max_chunk_len, float *ev_out_dev, uint64_t ev_cap, uint64_t *ev_off_dev,
-               uint64_t *total_events)
+// Enqueues K1 for chunks [0, n_chunks) of the given tables on the compute stream; no host synchronisation.
+// chained_first != 0 continues the CSR offsets from the value already in ev_off_dev[0].
+int events_launch(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_dev, const uint32_t *chunk_len_dev,
+                  uint32_t n_chunks, uint32_t max_chunk_len, float *ev_out_dev, uint64_t ev_cap, uint64_t *ev_off_dev,
+                  int chained_first, bool record_timing)
 {
 	const ra_mapopt_t &o = ctx->opt;
 	if (!ra::events_windows_supported(o.window_length1, o.window_length2))
 		return fail(RA_EUNSUP, "event detector windows (%u,%u) are not supported", o.window_length1, o.window_length2);
-	if (n_chunks == 0) { if (total_events) *total_events = 0; uint64_t z = 0; RA_CUDA(cudaMemcpyAsync(ev_off_dev, &z, 8, cudaMemcpyHostToDevice, ctx->stream)); RA_CUDA(cudaStreamSynchronize(ctx->stream)); return RA_OK; }
+	if (n_chunks == 0) {
+		if (!chained_first) RA_CUDA(cudaMemsetAsync(ev_off_dev, 0, 8, ctx->stream));
+		return RA_OK;
+	}
 	ra::EvParams p = { o.window_length1, o.window_length2, o.threshold1, o.threshold2, o.peak_height };
 	// K1 variants: v4 pipeline (default), v3 fused single pass (reserved bit 1), v2 five kernels (reserved bit 0 or windows > 14)
 	const bool pipe = ra::events_pipe_supported(o.window_length1, o.window_length2) && !ctx->force_unfused_events && !ctx->force_fused_events;
@@ -95,38 +137,158 @@ int events_dev(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_dev,
 	if (pipe) { uint32_t stride, pstride; ra::events_pipe_layout(max_chunk_len, p, &stride, &pstride, &fpc); }
 	const uint32_t sub = std::min(n_chunks, kEventSubBatch);
 	int rc;
+	if (ctx->raw.cap < (size_t)sub * fpc * sizeof(float) || ctx->nev.cap < (size_t)sub * sizeof(uint32_t) ||
+	    ctx->ev_pos.cap < (size_t)std::max<uint64_t>(ev_cap, 1) * sizeof(uint32_t))
+		RA_CUDA(cudaStreamSynchronize(ctx->stream));             // a grow-only buffer is about to be reallocated: drain its users first
 	if ((rc = ctx->raw.reserve((size_t)sub * fpc * sizeof(float)))) return rc;
 	if ((rc = ctx->nev.reserve((size_t)sub * sizeof(uint32_t)))) return rc;
 	if ((rc = ctx->ev_pos.reserve((size_t)std::max<uint64_t>(ev_cap, 1) * sizeof(uint32_t)))) return rc;
-	RA_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
+	if (record_timing) RA_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
 	for (uint32_t s0 = 0; s0 < n_chunks; s0 += sub) {
 		const uint32_t n = std::min(sub, n_chunks - s0);
 		const bool last = (s0 + n == n_chunks);
+		const int chained = (s0 != 0 || chained_first) ? 1 : 0;
+		cudaEvent_t after = (last && record_timing) ? ctx->ev[1] : nullptr;
 		if (pipe) {
 			RA_CUDA(ra::launch_events_pipe(sig_dev, chunk_off_dev + s0, chunk_len_dev + s0, n, max_chunk_len, p, (int)o.fp_contract,
-			                               ctx->raw.as<float>(), ctx->nev.as<uint32_t>(), ev_off_dev + s0, s0 != 0, ev_out_dev, ev_cap,
-			                               ctx->want_ev_pos ? ctx->ev_pos.as<uint32_t>() : nullptr, ctx->stream, last ? ctx->ev[1] : nullptr));
+			                               ctx->raw.as<float>(), ctx->nev.as<uint32_t>(), ev_off_dev + s0, chained, ev_out_dev, ev_cap,
+			                               ctx->want_ev_pos ? ctx->ev_pos.as<uint32_t>() : nullptr, ctx->stream, after));
 			ctx->launches += ra::kPipeEventKernels;
 		} else if (fused) {
 			RA_CUDA(ra::launch_events_fused(sig_dev, chunk_off_dev + s0, chunk_len_dev + s0, n, max_chunk_len, p, (int)o.fp_contract,
-			                                ctx->raw.as<float>(), ctx->nev.as<uint32_t>(), ev_off_dev + s0, s0 != 0, ev_out_dev, ev_cap,
-			                                ctx->want_ev_pos ? ctx->ev_pos.as<uint32_t>() : nullptr, ctx->n_sm, ctx->stream, last ? ctx->ev[1] : nullptr));
+			                                ctx->raw.as<float>(), ctx->nev.as<uint32_t>(), ev_off_dev + s0, chained, ev_out_dev, ev_cap,
+			                                ctx->want_ev_pos ? ctx->ev_pos.as<uint32_t>() : nullptr, ctx->n_sm, ctx->stream, after));
 			ctx->launches += ra::kFusedEventKernels;
 		} else {
 			RA_CUDA(ra::launch_events(sig_dev, chunk_off_dev + s0, chunk_len_dev + s0, n, max_chunk_len, p, (int)o.fp_contract,
-			                          ctx->raw.as<float>(), ctx->nev.as<uint32_t>(), ev_off_dev + s0, s0 != 0, ev_out_dev, ev_cap,
-			                          ctx->ev_pos.as<uint32_t>(), ctx->stream, last ? ctx->ev[1] : nullptr));
+			                          ctx->raw.as<float>(), ctx->nev.as<uint32_t>(), ev_off_dev + s0, chained, ev_out_dev, ev_cap,
+			                          ctx->ev_pos.as<uint32_t>(), ctx->stream, after));
 			ctx->launches += ra::kEventKernels;
 		}
 	}
-	RA_CUDA(cudaEventRecord(ctx->ev[2], ctx->stream));
-	ctx->timed_k1 = true;
+	if (record_timing) { RA_CUDA(cudaEventRecord(ctx->ev[2], ctx->stream)); ctx->timed_k1 = true; }
+	return RA_OK;
+}
+
+int events_dev(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_dev, const uint32_t *chunk_len_dev,
+               uint32_t n_chunks, uint32_t max_chunk_len, float *ev_out_dev, uint64_t ev_cap, uint64_t *ev_off_dev,
+               uint64_t *total_events)
+{
+	int rc = events_launch(ctx, sig_dev, chunk_off_dev, chunk_len_dev, n_chunks, max_chunk_len, ev_out_dev, ev_cap, ev_off_dev, 0, true);
+	if (rc) return rc;
 	uint64_t tot = 0;
 	RA_CUDA(cudaMemcpyAsync(&tot, ev_off_dev + n_chunks, sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
 	RA_CUDA(cudaStreamSynchronize(ctx->stream));
 	if (total_events) *total_events = tot;
 	ctx->last_events = tot;
 	if (tot > ev_cap) return fail(RA_EINVAL, "ev_out capacity %llu < %llu events", (unsigned long long)ev_cap, (unsigned long long)tot);
+	return RA_OK;
+}
+
+// Sliced K1: slice k = chunks [c0, c0+n) runs as soon as its inputs are on the device (slice_in[k]); the CSR offsets of
+// every finished slice go to pinned staging, and slices_collect streams the events of finished slices back to the host
+// on the d2h stream while later slices still compute.
+int slice_launch_concurrent(ra_ctx *ctx, const float *sig_dev, int k, uint32_t c0, uint32_t n, uint32_t max_len, uint64_t dev_cap);
+
+int slice_launch(ra_ctx *ctx, const float *sig_dev, int k, uint32_t c0, uint32_t n, uint32_t max_len, uint64_t dev_cap)
+{
+	int rc;
+	if (ctx->slices_concurrent) return slice_launch_concurrent(ctx, sig_dev, k, c0, n, max_len, dev_cap);
+	RA_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->slice_in[k], 0));
+	if ((rc = events_launch(ctx, sig_dev, ctx->chunk_off.as<uint64_t>() + c0, ctx->chunk_len.as<uint32_t>() + c0, n, max_len,
+	                        ctx->ev_out.as<float>(), dev_cap, ctx->ev_off.as<uint64_t>() + c0, k != 0, k == 0))) return rc;
+	uint64_t *stage = ctx->pin_off.as<uint64_t>();
+	RA_CUDA(cudaMemcpyAsync(stage + c0 + (k ? 1 : 0), ctx->ev_off.as<uint64_t>() + c0 + (k ? 1 : 0), (size_t)(n + (k ? 0 : 1)) * sizeof(uint64_t),
+	                        cudaMemcpyDeviceToHost, ctx->stream));
+	RA_CUDA(cudaEventRecord(ctx->slice_done[k], ctx->stream));
+	return RA_OK;
+}
+
+// Scratch for every chunk of the batch at once (slices then run on their own streams): worth it while it stays small.
+constexpr uint64_t kConcurrentSliceChunks = 65536;
+
+// Reserves the K1 scratch of the v4 pipeline for n_total chunks and decides whether slices can run concurrently.
+int slices_prepare(ra_ctx *ctx, uint32_t n_total, uint32_t max_len, uint64_t dev_cap)
+{
+	const ra_mapopt_t &o = ctx->opt;
+	const bool pipe = ra::events_pipe_supported(o.window_length1, o.window_length2) && !ctx->force_unfused_events && !ctx->force_fused_events;
+	ctx->slices_concurrent = pipe && n_total <= kConcurrentSliceChunks;
+	if (!ctx->slices_concurrent) return RA_OK;
+	ra::EvParams p = { o.window_length1, o.window_length2, o.threshold1, o.threshold2, o.peak_height };
+	uint32_t stride, pstride; size_t fpc;
+	ra::events_pipe_layout(max_len, p, &stride, &pstride, &fpc);
+	int rc;
+	if ((rc = ctx->raw.reserve((size_t)std::max<uint32_t>(n_total, 1) * fpc * sizeof(float)))) return rc;
+	if ((rc = ctx->nev.reserve((size_t)std::max<uint32_t>(n_total, 1) * sizeof(uint32_t)))) return rc;
+	if ((rc = ctx->ev_pos.reserve((size_t)std::max<uint64_t>(dev_cap, 1) * sizeof(uint32_t)))) return rc;
+	return RA_OK;
+}
+
+// RA_TRACE: device-side timestamps of slice k (start of K1, end of finish kernel, end of the offsets copy)
+cudaEvent_t g_tr_ev[kMaxSlices][3]; cudaEvent_t g_tr_t0 = nullptr; bool g_tr_init = false;
+void trace_events_init()
+{
+	if (g_tr_init) return;
+	cudaEventCreate(&g_tr_t0);
+	for (int k = 0; k < kMaxSlices; ++k) for (int j = 0; j < 3; ++j) cudaEventCreate(&g_tr_ev[k][j]);
+	g_tr_init = true;
+}
+
+// Slice k on its own stream: detection kernels run as soon as the slice's inputs are there; only the CSR scan waits for
+// the previous slice's scan.
+int slice_launch_concurrent(ra_ctx *ctx, const float *sig_dev, int k, uint32_t c0, uint32_t n, uint32_t max_len, uint64_t dev_cap)
+{
+	const ra_mapopt_t &o = ctx->opt;
+	cudaStream_t s = ctx->slice_stream[k % kSliceStreams];
+	RA_CUDA(cudaStreamWaitEvent(s, ctx->slice_in[k], 0));
+	const bool trace = getenv("RA_TRACE") != nullptr;
+	if (trace) { trace_events_init(); cudaEventRecord(g_tr_ev[k][0], s); }
+	if (k == 0) RA_CUDA(cudaEventRecord(ctx->ev[0], s));
+	uint64_t *ev_off_dev = ctx->ev_off.as<uint64_t>() + c0;
+	if (n) {
+		ra::EvParams p = { o.window_length1, o.window_length2, o.threshold1, o.threshold2, o.peak_height };
+		uint32_t stride, pstride; size_t fpc;
+		ra::events_pipe_layout(max_len, p, &stride, &pstride, &fpc);
+		RA_CUDA(ra::launch_events_pipe(sig_dev, ctx->chunk_off.as<uint64_t>() + c0, ctx->chunk_len.as<uint32_t>() + c0, n, max_len, p, (int)o.fp_contract,
+		                               ctx->raw.as<float>() + (size_t)c0 * fpc, ctx->nev.as<uint32_t>() + c0, ev_off_dev, k != 0, ctx->ev_out.as<float>(), dev_cap,
+		                               ctx->want_ev_pos ? ctx->ev_pos.as<uint32_t>() : nullptr, s, k == 0 ? ctx->ev[1] : nullptr,
+		                               k ? ctx->slice_scan[k - 1] : nullptr, ctx->slice_scan[k]));
+		ctx->launches += ra::kPipeEventKernels;
+	} else {
+		// empty slice: pass the running total on (ev_off_dev[0] already holds it once the previous scan is done)
+		if (k) RA_CUDA(cudaStreamWaitEvent(s, ctx->slice_scan[k - 1], 0));
+		else RA_CUDA(cudaMemsetAsync(ev_off_dev, 0, 8, s));
+		RA_CUDA(cudaEventRecord(ctx->slice_scan[k], s));
+	}
+	uint64_t *stage = ctx->pin_off.as<uint64_t>();
+	if (trace) cudaEventRecord(g_tr_ev[k][1], s);
+	RA_CUDA(cudaMemcpyAsync(stage + c0 + (k ? 1 : 0), ev_off_dev + (k ? 1 : 0), (size_t)(n + (k ? 0 : 1)) * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+	if (trace) cudaEventRecord(g_tr_ev[k][2], s);
+	RA_CUDA(cudaEventRecord(ctx->slice_done[k], s));
+	return RA_OK;
+}
+
+int slices_collect(ra_ctx *ctx, const uint32_t *cut, int n_slices, uint64_t dev_cap, float *ev_out, uint64_t ev_cap, uint64_t *ev_off,
+                   uint32_t n_chunks)
+{
+	if (ctx->slices_concurrent) {
+		for (int k = 0; k < n_slices; ++k) RA_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->slice_done[k], 0));   // later work on the compute stream sees the events
+		RA_CUDA(cudaEventRecord(ctx->ev[2], ctx->stream));
+		ctx->timed_k1 = true;
+	} else RA_CUDA(cudaEventRecord(ctx->ev[2], ctx->stream));
+	const uint64_t *stage = ctx->pin_off.as<uint64_t>();
+	Trace tr;
+	for (int k = 0; k < n_slices; ++k) {
+		RA_CUDA(cudaEventSynchronize(ctx->slice_done[k]));
+		tr.mark("  slice done", k);
+		const uint64_t e0 = stage[cut[k]], e1 = stage[cut[k + 1]];
+		if (e1 > dev_cap || e1 > ev_cap) { cudaStreamSynchronize(ctx->stream); return fail(RA_EINVAL, "ev_out capacity %llu < %llu events", (unsigned long long)std::min(dev_cap, ev_cap), (unsigned long long)e1); }
+		if (e1 > e0) RA_CUDA(cudaMemcpyAsync(ev_out + e0, ctx->ev_out.as<float>() + e0, (size_t)(e1 - e0) * sizeof(float), cudaMemcpyDeviceToHost, ctx->d2h));
+	}
+	memcpy(ev_off, stage, (size_t)(n_chunks + 1) * sizeof(uint64_t));
+	RA_CUDA(cudaStreamSynchronize(ctx->d2h));
+	RA_CUDA(cudaStreamSynchronize(ctx->stream));
+	ctx->last_events = ctx->resident_events = stage[n_chunks];
 	return RA_OK;
 }
 
@@ -303,6 +465,18 @@ int ra_init(int device, ra_ctx **out)
 		e = cudaEventCreate(&ctx->ev[k]);
 		if (e != cudaSuccess) { delete ctx; return fail(RA_ECUDA, "cudaEventCreate: %s", cudaGetErrorString(e)); }
 	}
+	cudaStream_t *extra[3] = { &ctx->h2d, &ctx->d2h, &ctx->aux };
+	for (cudaStream_t *s : extra) {
+		e = cudaStreamCreateWithFlags(s, cudaStreamNonBlocking);
+		if (e != cudaSuccess) { delete ctx; return fail(RA_ECUDA, "cudaStreamCreate: %s", cudaGetErrorString(e)); }
+	}
+	for (int k = 0; k < kMaxSlices; ++k) {
+		if ((e = cudaEventCreateWithFlags(&ctx->slice_in[k], cudaEventDisableTiming)) != cudaSuccess ||
+		    (e = cudaEventCreateWithFlags(&ctx->slice_done[k], cudaEventDisableTiming)) != cudaSuccess ||
+		    (e = cudaEventCreateWithFlags(&ctx->slice_dec[k], cudaEventDisableTiming)) != cudaSuccess ||
+		    (e = cudaEventCreateWithFlags(&ctx->slice_scan[k], cudaEventDisableTiming)) != cudaSuccess ||
+		    (k < kSliceStreams && (e = cudaStreamCreateWithFlags(&ctx->slice_stream[k], cudaStreamNonBlocking)) != cudaSuccess)) { delete ctx; return fail(RA_ECUDA, "cudaEventCreate: %s", cudaGetErrorString(e)); }
+	}
 	*out = ctx;
 	return RA_OK;
 }
@@ -318,6 +492,19 @@ void ra_destroy(ra_ctx *ctx)
 	                   &ctx->path_off, &ctx->out_i, &ctx->out_j, &ctx->out_d };
 	for (DevBuf *b : bufs) b->release();
 	for (int k = 0; k < 5; ++k) if (ctx->ev[k]) cudaEventDestroy(ctx->ev[k]);
+	for (int k = 0; k < kMaxSlices; ++k) {
+		if (ctx->slice_in[k]) cudaEventDestroy(ctx->slice_in[k]);
+		if (ctx->slice_done[k]) cudaEventDestroy(ctx->slice_done[k]);
+		if (ctx->slice_dec[k]) cudaEventDestroy(ctx->slice_dec[k]);
+		if (ctx->slice_scan[k]) cudaEventDestroy(ctx->slice_scan[k]);
+		if (k < kSliceStreams && ctx->slice_stream[k]) cudaStreamDestroy(ctx->slice_stream[k]);
+	}
+	DevBuf *dec[] = { &ctx->raw16, &ctx->rd_off, &ctx->rd_len, &ctx->rd_offset, &ctx->rd_scale, &ctx->rd_lsig };
+	for (DevBuf *b : dec) b->release();
+	ctx->pin_off.release(); ctx->pin_tab.release(); ctx->pin_lsig.release();
+	if (ctx->h2d) cudaStreamDestroy(ctx->h2d);
+	if (ctx->d2h) cudaStreamDestroy(ctx->d2h);
+	if (ctx->aux) cudaStreamDestroy(ctx->aux);
 	cudaStreamDestroy(ctx->stream);
 	delete ctx;
 }
@@ -416,6 +603,7 @@ int ra_detect_events_batch(ra_ctx *ctx, const float *sig, uint64_t n_sig, const 
 		if (chunk_off[c] + chunk_len[c] > n_sig) return fail(RA_EINVAL, "chunk %u exceeds the signal array", c);
 		max_len = std::max(max_len, chunk_len[c]); sum_len += chunk_len[c];
 	}
+	RA_CUDA(cudaStreamSynchronize(ctx->stream));                   // the staging buffers below may be reallocated
 	int rc;
 	if ((rc = ctx->sig.reserve((size_t)std::max<uint64_t>(n_sig, 4) * sizeof(float)))) return rc;
 	if ((rc = ctx->chunk_off.reserve((size_t)(n_chunks + 1) * sizeof(uint64_t)))) return rc;
@@ -423,20 +611,145 @@ int ra_detect_events_batch(ra_ctx *ctx, const float *sig, uint64_t n_sig, const 
 	if ((rc = ctx->ev_off.reserve((size_t)(n_chunks + 1) * sizeof(uint64_t)))) return rc;
 	const uint64_t dev_cap = std::min<uint64_t>(ev_cap, sum_len / 2 + n_chunks + 16);   // peaks are >= 3 samples apart per detector: < 0.54 events per sample
 	if ((rc = ctx->ev_out.reserve((size_t)std::max<uint64_t>(dev_cap, 1) * sizeof(float)))) return rc;
-	if (n_chunks) {
-		RA_CUDA(cudaMemcpyAsync(ctx->sig.p, sig, (size_t)n_sig * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-		RA_CUDA(cudaMemcpyAsync(ctx->chunk_off.p, chunk_off, (size_t)n_chunks * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
-		RA_CUDA(cudaMemcpyAsync(ctx->chunk_len.p, chunk_len, (size_t)n_chunks * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+	if (n_chunks == 0) { ev_off[0] = 0; ctx->last_events = ctx->resident_events = 0; return RA_OK; }
+	// Slices of chunks; slice k may start once sig[0 .. need[k]) is on the device (need = running max of chunk ends).
+	const int n_slices = (int)std::min<uint64_t>(kMaxSlices, std::max<uint64_t>(1, sum_len / (8u << 20)));   // >= 32 MB of signal per slice
+	uint32_t cut[kMaxSlices + 1]; uint64_t need[kMaxSlices + 1];
+	cut[0] = 0; need[0] = 0;
+	{
+		uint64_t run_max = 0; uint32_t c = 0;
+		for (int k = 1; k <= n_slices; ++k) {
+			const uint32_t end = (uint32_t)((uint64_t)n_chunks * k / n_slices);
+			for (; c < end; ++c) run_max = std::max<uint64_t>(run_max, chunk_off[c] + chunk_len[c]);
+			cut[k] = end; need[k] = (k == n_slices) ? std::max(run_max, need[k - 1]) : run_max;
+		}
 	}
-	uint64_t total = 0;
-	rc = events_dev(ctx, ctx->sig.as<float>(), ctx->chunk_off.as<uint64_t>(), ctx->chunk_len.as<uint32_t>(), n_chunks, max_len,
-	                ctx->ev_out.as<float>(), dev_cap, ctx->ev_off.as<uint64_t>(), &total);
-	if (rc) return rc;
-	ctx->resident_events = total;
-	RA_CUDA(cudaMemcpyAsync(ev_off, ctx->ev_off.p, (size_t)(n_chunks + 1) * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
-	if (total) RA_CUDA(cudaMemcpyAsync(ev_out, ctx->ev_out.p, (size_t)total * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+	RA_CUDA(cudaMemcpyAsync(ctx->chunk_off.p, chunk_off, (size_t)n_chunks * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->h2d));
+	RA_CUDA(cudaMemcpyAsync(ctx->chunk_len.p, chunk_len, (size_t)n_chunks * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->h2d));
+	for (int k = 0; k < n_slices; ++k) {
+		if (need[k + 1] > need[k])
+			RA_CUDA(cudaMemcpyAsync(ctx->sig.as<float>() + need[k], sig + need[k], (size_t)(need[k + 1] - need[k]) * sizeof(float), cudaMemcpyHostToDevice, ctx->h2d));
+		RA_CUDA(cudaEventRecord(ctx->slice_in[k], ctx->h2d));
+	}
+	if ((rc = ctx->pin_off.reserve((size_t)(n_chunks + 1) * sizeof(uint64_t)))) return rc;
+	if ((rc = slices_prepare(ctx, n_chunks, max_len, dev_cap))) return rc;
+	for (int k = 0; k < n_slices; ++k)
+		if ((rc = slice_launch(ctx, ctx->sig.as<float>(), k, cut[k], cut[k + 1] - cut[k], max_len, dev_cap))) return rc;
+	return slices_collect(ctx, cut, n_slices, dev_cap, ev_out, ev_cap, ev_off, n_chunks);
+}
+
+/* Raw-signal form: int16 DAC samples in, decoded and filtered on the device exactly as
+ * ri_read_sig does (rsig.cpp:213-222), cut into chunks as map_worker_for does (rmap.cpp:684-689). */
+int ra_detect_events_raw_batch(ra_ctx *ctx, const int16_t *raw, uint64_t n_raw, const uint64_t *raw_off, const uint32_t *raw_len,
+                               const float *offset, const float *scale, uint32_t n_reads, uint32_t chunk_size, uint32_t max_chunks,
+                               uint32_t *l_sig, uint32_t *chunk_first, float *ev_out, uint64_t ev_cap, uint64_t *ev_off)
+{
+	if (!ctx || !ev_off || !chunk_first || !l_sig || (n_reads && (!raw || !raw_off || !raw_len || !offset || !scale || !ev_out))) return fail(RA_EINVAL, "NULL argument");
+	if (chunk_size == 0 || max_chunks == 0) return fail(RA_EINVAL, "chunk_size and max_chunks must be positive");
+	RA_CUDA(cudaSetDevice(ctx->device));
+	uint64_t max_chunks_total = 0, max_samples = 0;
+	for (uint32_t r = 0; r < n_reads; ++r) {
+		if (raw_off[r] + raw_len[r] > n_raw) return fail(RA_EINVAL, "read %u exceeds the raw array", r);
+		if (r && raw_off[r] < raw_off[r - 1] + raw_len[r - 1]) return fail(RA_EINVAL, "reads must be laid out in order without overlap (read %u)", r);
+		const uint64_t nch = std::min<uint64_t>(max_chunks, ((uint64_t)raw_len[r] + chunk_size - 1) / chunk_size);
+		max_chunks_total += nch; max_samples += std::min<uint64_t>(raw_len[r], nch * chunk_size);
+	}
+	if (max_chunks_total >= 0xffffffffull) return fail(RA_EINVAL, "too many chunks in one batch");
 	RA_CUDA(cudaStreamSynchronize(ctx->stream));
-	return RA_OK;
+	int rc;
+	if ((rc = ctx->raw16.reserve((size_t)std::max<uint64_t>(n_raw, 8) * sizeof(int16_t) + 16))) return rc;
+	if ((rc = ctx->sig.reserve((size_t)std::max<uint64_t>(n_raw, 4) * sizeof(float)))) return rc;
+	if ((rc = ctx->rd_off.reserve((size_t)(n_reads + 1) * 8))) return rc;
+	if ((rc = ctx->rd_len.reserve((size_t)(n_reads + 1) * 4))) return rc;
+	if ((rc = ctx->rd_offset.reserve((size_t)(n_reads + 1) * 4))) return rc;
+	if ((rc = ctx->rd_scale.reserve((size_t)(n_reads + 1) * 4))) return rc;
+	if ((rc = ctx->rd_lsig.reserve((size_t)(n_reads + 1) * 4))) return rc;
+	if ((rc = ctx->chunk_off.reserve((size_t)(max_chunks_total + 1) * sizeof(uint64_t)))) return rc;
+	if ((rc = ctx->chunk_len.reserve((size_t)(max_chunks_total + 1) * sizeof(uint32_t)))) return rc;
+	if ((rc = ctx->ev_off.reserve((size_t)(max_chunks_total + 1) * sizeof(uint64_t)))) return rc;
+	const uint64_t dev_cap = std::min<uint64_t>(ev_cap, max_samples / 2 + max_chunks_total + 16);
+	if ((rc = ctx->ev_out.reserve((size_t)std::max<uint64_t>(dev_cap, 1) * sizeof(float)))) return rc;
+	if ((rc = ctx->pin_lsig.reserve((size_t)(n_reads + 1) * 4))) return rc;
+	chunk_first[0] = 0;
+	if (n_reads == 0) { ev_off[0] = 0; ctx->last_events = ctx->resident_events = 0; return RA_OK; }
+	// read slices of roughly equal raw size
+	const int n_slices = (int)std::min<uint64_t>(kMaxSlices, std::max<uint64_t>(1, n_raw / (16u << 20)));     // >= 32 MB of int16 per slice
+	uint32_t rcut[kMaxSlices + 1]; rcut[0] = 0;
+	{
+		uint32_t r = 0;
+		for (int k = 1; k <= n_slices; ++k) {
+			const uint64_t target = (k == n_slices) ? n_raw : n_raw * k / n_slices;
+			while (r < n_reads && raw_off[r] + raw_len[r] <= target) ++r;
+			if (k == n_slices) r = n_reads;
+			rcut[k] = r;
+		}
+	}
+	Trace tr; tr.mark("start");
+	if (tr.on) { trace_events_init(); cudaEventRecord(g_tr_t0, ctx->h2d); }
+	RA_CUDA(cudaMemcpyAsync(ctx->rd_off.p, raw_off, (size_t)n_reads * 8, cudaMemcpyHostToDevice, ctx->h2d));
+	RA_CUDA(cudaMemcpyAsync(ctx->rd_len.p, raw_len, (size_t)n_reads * 4, cudaMemcpyHostToDevice, ctx->h2d));
+	RA_CUDA(cudaMemcpyAsync(ctx->rd_offset.p, offset, (size_t)n_reads * 4, cudaMemcpyHostToDevice, ctx->h2d));
+	RA_CUDA(cudaMemcpyAsync(ctx->rd_scale.p, scale, (size_t)n_reads * 4, cudaMemcpyHostToDevice, ctx->h2d));
+	for (int k = 0; k < n_slices; ++k) {
+		if (rcut[k + 1] > rcut[k]) {
+			const uint64_t b0 = raw_off[rcut[k]], b1 = raw_off[rcut[k + 1] - 1] + raw_len[rcut[k + 1] - 1];
+			RA_CUDA(cudaMemcpyAsync(ctx->raw16.as<int16_t>() + b0, raw + b0, (size_t)(b1 - b0) * sizeof(int16_t), cudaMemcpyHostToDevice, ctx->h2d));
+		}
+		RA_CUDA(cudaEventRecord(ctx->slice_in[k], ctx->h2d));
+	}
+	// decode every slice on the aux stream as it arrives; l_sig comes back per slice (the host cuts the chunks)
+	for (int k = 0; k < n_slices; ++k) {
+		const uint32_t r0 = rcut[k], nr = rcut[k + 1] - r0;
+		RA_CUDA(cudaStreamWaitEvent(ctx->aux, ctx->slice_in[k], 0));
+		RA_CUDA(ra::launch_decode_raw(ctx->raw16.as<int16_t>(), ctx->rd_off.as<uint64_t>() + r0, ctx->rd_len.as<uint32_t>() + r0, ctx->rd_offset.as<float>() + r0,
+		                              ctx->rd_scale.as<float>() + r0, nr, ctx->sig.as<float>(), ctx->rd_lsig.as<uint32_t>() + r0, ctx->aux));
+		if (nr) { ctx->launches += 1; RA_CUDA(cudaMemcpyAsync(ctx->pin_lsig.as<uint32_t>() + r0, ctx->rd_lsig.as<uint32_t>() + r0, (size_t)nr * 4, cudaMemcpyDeviceToHost, ctx->aux)); }
+		RA_CUDA(cudaEventRecord(ctx->slice_dec[k], ctx->aux));
+	}
+	if ((rc = ctx->pin_off.reserve((size_t)(max_chunks_total + 1) * sizeof(uint64_t)))) return rc;
+	if ((rc = ctx->pin_tab.reserve((size_t)(max_chunks_total + 1) * 12))) return rc;
+	if ((rc = slices_prepare(ctx, (uint32_t)max_chunks_total, chunk_size, dev_cap))) return rc;
+	uint64_t *coff = ctx->pin_tab.as<uint64_t>();                               // pinned, so the table uploads are asynchronous
+	uint32_t *clen = reinterpret_cast<uint32_t *>(coff + max_chunks_total + 1);
+	uint32_t cut[kMaxSlices + 1]; cut[0] = 0;
+	uint32_t n_chunks = 0;
+	const uint32_t *lsig_stage = ctx->pin_lsig.as<uint32_t>();
+	for (int k = 0; k < n_slices; ++k) {
+		RA_CUDA(cudaEventSynchronize(ctx->slice_dec[k]));
+		tr.mark("decoded", k);
+		const uint32_t c_begin = n_chunks;
+		for (uint32_t r = rcut[k]; r < rcut[k + 1]; ++r) {
+			const uint32_t qlen = lsig_stage[r];
+			l_sig[r] = qlen;
+			uint32_t cs = 0, cc = 0;
+			for (; cs < qlen && cc < max_chunks; cs += chunk_size, ++cc) {       // rmap.cpp:684-689
+				coff[n_chunks] = raw_off[r] + cs; clen[n_chunks] = std::min(chunk_size, qlen - cs); ++n_chunks;
+			}
+			chunk_first[r + 1] = n_chunks;
+		}
+		const uint32_t n = n_chunks - c_begin;
+		cut[k + 1] = n_chunks;
+		// the table goes up on the stream that runs this slice's K1 (the aux stream still holds the decodes of later slices,
+		// which wait for their copies: anything queued behind them would start late)
+		cudaStream_t ks = ctx->slices_concurrent ? ctx->slice_stream[k % kSliceStreams] : ctx->stream;
+		if (n) {
+			RA_CUDA(ra::launch_fetch_tables(coff + c_begin, clen + c_begin, ctx->chunk_off.as<uint64_t>() + c_begin, ctx->chunk_len.as<uint32_t>() + c_begin, n, ks));
+			ctx->launches += 1;
+		}
+		RA_CUDA(cudaEventRecord(ctx->slice_in[k], ks));                         // slice k is ready for K1: signal decoded (host saw slice_dec[k]), table on the device
+		if ((rc = slice_launch(ctx, ctx->sig.as<float>(), k, c_begin, n, chunk_size, dev_cap))) return rc;
+	}
+	tr.mark("all launched");
+	rc = slices_collect(ctx, cut, n_slices, dev_cap, ev_out, ev_cap, ev_off, n_chunks);
+	RA_CUDA(cudaStreamSynchronize(ctx->aux));
+	tr.mark("collected");
+	if (tr.on && ctx->slices_concurrent)
+		for (int k = 0; k < n_slices; ++k) {
+			float a0 = 0, a1 = 0, a2 = 0;
+			cudaEventElapsedTime(&a0, g_tr_t0, g_tr_ev[k][0]); cudaEventElapsedTime(&a1, g_tr_t0, g_tr_ev[k][1]); cudaEventElapsedTime(&a2, g_tr_t0, g_tr_ev[k][2]);
+			fprintf(stderr, "[ra trace] device: slice %d K1 start %.3f  K1 end %.3f  offsets copied %.3f ms\n", k, a0, a1, a2);
+		}
+	return rc;
 }
 
 int ra_last_event_positions(ra_ctx *ctx, uint32_t *pos_out, uint64_t cap)

@@ -454,7 +454,7 @@ void events_pipe_layout(uint32_t max_len, const EvParams &p, uint32_t *stride, u
 cudaError_t launch_events_pipe(const float *sig, const uint64_t *chunk_off, const uint32_t *chunk_len, uint32_t n_chunks,
                                uint32_t max_len, const EvParams &p, int contract, float *scratch, uint32_t *n_ev,
                                uint64_t *ev_off, int chained, float *ev_out, uint64_t ev_cap, uint32_t *ev_pos, cudaStream_t s,
-                               cudaEvent_t after_detect)
+                               cudaEvent_t after_detect, cudaEvent_t scan_wait, cudaEvent_t scan_done)
 {
 	using namespace evp;
 	if (n_chunks == 0) return cudaSuccess;
@@ -478,8 +478,11 @@ cudaError_t launch_events_pipe(const float *sig, const uint64_t *chunk_off, cons
 	}
 	k_fsm_pipe<<<lane_ctas, 32, 0, s>>>(chunk_len, n_chunks, t1, t2, stride, p, peaks, pstride, n_ev);
 	if (after_detect) cudaEventRecord(after_detect, s);
+	// CSR offsets continue from the previous launch group: when that group runs on another stream, only the scan waits for it
+	if (scan_wait) cudaStreamWaitEvent(s, scan_wait, 0);
 	cudaError_t e = launch_exclusive_scan_u32_chained(n_ev, ev_off, n_chunks, chained, s);
 	if (e != cudaSuccess) return e;
+	if (scan_done) cudaEventRecord(scan_done, s);
 	const unsigned fblocks = (unsigned)(((uint64_t)n_chunks * 32 + 127) / 128);
 	if (contract) k_finish_pipe<true><<<fblocks, 128, 0, s>>>(chunk_len, n_chunks, psx, stride, peaks, pstride, n_ev, ev_off, ev_out, ev_cap, raw, ev_pos);
 	else k_finish_pipe<false><<<fblocks, 128, 0, s>>>(chunk_len, n_chunks, psx, stride, peaks, pstride, n_ev, ev_off, ev_out, ev_cap, raw, ev_pos);

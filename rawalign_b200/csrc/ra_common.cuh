@@ -47,7 +47,13 @@ void events_pipe_layout(uint32_t max_len, const EvParams &p, uint32_t *stride, u
 cudaError_t launch_events_pipe(const float *sig, const uint64_t *chunk_off, const uint32_t *chunk_len, uint32_t n_chunks,
                                uint32_t max_len, const EvParams &p, int contract, float *scratch, uint32_t *n_ev,
                                uint64_t *ev_off, int chained, float *ev_out, uint64_t ev_cap, uint32_t *ev_pos, cudaStream_t s,
-                               cudaEvent_t after_detect);
+                               cudaEvent_t after_detect, cudaEvent_t scan_wait = nullptr, cudaEvent_t scan_done = nullptr);
+
+// ---- launcher (decode.cu): ri_read_sig's int16 -> pA conversion + (30,200) filter + compaction, one warp per read ----
+cudaError_t launch_decode_raw(const int16_t *raw, const uint64_t *raw_off, const uint32_t *raw_len, const float *offset,
+                              const float *scale, uint32_t n_reads, float *sig, uint32_t *l_sig, cudaStream_t s);
+
+cudaError_t launch_fetch_tables(const uint64_t *off_host, const uint32_t *len_host, uint64_t *off_dev, uint32_t *len_dev, uint32_t n, cudaStream_t s);
 
 // ---- launchers (dtw.cu) ------------------------------------------------------------------------
 struct DtwLaunch {

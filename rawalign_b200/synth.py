@@ -19,6 +19,9 @@ MAX_NUM_CHUNK = 30         # roptions.c:24
 SAMPLES_PER_BASE = 4000.0 / 450.0
 
 
+DAC_DIGITISATION, DAC_RANGE, DAC_OFFSET = 8192.0, 1467.61, 10.0     # R9.4 channel attributes
+
+
 def pore_model(seed: int = 7):
     rng = np.random.default_rng(seed)
     mean = np.clip(rng.normal(90.2, 12.9, 4 ** K), 55.0, 130.0)
@@ -57,6 +60,9 @@ class Reads:
     strand: np.ndarray       # uint8
     n_bases: np.ndarray
     base_start: list         # per read: first sample of every base (int64), truth for anchor placement
+    raw: np.ndarray = None       # int16 DAC samples, same layout as sig (what a FAST5 Signal dataset holds)
+    dac_offset: np.ndarray = None  # float32 per read: ri_sig_t::offset
+    dac_scale: np.ndarray = None   # float32 per read: range / digitisation (rsig.cpp:215)
 
 
 def simulate_reads(ref: np.ndarray, n_reads: int, seed: int = 2, mean_len: float = 8000.0, max_chunks: int = MAX_NUM_CHUNK,
@@ -89,7 +95,16 @@ def simulate_reads(ref: np.ndarray, n_reads: int, seed: int = 2, mean_len: float
     sig = np.zeros(int(off[-1]), np.float32)
     for r in range(n_reads):
         sig[int(off[r]):int(off[r]) + lens[r]] = sigs[r]
-    return Reads(sig, off, lens, start, strand, nb, bstarts)
+    # what the sequencer stores: raw = round(pA * digitisation / range - offset) as int16; the signal every
+    # consumer sees is the reference's decode of it, pA = ((float)raw + offset) * (range / digitisation) in fp32
+    dac_off = np.float32(DAC_OFFSET); dac_scale = np.float32(np.float32(DAC_RANGE) / np.float32(DAC_DIGITISATION))
+    raw = np.rint(sig.astype(np.float64) * (DAC_DIGITISATION / DAC_RANGE) - DAC_OFFSET).astype(np.int16)
+    dec = (raw.astype(np.float32) + dac_off) * dac_scale
+    for r in range(n_reads):                                   # padding between reads stays out of the (30, 200) window check
+        a, b = int(off[r]), int(off[r]) + int(lens[r])
+        assert dec[a:b].min() > 30.0 and dec[a:b].max() < 200.0
+    sig = dec.astype(np.float32)
+    return Reads(sig, off, lens, start, strand, nb, bstarts, raw, np.full(n_reads, dac_off, np.float32), np.full(n_reads, dac_scale, np.float32))
 
 
 def chunk_table(read_off: np.ndarray, read_len: np.ndarray, chunk_size: int = CHUNK_SIZE, max_chunks: int = MAX_NUM_CHUNK):

@@ -314,3 +314,68 @@ def test_align_chain_cigar_vs_oracle(ctx, oracle):
         assert e.value.code == -5
     finally:
         ctx.set_opt(ra.ri_mapopt_init())
+
+
+# ---- raw-signal decode + sliced/overlapped entry points -------------------------------------------------
+def _oracle_raw_pipeline(oracle, raw, raw_off, raw_len, offset, scale, chunk_size, max_chunks):
+    sigs, coff, clen, first, lsig = [], [], [], [0], []
+    pos = 0
+    for r in range(len(raw_len)):
+        a = int(raw_off[r])
+        d = oracle.decode_raw(raw[a:a + int(raw_len[r])], offset[r], scale[r])
+        lsig.append(len(d))
+        c = 0; cs = 0
+        while cs < len(d) and c < max_chunks:                      # rmap.cpp:684-689
+            coff.append(pos + cs); clen.append(min(chunk_size, len(d) - cs)); cs += chunk_size; c += 1
+        first.append(len(coff))
+        sigs.append(d); pos += len(d)
+    sig = np.concatenate(sigs) if sigs else np.zeros(0, np.float32)
+    ev, off = oracle.detect_events_batch(sig, np.array(coff, np.uint64), np.array(clen, np.uint32))
+    return ev, off, np.array(lsig, np.uint32), np.array(first, np.uint32)
+
+
+@pytest.mark.parametrize("align", [8, 1])
+def test_events_raw_batch_vs_oracle(ctx, oracle, align):
+    from rawalign_b200 import synth
+    rng = np.random.default_rng(77)
+    ref = synth.random_reference(30_000, seed=1)
+    rd = synth.simulate_reads(ref, 24, seed=12, max_chunks=3)
+    # re-lay the reads with the requested alignment, ragged lengths, and samples outside (30, 200) pA to exercise the filter
+    raws, offs, lens = [], [], []
+    pos = 5 if align == 1 else 0
+    for r in range(24):
+        a = int(rd.read_off[r]); n = int(rd.read_len[r]) - int(rng.integers(0, 50))
+        x = rd.raw[a:a + n].copy()
+        bad = rng.random(n) < 0.03
+        x[bad] = rng.choice(np.array([0, 40, 100, 1200, 3000, -500], np.int16), int(bad.sum()))
+        if r == 3: x = x[:7]                                       # shorter than the detector windows
+        if r == 5: x[:] = 3000                                     # everything filtered out -> no chunk at all
+        raws.append(x); offs.append(pos); lens.append(len(x)); pos += len(x); pos = (pos + align - 1) // align * align
+    raw = np.zeros(pos + 16, np.int16)
+    for x, o in zip(raws, offs):
+        raw[o:o + len(x)] = x
+    raw_off = np.array(offs, np.uint64); raw_len = np.array(lens, np.uint32)
+    offset = rd.dac_offset[:24].copy(); scale = rd.dac_scale[:24].copy()
+    offset[7] = np.float32(-3.5); scale[9] = np.float32(0.21)       # per-read channel attributes differ
+    for max_chunks in (2, 30):
+        ev, off, lsig, first = ctx.detect_events_raw_batch(raw, raw_off, raw_len, offset, scale, 4000, max_chunks)
+        ev_o, off_o, lsig_o, first_o = _oracle_raw_pipeline(oracle, raw, raw_off, raw_len, offset, scale, 4000, max_chunks)
+        assert np.array_equal(lsig, lsig_o), "filtered lengths differ"
+        assert np.array_equal(first, first_o), "chunk tables differ"
+        assert np.array_equal(off, off_o), "event counts differ"
+        assert np.array_equal(bits(ev), bits(ev_o)), "event values differ"
+
+
+def test_events_sliced_copies_large_batch(ctx, oracle):
+    """Enough signal (> 64 MB) for the host->device copy to be cut into several slices that overlap K1."""
+    from rawalign_b200 import synth
+    ref = synth.random_reference(60_000, seed=1)
+    rd = synth.simulate_reads(ref, 640, seed=21, max_chunks=8)
+    coff, clen, _ = synth.chunk_table(rd.read_off, rd.read_len, max_chunks=8)
+    assert int(clen.sum()) > (16 << 20)
+    ev, off = ctx.detect_events_batch(rd.sig, coff, clen)
+    ev_o, off_o = oracle.detect_events_batch(rd.sig, coff, clen)
+    assert np.array_equal(off, off_o) and np.array_equal(bits(ev), bits(ev_o))
+    ev2, off2, lsig, first = ctx.detect_events_raw_batch(rd.raw, rd.read_off[:-1], rd.read_len, rd.dac_offset, rd.dac_scale, 4000, 8)
+    assert np.array_equal(lsig, rd.read_len) and int(first[-1]) == len(coff)
+    assert np.array_equal(off2, off_o) and np.array_equal(bits(ev2), bits(ev_o))

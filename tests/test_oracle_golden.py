@@ -106,3 +106,16 @@ def test_align_chain_restates_rmap(oracle):
             ra = read[s0["query_position"]:e0["query_position"] + 1]; rb = ref[s0["target_position"]:e0["target_position"] + 1]
             c = oracle.dtw_global(ra, rb) if fill == 0 else oracle.dtw_banded(ra, rb, max(1, int(np.float32(len(ra)) * np.float32(0.1))))
             assert bits(oracle.align_chain(anc, read, ref, og)) == bits(np.float32(np.float32(np.float32(len(ra)) * np.float32(0.4)) - c))
+
+
+def test_decode_raw_restates_rsig(oracle):
+    """ri_read_sig's conversion (rsig.cpp:213-222) against an independent numpy fp32 evaluation, filter included."""
+    rng = np.random.default_rng(5)
+    raw = rng.integers(-200, 2500, 20000).astype(np.int16)
+    for offset, scale in ((10.0, 1467.61 / 8192.0), (-3.5, 0.21), (0.0, 0.05)):
+        o32, s32 = np.float32(offset), np.float32(scale)
+        pa = (raw.astype(np.float32) + o32) * s32
+        want = pa[(pa > 30) & (pa < 200)]
+        got = oracle.decode_raw(raw, o32, s32)
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    assert len(oracle.decode_raw(np.zeros(0, np.int16), 1.0, 1.0)) == 0
