@@ -95,7 +95,7 @@ struct ra_ctx {
 	// events
 	DevBuf sig, chunk_off, chunk_len, raw, nev, ev_off, ev_out, ev_pos;
 	DevBuf raw16, rd_off, rd_len, rd_offset, rd_scale, rd_lsig;   // raw-signal decode (decode.cu)
-	PinBuf pin_off, pin_tab, pin_lsig;
+	PinBuf pin_off, pin_tab, pin_lsig, pin_gf;
 	uint64_t last_events = 0;
 	// dtw
 	DevBuf a_arena, b_arena, items, cost, counter, ring, order;
@@ -112,6 +112,8 @@ struct ra_ctx {
 
 namespace {
 
+// Scratch for every chunk of the batch at once (groups of chunks then run on their own streams): worth it while it stays small.
+constexpr uint64_t kConcurrentSliceChunks = 65536;
 constexpr uint32_t kEventSubBatch = 32768;   // chunks per launch group: bounds the scratch arena (~2.4 GB at 4000 samples)
 
 // Enqueues K1 for chunks [0, n_chunks) of the given tables on the compute stream; no host synchronisation.
@@ -170,12 +172,40 @@ int events_launch(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_d
 	return RA_OK;
 }
 
+// Device-resident K1.  The stages of the v4 pipeline are bound differently (t-stat: issue; prefix sums and the detector
+// state machine: dependent-instruction latency), so large batches are cut into kSliceStreams groups of chunks that run on
+// their own streams and fill each other's stalls; only the CSR scans are chained (group k waits for the scan of group k-1).
 int events_dev(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_dev, const uint32_t *chunk_len_dev,
                uint32_t n_chunks, uint32_t max_chunk_len, float *ev_out_dev, uint64_t ev_cap, uint64_t *ev_off_dev,
                uint64_t *total_events)
 {
-	int rc = events_launch(ctx, sig_dev, chunk_off_dev, chunk_len_dev, n_chunks, max_chunk_len, ev_out_dev, ev_cap, ev_off_dev, 0, true);
-	if (rc) return rc;
+	const ra_mapopt_t &o = ctx->opt;
+	const bool pipe = ra::events_pipe_supported(o.window_length1, o.window_length2) && !ctx->force_unfused_events && !ctx->force_fused_events;
+	int rc;
+	if (pipe && n_chunks >= 2048u && n_chunks <= kConcurrentSliceChunks) {
+		ra::EvParams p = { o.window_length1, o.window_length2, o.threshold1, o.threshold2, o.peak_height };
+		uint32_t stride, pstride; size_t fpc;
+		ra::events_pipe_layout(max_chunk_len, p, &stride, &pstride, &fpc);
+		if ((rc = ctx->raw.reserve((size_t)n_chunks * fpc * sizeof(float)))) return rc;
+		if ((rc = ctx->nev.reserve((size_t)n_chunks * sizeof(uint32_t)))) return rc;
+		if ((rc = ctx->ev_pos.reserve((size_t)std::max<uint64_t>(ev_cap, 1) * sizeof(uint32_t)))) return rc;
+		RA_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
+		for (int k = 0; k < kSliceStreams; ++k) {
+			const uint32_t c0 = (uint32_t)((uint64_t)n_chunks * k / kSliceStreams), c1 = (uint32_t)((uint64_t)n_chunks * (k + 1) / kSliceStreams);
+			cudaStream_t s = ctx->slice_stream[k];
+			RA_CUDA(cudaStreamWaitEvent(s, ctx->ev[0], 0));
+			RA_CUDA(ra::launch_events_pipe(sig_dev, chunk_off_dev + c0, chunk_len_dev + c0, c1 - c0, max_chunk_len, p, (int)o.fp_contract,
+			                               ctx->raw.as<float>() + (size_t)c0 * fpc, ctx->nev.as<uint32_t>() + c0, ev_off_dev + c0, k != 0, ev_out_dev, ev_cap,
+			                               ctx->want_ev_pos ? ctx->ev_pos.as<uint32_t>() : nullptr, s, nullptr,
+			                               k ? ctx->slice_scan[k - 1] : nullptr, ctx->slice_scan[k]));
+			ctx->launches += ra::kPipeEventKernels;
+			RA_CUDA(cudaEventRecord(ctx->slice_done[k], s));
+		}
+		for (int k = 0; k < kSliceStreams; ++k) RA_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->slice_done[k], 0));
+		RA_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
+		RA_CUDA(cudaEventRecord(ctx->ev[2], ctx->stream));
+		ctx->timed_k1 = true;
+	} else if ((rc = events_launch(ctx, sig_dev, chunk_off_dev, chunk_len_dev, n_chunks, max_chunk_len, ev_out_dev, ev_cap, ev_off_dev, 0, true))) return rc;
 	uint64_t tot = 0;
 	RA_CUDA(cudaMemcpyAsync(&tot, ev_off_dev + n_chunks, sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
 	RA_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -203,9 +233,6 @@ int slice_launch(ra_ctx *ctx, const float *sig_dev, int k, uint32_t c0, uint32_t
 	RA_CUDA(cudaEventRecord(ctx->slice_done[k], ctx->stream));
 	return RA_OK;
 }
-
-// Scratch for every chunk of the batch at once (slices then run on their own streams): worth it while it stays small.
-constexpr uint64_t kConcurrentSliceChunks = 65536;
 
 // Reserves the K1 scratch of the v4 pipeline for n_total chunks and decides whether slices can run concurrently.
 int slices_prepare(ra_ctx *ctx, uint32_t n_total, uint32_t max_len, uint64_t dev_cap)
@@ -333,7 +360,7 @@ int dtw_dev(ra_ctx *ctx, const float *a_dev, const float *b_dev, const ra_dtw_it
 // Sparse border: plan (which chains, slots for their parts and tiles), flat part-cost kernel, replay -- once
 // for min_score_mode 0, twice (first chain of every group, then the rest) for the running threshold.  No host
 // synchronisation inside: capacities come from the anchor count (a chain of k anchors has k-1 parts).
-int sparse_pipeline(ra_ctx *ctx, const ra::ChainLaunch &L, uint32_t n_chains, uint64_t n_anchors)
+int sparse_pipeline(ra_ctx *ctx, const ra::ChainLaunch &L, uint32_t n_chains, uint64_t n_anchors, bool reset_counters = true)
 {
 	int rc;
 	if (n_chains == 0) return RA_OK;
@@ -347,8 +374,10 @@ int sparse_pipeline(ra_ctx *ctx, const ra::ChainLaunch &L, uint32_t n_chains, ui
 	if ((rc = ctx->sp_cost.reserve((size_t)part_cap * 4))) return rc;
 	if (L.cells && (rc = ctx->sp_pcells.reserve((size_t)part_cap * 4))) return rc;
 	if ((rc = ctx->sp_ntiles.reserve(64))) return rc;
-	if (L.cells) RA_CUDA(cudaMemsetAsync(L.cells, 0, 2 * sizeof(uint64_t), ctx->stream));
-	RA_CUDA(cudaMemsetAsync(L.need_cap, 0, sizeof(uint32_t), ctx->stream));
+	if (reset_counters) {
+		if (L.cells) RA_CUDA(cudaMemsetAsync(L.cells, 0, 2 * sizeof(uint64_t), ctx->stream));
+		RA_CUDA(cudaMemsetAsync(L.need_cap, 0, sizeof(uint32_t), ctx->stream));
+	}
 	ra::SparsePlan P; memset(&P, 0, sizeof(P));
 	P.n_chains = n_chains;
 	P.n_parts = ctx->sp_nparts.as<uint32_t>(); P.part_base = ctx->sp_pbase.as<uint64_t>();
@@ -501,7 +530,7 @@ void ra_destroy(ra_ctx *ctx)
 	}
 	DevBuf *dec[] = { &ctx->raw16, &ctx->rd_off, &ctx->rd_len, &ctx->rd_offset, &ctx->rd_scale, &ctx->rd_lsig };
 	for (DevBuf *b : dec) b->release();
-	ctx->pin_off.release(); ctx->pin_tab.release(); ctx->pin_lsig.release();
+	ctx->pin_off.release(); ctx->pin_tab.release(); ctx->pin_lsig.release(); ctx->pin_gf.release();
 	if (ctx->h2d) cudaStreamDestroy(ctx->h2d);
 	if (ctx->d2h) cudaStreamDestroy(ctx->d2h);
 	if (ctx->aux) cudaStreamDestroy(ctx->aux);
@@ -969,18 +998,29 @@ int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
 {
 	if (!ctx || (n_chains && (!anchors || !chains || !alignment_score))) return fail(RA_EINVAL, "NULL argument");
 	RA_CUDA(cudaSetDevice(ctx->device));
+	Trace tr; tr.mark("chains: start");
 	if (n_chains == 0) { if (cells_issued) *cells_issued = 0; if (cells_useful) *cells_useful = 0; return RA_OK; }
 	if (!read_arena && !ctx->resident_events) return fail(RA_EINVAL, "read_arena is NULL and no events are resident on the device");
 	if (!ref_arena && !ctx->ref.p) return fail(RA_EINVAL, "no reference arena: pass ref_arena or call ra_ref_load first");
 	const uint64_t nr = read_arena ? n_read : ctx->resident_events, nf = ref_arena ? n_ref : ctx->ref_n;
-	for (uint32_t k = 0; k < n_chains; ++k) {          // bounds: the kernel trusts these
+	// bounds the kernels trust, pass 1: the chain records only (sequential, cheap); pass 2, which touches the anchors, runs
+	// after the uploads have been queued so that it overlaps them
+	bool laid_in_order = true;
+	for (uint32_t k = 0; k < n_chains; ++k) {
 		const ra_chain_t &ch = chains[k];
 		if (ch.n_anchors < 1 || ch.anchor_off + ch.n_anchors > n_anchors) return fail(RA_EINVAL, "chain %u: anchors out of range", k);
-		const ra_anchor_t &s = anchors[ch.anchor_off + ch.n_anchors - 1], &e = anchors[ch.anchor_off];
-		if (e.query_position < s.query_position || e.target_position < s.target_position) return fail(RA_EINVAL, "chain %u: anchors[0] must be the chain end", k);
-		if (ch.read_off + e.query_position >= nr) return fail(RA_EINVAL, "chain %u: read span exceeds the read arena", k);
-		if (ch.ref_off + e.target_position >= nf) return fail(RA_EINVAL, "chain %u: reference span exceeds the reference arena", k);
+		if (k && ch.anchor_off < chains[k - 1].anchor_off + chains[k - 1].n_anchors) laid_in_order = false;
 	}
+	auto validate_spans = [&](uint32_t kb, uint32_t ke) -> int {
+		for (uint32_t k = kb; k < ke; ++k) {
+			const ra_chain_t &ch = chains[k];
+			const ra_anchor_t &s = anchors[ch.anchor_off + ch.n_anchors - 1], &e = anchors[ch.anchor_off];
+			if (e.query_position < s.query_position || e.target_position < s.target_position) return fail(RA_EINVAL, "chain %u: anchors[0] must be the chain end", k);
+			if (ch.read_off + e.query_position >= nr) return fail(RA_EINVAL, "chain %u: read span exceeds the read arena", k);
+			if (ch.ref_off + e.target_position >= nf) return fail(RA_EINVAL, "chain %u: reference span exceeds the reference arena", k);
+		}
+		return RA_OK;
+	};
 	std::vector<uint32_t> gf;
 	group_boundaries(chains, n_chains, min_score_mode, gf);
 	int rc;
@@ -1001,9 +1041,7 @@ int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
 	if ((rc = ctx->group_first.reserve(gf.size() * sizeof(uint32_t)))) return rc;
 	if ((rc = ctx->score.reserve((size_t)n_chains * sizeof(float)))) return rc;
 	if ((rc = ctx->keep.reserve((size_t)n_chains))) return rc;
-	RA_CUDA(cudaMemcpyAsync(ctx->anchors.p, anchors, (size_t)n_anchors * sizeof(ra_anchor_t), cudaMemcpyHostToDevice, ctx->stream));
-	RA_CUDA(cudaMemcpyAsync(ctx->chains.p, chains, (size_t)n_chains * sizeof(ra_chain_t), cudaMemcpyHostToDevice, ctx->stream));
-	RA_CUDA(cudaMemcpyAsync(ctx->group_first.p, gf.data(), gf.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+	const uint32_t n_groups = (uint32_t)gf.size() - 1;
 	const float *ms_dev = nullptr;
 	if (min_score_mode != 1 && min_score) {
 		if ((rc = ctx->min_score.reserve((size_t)n_chains * sizeof(float)))) return rc;
@@ -1011,8 +1049,88 @@ int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
 		ms_dev = ctx->min_score.as<float>();
 	}
 	uint64_t cells[2] = {0, 0};
+	const bool want_cells = cells_issued || cells_useful;
+	// Sparse border with chains laid out in order: anchors and chain records go up in slices (h2d stream) and every slice is
+	// evaluated as soon as it has arrived; anything else takes the one-shot path.
+	const bool in_order = laid_in_order && ctx->opt.dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_SPARSE;
+	const int n_slices = in_order ? (int)std::min<uint64_t>(kMaxSlices, std::max<uint64_t>(1, n_anchors / (2u << 20))) : 1;   // >= 16 MB of anchors per slice
+	if (n_slices > 1) {
+		if ((rc = ctx->counter.reserve(64))) return rc;
+		if ((rc = ctx->cells.reserve(64))) return rc;
+		if ((rc = ctx->pin_gf.reserve(gf.size() * sizeof(uint32_t)))) return rc;
+		memcpy(ctx->pin_gf.p, gf.data(), gf.size() * sizeof(uint32_t));
+		RA_CUDA(cudaStreamSynchronize(ctx->stream));              // previous users of the staging buffers are done; the events are resident
+		RA_CUDA(cudaMemcpyAsync(ctx->group_first.p, ctx->pin_gf.p, gf.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->h2d));
+		uint32_t gcut[kMaxSlices + 1]; gcut[0] = 0;
+		{
+			uint32_t g = 0;
+			for (int k = 1; k <= n_slices; ++k) {
+				const uint64_t target = n_anchors * k / n_slices;
+				while (g < n_groups && chains[gf[g + 1] - 1].anchor_off + chains[gf[g + 1] - 1].n_anchors <= target) ++g;
+				if (k == n_slices) g = n_groups;
+				gcut[k] = g;
+			}
+		}
+		for (int k = 0; k < n_slices; ++k) {
+			const uint32_t k0 = gf[gcut[k]], k1 = gf[gcut[k + 1]];
+			if (k1 > k0) {
+				const uint64_t a0 = chains[k0].anchor_off, a1 = chains[k1 - 1].anchor_off + chains[k1 - 1].n_anchors;
+				RA_CUDA(cudaMemcpyAsync(ctx->anchors.as<ra_anchor_t>() + a0, anchors + a0, (size_t)(a1 - a0) * sizeof(ra_anchor_t), cudaMemcpyHostToDevice, ctx->h2d));
+				RA_CUDA(cudaMemcpyAsync(ctx->chains.as<ra_chain_t>() + k0, chains + k0, (size_t)(k1 - k0) * sizeof(ra_chain_t), cudaMemcpyHostToDevice, ctx->h2d));
+			}
+			RA_CUDA(cudaEventRecord(ctx->slice_in[k], ctx->h2d));
+		}
+		tr.mark("chains: copies queued");
+		const ra_mapopt_t &o = ctx->opt;
+		ra::ChainLaunch L; memset(&L, 0, sizeof(L));
+		L.read_arena = read_dev; L.ref_arena = ref_dev; L.anchors = ctx->anchors.as<ra_anchor_t>(); L.chains = ctx->chains.as<ra_chain_t>();
+		L.border = o.dtw_border_constraint; L.fill = o.dtw_fill_method; L.fp_contract = o.fp_contract;
+		L.band_frac = o.dtw_band_radius_frac; L.match_bonus = o.dtw_match_bonus; L.min_dtw_score = o.dtw_min_score;
+		L.min_score_mode = min_score_mode; L.min_score = ms_dev; L.score = ctx->score.as<float>(); L.keep = ctx->keep.as<uint8_t>();
+		L.work_counter = ctx->counter.as<uint32_t>(); L.need_cap = ctx->counter.as<uint32_t>() + 4;
+		L.cells = want_cells ? ctx->cells.as<uint64_t>() : nullptr;
+		const size_t warps = (size_t)ctx->n_sm * ra::kChainCtasPerSm * 4;
+		uint32_t ring_cap = ctx->chain_ring.cap ? (uint32_t)(ctx->chain_ring.cap / (warps * 3 * sizeof(float))) : 0;
+		{ uint32_t c = 1; while (c * 2 <= ring_cap) c *= 2; ring_cap = ring_cap ? c : 0; }
+		L.ring_scratch = ring_cap ? ctx->chain_ring.as<float>() : nullptr; L.ring_cap = ring_cap;
+		RA_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
+		for (int k = 0; k < n_slices; ++k) {
+			const uint32_t g0 = gcut[k], g1 = gcut[k + 1];
+			if ((rc = validate_spans(gf[g0], gf[g1]))) { cudaStreamSynchronize(ctx->h2d); cudaStreamSynchronize(ctx->stream); return rc; }   // overlaps the uploads
+			RA_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->slice_in[k], 0));
+			if (g1 == g0) continue;
+			ra::ChainLaunch Ls = L;
+			Ls.group_first = ctx->group_first.as<uint32_t>() + g0; Ls.n_groups = g1 - g0;
+			const uint32_t k0 = gf[g0], k1 = gf[g1];
+			const uint64_t a0 = chains[k0].anchor_off, a1 = chains[k1 - 1].anchor_off + chains[k1 - 1].n_anchors;
+			(void)a0; (void)a1;
+			if ((rc = sparse_pipeline(ctx, Ls, n_chains, n_anchors, k == 0))) return rc;
+		}
+		RA_CUDA(cudaEventRecord(ctx->ev[4], ctx->stream));
+		ctx->timed_dtw = true;
+		tr.mark("chains: kernels queued");
+		if (tr.on) { cudaStreamSynchronize(ctx->h2d); tr.mark("chains: h2d done"); cudaStreamSynchronize(ctx->stream); tr.mark("chains: kernels done"); }
+		uint32_t need = 0;
+		RA_CUDA(cudaMemcpyAsync(&need, L.need_cap, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+		if (L.cells) RA_CUDA(cudaMemcpyAsync(cells, L.cells, sizeof(cells), cudaMemcpyDeviceToHost, ctx->stream));
+		RA_CUDA(cudaMemcpyAsync(alignment_score, ctx->score.p, (size_t)n_chains * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+		if (keep) RA_CUDA(cudaMemcpyAsync(keep, ctx->keep.p, (size_t)n_chains, cudaMemcpyDeviceToHost, ctx->stream));
+		RA_CUDA(cudaStreamSynchronize(ctx->stream));
+		tr.mark("chains: results back");
+		if (need == 0) {
+			if (cells_issued) *cells_issued = cells[0];
+			if (cells_useful) *cells_useful = cells[1];
+			return RA_OK;
+		}
+		// a part was wider than the rings at hand: everything is on the device now, take the one-shot path (it grows the ring)
+	} else {
+		if ((rc = validate_spans(0, n_chains))) return rc;
+		RA_CUDA(cudaMemcpyAsync(ctx->anchors.p, anchors, (size_t)n_anchors * sizeof(ra_anchor_t), cudaMemcpyHostToDevice, ctx->stream));
+		RA_CUDA(cudaMemcpyAsync(ctx->chains.p, chains, (size_t)n_chains * sizeof(ra_chain_t), cudaMemcpyHostToDevice, ctx->stream));
+		RA_CUDA(cudaMemcpyAsync(ctx->group_first.p, gf.data(), gf.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+	}
 	if ((rc = chains_dev(ctx, read_dev, ref_dev, ctx->anchors.as<ra_anchor_t>(), ctx->chains.as<ra_chain_t>(), ctx->group_first.as<uint32_t>(),
-	                     (uint32_t)gf.size() - 1, min_score_mode, ms_dev, ctx->score.as<float>(), ctx->keep.as<uint8_t>(), (cells_issued || cells_useful) ? cells : nullptr, n_chains, n_anchors))) return rc;
+	                     n_groups, min_score_mode, ms_dev, ctx->score.as<float>(), ctx->keep.as<uint8_t>(), want_cells ? cells : nullptr, n_chains, n_anchors))) return rc;
 	RA_CUDA(cudaMemcpyAsync(alignment_score, ctx->score.p, (size_t)n_chains * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
 	if (keep) RA_CUDA(cudaMemcpyAsync(keep, ctx->keep.p, (size_t)n_chains, cudaMemcpyDeviceToHost, ctx->stream));
 	RA_CUDA(cudaStreamSynchronize(ctx->stream));

@@ -27,6 +27,7 @@
 // Compiled with -fmad=false: fused multiply-adds exist only where the reference build has them (CONTRACT).
 #include "ra_common.cuh"
 #include <float.h>
+#include <math.h>
 
 namespace ra {
 namespace evp {
@@ -147,11 +148,12 @@ k_prefix_pipe(const float *__restrict__ sig, const uint64_t *__restrict__ chunk_
 // ---------------------------------------------------------------------------------------------------
 // t-statistics
 // ---------------------------------------------------------------------------------------------------
-// x / wf, correctly rounded, for wf = a window length in [2, 32] (exhaustive check: tests/test_fastdiv.py)
+// x / wf, correctly rounded, for wf = a window length in [2, 32] and 1e-30 <= |x| <= 1e30 (exhaustive check of the
+// three-instruction sequence: tests/test_fastdiv.py); anything else (zeros, subnormals, huge values) takes the IEEE division.
 __device__ __forceinline__ float fdiv_w(float x, float wf, float rcp)
 {
 	const float ax = fabsf(x);
-	if ((ax >= 1e-30f && ax <= 1e30f) || ax == 0.0f) {
+	if (ax >= 1e-30f && ax <= 1e30f) {
 		const float q0 = __fmul_rn(x, rcp);
 		const float r = __fmaf_rn(-q0, wf, x);
 		return __fmaf_rn(r, rcp, q0);
@@ -159,26 +161,39 @@ __device__ __forceinline__ float fdiv_w(float x, float wf, float rcp)
 	return __fdiv_rn(x, wf);
 }
 
+// Per-window constants of the clamped-variance case: with fp32 prefix sums of ~1e7 the window variance of revent.c:61 is
+// rounding noise late in a chunk and is clamped to FLT_MIN at :63 for a sizeable share of positions (ncu: 19 % of warps had
+// such a lane), so that case gets a straight-line path of its own instead of the IEEE fallbacks.
+struct TsWin {
+	float wf, rcp;
+	float vw_min;        // FLT_MIN / wf            (fp32 division, :69's var/w)
+	double rs_min;       // 1 / sqrt((double)vw_min)
+};
+
 // revent.c:61-69 from the window means (mean1, mean2) and mean squares (e1, e2)
 template <bool CONTRACT>
-__device__ __forceinline__ float tstat_from_means(float mean1, float mean2, float e1, float e2, float wf, float rcp)
+__device__ __forceinline__ float tstat_from_means(float mean1, float mean2, float e1, float e2, const TsWin W)
 {
 	float var;
 	if (CONTRACT) var = __fmaf_rn(-mean2, mean2, __fadd_rn(__fmaf_rn(-mean1, mean1, e1), e2));            // :61, two vfnmadd
 	else var = __fsub_rn(__fadd_rn(__fsub_rn(e1, __fmul_rn(mean1, mean1)), e2), __fmul_rn(mean2, mean2));
-	var = fmaxf(var, FLT_MIN);                                                                              // :63
+	const bool clamped = !(var > FLT_MIN);                                                                  // :63 fmaxf(var, FLT_MIN); NaN -> FLT_MIN too
 	const float dm = __fsub_rn(mean2, mean1);                                                               // :68
-	const float vw = fdiv_w(var, wf, rcp);
 	const float x = fabsf(dm);
-	// :69  (float)(fabs((double)dm) / sqrt((double)vw)).  y = x * rsqrt(vw) to ~2^-43 by one Newton step in fp64; the
-	// reference's doubly rounded quotient is within 2^-52 of the exact value, so both round to the same float unless y
-	// sits within 2^13 double ulps of a float rounding boundary -- then the exact path runs.
-	if (vw >= 1e-30f && vw <= 1e30f && x <= 1e30f) {
+	const float vw = clamped ? W.vw_min : fdiv_w(var, W.wf, W.rcp);
+	// :69  (float)(fabs((double)dm) / sqrt((double)vw)).  y = x * r with r = 1/sqrt(vw) to ~2^-50 (one Newton step in fp64
+	// from the fp32 rsqrt; the host-computed constant when clamped); the reference's doubly rounded quotient is within 2^-52
+	// of the exact value, so both round to the same float unless y sits within 2^13 double ulps of a float rounding
+	// boundary -- then, and for operands outside the comfortable range, the exact path runs.
+	const bool ok = clamped || (vw >= 1e-30f && vw <= 1e30f);
+	if (ok && x <= 1e30f) {
+		const float vs = clamped ? 1.0f : vw;
 		float r0f;
-		asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r0f) : "f"(vw));
-		const double r0 = (double)r0f, vd = (double)vw;
+		asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r0f) : "f"(vs));
+		const double r0 = (double)r0f, vd = (double)vs;
 		const double e = __fma_rn(-__dmul_rn(vd, r0), r0, 1.0);
-		const double r1 = __fma_rn(__dmul_rn(r0, 0.5), e, r0);
+		const double rn = __fma_rn(__dmul_rn(r0, 0.5), e, r0);
+		const double r1 = clamped ? W.rs_min : rn;
 		const double y = __dmul_rn((double)x, r1);
 		const uint32_t lo = (uint32_t)__double2loint(y);
 		const bool near_boundary = ((lo - (0x10000000u - 0x2000u)) & 0x1FFFFFFFu) < 0x4000u;
@@ -194,54 +209,53 @@ constexpr int kTsThreads = kTsBlock + 32;
 template <bool CONTRACT>
 __global__ void __launch_bounds__(kTsThreads)
 k_tstat_pipe(const uint32_t *__restrict__ chunk_len, const float *__restrict__ psx, const float *__restrict__ pssx, uint32_t stride,
-             float *__restrict__ t1, float *__restrict__ t2, uint32_t w1, uint32_t w2, float rcp1, float rcp2)
+             float *__restrict__ t1, float *__restrict__ t2, uint32_t w1, uint32_t w2, TsWin W1, TsWin W2)
 {
 	__shared__ float sp[kTsThreads + kHalo], sq[kTsThreads + kHalo];  // ps[j], pss[j] for j = base - kHalo + t
 	__shared__ float M1[kTsThreads], E1[kTsThreads], M2[kTsThreads], E2[kTsThreads];
 	const uint32_t c = blockIdx.y;
 	const uint32_t len = chunk_len[c];
-	const int base = (int)(blockIdx.x * kTsBlock);
-	if ((uint32_t)base >= len) return;
-	const int u = threadIdx.x;
-	const float *__restrict__ prow = psx + (size_t)c * stride;
-	const float *__restrict__ qrow = pssx + (size_t)c * stride;
-	const int j = base + u;
+	const uint32_t base = blockIdx.x * kTsBlock;
+	if (base >= len) return;
+	const uint32_t u = threadIdx.x;
+	const float *__restrict__ prow = psx + (size_t)c * stride + base;  // prow[k] = ps[base + k + 1]
+	const float *__restrict__ qrow = pssx + (size_t)c * stride + base;
+	const uint32_t j = base + u;
 	{
-		const bool in = j >= 1 && j <= (int)len;                     // ps[0] = pss[0] = +0.0f (:26-27)
-		sp[u + kHalo] = in ? __ldg(prow + j - 1) : 0.0f;
-		sq[u + kHalo] = in ? __ldg(qrow + j - 1) : 0.0f;
-		if (u < kHalo) {
-			const int jh = base - kHalo + u;
-			const bool inh = jh >= 1;                                // jh < base < len
-			sp[u] = inh ? __ldg(prow + jh - 1) : 0.0f;
-			sq[u] = inh ? __ldg(qrow + jh - 1) : 0.0f;
+		const bool in = j >= 1u && j <= len;                         // ps[0] = pss[0] = +0.0f (:26-27)
+		sp[u + kHalo] = in ? __ldg(prow + (int)u - 1) : 0.0f;
+		sq[u + kHalo] = in ? __ldg(qrow + (int)u - 1) : 0.0f;
+		if (u < (uint32_t)kHalo) {
+			const bool inh = base + u >= (uint32_t)kHalo + 1u;       // jh = base - kHalo + u >= 1  (jh < base < len)
+			sp[u] = inh ? __ldg(prow + (int)u - kHalo - 1) : 0.0f;
+			sq[u] = inh ? __ldg(qrow + (int)u - kHalo - 1) : 0.0f;
 		}
 	}
 	__syncthreads();
-	const float w1f = (float)w1, w2f = (float)w2;
 	// window mean ending at j:  M(j) = (ps[j] - ps[j-w]) / w, j in [w, len].  At j == w the reference skips the
 	// subtraction (:53-56); ps[0] = +0.0f and x - 0.0f == x bit for bit.
-	if (j <= (int)len) {
+	if (j <= len) {
 		const float s0 = sp[u + kHalo], q0 = sq[u + kHalo];
-		if (j >= (int)w1) {
-			M1[u] = fdiv_w(__fsub_rn(s0, sp[u + kHalo - (int)w1]), w1f, rcp1);
-			E1[u] = fdiv_w(__fsub_rn(q0, sq[u + kHalo - (int)w1]), w1f, rcp1);
+		if (j >= w1) {
+			M1[u] = fdiv_w(__fsub_rn(s0, sp[u + kHalo - w1]), W1.wf, W1.rcp);
+			E1[u] = fdiv_w(__fsub_rn(q0, sq[u + kHalo - w1]), W1.wf, W1.rcp);
 		}
-		if (j >= (int)w2) {
-			M2[u] = fdiv_w(__fsub_rn(s0, sp[u + kHalo - (int)w2]), w2f, rcp2);
-			E2[u] = fdiv_w(__fsub_rn(q0, sq[u + kHalo - (int)w2]), w2f, rcp2);
+		if (j >= w2) {
+			M2[u] = fdiv_w(__fsub_rn(s0, sp[u + kHalo - w2]), W2.wf, W2.rcp);
+			E2[u] = fdiv_w(__fsub_rn(q0, sq[u + kHalo - w2]), W2.wf, W2.rcp);
 		}
 	}
 	__syncthreads();
-	const uint32_t p = (uint32_t)j;
-	if (u >= kTsBlock || p >= len) return;
+	if (u >= (uint32_t)kTsBlock || j >= len) return;
 	float v1 = 0.0f, v2 = 0.0f;
-	if (len >= 2u * w1 && w1 >= 2u && p >= w1 && p + w1 <= len)      // :46, :50
-		v1 = tstat_from_means<CONTRACT>(M1[u], M1[u + w1], E1[u], E1[u + w1], w1f, rcp1);
-	if (len >= 2u * w2 && w2 >= 2u && p >= w2 && p + w2 <= len)
-		v2 = tstat_from_means<CONTRACT>(M2[u], M2[u + w2], E2[u], E2[u + w2], w2f, rcp2);
-	t1[(size_t)c * stride + p] = v1;
-	t2[(size_t)c * stride + p] = v2;
+	// :46, :50  valid iff w >= 2, len >= 2w, w <= p <= len - w   (one unsigned compare once len >= 2w)
+	if (w1 >= 2u && len >= 2u * w1 && j - w1 <= len - 2u * w1)
+		v1 = tstat_from_means<CONTRACT>(M1[u], M1[u + w1], E1[u], E1[u + w1], W1);
+	if (w2 >= 2u && len >= 2u * w2 && j - w2 <= len - 2u * w2)
+		v2 = tstat_from_means<CONTRACT>(M2[u], M2[u + w2], E2[u], E2[u + w2], W2);
+	const size_t o = (size_t)c * stride + j;
+	t1[o] = v1;
+	t2[o] = v2;
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -439,6 +453,17 @@ k_finish_pipe(const uint32_t *__restrict__ chunk_len, uint32_t n_chunks, const f
 
 } // namespace evp
 
+// host side: IEEE fp32 division / fp64 sqrt and division, exactly the operations of revent.c:69 on the clamped variance
+static evp::TsWin make_tswin(uint32_t w)
+{
+	evp::TsWin W;
+	W.wf = (float)w; W.rcp = 1.0f / W.wf;
+	volatile float vmin = FLT_MIN / W.wf;          // subnormal for w >= 2: x86 SSE keeps it (no flush-to-zero on the host)
+	W.vw_min = vmin;
+	W.rs_min = 1.0 / sqrt((double)vmin);
+	return W;
+}
+
 bool events_pipe_supported(uint32_t w1, uint32_t w2) { return w1 >= 1 && w2 >= 1 && w1 <= kPipeMaxWindow && w2 <= kPipeMaxWindow; }
 
 void events_pipe_layout(uint32_t max_len, const EvParams &p, uint32_t *stride, uint32_t *peak_stride, size_t *floats_per_chunk)
@@ -468,13 +493,13 @@ cudaError_t launch_events_pipe(const float *sig, const uint64_t *chunk_off, cons
 	float *raw = reinterpret_cast<float *>(peaks + (size_t)n_chunks * pstride);
 	const uint32_t lane_ctas = (n_chunks + 31u) / 32u;
 	const dim3 tgrid((max_len + kTsBlock - 1) / kTsBlock, n_chunks);
-	const float rcp1 = 1.0f / (float)p.w1, rcp2 = 1.0f / (float)p.w2;      // correctly rounded reciprocals (IEEE division on the host)
+	const TsWin W1 = make_tswin(p.w1), W2 = make_tswin(p.w2);
 	if (contract) {
 		k_prefix_pipe<true><<<lane_ctas, 32, 0, s>>>(sig, chunk_off, chunk_len, n_chunks, psx, pssx, stride);
-		k_tstat_pipe<true><<<tgrid, kTsThreads, 0, s>>>(chunk_len, psx, pssx, stride, t1, t2, p.w1, p.w2, rcp1, rcp2);
+		k_tstat_pipe<true><<<tgrid, kTsThreads, 0, s>>>(chunk_len, psx, pssx, stride, t1, t2, p.w1, p.w2, W1, W2);
 	} else {
 		k_prefix_pipe<false><<<lane_ctas, 32, 0, s>>>(sig, chunk_off, chunk_len, n_chunks, psx, pssx, stride);
-		k_tstat_pipe<false><<<tgrid, kTsThreads, 0, s>>>(chunk_len, psx, pssx, stride, t1, t2, p.w1, p.w2, rcp1, rcp2);
+		k_tstat_pipe<false><<<tgrid, kTsThreads, 0, s>>>(chunk_len, psx, pssx, stride, t1, t2, p.w1, p.w2, W1, W2);
 	}
 	k_fsm_pipe<<<lane_ctas, 32, 0, s>>>(chunk_len, n_chunks, t1, t2, stride, p, peaks, pstride, n_ev);
 	if (after_detect) cudaEventRecord(after_detect, s);
