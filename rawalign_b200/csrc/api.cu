@@ -105,6 +105,7 @@ struct ra_ctx {
 	uint64_t resident_events = 0;      // events left on the device by the last ra_detect_events_batch
 	bool force_unfused_events = false; // test hook: run the five-kernel K1 v2 (also the path for windows > kFusedMaxWindow)
 	bool force_fused_events = false;   // test hook: run the single-pass K1 v3
+	bool force_generic_dtw = false;    // test hook (reserved bit 2): every item through the generic shared-memory DTW kernel
 	bool want_ev_pos = true;           // keep the event start samples of the last K1 call (ra_last_event_positions)
 	// traceback
 	DevBuf dirs, dir_off, slot_off, slot_i, slot_j, slot_d, path_len, path_off, out_i, out_j, out_d;
@@ -330,30 +331,58 @@ uint32_t item_width(const ra_dtw_item_t &it, bool tb)
 	return (uint32_t)it.band_radius + extra + 1u;
 }
 
-// Launches the cost kernels for items already on the device. items_host is used for sizing only.
+// Launches the cost kernels for items already on the device.  items_host is used for sizing and for sorting the items into
+// kernel classes: problems whose band fits one warp's register wavefront go to dtw_wave.cu (by rows per lane), the rest
+// (very tall bands or full matrices) to the generic shared-memory kernel.
 int dtw_dev(ra_ctx *ctx, const float *a_dev, const float *b_dev, const ra_dtw_item_t *items_dev,
             const ra_dtw_item_t *items_host, uint32_t n_items, float *cost_dev)
 {
 	if (n_items == 0) return RA_OK;
 	int rc;
+	static const int kNC = 9;
+	static const int kClassH[kNC] = { 1, 2, 4, 8, 16, 32, 64 + 8, 64 + 16, 64 + 32 };   // dtw_wave_class codes
+	std::vector<uint32_t> cls[kNC + 1];                          // wave classes, then [kNC] generic
 	uint32_t maxw = 0;
-	for (uint32_t k = 0; k < n_items; ++k) maxw = std::max(maxw, item_width(items_host[k], false));
-	ra::DtwLaunch L; memset(&L, 0, sizeof(L));
-	L.a_arena = a_dev; L.b_arena = b_dev; L.items = items_dev; L.n_items = n_items; L.cost = cost_dev;
-	if ((rc = ctx->counter.reserve(64))) return rc;
-	L.work_counter = ctx->counter.as<uint32_t>();
-	if (maxw > ra::dtw_generic_smem_ring_cap()) {
-		uint32_t cap = 1; while (cap < maxw) cap <<= 1;
-		const size_t warps = (size_t)ctx->n_sm * 4 * 4;
-		if ((rc = ctx->ring.reserve(warps * 3 * cap * sizeof(float)))) return rc;
-		L.ring_scratch = ctx->ring.as<float>(); L.ring_cap = cap;
+	for (uint32_t k = 0; k < n_items; ++k) {
+		const int H = ctx->force_generic_dtw ? 0 : ra::dtw_wave_class(items_host[k].a_len, items_host[k].b_len, items_host[k].band_radius);
+		int c = kNC;
+		for (int q = 0; q < kNC; ++q) if (H == kClassH[q]) c = q;
+		cls[c].push_back(k);
+		if (c == kNC) maxw = std::max(maxw, item_width(items_host[k], false));
 	}
-	int nl = 0;
+	std::vector<uint32_t> order; order.reserve(n_items);
+	uint32_t first[kNC + 2]; first[0] = 0;
+	for (int c = 0; c <= kNC; ++c) { order.insert(order.end(), cls[c].begin(), cls[c].end()); first[c + 1] = (uint32_t)order.size(); }
+	if ((rc = ctx->order.reserve((size_t)n_items * sizeof(uint32_t)))) return rc;
+	if ((rc = ctx->counter.reserve(64))) return rc;
+	RA_CUDA(cudaMemcpyAsync(ctx->order.p, order.data(), (size_t)n_items * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+	ra::DtwLaunch L; memset(&L, 0, sizeof(L));
+	L.a_arena = a_dev; L.b_arena = b_dev; L.items = items_dev; L.cost = cost_dev;
 	RA_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
-	RA_CUDA(ra::launch_dtw_generic(L, false, ctx->n_sm, ctx->stream, &nl));
+	for (int c = 0; c < kNC; ++c) {
+		const uint32_t nc = first[c + 1] - first[c];
+		if (!nc) continue;
+		L.n_items = n_items;
+		RA_CUDA(ra::launch_dtw_wave(L, kClassH[c], ctx->order.as<uint32_t>() + first[c], nc, ctx->counter.as<uint32_t>() + 6 + c, ctx->n_sm, ctx->stream));
+		ctx->launches += 1;
+	}
+	const uint32_t ng = first[kNC + 1] - first[kNC];
+	if (ng) {
+		L.order = ctx->order.as<uint32_t>() + first[kNC]; L.n_items = ng;
+		L.work_counter = ctx->counter.as<uint32_t>();
+		if (maxw > ra::dtw_generic_smem_ring_cap()) {
+			uint32_t cap = 1; while (cap < maxw) cap <<= 1;
+			const size_t warps = (size_t)ctx->n_sm * 4 * 4;
+			if ((rc = ctx->ring.reserve(warps * 3 * cap * sizeof(float)))) return rc;
+			L.ring_scratch = ctx->ring.as<float>(); L.ring_cap = cap;
+		}
+		int nl = 0;
+		RA_CUDA(ra::launch_dtw_generic(L, false, ctx->n_sm, ctx->stream, &nl));
+		ctx->launches += nl;
+	}
 	RA_CUDA(cudaEventRecord(ctx->ev[4], ctx->stream));
 	ctx->timed_dtw = true;
-	ctx->launches += nl;
+	RA_CUDA(cudaStreamSynchronize(ctx->stream));                  // `order` lives on this stack frame until the copy has been consumed
 	return RA_OK;
 }
 
@@ -546,6 +575,7 @@ int ra_set_opt(ra_ctx *ctx, const ra_mapopt_t *opt)
 	ctx->opt = *opt;
 	ctx->force_unfused_events = (opt->reserved & 1u) != 0;
 	ctx->force_fused_events = (opt->reserved & 2u) != 0;
+	ctx->force_generic_dtw = (opt->reserved & 4u) != 0;
 	return RA_OK;
 }
 

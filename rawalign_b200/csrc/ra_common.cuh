@@ -79,6 +79,9 @@ cudaError_t launch_path_compact(const uint32_t *slot_i, const uint32_t *slot_j, 
                                 const uint64_t *path_off, uint32_t n_items, uint32_t *out_i, uint32_t *out_j,
                                 float *out_d, cudaStream_t s);
 uint32_t dtw_generic_smem_ring_cap();
+// dtw_wave.cu: one warp per problem, register-resident skewed wavefront (H rows per lane; 0 = not eligible)
+int dtw_wave_class(uint32_t a_len, uint32_t b_len, int32_t band_radius);
+cudaError_t launch_dtw_wave(const DtwLaunch &L, int H, const uint32_t *order_dev, uint32_t n_order, uint32_t *work_counter, int n_sm, cudaStream_t s);
 
 // ---- launcher (chains.cu) ----------------------------------------------------------------------
 struct ChainLaunch {
