@@ -1153,6 +1153,46 @@ int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
 			return RA_OK;
 		}
 		// a part was wider than the rings at hand: everything is on the device now, take the one-shot path (it grows the ring)
+	} else if (ctx->opt.dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_GLOBAL && !ctx->force_generic_dtw) {
+		// Global border: one region per chain (rmap.cpp:192-237).  The sub-DTWs go through the item kernels (sorted into the
+		// register-wavefront classes by size); the pre-check against min_score (:205-209), alignment_score (:306) and the running
+		// best_found_alignment of the evaluation loop (:515-524) are replayed here in the reference's order and float arithmetic.
+		if ((rc = validate_spans(0, n_chains))) return rc;
+		const ra_mapopt_t &o = ctx->opt;
+		std::vector<ra_dtw_item_t> items(n_chains);
+		for (uint32_t k = 0; k < n_chains; ++k) {
+			const ra_chain_t &ch = chains[k];
+			const ra_anchor_t &s = anchors[ch.anchor_off + ch.n_anchors - 1], &e = anchors[ch.anchor_off];     // :195-196
+			ra_dtw_item_t &it = items[k];
+			it.a_off = ch.read_off + s.query_position; it.b_off = ch.ref_off + s.target_position;
+			it.a_len = e.query_position - s.query_position + 1; it.b_len = e.target_position - s.target_position + 1;
+			it.band_radius = (o.dtw_fill_method == RA_DTW_FILL_METHOD_BANDED) ? std::max(1, (int)((float)it.a_len * o.dtw_band_radius_frac)) : -1;   // :214
+			it.exclude_last = 0;
+		}
+		if ((rc = ctx->items.reserve((size_t)n_chains * sizeof(ra_dtw_item_t)))) return rc;
+		if ((rc = ctx->cost.reserve((size_t)n_chains * sizeof(float)))) return rc;
+		RA_CUDA(cudaMemcpyAsync(ctx->items.p, items.data(), (size_t)n_chains * sizeof(ra_dtw_item_t), cudaMemcpyHostToDevice, ctx->stream));
+		if ((rc = dtw_dev(ctx, read_dev, ref_dev, ctx->items.as<ra_dtw_item_t>(), items.data(), n_chains, ctx->cost.as<float>()))) return rc;
+		std::vector<float> cost(n_chains);
+		RA_CUDA(cudaMemcpyAsync(cost.data(), ctx->cost.p, (size_t)n_chains * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+		RA_CUDA(cudaStreamSynchronize(ctx->stream));
+		float best = 0.0f;                                                                                     // :515
+		for (uint32_t k = 0; k < n_chains; ++k) {
+			if (min_score_mode == 1 && (k == 0 || chains[k].group != chains[k - 1].group)) best = 0.0f;
+			const float ms = (min_score_mode == 1) ? best : (min_score ? min_score[k] : RA_SCORE_DROPPED);
+			const ra_dtw_item_t &it = items[k];
+			const uint64_t c = ra_dtw_cells(it.a_len, it.b_len, it.band_radius);
+			cells[0] += c;
+			float score = RA_SCORE_DROPPED;
+			if (!((float)it.a_len * o.dtw_match_bonus < ms)) { score = chain_score(o, it.a_len, cost[k]); cells[1] += c; }   // :205-209, :236, :306
+			alignment_score[k] = score;
+			const bool kp = score >= o.dtw_min_score;                                                           // :518
+			if (keep) keep[k] = kp ? 1 : 0;
+			if (kp && score > best) best = score;                                                               // :519-521
+		}
+		if (cells_issued) *cells_issued = cells[0];
+		if (cells_useful) *cells_useful = cells[1];
+		return RA_OK;
 	} else {
 		if ((rc = validate_spans(0, n_chains))) return rc;
 		RA_CUDA(cudaMemcpyAsync(ctx->anchors.p, anchors, (size_t)n_anchors * sizeof(ra_anchor_t), cudaMemcpyHostToDevice, ctx->stream));
