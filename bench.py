@@ -26,6 +26,9 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# two batches are in flight per GPU (PIPELINE_DEPTH contexts, 8 streams each): give every stream its own hardware queue
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+PIPELINE_DEPTH = int(os.environ.get("RA_BENCH_PIPELINE", 2))
 
 REF_BASES = 5_000_000
 MAX_CHUNKS = 8
@@ -251,7 +254,7 @@ def main():
         args.warmup = max(args.warmup, 3)
     config = {"workload": "C2: 5 Mb synthetic reference, simulated R9.4 reads, sparse border, banded=0.1",
               "reads_per_gpu": args.reads_per_gpu, "batch_note": "one batch ~ the reference's default mini-batch (-K 500M of signal, roptions.c:34)",
-              "max_chunks_per_read": MAX_CHUNKS, "chains_per_round": CHAINS_PER_ROUND,
+              "max_chunks_per_read": MAX_CHUNKS, "chains_per_round": CHAINS_PER_ROUND, "batches_in_flight_per_gpu": max(1, PIPELINE_DEPTH),
               "l2_policy": "inputs larger than L2 (signal batch >> 126 MB)"}
 
     if args.impl == "reference":
@@ -279,6 +282,16 @@ def main():
     # reference mirror: rank 0 loads, everyone else receives it by one NCCL broadcast
     from rawalign_b200.shard import broadcast_reference
     broadcast_reference(ctx, ref_arena if rank == 0 else None, rank, dev)
+    # software pipelining across steps: PIPELINE_DEPTH contexts on this GPU, each driven by its own host thread, so that one
+    # batch's uploads / latency-bound kernels overlap the other's issue-bound kernels (what a production map loop does with
+    # double-buffered batches).  Every step still does all of its work.
+    ctxs = [ctx]
+    for _ in range(1, max(1, PIPELINE_DEPTH)):
+        c2 = ra.Context(local)
+        c2.ref_alloc(len(ref_arena))
+        p_src, _n = ctx.ref_device(); p_dst, _n = c2.ref_device()
+        _dev_copy(torch, dev, p_dst, p_src, len(ref_arena))
+        ctxs.append(c2)
 
     n_chunks = len(coff)
     sig_pinned = torch.from_numpy(reads.sig).pin_memory()
@@ -290,9 +303,12 @@ def main():
     max_len = int(clen.max())
     torch.cuda.synchronize()
 
-    def k1_dev():
-        return ctx.detect_events_batch_dev(sig_d.data_ptr(), coff_d.data_ptr(), clen_d.data_ptr(), n_chunks, max_len,
-                                           ev_d.data_ptr(), ev_d.numel(), evoff_d.data_ptr())
+    ev_ds = [ev_d] + [torch.empty_like(ev_d) for _ in ctxs[1:]]
+    evoff_ds = [evoff_d] + [torch.empty_like(evoff_d) for _ in ctxs[1:]]
+
+    def k1_dev(w=0):
+        return ctxs[w].detect_events_batch_dev(sig_d.data_ptr(), coff_d.data_ptr(), clen_d.data_ptr(), n_chunks, max_len,
+                                               ev_ds[w].data_ptr(), ev_ds[w].numel(), evoff_ds[w].data_ptr())
     n_events = k1_dev()
     ev_off = evoff_d.cpu().numpy().view(np.uint64)
     ev_pos = ctx.last_event_positions(n_events)
@@ -308,25 +324,29 @@ def main():
     n_parts = int((chains["n_anchors"].astype(np.int64) - 1).sum())
     n_samples = int(clen.sum())
 
-    def k2_dev(count=False):
-        return ctx.align_chains_batch_dev(ev_d.data_ptr(), None, anchors_d.data_ptr(), len(anchors), chains_d.data_ptr(), len(chains), gfirst_d.data_ptr(),
-                                          n_groups, score_d.data_ptr(), keep_d.data_ptr(), min_score_mode=1, count_cells=count)
+    score_ds = [score_d] + [torch.empty_like(score_d) for _ in ctxs[1:]]
+    keep_ds = [keep_d] + [torch.empty_like(keep_d) for _ in ctxs[1:]]
+
+    def k2_dev(count=False, w=0):
+        return ctxs[w].align_chains_batch_dev(ev_ds[w].data_ptr(), None, anchors_d.data_ptr(), len(anchors), chains_d.data_ptr(), len(chains), gfirst_d.data_ptr(),
+                                              n_groups, score_ds[w].data_ptr(), keep_ds[w].data_ptr(), min_score_mode=1, count_cells=count)
     cells_issued, cells_useful = k2_dev(True)      # cell counting is instrumentation: one counted pass, timed passes run without it
     log(f"[rank {rank}] setup {time.time() - t_setup:.1f}s: reads={args.reads_per_gpu} chunks={n_chunks} samples={n_samples} "
         f"events={n_events} chains={len(chains)} groups={n_groups} sub-DTWs={n_parts} cells issued={cells_issued} useful={cells_useful}")
 
-    ev_host = torch.empty(ev_cap, dtype=torch.float32).pin_memory().numpy()
+    ev_hosts = [torch.empty(ev_cap, dtype=torch.float32).pin_memory().numpy() for _ in ctxs]
     raw_h = torch.from_numpy(reads.raw).pin_memory().numpy()
     raw_off = np.ascontiguousarray(reads.read_off[:-1]); raw_len = reads.read_len
     e2e_out = {}
 
-    def step_e2e():
+    def step_e2e(w=0):
         # int16 DAC samples (what a FAST5 holds) -> device in slices that overlap the kernels, decode + K1, events back to the
         # host (the map loop seeds from them), anchors/chains -> device, chain evaluation against the events that stayed on the
         # device, scores back
-        ev, off, lsig, first = ctx.detect_events_raw_batch(raw_h, raw_off, raw_len, reads.dac_offset, reads.dac_scale, 4000, MAX_CHUNKS, ev_host)
-        s, keep, _, _ = ctx.align_chains_batch(None, None, anchors_h, chains_h, min_score_mode=1, count_cells=False)
-        e2e_out["score"] = s; e2e_out["n_ev"] = len(ev); e2e_out["ev"] = ev
+        ev, off, lsig, first = ctxs[w].detect_events_raw_batch(raw_h, raw_off, raw_len, reads.dac_offset, reads.dac_scale, 4000, MAX_CHUNKS, ev_hosts[w])
+        s, keep, _, _ = ctxs[w].align_chains_batch(None, None, anchors_h, chains_h, min_score_mode=1, count_cells=False)
+        if w == 0:
+            e2e_out["score"] = s; e2e_out["n_ev"] = len(ev); e2e_out["ev"] = ev
 
     def barrier():
         torch.cuda.synchronize()
@@ -334,28 +354,53 @@ def main():
             dist.barrier()
             torch.cuda.synchronize()
 
+    def run_steps(step_fn, n_steps):
+        """n_steps steps dealt round-robin to the pipelines (one host thread per context); returns when all are done."""
+        if len(ctxs) == 1:
+            for _ in range(n_steps):
+                step_fn(0)
+            return
+        errs = []
+
+        def worker(w):
+            try:
+                for _ in range(w, n_steps, len(ctxs)):
+                    step_fn(w)
+            except Exception as e:      # noqa: BLE001
+                errs.append(e)
+        ths = [threading.Thread(target=worker, args=(w,)) for w in range(len(ctxs))]
+        for t in ths:
+            t.start()
+        for t in ths:
+            t.join()
+        if errs:
+            raise errs[0]
+
+    def step_dev(w=0):
+        k1_dev(w); k2_dev(False, w)
+
     # ---- device-resident timing ----
-    for _ in range(args.warmup):
-        k1_dev(); k2_dev()
+    run_steps(step_dev, max(args.warmup, len(ctxs)) * len(ctxs))
     barrier()
-    sampler = ClockSampler(local); sampler.start()
-    l0 = ctx.launch_count
-    t0 = time.perf_counter()
+    # per-stage device times: one un-pipelined step on context 0 (CUDA events on the library streams)
     ev_ms, dtw_ms, det_ms = [], [], []
-    for _ in range(args.steps):
-        k1_dev(); k2_dev()
+    for _ in range(3):
+        step_dev(0)
         tm = ctx.last_timing()
         det_ms.append(tm[0]); ev_ms.append(tm[1]); dtw_ms.append(tm[2])
     barrier()
+    sampler = ClockSampler(local); sampler.start()
+    l0 = sum(c.launch_count for c in ctxs)
+    t0 = time.perf_counter()
+    run_steps(step_dev, args.steps)
+    barrier()
     dt = time.perf_counter() - t0
-    launches = ctx.launch_count - l0
+    launches = sum(c.launch_count for c in ctxs) - l0
     # ---- end-to-end timing (host buffers, copies inside) ----
-    for _ in range(2):
-        step_e2e()
+    run_steps(step_e2e, 2 * len(ctxs))
     barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        step_e2e()
+    run_steps(step_e2e, args.steps)
     barrier()
     dt_e2e = time.perf_counter() - t0
     clocks = sampler.stop()            # sampled over both timed regions (device-resident and end-to-end)
@@ -416,10 +461,20 @@ def main():
             out["cpu_baseline"]["parity_bit_exact"] = bool(parity_check(ch_sub, anchors, ev_d, n_events, ref_arena, score_d, chains))
         sys.stdout.flush()
         os.write(json_fd, (json.dumps(out) + "\n").encode())
-    ctx.close()
+    for c in ctxs:
+        c.close()
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def _dev_copy(torch, dev, dst_ptr, src_ptr, n_floats):
+    """device-to-device copy between two raw float arenas (the contexts' reference mirrors)"""
+    class _V:
+        def __init__(self, p):
+            self.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (p, False), "version": 2}
+    torch.as_tensor(_V(dst_ptr), device=dev).copy_(torch.as_tensor(_V(src_ptr), device=dev))
+    torch.cuda.synchronize(dev)
 
 
 def parity_check(ch_sub, anchors, ev_d, n_events, ref_arena, score_d, chains):
