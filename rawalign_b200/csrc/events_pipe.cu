@@ -34,7 +34,12 @@ namespace evp {
 
 constexpr int kTile = 32;            // samples per tile per chunk
 constexpr int kRow = 36;             // shared-memory row stride (floats)
-constexpr int kStages = 4;
+constexpr int kStages = 4;          // prefix: input ring depth
+constexpr int kFsmStages = 3;       // state machine: ring depth per track
+// The lane-per-chunk kernels run kLaneWarps independent warps per CTA, one per SM sub-partition: a CTA's warp i is scheduled
+// on sub-partition i % 4, so single-warp CTAs would all pile onto sub-partition 0 (ncu: 2.4 warps on the busiest one with
+// two CTAs per SM).  Each warp has a private slice of the dynamic shared memory and synchronises only with itself.
+constexpr int kLaneWarps = 4;
 constexpr int kTsBlock = 256;
 constexpr int kHalo = 16;            // >= kPipeMaxWindow
 
@@ -77,18 +82,28 @@ __device__ __forceinline__ void load_tile(float *dst, const float *const *rowp, 
 // ---------------------------------------------------------------------------------------------------
 // k_prefix_pipe: psx[j] = ps[j+1], pssx[j] = pss[j+1] for j in [0, len)   (ps[0] = pss[0] = 0 is implicit)
 // ---------------------------------------------------------------------------------------------------
+struct __align__(16) PrefixSmem {
+	float in[kStages][32 * kRow];
+	float outs[32 * kRow];
+	float outq[32 * kRow];
+	const float *rowp[32];
+	uint32_t rowl[32];
+};
+
 template <bool CONTRACT>
-__global__ void __launch_bounds__(32)
+__global__ void __launch_bounds__(32 * kLaneWarps)
 k_prefix_pipe(const float *__restrict__ sig, const uint64_t *__restrict__ chunk_off, const uint32_t *__restrict__ chunk_len,
               uint32_t n_chunks, float *__restrict__ psx, float *__restrict__ pssx, uint32_t stride)
 {
-	__shared__ __align__(16) float in[kStages][32 * kRow];
-	__shared__ __align__(16) float outs[32 * kRow];
-	__shared__ __align__(16) float outq[32 * kRow];
-	__shared__ const float *rowp[32];
-	__shared__ uint32_t rowl[32];
-	const int lane = threadIdx.x;
-	const uint32_t c0 = blockIdx.x * 32u, c = c0 + (uint32_t)lane;
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	PrefixSmem &S = reinterpret_cast<PrefixSmem *>(smem_raw)[threadIdx.x >> 5];
+	float (*in)[32 * kRow] = S.in;
+	float *outs = S.outs, *outq = S.outq;
+	const float **rowp = S.rowp;
+	uint32_t *rowl = S.rowl;
+	const int lane = threadIdx.x & 31;
+	const uint32_t c0 = (blockIdx.x * (uint32_t)kLaneWarps + (threadIdx.x >> 5)) * 32u, c = c0 + (uint32_t)lane;
+	if (c0 >= n_chunks) return;                                       // whole warp; warps never synchronise with each other
 	const uint32_t my_len = c < n_chunks ? chunk_len[c] : 0u;
 	rowp[lane] = c < n_chunks ? sig + chunk_off[c] : sig;
 	rowl[lane] = my_len;
@@ -319,17 +334,28 @@ __device__ __forceinline__ void fsm_step(DetS &S, DetL &L, uint32_t i, float v1,
 	}
 }
 
-__global__ void __launch_bounds__(32)
+struct __align__(16) FsmSmem {
+	float s1[kFsmStages][32 * kRow];
+	float s2[kFsmStages][32 * kRow];
+	const float *rowp1[32];
+	const float *rowp2[32];
+	uint32_t rowl[32];
+};
+
+__global__ void __launch_bounds__(32 * kLaneWarps)
 k_fsm_pipe(const uint32_t *__restrict__ chunk_len, uint32_t n_chunks, const float *__restrict__ t1, const float *__restrict__ t2,
            uint32_t stride, EvParams prm, uint32_t *__restrict__ peaks_base, uint32_t peak_stride, uint32_t *__restrict__ n_peaks_out)
 {
-	__shared__ __align__(16) float s1[kStages][32 * kRow];
-	__shared__ __align__(16) float s2[kStages][32 * kRow];
-	__shared__ const float *rowp1[32];
-	__shared__ const float *rowp2[32];
-	__shared__ uint32_t rowl[32];
-	const int lane = threadIdx.x;
-	const uint32_t c0 = blockIdx.x * 32u, c = c0 + (uint32_t)lane;
+	extern __shared__ __align__(16) unsigned char smem_raw[];
+	FsmSmem &S = reinterpret_cast<FsmSmem *>(smem_raw)[threadIdx.x >> 5];
+	float (*s1)[32 * kRow] = S.s1;
+	float (*s2)[32 * kRow] = S.s2;
+	const float **rowp1 = S.rowp1, **rowp2 = S.rowp2;
+	uint32_t *rowl = S.rowl;
+	constexpr int kStages = kFsmStages;
+	const int lane = threadIdx.x & 31;
+	const uint32_t c0 = (blockIdx.x * (uint32_t)kLaneWarps + (threadIdx.x >> 5)) * 32u, c = c0 + (uint32_t)lane;
+	if (c0 >= n_chunks) return;                                       // whole warp; warps never synchronise with each other
 	const uint32_t my_len = c < n_chunks ? chunk_len[c] : 0u;
 	rowp1[lane] = t1 + (size_t)min(c, n_chunks - 1) * stride;
 	rowp2[lane] = t2 + (size_t)min(c, n_chunks - 1) * stride;
@@ -491,17 +517,28 @@ cudaError_t launch_events_pipe(const float *sig, const uint64_t *chunk_off, cons
 	float *t2 = t1 + (size_t)n_chunks * stride;
 	uint32_t *peaks = reinterpret_cast<uint32_t *>(t2 + (size_t)n_chunks * stride);
 	float *raw = reinterpret_cast<float *>(peaks + (size_t)n_chunks * pstride);
-	const uint32_t lane_ctas = (n_chunks + 31u) / 32u;
+	const uint32_t lane_ctas = (n_chunks + 32u * kLaneWarps - 1u) / (32u * kLaneWarps);
+	constexpr size_t kPrefixSmem = sizeof(PrefixSmem) * kLaneWarps, kFsmSmem = sizeof(FsmSmem) * kLaneWarps;
+	static unsigned long long attr_devices = 0;                       // > 48 KB of dynamic shared memory is opt-in, per function and device
+	int dev = 0;
+	cudaGetDevice(&dev);
+	if (!((attr_devices >> (dev & 63)) & 1ull)) {
+		cudaError_t ae = cudaFuncSetAttribute(k_prefix_pipe<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPrefixSmem);
+		if (ae == cudaSuccess) ae = cudaFuncSetAttribute(k_prefix_pipe<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPrefixSmem);
+		if (ae == cudaSuccess) ae = cudaFuncSetAttribute(k_fsm_pipe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFsmSmem);
+		if (ae != cudaSuccess) return ae;
+		__atomic_fetch_or(&attr_devices, 1ull << (dev & 63), __ATOMIC_RELAXED);   // idempotent, so a race between host threads is harmless
+	}
 	const dim3 tgrid((max_len + kTsBlock - 1) / kTsBlock, n_chunks);
 	const TsWin W1 = make_tswin(p.w1), W2 = make_tswin(p.w2);
 	if (contract) {
-		k_prefix_pipe<true><<<lane_ctas, 32, 0, s>>>(sig, chunk_off, chunk_len, n_chunks, psx, pssx, stride);
+		k_prefix_pipe<true><<<lane_ctas, 32 * kLaneWarps, kPrefixSmem, s>>>(sig, chunk_off, chunk_len, n_chunks, psx, pssx, stride);
 		k_tstat_pipe<true><<<tgrid, kTsThreads, 0, s>>>(chunk_len, psx, pssx, stride, t1, t2, p.w1, p.w2, W1, W2);
 	} else {
-		k_prefix_pipe<false><<<lane_ctas, 32, 0, s>>>(sig, chunk_off, chunk_len, n_chunks, psx, pssx, stride);
+		k_prefix_pipe<false><<<lane_ctas, 32 * kLaneWarps, kPrefixSmem, s>>>(sig, chunk_off, chunk_len, n_chunks, psx, pssx, stride);
 		k_tstat_pipe<false><<<tgrid, kTsThreads, 0, s>>>(chunk_len, psx, pssx, stride, t1, t2, p.w1, p.w2, W1, W2);
 	}
-	k_fsm_pipe<<<lane_ctas, 32, 0, s>>>(chunk_len, n_chunks, t1, t2, stride, p, peaks, pstride, n_ev);
+	k_fsm_pipe<<<lane_ctas, 32 * kLaneWarps, kFsmSmem, s>>>(chunk_len, n_chunks, t1, t2, stride, p, peaks, pstride, n_ev);
 	if (after_detect) cudaEventRecord(after_detect, s);
 	// CSR offsets continue from the previous launch group: when that group runs on another stream, only the scan waits for it
 	if (scan_wait) cudaStreamWaitEvent(s, scan_wait, 0);
