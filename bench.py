@@ -239,6 +239,31 @@ def subset_reads(n_sub, crid, coff, clen, anchors, chains):
 
 
 # ------------------------------------------------------------------------------------------------------
+def bind_to_gpu_numa_node(index):
+    """Pin this process to the CPUs NVML reports as local to GPU `index` (the cores of the socket / NUMA node its PCIe root
+    hangs off), BEFORE CUDA initialises and before any pinned buffer is allocated: pinned pages are placed on the node of
+    the allocating thread, and a host<->device copy whose pages sit on the other socket crosses the inter-socket link,
+    which eight ranks share.  Returns a short description for the JSON line; never fatal."""
+    if os.environ.get("RA_BENCH_NO_BIND"):
+        return "off (RA_BENCH_NO_BIND)"
+    try:
+        import pynvml as nv
+        nv.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        idx = int(vis.split(",")[index]) if vis and vis.split(",")[index].isdigit() else index
+        h = nv.nvmlDeviceGetHandleByIndex(idx)
+        n_cpu = os.cpu_count() or 64
+        words = nv.nvmlDeviceGetCpuAffinity(h, (n_cpu + 63) // 64)
+        cpus = {64 * w + b for w, m in enumerate(words) for b in range(64) if (int(m) >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return "unchanged (NVML reports no local CPUs within the allowed set)"
+        os.sched_setaffinity(0, cpus)
+        return f"gpu-local: {len(cpus)} of {n_cpu} cpus [{min(cpus)}..{max(cpus)}]"
+    except Exception as e:   # noqa: BLE001 -- a box without NVML affinity data still runs the bench
+        return f"unchanged ({type(e).__name__}: {e})"
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -265,6 +290,7 @@ def main():
     # exactly one line on stdout: anything a C library prints (e.g. the NCCL version banner) goes to stderr instead
     sys.stdout.flush()
     json_fd = os.dup(1); os.dup2(2, 1)
+    config["cpu_binding"] = bind_to_gpu_numa_node(local)
     import torch
     import torch.distributed as dist
     import rawalign_b200 as ra

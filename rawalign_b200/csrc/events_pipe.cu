@@ -40,7 +40,7 @@ constexpr int kFsmStages = 3;       // state machine: ring depth per track
 // on sub-partition i % 4, so single-warp CTAs would all pile onto sub-partition 0 (ncu: 2.4 warps on the busiest one with
 // two CTAs per SM).  Each warp has a private slice of the dynamic shared memory and synchronises only with itself.
 constexpr int kLaneWarps = 4;
-constexpr int kTsBlock = 256;
+constexpr int kTsBlock = 512;
 constexpr int kHalo = 16;            // >= kPipeMaxWindow
 
 __device__ __forceinline__ void cp_async16(float *smem_dst, const float *gsrc, int src_bytes)
@@ -217,60 +217,113 @@ __device__ __forceinline__ float tstat_from_means(float mean1, float mean2, floa
 	return __double2float_rn(__ddiv_rn((double)x, __dsqrt_rn((double)vw)));
 }
 
-// grid: x = tiles of kTsBlock positions, y = chunk.  kTsThreads = kTsBlock + 32: thread u owns position base + u for the
-// window means (the last 32 threads only serve the look-ahead of up to kPipeMaxWindow positions), threads < kTsBlock
-// then own one output position each.
-constexpr int kTsThreads = kTsBlock + 32;
+// The common case of tstat_from_means as straight-line code: the same operations in the same order, with every range
+// condition folded into one flag instead of a branch per operation.  ok == false means "take tstat_from_means".
+template <bool CONTRACT>
+__device__ __forceinline__ float tstat_fast(float mean1, float mean2, float e1, float e2, const TsWin W, bool &ok)
+{
+	float var;
+	if (CONTRACT) var = __fmaf_rn(-mean2, mean2, __fadd_rn(__fmaf_rn(-mean1, mean1, e1), e2));            // :61
+	else var = __fsub_rn(__fadd_rn(__fsub_rn(e1, __fmul_rn(mean1, mean1)), e2), __fmul_rn(mean2, mean2));
+	const bool clamped = !(var > FLT_MIN);                                                                  // :63
+	const float x = fabsf(__fsub_rn(mean2, mean1));                                                         // :68
+	const float q0 = __fmul_rn(var, W.rcp);                                                                 // fdiv_w(var)
+	const float vwf = __fmaf_rn(__fmaf_rn(-q0, W.wf, var), W.rcp, q0);
+	const float vs = clamped ? 1.0f : vwf;
+	float r0f;
+	asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r0f) : "f"(vs));
+	const double r0 = (double)r0f, vd = (double)vs;
+	const double e = __fma_rn(-__dmul_rn(vd, r0), r0, 1.0);
+	const double rn = __fma_rn(__dmul_rn(r0, 0.5), e, r0);
+	const double r1 = clamped ? W.rs_min : rn;
+	const double y = __dmul_rn((double)x, r1);
+	const uint32_t lo = (uint32_t)__double2loint(y);
+	const bool near_boundary = ((lo - (0x10000000u - 0x2000u)) & 0x1FFFFFFFu) < 0x4000u;
+	const bool in_range = clamped | ((var <= 1e30f) & (var >= 1e-30f) & (vwf >= 1e-30f) & (vwf <= 1e30f));
+	ok = in_range & (x <= 1e30f) & !near_boundary & ((y >= 1e-37) | (y == 0.0));
+	return __double2float_rn(y);
+}
+
+// grid: x = tiles of kTsBlock positions, y = chunk.  Thread u owns positions base + u + kTsThreads * e, e < kTsPer
+// (conflict-free shared memory, coalesced stores); the window means of a position are computed once and shared.
+constexpr int kTsThreads = 128;
+constexpr int kTsPer = kTsBlock / kTsThreads;
+constexpr int kTsLead = 20;          // floats staged before psx[base]: >= kPipeMaxWindow + 1, multiple of 4
+constexpr int kTsSp = kTsLead + kTsBlock + kHalo;           // ps[j] sits at index j - base + kTsLead - 1
+constexpr int kTsMeans = kTsBlock + kHalo;
+static_assert(kTsLead % 4 == 0 && kTsLead >= (int)kPipeMaxWindow + 1 && kHalo >= (int)kPipeMaxWindow && kHalo % 4 == 0 && kHalo <= kTsThreads, "t-stat tile");
 template <bool CONTRACT>
 __global__ void __launch_bounds__(kTsThreads)
 k_tstat_pipe(const uint32_t *__restrict__ chunk_len, const float *__restrict__ psx, const float *__restrict__ pssx, uint32_t stride,
              float *__restrict__ t1, float *__restrict__ t2, uint32_t w1, uint32_t w2, TsWin W1, TsWin W2)
 {
-	__shared__ float sp[kTsThreads + kHalo], sq[kTsThreads + kHalo];  // ps[j], pss[j] for j = base - kHalo + t
-	__shared__ float M1[kTsThreads], E1[kTsThreads], M2[kTsThreads], E2[kTsThreads];
+	__shared__ __align__(16) float sp[kTsSp], sq[kTsSp];
+	__shared__ float M1[kTsMeans], E1[kTsMeans], M2[kTsMeans], E2[kTsMeans];
 	const uint32_t c = blockIdx.y;
 	const uint32_t len = chunk_len[c];
 	const uint32_t base = blockIdx.x * kTsBlock;
 	if (base >= len) return;
 	const uint32_t u = threadIdx.x;
-	const float *__restrict__ prow = psx + (size_t)c * stride + base;  // prow[k] = ps[base + k + 1]
-	const float *__restrict__ qrow = pssx + (size_t)c * stride + base;
-	const uint32_t j = base + u;
 	{
-		const bool in = j >= 1u && j <= len;                         // ps[0] = pss[0] = +0.0f (:26-27)
-		sp[u + kHalo] = in ? __ldg(prow + (int)u - 1) : 0.0f;
-		sq[u + kHalo] = in ? __ldg(qrow + (int)u - 1) : 0.0f;
-		if (u < (uint32_t)kHalo) {
-			const bool inh = base + u >= (uint32_t)kHalo + 1u;       // jh = base - kHalo + u >= 1  (jh < base < len)
-			sp[u] = inh ? __ldg(prow + (int)u - kHalo - 1) : 0.0f;
-			sq[u] = inh ? __ldg(qrow + (int)u - kHalo - 1) : 0.0f;
+		// 16-byte pieces f of psx[base - kTsLead + 4f ...]; psx[-1] stands for ps[0] = +0.0f (:26-27), nothing before it is used.
+		// Pieces past the chunk's samples hold stale scratch (never consumed: every use below is guarded by len).
+		const float4 *__restrict__ prow = reinterpret_cast<const float4 *>(psx + (size_t)c * stride + base) - kTsLead / 4;
+		const float4 *__restrict__ qrow = reinterpret_cast<const float4 *>(pssx + (size_t)c * stride + base) - kTsLead / 4;
+		const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+		for (uint32_t f = u; f < (uint32_t)(kTsSp / 4); f += kTsThreads) {
+			const bool in = base != 0u || f >= (uint32_t)(kTsLead / 4);
+			reinterpret_cast<float4 *>(sp)[f] = in ? __ldg(prow + f) : z;
+			reinterpret_cast<float4 *>(sq)[f] = in ? __ldg(qrow + f) : z;
 		}
 	}
 	__syncthreads();
-	// window mean ending at j:  M(j) = (ps[j] - ps[j-w]) / w, j in [w, len].  At j == w the reference skips the
-	// subtraction (:53-56); ps[0] = +0.0f and x - 0.0f == x bit for bit.
-	if (j <= len) {
-		const float s0 = sp[u + kHalo], q0 = sq[u + kHalo];
-		if (j >= w1) {
-			M1[u] = fdiv_w(__fsub_rn(s0, sp[u + kHalo - w1]), W1.wf, W1.rcp);
-			E1[u] = fdiv_w(__fsub_rn(q0, sq[u + kHalo - w1]), W1.wf, W1.rcp);
+	// window mean ending at j = base + m:  M(j) = (ps[j] - ps[j-w]) / w, meaningful for j in [w, len].  At j == w the
+	// reference skips the subtraction (:53-56); ps[0] = +0.0f and x - 0.0f == x bit for bit.  Computed for every m
+	// (garbage in, garbage out where j is outside that range -- nothing reads those).
+	float m1o[kTsPer], e1o[kTsPer], m2o[kTsPer], e2o[kTsPer];
+	auto means = [&](uint32_t m, float &a1, float &b1, float &a2, float &b2) {
+		const uint32_t k = m + (uint32_t)(kTsLead - 1);
+		const float s0 = sp[k], q0 = sq[k];
+		const float x1 = __fsub_rn(s0, sp[k - w1]), y1 = __fsub_rn(q0, sq[k - w1]);
+		const float x2 = __fsub_rn(s0, sp[k - w2]), y2 = __fsub_rn(q0, sq[k - w2]);
+		const float f1 = __fmul_rn(x1, W1.rcp), g1 = __fmul_rn(y1, W1.rcp), f2 = __fmul_rn(x2, W2.rcp), g2 = __fmul_rn(y2, W2.rcp);
+		a1 = __fmaf_rn(__fmaf_rn(-f1, W1.wf, x1), W1.rcp, f1);
+		b1 = __fmaf_rn(__fmaf_rn(-g1, W1.wf, y1), W1.rcp, g1);
+		a2 = __fmaf_rn(__fmaf_rn(-f2, W2.wf, x2), W2.rcp, f2);
+		b2 = __fmaf_rn(__fmaf_rn(-g2, W2.wf, y2), W2.rcp, g2);
+		const float lo = fminf(fminf(fabsf(x1), fabsf(y1)), fminf(fabsf(x2), fabsf(y2)));
+		const float hi = fmaxf(fmaxf(fabsf(x1), fabsf(y1)), fmaxf(fabsf(x2), fabsf(y2)));
+		const uint32_t j = base + m;
+		if (!(lo >= 1e-30f && hi <= 1e30f) && j <= len) {             // rare: zeros, subnormals, huge or NaN sums -> IEEE division
+			if (j >= w1) { a1 = fdiv_w(x1, W1.wf, W1.rcp); b1 = fdiv_w(y1, W1.wf, W1.rcp); }
+			if (j >= w2) { a2 = fdiv_w(x2, W2.wf, W2.rcp); b2 = fdiv_w(y2, W2.wf, W2.rcp); }
 		}
-		if (j >= w2) {
-			M2[u] = fdiv_w(__fsub_rn(s0, sp[u + kHalo - w2]), W2.wf, W2.rcp);
-			E2[u] = fdiv_w(__fsub_rn(q0, sq[u + kHalo - w2]), W2.wf, W2.rcp);
-		}
-	}
+		M1[m] = a1; E1[m] = b1; M2[m] = a2; E2[m] = b2;
+	};
+#pragma unroll
+	for (int e = 0; e < kTsPer; ++e) means(u + (uint32_t)(kTsThreads * e), m1o[e], e1o[e], m2o[e], e2o[e]);
+	if (u < (uint32_t)kHalo) { float a, b, cc, d; means((uint32_t)kTsBlock + u, a, b, cc, d); }
 	__syncthreads();
-	if (u >= (uint32_t)kTsBlock || j >= len) return;
-	float v1 = 0.0f, v2 = 0.0f;
 	// :46, :50  valid iff w >= 2, len >= 2w, w <= p <= len - w   (one unsigned compare once len >= 2w)
-	if (w1 >= 2u && len >= 2u * w1 && j - w1 <= len - 2u * w1)
-		v1 = tstat_from_means<CONTRACT>(M1[u], M1[u + w1], E1[u], E1[u + w1], W1);
-	if (w2 >= 2u && len >= 2u * w2 && j - w2 <= len - 2u * w2)
-		v2 = tstat_from_means<CONTRACT>(M2[u], M2[u + w2], E2[u], E2[u + w2], W2);
-	const size_t o = (size_t)c * stride + j;
-	t1[o] = v1;
-	t2[o] = v2;
+	const bool any1 = w1 >= 2u && len >= 2u * w1, any2 = w2 >= 2u && len >= 2u * w2;
+	const uint32_t span1 = len - 2u * w1, span2 = len - 2u * w2;
+	float *__restrict__ o1 = t1 + (size_t)c * stride + base;
+	float *__restrict__ o2 = t2 + (size_t)c * stride + base;
+#pragma unroll
+	for (int e = 0; e < kTsPer; ++e) {
+		const uint32_t m = u + (uint32_t)(kTsThreads * e), p = base + m;
+		const bool valid1 = any1 && p - w1 <= span1, valid2 = any2 && p - w2 <= span2;
+		const float m1n = M1[m + w1], e1n = E1[m + w1], m2n = M2[m + w2], e2n = E2[m + w2];
+		bool ok1, ok2;
+		float v1 = tstat_fast<CONTRACT>(m1o[e], m1n, e1o[e], e1n, W1, ok1);
+		float v2 = tstat_fast<CONTRACT>(m2o[e], m2n, e2o[e], e2n, W2, ok2);
+		if (valid1 && !ok1) v1 = tstat_from_means<CONTRACT>(m1o[e], m1n, e1o[e], e1n, W1);
+		if (valid2 && !ok2) v2 = tstat_from_means<CONTRACT>(m2o[e], m2n, e2o[e], e2n, W2);
+		if (p < len) {
+			o1[m] = valid1 ? v1 : 0.0f;
+			o2[m] = valid2 ? v2 : 0.0f;
+		}
+	}
 }
 
 // ---------------------------------------------------------------------------------------------------
