@@ -34,8 +34,14 @@ namespace evp {
 
 constexpr int kTile = 32;            // samples per tile per chunk
 constexpr int kRow = 36;             // shared-memory row stride (floats)
-constexpr int kStages = 4;          // prefix: input ring depth
-constexpr int kFsmStages = 3;       // state machine: ring depth per track
+#ifndef RA_PREFIX_STAGES
+#define RA_PREFIX_STAGES 2
+#endif
+#ifndef RA_FSM_STAGES
+#define RA_FSM_STAGES 2
+#endif
+constexpr int kStages = RA_PREFIX_STAGES;      // prefix: input ring depth
+constexpr int kFsmStages = RA_FSM_STAGES;     // state machine: ring depth per track
 // The lane-per-chunk kernels run kLaneWarps independent warps per CTA, one per SM sub-partition: a CTA's warp i is scheduled
 // on sub-partition i % 4, so single-warp CTAs would all pile onto sub-partition 0 (ncu: 2.4 warps on the busiest one with
 // two CTAs per SM).  Each warp has a private slice of the dynamic shared memory and synchronises only with itself.
@@ -217,6 +223,15 @@ __device__ __forceinline__ float tstat_from_means(float mean1, float mean2, floa
 	return __double2float_rn(__ddiv_rn((double)x, __dsqrt_rn((double)vw)));
 }
 
+// out-of-line copies for the rare cases of k_tstat_pipe (keeps its hot loop compact)
+template <bool CONTRACT>
+__device__ __noinline__ float tstat_exact(float mean1, float mean2, float e1, float e2, float wf, float rcp, float vw_min, double rs_min)
+{
+	const TsWin W = { wf, rcp, vw_min, rs_min };
+	return tstat_from_means<CONTRACT>(mean1, mean2, e1, e2, W);
+}
+__device__ __noinline__ float fdiv_w_exact(float x, float wf, float rcp) { return fdiv_w(x, wf, rcp); }
+
 // The common case of tstat_from_means as straight-line code: the same operations in the same order, with every range
 // condition folded into one flag instead of a branch per operation.  ok == false means "take tstat_from_means".
 template <bool CONTRACT>
@@ -295,8 +310,8 @@ k_tstat_pipe(const uint32_t *__restrict__ chunk_len, const float *__restrict__ p
 		const float hi = fmaxf(fmaxf(fabsf(x1), fabsf(y1)), fmaxf(fabsf(x2), fabsf(y2)));
 		const uint32_t j = base + m;
 		if (!(lo >= 1e-30f && hi <= 1e30f) && j <= len) {             // rare: zeros, subnormals, huge or NaN sums -> IEEE division
-			if (j >= w1) { a1 = fdiv_w(x1, W1.wf, W1.rcp); b1 = fdiv_w(y1, W1.wf, W1.rcp); }
-			if (j >= w2) { a2 = fdiv_w(x2, W2.wf, W2.rcp); b2 = fdiv_w(y2, W2.wf, W2.rcp); }
+			if (j >= w1) { a1 = fdiv_w_exact(x1, W1.wf, W1.rcp); b1 = fdiv_w_exact(y1, W1.wf, W1.rcp); }
+			if (j >= w2) { a2 = fdiv_w_exact(x2, W2.wf, W2.rcp); b2 = fdiv_w_exact(y2, W2.wf, W2.rcp); }
 		}
 		M1[m] = a1; E1[m] = b1; M2[m] = a2; E2[m] = b2;
 	};
@@ -317,8 +332,8 @@ k_tstat_pipe(const uint32_t *__restrict__ chunk_len, const float *__restrict__ p
 		bool ok1, ok2;
 		float v1 = tstat_fast<CONTRACT>(m1o[e], m1n, e1o[e], e1n, W1, ok1);
 		float v2 = tstat_fast<CONTRACT>(m2o[e], m2n, e2o[e], e2n, W2, ok2);
-		if (valid1 && !ok1) v1 = tstat_from_means<CONTRACT>(m1o[e], m1n, e1o[e], e1n, W1);
-		if (valid2 && !ok2) v2 = tstat_from_means<CONTRACT>(m2o[e], m2n, e2o[e], e2n, W2);
+		if (valid1 && !ok1) v1 = tstat_exact<CONTRACT>(m1o[e], m1n, e1o[e], e1n, W1.wf, W1.rcp, W1.vw_min, W1.rs_min);
+		if (valid2 && !ok2) v2 = tstat_exact<CONTRACT>(m2o[e], m2n, e2o[e], e2n, W2.wf, W2.rcp, W2.vw_min, W2.rs_min);
 		if (p < len) {
 			o1[m] = valid1 ? v1 : 0.0f;
 			o2[m] = valid2 ? v2 : 0.0f;
