@@ -304,7 +304,8 @@ def main():
     t_setup = time.time()
     ref_seq, ref_arena = build_reference()
     reads, coff, clen, crid = build_reads(ref_seq, args.reads_per_gpu, seed=2 + rank)
-    ctx = ra.Context(local)
+    hook_opt = ra.ri_mapopt_init(); hook_opt.reserved = int(os.environ.get("RA_BENCH_RESERVED", "0"))   # A/B of kernel variants (test hooks)
+    ctx = ra.Context(local, hook_opt)
     # reference mirror: rank 0 loads, everyone else receives it by one NCCL broadcast
     from rawalign_b200.shard import broadcast_reference
     broadcast_reference(ctx, ref_arena if rank == 0 else None, rank, dev)
@@ -313,7 +314,7 @@ def main():
     # double-buffered batches).  Every step still does all of its work.
     ctxs = [ctx]
     for _ in range(1, max(1, PIPELINE_DEPTH)):
-        c2 = ra.Context(local)
+        c2 = ra.Context(local, hook_opt)
         c2.ref_alloc(len(ref_arena))
         p_src, _n = ctx.ref_device(); p_dst, _n = c2.ref_device()
         _dev_copy(torch, dev, p_dst, p_src, len(ref_arena))

@@ -101,11 +101,12 @@ struct ra_ctx {
 	DevBuf a_arena, b_arena, items, cost, counter, ring, order;
 	// chains
 	DevBuf anchors, chains, group_first, min_score, score, keep, cells, chain_ring;
-	DevBuf sp_nparts, sp_ntiles, sp_pbase, sp_tbase, sp_tchain, sp_cost, sp_pcells, sp_best;   // sparse-border plan (chains_sparse.cu)
+	DevBuf sp_nparts, sp_ntiles, sp_pbase, sp_tbase, sp_tchain, sp_cost, sp_pcells, sp_best, sp_rest;   // sparse-border plan (chains_sparse.cu)
 	uint64_t resident_events = 0;      // events left on the device by the last ra_detect_events_batch
 	bool force_unfused_events = false; // test hook: run the five-kernel K1 v2 (also the path for windows > kFusedMaxWindow)
 	bool force_fused_events = false;   // test hook: run the single-pass K1 v3
 	bool force_generic_dtw = false;    // test hook (reserved bit 2): every item through the generic shared-memory DTW kernel
+	bool legacy_sparse_tiles = false;  // test hook (reserved bit 3): sparse parts through the CTA-wide tiles of k_sp_parts instead of k_sp_parts2
 	bool want_ev_pos = true;           // keep the event start samples of the last K1 call (ra_last_event_positions)
 	// traceback
 	DevBuf dirs, dir_off, slot_off, slot_i, slot_j, slot_d, path_len, path_off, out_i, out_j, out_d;
@@ -393,7 +394,8 @@ int sparse_pipeline(ra_ctx *ctx, const ra::ChainLaunch &L, uint32_t n_chains, ui
 {
 	int rc;
 	if (n_chains == 0) return RA_OK;
-	const uint64_t part_cap = n_anchors + 1, tile_cap = n_anchors / ra::kSparseTileParts + n_chains + 1;
+	const uint32_t tile_parts = ctx->legacy_sparse_tiles ? ra::kSparseTileParts : ra::kSparseTileParts2;
+	const uint64_t part_cap = n_anchors + 1, tile_cap = n_anchors / tile_parts + n_chains + 1;
 	if (tile_cap >= 0xffffffffull) return fail(RA_EINVAL, "too many part tiles in one batch (%llu)", (unsigned long long)tile_cap);
 	if ((rc = ctx->sp_nparts.reserve((size_t)n_chains * 4))) return rc;
 	if ((rc = ctx->sp_pbase.reserve((size_t)n_chains * 8))) return rc;
@@ -403,6 +405,7 @@ int sparse_pipeline(ra_ctx *ctx, const ra::ChainLaunch &L, uint32_t n_chains, ui
 	if ((rc = ctx->sp_cost.reserve((size_t)part_cap * 4))) return rc;
 	if (L.cells && (rc = ctx->sp_pcells.reserve((size_t)part_cap * 4))) return rc;
 	if ((rc = ctx->sp_ntiles.reserve(64))) return rc;
+	if (!ctx->legacy_sparse_tiles && (rc = ctx->sp_rest.reserve((size_t)part_cap * 8))) return rc;
 	if (reset_counters) {
 		if (L.cells) RA_CUDA(cudaMemsetAsync(L.cells, 0, 2 * sizeof(uint64_t), ctx->stream));
 		RA_CUDA(cudaMemsetAsync(L.need_cap, 0, sizeof(uint32_t), ctx->stream));
@@ -414,6 +417,7 @@ int sparse_pipeline(ra_ctx *ctx, const ra::ChainLaunch &L, uint32_t n_chains, ui
 	P.totals = ctx->sp_ntiles.as<unsigned long long>();
 	P.part_cost = ctx->sp_cost.as<float>(); P.part_cells = L.cells ? ctx->sp_pcells.as<uint32_t>() : nullptr;
 	P.best = ctx->sp_best.as<float>();
+	P.tile_parts = tile_parts; P.rest = ctx->legacy_sparse_tiles ? nullptr : ctx->sp_rest.as<uint64_t>();
 	const int first = (L.min_score_mode == 1) ? 1 : 0, last = (L.min_score_mode == 1) ? 2 : 0;
 	for (int phase = first; phase <= last; ++phase) {
 		RA_CUDA(ra::launch_sparse_prep(L, P, phase, ctx->stream));
@@ -545,7 +549,7 @@ void ra_destroy(ra_ctx *ctx)
 	cudaSetDevice(ctx->device);
 	cudaStreamSynchronize(ctx->stream);
 	DevBuf *bufs[] = { &ctx->ref, &ctx->sig, &ctx->chunk_off, &ctx->chunk_len, &ctx->raw, &ctx->nev, &ctx->ev_pos, &ctx->ev_off,
-	                   &ctx->ev_out, &ctx->a_arena, &ctx->b_arena, &ctx->items, &ctx->cost, &ctx->counter, &ctx->ring, &ctx->order, &ctx->anchors, &ctx->chains, &ctx->group_first, &ctx->min_score, &ctx->score, &ctx->keep, &ctx->cells, &ctx->chain_ring, &ctx->sp_nparts, &ctx->sp_ntiles, &ctx->sp_pbase, &ctx->sp_tbase, &ctx->sp_tchain, &ctx->sp_cost, &ctx->sp_pcells, &ctx->sp_best,
+	                   &ctx->ev_out, &ctx->a_arena, &ctx->b_arena, &ctx->items, &ctx->cost, &ctx->counter, &ctx->ring, &ctx->order, &ctx->anchors, &ctx->chains, &ctx->group_first, &ctx->min_score, &ctx->score, &ctx->keep, &ctx->cells, &ctx->chain_ring, &ctx->sp_nparts, &ctx->sp_ntiles, &ctx->sp_pbase, &ctx->sp_tbase, &ctx->sp_tchain, &ctx->sp_cost, &ctx->sp_pcells, &ctx->sp_best, &ctx->sp_rest,
 	                   &ctx->dirs, &ctx->dir_off, &ctx->slot_off, &ctx->slot_i, &ctx->slot_j, &ctx->slot_d, &ctx->path_len,
 	                   &ctx->path_off, &ctx->out_i, &ctx->out_j, &ctx->out_d };
 	for (DevBuf *b : bufs) b->release();
@@ -576,6 +580,7 @@ int ra_set_opt(ra_ctx *ctx, const ra_mapopt_t *opt)
 	ctx->force_unfused_events = (opt->reserved & 1u) != 0;
 	ctx->force_fused_events = (opt->reserved & 2u) != 0;
 	ctx->force_generic_dtw = (opt->reserved & 4u) != 0;
+	ctx->legacy_sparse_tiles = (opt->reserved & 8u) != 0;
 	return RA_OK;
 }
 

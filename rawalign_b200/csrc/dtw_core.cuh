@@ -212,9 +212,14 @@ __device__ __forceinline__ float thread_dtw_narrow(const LA A, int n, const LB B
 // the centre staircase (c, r(c)) is always connected, dp(n-1, m-1) is bit-identical to the reference's
 // (whose out-of-band value is 1e10f) -- asserted against the oracle in tests/test_gpu_parity.py.
 // ---------------------------------------------------------------------------------------------------
-template <int RP, bool COUNT, class LA, class LB>
-__device__ __forceinline__ float thread_dtw_diag(const LA A, int n, const LB B, int m, uint32_t *cells)
+//
+// MIXED (RP == 2 only): lanes whose problem has R' = 1 run the same code with `r1` set.  The R' = 1 cell set is the R' = 2
+// set without the two outer cells of every primary diagonal (same secondaries, same centre cell), so forcing those two
+// values to kInf -- what the reference holds for an out-of-set cell -- evaluates the R' = 1 problem exactly.
+template <int RP, bool COUNT, bool MIXED = false, class LA, class LB>
+__device__ __forceinline__ float thread_dtw_diag(const LA A, int n, const LB B, int m, uint32_t *cells, bool r1 = false)
 {
+	static_assert(!MIXED || RP == 2, "MIXED is the R' = 1 inside R' = 2 embedding");
 	constexpr bool ODD = (RP & 1) != 0;
 	constexpr int h = ODD ? (RP - 1) / 2 : RP / 2;
 	constexpr int NP = 2 * h + 1;                 // primary length (odd)
@@ -236,16 +241,16 @@ __device__ __forceinline__ float thread_dtw_diag(const LA A, int n, const LB B, 
 #pragma unroll 1
 	for (int c = 0; c < n; ++c) {
 		bool inc = false;
-		if (c > 0) {
-			e += m; if (e >= n) { e -= n; ++r; inc = true; }          // dtw.cpp:352-359
+		if (c > 0) {                                                  // same for every lane that is still running
+			e += m; inc = e >= n; e -= inc ? n : 0; r += inc ? 1 : 0;  // dtw.cpp:352-359
 #pragma unroll
 			for (int u = 0; u < NW - 1; ++u) aw[u] = aw[u + 1];
 			aw[NW - 1] = (c + h < n) ? A[c + h] : SA;
-			if (inc) {
+			// lanes differ in inc at every column: the B window moves by selects, not by a branch
+			const float bnew = (r + h < m) ? B[min(r + h, m - 1)] : SB;
 #pragma unroll
-				for (int u = 0; u < NW - 1; ++u) bw[u] = bw[u + 1];
-				bw[NW - 1] = (r + h < m) ? B[r + h] : SB;
-			}
+			for (int u = 0; u < NW - 1; ++u) bw[u] = inc ? bw[u + 1] : bw[u];
+			bw[NW - 1] = inc ? bnew : bw[NW - 1];
 		}
 		// ---- secondary diagonal S(c), only meaningful when inc ----
 		float s[NS > 0 ? NS : 1];
@@ -275,6 +280,7 @@ __device__ __forceinline__ float thread_dtw_diag(const LA A, int n, const LB B, 
 			const float na = pold[t], nb = (t + 1 <= 2 * h) ? pold[t + 1] : kInf, ntl = xq[t + 1];
 			const float pa = inc ? sa : na, pb = inc ? sb : nb, tl = inc ? pold[t] : ntl;
 			pnew[t] = fminf(fminf(pa, pb), tl) + fabsf(aw[t + 1] - bw[2 * h + 1 - t]);
+			if (MIXED && t != h) pnew[t] = r1 ? kInf : pnew[t];
 		}
 		// ---- the d-2 diagonal of the next column, anchored at i = c-h-1 ----
 #pragma unroll
@@ -289,7 +295,8 @@ __device__ __forceinline__ float thread_dtw_diag(const LA A, int n, const LB B, 
 		for (int t = 0; t < NP; ++t) pold[t] = pnew[t];
 		if (COUNT) {
 			// cells of P(c) and S(c) inside the matrix (dtw.cpp:365-366, :419-420)
-			const int klo = max(max(-h, -c), r - (m - 1)), khi = min(min(h, n - 1 - c), r);
+			const int hh = (MIXED && r1) ? 0 : h;
+			const int klo = max(max(-hh, -c), r - (m - 1)), khi = min(min(hh, n - 1 - c), r);
 			cnt += (uint32_t)max(0, khi - klo + 1);
 			if (inc) {
 				// S(c): (c+k, r-1-k), k in [-NS/2, NS/2-1]

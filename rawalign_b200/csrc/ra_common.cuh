@@ -110,14 +110,18 @@ struct SparsePlan {
 	uint32_t *n_parts;               // per chain: parts evaluated in this phase (0 = chain inactive)
 	uint64_t *part_base;             // per chain: first slot of its parts in part_cost / part_cells
 	uint32_t *tile_chain, *tile_t0;  // per tile: chain and first part
-	unsigned long long *totals;      // [0] parts, [1] tiles allocated so far in this phase (device counters)
+	unsigned long long *totals;      // [0] parts, [1] tiles allocated so far in this phase, [2] parts deferred to k_sp_rest (device counters)
 	float *part_cost;                // per evaluated part, at part_base[chain] + p
 	uint32_t *part_cells;
 	float *best;                     // per group: best score after phase A
+	uint32_t tile_parts;             // parts per tile: kSparseTileParts2 (warp tiles, default) or kSparseTileParts (CTA tiles, test hook)
+	uint64_t *rest;                  // chain << 32 | part of the parts deferred to k_sp_rest, counted in totals[2]; may be null
 };
 constexpr int kSparseCtasPerSm = 6;
+constexpr int kSparse2CtasPerSm = 4;
 constexpr int kSparseTileParts = 256;
-constexpr int kSparseKernelsPerPhase = 3;   // prep, parts, replay
+constexpr int kSparseTileParts2 = 128;
+constexpr int kSparseKernelsPerPhase = 4;   // prep, parts, rest, replay
 // phase 0: min_score_mode 0; 1 / 2: first chain of every group / the remaining chains (min_score_mode 1)
 cudaError_t launch_sparse_prep(const ChainLaunch &L, const SparsePlan &P, int phase, cudaStream_t s);
 cudaError_t launch_sparse_eval(const ChainLaunch &L, const SparsePlan &P, int phase, int n_sm, cudaStream_t s);

@@ -302,6 +302,39 @@ def test_align_chains_batch_vs_oracle(ctx, oracle, border, fill):
         assert dropped > 0, "the early-termination replay was never exercised"
 
 
+@pytest.mark.parametrize("legacy", [0, 1])       # 0: warp tiles (k_sp_parts2 + k_sp_rest), 1: CTA tiles (k_sp_parts)
+@pytest.mark.parametrize("gap_p,frac", [(0.2, 0.10), (0.05, 0.10), (0.02, 0.25), (0.004, 0.10)])
+def test_sparse_chain_part_shapes_vs_oracle(oracle, legacy, gap_p, frac):
+    """Sparse-border chains whose parts are tiny (R' = 1 / 2: the register evaluator), medium (other narrow parts: full
+    rounds in the tile and the deferred remainder), wide, and larger than a warp's staging window (gap_p 0.004: parts of
+    hundreds of events, some beyond 1024) -- every class of k_sp_parts2, bit for bit against the oracle."""
+    import rawalign_b200 as ra
+    from rawalign_b200 import synth
+    from oracle import DtwOpt
+    rng = np.random.default_rng(int(1000 * gap_p) + 7)
+    n_reads = 12
+    n_ev = rng.integers(600, 5000, n_reads)
+    ev_off = np.concatenate(([0], np.cumsum(n_ev)))
+    read = rng.normal(0, 1, int(ev_off[-1])).astype(np.float32)
+    ref = rng.normal(0, 1, 120_000).astype(np.float32)
+    anchors, chains = synth.synth_chains(n_ev, ev_off[:-1], len(ref), seed=11, chains_per_read=3, gap_p=gap_p)
+    opt = ra.ri_mapopt_init(); opt.dtw_band_radius_frac = frac; opt.reserved = 8 * legacy; opt.dtw_min_score = -1e9
+    c = ra.Context(0, opt)
+    try:
+        ms = np.full(len(chains), -1e10, np.float32)                       # no early termination: every part is evaluated
+        score, keep, issued, useful = c.align_chains_batch(read, ref, anchors, chains, min_score_mode=0, min_score=ms)
+    finally:
+        c.close()
+    oo = DtwOpt(1, 1, frac, 0.4, -1e9)
+    tot = 0
+    for k, ch in enumerate(chains):
+        a = anchors[int(ch["anchor_off"]):int(ch["anchor_off"]) + int(ch["n_anchors"])]
+        sc, cells = oracle.align_chain(a, read[int(ch["read_off"]):], ref, oo, min_score=-1e10, score_fma=1, return_cells=True)
+        tot += cells
+        assert bits(score[k]) == bits(sc), (k, score[k], sc)
+    assert useful == tot and issued == tot
+
+
 def test_align_chain_cigar_vs_oracle(ctx, oracle):
     import rawalign_b200 as ra
     read, ref, anchors, chains = _workload(n_reads=6, seed=43)
