@@ -216,6 +216,10 @@ __device__ __forceinline__ float thread_dtw_narrow(const LA A, int n, const LB B
 // MIXED (RP == 2 only): lanes whose problem has R' = 1 run the same code with `r1` set.  The R' = 1 cell set is the R' = 2
 // set without the two outer cells of every primary diagonal (same secondaries, same centre cell), so forcing those two
 // values to kInf -- what the reference holds for an out-of-set cell -- evaluates the R' = 1 problem exactly.
+#ifndef RA_DIAG_UNROLL
+#define RA_DIAG_UNROLL 2
+#endif
+constexpr int kDiagUnroll = RA_DIAG_UNROLL;
 template <int RP, bool COUNT, bool MIXED = false, class LA, class LB>
 __device__ __forceinline__ float thread_dtw_diag(const LA A, int n, const LB B, int m, uint32_t *cells, bool r1 = false)
 {
@@ -238,7 +242,7 @@ __device__ __forceinline__ float thread_dtw_diag(const LA A, int n, const LB B, 
 	}
 	int r = 0, e = 0;
 	uint32_t cnt = 0;
-#pragma unroll 1
+#pragma unroll kDiagUnroll
 	for (int c = 0; c < n; ++c) {
 		bool inc = false;
 		if (c > 0) {                                                  // same for every lane that is still running
