@@ -29,6 +29,10 @@ sys.path.insert(0, ROOT)
 # two batches are in flight per GPU (PIPELINE_DEPTH contexts, 8 streams each): give every stream its own hardware queue
 os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 PIPELINE_DEPTH = int(os.environ.get("RA_BENCH_PIPELINE", 2))
+# measured with ncu on this build (profiles/r01_ncu_full_v5_k1.ncu-rep, profiles/r01_k1_v5_summary.md): DRAM bytes and warp
+# instructions of the K1 kernels per signal sample
+K1_DRAM_BYTES_PER_SAMPLE = 38.98
+K1_WARP_INSTR_PER_SAMPLE = 10.64
 
 REF_BASES = 5_000_000
 MAX_CHUNKS = 8
@@ -467,11 +471,19 @@ def main():
                     "events_equal_resident_path": bool(e2e_out["n_ev"] == n_events and np.array_equal(e2e_out["ev"][:4096], ev_d[:4096].cpu().numpy()))},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"kernel": "K1 event detection (k_prefix_pipe + k_tstat_pipe + k_fsm_pipe + k_exclusive_scan_u32 + k_finish_pipe)", "bound": "hbm",
-                         "achieved": k1_bytes / (k1_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": k1_bytes / (k1_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None, "peak_source": peak_src,
-                         "algorithmic_bytes": "4 B/sample in + 4 B/event out + 20 B/chunk of tables"},
-            "roofline_dtw": {"kernel": "sparse chain DTW (k_sp_prep + k_sp_parts + k_sp_replay, two phases)", "bound": "alu", "achieved": cells_issued / (k2_ms * 1e-3) / 1e9, "peak": alu_peak_gcups,
+            "roofline": {"kernel": "K1 event detection (k_prefix_pipe + k_tstat_pipe + k_fsm_pipe + k_exclusive_scan_u32 + k_finish_pipe, four chunk groups on concurrent streams)",
+                         "bound": "hbm", "achieved": k1_bytes / (k1_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": k1_bytes / (k1_ms * 1e-3) / 1e9 / hbm_peak,
+                         "traffic": int(K1_DRAM_BYTES_PER_SAMPLE * n_samples), "peak_source": peak_src,
+                         "algorithmic_bytes": "4 B/sample in + 4 B/event out + 20 B/chunk of tables, per step like achieved / traffic",
+                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of the four K1 kernels, ncu --set full of this build "
+                                           "(profiles/r01_ncu_full_v5_k1.ncu-rep): 38.98 B/sample = 4 B signal + the fp32 prefix sums and the two "
+                                           "t-stat tracks written once and read once (32 B) + the prefix sums re-read at the peaks; the stages are "
+                                           "separate kernels, so the intermediates cross HBM -- no stage re-reads its input",
+                         "note": "K1 is issue-bound, not HBM-bound: ~10.6 warp instructions per sample (ncu) at "
+                                 f"{K1_WARP_INSTR_PER_SAMPLE * n_samples / (k1_ms * 1e-3) / (148 * 4 * clocks.get('sm_mhz', 1965.0) * 1e6):.2f} of the SM issue rate"},
+            "roofline_dtw": {"kernel": "sparse chain DTW (k_sp_prep + k_sp_parts2 + k_sp_rest + k_sp_replay, two phases)", "bound": "alu",
+                             "achieved": cells_issued / (k2_ms * 1e-3) / 1e9, "peak": alu_peak_gcups,
                              "unit": "GCUPS", "frac": cells_issued / (k2_ms * 1e-3) / 1e9 / alu_peak_gcups,
                              "peak_source": "148 SMs x 128 fp32 lanes x 1.965 GHz / 4 lane-ops per cell (SURVEY 8d)"},
         }

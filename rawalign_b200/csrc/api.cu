@@ -38,7 +38,9 @@ int fail(int code, const char *fmt, ...)
 	} while (0)
 
 constexpr int kMaxSlices = 8;
-constexpr int kSliceStreams = 4;      // with compute, h2d, d2h and aux: 8 streams = the default number of hardware queues (no false dependencies)         // host<->device copies of the e2e entry points are cut into slices that overlap the kernels
+constexpr int kCopySliceStreams = 4;  // streams the sliced host<->device entry points spread their slices over
+constexpr int kSliceStreams = 8;      // chunk groups of the resident K1 (hosts should export CUDA_DEVICE_MAX_CONNECTIONS=32: more streams than hardware queues means false dependencies)
+// host<->device copies of the e2e entry points are cut into slices that overlap the kernels
 
 // grow-only device buffer
 struct DevBuf {
@@ -83,6 +85,9 @@ struct ra_ctx {
 	int n_sm = 0;
 	cudaStream_t stream = nullptr;       // compute
 	cudaStream_t h2d = nullptr, d2h = nullptr, aux = nullptr;   // copy engines and the decode kernel of the sliced e2e entry points
+	cudaStream_t slice_hi[kSliceStreams] = {};                    // high-priority twins for the latency-bound K1 kernels (RA_K1_PRIO)
+	cudaEvent_t split_ev[kSliceStreams][4] = {};
+	int k1_groups = 8; bool k1_prio = true;                       // A/B on one box (profiles/r01_ab_k1_groups_prio.txt); RA_K1_GROUPS / RA_K1_PRIO override
 	cudaStream_t slice_stream[kSliceStreams] = {};                // K1 of different slices runs concurrently (each slice is latency-bound)
 	cudaEvent_t slice_in[kMaxSlices] = {}, slice_done[kMaxSlices] = {}, slice_dec[kMaxSlices] = {}, slice_scan[kMaxSlices] = {};
 	bool slices_concurrent = false;
@@ -192,18 +197,20 @@ int events_dev(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_dev,
 		if ((rc = ctx->nev.reserve((size_t)n_chunks * sizeof(uint32_t)))) return rc;
 		if ((rc = ctx->ev_pos.reserve((size_t)std::max<uint64_t>(ev_cap, 1) * sizeof(uint32_t)))) return rc;
 		RA_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
-		for (int k = 0; k < kSliceStreams; ++k) {
-			const uint32_t c0 = (uint32_t)((uint64_t)n_chunks * k / kSliceStreams), c1 = (uint32_t)((uint64_t)n_chunks * (k + 1) / kSliceStreams);
+		const int G = ctx->k1_groups;
+		for (int k = 0; k < G; ++k) {
+			const uint32_t c0 = (uint32_t)((uint64_t)n_chunks * k / G), c1 = (uint32_t)((uint64_t)n_chunks * (k + 1) / G);
 			cudaStream_t s = ctx->slice_stream[k];
 			RA_CUDA(cudaStreamWaitEvent(s, ctx->ev[0], 0));
+			ra::PipeSplit sp = { ctx->slice_hi[k], { ctx->split_ev[k][0], ctx->split_ev[k][1], ctx->split_ev[k][2], ctx->split_ev[k][3] } };
 			RA_CUDA(ra::launch_events_pipe(sig_dev, chunk_off_dev + c0, chunk_len_dev + c0, c1 - c0, max_chunk_len, p, (int)o.fp_contract,
 			                               ctx->raw.as<float>() + (size_t)c0 * fpc, ctx->nev.as<uint32_t>() + c0, ev_off_dev + c0, k != 0, ev_out_dev, ev_cap,
 			                               ctx->want_ev_pos ? ctx->ev_pos.as<uint32_t>() : nullptr, s, nullptr,
-			                               k ? ctx->slice_scan[k - 1] : nullptr, ctx->slice_scan[k]));
+			                               k ? ctx->slice_scan[k - 1] : nullptr, ctx->slice_scan[k], ctx->k1_prio ? &sp : nullptr));
 			ctx->launches += ra::kPipeEventKernels;
 			RA_CUDA(cudaEventRecord(ctx->slice_done[k], s));
 		}
-		for (int k = 0; k < kSliceStreams; ++k) RA_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->slice_done[k], 0));
+		for (int k = 0; k < G; ++k) RA_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->slice_done[k], 0));
 		RA_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
 		RA_CUDA(cudaEventRecord(ctx->ev[2], ctx->stream));
 		ctx->timed_k1 = true;
@@ -268,7 +275,7 @@ void trace_events_init()
 int slice_launch_concurrent(ra_ctx *ctx, const float *sig_dev, int k, uint32_t c0, uint32_t n, uint32_t max_len, uint64_t dev_cap)
 {
 	const ra_mapopt_t &o = ctx->opt;
-	cudaStream_t s = ctx->slice_stream[k % kSliceStreams];
+	cudaStream_t s = ctx->slice_stream[k % kCopySliceStreams];
 	RA_CUDA(cudaStreamWaitEvent(s, ctx->slice_in[k], 0));
 	const bool trace = getenv("RA_TRACE") != nullptr;
 	if (trace) { trace_events_init(); cudaEventRecord(g_tr_ev[k][0], s); }
@@ -539,6 +546,17 @@ int ra_init(int device, ra_ctx **out)
 		    (e = cudaEventCreateWithFlags(&ctx->slice_scan[k], cudaEventDisableTiming)) != cudaSuccess ||
 		    (k < kSliceStreams && (e = cudaStreamCreateWithFlags(&ctx->slice_stream[k], cudaStreamNonBlocking)) != cudaSuccess)) { delete ctx; return fail(RA_ECUDA, "cudaEventCreate: %s", cudaGetErrorString(e)); }
 	}
+	{
+		int lo = 0, hi = 0;
+		cudaDeviceGetStreamPriorityRange(&lo, &hi);                       // hi = numerically lowest = greatest priority
+		for (int k = 0; k < kSliceStreams; ++k) {
+			if ((e = cudaStreamCreateWithPriority(&ctx->slice_hi[k], cudaStreamNonBlocking, hi)) != cudaSuccess) { delete ctx; return fail(RA_ECUDA, "cudaStreamCreateWithPriority: %s", cudaGetErrorString(e)); }
+			for (int j = 0; j < 4; ++j)
+				if ((e = cudaEventCreateWithFlags(&ctx->split_ev[k][j], cudaEventDisableTiming)) != cudaSuccess) { delete ctx; return fail(RA_ECUDA, "cudaEventCreate: %s", cudaGetErrorString(e)); }
+		}
+		if (const char *g = getenv("RA_K1_GROUPS")) { const int v = atoi(g); if (v >= 1 && v <= kSliceStreams) ctx->k1_groups = v; }
+		if (const char *g = getenv("RA_K1_PRIO")) ctx->k1_prio = atoi(g) != 0;
+	}
 	*out = ctx;
 	return RA_OK;
 }
@@ -560,6 +578,8 @@ void ra_destroy(ra_ctx *ctx)
 		if (ctx->slice_dec[k]) cudaEventDestroy(ctx->slice_dec[k]);
 		if (ctx->slice_scan[k]) cudaEventDestroy(ctx->slice_scan[k]);
 		if (k < kSliceStreams && ctx->slice_stream[k]) cudaStreamDestroy(ctx->slice_stream[k]);
+		if (k < kSliceStreams && ctx->slice_hi[k]) cudaStreamDestroy(ctx->slice_hi[k]);
+		if (k < kSliceStreams) for (int j = 0; j < 4; ++j) if (ctx->split_ev[k][j]) cudaEventDestroy(ctx->split_ev[k][j]);
 	}
 	DevBuf *dec[] = { &ctx->raw16, &ctx->rd_off, &ctx->rd_len, &ctx->rd_offset, &ctx->rd_scale, &ctx->rd_lsig };
 	for (DevBuf *b : dec) b->release();
@@ -795,7 +815,7 @@ int ra_detect_events_raw_batch(ra_ctx *ctx, const int16_t *raw, uint64_t n_raw, 
 		cut[k + 1] = n_chunks;
 		// the table goes up on the stream that runs this slice's K1 (the aux stream still holds the decodes of later slices,
 		// which wait for their copies: anything queued behind them would start late)
-		cudaStream_t ks = ctx->slices_concurrent ? ctx->slice_stream[k % kSliceStreams] : ctx->stream;
+		cudaStream_t ks = ctx->slices_concurrent ? ctx->slice_stream[k % kCopySliceStreams] : ctx->stream;
 		if (n) {
 			RA_CUDA(ra::launch_fetch_tables(coff + c_begin, clen + c_begin, ctx->chunk_off.as<uint64_t>() + c_begin, ctx->chunk_len.as<uint32_t>() + c_begin, n, ks));
 			ctx->launches += 1;

@@ -224,6 +224,7 @@ template <int RP, bool COUNT, bool MIXED = false, class LA, class LB>
 __device__ __forceinline__ float thread_dtw_diag(const LA A, int n, const LB B, int m, uint32_t *cells, bool r1 = false)
 {
 	static_assert(!MIXED || RP == 2, "MIXED is the R' = 1 inside R' = 2 embedding");
+	static_assert(!(MIXED && COUNT), "cell counting of mixed rounds is done outside the evaluator (diag_cells, chains_sparse.cu)");
 	constexpr bool ODD = (RP & 1) != 0;
 	constexpr int h = ODD ? (RP - 1) / 2 : RP / 2;
 	constexpr int NP = 2 * h + 1;                 // primary length (odd)
@@ -299,8 +300,7 @@ __device__ __forceinline__ float thread_dtw_diag(const LA A, int n, const LB B, 
 		for (int t = 0; t < NP; ++t) pold[t] = pnew[t];
 		if (COUNT) {
 			// cells of P(c) and S(c) inside the matrix (dtw.cpp:365-366, :419-420)
-			const int hh = (MIXED && r1) ? 0 : h;
-			const int klo = max(max(-hh, -c), r - (m - 1)), khi = min(min(hh, n - 1 - c), r);
+			const int klo = max(max(-h, -c), r - (m - 1)), khi = min(min(h, n - 1 - c), r);
 			cnt += (uint32_t)max(0, khi - klo + 1);
 			if (inc) {
 				// S(c): (c+k, r-1-k), k in [-NS/2, NS/2-1]

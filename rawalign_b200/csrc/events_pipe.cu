@@ -573,7 +573,7 @@ void events_pipe_layout(uint32_t max_len, const EvParams &p, uint32_t *stride, u
 cudaError_t launch_events_pipe(const float *sig, const uint64_t *chunk_off, const uint32_t *chunk_len, uint32_t n_chunks,
                                uint32_t max_len, const EvParams &p, int contract, float *scratch, uint32_t *n_ev,
                                uint64_t *ev_off, int chained, float *ev_out, uint64_t ev_cap, uint32_t *ev_pos, cudaStream_t s,
-                               cudaEvent_t after_detect, cudaEvent_t scan_wait, cudaEvent_t scan_done)
+                               cudaEvent_t after_detect, cudaEvent_t scan_wait, cudaEvent_t scan_done, const PipeSplit *split)
 {
 	using namespace evp;
 	if (n_chunks == 0) return cudaSuccess;
@@ -599,14 +599,18 @@ cudaError_t launch_events_pipe(const float *sig, const uint64_t *chunk_off, cons
 	}
 	const dim3 tgrid((max_len + kTsBlock - 1) / kTsBlock, n_chunks);
 	const TsWin W1 = make_tswin(p.w1), W2 = make_tswin(p.w2);
-	if (contract) {
-		k_prefix_pipe<true><<<lane_ctas, 32 * kLaneWarps, kPrefixSmem, s>>>(sig, chunk_off, chunk_len, n_chunks, psx, pssx, stride);
-		k_tstat_pipe<true><<<tgrid, kTsThreads, 0, s>>>(chunk_len, psx, pssx, stride, t1, t2, p.w1, p.w2, W1, W2);
-	} else {
-		k_prefix_pipe<false><<<lane_ctas, 32 * kLaneWarps, kPrefixSmem, s>>>(sig, chunk_off, chunk_len, n_chunks, psx, pssx, stride);
-		k_tstat_pipe<false><<<tgrid, kTsThreads, 0, s>>>(chunk_len, psx, pssx, stride, t1, t2, p.w1, p.w2, W1, W2);
-	}
-	k_fsm_pipe<<<lane_ctas, 32 * kLaneWarps, kFsmSmem, s>>>(chunk_len, n_chunks, t1, t2, stride, p, peaks, pstride, n_ev);
+	// The two lane-per-chunk kernels are latency-bound and small (one CTA per 128 chunks); with `split` they go to a
+	// high-priority stream so that their CTAs are placed ahead of the pending CTAs of other groups' t-stat grids.
+	cudaStream_t sl = split ? split->hi : s;
+	if (split) { cudaEventRecord(split->e[0], s); cudaStreamWaitEvent(sl, split->e[0], 0); }
+	if (contract) k_prefix_pipe<true><<<lane_ctas, 32 * kLaneWarps, kPrefixSmem, sl>>>(sig, chunk_off, chunk_len, n_chunks, psx, pssx, stride);
+	else k_prefix_pipe<false><<<lane_ctas, 32 * kLaneWarps, kPrefixSmem, sl>>>(sig, chunk_off, chunk_len, n_chunks, psx, pssx, stride);
+	if (split) { cudaEventRecord(split->e[1], sl); cudaStreamWaitEvent(s, split->e[1], 0); }
+	if (contract) k_tstat_pipe<true><<<tgrid, kTsThreads, 0, s>>>(chunk_len, psx, pssx, stride, t1, t2, p.w1, p.w2, W1, W2);
+	else k_tstat_pipe<false><<<tgrid, kTsThreads, 0, s>>>(chunk_len, psx, pssx, stride, t1, t2, p.w1, p.w2, W1, W2);
+	if (split) { cudaEventRecord(split->e[2], s); cudaStreamWaitEvent(sl, split->e[2], 0); }
+	k_fsm_pipe<<<lane_ctas, 32 * kLaneWarps, kFsmSmem, sl>>>(chunk_len, n_chunks, t1, t2, stride, p, peaks, pstride, n_ev);
+	if (split) { cudaEventRecord(split->e[3], sl); cudaStreamWaitEvent(s, split->e[3], 0); }
 	if (after_detect) cudaEventRecord(after_detect, s);
 	// CSR offsets continue from the previous launch group: when that group runs on another stream, only the scan waits for it
 	if (scan_wait) cudaStreamWaitEvent(s, scan_wait, 0);

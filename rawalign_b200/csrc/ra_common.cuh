@@ -44,10 +44,13 @@ constexpr uint32_t kPipeMaxWindow = 14;
 constexpr int kPipeEventKernels = 5;
 bool events_pipe_supported(uint32_t w1, uint32_t w2);
 void events_pipe_layout(uint32_t max_len, const EvParams &p, uint32_t *stride, uint32_t *peak_stride, size_t *floats_per_chunk);
+// optional second stream (created with a higher priority) for the two latency-bound kernels of the pipeline, and the four
+// events that order them against the rest
+struct PipeSplit { cudaStream_t hi; cudaEvent_t e[4]; };
 cudaError_t launch_events_pipe(const float *sig, const uint64_t *chunk_off, const uint32_t *chunk_len, uint32_t n_chunks,
                                uint32_t max_len, const EvParams &p, int contract, float *scratch, uint32_t *n_ev,
                                uint64_t *ev_off, int chained, float *ev_out, uint64_t ev_cap, uint32_t *ev_pos, cudaStream_t s,
-                               cudaEvent_t after_detect, cudaEvent_t scan_wait = nullptr, cudaEvent_t scan_done = nullptr);
+                               cudaEvent_t after_detect, cudaEvent_t scan_wait = nullptr, cudaEvent_t scan_done = nullptr, const PipeSplit *split = nullptr);
 
 // ---- launcher (decode.cu): ri_read_sig's int16 -> pA conversion + (30,200) filter + compaction, one warp per read ----
 cudaError_t launch_decode_raw(const int16_t *raw, const uint64_t *raw_off, const uint32_t *raw_len, const float *offset,
