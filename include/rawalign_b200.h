@@ -65,8 +65,10 @@ typedef struct ra_mapopt_s {
 	float    dtw_match_bonus;     /* 0.4f */
 	float    dtw_min_score;       /* 20.0f */
 	uint32_t fp_contract;         /* 1 */
-	uint32_t reserved;            /* 0 = default event-detection pipeline; test hooks: bit 0 = the earlier five-kernel form
-	                                 (also the path taken for windows > 14), bit 1 = the single-pass fused kernel */
+	uint32_t reserved;            /* 0 = default kernels; test hooks (parity-tested alternatives): bit 0 = the earlier five-kernel
+	                                 event detection (also the path taken for windows > 14), bit 1 = the single-pass fused
+	                                 event kernel, bit 2 = every DTW item through the generic shared-memory kernel,
+	                                 bit 3 = sparse chain parts through CTA-wide tiles instead of warp tiles */
 } ra_mapopt_t;
 
 /* One DTW problem = one call of DTW_global / DTW_global_slantedbanded_antidiagonalwise /
