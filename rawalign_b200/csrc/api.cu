@@ -350,8 +350,10 @@ int dtw_dev(ra_ctx *ctx, const float *a_dev, const float *b_dev, const ra_dtw_it
 	static const int kNC = 9;
 	static const int kClassH[kNC] = { 1, 2, 4, 8, 16, 32, 64 + 8, 64 + 16, 64 + 32 };   // dtw_wave_class codes
 	std::vector<uint32_t> cls[kNC + 1];                          // wave classes, then [kNC] generic
+	std::vector<uint32_t> tiny;                                   // R' <= 2: one item per thread, sorted by height below
 	uint32_t maxw = 0;
 	for (uint32_t k = 0; k < n_items; ++k) {
+		if (!ctx->force_generic_dtw && ra::dtw_tiny_supported(items_host[k].a_len, items_host[k].b_len, items_host[k].band_radius)) { tiny.push_back(k); continue; }
 		const int H = ctx->force_generic_dtw ? 0 : ra::dtw_wave_class(items_host[k].a_len, items_host[k].b_len, items_host[k].band_radius);
 		int c = kNC;
 		for (int q = 0; q < kNC; ++q) if (H == kClassH[q]) c = q;
@@ -361,6 +363,16 @@ int dtw_dev(ra_ctx *ctx, const float *a_dev, const float *b_dev, const ra_dtw_it
 	std::vector<uint32_t> order; order.reserve(n_items);
 	uint32_t first[kNC + 2]; first[0] = 0;
 	for (int c = 0; c <= kNC; ++c) { order.insert(order.end(), cls[c].begin(), cls[c].end()); first[c + 1] = (uint32_t)order.size(); }
+	const uint32_t tiny_first = (uint32_t)order.size();
+	if (!tiny.empty()) {                                          // counting sort by height: the lanes of a warp run equally long
+		constexpr uint32_t kBins = 1024;
+		std::vector<uint32_t> start(kBins + 1, 0);
+		auto height = [&](uint32_t k) { return std::min<uint32_t>(std::max(items_host[k].a_len, items_host[k].b_len), kBins - 1); };
+		for (uint32_t k : tiny) ++start[height(k) + 1];
+		for (uint32_t h = 0; h < kBins; ++h) start[h + 1] += start[h];
+		order.resize(tiny_first + tiny.size());
+		for (uint32_t k : tiny) order[tiny_first + start[height(k)]++] = k;
+	}
 	if ((rc = ctx->order.reserve((size_t)n_items * sizeof(uint32_t)))) return rc;
 	if ((rc = ctx->counter.reserve(64))) return rc;
 	RA_CUDA(cudaMemcpyAsync(ctx->order.p, order.data(), (size_t)n_items * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
@@ -372,6 +384,11 @@ int dtw_dev(ra_ctx *ctx, const float *a_dev, const float *b_dev, const ra_dtw_it
 		if (!nc) continue;
 		L.n_items = n_items;
 		RA_CUDA(ra::launch_dtw_wave(L, kClassH[c], ctx->order.as<uint32_t>() + first[c], nc, ctx->counter.as<uint32_t>() + 6 + c, ctx->n_sm, ctx->stream));
+		ctx->launches += 1;
+	}
+	if (!tiny.empty()) {
+		L.n_items = n_items;
+		RA_CUDA(ra::launch_dtw_tiny(L, ctx->order.as<uint32_t>() + tiny_first, (uint32_t)tiny.size(), ctx->stream));
 		ctx->launches += 1;
 	}
 	const uint32_t ng = first[kNC + 1] - first[kNC];

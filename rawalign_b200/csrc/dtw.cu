@@ -10,8 +10,8 @@
 //
 // This is the shape-agnostic kernel: lanes stride over the rows of one anti-diagonal, three rolling
 // anti-diagonals live in a per-warp shared-memory ring (or in an HBM/L2 ring when a band is wider than
-// the ring), warps pull problems from a global work counter.  The register-resident small-band kernels
-// in dtw_small.cu take the sparse anchor-to-anchor problems; everything they do not cover lands here.
+// the ring), warps pull problems from a global work counter.  k_dtw_tiny (below) takes the sparse anchor-to-anchor shapes
+// (R' <= 2) one per thread and dtw_wave.cu the problems whose band fits a register wavefront; the rest lands here.
 #include "dtw_core.cuh"
 
 namespace ra {
@@ -154,6 +154,43 @@ k_path_compact(const uint32_t *__restrict__ slot_i, const uint32_t *__restrict__
 		out_j[dst + t] = slot_j[src + t];
 		if (out_d) out_d[dst + t] = slot_d[src + t];
 	}
+}
+
+// Items whose slant-extended radius R' is 1 or 2 (band_radius 1: the sparse anchor-to-anchor shapes): the band is at most
+// five cells wide, so a wavefront across lanes would leave most of a warp idle.  One item per THREAD through the
+// register-resident anti-diagonal evaluator of the chain kernels (R' = 1 embedded in the R' = 2 schedule, dtw_core.cuh);
+// the host sorts these items by height, so the lanes of a warp run equally long.
+__global__ void __launch_bounds__(128)
+k_dtw_tiny(DtwLaunch L, const uint32_t *__restrict__ order, uint32_t n_order)
+{
+	const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= n_order) return;
+	const uint32_t k = order[t];
+	const ra_dtw_item_t it = L.items[k];
+	const float *a = L.a_arena + it.a_off, *b = L.b_arena + it.b_off;
+	const bool swap = it.a_len < it.b_len;                               // dtw.cpp:284-292: A is the longer sequence
+	const LdgLoader LA{swap ? b : a}, LB{swap ? a : b};
+	const int n = (int)(swap ? it.b_len : it.a_len), m = (int)(swap ? it.a_len : it.b_len);
+	const int rp = slant_radius(n, m, it.band_radius);
+	float c = thread_dtw_diag<2, false, true>(LA, n, LB, m, nullptr, rp == 1);
+	if (it.exclude_last) c -= fabsf(__ldg(a + it.a_len - 1) - __ldg(b + it.b_len - 1));   // dtw.cpp:514-516
+	L.cost[k] = c;
+}
+
+bool dtw_tiny_supported(uint32_t a_len, uint32_t b_len, int32_t band_radius)
+{
+	if (band_radius < 1 || band_radius > 2 || a_len == 0 || b_len == 0) return false;
+	const uint64_t n = a_len > b_len ? a_len : b_len, m = a_len > b_len ? b_len : a_len;
+	if (n >= (1u << 28)) return false;
+	const uint64_t rp = (uint64_t)band_radius + ((n - m) * (uint64_t)band_radius + n - 1) / n;    // dtw.cpp:298-300
+	return rp <= 2;
+}
+
+cudaError_t launch_dtw_tiny(const DtwLaunch &L, const uint32_t *order_dev, uint32_t n_order, cudaStream_t s)
+{
+	if (n_order == 0) return cudaSuccess;
+	k_dtw_tiny<<<(n_order + 127) / 128, 128, 0, s>>>(L, order_dev, n_order);
+	return cudaGetLastError();
 }
 
 cudaError_t launch_dtw_generic(const DtwLaunch &L, bool traceback, int n_sm, cudaStream_t s, int *n_launches)

@@ -77,6 +77,8 @@ struct DtwLaunch {
 	uint32_t *path_len;
 };
 cudaError_t launch_dtw_generic(const DtwLaunch &L, bool traceback, int n_sm, cudaStream_t s, int *n_launches);
+bool dtw_tiny_supported(uint32_t a_len, uint32_t b_len, int32_t band_radius);      // R' <= 2: one item per thread
+cudaError_t launch_dtw_tiny(const DtwLaunch &L, const uint32_t *order_dev, uint32_t n_order, cudaStream_t s);
 cudaError_t launch_path_compact(const uint32_t *slot_i, const uint32_t *slot_j, const float *slot_d,
                                 const uint64_t *slot_off, const ra_dtw_item_t *items, const uint32_t *path_len,
                                 const uint64_t *path_off, uint32_t n_items, uint32_t *out_i, uint32_t *out_j,

@@ -31,4 +31,31 @@ for name, al, bl, R, n in shapes:
     g = cells / (ms * 1e-3) / 1e9
     out.append({"case": name, "items": n, "cells": int(cells), "ms": ms, "gcups": g, "frac_of_alu_roofline": g / ALU_PEAK})
     print(out[-1], flush=True)
+# (ii) sparse-like stream: anchor-to-anchor shapes, a_len, b_len ~ 2 + Geom(0.2), band radius 1, laid end to end
+n = int(os.environ.get("RA_MB_SPARSE_ITEMS", 4_000_000))
+al = (1 + rng.geometric(0.2, n)).astype(np.int64); bl = np.maximum(1, al + rng.integers(-1, 2, n)).astype(np.int64)
+a_off = np.concatenate(([0], np.cumsum(al)[:-1])); b_off = np.concatenate(([0], np.cumsum(bl)[:-1]))
+a = rng.uniform(-2.5, 2.5, int(al.sum())).astype(np.float32); b = rng.uniform(-2.5, 2.5, int(bl.sum())).astype(np.float32)
+items = ra.make_items(a_off, b_off, al, bl, np.ones(n, int), np.ones(n, int))
+a_d = torch.from_numpy(a).to(dev); b_d = torch.from_numpy(b).to(dev)
+it_d = torch.from_numpy(items.view(np.uint8).reshape(-1)).to(dev); c_d = torch.empty(n, dtype=torch.float32, device=dev)
+key = (al.astype(np.uint64) << np.uint64(32)) | bl.astype(np.uint64)
+uniq, inv = np.unique(key, return_inverse=True)
+cells = int(np.array([ra.Context.dtw_cells(int(k >> np.uint64(32)), int(k & np.uint64(0xffffffff)), 1) for k in uniq], np.int64)[inv].sum())
+for hook, label in ((0, "sparse-like stream, R=1 (one item per thread)"), (4, "sparse-like stream, R=1 (generic warp-per-item kernel, test hook)")):
+    opt = ra.ri_mapopt_init(); opt.reserved = hook
+    c2 = ra.Context(0, opt)
+    nn = n if hook == 0 else n // 8
+    ts = []
+    for rep in range(4):
+        t0 = time.perf_counter()
+        c2.dtw_batch_dev(a_d.data_ptr(), b_d.data_ptr(), it_d.data_ptr(), items[:nn], c_d.data_ptr())
+        wall = (time.perf_counter() - t0) * 1e3
+        if rep: ts.append((c2.last_timing()[2], wall))
+    ms = float(np.median([t[0] for t in ts])); wall = float(np.median([t[1] for t in ts]))
+    cc = cells if hook == 0 else int(cells * (nn / n))
+    g = cc / (ms * 1e-3) / 1e9
+    out.append({"case": label, "items": nn, "cells": cc, "ms": ms, "call_wall_ms_incl_host_sort": wall, "gcups": g, "frac_of_alu_roofline": g / ALU_PEAK})
+    print(out[-1], flush=True)
+    c2.close()
 json.dump(out, open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out", "microbench_dtw.json"), "w"), indent=1)
