@@ -123,7 +123,10 @@ struct SparsePlan {
 	uint64_t *rest;                  // chain << 32 | part of the parts deferred to k_sp_rest, counted in totals[2]; may be null
 };
 constexpr int kSparseCtasPerSm = 6;
-constexpr int kSparse2CtasPerSm = 4;
+#ifndef RA_SP2_CTAS
+#define RA_SP2_CTAS 4
+#endif
+constexpr int kSparse2CtasPerSm = RA_SP2_CTAS;
 constexpr int kSparseTileParts = 256;
 constexpr int kSparseTileParts2 = 128;
 constexpr int kSparseKernelsPerPhase = 4;   // prep, parts, rest, replay
