@@ -31,7 +31,7 @@ os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 PIPELINE_DEPTH = int(os.environ.get("RA_BENCH_PIPELINE", 2))
 # measured with ncu on this build (profiles/r01_ncu_full_v5_k1.ncu-rep, profiles/r01_k1_v5_summary.md): DRAM bytes and warp
 # instructions of the K1 kernels per signal sample
-K1_DRAM_BYTES_PER_SAMPLE = 38.98
+K1_DRAM_BYTES_PER_SAMPLE = 35.75
 K1_WARP_INSTR_PER_SAMPLE = 10.64
 
 REF_BASES = 5_000_000
@@ -477,8 +477,8 @@ def main():
                          "traffic": int(K1_DRAM_BYTES_PER_SAMPLE * n_samples), "peak_source": peak_src,
                          "algorithmic_bytes": "4 B/sample in + 4 B/event out + 20 B/chunk of tables, per step like achieved / traffic",
                          "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of the four K1 kernels, ncu --set full of this build "
-                                           "(profiles/r01_ncu_full_v5_k1.ncu-rep): 38.98 B/sample = 4 B signal + the fp32 prefix sums and the two "
-                                           "t-stat tracks written once and read once (32 B) + the prefix sums re-read at the peaks; the stages are "
+                                           "(profiles/r01_ncu_full_v5_k1.ncu-rep): 35.75 B/sample = 4 B signal + the fp32 prefix sums and the two "
+                                           "t-stat tracks written once and read once (32 B, part of it absorbed by the 126 MB L2) + the prefix sums re-read at the peaks; the stages are "
                                            "separate kernels, so the intermediates cross HBM -- no stage re-reads its input",
                          "note": "K1 is issue-bound, not HBM-bound: ~10.6 warp instructions per sample (ncu) at "
                                  f"{K1_WARP_INSTR_PER_SAMPLE * n_samples / (k1_ms * 1e-3) / (148 * 4 * clocks.get('sm_mhz', 1965.0) * 1e6):.2f} of the SM issue rate"},

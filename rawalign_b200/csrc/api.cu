@@ -349,30 +349,33 @@ int dtw_dev(ra_ctx *ctx, const float *a_dev, const float *b_dev, const ra_dtw_it
 	int rc;
 	static const int kNC = 9;
 	static const int kClassH[kNC] = { 1, 2, 4, 8, 16, 32, 64 + 8, 64 + 16, 64 + 32 };   // dtw_wave_class codes
-	std::vector<uint32_t> cls[kNC + 1];                          // wave classes, then [kNC] generic
-	std::vector<uint32_t> tiny;                                   // R' <= 2: one item per thread, sorted by height below
+	// Two flat passes (class of every item, then a counting-sort scatter): item streams run to millions of tiny problems, and
+	// per-class vectors cost more host time than the kernels take.  Slots: wave classes [0, kNC), generic kNC, then the
+	// R' <= 2 items (one per thread) by height -- kTinyBins slots, so the lanes of a warp run equally long.
+	constexpr uint32_t kTinyBins = 1024, kSlots = kNC + 1 + kTinyBins;
+	std::vector<uint16_t> slot(n_items);
+	std::vector<uint32_t> start(kSlots + 1, 0);
 	uint32_t maxw = 0;
 	for (uint32_t k = 0; k < n_items; ++k) {
-		if (!ctx->force_generic_dtw && ra::dtw_tiny_supported(items_host[k].a_len, items_host[k].b_len, items_host[k].band_radius)) { tiny.push_back(k); continue; }
-		const int H = ctx->force_generic_dtw ? 0 : ra::dtw_wave_class(items_host[k].a_len, items_host[k].b_len, items_host[k].band_radius);
-		int c = kNC;
-		for (int q = 0; q < kNC; ++q) if (H == kClassH[q]) c = q;
-		cls[c].push_back(k);
-		if (c == kNC) maxw = std::max(maxw, item_width(items_host[k], false));
+		const ra_dtw_item_t &it = items_host[k];
+		uint32_t sl;
+		if (!ctx->force_generic_dtw && ra::dtw_tiny_supported(it.a_len, it.b_len, it.band_radius))
+			sl = kNC + 1 + std::min<uint32_t>(std::max(it.a_len, it.b_len), kTinyBins - 1);
+		else {
+			const int H = ctx->force_generic_dtw ? 0 : ra::dtw_wave_class(it.a_len, it.b_len, it.band_radius);
+			sl = kNC;
+			for (int q = 0; q < kNC; ++q) if (H == kClassH[q]) sl = (uint32_t)q;
+			if (sl == (uint32_t)kNC) maxw = std::max(maxw, item_width(it, false));
+		}
+		slot[k] = (uint16_t)sl;
+		++start[sl + 1];
 	}
-	std::vector<uint32_t> order; order.reserve(n_items);
-	uint32_t first[kNC + 2]; first[0] = 0;
-	for (int c = 0; c <= kNC; ++c) { order.insert(order.end(), cls[c].begin(), cls[c].end()); first[c + 1] = (uint32_t)order.size(); }
-	const uint32_t tiny_first = (uint32_t)order.size();
-	if (!tiny.empty()) {                                          // counting sort by height: the lanes of a warp run equally long
-		constexpr uint32_t kBins = 1024;
-		std::vector<uint32_t> start(kBins + 1, 0);
-		auto height = [&](uint32_t k) { return std::min<uint32_t>(std::max(items_host[k].a_len, items_host[k].b_len), kBins - 1); };
-		for (uint32_t k : tiny) ++start[height(k) + 1];
-		for (uint32_t h = 0; h < kBins; ++h) start[h + 1] += start[h];
-		order.resize(tiny_first + tiny.size());
-		for (uint32_t k : tiny) order[tiny_first + start[height(k)]++] = k;
-	}
+	for (uint32_t q = 0; q < kSlots; ++q) start[q + 1] += start[q];
+	uint32_t first[kNC + 2];
+	for (int c = 0; c <= kNC + 1; ++c) first[c] = start[c];
+	const uint32_t tiny_first = start[kNC + 1], n_tiny = n_items - tiny_first;
+	std::vector<uint32_t> order(n_items);
+	for (uint32_t k = 0; k < n_items; ++k) order[start[slot[k]]++] = k;     // stable: input order within a class
 	if ((rc = ctx->order.reserve((size_t)n_items * sizeof(uint32_t)))) return rc;
 	if ((rc = ctx->counter.reserve(64))) return rc;
 	RA_CUDA(cudaMemcpyAsync(ctx->order.p, order.data(), (size_t)n_items * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
@@ -386,9 +389,9 @@ int dtw_dev(ra_ctx *ctx, const float *a_dev, const float *b_dev, const ra_dtw_it
 		RA_CUDA(ra::launch_dtw_wave(L, kClassH[c], ctx->order.as<uint32_t>() + first[c], nc, ctx->counter.as<uint32_t>() + 6 + c, ctx->n_sm, ctx->stream));
 		ctx->launches += 1;
 	}
-	if (!tiny.empty()) {
+	if (n_tiny) {
 		L.n_items = n_items;
-		RA_CUDA(ra::launch_dtw_tiny(L, ctx->order.as<uint32_t>() + tiny_first, (uint32_t)tiny.size(), ctx->stream));
+		RA_CUDA(ra::launch_dtw_tiny(L, ctx->order.as<uint32_t>() + tiny_first, n_tiny, ctx->stream));
 		ctx->launches += 1;
 	}
 	const uint32_t ng = first[kNC + 1] - first[kNC];

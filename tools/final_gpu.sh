@@ -11,3 +11,4 @@ python bench.py --steps 2 --warmup 3 --no-cpu-baseline > /dev/null 2> gpurun_out
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches_final.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:"pipe|k_decode_raw" -s 24 -c 6 -o gpurun_out/r01_ncu_full_v5_k1 -f python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_k1.log 2>&1
 ls -la gpurun_out/*.ncu-rep gpurun_out/launches_final.csv
+python tools/microbench_dtw.py 2>&1 | tail -3 | cut -c1-300
