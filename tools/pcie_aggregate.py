@@ -14,6 +14,8 @@ N = 256 << 20
 h = torch.empty(N, dtype=torch.uint8).pin_memory(); h.fill_(1)
 d = torch.empty(N, dtype=torch.uint8, device=dev)
 h2 = torch.empty(N, dtype=torch.uint8).pin_memory()
+d2 = torch.empty(N, dtype=torch.uint8, device=dev)
+s2 = torch.cuda.Stream()
 
 
 def barrier():
@@ -30,18 +32,17 @@ def run(direction, reps=20):
             d.copy_(h, non_blocking=True)
         elif direction == "d2h":
             h2.copy_(d, non_blocking=True)
-        else:
-            s2 = torch.cuda.Stream()
+        else:                                    # both directions at once, on two streams (GB/s is per direction)
             d.copy_(h, non_blocking=True)
             with torch.cuda.stream(s2):
-                h2.copy_(d, non_blocking=True)
+                h2.copy_(d2, non_blocking=True)
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
     return N * reps / dt / 1e9
 
 
 out = {}
-for direction in ("h2d", "d2h"):
+for direction in ("h2d", "d2h", "both"):
     run(direction, 3)
     together = run(direction)
     t = torch.tensor([together], dtype=torch.float64, device=dev)
