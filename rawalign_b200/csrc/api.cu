@@ -87,6 +87,7 @@ struct ra_ctx {
 	cudaStream_t h2d = nullptr, d2h = nullptr, aux = nullptr;   // copy engines and the decode kernel of the sliced e2e entry points
 	cudaStream_t slice_hi[kSliceStreams] = {};                    // high-priority twins for the latency-bound K1 kernels (RA_K1_PRIO)
 	cudaEvent_t split_ev[kSliceStreams][4] = {};
+	cudaEvent_t grp_scan[kSliceStreams] = {}, grp_done[kSliceStreams] = {};   // per chunk group of the resident K1
 	int k1_groups = 8; bool k1_prio = true;                       // A/B on one box (profiles/r01_ab_k1_groups_prio.txt); RA_K1_GROUPS / RA_K1_PRIO override
 	cudaStream_t slice_stream[kSliceStreams] = {};                // K1 of different slices runs concurrently (each slice is latency-bound)
 	cudaEvent_t slice_in[kMaxSlices] = {}, slice_done[kMaxSlices] = {}, slice_dec[kMaxSlices] = {}, slice_scan[kMaxSlices] = {};
@@ -206,11 +207,11 @@ int events_dev(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_dev,
 			RA_CUDA(ra::launch_events_pipe(sig_dev, chunk_off_dev + c0, chunk_len_dev + c0, c1 - c0, max_chunk_len, p, (int)o.fp_contract,
 			                               ctx->raw.as<float>() + (size_t)c0 * fpc, ctx->nev.as<uint32_t>() + c0, ev_off_dev + c0, k != 0, ev_out_dev, ev_cap,
 			                               ctx->want_ev_pos ? ctx->ev_pos.as<uint32_t>() : nullptr, s, nullptr,
-			                               k ? ctx->slice_scan[k - 1] : nullptr, ctx->slice_scan[k], ctx->k1_prio ? &sp : nullptr));
+			                               k ? ctx->grp_scan[k - 1] : nullptr, ctx->grp_scan[k], ctx->k1_prio ? &sp : nullptr));
 			ctx->launches += ra::kPipeEventKernels;
-			RA_CUDA(cudaEventRecord(ctx->slice_done[k], s));
+			RA_CUDA(cudaEventRecord(ctx->grp_done[k], s));
 		}
-		for (int k = 0; k < G; ++k) RA_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->slice_done[k], 0));
+		for (int k = 0; k < G; ++k) RA_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->grp_done[k], 0));
 		RA_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
 		RA_CUDA(cudaEventRecord(ctx->ev[2], ctx->stream));
 		ctx->timed_k1 = true;
@@ -563,16 +564,18 @@ int ra_init(int device, ra_ctx **out)
 		if ((e = cudaEventCreateWithFlags(&ctx->slice_in[k], cudaEventDisableTiming)) != cudaSuccess ||
 		    (e = cudaEventCreateWithFlags(&ctx->slice_done[k], cudaEventDisableTiming)) != cudaSuccess ||
 		    (e = cudaEventCreateWithFlags(&ctx->slice_dec[k], cudaEventDisableTiming)) != cudaSuccess ||
-		    (e = cudaEventCreateWithFlags(&ctx->slice_scan[k], cudaEventDisableTiming)) != cudaSuccess ||
-		    (k < kSliceStreams && (e = cudaStreamCreateWithFlags(&ctx->slice_stream[k], cudaStreamNonBlocking)) != cudaSuccess)) { delete ctx; return fail(RA_ECUDA, "cudaEventCreate: %s", cudaGetErrorString(e)); }
+		    (e = cudaEventCreateWithFlags(&ctx->slice_scan[k], cudaEventDisableTiming)) != cudaSuccess) { delete ctx; return fail(RA_ECUDA, "cudaEventCreate: %s", cudaGetErrorString(e)); }
 	}
 	{
 		int lo = 0, hi = 0;
 		cudaDeviceGetStreamPriorityRange(&lo, &hi);                       // hi = numerically lowest = greatest priority
 		for (int k = 0; k < kSliceStreams; ++k) {
-			if ((e = cudaStreamCreateWithPriority(&ctx->slice_hi[k], cudaStreamNonBlocking, hi)) != cudaSuccess) { delete ctx; return fail(RA_ECUDA, "cudaStreamCreateWithPriority: %s", cudaGetErrorString(e)); }
+			if ((e = cudaStreamCreateWithFlags(&ctx->slice_stream[k], cudaStreamNonBlocking)) != cudaSuccess ||
+			    (e = cudaStreamCreateWithPriority(&ctx->slice_hi[k], cudaStreamNonBlocking, hi)) != cudaSuccess) { delete ctx; return fail(RA_ECUDA, "cudaStreamCreateWithPriority: %s", cudaGetErrorString(e)); }
 			for (int j = 0; j < 4; ++j)
 				if ((e = cudaEventCreateWithFlags(&ctx->split_ev[k][j], cudaEventDisableTiming)) != cudaSuccess) { delete ctx; return fail(RA_ECUDA, "cudaEventCreate: %s", cudaGetErrorString(e)); }
+			if ((e = cudaEventCreateWithFlags(&ctx->grp_scan[k], cudaEventDisableTiming)) != cudaSuccess ||
+			    (e = cudaEventCreateWithFlags(&ctx->grp_done[k], cudaEventDisableTiming)) != cudaSuccess) { delete ctx; return fail(RA_ECUDA, "cudaEventCreate: %s", cudaGetErrorString(e)); }
 		}
 		if (const char *g = getenv("RA_K1_GROUPS")) { const int v = atoi(g); if (v >= 1 && v <= kSliceStreams) ctx->k1_groups = v; }
 		if (const char *g = getenv("RA_K1_PRIO")) ctx->k1_prio = atoi(g) != 0;
@@ -597,9 +600,13 @@ void ra_destroy(ra_ctx *ctx)
 		if (ctx->slice_done[k]) cudaEventDestroy(ctx->slice_done[k]);
 		if (ctx->slice_dec[k]) cudaEventDestroy(ctx->slice_dec[k]);
 		if (ctx->slice_scan[k]) cudaEventDestroy(ctx->slice_scan[k]);
-		if (k < kSliceStreams && ctx->slice_stream[k]) cudaStreamDestroy(ctx->slice_stream[k]);
-		if (k < kSliceStreams && ctx->slice_hi[k]) cudaStreamDestroy(ctx->slice_hi[k]);
-		if (k < kSliceStreams) for (int j = 0; j < 4; ++j) if (ctx->split_ev[k][j]) cudaEventDestroy(ctx->split_ev[k][j]);
+	}
+	for (int k = 0; k < kSliceStreams; ++k) {
+		if (ctx->slice_stream[k]) cudaStreamDestroy(ctx->slice_stream[k]);
+		if (ctx->slice_hi[k]) cudaStreamDestroy(ctx->slice_hi[k]);
+		for (int j = 0; j < 4; ++j) if (ctx->split_ev[k][j]) cudaEventDestroy(ctx->split_ev[k][j]);
+		if (ctx->grp_scan[k]) cudaEventDestroy(ctx->grp_scan[k]);
+		if (ctx->grp_done[k]) cudaEventDestroy(ctx->grp_done[k]);
 	}
 	DevBuf *dec[] = { &ctx->raw16, &ctx->rd_off, &ctx->rd_len, &ctx->rd_offset, &ctx->rd_scale, &ctx->rd_lsig };
 	for (DevBuf *b : dec) b->release();
