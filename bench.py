@@ -471,7 +471,7 @@ def main():
                     "events_equal_resident_path": bool(e2e_out["n_ev"] == n_events and np.array_equal(e2e_out["ev"][:4096], ev_d[:4096].cpu().numpy()))},
             "gpu_launches": int(launches),
             "clocks": clocks,
-            "roofline": {"kernel": "K1 event detection (k_prefix_pipe + k_tstat_pipe + k_fsm_pipe + k_exclusive_scan_u32 + k_finish_pipe, four chunk groups on concurrent streams)",
+            "roofline": {"kernel": "K1 event detection (k_prefix_pipe + k_tstat_pipe + k_fsm_pipe + k_exclusive_scan_u32 + k_finish_pipe, eight chunk groups on concurrent streams)",
                          "bound": "hbm", "achieved": k1_bytes / (k1_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                          "frac": k1_bytes / (k1_ms * 1e-3) / 1e9 / hbm_peak,
                          "traffic": int(K1_DRAM_BYTES_PER_SAMPLE * n_samples), "peak_source": peak_src,

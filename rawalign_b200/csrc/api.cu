@@ -181,7 +181,7 @@ int events_launch(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_d
 }
 
 // Device-resident K1.  The stages of the v4 pipeline are bound differently (t-stat: issue; prefix sums and the detector
-// state machine: dependent-instruction latency), so large batches are cut into kSliceStreams groups of chunks that run on
+// state machine: dependent-instruction latency), so large batches are cut into k1_groups (8) groups of chunks that run on
 // their own streams and fill each other's stalls; only the CSR scans are chained (group k waits for the scan of group k-1).
 int events_dev(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_dev, const uint32_t *chunk_len_dev,
                uint32_t n_chunks, uint32_t max_chunk_len, float *ev_out_dev, uint64_t ev_cap, uint64_t *ev_off_dev,

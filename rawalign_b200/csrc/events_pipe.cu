@@ -1,4 +1,4 @@
-// events_pipe.cu -- K1 v4: detect_events() (src/revent.c:190-210) for a batch of chunks as a pipeline of
+// events_pipe.cu -- K1 (v4 pipeline, v5 tuning): detect_events() (src/revent.c:190-210) for a batch of chunks as a pipeline of
 // kernels that each use exactly the parallelism their stage has.  Bit-identical to the reference build.
 //
 // What the reference's arithmetic forces to be sequential per chunk: the fp32 prefix sums (revent.c:22-32,
@@ -6,13 +6,13 @@
 // kernel (profiles/r01_ncu_full_v3_summary.md) showed it issue-bound at 7.7 of 32 active lanes because those
 // sections ran on k = 3 lanes per warp.  Here every lane of a warp owns one chunk in the sequential stages
 // (32 chunks per warp, all lanes busy, nothing but the recurrence on the critical path), HBM latency is
-// hidden by a 4-stage cp.async ring of 32-sample x 32-chunk tiles in shared memory, and everything that is
+// hidden by a 2-stage cp.async ring of 32-sample x 32-chunk tiles in shared memory, and everything that is
 // position-independent runs in fully parallel kernels:
 //
 //   k_prefix_pipe  lane per chunk   ps/pss recurrences; tiles in by cp.async (16 B, coalesced 128 B rows),
 //                                   results out as 128-bit stores.  Row stride 36 floats: 16-byte aligned and
 //                                   conflict-free for lane-per-row LDS.128/STS.128.
-//   k_tstat_pipe   thread per sample both windows (:34-75).  mean2/e2 of position p equal mean1/e1 of position
+//   k_tstat_pipe   4 positions/thread both windows (:34-75), 512 positions of a chunk per CTA.  mean2/e2 of position p equal mean1/e1 of position
 //                                   p+w (same expression, same operands), so every window mean is divided once
 //                                   and shared through shared memory: 3 instead of 5 divisions per window.
 //   k_fsm_pipe     lane per chunk   the detector state machine only: peak positions to a per-chunk list.  The
