@@ -199,7 +199,12 @@ int events_dev(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_dev,
 		if ((rc = ctx->ev_pos.reserve((size_t)std::max<uint64_t>(ev_cap, 1) * sizeof(uint32_t)))) return rc;
 		RA_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
 		const int G = ctx->k1_groups;
+		static cudaEvent_t tr_ev[kSliceStreams][5], tr_t0; static bool tr_init = false;
+		const bool k1_trace = getenv("RA_K1_TRACE") != nullptr;
+		if (k1_trace && !tr_init) { for (auto &g : tr_ev) for (auto &e : g) cudaEventCreate(&e); cudaEventCreate(&tr_t0); tr_init = true; }
+		if (k1_trace) cudaEventRecord(tr_t0, ctx->stream);
 		for (int k = 0; k < G; ++k) {
+			ra::g_pipe_trace = k1_trace ? tr_ev[k] : nullptr;
 			const uint32_t c0 = (uint32_t)((uint64_t)n_chunks * k / G), c1 = (uint32_t)((uint64_t)n_chunks * (k + 1) / G);
 			cudaStream_t s = ctx->slice_stream[k];
 			RA_CUDA(cudaStreamWaitEvent(s, ctx->ev[0], 0));
@@ -211,7 +216,16 @@ int events_dev(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_dev,
 			ctx->launches += ra::kPipeEventKernels;
 			RA_CUDA(cudaEventRecord(ctx->grp_done[k], s));
 		}
+		ra::g_pipe_trace = nullptr;
 		for (int k = 0; k < G; ++k) RA_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->grp_done[k], 0));
+		if (k1_trace) {                                             // timeline of the groups' stages (ms after the start), debug aid
+			cudaStreamSynchronize(ctx->stream);
+			for (int k = 0; k < G; ++k) {
+				float t[5] = {0, 0, 0, 0, 0};
+				for (int j = 0; j < 5; ++j) cudaEventElapsedTime(&t[j], tr_t0, tr_ev[k][j]);
+				fprintf(stderr, "[k1 trace] group %d: prefix %.3f tstat %.3f fsm %.3f scan %.3f finish %.3f\n", k, t[0], t[1], t[2], t[3], t[4]);
+			}
+		}
 		RA_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
 		RA_CUDA(cudaEventRecord(ctx->ev[2], ctx->stream));
 		ctx->timed_k1 = true;

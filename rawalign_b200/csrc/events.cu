@@ -225,7 +225,7 @@ __global__ void __launch_bounds__(1024) k_exclusive_scan_u32(const uint32_t *__r
 		if (lane == 31) warp_tot[wid] = incl;
 		__syncthreads();
 		if (wid == 0) {
-			const uint64_t w = warp_tot[lane];
+			const uint64_t w = lane < (int)(blockDim.x >> 5) ? warp_tot[lane] : 0;   // any CTA size that is a multiple of 32
 			uint64_t wi = w;
 #pragma unroll
 			for (int o = 1; o < 32; o <<= 1) { uint64_t y = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += y; }

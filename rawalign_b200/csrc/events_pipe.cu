@@ -28,6 +28,7 @@
 #include "ra_common.cuh"
 #include <float.h>
 #include <math.h>
+#include <stdlib.h>
 
 namespace ra {
 namespace evp {
@@ -355,7 +356,8 @@ struct DetS { int pos; float pv; unsigned valid; };
 struct DetL { uint32_t masked_to; int pos; float pv; unsigned valid; };
 
 __device__ __forceinline__ void fsm_step(DetS &S, DetL &L, uint32_t i, float v1, float v2, float thr1, float thr2, float h,
-                                         uint32_t w1, uint32_t half1, uint32_t half2, uint32_t *__restrict__ peaks, uint32_t &n)
+                                         uint32_t w1, uint32_t half1, uint32_t half2, uint32_t *__restrict__ peaks, uint32_t &n,
+                                         unsigned out_on = 1u)
 {
 	// bitwise (&, |) on 0/1 flags instead of && / ||: no short-circuit evaluation, so nothing here needs a branch
 	// ---- short detector ----
@@ -378,8 +380,8 @@ __device__ __forceinline__ void fsm_step(DetS &S, DetL &L, uint32_t i, float v1,
 		L.valid = dom ? 0u : L.valid;
 		const unsigned valid = S.valid | (dom & (unsigned)(__fsub_rn(pv, v1) > h));     // :122
 		const unsigned emit = trk & valid & (unsigned)((i - (uint32_t)pos) > half1);    // :126
-		if (emit) peaks[n] = (uint32_t)pos;                          // :128
-		n += emit;
+		if (emit & out_on) peaks[n] = (uint32_t)pos;                 // :128
+		n += emit & out_on;
 		S.pos = emit ? -1 : pos; S.pv = emit ? v1 : pv; S.valid = emit ? 0u : valid;
 	}
 	// ---- long detector ----
@@ -396,8 +398,8 @@ __device__ __forceinline__ void fsm_step(DetS &S, DetL &L, uint32_t i, float v1,
 		const unsigned trk = act & (srch ^ 1u);
 		const unsigned valid = L.valid | (trk & (unsigned)(pv > thr2) & (unsigned)(__fsub_rn(pv, v2) > h));
 		const unsigned emit = trk & valid & (unsigned)((i - (uint32_t)pos) > half2);
-		if (emit) peaks[n] = (uint32_t)pos;
-		n += emit;
+		if (emit & out_on) peaks[n] = (uint32_t)pos;
+		n += emit & out_on;
 		L.pos = emit ? -1 : pos; L.pv = emit ? v2 : pv; L.valid = emit ? 0u : valid;
 	}
 }
@@ -410,9 +412,25 @@ struct __align__(16) FsmSmem {
 	uint32_t rowl[32];
 };
 
+// SEG > 1: every chunk is cut into SEG segments at tile boundaries and each segment gets its own lane (32 / SEG chunks per
+// warp), which divides the length of the recurrence -- the only thing this kernel is bound by -- by SEG.  A segment after
+// the first cannot know the detectors' state at its first sample, so it starts kFsmWarm samples early from the reset
+// state with emission switched off; the detectors re-synchronise at the next emitted peak (every ~9 samples), so by the
+// segment's first sample its state is, in practice always, the true one.  That is VERIFIED, not assumed: the state a
+// segment starts its own samples with must equal, field by field and bit for bit, the state the previous segment ends
+// with (equal state => identical continuation, so the concatenated peak lists are exactly the sequential ones).  A
+// chunk with any mismatch is replayed sequentially by its first lane (test hook: force_replay).  Peaks are partitioned
+// by EMISSION step, so a peak found late in one segment and emitted early in the next belongs to the next one.
+// A masked_to below the junction is equivalent to 0 (act = masked_to < i holds either way from there on).
+constexpr int kFsmMaxSeg = 4;
+constexpr uint32_t kFsmWarm = 64;        // warm-up samples (2 tiles); must be a multiple of kTile
+constexpr uint32_t kFsmMinSplit = 512;   // shorter chunks run unsplit on their first lane
+
+template <int SEG>
 __global__ void __launch_bounds__(32 * kLaneWarps)
 k_fsm_pipe(const uint32_t *__restrict__ chunk_len, uint32_t n_chunks, const float *__restrict__ t1, const float *__restrict__ t2,
-           uint32_t stride, EvParams prm, uint32_t *__restrict__ peaks_base, uint32_t peak_stride, uint32_t *__restrict__ n_peaks_out)
+           uint32_t stride, EvParams prm, uint32_t *__restrict__ peaks_base, uint32_t peak_stride, uint32_t *__restrict__ n_peaks_out,
+           uint32_t *__restrict__ seg_counts, int force_replay)
 {
 	extern __shared__ __align__(16) unsigned char smem_raw[];
 	FsmSmem &S = reinterpret_cast<FsmSmem *>(smem_raw)[threadIdx.x >> 5];
@@ -421,61 +439,118 @@ k_fsm_pipe(const uint32_t *__restrict__ chunk_len, uint32_t n_chunks, const floa
 	const float **rowp1 = S.rowp1, **rowp2 = S.rowp2;
 	uint32_t *rowl = S.rowl;
 	constexpr int kStages = kFsmStages;
+	constexpr uint32_t kFull = 0xffffffffu;
+	constexpr int CPW = 32 / SEG;                                      // chunks per warp
 	const int lane = threadIdx.x & 31;
-	const uint32_t c0 = (blockIdx.x * (uint32_t)kLaneWarps + (threadIdx.x >> 5)) * 32u, c = c0 + (uint32_t)lane;
+	const int seg = lane % SEG, ci = lane / SEG;                       // the SEG lanes of a chunk are adjacent
+	const uint32_t c0 = (blockIdx.x * (uint32_t)kLaneWarps + (threadIdx.x >> 5)) * (uint32_t)CPW, c = c0 + (uint32_t)ci;
 	if (c0 >= n_chunks) return;                                       // whole warp; warps never synchronise with each other
-	const uint32_t my_len = c < n_chunks ? chunk_len[c] : 0u;
-	rowp1[lane] = t1 + (size_t)min(c, n_chunks - 1) * stride;
-	rowp2[lane] = t2 + (size_t)min(c, n_chunks - 1) * stride;
-	rowl[lane] = my_len;
-	uint32_t max_len = my_len;
-#pragma unroll
-	for (int o = 16; o > 0; o >>= 1) max_len = max(max_len, __shfl_xor_sync(0xffffffffu, max_len, o));
-	__syncwarp();
-	const int n_tiles = (int)((max_len + kTile - 1) / kTile);
-#pragma unroll
-	for (int t = 0; t < kStages - 1; ++t) {
-		if (t < n_tiles) { load_tile<true>(s1[t], rowp1, rowl, (uint32_t)t * kTile, lane); load_tile<true>(s2[t], rowp2, rowl, (uint32_t)t * kTile, lane); }
-		cp_async_commit();
-	}
-	DetS sd = { -1, FLT_MAX, 0u };                                 // :198-202
-	DetL ld = { 0u, -1, FLT_MAX, 0u };
-	uint32_t n_peaks = 0;
-	uint32_t *__restrict__ peaks = peaks_base + (size_t)min(c, n_chunks - 1) * peak_stride;
+	const uint32_t cc = min(c, n_chunks - 1);
+	const uint32_t len = c < n_chunks ? chunk_len[c] : 0u;
+	const uint32_t segcap = peak_stride / (uint32_t)SEG;
 	const float thr1 = prm.thr1, thr2 = prm.thr2, ph = prm.peak_height;
 	const uint32_t w1 = prm.w1, half1 = prm.w1 / 2, half2 = prm.w2 / 2;
-	for (int t = 0; t < n_tiles; ++t) {
-		if (t + kStages - 1 < n_tiles) {
-			const int st = (t + kStages - 1) % kStages;
-			load_tile<true>(s1[st], rowp1, rowl, (uint32_t)(t + kStages - 1) * kTile, lane);
-			load_tile<true>(s2[st], rowp2, rowl, (uint32_t)(t + kStages - 1) * kTile, lane);
-		}
-		cp_async_commit();
-		cp_async_wait<kStages - 1>();
-		__syncwarp();
-		const uint32_t base = (uint32_t)t * kTile;
-		if (base < my_len) {
-			const float *r1 = s1[t % kStages] + lane * kRow, *r2 = s2[t % kStages] + lane * kRow;
-			const uint32_t cnt = min((uint32_t)kTile, my_len - base);
-			if (cnt == (uint32_t)kTile) {                               // full tile: no per-step guard
-#pragma unroll 2
-				for (int k = 0; k < 8; ++k) {
-					const float4 a = *reinterpret_cast<const float4 *>(r1 + 4 * k);
-					const float4 b = *reinterpret_cast<const float4 *>(r2 + 4 * k);
-					const uint32_t i = base + (uint32_t)(4 * k);
-					fsm_step(sd, ld, i, a.x, b.x, thr1, thr2, ph, w1, half1, half2, peaks, n_peaks);
-					fsm_step(sd, ld, i + 1u, a.y, b.y, thr1, thr2, ph, w1, half1, half2, peaks, n_peaks);
-					fsm_step(sd, ld, i + 2u, a.z, b.z, thr1, thr2, ph, w1, half1, half2, peaks, n_peaks);
-					fsm_step(sd, ld, i + 3u, a.w, b.w, thr1, thr2, ph, w1, half1, half2, peaks, n_peaks);
-				}
-			} else {
-#pragma unroll 1
-				for (uint32_t e = 0; e < cnt; ++e) fsm_step(sd, ld, base + e, r1[e], r2[e], thr1, thr2, ph, w1, half1, half2, peaks, n_peaks);
-			}
-		}
-		__syncwarp();
+	// segment [b0, b1) of the chunk; the lane starts at ws <= b0
+	const bool split = SEG > 1 && len >= kFsmMinSplit;
+	uint32_t b0 = seg == 0 ? 0u : len, b1 = len, ws = b0;
+	if (split) {
+		const uint32_t q = (((len + SEG - 1) / SEG) + kTile - 1) / kTile * kTile;   // >= 128 > kFsmWarm
+		b0 = min(len, (uint32_t)seg * q); b1 = min(len, (uint32_t)(seg + 1) * q);
+		ws = (seg > 0 && b0 < b1) ? b0 - kFsmWarm : b0;
 	}
-	if (c < n_chunks) n_peaks_out[c] = n_peaks;                       // == number of events (see k_finish_pipe)
+	const bool warm = ws != b0;
+
+	DetS sd; DetL ld; uint32_t n_peaks;
+	DetS snap_s = { -1, FLT_MAX, 0u }; DetL snap_l = { 0u, -1, FLT_MAX, 0u };
+	// runs the lane over samples [from, to) of its chunk; emission on from sample `emit_from`; lanes with from >= to idle
+	auto run = [&](uint32_t from, uint32_t to, uint32_t emit_from, uint32_t *__restrict__ peaks, bool take_snapshot) {
+		const uint32_t rl = to > from ? to - from : 0u;
+		__syncwarp();
+		rowp1[lane] = t1 + (size_t)cc * stride + from;
+		rowp2[lane] = t2 + (size_t)cc * stride + from;
+		rowl[lane] = rl;
+		uint32_t max_len = rl;
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1) max_len = max(max_len, __shfl_xor_sync(kFull, max_len, o));
+		__syncwarp();
+		const int n_tiles = (int)((max_len + kTile - 1) / kTile);
+#pragma unroll
+		for (int t = 0; t < kStages - 1; ++t) {
+			if (t < n_tiles) { load_tile<true>(s1[t], rowp1, rowl, (uint32_t)t * kTile, lane); load_tile<true>(s2[t], rowp2, rowl, (uint32_t)t * kTile, lane); }
+			cp_async_commit();
+		}
+		for (int t = 0; t < n_tiles; ++t) {
+			if (t + kStages - 1 < n_tiles) {
+				const int st = (t + kStages - 1) % kStages;
+				load_tile<true>(s1[st], rowp1, rowl, (uint32_t)(t + kStages - 1) * kTile, lane);
+				load_tile<true>(s2[st], rowp2, rowl, (uint32_t)(t + kStages - 1) * kTile, lane);
+			}
+			cp_async_commit();
+			cp_async_wait<kStages - 1>();
+			__syncwarp();
+			const uint32_t base = (uint32_t)t * kTile;
+			if (base < rl) {
+				const float *r1 = s1[t % kStages] + lane * kRow, *r2 = s2[t % kStages] + lane * kRow;
+				const uint32_t cnt = min((uint32_t)kTile, rl - base);
+				const uint32_t i0 = from + base;
+				const unsigned on = i0 >= emit_from;                   // emit_from is a tile boundary of this lane
+				if (cnt == (uint32_t)kTile) {                           // full tile: no per-step guard
+#pragma unroll 2
+					for (int k = 0; k < 8; ++k) {
+						const float4 a = *reinterpret_cast<const float4 *>(r1 + 4 * k);
+						const float4 b = *reinterpret_cast<const float4 *>(r2 + 4 * k);
+						const uint32_t i = i0 + (uint32_t)(4 * k);
+						fsm_step(sd, ld, i, a.x, b.x, thr1, thr2, ph, w1, half1, half2, peaks, n_peaks, on);
+						fsm_step(sd, ld, i + 1u, a.y, b.y, thr1, thr2, ph, w1, half1, half2, peaks, n_peaks, on);
+						fsm_step(sd, ld, i + 2u, a.z, b.z, thr1, thr2, ph, w1, half1, half2, peaks, n_peaks, on);
+						fsm_step(sd, ld, i + 3u, a.w, b.w, thr1, thr2, ph, w1, half1, half2, peaks, n_peaks, on);
+					}
+				} else {
+#pragma unroll 1
+					for (uint32_t e = 0; e < cnt; ++e) fsm_step(sd, ld, i0 + e, r1[e], r2[e], thr1, thr2, ph, w1, half1, half2, peaks, n_peaks, on);
+				}
+				if (take_snapshot && i0 + (uint32_t)kTile == emit_from) { snap_s = sd; snap_l = ld; }   // state before the segment's own first sample
+			}
+			__syncwarp();
+		}
+	};
+
+	uint32_t *__restrict__ peaks_c = peaks_base + (size_t)cc * peak_stride;
+	sd = { -1, FLT_MAX, 0u }; ld = { 0u, -1, FLT_MAX, 0u }; n_peaks = 0;   // :198-202
+	run(ws, b1, b0, peaks_c + (size_t)seg * segcap, warm);
+
+	bool replay = false;
+	if (SEG > 1) {
+		// the state this lane ends with against the snapshot of the next segment's lane
+		const int nxt = min(lane + 1, 31);
+		const unsigned n_warm = __shfl_sync(kFull, (unsigned)warm, nxt);
+		const int ns_pos = __shfl_sync(kFull, snap_s.pos, nxt); const float ns_pv = __shfl_sync(kFull, snap_s.pv, nxt);
+		const unsigned ns_valid = __shfl_sync(kFull, snap_s.valid, nxt);
+		const uint32_t nl_mask = __shfl_sync(kFull, snap_l.masked_to, nxt); const int nl_pos = __shfl_sync(kFull, snap_l.pos, nxt);
+		const float nl_pv = __shfl_sync(kFull, snap_l.pv, nxt); const unsigned nl_valid = __shfl_sync(kFull, snap_l.valid, nxt);
+		bool ok = true;
+		if (seg + 1 < SEG && n_warm) {                                  // the next lane exists, belongs to this chunk and speculated
+			const uint32_t ma = ld.masked_to < b1 ? 0u : ld.masked_to, mb = nl_mask < b1 ? 0u : nl_mask;
+			ok = sd.pos == ns_pos && __float_as_uint(sd.pv) == __float_as_uint(ns_pv) && sd.valid == ns_valid && ma == mb &&
+			     ld.pos == nl_pos && __float_as_uint(ld.pv) == __float_as_uint(nl_pv) && ld.valid == nl_valid;
+		}
+		if (force_replay && split) ok = false;
+		const unsigned bad = __ballot_sync(kFull, !ok);
+		replay = ((bad >> (ci * SEG)) & ((1u << SEG) - 1u)) != 0u;
+		if (bad) {                                                     // some chunk of the warp is replayed by its first lane
+			const bool mine = replay && seg == 0;
+			if (mine) { sd = { -1, FLT_MAX, 0u }; ld = { 0u, -1, FLT_MAX, 0u }; n_peaks = 0; }
+			run(0u, mine ? len : 0u, 0u, peaks_c, false);
+			if (replay && seg != 0) n_peaks = 0;
+		}
+	}
+	uint32_t tot = n_peaks;
+#pragma unroll
+	for (int o = 1; o < SEG; o <<= 1) tot += __shfl_xor_sync(kFull, tot, o);   // the SEG lanes of a chunk are an aligned group
+	if (c < n_chunks) {
+		if (SEG > 1) seg_counts[(size_t)c * SEG + seg] = n_peaks;
+		if (seg == 0) n_peaks_out[c] = tot;                            // == number of events (see k_finish_pipe)
+	}
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -490,7 +565,7 @@ __global__ void __launch_bounds__(128)
 k_finish_pipe(const uint32_t *__restrict__ chunk_len, uint32_t n_chunks, const float *__restrict__ psx, uint32_t stride,
               const uint32_t *__restrict__ peaks_base, uint32_t peak_stride, const uint32_t *__restrict__ n_peaks_in,
               const uint64_t *__restrict__ ev_off, float *__restrict__ ev_out, uint64_t ev_cap, float *__restrict__ raw_base,
-              uint32_t *__restrict__ ev_pos)
+              uint32_t *__restrict__ ev_pos, const uint32_t *__restrict__ seg_counts, int n_seg)
 {
 	const uint32_t c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
 	const int lane = threadIdx.x & 31;
@@ -499,8 +574,23 @@ k_finish_pipe(const uint32_t *__restrict__ chunk_len, uint32_t n_chunks, const f
 	if (n_ev == 0) return;                                            // detect_events returns NULL, *n untouched (:205-206)
 	const uint32_t len = chunk_len[c];
 	const float *__restrict__ ps1 = psx + (size_t)c * stride;         // ps[j] = ps1[j-1], j >= 1
-	const uint32_t *__restrict__ peaks = peaks_base + (size_t)c * peak_stride;
+	const uint32_t *__restrict__ peaks_c = peaks_base + (size_t)c * peak_stride;
 	float *__restrict__ raw = raw_base + (size_t)c * peak_stride;
+	// the state machine leaves the chunk's peaks as up to kFsmMaxSeg lists (one per segment, in order): k-th peak overall
+	uint32_t cum[kFsmMaxSeg];
+	{
+		uint32_t acc = 0;
+#pragma unroll
+		for (int q = 0; q < kFsmMaxSeg; ++q) { acc += (q < n_seg && n_seg > 1) ? seg_counts[(size_t)c * n_seg + q] : 0u; cum[q] = acc; }
+	}
+	const uint32_t segcap = peak_stride / (uint32_t)max(n_seg, 1);
+	auto peak_at = [&](uint32_t k) -> uint32_t {
+		if (n_seg <= 1) return peaks_c[k];
+		uint32_t sgm = 0, base = 0;
+#pragma unroll
+		for (int q = 0; q + 1 < kFsmMaxSeg; ++q) { const bool past = k >= cum[q] && q + 1 < n_seg; sgm += past ? 1u : 0u; base = past ? cum[q] : base; }
+		return peaks_c[sgm * segcap + (k - base)];
+	};
 	// event k: (ps[end_k] - ps[start_k]) / ((float)end_k - (float)start_k), end_k = peaks[k] (k < n_ev-1) or len,
 	// start_k = peaks[k-1] or 0                                      :160-172
 	double sum = 0.0, sum2 = 0.0;
@@ -508,8 +598,8 @@ k_finish_pipe(const uint32_t *__restrict__ chunk_len, uint32_t n_chunks, const f
 		const uint32_t k = kb + (uint32_t)lane;
 		float ev = 0.0f;
 		if (k < n_ev) {
-			const uint32_t e_pos = (k + 1 < n_ev) ? peaks[k] : len;
-			const uint32_t s_pos = (k > 0) ? peaks[k - 1] : 0u;
+			const uint32_t e_pos = (k + 1 < n_ev) ? peak_at(k) : len;
+			const uint32_t s_pos = (k > 0) ? peak_at(k - 1) : 0u;
 			const float l_ps = (s_pos > 0) ? __ldg(ps1 + s_pos - 1) : 0.0f;
 			const float e_ps = (e_pos > 0) ? __ldg(ps1 + e_pos - 1) : 0.0f;
 			ev = __fdiv_rn(__fsub_rn(e_ps, l_ps), __fsub_rn(__uint2float_rn(e_pos), __uint2float_rn(s_pos)));
@@ -541,7 +631,7 @@ k_finish_pipe(const uint32_t *__restrict__ chunk_len, uint32_t n_chunks, const f
 	for (uint32_t k = lane; k < n_ev; k += 32)
 		if (off + k < ev_cap) {
 			ev_out[off + k] = __double2float_rn(__ddiv_rn(__dsub_rn((double)raw[k], mean), sd));           // :183
-			if (ev_pos) ev_pos[off + k] = (k > 0) ? peaks[k - 1] : 0u;   // first sample of the event (not part of the reference's output)
+			if (ev_pos) ev_pos[off + k] = (k > 0) ? peak_at(k - 1) : 0u;   // first sample of the event (not part of the reference's output)
 		}
 }
 
@@ -560,14 +650,39 @@ static evp::TsWin make_tswin(uint32_t w)
 
 bool events_pipe_supported(uint32_t w1, uint32_t w2) { return w1 >= 1 && w2 >= 1 && w1 <= kPipeMaxWindow && w2 <= kPipeMaxWindow; }
 
+// RA_K1_TRACE: api.cu points this at five timing events (after prefix, t-stat, state machine, scan, finish) per launch
+cudaEvent_t *g_pipe_trace = nullptr;
+
+// Segments the state machine cuts a chunk into.  Splitting shortens the recurrence (latency) at the price of ~7 % more
+// instructions and four times as many high-priority warps: measured on one box it takes K1 of a 4096-read batch from 2.18
+// to 2.04 ms when run alone but lowers the throughput of two batches in flight by 9 % (profiles/r01_ab_fsm_segments.txt).
+// So: launches that cannot fill the GPU anyway (< kFsmSplitBelow chunks) are split four ways, large ones are not.
+// RA_FSM_SEG = 1 / 2 / 4 forces a count, RA_FSM_FORCE_REPLAY = 1 sends every split chunk through the replay (test hooks).
+constexpr uint32_t kFsmSplitBelow = 2048;
+static int g_fsm_seg = -1, g_fsm_force_replay = 0;
+static int fsm_seg_override()
+{
+	if (g_fsm_seg < 0) {
+		int v = 0;
+		if (const char *e = getenv("RA_FSM_SEG")) { const int u = atoi(e); if (u == 1 || u == 2 || u == 4) v = u; }
+		if (const char *e = getenv("RA_FSM_FORCE_REPLAY")) g_fsm_force_replay = atoi(e) != 0;
+		g_fsm_seg = v;
+	}
+	return g_fsm_seg;
+}
+int events_pipe_segments() { return evp::kFsmMaxSeg; }               // what the scratch layout provides for
+
 void events_pipe_layout(uint32_t max_len, const EvParams &p, uint32_t *stride, uint32_t *peak_stride, size_t *floats_per_chunk)
 {
 	*stride = (max_len + 31u) & ~31u;
 	if (*stride == 0) *stride = 32;
-	// a detector emits at i >= peak_pos + w/2 + 1 and can only start its next peak at a later sample, so peaks of one
-	// detector are >= w/2 + 2 apart
-	*peak_stride = ((max_len / (p.w1 / 2 + 2) + max_len / (p.w2 / 2 + 2) + 4) + 3u) & ~3u;
-	*floats_per_chunk = 4 * (size_t)*stride + 2 * (size_t)*peak_stride;
+	// a detector emits at i >= peak_pos + w/2 + 1 and can only start its next peak at a later sample, so the emissions of one
+	// detector are >= w/2 + 2 apart; a segment is at most ceil(max_len / n_seg) rounded up to a tile
+	const uint32_t n_seg = (uint32_t)events_pipe_segments();
+	const uint32_t seg_len = ((max_len + n_seg - 1) / n_seg + 31u) & ~31u;
+	const uint32_t segcap = ((seg_len / (p.w1 / 2 + 2) + seg_len / (p.w2 / 2 + 2) + 4) + 3u) & ~3u;
+	*peak_stride = n_seg * segcap;
+	*floats_per_chunk = 4 * (size_t)*stride + 2 * (size_t)*peak_stride + evp::kFsmMaxSeg;   // + segment counts
 }
 
 cudaError_t launch_events_pipe(const float *sig, const uint64_t *chunk_off, const uint32_t *chunk_len, uint32_t n_chunks,
@@ -585,6 +700,9 @@ cudaError_t launch_events_pipe(const float *sig, const uint64_t *chunk_off, cons
 	float *t2 = t1 + (size_t)n_chunks * stride;
 	uint32_t *peaks = reinterpret_cast<uint32_t *>(t2 + (size_t)n_chunks * stride);
 	float *raw = reinterpret_cast<float *>(peaks + (size_t)n_chunks * pstride);
+	uint32_t *segcnt = reinterpret_cast<uint32_t *>(raw + (size_t)n_chunks * pstride);
+	const int n_seg = fsm_seg_override() ? fsm_seg_override() : (n_chunks < kFsmSplitBelow ? kFsmMaxSeg : 1);
+	const uint32_t fsm_ctas = (n_chunks * (uint32_t)n_seg + 32u * kLaneWarps - 1u) / (32u * kLaneWarps);
 	const uint32_t lane_ctas = (n_chunks + 32u * kLaneWarps - 1u) / (32u * kLaneWarps);
 	constexpr size_t kPrefixSmem = sizeof(PrefixSmem) * kLaneWarps, kFsmSmem = sizeof(FsmSmem) * kLaneWarps;
 	static unsigned long long attr_devices = 0;                       // > 48 KB of dynamic shared memory is opt-in, per function and device
@@ -593,7 +711,9 @@ cudaError_t launch_events_pipe(const float *sig, const uint64_t *chunk_off, cons
 	if (!((attr_devices >> (dev & 63)) & 1ull)) {
 		cudaError_t ae = cudaFuncSetAttribute(k_prefix_pipe<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPrefixSmem);
 		if (ae == cudaSuccess) ae = cudaFuncSetAttribute(k_prefix_pipe<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPrefixSmem);
-		if (ae == cudaSuccess) ae = cudaFuncSetAttribute(k_fsm_pipe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFsmSmem);
+		if (ae == cudaSuccess) ae = cudaFuncSetAttribute(k_fsm_pipe<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFsmSmem);
+		if (ae == cudaSuccess) ae = cudaFuncSetAttribute(k_fsm_pipe<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFsmSmem);
+		if (ae == cudaSuccess) ae = cudaFuncSetAttribute(k_fsm_pipe<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFsmSmem);
 		if (ae != cudaSuccess) return ae;
 		__atomic_fetch_or(&attr_devices, 1ull << (dev & 63), __ATOMIC_RELAXED);   // idempotent, so a race between host threads is harmless
 	}
@@ -605,21 +725,31 @@ cudaError_t launch_events_pipe(const float *sig, const uint64_t *chunk_off, cons
 	if (split) { cudaEventRecord(split->e[0], s); cudaStreamWaitEvent(sl, split->e[0], 0); }
 	if (contract) k_prefix_pipe<true><<<lane_ctas, 32 * kLaneWarps, kPrefixSmem, sl>>>(sig, chunk_off, chunk_len, n_chunks, psx, pssx, stride);
 	else k_prefix_pipe<false><<<lane_ctas, 32 * kLaneWarps, kPrefixSmem, sl>>>(sig, chunk_off, chunk_len, n_chunks, psx, pssx, stride);
+	if (g_pipe_trace) cudaEventRecord(g_pipe_trace[0], sl);
 	if (split) { cudaEventRecord(split->e[1], sl); cudaStreamWaitEvent(s, split->e[1], 0); }
 	if (contract) k_tstat_pipe<true><<<tgrid, kTsThreads, 0, s>>>(chunk_len, psx, pssx, stride, t1, t2, p.w1, p.w2, W1, W2);
 	else k_tstat_pipe<false><<<tgrid, kTsThreads, 0, s>>>(chunk_len, psx, pssx, stride, t1, t2, p.w1, p.w2, W1, W2);
+	if (g_pipe_trace) cudaEventRecord(g_pipe_trace[1], s);
 	if (split) { cudaEventRecord(split->e[2], s); cudaStreamWaitEvent(sl, split->e[2], 0); }
-	k_fsm_pipe<<<lane_ctas, 32 * kLaneWarps, kFsmSmem, sl>>>(chunk_len, n_chunks, t1, t2, stride, p, peaks, pstride, n_ev);
+	if (n_seg == 4) k_fsm_pipe<4><<<fsm_ctas, 32 * kLaneWarps, kFsmSmem, sl>>>(chunk_len, n_chunks, t1, t2, stride, p, peaks, pstride, n_ev, segcnt, g_fsm_force_replay);
+	else if (n_seg == 2) k_fsm_pipe<2><<<fsm_ctas, 32 * kLaneWarps, kFsmSmem, sl>>>(chunk_len, n_chunks, t1, t2, stride, p, peaks, pstride, n_ev, segcnt, g_fsm_force_replay);
+	else k_fsm_pipe<1><<<fsm_ctas, 32 * kLaneWarps, kFsmSmem, sl>>>(chunk_len, n_chunks, t1, t2, stride, p, peaks, pstride, n_ev, segcnt, 0);
+	if (g_pipe_trace) cudaEventRecord(g_pipe_trace[2], sl);
 	if (split) { cudaEventRecord(split->e[3], sl); cudaStreamWaitEvent(s, split->e[3], 0); }
 	if (after_detect) cudaEventRecord(after_detect, s);
-	// CSR offsets continue from the previous launch group: when that group runs on another stream, only the scan waits for it
+	// CSR offsets continue from the previous launch group: when that group runs on another stream, only the scan waits for it.
+	// (Traced with RA_K1_TRACE: in a large batch run alone the one-CTA scans and the finish kernels sit behind the pending
+	// t-stat grids of the other groups; moving the scan to the high-priority stream frees the scans but not the finish
+	// kernels, and costs 3 % of the throughput of two batches in flight -- profiles/r01_ab_fsm_segments.txt.)
 	if (scan_wait) cudaStreamWaitEvent(s, scan_wait, 0);
 	cudaError_t e = launch_exclusive_scan_u32_chained(n_ev, ev_off, n_chunks, chained, s);
 	if (e != cudaSuccess) return e;
 	if (scan_done) cudaEventRecord(scan_done, s);
+	if (g_pipe_trace) cudaEventRecord(g_pipe_trace[3], s);
 	const unsigned fblocks = (unsigned)(((uint64_t)n_chunks * 32 + 127) / 128);
-	if (contract) k_finish_pipe<true><<<fblocks, 128, 0, s>>>(chunk_len, n_chunks, psx, stride, peaks, pstride, n_ev, ev_off, ev_out, ev_cap, raw, ev_pos);
-	else k_finish_pipe<false><<<fblocks, 128, 0, s>>>(chunk_len, n_chunks, psx, stride, peaks, pstride, n_ev, ev_off, ev_out, ev_cap, raw, ev_pos);
+	if (contract) k_finish_pipe<true><<<fblocks, 128, 0, s>>>(chunk_len, n_chunks, psx, stride, peaks, pstride, n_ev, ev_off, ev_out, ev_cap, raw, ev_pos, segcnt, n_seg);
+	else k_finish_pipe<false><<<fblocks, 128, 0, s>>>(chunk_len, n_chunks, psx, stride, peaks, pstride, n_ev, ev_off, ev_out, ev_cap, raw, ev_pos, segcnt, n_seg);
+	if (g_pipe_trace) cudaEventRecord(g_pipe_trace[4], s);
 	return cudaGetLastError();
 }
 

@@ -47,6 +47,7 @@ void events_pipe_layout(uint32_t max_len, const EvParams &p, uint32_t *stride, u
 // optional second stream (created with a higher priority) for the two latency-bound kernels of the pipeline, and the four
 // events that order them against the rest
 struct PipeSplit { cudaStream_t hi; cudaEvent_t e[4]; };
+extern cudaEvent_t *g_pipe_trace;             // RA_K1_TRACE: five timing events recorded by the next launch_events_pipe
 cudaError_t launch_events_pipe(const float *sig, const uint64_t *chunk_off, const uint32_t *chunk_len, uint32_t n_chunks,
                                uint32_t max_len, const EvParams &p, int contract, float *scratch, uint32_t *n_ev,
                                uint64_t *ev_off, int chained, float *ev_out, uint64_t ev_cap, uint32_t *ev_pos, cudaStream_t s,

@@ -250,6 +250,20 @@ def test_traceback_large_and_ties(ctx, oracle):
         assert np.array_equal(bits(pd[s:e]), bits(d2)), k
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("env", [{"RA_FSM_SEG": "1"}, {"RA_FSM_SEG": "2"}, {"RA_FSM_SEG": "4", "RA_FSM_FORCE_REPLAY": "1"}])
+def test_fsm_segment_modes(env):
+    """The state machine's segment count and its replay path are fixed per process (environment), so the event parity
+    tests are re-run in a child process for: the sequential form (1 segment), 2 segments, and 4 segments with every split
+    chunk forced through the sequential replay."""
+    import os, subprocess, sys
+    e = dict(os.environ); e.update(env)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_gpu_parity.py"), "-q", "-x", "-m", "gpu",
+                        "-k", "events and not segment_modes", "-p", "no:cacheprovider"], env=e, cwd=root, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
 # ---- chain level --------------------------------------------------------------------------------------
 def _workload(n_reads=40, seed=41):
     from rawalign_b200 import synth
