@@ -493,7 +493,7 @@ k_fsm_pipe(const uint32_t *__restrict__ chunk_len, uint32_t n_chunks, const floa
 				const float *r1 = s1[t % kStages] + lane * kRow, *r2 = s2[t % kStages] + lane * kRow;
 				const uint32_t cnt = min((uint32_t)kTile, rl - base);
 				const uint32_t i0 = from + base;
-				const unsigned on = i0 >= emit_from;                   // emit_from is a tile boundary of this lane
+				const unsigned on = SEG == 1 ? 1u : (unsigned)(i0 >= emit_from);   // emit_from is a tile boundary of this lane
 				if (cnt == (uint32_t)kTile) {                           // full tile: no per-step guard
 #pragma unroll 2
 					for (int k = 0; k < 8; ++k) {
@@ -509,7 +509,7 @@ k_fsm_pipe(const uint32_t *__restrict__ chunk_len, uint32_t n_chunks, const floa
 #pragma unroll 1
 					for (uint32_t e = 0; e < cnt; ++e) fsm_step(sd, ld, i0 + e, r1[e], r2[e], thr1, thr2, ph, w1, half1, half2, peaks, n_peaks, on);
 				}
-				if (take_snapshot && i0 + (uint32_t)kTile == emit_from) { snap_s = sd; snap_l = ld; }   // state before the segment's own first sample
+				if (SEG > 1 && take_snapshot && i0 + (uint32_t)kTile == emit_from) { snap_s = sd; snap_l = ld; }   // state before the segment's own first sample
 			}
 			__syncwarp();
 		}
@@ -560,7 +560,7 @@ k_fsm_pipe(const uint32_t *__restrict__ chunk_len, uint32_t n_chunks, const floa
 // peak of a chunk never bounds an event.  n_ev == n_peaks because the filter of :145-147 (0 < peaks[i] < s_len)
 // always holds: position 0 is never examined (masked_to(0) >= 0, :91) and positions are < s_len by construction.
 // ---------------------------------------------------------------------------------------------------
-template <bool CONTRACT>
+template <bool CONTRACT, bool SEGS>
 __global__ void __launch_bounds__(128)
 k_finish_pipe(const uint32_t *__restrict__ chunk_len, uint32_t n_chunks, const float *__restrict__ psx, uint32_t stride,
               const uint32_t *__restrict__ peaks_base, uint32_t peak_stride, const uint32_t *__restrict__ n_peaks_in,
@@ -581,11 +581,11 @@ k_finish_pipe(const uint32_t *__restrict__ chunk_len, uint32_t n_chunks, const f
 	{
 		uint32_t acc = 0;
 #pragma unroll
-		for (int q = 0; q < kFsmMaxSeg; ++q) { acc += (q < n_seg && n_seg > 1) ? seg_counts[(size_t)c * n_seg + q] : 0u; cum[q] = acc; }
+		for (int q = 0; q < kFsmMaxSeg; ++q) { acc += (SEGS && q < n_seg) ? seg_counts[(size_t)c * n_seg + q] : 0u; cum[q] = acc; }
 	}
 	const uint32_t segcap = peak_stride / (uint32_t)max(n_seg, 1);
 	auto peak_at = [&](uint32_t k) -> uint32_t {
-		if (n_seg <= 1) return peaks_c[k];
+		if (!SEGS) return peaks_c[k];
 		uint32_t sgm = 0, base = 0;
 #pragma unroll
 		for (int q = 0; q + 1 < kFsmMaxSeg; ++q) { const bool past = k >= cum[q] && q + 1 < n_seg; sgm += past ? 1u : 0u; base = past ? cum[q] : base; }
@@ -747,8 +747,10 @@ cudaError_t launch_events_pipe(const float *sig, const uint64_t *chunk_off, cons
 	if (scan_done) cudaEventRecord(scan_done, s);
 	if (g_pipe_trace) cudaEventRecord(g_pipe_trace[3], s);
 	const unsigned fblocks = (unsigned)(((uint64_t)n_chunks * 32 + 127) / 128);
-	if (contract) k_finish_pipe<true><<<fblocks, 128, 0, s>>>(chunk_len, n_chunks, psx, stride, peaks, pstride, n_ev, ev_off, ev_out, ev_cap, raw, ev_pos, segcnt, n_seg);
-	else k_finish_pipe<false><<<fblocks, 128, 0, s>>>(chunk_len, n_chunks, psx, stride, peaks, pstride, n_ev, ev_off, ev_out, ev_cap, raw, ev_pos, segcnt, n_seg);
+#define RA_FINISH(C, SG) k_finish_pipe<C, SG><<<fblocks, 128, 0, s>>>(chunk_len, n_chunks, psx, stride, peaks, pstride, n_ev, ev_off, ev_out, ev_cap, raw, ev_pos, segcnt, n_seg)
+	if (contract) { if (n_seg > 1) RA_FINISH(true, true); else RA_FINISH(true, false); }
+	else { if (n_seg > 1) RA_FINISH(false, true); else RA_FINISH(false, false); }
+#undef RA_FINISH
 	if (g_pipe_trace) cudaEventRecord(g_pipe_trace[4], s);
 	return cudaGetLastError();
 }
