@@ -682,7 +682,9 @@ void events_pipe_layout(uint32_t max_len, const EvParams &p, uint32_t *stride, u
 	const uint32_t seg_len = ((max_len + n_seg - 1) / n_seg + 31u) & ~31u;
 	const uint32_t segcap = ((seg_len / (p.w1 / 2 + 2) + seg_len / (p.w2 / 2 + 2) + 4) + 3u) & ~3u;
 	*peak_stride = n_seg * segcap;
-	*floats_per_chunk = 4 * (size_t)*stride + 2 * (size_t)*peak_stride + evp::kFsmMaxSeg;   // + segment counts
+	// + segment counts; a multiple of 32 floats, so that the scratch of every chunk group starts on a 128-byte line (callers
+	// offset by first_chunk * floats_per_chunk) and the 128-byte rows of the stages stay line- and sector-aligned
+	*floats_per_chunk = (4 * (size_t)*stride + 2 * (size_t)*peak_stride + evp::kFsmMaxSeg + 31u) & ~(size_t)31u;
 }
 
 cudaError_t launch_events_pipe(const float *sig, const uint64_t *chunk_off, const uint32_t *chunk_len, uint32_t n_chunks,
