@@ -47,7 +47,7 @@ def log(*a):
 # workload
 # ------------------------------------------------------------------------------------------------------
 def build_reference():
-    from rawalign_b200 import synth
+    from workload import synth
     ref = synth.random_reference(REF_BASES, seed=1)
     mm, _ = synth.pore_model()
     fwd = synth.seq_to_sig(ref, mm, 0); rev = synth.seq_to_sig(ref, mm, 1)
@@ -55,7 +55,7 @@ def build_reference():
 
 
 def build_reads(ref, n_reads, seed):
-    from rawalign_b200 import synth
+    from workload import synth
     reads = synth.simulate_reads(ref, n_reads, seed=seed, max_chunks=MAX_CHUNKS)
     coff, clen, crid = synth.chunk_table(reads.read_off, reads.read_len, max_chunks=MAX_CHUNKS)
     return reads, coff, clen, crid
@@ -66,7 +66,8 @@ def build_chains(ev_off, ev_pos, coff, crid, reads, n_reads, ref_len, seed):
     the CSR event arena because chunks of a read are consecutive).  Per round: the true chain (anchors placed from the
     simulator's ground truth, as exact seed hits would be) followed by CHAINS_PER_ROUND-1 decoys at random positions,
     i.e. the reference's evaluation order, best chaining score first."""
-    from rawalign_b200 import CHAIN_DTYPE, synth
+    from rawalign_b200 import CHAIN_DTYPE
+    from workload import synth
     rng = np.random.default_rng(seed)
     per_chunk = np.diff(ev_off.astype(np.int64))
     first_chunk = np.searchsorted(crid, np.arange(n_reads), "left")

@@ -234,3 +234,268 @@ class Reference:
         out = np.empty(n, np.float32)
         self.lib.ref_checkdtw_vector(int(n), int(seed), out)
         return out
+
+
+# ------------------------------------------------------------------------------------------------------
+# The reference's whole map loop: oracle/_ref/libra_refmap.so (oracle/refmap_shim.cpp + every reference object)
+# ------------------------------------------------------------------------------------------------------
+class RiMapOpt(C.Structure):
+    """ri_mapopt_t, roptions.h:39-87 (field for field; size checked against the compiled reference)."""
+    _fields_ = [("bp_per_sec", C.c_uint32), ("sample_rate", C.c_uint32), ("chunk_size", C.c_uint32),
+                ("min_events", C.c_uint32), ("max_gap_length", C.c_uint32), ("max_target_gap_length", C.c_uint32),
+                ("chaining_band_length", C.c_uint32), ("max_num_skips", C.c_uint32), ("min_num_anchors", C.c_uint32),
+                ("num_best_chains", C.c_uint32), ("min_chaining_score", C.c_float),
+                ("step_size", C.c_uint32), ("max_num_chunk", C.c_uint32), ("min_chain_anchor", C.c_uint32),
+                ("min_chain_anchor_out", C.c_uint32), ("dtw_border_constraint", C.c_uint32), ("dtw_fill_method", C.c_uint32),
+                ("dtw_band_radius_frac", C.c_float), ("dtw_match_bonus", C.c_float), ("dtw_min_score", C.c_float),
+                ("min_bestmap_ratio", C.c_float), ("min_bestmap_ratio_out", C.c_float),
+                ("min_meanmap_ratio", C.c_float), ("min_meanmap_ratio_out", C.c_float),
+                ("t_threshold", C.c_float), ("tn_samples", C.c_uint32), ("ttest_freq", C.c_uint32), ("tmin_reads", C.c_uint32),
+                ("flag", C.c_int64), ("mini_batch_size", C.c_int64),
+                ("window_length1", C.c_uint32), ("window_length2", C.c_uint32),
+                ("threshold1", C.c_float), ("threshold2", C.c_float), ("peak_height", C.c_float)]
+
+
+RI_M_DTW_EVALUATE_CHAINS = 0x2      # roptions.h:12-13
+RI_M_DTW_OUTPUT_CIGAR = 0x4
+SHIM_CHAIN_DTYPE = np.dtype([("anchor_off", "<u8"), ("n_anchors", "<u4"), ("group", "<u4"), ("read_off", "<u8"), ("ref_off", "<u8")])
+CHAIN_OUT_DTYPE = np.dtype([("chaining_score", "<f4"), ("alignment_score", "<f4"), ("reference_sequence_index", "<u4"),
+                            ("start_position", "<u4"), ("end_position", "<u4"), ("n_anchors", "<u4"), ("mapq", "<u4"),
+                            ("strand", "<i4"), ("anchor_off", "<u8")])
+# -x presets of main.cpp:131-150: (e, q, lq, w, n)
+PRESETS = {"sensitive": (6, 9, 3, 0, 0), "fast": (7, 9, 3, 0, 0), "faster": (7, 9, 3, 5, 0), "viral": (5, 9, 3, 0, 0)}
+
+
+class RefMap:
+    """ctypes binding of oracle/_ref/libra_refmap.so: the reference's own align_chain / gen_chains / map_worker_for /
+    ri_sketch / ri_idx_get / ri_seq_to_sig / ri_read_sig, compiled where they lie."""
+    PATH = os.path.join(_HERE, "_ref", "libra_refmap.so")
+
+    @staticmethod
+    def available() -> bool:
+        return os.path.exists(RefMap.PATH)
+
+    def __init__(self):
+        self.lib = L = C.CDLL(self.PATH)
+        assert L.refmap_sizeof_mapopt() == C.sizeof(RiMapOpt), "RiMapOpt does not mirror ri_mapopt_t"
+        vp = C.c_void_p
+        L.refmap_index_build.restype = vp
+        L.refmap_index_build.argtypes = [C.c_char_p, C.c_char_p] + [C.c_int] * 7 + [C.c_char_p]
+        L.refmap_index_load.restype = vp; L.refmap_index_load.argtypes = [C.c_char_p]
+        L.refmap_index_free.argtypes = [vp]
+        L.refmap_index_info.argtypes = [vp, C.POINTER(C.c_int32)]
+        L.refmap_index_seq.restype = C.c_uint32; L.refmap_index_seq.argtypes = [vp, C.c_uint32, C.c_char_p, C.c_uint32]
+        L.refmap_index_signal.restype = C.POINTER(C.c_float); L.refmap_index_signal.argtypes = [vp, C.c_uint32, C.c_int]
+        L.refmap_index_get.restype = C.c_int; L.refmap_index_get.argtypes = [vp, C.c_uint64, _u64p, C.c_int]
+        L.refmap_pore_model.restype = C.c_int; L.refmap_pore_model.argtypes = [C.c_char_p, _f32p, C.c_uint32]
+        L.refmap_sketch.restype = C.c_uint32
+        L.refmap_sketch.argtypes = [_f32p, C.c_int] + [C.c_int] * 6 + [_u64p, _u64p, C.c_uint32]
+        L.refmap_seq_to_sig.argtypes = [C.c_char_p, C.c_int, _f32p, C.c_int, C.c_int, C.POINTER(C.c_uint32), _f32p]
+        L.refmap_align_chain.restype = C.c_float
+        L.refmap_align_chain.argtypes = [vp, C.c_uint32, _f32p, _f32p, C.POINTER(RiMapOpt), C.c_int, C.c_float,
+                                         C.POINTER(C.c_float), vp, vp, vp, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.refmap_evaluate_chains_batch.argtypes = [_f32p, _f32p, vp, vp, _u32p, C.c_uint32, C.POINTER(RiMapOpt), C.c_int, vp,
+                                                   _f32p, _u8p, C.c_int]
+        L.refmap_hotpath_batch.restype = C.c_uint64
+        L.refmap_hotpath_batch.argtypes = [_f32p, _u64p, _u32p, C.c_uint32, C.c_uint32, C.c_uint32, vp, vp, vp, vp,
+                                           C.POINTER(RiMapOpt), vp, vp, vp, vp, vp, C.c_int]
+        L.refmap_reader_new.restype = vp; L.refmap_reader_new.argtypes = [vp, C.POINTER(RiMapOpt)]
+        L.refmap_reader_chunk.restype = C.c_int; L.refmap_reader_chunk.argtypes = [vp, _f32p, C.c_uint32]
+        L.refmap_reader_chains.restype = C.c_uint32
+        L.refmap_reader_chains.argtypes = [vp, vp, C.c_uint32, vp, C.c_uint64, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+        L.refmap_reader_events.restype = C.c_uint32; L.refmap_reader_events.argtypes = [vp, _f32p, C.c_uint32]
+        L.refmap_reader_free.argtypes = [vp]
+        L.refmap_map_reads.restype = C.c_uint64
+        L.refmap_map_reads.argtypes = [vp, C.POINTER(RiMapOpt), _f32p, _u64p, _u32p, C.c_uint32, C.c_int, C.c_char_p, C.c_uint64, vp, vp]
+        L.refmap_read_fast5.restype = C.c_int
+        L.refmap_read_fast5.argtypes = [C.c_char_p, vp, C.c_uint64, _u32p, C.c_uint32, vp, vp, vp, vp, C.c_uint32]
+        L.refmap_write_fast5.restype = C.c_int
+        L.refmap_write_fast5.argtypes = [C.c_char_p, vp, _u64p, _u32p, C.c_uint32, C.c_uint32, C.c_double, C.c_double, C.c_double]
+
+    # ---- options ----
+    def mapopt(self, **kw) -> RiMapOpt:
+        o = RiMapOpt()
+        self.lib.refmap_mapopt_init(C.byref(o))
+        for k, v in kw.items():
+            setattr(o, k, v)
+        return o
+
+    # ---- index ----
+    def index_build(self, fasta: str, model: str, preset: str = "sensitive", k: int = 6, n_threads: int = 4, dump: str | None = None):
+        e, q, lq, w, n = PRESETS[preset]
+        h = self.lib.refmap_index_build(fasta.encode(), model.encode(), e, q, lq, w, n, k, n_threads, dump.encode() if dump else None)
+        if not h:
+            raise RuntimeError("ri_idx_reader_open failed")
+        return h
+
+    def index_load(self, path: str):
+        h = self.lib.refmap_index_load(path.encode())
+        if not h:
+            raise RuntimeError("index load failed")
+        return h
+
+    def index_free(self, h):
+        self.lib.refmap_index_free(h)
+
+    def index_info(self, h) -> dict:
+        a = (C.c_int32 * 9)()
+        self.lib.refmap_index_info(h, a)
+        return dict(zip(("b", "w", "e", "n", "q", "lq", "k", "flag", "n_seq"), list(a)))
+
+    def index_signals(self, h):
+        """[(name, len, forward_signals[i], reverse_signals[i])]: arrays of seq.len floats as ri_idx_dump writes them."""
+        out = []
+        for i in range(self.index_info(h)["n_seq"]):
+            nm = C.create_string_buffer(256)
+            ln = self.lib.refmap_index_seq(h, i, nm, 256)
+            f = np.ctypeslib.as_array(self.lib.refmap_index_signal(h, i, 1), (ln,)).copy()
+            r = np.ctypeslib.as_array(self.lib.refmap_index_signal(h, i, 0), (ln,)).copy()
+            out.append((nm.value.decode(), ln, f, r))
+        return out
+
+    def index_get(self, h, hashval: int) -> np.ndarray:
+        buf = np.empty(64, np.uint64)
+        t = self.lib.refmap_index_get(h, int(hashval), buf, len(buf))
+        if t > len(buf):
+            buf = np.empty(t, np.uint64)
+            self.lib.refmap_index_get(h, int(hashval), buf, len(buf))
+        return buf[:t].copy()
+
+    def pore_model(self, path: str) -> np.ndarray:
+        lv = np.zeros(1 << 20, np.float32)
+        k = self.lib.refmap_pore_model(path.encode(), lv, len(lv))
+        return lv[: 1 << (2 * k)].copy()
+
+    # ---- stages ----
+    def sketch(self, ev, w=0, e=6, n=0, q=9, lq=3, k=6):
+        ev = _f32(ev)
+        x = np.empty(len(ev) * 3 + 8, np.uint64); y = np.empty_like(x)
+        m = self.lib.refmap_sketch(ev, len(ev), w, e, n, q, lq, k, x, y, len(x))
+        assert m <= len(x)
+        return x[:m].copy(), y[:m].copy()
+
+    def seq_to_sig(self, seq: bytes, pore_vals, k: int, strand: int) -> np.ndarray:
+        out = np.zeros(len(seq) + 1, np.float32)
+        n = C.c_uint32(0)
+        self.lib.refmap_seq_to_sig(seq, len(seq), _f32(pore_vals), k, strand, C.byref(n), out)
+        return out[: n.value].copy()
+
+    # ---- align_chain ----
+    def align_chain(self, anchors, read, ref, opt: RiMapOpt, min_score=-1e10):
+        anchors = np.ascontiguousarray(anchors, dtype=ANCHOR_DTYPE)
+        return np.float32(self.lib.refmap_align_chain(anchors.ctypes.data, len(anchors), _f32(read), _f32(ref), C.byref(opt), 0,
+                                                      C.c_float(min_score), None, None, None, None, 0, None))
+
+    def align_chain_cigar(self, anchors, read, ref, opt: RiMapOpt):
+        anchors = np.ascontiguousarray(anchors, dtype=ANCHOR_DTYPE)
+        q = anchors["query_position"].astype(np.int64); t = anchors["target_position"].astype(np.int64)
+        cap = int((q[0] - q[-1]) + (t[0] - t[-1]) + 4 * len(anchors) + 16)
+        pi = np.empty(cap, np.uint64); pj = np.empty(cap, np.uint64); pd = np.empty(cap, np.float32)
+        n = C.c_uint64(0); cost = C.c_float(0)
+        s = self.lib.refmap_align_chain(anchors.ctypes.data, len(anchors), _f32(read), _f32(ref), C.byref(opt), 1, C.c_float(-1e10),
+                                        C.byref(cost), pi.ctypes.data, pj.ctypes.data, pd.ctypes.data, cap, C.byref(n))
+        assert n.value <= cap
+        return np.float32(s), np.float32(cost.value), pi[: n.value].copy(), pj[: n.value].copy(), pd[: n.value].copy()
+
+    def evaluate_chains_batch(self, read_arena, ref_arena, anchors, chains, opt: RiMapOpt, running=True, min_score=None, n_threads=1):
+        anchors = np.ascontiguousarray(anchors, dtype=ANCHOR_DTYPE)
+        chains = np.ascontiguousarray(chains, dtype=SHIM_CHAIN_DTYPE)
+        g = chains["group"]
+        gfirst = np.concatenate((np.nonzero(np.concatenate(([True], g[1:] != g[:-1])))[0], [len(chains)])).astype(np.uint32) if len(chains) else np.zeros(1, np.uint32)
+        score = np.empty(len(chains), np.float32); keep = np.empty(len(chains), np.uint8)
+        ms = None if min_score is None else np.ascontiguousarray(min_score, np.float32)
+        self.lib.refmap_evaluate_chains_batch(_f32(read_arena), _f32(ref_arena), anchors.ctypes.data, chains.ctypes.data, gfirst, len(gfirst) - 1,
+                                              C.byref(opt), int(running), None if ms is None else ms.ctypes.data, score, keep, n_threads)
+        return score, keep
+
+    def hotpath_batch(self, sig, read_sig_off, read_l_sig, ref_arena, anchors, chains, round_first, opt: RiMapOpt, n_threads=1,
+                      max_chunks=None, want_events=False):
+        """One pass of the hot path over a batch of reads inside ONE C call (see refmap_shim.cpp)."""
+        sig = _f32(sig)
+        roff = np.ascontiguousarray(read_sig_off, np.uint64); rl = np.ascontiguousarray(read_l_sig, np.uint32)
+        n_reads = len(rl)
+        mc = int(max_chunks or opt.max_num_chunk)
+        has = chains is not None and len(chains) > 0
+        if has:
+            anchors = np.ascontiguousarray(anchors, dtype=ANCHOR_DTYPE); chains = np.ascontiguousarray(chains, dtype=SHIM_CHAIN_DTYPE)
+            round_first = np.ascontiguousarray(round_first, np.uint32)
+            assert round_first.size == n_reads * (mc + 1)
+            score = np.zeros(len(chains), np.float32); keep = np.zeros(len(chains), np.uint8)
+            ref_arena = _f32(ref_arena)
+        else:
+            score = np.zeros(0, np.float32); keep = np.zeros(0, np.uint8)
+        cnt = np.zeros(n_reads, np.uint32)
+        ev = base = None
+        if want_events:
+            base = np.concatenate(([0], np.cumsum(np.minimum(rl.astype(np.int64), mc * int(opt.chunk_size)))))[:-1].astype(np.uint64)
+            ev = np.zeros(int(np.minimum(rl.astype(np.int64), mc * int(opt.chunk_size)).sum()) + 1, np.float32)
+        tot = self.lib.refmap_hotpath_batch(sig, roff, rl, n_reads, int(opt.chunk_size), mc,
+                                            ref_arena.ctypes.data if has else None, anchors.ctypes.data if has else None,
+                                            chains.ctypes.data if has else None, round_first.ctypes.data if has else None, C.byref(opt),
+                                            score.ctypes.data if has else None, keep.ctypes.data if has else None,
+                                            ev.ctypes.data if want_events else None, base.ctypes.data if want_events else None,
+                                            cnt.ctypes.data, n_threads)
+        return int(tot), score, keep, cnt, ev, base
+
+    # ---- gen_chains / map loop ----
+    def read_chains(self, idx, opt: RiMapOpt, sig, max_chunks=None, stop_when_mapped=True):
+        """The chunk loop of map_worker_for (rmap.cpp:685-693) for one read; returns per chunk (chains, anchors, mapped)."""
+        sig = _f32(sig)
+        h = self.lib.refmap_reader_new(idx, C.byref(opt))
+        out = []
+        cs = int(opt.chunk_size); mc = int(max_chunks or opt.max_num_chunk)
+        try:
+            c = 0; start = 0
+            while start < len(sig) and c < mc:
+                end = min(len(sig), start + cs)
+                mapped = self.lib.refmap_reader_chunk(h, sig[start:end], end - start)
+                ch = np.zeros(64, CHAIN_OUT_DTYPE); an = np.zeros(1 << 16, ANCHOR_DTYPE)
+                ne = C.c_uint32(0); ro = C.c_uint32(0)
+                n = self.lib.refmap_reader_chains(h, ch.ctypes.data, len(ch), an.ctypes.data, len(an), C.byref(ne), C.byref(ro))
+                tot = int(ch["n_anchors"][:n].sum())
+                out.append(dict(chains=ch[:n].copy(), anchors=an[:tot].copy(), mapped=bool(mapped), n_events=ne.value, offset=ro.value))
+                if mapped and stop_when_mapped:
+                    break
+                start += cs; c += 1
+            ev = np.empty(max(1, out[-1]["n_events"] if out else 1), np.float32)
+            n = self.lib.refmap_reader_events(h, ev, len(ev))
+            return out, ev[:n].copy()
+        finally:
+            self.lib.refmap_reader_free(h)
+
+    def map_reads(self, idx, opt: RiMapOpt, sig, sig_off, l_sig, n_threads=1):
+        sig = _f32(sig); so = np.ascontiguousarray(sig_off, np.uint64); ls = np.ascontiguousarray(l_sig, np.uint32)
+        cap = 4096 * len(ls) + (1 << 20)
+        if opt.flag & RI_M_DTW_OUTPUT_CIGAR:
+            cap += 64 * int(ls.sum()) // 4
+        buf = C.create_string_buffer(cap)
+        mapped = np.zeros(len(ls), np.uint8); chunks = np.zeros(len(ls), np.uint32)
+        n = self.lib.refmap_map_reads(idx, C.byref(opt), sig, so, ls, len(ls), n_threads, buf, cap, mapped.ctypes.data, chunks.ctypes.data)
+        return buf.raw[:n].decode().splitlines(), mapped, chunks
+
+    # ---- FAST5 ----
+    def write_fast5(self, path, raw, raw_off, raw_len, first_id=0, digitisation=8192.0, range_=1467.61, offset=10.0):
+        raw = np.ascontiguousarray(raw, np.int16)
+        rc = self.lib.refmap_write_fast5(path.encode(), raw.ctypes.data, np.ascontiguousarray(raw_off, np.uint64),
+                                         np.ascontiguousarray(raw_len, np.uint32), len(raw_len), first_id, digitisation, range_, offset)
+        if rc:
+            raise RuntimeError("write_fast5 failed")
+
+    def read_fast5(self, path, n_reads_cap, sig_cap):
+        l_sig = np.zeros(n_reads_cap, np.uint32); sig = np.zeros(sig_cap, np.float32)
+        dig = np.zeros(n_reads_cap, np.float32); ran = np.zeros(n_reads_cap, np.float32); off = np.zeros(n_reads_cap, np.float32)
+        names = C.create_string_buffer(64 * n_reads_cap)
+        n = self.lib.refmap_read_fast5(path.encode(), sig.ctypes.data, sig_cap, l_sig, n_reads_cap, dig.ctypes.data, ran.ctypes.data,
+                                       off.ctypes.data, C.cast(names, C.c_void_p), 64)
+        if n < 0:
+            raise RuntimeError("open_sig failed")
+        nm = [names.raw[i * 64:(i + 1) * 64].split(b"\0")[0].decode() for i in range(n)]
+        return sig, l_sig[:n], dig[:n], ran[:n], off[:n], nm
+
+
+def build_refmap(ref_root: str = "/root/reference") -> bool:
+    """oracle/_ref/libra_refmap.so + oracle/_ref/rawalign (needs the reference tree; about two minutes the first time)."""
+    if not os.path.isdir(os.path.join(ref_root, "src")):
+        return RefMap.available()
+    subprocess.check_call(["make", "-C", _HERE, "refmap", f"REF={ref_root}"], stdout=subprocess.DEVNULL)
+    return True

@@ -2,7 +2,7 @@
 batched event detection (reference src/revent.c) and batched DTW evaluation of chained candidate
 regions (reference src/dtw.cpp, src/rmap.cpp:align_chain), behind the C ABI in
 include/rawalign_b200.h.  ``csrc/`` holds the CUDA kernels and the C ABI, ``api.py`` mirrors the
-reference's function names on top of it, ``synth.py`` generates the seeded synthetic workload.
+reference's function names on top of it, the seeded synthetic workload generator lives outside the package (``workload/synth.py``).
 """
 from ._lib import ANCHOR_DTYPE, CHAIN_DTYPE, ITEM_DTYPE, LIB_PATH, MapOpt, RawAlignError  # noqa: F401
 from .api import (  # noqa: F401

@@ -47,7 +47,7 @@ def test_events_golden(ctx, event_golden, contract, key, unfused):
 
 
 def test_events_vs_oracle_simulated_reads(ctx, oracle):
-    from rawalign_b200 import synth
+    from workload import synth
     ref = synth.random_reference(200_000, seed=1)
     reads = synth.simulate_reads(ref, 96, seed=21, max_chunks=8)
     coff, clen, _ = synth.chunk_table(reads.read_off, reads.read_len, max_chunks=8)
@@ -266,7 +266,7 @@ def test_fsm_segment_modes(env):
 
 # ---- chain level --------------------------------------------------------------------------------------
 def _workload(n_reads=40, seed=41):
-    from rawalign_b200 import synth
+    from workload import synth
     rng = np.random.default_rng(seed)
     n_ev = rng.integers(100, 2500, n_reads)
     ev_off = np.concatenate(([0], np.cumsum(n_ev)))
@@ -323,7 +323,7 @@ def test_sparse_chain_part_shapes_vs_oracle(oracle, legacy, gap_p, frac):
     rounds in the tile and the deferred remainder), wide, and larger than a warp's staging window (gap_p 0.004: parts of
     hundreds of events, some beyond 1024) -- every class of k_sp_parts2, bit for bit against the oracle."""
     import rawalign_b200 as ra
-    from rawalign_b200 import synth
+    from workload import synth
     from oracle import DtwOpt
     rng = np.random.default_rng(int(1000 * gap_p) + 7)
     n_reads = 12
@@ -414,7 +414,7 @@ def _oracle_raw_pipeline(oracle, raw, raw_off, raw_len, offset, scale, chunk_siz
 
 @pytest.mark.parametrize("align", [8, 1])
 def test_events_raw_batch_vs_oracle(ctx, oracle, align):
-    from rawalign_b200 import synth
+    from workload import synth
     rng = np.random.default_rng(77)
     ref = synth.random_reference(30_000, seed=1)
     rd = synth.simulate_reads(ref, 24, seed=12, max_chunks=3)
@@ -446,7 +446,7 @@ def test_events_raw_batch_vs_oracle(ctx, oracle, align):
 
 def test_events_sliced_copies_large_batch(ctx, oracle):
     """Enough signal (> 64 MB) for the host->device copy to be cut into several slices that overlap K1."""
-    from rawalign_b200 import synth
+    from workload import synth
     ref = synth.random_reference(60_000, seed=1)
     rd = synth.simulate_reads(ref, 640, seed=21, max_chunks=8)
     coff, clen, _ = synth.chunk_table(rd.read_off, rd.read_len, max_chunks=8)

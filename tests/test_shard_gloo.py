@@ -32,7 +32,7 @@ def _worker(rank, world, port, tmp):
     sys.path.insert(0, ROOT)
     import torch.distributed as dist
     from oracle import Oracle
-    from rawalign_b200 import synth
+    from workload import synth
     from rawalign_b200.shard import merge_in_order, shard_reads
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:

@@ -11,7 +11,7 @@ from dataclasses import dataclass
 
 import numpy as np
 
-from ._lib import ANCHOR_DTYPE, CHAIN_DTYPE
+from rawalign_b200._lib import ANCHOR_DTYPE, CHAIN_DTYPE
 
 K = 6
 CHUNK_SIZE = 4000          # roptions.c:11
@@ -182,3 +182,37 @@ def truth_chain(ev_sample_pos: np.ndarray, base_start: np.ndarray, ref_start: in
     a = np.zeros(len(q), ANCHOR_DTYPE)
     a["query_position"] = q[::-1]; a["target_position"] = t[::-1]
     return a
+
+
+# ------------------------------------------------------------------------------------------------------
+# Files in the reference's own input formats (FASTA, k-mer model text), so its index builder and CLI can be driven
+# ------------------------------------------------------------------------------------------------------
+def write_fasta(path: str, seqs, names=None, width: int = 80):
+    """seqs: list of uint8 arrays over {0,1,2,3} = ACGT."""
+    lut = np.frombuffer(b"ACGT", np.uint8)
+    with open(path, "wb") as f:
+        for i, s in enumerate(seqs):
+            f.write(b">" + (names[i] if names else f"ref{i}").encode() + b"\n")
+            txt = lut[s]
+            pad = (-len(txt)) % width
+            rows = np.concatenate([txt, np.zeros(pad, np.uint8)]).reshape(-1, width)
+            out = np.concatenate([rows, np.full((len(rows), 1), 10, np.uint8)], axis=1).reshape(-1)
+            if pad:
+                out = np.concatenate([out[: len(out) - pad - 1], [10]]).astype(np.uint8)
+            f.write(out.tobytes())
+
+
+def write_pore_model(path: str, model=None):
+    """The k-mer model text format pore_model.cpp:57-82 parses: header line, then `kmer level_mean level_stdv sd_mean sd_stdv weight`."""
+    mm, ms = model or pore_model()
+    with open(path, "w") as f:
+        f.write("kmer\tlevel_mean\tlevel_stdv\tsd_mean\tsd_stdv\tweight\n")
+        for r in range(4 ** K):
+            kmer = "".join("ACGT"[(r >> (2 * (K - 1 - i))) & 3] for i in range(K))
+            f.write(f"{kmer}\t{mm[r]:.6f}\t{ms[r]:.6f}\t1.000000\t0.500000\t1000.0\n")
+
+
+def pore_model_as_loaded(model=None) -> np.ndarray:
+    """level_mean as the reference holds it after parsing the text written by write_pore_model: 6 decimals -> float."""
+    mm, _ = model or pore_model()
+    return np.array([float(f"{v:.6f}") for v in mm], np.float64).astype(np.float32)
