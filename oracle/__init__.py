@@ -51,7 +51,7 @@ def build_oracle(force: bool = False) -> str:
     """Compile ra_oracle.c -> libra_oracle.so (gcc only; works on the GPU box too)."""
     so = os.path.join(_HERE, "libra_oracle.so")
     src = os.path.join(_HERE, "ra_oracle.c")
-    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+    if force or not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(os.path.join(_HERE, f)) for f in ("ra_oracle.c", "ra_oracle_map.c", "ra_oracle.h", "ra_oracle_map.h")):
         subprocess.check_call(["make", "-C", _HERE, "oracle"], stdout=subprocess.DEVNULL)
     return so
 
@@ -499,3 +499,216 @@ def build_refmap(ref_root: str = "/root/reference") -> bool:
         return RefMap.available()
     subprocess.check_call(["make", "-C", _HERE, "refmap", f"REF={ref_root}"], stdout=subprocess.DEVNULL)
     return True
+
+
+# ------------------------------------------------------------------------------------------------------
+# Map-loop restatement (oracle/ra_oracle_map.c): sketch, index lookup, chaining, primary chains, mapq, chunk loop
+# ------------------------------------------------------------------------------------------------------
+PAF_DTYPE = np.dtype([("mapped", "<u4"), ("ref_id", "<u4"), ("read_length", "<u4"), ("read_start_position", "<u4"),
+                      ("read_end_position", "<u4"), ("fragment_start_position", "<u4"), ("fragment_length", "<u4"), ("mapq", "<u4"),
+                      ("rev", "<u4"), ("ci", "<u4"), ("sl", "<u4"), ("cm", "<u4"), ("nc", "<u4"),
+                      ("s1", "<f4"), ("s2", "<f4"), ("sm", "<f4"), ("at", "<f4"), ("aq", "<f4"), ("alns", "<f4"),
+                      ("n_events", "<u4"), ("cells", "<u8")], align=True)
+
+
+def parse_index_file(path: str) -> dict:
+    """The reference's index file (ri_idx_dump, rawindex.cpp:275-315): magic "RI", 8 x u32 (w, e, n, q, lq, k, n_seq, flag),
+    per sequence (u8 name length, name, u32 len, len fp32 forward_signals, len fp32 reverse_signals), then for each of the
+    2^14 buckets: i32 n, n x u64 p[], u32 size, size x (u64 key, u64 val).  key = (hash >> 14) << 1 | single; val = the one
+    position (single) or p_start << 32 | count.  Returns the flat table sorted by hash."""
+    buf = np.fromfile(path, np.uint8)
+    assert bytes(buf[:2]) == b"RI"
+    pars = buf[2:34].view(np.uint32)
+    w, e, n, q, lq, k, n_seq, flag = [int(x) for x in pars]
+    o = 34
+    names, lens, fwd, rev = [], [], [], []
+    for _ in range(n_seq):
+        l = int(buf[o]); o += 1
+        names.append(bytes(buf[o:o + l]).decode()); o += l
+        ln = int(buf[o:o + 4].view(np.uint32)[0]); o += 4
+        fwd.append(buf[o:o + 4 * ln].view(np.float32).copy()); o += 4 * ln
+        rev.append(buf[o:o + 4 * ln].view(np.float32).copy()); o += 4 * ln
+        lens.append(ln)
+    b = 14
+    H, V, C = [], [], []
+    for i in range(1 << b):
+        nb = int(buf[o:o + 4].view(np.int32)[0]); o += 4
+        p = buf[o:o + 8 * nb].view(np.uint64); o += 8 * nb
+        size = int(buf[o:o + 4].view(np.uint32)[0]); o += 4
+        if size == 0:
+            continue
+        kv = buf[o:o + 16 * size].view(np.uint64).reshape(size, 2); o += 16 * size
+        key, val = kv[:, 0], kv[:, 1]
+        h = ((key >> np.uint64(1)) << np.uint64(b)) | np.uint64(i)
+        single = (key & np.uint64(1)).astype(bool)
+        cnt = np.where(single, 1, (val & np.uint64(0xFFFFFFFF))).astype(np.int64)
+        start = (val >> np.uint64(32)).astype(np.int64)
+        vals = np.empty(int(cnt.sum()), np.uint64)
+        offs = np.concatenate(([0], np.cumsum(cnt)))
+        vals[offs[:-1][single]] = val[single]
+        for j in np.nonzero(~single)[0]:
+            vals[offs[j]:offs[j + 1]] = p[start[j]:start[j] + cnt[j]]
+        H.append(h); C.append(cnt); V.append(vals)
+    assert o == len(buf), "trailing bytes in the index file"
+    h = np.concatenate(H) if H else np.zeros(0, np.uint64)
+    c = np.concatenate(C) if C else np.zeros(0, np.int64)
+    v = np.concatenate(V) if V else np.zeros(0, np.uint64)
+    order = np.argsort(h, kind="stable")
+    offs = np.concatenate(([0], np.cumsum(c)))
+    idx = np.concatenate([np.arange(offs[j], offs[j + 1]) for j in order]) if len(order) else np.zeros(0, np.int64)
+    keys = h[order]; cnt = c[order]
+    return dict(w=w, e=e, n=n, q=q, lq=lq, k=k, flag=flag, n_seq=n_seq, names=names, seq_len=np.array(lens, np.uint32), fwd=fwd, rev=rev,
+                keys=np.ascontiguousarray(keys), key_off=np.concatenate(([0], np.cumsum(cnt))).astype(np.uint64), vals=np.ascontiguousarray(v[idx]))
+
+
+class _OraIndex(C.Structure):
+    _fields_ = [("w", C.c_int32), ("e", C.c_int32), ("n", C.c_int32), ("q", C.c_int32), ("lq", C.c_int32), ("k", C.c_int32),
+                ("n_seq", C.c_uint32), ("seq_len", C.c_void_p), ("fwd", C.c_void_p), ("rev", C.c_void_p),
+                ("n_keys", C.c_uint64), ("keys", C.c_void_p), ("key_off", C.c_void_p), ("vals", C.c_void_p)]
+
+
+class MapOracle:
+    """ctypes binding of the map-loop restatement (ra_oracle_map.c) over an index parsed by parse_index_file."""
+
+    def __init__(self, index: dict):
+        self.lib = L = C.CDLL(build_oracle())
+        self.index = index
+        self._fwd = (C.c_void_p * index["n_seq"])(*[a.ctypes.data for a in index["fwd"]])
+        self._rev = (C.c_void_p * index["n_seq"])(*[a.ctypes.data for a in index["rev"]])
+        self.ix = _OraIndex(index["w"], index["e"], index["n"], index["q"], index["lq"], index["k"], index["n_seq"],
+                            index["seq_len"].ctypes.data, C.cast(self._fwd, C.c_void_p), C.cast(self._rev, C.c_void_p),
+                            len(index["keys"]), index["keys"].ctypes.data, index["key_off"].ctypes.data, index["vals"].ctypes.data)
+        vp = C.c_void_p
+        L.ora_seq_to_sig.restype = C.c_uint32; L.ora_seq_to_sig.argtypes = [vp, C.c_int, _f32p, C.c_int, C.c_int, C.c_int, _f32p]
+        L.ora_sketch.restype = C.c_uint32
+        L.ora_sketch.argtypes = [_f32p, C.c_uint32] + [C.c_int] * 6 + [_u64p, _u32p, C.POINTER(C.c_int)]
+        L.ora_reader_new.restype = vp; L.ora_reader_new.argtypes = [C.POINTER(_OraIndex), C.POINTER(RiMapOpt), C.c_int]
+        L.ora_reader_free.argtypes = [vp]
+        L.ora_reader_chunk.restype = C.c_int; L.ora_reader_chunk.argtypes = [vp, _f32p, C.c_uint32]
+        L.ora_reader_chunk_events.restype = C.c_int; L.ora_reader_chunk_events.argtypes = [vp, _f32p, C.c_uint32]
+        L.ora_reader_state.restype = C.c_uint32
+        L.ora_reader_state.argtypes = [vp, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.ora_reader_events.restype = C.POINTER(C.c_float); L.ora_reader_events.argtypes = [vp]
+        L.ora_reader_chains.restype = C.c_uint32; L.ora_reader_chains.argtypes = [vp, C.c_int, vp, C.c_uint32, vp, C.c_uint64]
+        L.ora_map_read.argtypes = [C.POINTER(_OraIndex), C.POINTER(RiMapOpt), C.c_int, _f32p, C.c_uint32, vp]
+        L.ora_paf_format.restype = C.c_int; L.ora_paf_format.argtypes = [vp, C.c_char_p, C.c_char_p, C.c_uint32, C.c_char_p, C.c_int]
+
+    @staticmethod
+    def mapopt(**kw) -> RiMapOpt:
+        """ri_mapopt_init, roptions.c:5-61."""
+        o = RiMapOpt(bp_per_sec=450, sample_rate=4000, chunk_size=4000, max_gap_length=2000, max_target_gap_length=5000,
+                     chaining_band_length=5000, max_num_skips=25, min_num_anchors=2, num_best_chains=3, min_chaining_score=10.0,
+                     step_size=1, min_events=50, max_num_chunk=30, min_chain_anchor=2, min_chain_anchor_out=2,
+                     min_bestmap_ratio=1.2, min_bestmap_ratio_out=1.2, min_meanmap_ratio=5, min_meanmap_ratio_out=5,
+                     mini_batch_size=500000000, window_length1=3, window_length2=6, threshold1=4.30265, threshold2=2.57058, peak_height=1.0,
+                     t_threshold=1.5, tn_samples=5, ttest_freq=500, tmin_reads=500,
+                     dtw_border_constraint=1, dtw_fill_method=1, dtw_band_radius_frac=0.10, dtw_match_bonus=0.4, dtw_min_score=20.0)
+        for k, v in kw.items():
+            setattr(o, k, v)
+        return o
+
+    def seq_to_sig(self, seq2bit, pore_vals, k=6, strand=0, contract=1):
+        seq2bit = np.ascontiguousarray(seq2bit, np.uint8)
+        out = np.zeros(len(seq2bit) + 1, np.float32)
+        n = self.lib.ora_seq_to_sig(seq2bit.ctypes.data, len(seq2bit), _f32(pore_vals), k, strand, contract, out)
+        return out[:n].copy()
+
+    def sketch(self, ev):
+        ev = _f32(ev); ix = self.index
+        h = np.empty(len(ev) + 1, np.uint64); p = np.empty(len(ev) + 1, np.uint32); un = C.c_int(0)
+        m = self.lib.ora_sketch(ev, len(ev), ix["w"], ix["e"], ix["n"], ix["q"], ix["lq"], ix["k"], h, p, C.byref(un))
+        if un.value:
+            raise NotImplementedError("minimizer / BLEND sketching is not restated")
+        return h[:m].copy(), p[:m].copy()
+
+    def idx_get(self, h: int) -> np.ndarray:
+        k = np.searchsorted(self.index["keys"], np.uint64(h))
+        if k < len(self.index["keys"]) and self.index["keys"][k] == np.uint64(h):
+            return self.index["vals"][int(self.index["key_off"][k]):int(self.index["key_off"][k + 1])].copy()
+        return np.zeros(0, np.uint64)
+
+    def _chains(self, h, which):
+        ch = np.zeros(256, CHAIN_OUT_DTYPE); an = np.zeros(1 << 17, ANCHOR_DTYPE)
+        n = self.lib.ora_reader_chains(h, which, ch.ctypes.data, len(ch), an.ctypes.data, len(an))
+        tot = int(ch["n_anchors"][:n].sum())
+        return ch[:n].copy(), an[:tot].copy()
+
+    def read_chains(self, opt: RiMapOpt, sig, max_chunks=None, stop_when_mapped=True, contract=1, events=None):
+        """Chunk loop of map_worker_for for one read; per chunk: reg->chains, the pre-filter candidates in evaluation order, mapped.
+        events = (ev, off): feed already detected per-chunk events instead of detecting from the signal."""
+        sig = _f32(sig)
+        h = self.lib.ora_reader_new(C.byref(self.ix), C.byref(opt), contract)
+        out = []
+        cs = int(opt.chunk_size); mc = int(max_chunks or opt.max_num_chunk)
+        try:
+            c = 0; start = 0
+            while start < len(sig) and c < mc:
+                end = min(len(sig), start + cs)
+                if events is None:
+                    mapped = self.lib.ora_reader_chunk(h, sig[start:end], end - start)
+                else:
+                    ev, off = events
+                    e = _f32(ev[int(off[c]):int(off[c + 1])])
+                    mapped = self.lib.ora_reader_chunk_events(h, e if len(e) else np.zeros(1, np.float32), len(e))
+                ch, an = self._chains(h, 0); cand, can = self._chains(h, 1)
+                ne = C.c_uint32(0); ro = C.c_uint32(0); cells = C.c_uint64(0); ns = C.c_uint64(0); nh = C.c_uint64(0)
+                self.lib.ora_reader_state(h, C.byref(ne), C.byref(ro), C.byref(cells), C.byref(ns), C.byref(nh))
+                out.append(dict(chains=ch, anchors=an, cand=cand, cand_anchors=can, mapped=bool(mapped), n_events=ne.value, offset=ro.value,
+                                cells=cells.value, seeds=ns.value, hits=nh.value))
+                if mapped and stop_when_mapped:
+                    break
+                start += cs; c += 1
+            n = out[-1]["n_events"] if out else 0
+            ev = np.ctypeslib.as_array(self.lib.ora_reader_events(h), (max(n, 1),))[:n].copy() if n else np.zeros(0, np.float32)
+            return out, ev
+        finally:
+            self.lib.ora_reader_free(h)
+
+    def map_reads(self, opt: RiMapOpt, sig, sig_off, l_sig, contract=1, names=None):
+        sig = _f32(sig)
+        res = np.zeros(len(l_sig), PAF_DTYPE)
+        for r in range(len(l_sig)):
+            a = int(sig_off[r]); n = int(l_sig[r])
+            self.lib.ora_map_read(C.byref(self.ix), C.byref(opt), contract, sig[a:a + n] if n else np.zeros(1, np.float32), n, res[r:r + 1].ctypes.data)
+        return res
+
+    def paf_lines(self, res, names=None):
+        out = []
+        buf = C.create_string_buffer(4096)
+        for r in range(len(res)):
+            nm = (names[r] if names else f"read_{r}").encode()
+            rid = int(res["ref_id"][r])
+            n = self.lib.ora_paf_format(res[r:r + 1].ctypes.data, nm, self.index["names"][rid].encode(), int(self.index["seq_len"][rid]), buf, 4096)
+            out.append(buf.raw[:n].decode())
+        return out
+
+
+def build_flat_index(seqs, pore_vals, preset="sensitive", k=6, contract=1, names=None) -> dict:
+    """Index construction restated (rawindex.cpp:127-153 per sequence: ri_seq_to_sig + ri_sketch for strand flag 1 then 0;
+    ri_idx_add / worker_post: group by hash, positions ascending): the same flat table parse_index_file returns for an index
+    the reference built.  Signal arrays are seq.len floats with a zero tail, as the reference allocates and dumps them
+    (rawindex.cpp:136-137, 294-295)."""
+    e, q, lq, w, n = PRESETS[preset]
+    mo = MapOracle.__new__(MapOracle)
+    mo.lib = C.CDLL(build_oracle())
+    mo.lib.ora_seq_to_sig.restype = C.c_uint32
+    mo.lib.ora_seq_to_sig.argtypes = [C.c_void_p, C.c_int, _f32p, C.c_int, C.c_int, C.c_int, _f32p]
+    mo.lib.ora_sketch.restype = C.c_uint32
+    mo.lib.ora_sketch.argtypes = [_f32p, C.c_uint32] + [C.c_int] * 6 + [_u64p, _u32p, C.POINTER(C.c_int)]
+    mo.index = dict(w=w, e=e, n=n, q=q, lq=lq, k=k)
+    H, Y, fwd, rev = [], [], [], []
+    for i, s in enumerate(seqs):
+        for strand, store in ((1, fwd), (0, rev)):
+            sig = mo.seq_to_sig(s, pore_vals, k, strand, contract)
+            full = np.zeros(len(s), np.float32); full[:len(sig)] = sig
+            store.append(full)
+            h, p = mo.sketch(sig)
+            H.append(h); Y.append((np.uint64(i) << np.uint64(32)) | (p.astype(np.uint64) << np.uint64(1)) | np.uint64(strand))
+    h = np.concatenate(H); y = np.concatenate(Y)
+    order = np.lexsort((y, h))
+    h = h[order]; y = y[order]
+    keys, first = np.unique(h, return_index=True)
+    key_off = np.concatenate((first, [len(h)])).astype(np.uint64)
+    return dict(w=w, e=e, n=n, q=q, lq=lq, k=k, flag=0, n_seq=len(seqs), names=names or [f"ref{i}" for i in range(len(seqs))],
+                seq_len=np.array([len(s) for s in seqs], np.uint32), fwd=fwd, rev=rev, keys=np.ascontiguousarray(keys), key_off=key_off,
+                vals=np.ascontiguousarray(y))
