@@ -235,6 +235,74 @@ int ra_align_chains_cigar_batch(ra_ctx *ctx, const float *read_arena, uint64_t n
                                 uint64_t *path_i, uint64_t *path_j, float *path_diff, uint64_t path_cap,
                                 uint64_t *path_off);
 
+
+/* ================================================================================================================
+ * The map loop around the hot path on the device: seeding (ri_sketch, rsketch.c:223-274),
+ * index lookup (ri_idx_get, rawindex.cpp:256-273), anchor sort and chaining DP (gen_chains, rmap.cpp:315-507),
+ * chain evaluation (the hot path above), gen_primary_chains / comp_mapq (:65-128), the chunk loop with
+ * is_mapped_with_high_confidence (:594-665, :685-693) and the PAF fields of map_worker_for (:696-800) -- for a whole batch
+ * of reads, so that anchors and events never cross the bus: the int16 signal goes up, one ra_paf_t per read comes back.
+ * ra_map_batch is the batched form of kt_for(n_threads, map_worker_for, step, n_sig) (rmap.cpp:916).
+ * ================================================================================================================ */
+
+/* ri_mapopt_t (roptions.h:39-87) field for field, so that a caller holding the reference's struct can pass it as is. */
+typedef struct ra_ri_mapopt_s {
+	uint32_t bp_per_sec, sample_rate, chunk_size;
+	uint32_t min_events, max_gap_length, max_target_gap_length, chaining_band_length, max_num_skips, min_num_anchors, num_best_chains;
+	float    min_chaining_score;
+	uint32_t step_size, max_num_chunk, min_chain_anchor, min_chain_anchor_out, dtw_border_constraint, dtw_fill_method;
+	float    dtw_band_radius_frac, dtw_match_bonus, dtw_min_score;
+	float    min_bestmap_ratio, min_bestmap_ratio_out, min_meanmap_ratio, min_meanmap_ratio_out;
+	float    t_threshold; uint32_t tn_samples, ttest_freq, tmin_reads;
+	int64_t  flag, mini_batch_size;
+	uint32_t window_length1, window_length2; float threshold1, threshold2, peak_height;
+} ra_ri_mapopt_t;
+#define RA_M_DTW_EVALUATE_CHAINS 0x2              /* roptions.h:12 */
+#define RA_M_DTW_OUTPUT_CIGAR    0x4
+#define RA_M_DISABLE_CHAININGSCORE_FILTERING 0x10
+void ra_ri_mapopt_init(ra_ri_mapopt_t *opt);     /* ri_mapopt_init, roptions.c:5-61 */
+
+/* The index on the device: an open-addressing table over the 32-bit seed hashes (built from the reference's unchanged
+ * index file or from a flat table) plus the per-sequence signal offsets in the reference mirror, which it also loads. */
+typedef struct ra_index ra_index;
+/* Parses the file ri_idx_dump writes (rawindex.cpp:275-315): magic, (w,e,n,q,lq,k,n_seq,flag), per sequence name / len /
+ * forward_signals / reverse_signals, then the 2^14 buckets.  Also loads the signals as the context's reference mirror. */
+int ra_index_load_file(ra_ctx *ctx, const char *path, ra_index **out);
+/* Same from memory: keys[n_keys] ascending unique seed hashes (riv.a[i].x >> RI_HASH_SHIFT), key_off[n_keys+1] into vals[],
+ * vals = ref_id << 32 | position << 1 | strand (rsketch.h:40).  fwd/rev: ri_idx_t::forward_signals / reverse_signals. */
+int ra_index_load_flat(ra_ctx *ctx, int32_t w, int32_t e, int32_t n, int32_t q, int32_t lq, int32_t k, uint32_t n_seq, const uint32_t *seq_len,
+                       const float *const *fwd, const float *const *rev, uint64_t n_keys, const uint64_t *keys, const uint64_t *key_off,
+                       const uint64_t *vals, ra_index **out);
+void ra_index_destroy(ra_index *ix);
+/* out[0..8] = w, e, n, q, lq, k, n_seq, n_keys (low 32 bits), n_vals (low 32 bits); seq_len_out (optional) n_seq entries */
+int ra_index_info(const ra_index *ix, int32_t *out, uint32_t *seq_len_out);
+
+/* The numbers behind one PAF line (rmap.cpp:730-758, :954-972); the caller formats them (mt:f:, the per-read wall time, has no
+ * per-read meaning in a batch). */
+typedef struct ra_paf_s {
+	uint32_t mapped, ref_id, read_length, read_start_position, read_end_position, fragment_start_position, fragment_length, mapq, rev;
+	uint32_t ci, sl, cm, nc;          /* chunks used, l_sig, anchors of chain 0, chains */
+	float    s1, s2, sm, at, aq, alns;
+	uint32_t n_events;
+	uint32_t reserved;
+} ra_paf_t;
+
+/* Per-stage device time of the most recent ra_map_batch (milliseconds, CUDA events) and its work counters. */
+typedef struct ra_map_stats_s {
+	float    decode_ms, events_ms, seed_ms, sort_ms, chain_ms, dtw_ms, select_ms, total_ms;
+	uint32_t rounds; uint32_t reserved;
+	uint64_t chunks, events, seeds, anchors, chains_evaluated, launches;
+} ra_map_stats_t;
+
+/* Maps a batch of reads.  Signal either as int16 DAC samples (raw != NULL: read r is raw[raw_off[r] .. +raw_len[r]),
+ * offset[r] / scale[r] as in ra_detect_events_raw_batch; decoded on the device, rsig.cpp:213-222) or as float pA
+ * (raw == NULL: sig[sig_off[r] .. +sig_len[r]) = ri_sig_t::sig).  All pointers are host pointers.  out: n_reads records in
+ * input order.  Minimizer (w > 0) and BLEND (n > 0) indexes return RA_EUNSUP. */
+int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt,
+                 const int16_t *raw, const uint64_t *raw_off, const uint32_t *raw_len, const float *offset, const float *scale,
+                 const float *sig, const uint64_t *sig_off, const uint32_t *sig_len,
+                 uint32_t n_reads, ra_paf_t *out, ra_map_stats_t *stats);
+
 #ifdef __cplusplus
 }
 #endif

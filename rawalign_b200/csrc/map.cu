@@ -1,0 +1,257 @@
+// map.cu -- the map loop around the hot path, on the device (include/rawalign_b200.h, "ra_map_batch").
+//
+// Batched form of the reference's per-read map loop (src/rmap.cpp:667-822, map_worker_for): for every chunk round of a
+// batch of reads: event detection (K1, through ra_detect_events_batch_dev), seeding (ri_sketch_reg, src/rsketch.c:223-274),
+// index lookup (ri_idx_get, src/rawindex.cpp:256-273), anchor sort + chaining DP + traceback (gen_chains,
+// src/rmap.cpp:315-507), DTW evaluation of the candidate chains (the hot path, through ra_align_chains_batch_dev),
+// gen_primary_chains / comp_mapq (:65-128), is_mapped_with_high_confidence (:594-665) and, when a read leaves the loop, the
+// PAF fields of :696-800.  Nothing but the signal goes up and one ra_paf_t per read comes back.
+//
+// Layout per round (all device-resident):
+//   anchors of one read = one segment of 64-bit keys  ref:15 | strand:1 | target:31 | query:17  (the reference sorts every
+//   (strand, ref) list by (target, query), rmap.cpp:396-401, and walks the lists ref-major, strand 0 then 1, :429-430: one
+//   ascending sort of the packed key gives both), padded to a power of two for the bitonic network;
+//   score / predecessor / used flags parallel to the keys; chain anchors (ra_anchor_t, chain END first as traceback_chains
+//   emits them, :130-173) in one of two arenas that alternate between rounds, so that the chains kept for re-injection into
+//   the next round (:343-357) stay readable while the next round writes its own.
+#include "ra_common.cuh"
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <cstdlib>
+#include <string>
+#include <vector>
+
+extern "C" void ra__add_launches(ra_ctx *ctx, uint64_t n);        // api.cu
+extern "C" int ra__fail(int code, const char *fmt, ...);            // api.cu: sets ra_last_error()
+
+namespace {
+
+#define MAP_CUDA(call)                                                                                  \
+	do {                                                                                                \
+		cudaError_t e__ = (call);                                                                       \
+		if (e__ != cudaSuccess) return ra__fail(RA_ECUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+	} while (0)
+
+constexpr int kQueryBits = 17, kTargetBits = 31, kRefShift = kQueryBits + kTargetBits + 1;     // 49
+constexpr uint32_t kMaxSeq = 1u << (64 - kRefShift);                                           // 32768 sequences
+constexpr uint64_t kPadKey = ~0ull;
+
+struct Buf {                                                       // grow-only device buffer
+	void *p = nullptr; size_t cap = 0;
+	int reserve(size_t bytes)
+	{
+		if (bytes <= cap) return RA_OK;
+		if (p) cudaFree(p);
+		p = nullptr; cap = 0;
+		const size_t want = bytes + bytes / 4 + 256;
+		if (cudaMalloc(&p, want) != cudaSuccess) { (void)cudaGetLastError(); p = nullptr; return ra__fail(RA_ENOMEM, "cudaMalloc(%zu) failed", want); }
+		cap = want;
+		return RA_OK;
+	}
+	void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+	template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+struct Slot { uint32_t key, cnt; uint64_t off; };                  // cnt == 0: empty
+
+struct ChainRec {                                                  // ri_chain_t (rmap.h:30-46) with the anchors as an arena offset
+	float chaining_score, alignment_score;
+	uint32_t ref, start_position, end_position, n_anchors;
+	uint32_t mapq, strand;
+	uint64_t anchor_off;
+};
+
+struct ReadState {
+	uint64_t sig_off; uint32_t l_sig;                              // ri_sig_t::sig / l_sig
+	uint64_t ev_base; uint32_t n_events;                           // p->events[read_id]
+	uint32_t offset;                                               // reg->offset
+	uint32_t chunk_start, current_chunk;                           // the loop variables of rmap.cpp:685
+	uint32_t n_chains;                                             // reg->n_chains
+	uint32_t active, done;
+	uint32_t arena;                                                // which chain-anchor arena holds reg->chains' anchors
+};
+
+} // namespace
+
+struct ra_index {
+	ra_ctx *ctx = nullptr;
+	int32_t w = 0, e = 0, n = 0, q = 0, lq = 0, k = 0;
+	uint32_t n_seq = 0;
+	uint64_t n_keys = 0, n_vals = 0;
+	std::vector<uint32_t> seq_len;
+	std::vector<std::string> names;
+	Buf slots, vals, seq_tab;                                      // seq_tab: per sequence {fwd_off u64, rev_off u64, len u64}
+	uint32_t slot_bits = 0;
+	// per-context scratch of ra_map_batch lives with the index (one index per context)
+	Buf raw16, rd_off, rd_len, rd_offset, rd_scale, sig, state, chains, chains_tmp, paf;
+	Buf act, coff, clen, ev_round, evoff_round, ev, seeds_h, seeds_p, seed_cnt, seed_off, n_seed, n_hits, seg_n, seg_base, counters;
+	Buf keys, score, pred, used, anc[2], cand, n_cand, cand_base, dtw_chains, group_first, dscore, dkeep, scan_tmp;
+	void *pin = nullptr; size_t pin_cap = 0;
+	cudaStream_t stream = nullptr;
+	cudaEvent_t ev_t[16] = {};
+};
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------------------------
+// host: index file -> flat table -> device open-addressing table
+// ---------------------------------------------------------------------------------------------------------------
+int build_device_index(ra_ctx *ctx, ra_index *ix, const float *const *fwd, const float *const *rev, const uint64_t *keys, const uint64_t *key_off,
+                       const uint64_t *vals)
+{
+	if (ix->n_seq == 0 || ix->n_seq > kMaxSeq) return ra__fail(RA_EUNSUP, "%u reference sequences (supported: 1..%u)", ix->n_seq, kMaxSeq);
+	std::vector<uint64_t> arena_off(2 * (size_t)ix->n_seq);
+	int rc = ra_ref_load(ctx, ix->n_seq, fwd, rev, ix->seq_len.data(), arena_off.data());
+	if (rc) return rc;
+	std::vector<uint64_t> tab(3 * (size_t)ix->n_seq);
+	for (uint32_t i = 0; i < ix->n_seq; ++i) { tab[3 * i] = arena_off[2 * i]; tab[3 * i + 1] = arena_off[2 * i + 1]; tab[3 * i + 2] = ix->seq_len[i]; }
+	if ((rc = ix->seq_tab.reserve(tab.size() * 8))) return rc;
+	MAP_CUDA(cudaMemcpy(ix->seq_tab.p, tab.data(), tab.size() * 8, cudaMemcpyHostToDevice));
+	uint32_t bits = 4;
+	while ((1ull << bits) < 2 * ix->n_keys + 16) ++bits;
+	if (bits > 31) return ra__fail(RA_EUNSUP, "index has too many distinct seeds (%llu)", (unsigned long long)ix->n_keys);
+	ix->slot_bits = bits;
+	const uint64_t n_slots = 1ull << bits;
+	std::vector<Slot> slots(n_slots, Slot{0, 0, 0});
+	for (uint64_t i = 0; i < ix->n_keys; ++i) {
+		if (keys[i] >> 32) return ra__fail(RA_EINVAL, "seed hash %llu does not fit 32 bits (rsketch.c masks hash64 to 32 bits)", (unsigned long long)keys[i]);
+		const uint32_t key = (uint32_t)keys[i];
+		uint64_t h = ((uint32_t)(key * 0x9E3779B1u)) >> (32 - bits);
+		while (slots[h].cnt) h = (h + 1) & (n_slots - 1);
+		slots[h].key = key; slots[h].cnt = (uint32_t)(key_off[i + 1] - key_off[i]); slots[h].off = key_off[i];
+	}
+	if ((rc = ix->slots.reserve(n_slots * sizeof(Slot)))) return rc;
+	MAP_CUDA(cudaMemcpy(ix->slots.p, slots.data(), n_slots * sizeof(Slot), cudaMemcpyHostToDevice));
+	if ((rc = ix->vals.reserve(std::max<uint64_t>(ix->n_vals, 1) * 8))) return rc;
+	if (ix->n_vals) MAP_CUDA(cudaMemcpy(ix->vals.p, vals, ix->n_vals * 8, cudaMemcpyHostToDevice));
+	MAP_CUDA(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
+	for (auto &e : ix->ev_t) MAP_CUDA(cudaEventCreate(&e));
+	return RA_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+void ra_ri_mapopt_init(ra_ri_mapopt_t *o)
+{
+	memset(o, 0, sizeof(*o));
+	o->bp_per_sec = 450; o->sample_rate = 4000; o->chunk_size = 4000;
+	o->max_gap_length = 2000; o->max_target_gap_length = 5000; o->chaining_band_length = 5000; o->max_num_skips = 25;
+	o->min_num_anchors = 2; o->num_best_chains = 3; o->min_chaining_score = 10.0f;
+	o->step_size = 1; o->min_events = 50; o->max_num_chunk = 30; o->min_chain_anchor = 2; o->min_chain_anchor_out = 2;
+	o->min_bestmap_ratio = 1.2f; o->min_bestmap_ratio_out = 1.2f; o->min_meanmap_ratio = 5; o->min_meanmap_ratio_out = 5;
+	o->mini_batch_size = 500000000;
+	o->window_length1 = 3; o->window_length2 = 6; o->threshold1 = 4.30265f; o->threshold2 = 2.57058f; o->peak_height = 1.0f;
+	o->t_threshold = 1.5f; o->tn_samples = 5; o->ttest_freq = 500; o->tmin_reads = 500;
+	o->dtw_border_constraint = RA_DTW_BORDER_CONSTRAINT_SPARSE; o->dtw_fill_method = RA_DTW_FILL_METHOD_BANDED;
+	o->dtw_band_radius_frac = 0.10f; o->dtw_match_bonus = 0.4f; o->dtw_min_score = 20.0f;
+}
+
+int ra_index_load_flat(ra_ctx *ctx, int32_t w, int32_t e, int32_t n, int32_t q, int32_t lq, int32_t k, uint32_t n_seq, const uint32_t *seq_len,
+                       const float *const *fwd, const float *const *rev, uint64_t n_keys, const uint64_t *keys, const uint64_t *key_off,
+                       const uint64_t *vals, ra_index **out)
+{
+	if (!ctx || !out || !seq_len || !fwd || !rev || (n_keys && (!keys || !key_off || !vals))) return ra__fail(RA_EINVAL, "NULL argument");
+	if (e < 2 || e > 9 || (lq + 2) * e > 63 || q < 1 || q > 32 || lq < 0 || lq > q) return ra__fail(RA_EINVAL, "bad sketch parameters e=%d q=%d lq=%d", e, q, lq);
+	ra_index *ix = new ra_index();
+	ix->ctx = ctx; ix->w = w; ix->e = e; ix->n = n; ix->q = q; ix->lq = lq; ix->k = k; ix->n_seq = n_seq; ix->n_keys = n_keys;
+	ix->n_vals = n_keys ? key_off[n_keys] : 0;
+	ix->seq_len.assign(seq_len, seq_len + n_seq);
+	int rc = build_device_index(ctx, ix, fwd, rev, keys, key_off, vals);
+	if (rc) { ra_index_destroy(ix); return rc; }
+	*out = ix;
+	return RA_OK;
+}
+
+// rawindex.cpp:275-315 (ri_idx_dump) read back: see the header comment.
+int ra_index_load_file(ra_ctx *ctx, const char *path, ra_index **out)
+{
+	if (!ctx || !path || !out) return ra__fail(RA_EINVAL, "NULL argument");
+	FILE *f = fopen(path, "rb");
+	if (!f) return ra__fail(RA_EINVAL, "cannot open index file %s", path);
+	auto bad = [&](const char *what) { fclose(f); return ra__fail(RA_EINVAL, "index file %s: %s", path, what); };
+	char magic[2];
+	uint32_t pars[8];
+	if (fread(magic, 1, 2, f) != 2 || magic[0] != 'R' || magic[1] != 'I') return bad("bad magic");
+	if (fread(pars, 4, 8, f) != 8) return bad("truncated header");
+	const uint32_t n_seq = pars[6];
+	std::vector<uint32_t> seq_len(n_seq);
+	std::vector<std::vector<float>> fw(n_seq), rv(n_seq);
+	std::vector<std::string> names(n_seq);
+	for (uint32_t i = 0; i < n_seq; ++i) {
+		uint8_t l;
+		if (fread(&l, 1, 1, f) != 1) return bad("truncated sequence table");
+		names[i].resize(l);
+		if (l && fread(&names[i][0], 1, l, f) != l) return bad("truncated sequence name");
+		if (fread(&seq_len[i], 4, 1, f) != 1) return bad("truncated sequence length");
+		fw[i].resize(seq_len[i]); rv[i].resize(seq_len[i]);
+		if (fread(fw[i].data(), 4, seq_len[i], f) != seq_len[i] || fread(rv[i].data(), 4, seq_len[i], f) != seq_len[i]) return bad("truncated signal");
+	}
+	const int b = 14;                                              // ri_idx_load: ri_idx_init(14, ...), rawindex.cpp:330
+	struct KV { uint64_t hash, start, cnt; };
+	std::vector<KV> kv;
+	std::vector<uint64_t> pool;                                    // every bucket's p[] and the single positions, in file order
+	for (uint32_t i = 0; i < (1u << b); ++i) {
+		int32_t nb; uint32_t size;
+		if (fread(&nb, 4, 1, f) != 1) return bad("truncated bucket");
+		const uint64_t pbase = pool.size();
+		pool.resize(pbase + (size_t)nb);
+		if (nb && fread(pool.data() + pbase, 8, (size_t)nb, f) != (size_t)nb) return bad("truncated bucket positions");
+		if (fread(&size, 4, 1, f) != 1) return bad("truncated bucket");
+		for (uint32_t j = 0; j < size; ++j) {
+			uint64_t x[2];
+			if (fread(x, 8, 2, f) != 2) return bad("truncated hash table");
+			const uint64_t hash = ((x[0] >> 1) << b) | i;          // key = hash >> b << 1 | single (rawindex.cpp:222-226)
+			if (x[0] & 1) { pool.push_back(x[1]); kv.push_back({hash, pool.size() - 1, 1}); }
+			else kv.push_back({hash, pbase + (x[1] >> 32), (uint32_t)x[1]});
+		}
+	}
+	fclose(f);
+	std::sort(kv.begin(), kv.end(), [](const KV &a, const KV &c) { return a.hash < c.hash; });
+	std::vector<uint64_t> keys(kv.size()), key_off(kv.size() + 1), vals;
+	uint64_t tot = 0;
+	for (auto &x : kv) tot += x.cnt;
+	vals.reserve(tot);
+	for (size_t i = 0; i < kv.size(); ++i) {
+		keys[i] = kv[i].hash; key_off[i] = vals.size();
+		vals.insert(vals.end(), pool.begin() + kv[i].start, pool.begin() + kv[i].start + kv[i].cnt);
+	}
+	key_off[kv.size()] = vals.size();
+	std::vector<const float *> fp(n_seq), rp(n_seq);
+	for (uint32_t i = 0; i < n_seq; ++i) { fp[i] = fw[i].data(); rp[i] = rv[i].data(); }
+	int rc = ra_index_load_flat(ctx, (int32_t)pars[0], (int32_t)pars[1], (int32_t)pars[2], (int32_t)pars[3], (int32_t)pars[4], (int32_t)pars[5], n_seq,
+	                            seq_len.data(), fp.data(), rp.data(), keys.size(), keys.data(), key_off.data(), vals.data(), out);
+	if (rc == RA_OK) (*out)->names = names;
+	return rc;
+}
+
+void ra_index_destroy(ra_index *ix)
+{
+	if (!ix) return;
+	Buf *all[] = { &ix->slots, &ix->vals, &ix->seq_tab, &ix->raw16, &ix->rd_off, &ix->rd_len, &ix->rd_offset, &ix->rd_scale, &ix->sig, &ix->state, &ix->chains,
+	               &ix->chains_tmp, &ix->paf, &ix->act, &ix->coff, &ix->clen, &ix->ev_round, &ix->evoff_round, &ix->ev, &ix->seeds_h, &ix->seeds_p,
+	               &ix->seed_cnt, &ix->seed_off, &ix->n_seed, &ix->n_hits, &ix->seg_n, &ix->seg_base, &ix->counters, &ix->keys, &ix->score, &ix->pred,
+	               &ix->used, &ix->anc[0], &ix->anc[1], &ix->cand, &ix->n_cand, &ix->cand_base, &ix->dtw_chains, &ix->group_first, &ix->dscore,
+	               &ix->dkeep, &ix->scan_tmp };
+	for (Buf *b : all) b->release();
+	if (ix->pin) cudaFreeHost(ix->pin);
+	if (ix->stream) cudaStreamDestroy(ix->stream);
+	for (auto &e : ix->ev_t) if (e) cudaEventDestroy(e);
+	delete ix;
+}
+
+int ra_index_info(const ra_index *ix, int32_t *out, uint32_t *seq_len_out)
+{
+	if (!ix || !out) return ra__fail(RA_EINVAL, "NULL argument");
+	out[0] = ix->w; out[1] = ix->e; out[2] = ix->n; out[3] = ix->q; out[4] = ix->lq; out[5] = ix->k; out[6] = (int32_t)ix->n_seq;
+	out[7] = (int32_t)ix->n_keys; out[8] = (int32_t)ix->n_vals;
+	if (seq_len_out) memcpy(seq_len_out, ix->seq_len.data(), ix->n_seq * 4);
+	return RA_OK;
+}
+
+} // extern "C"
+
+#include "map_kernels.cuh"
+#include "map_batch.cuh"

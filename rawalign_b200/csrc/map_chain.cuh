@@ -1,0 +1,290 @@
+// map_chain.cuh -- chaining DP, traceback, chain selection and the PAF fields (included by map.cu only).
+#pragma once
+
+namespace mapk {
+
+constexpr int kMaxBest = 8;                                        // num_best_chains supported (default 3, roptions.c:18)
+
+// traceback_chains, rmap.cpp:130-173.  score / pred / used are indexed like the keys of the segment (pred = segment index).
+__device__ __forceinline__ bool traceback(const uint64_t *__restrict__ keys, const float *__restrict__ score, const uint32_t *__restrict__ pred,
+                                          uint8_t *__restrict__ used, uint32_t end_idx, int min_num_anchors, ra_anchor_t *__restrict__ out,
+                                          ChainRec *rec)
+{
+	if (used[end_idx]) return false;                               // :139
+	bool stop_at_used = false;
+	uint32_t start = end_idx, n = 1;
+	out[0] = ra_anchor_t{ key_target(keys[start]), key_query(keys[start]) };
+	if (pred[start] != start && used[pred[start]]) stop_at_used = true;
+	used[start] = 1;
+	while (pred[start] != start && !used[pred[start]]) {
+		start = pred[start];
+		out[n] = ra_anchor_t{ key_target(keys[start]), key_query(keys[start]) };
+		if (pred[start] != start && used[pred[start]]) stop_at_used = true;
+		used[start] = 1;
+		++n;
+	}
+	if (n < (uint32_t)min_num_anchors) return false;               // :159
+	float adj = score[end_idx];
+	if (stop_at_used) adj = __fsub_rn(adj, score[pred[start]]);    // :161-163
+	rec->chaining_score = adj; rec->alignment_score = 0.0f;
+	rec->start_position = key_target(keys[start]); rec->end_position = key_target(keys[end_idx]);
+	rec->n_anchors = n; rec->mapq = 0;
+	return true;
+}
+
+// Chaining DP of gen_chains (rmap.cpp:427-507) for every (ref, strand) list of one read, in the reference's list order,
+// with the running max_chaining_score shared by the lists (:428).  One warp per read; the recurrences (the predecessor scan
+// with its skip counter, the running maximum, the used flags of the tracebacks) are sequential, so lane 0 walks them.
+// Candidate chains go to cand[i * cap + k] in generation order, or sorted by chaining score (stable, :512) when they are to
+// be evaluated by DTW.
+__global__ void __launch_bounds__(128)
+k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_base,
+        const uint32_t *__restrict__ seg_n, const uint32_t *__restrict__ skip, float *__restrict__ score, uint32_t *__restrict__ pred,
+        uint8_t *__restrict__ used, ra_anchor_t *__restrict__ anc_cur, ChainRec *__restrict__ cand, uint32_t *__restrict__ n_cand)
+{
+	const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const int lane = threadIdx.x & 31;
+	if (i >= n_act) return;
+	if (skip[i]) { if (lane == 0) n_cand[i] = 0; return; }
+	const uint64_t base = seg_base[i];
+	const uint32_t n = seg_n[i];
+	const uint64_t *__restrict__ K = keys + base;
+	float *__restrict__ S = score + base;
+	uint32_t *__restrict__ Pd = pred + base;
+	uint8_t *__restrict__ U = used + base;
+	for (uint32_t k = lane; k < n; k += 32) U[k] = 0;
+	__syncwarp();
+	if (lane != 0) return;
+	ChainRec *out = cand + (size_t)i * P.cap_chains;
+	uint32_t nc = 0;
+	uint64_t wo = base;                                            // next free chain-anchor slot of this read
+	float max_chaining_score = 0.0f;                               // :428
+	const float fe = (float)P.e;
+	uint32_t ls = 0;
+	while (ls < n) {
+		const uint32_t list = key_list(K[ls]);
+		float cs[kMaxBest]; uint32_t ci[kMaxBest]; int ncand = 0;
+		uint32_t ai = ls;
+		for (; ai < n; ++ai) {
+			const uint64_t kc = K[ai];
+			if (key_list(kc) != list) break;
+			float sc = fe; uint32_t pr = ai;                       // :442-443
+			const int32_t ct = (int32_t)key_target(kc), cq = (int32_t)key_query(kc);
+			uint32_t start = ls;
+			if (ai - ls > (uint32_t)P.chaining_band_length) start = ai - (uint32_t)P.chaining_band_length;   // :448
+			int32_t num_skips = 0;
+			for (uint32_t pi = ai; pi-- > start;) {                // :452
+				const uint64_t kp = K[pi];
+				const int32_t pt = (int32_t)key_target(kp), pq = (int32_t)key_query(kp);
+				if (pq == cq) continue;
+				if (pt == ct) continue;
+				if (pt + P.max_target_gap_length < ct) break;      // :458
+				const int32_t td = ct - pt, qd = cq - pq;
+				if (qd < 0) continue;                              // :465
+				float cur = 0.0f;
+				const int32_t md = min(min(td, qd), P.e);
+				const int32_t gap = abs(td - qd);
+				const float gap_scale = td > 0 ? __fdiv_rn((float)qd, (float)td) : 1.0f;   // :469
+				if (gap < P.max_gap_length && gap_scale < 5.0f && gap_scale > 0.75f) cur = __fadd_rn(S[pi], (float)md);   // :472-474
+				if (cur > sc) { sc = cur; pr = pi; --num_skips; }
+				else { ++num_skips; if (num_skips > P.max_num_skips) break; }
+			}
+			S[ai] = sc; Pd[ai] = pr;
+			if (sc > max_chaining_score) max_chaining_score = sc;  // :485-487
+			if (P.no_filter || (sc >= P.min_chaining_score && sc > max_chaining_score / 2)) {   // :488-492
+				// keep the num_best_chains best by (score desc, index desc) (compare(), :175-179): ai only grows, so a tie goes in front
+				int p = 0;
+				while (p < ncand && !(sc >= cs[p])) ++p;
+				if (p < P.num_best_chains) {
+					const int lastp = min(ncand, P.num_best_chains - 1);
+					for (int t = lastp; t > p; --t) { cs[t] = cs[t - 1]; ci[t] = ci[t - 1]; }
+					cs[p] = sc; ci[p] = ai;
+					if (ncand < P.num_best_chains) ++ncand;
+				}
+			}
+		}
+		for (int k = 0; k < ncand; ++k) {                          // :498-505
+			ChainRec rec;
+			if (nc < P.cap_chains && traceback(K, S, Pd, U, ci[k], P.min_num_anchors, anc_cur + wo, &rec)) {
+				rec.ref = list >> 1; rec.strand = list & 1u; rec.anchor_off = wo;
+				wo += rec.n_anchors;
+				out[nc++] = rec;
+			}
+			if (!P.no_filter && S[ci[k]] < max_chaining_score / 2) break;
+		}
+		ls = ai;
+	}
+	if (P.dtw)                                                     // :512, insertion sort = libstdc++'s std::sort for <= 16 elements
+		for (uint32_t a = 1; a < nc; ++a) {
+			const ChainRec x = out[a];
+			uint32_t b = a;
+			while (b > 0 && x.chaining_score > out[b - 1].chaining_score) { out[b] = out[b - 1]; --b; }
+			out[b] = x;
+		}
+	n_cand[i] = nc;
+}
+
+// the candidates as ra_chain_t for ra_align_chains_batch_dev: one group per active read (possibly empty)
+__global__ void __launch_bounds__(128)
+k_emit_dtw_chains(const ReadState *__restrict__ st, const uint32_t *__restrict__ act, uint32_t n_act, Params P, const ChainRec *__restrict__ cand,
+                  const uint32_t *__restrict__ n_cand, const uint64_t *__restrict__ cand_base, const uint64_t *__restrict__ seq_tab,
+                  ra_chain_t *__restrict__ out, uint32_t *__restrict__ group_first)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i > n_act) return;
+	group_first[i] = (uint32_t)cand_base[i];
+	if (i == n_act) return;
+	const uint32_t r = act[i];
+	const ChainRec *c = cand + (size_t)i * P.cap_chains;
+	const uint64_t b = cand_base[i];
+	for (uint32_t k = 0; k < n_cand[i]; ++k) {
+		ra_chain_t o;
+		o.anchor_off = c[k].anchor_off; o.n_anchors = c[k].n_anchors; o.group = i; o.read_off = st[r].ev_base;
+		o.ref_off = seq_tab[3 * (size_t)c[k].ref + (c[k].strand == 1 ? 0 : 1)];                     // rmap.cpp:183-188
+		out[b + k] = o;
+	}
+}
+
+__device__ __forceinline__ bool tuple_greater(const ChainRec &a, const ChainRec &b)                  // rmap.h:41-45
+{
+	if (a.alignment_score != b.alignment_score) return a.alignment_score > b.alignment_score;
+	if (a.chaining_score != b.chaining_score) return a.chaining_score > b.chaining_score;
+	if (a.n_anchors != b.n_anchors) return a.n_anchors > b.n_anchors;
+	if (a.strand != b.strand) return a.strand > b.strand;
+	if (a.ref != b.ref) return a.ref > b.ref;
+	if (a.start_position != b.start_position) return a.start_position > b.start_position;
+	return a.end_position > b.end_position;
+}
+
+// is_mapped_with_high_confidence, rmap.cpp:594-665
+__device__ __forceinline__ bool is_mapped(const ChainRec *c, uint32_t n_chains, const Params &P)
+{
+	const uint32_t n_anchors0 = n_chains ? c[0].n_anchors : 0u;
+	if (n_anchors0 == 0) return false;
+#define RA_SC(x) (P.dtw ? (x).alignment_score : (x).chaining_score)
+	if (n_chains >= 2) {
+		if (__fdiv_rn(RA_SC(c[0]), RA_SC(c[1])) >= P.min_bestmap_ratio) return true;
+		float mean = 0.0f;
+		for (uint32_t k = 0; k < n_chains; ++k) mean = __fadd_rn(mean, RA_SC(c[k]));
+		mean = __fdiv_rn(mean, (float)n_chains);
+		if (RA_SC(c[0]) >= __fmul_rn(P.min_meanmap_ratio, mean)) return true;
+	} else if (n_chains == 1 && c[0].n_anchors >= P.min_chain_anchor) return true;
+#undef RA_SC
+	return false;
+}
+
+// After the DTW evaluation of a round: the filter of rmap.cpp:518-523, gen_primary_chains (:90-128), comp_mapq (:65-88), the
+// loop control of :685-693 and, for reads leaving the loop, the PAF fields of :696-800.  One thread per active read.
+__global__ void __launch_bounds__(64)
+k_select(ReadState *__restrict__ st, const uint32_t *__restrict__ act, uint32_t n_act, Params P, ChainRec *__restrict__ cand,
+         const uint32_t *__restrict__ n_cand, const uint64_t *__restrict__ cand_base, const float *__restrict__ dscore, const uint8_t *__restrict__ dkeep,
+         const uint32_t *__restrict__ skip, ChainRec *__restrict__ chains, const ra_anchor_t *__restrict__ anc_cur, uint32_t cur_arena,
+         const uint64_t *__restrict__ seq_tab, ra_paf_t *__restrict__ paf, uint32_t *__restrict__ counters /* [2] still active */)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_act) return;
+	const uint32_t r = act[i];
+	ReadState s = st[r];
+	ChainRec *rc = chains + (size_t)r * P.cap_chains;
+	if (!skip[i]) {
+		ChainRec *c = cand + (size_t)i * P.cap_chains;
+		uint32_t n = n_cand[i];
+		if (P.dtw) {                                               // :515-527
+			const uint64_t b = cand_base[i];
+			uint32_t m = 0;
+			for (uint32_t k = 0; k < n; ++k) {
+				ChainRec x = c[k];
+				x.alignment_score = dscore[b + k];
+				if (dkeep[b + k]) c[m++] = x;
+			}
+			n = m;
+		}
+		uint32_t np = 0;
+		if (n > 0) {
+			for (uint32_t a = 1; a < n; ++a) {                     // std::sort(greater) :91 (stable insertion)
+				const ChainRec x = c[a];
+				uint32_t b = a;
+				while (b > 0 && tuple_greater(x, c[b - 1])) { c[b] = c[b - 1]; --b; }
+				c[b] = x;
+			}
+			rc[np++] = c[0];
+			for (uint32_t ci = 1; ci < n; ++ci) {
+				const ChainRec &last = rc[np - 1];
+				if (P.dtw) { if (c[ci].alignment_score < __fdiv_rn(last.alignment_score, 3.0f)) break; }   // :100-104
+				else if (c[ci].chaining_score < __fdiv_rn(last.chaining_score, 3.0f)) break;
+				bool primary = true;
+				for (uint32_t pi = 0; pi < np; ++pi)
+					if (c[ci].ref == rc[pi].ref && max(c[ci].start_position, rc[pi].start_position) <= min(c[ci].end_position, rc[pi].end_position)) { primary = false; break; }
+				if (primary) rc[np++] = c[ci];
+			}
+			if (np == 1) rc[0].mapq = 60;                          // comp_mapq
+			else {
+				const float q = P.dtw ? __fdiv_rn(rc[1].alignment_score, rc[0].alignment_score) : __fdiv_rn(rc[1].chaining_score, rc[0].chaining_score);
+				int mapq = (int)__fmul_rn(40.0f, __fsub_rn(1.0f, q));
+				mapq = min(60, max(0, mapq));
+				rc[0].mapq = (uint32_t)mapq;
+			}
+		}
+		s.n_chains = np; s.arena = cur_arena;
+		s.offset += (uint32_t)0;                                   // reg->offset is advanced by the caller-side bookkeeping below
+	}
+	const bool mapped = is_mapped(rc, s.n_chains, P);
+	bool leave = mapped;
+	if (!mapped) {                                                 // :685: chunk_start += l_chunk, ++current_chunk
+		s.chunk_start += P.chunk_size; s.current_chunk += 1;
+		if (s.chunk_start >= s.l_sig || s.current_chunk >= P.max_num_chunk) leave = true;
+	}
+	if (leave) {
+		s.active = 0; s.done = 1;
+		uint32_t current_chunk = s.current_chunk;
+		if (current_chunk > 0 && (s.chunk_start >= s.l_sig || current_chunk == P.max_num_chunk)) --current_chunk;   // :696
+		const float scale = __fdiv_rn(__fdiv_rn(__fmul_rn((float)(current_chunk + 1), (float)P.chunk_size), (float)s.offset),
+		                              __fdiv_rn((float)P.sample_rate, (float)P.bp_per_sec));                      // :698
+		const uint32_t n_chains = s.n_chains;
+		const uint32_t n_anchors0 = n_chains ? rc[0].n_anchors : 0u;
+		float mean_chain_score = 0.0f;
+		for (uint32_t k = 0; k < n_chains; ++k) mean_chain_score = __fadd_rn(mean_chain_score, rc[k].chaining_score);
+		mean_chain_score = __fdiv_rn(mean_chain_score, (float)n_chains);
+		ra_paf_t o; memset(&o, 0, sizeof(o));
+		o.ci = current_chunk + 1; o.sl = s.l_sig; o.n_events = s.n_events;
+		float at = 0.0f, aq = 0.0f;
+		const ra_anchor_t *a0 = n_chains ? anc_cur + rc[0].anchor_off : nullptr;
+		for (uint32_t ai = 0; ai + 1 < n_anchors0; ++ai) {
+			at = __fadd_rn(at, (float)(a0[ai].target_position - a0[ai + 1].target_position));
+			aq = __fadd_rn(aq, (float)(a0[ai].query_position - a0[ai + 1].query_position));
+		}
+		if (mapped) {
+			at = __fdiv_rn(at, (float)n_anchors0); aq = __fdiv_rn(aq, (float)n_anchors0);
+			o.mapped = 1; o.cm = n_anchors0; o.nc = n_chains; o.s1 = rc[0].chaining_score; o.s2 = n_chains > 1 ? rc[1].chaining_score : 0.0f;
+			o.sm = mean_chain_score; o.at = at; o.aq = aq; o.alns = rc[0].alignment_score;
+			o.ref_id = rc[0].ref;
+			o.read_length = (uint32_t)__fmul_rn(scale, (float)a0[0].query_position);
+			o.read_start_position = (uint32_t)__fmul_rn(scale, (float)a0[n_anchors0 - 1].query_position);
+			o.read_end_position = (uint32_t)__fmul_rn(scale, (float)a0[0].query_position);
+			const uint32_t ref_len = (uint32_t)seq_tab[3 * (size_t)rc[0].ref + 2];
+			o.fragment_start_position = rc[0].strand ? (ref_len + 1u - rc[0].end_position) : rc[0].start_position;
+			o.fragment_length = rc[0].end_position - rc[0].start_position + 1u;
+			o.mapq = rc[0].mapq & 63u; o.rev = rc[0].strand & 1u;
+		} else {
+			if (n_chains >= 1) {
+				if (n_anchors0) { at = __fdiv_rn(at, (float)n_anchors0); aq = __fdiv_rn(aq, (float)n_anchors0); }
+				o.cm = n_anchors0; o.nc = n_chains; o.s1 = rc[0].chaining_score; o.s2 = n_chains > 1 ? rc[1].chaining_score : 0.0f;
+				o.sm = mean_chain_score; o.at = at; o.aq = aq;
+			}
+			o.read_length = (uint32_t)__fmul_rn(scale, (float)s.offset);
+		}
+		paf[r] = o;
+	} else atomicAdd(&counters[2], 1u);
+	st[r] = s;
+}
+
+// reg->offset += n_chunk_events for the reads that chained this round (rmap.cpp:575), before k_select looks at it
+__global__ void k_advance_offset(ReadState *__restrict__ st, const uint32_t *__restrict__ act, uint32_t n_act, const uint64_t *__restrict__ evoff,
+                                 const uint32_t *__restrict__ skip)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n_act || skip[i]) return;
+	st[act[i]].offset += (uint32_t)(evoff[i + 1] - evoff[i]);
+}
+
+} // namespace mapk

@@ -1,0 +1,293 @@
+// map_kernels.cuh -- device kernels of the map loop (included by map.cu only).
+#pragma once
+
+namespace mapk {
+
+struct Params {                                                    // what the kernels read from ri_mapopt_t / ri_idx_t
+	uint32_t chunk_size, max_num_chunk, min_events;
+	int32_t max_gap_length, max_target_gap_length, chaining_band_length, max_num_skips, min_num_anchors, num_best_chains;
+	float min_chaining_score;
+	uint32_t min_chain_anchor;
+	float min_bestmap_ratio, min_meanmap_ratio, dtw_min_score;
+	uint32_t sample_rate, bp_per_sec;
+	uint32_t dtw, no_filter;                                       // RI_M_DTW_EVALUATE_CHAINS, RI_M_DISABLE_CHAININGSCORE_FILTERING
+	int32_t e, q, lq;
+	uint32_t n_seq, cap_chains, slot_bits;
+};
+
+__device__ __forceinline__ uint64_t hash64(uint64_t key, uint64_t mask)                  // rsketch.c:6-15
+{
+	key = (~key + (key << 21)) & mask;
+	key = key ^ key >> 24;
+	key = ((key + (key << 3)) + (key << 8)) & mask;
+	key = key ^ key >> 14;
+	key = ((key + (key << 2)) + (key << 4)) & mask;
+	key = key ^ key >> 28;
+	key = (key + (key << 31)) & mask;
+	return key;
+}
+
+__device__ __forceinline__ uint64_t pack_key(uint32_t ref, uint32_t strand, uint32_t target, uint32_t query)
+{
+	return ((uint64_t)ref << kRefShift) | ((uint64_t)strand << (kQueryBits + kTargetBits)) | ((uint64_t)target << kQueryBits) | (uint64_t)query;
+}
+__device__ __forceinline__ uint32_t key_target(uint64_t k) { return (uint32_t)(k >> kQueryBits) & 0x7fffffffu; }
+__device__ __forceinline__ uint32_t key_query(uint64_t k) { return (uint32_t)k & ((1u << kQueryBits) - 1u); }
+__device__ __forceinline__ uint32_t key_list(uint64_t k) { return (uint32_t)(k >> (kQueryBits + kTargetBits)); }   // ref << 1 | strand
+
+// ---------------------------------------------------------------------------------------------------------------
+// round set-up: the reads still in the chunk loop of rmap.cpp:685, in read order, and their next chunk
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024)
+k_round_setup(ReadState *__restrict__ st, uint32_t n_reads, Params P, uint32_t *__restrict__ act, uint64_t *__restrict__ coff,
+              uint32_t *__restrict__ clen, uint32_t *__restrict__ counters /* [0] n_act, [1] max chunk length */)
+{
+	__shared__ uint32_t warp_tot[32];
+	__shared__ uint32_t base_s, maxlen_s;
+	const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+	if (tid == 0) { base_s = 0; maxlen_s = 0; }
+	__syncthreads();
+	for (uint32_t r0 = 0; r0 < n_reads; r0 += 1024) {
+		const uint32_t r = r0 + tid;
+		const bool on = r < n_reads && st[r].active;
+		const uint32_t m = __ballot_sync(0xffffffffu, on);
+		if (lane == 0) warp_tot[wid] = __popc(m);
+		__syncthreads();
+		uint32_t before = 0, total = 0;
+		for (int w = 0; w < 32; ++w) { const uint32_t t = warp_tot[w]; if (w < wid) before += t; total += t; }
+		const uint32_t base = base_s;
+		if (on) {
+			const uint32_t i = base + before + __popc(m & ((1u << lane) - 1u));
+			const ReadState s = st[r];
+			const uint32_t len = min(P.chunk_size, s.l_sig - s.chunk_start);                      // rmap.cpp:686-687
+			act[i] = r; coff[i] = s.sig_off + s.chunk_start; clen[i] = len;
+			atomicMax(&maxlen_s, len);
+		}
+		__syncthreads();
+		if (tid == 0) base_s = base + total;
+		__syncthreads();
+	}
+	if (tid == 0) { counters[0] = base_s; counters[1] = maxlen_s; }
+}
+
+// events of the round's chunks (packed CSR over the active list) appended to each read's event array, rmap.cpp:554-567
+__global__ void __launch_bounds__(128)
+k_append_events(ReadState *__restrict__ st, const uint32_t *__restrict__ act, uint32_t n_act, const float *__restrict__ ev_round,
+                const uint64_t *__restrict__ evoff, float *__restrict__ ev)
+{
+	const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const int lane = threadIdx.x & 31;
+	if (i >= n_act) return;
+	const uint32_t r = act[i];
+	const uint64_t a = evoff[i];
+	const uint32_t n = (uint32_t)(evoff[i + 1] - a);
+	float *dst = ev + st[r].ev_base + st[r].n_events;
+	for (uint32_t k = lane; k < n; k += 32) dst[k] = ev_round[a + k];
+	__syncwarp();
+	if (lane == 0) st[r].n_events += n;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// seeding: ri_sketch_reg (rsketch.c:223-274) + ri_idx_get (rawindex.cpp:256-273), one warp per read
+// ---------------------------------------------------------------------------------------------------------------
+// The accept filter (:243: skip an event closer than LAST_SIG_DIFF to the last ACCEPTED one) is a recurrence; the warp
+// resolves it 32 events at a time in registers (every lane replays the same 32 steps on shuffled values), the 5-bit
+// quantised symbols of the accepted events go to shared memory, and every accepted event of rank >= e-1 hashes the last e
+// symbols (:254-255).  Seeds land at seeds_*[evoff[i] + s] (there are fewer seeds than events).
+__global__ void __launch_bounds__(32)
+k_seed(const ReadState *__restrict__ st, const uint32_t *__restrict__ act, uint32_t n_act, const float *__restrict__ ev_round,
+       const uint64_t *__restrict__ evoff, Params P, const Slot *__restrict__ slots, const ChainRec *__restrict__ chains,
+       uint32_t *__restrict__ seeds_h, uint32_t *__restrict__ seeds_p, uint32_t *__restrict__ seed_cnt, uint64_t *__restrict__ seed_off,
+       uint32_t *__restrict__ n_seed_out, uint32_t *__restrict__ seg_n /* anchors of the read this round */, uint32_t *__restrict__ seg_pad,
+       uint32_t *__restrict__ skip, unsigned long long *__restrict__ totals /* [0] seeds, [1] anchors */)
+{
+	extern __shared__ uint8_t sym[];                               // quantised symbols of the accepted events
+	const uint32_t i = blockIdx.x;
+	const int lane = threadIdx.x;
+	if (i >= n_act) return;
+	const uint32_t r = act[i];
+	const uint64_t a = evoff[i];
+	const uint32_t n_ev = (uint32_t)(evoff[i + 1] - a);
+	const float *__restrict__ ev = ev_round + a;
+	uint32_t prev = 0;
+	{
+		const uint32_t nc = st[r].n_chains;
+		for (uint32_t c = lane; c < nc; c += 32) prev += chains[(size_t)r * P.cap_chains + c].n_anchors;
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1) prev += __shfl_xor_sync(0xffffffffu, prev, o);
+	}
+	if (n_ev < P.min_events) {                                     // rmap.cpp:569-572: no chaining this round; reg->chains stay
+		if (lane == 0) { n_seed_out[i] = 0; seg_n[i] = prev; seg_pad[i] = prev; skip[i] = 1; }
+		return;
+	}
+	const uint32_t quant_bit = (uint32_t)P.lq + 2u, shift_r = 32u - (uint32_t)P.q;
+	const uint32_t mask_l_quant = (1u << P.lq) - 1u;
+	const uint64_t mask = (1ull << 32) - 1, mask_events = (1ull << (quant_bit * (uint32_t)P.e)) - 1;
+	float last = 0.0f;
+	uint32_t n_acc = 0;
+	for (uint32_t b = 0; b < n_ev; b += 32) {
+		const uint32_t idx = b + lane;
+		const float v = idx < n_ev ? ev[idx] : 0.0f;
+		const uint32_t cnt = min(32u, n_ev - b);
+		uint32_t accmask = 0;
+		for (uint32_t t = 0; t < cnt; ++t) {
+			const float x = __shfl_sync(0xffffffffu, v, (int)t);
+			// fabs(s[i] - s[l_sigpos]) < LAST_SIG_DIFF in double after an fp32 subtraction == fabsf(d) < 0.3f; RI_MASK_SIGNAL :243
+			const bool rej = ((b + t) > 0 && fabsf(__fsub_rn(x, last)) < 0.3f) || x == 3.402823466e+32f;
+			if (!rej) { last = x; accmask |= 1u << t; }
+		}
+		const bool mine = (accmask >> lane) & 1u;
+		const uint32_t rank = n_acc + __popc(accmask & ((1u << lane) - 1u));
+		if (mine) {
+			const uint32_t s = __float_as_uint(v);
+			sym[rank] = (uint8_t)((s >> 30 << P.lq) | ((s >> shift_r) & mask_l_quant));             // :247
+		}
+		__syncwarp();
+		if (mine && rank + 1u >= (uint32_t)P.e) {
+			uint64_t qv = 0;
+			for (int j = P.e - 1; j >= 0; --j) qv = (qv << quant_bit) | sym[rank - (uint32_t)j];    // oldest symbol highest, :254
+			qv &= mask_events;
+			const uint32_t sidx = rank + 1u - (uint32_t)P.e;
+			seeds_h[a + sidx] = (uint32_t)hash64(qv, mask);
+			seeds_p[a + sidx] = idx;
+		}
+		n_acc += __popc(accmask);
+		__syncwarp();
+	}
+	const uint32_t n_seed = n_acc + 1u >= (uint32_t)P.e ? n_acc + 1u - (uint32_t)P.e : 0u;
+	__syncwarp();
+	uint32_t hits = 0;
+	const uint32_t nslots_mask = (1u << P.slot_bits) - 1u;
+	for (uint32_t s = lane; s < n_seed; s += 32) {
+		const uint32_t key = seeds_h[a + s];
+		uint32_t h = (uint32_t)(key * 0x9E3779B1u) >> (32 - P.slot_bits);
+		uint32_t c = 0; uint64_t off = 0;
+		for (;;) {
+			const Slot sl = slots[h];
+			if (sl.cnt == 0) break;
+			if (sl.key == key) { c = sl.cnt; off = sl.off; break; }
+			h = (h + 1) & nslots_mask;
+		}
+		seed_cnt[a + s] = c; seed_off[a + s] = off;
+		hits += c;
+	}
+#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) hits += __shfl_xor_sync(0xffffffffu, hits, o);
+	if (lane == 0) {
+		const uint32_t n = hits + prev;
+		uint32_t pad = 1; while (pad < n) pad <<= 1;
+		if (n == 0) pad = 0;
+		n_seed_out[i] = n_seed; seg_n[i] = n; seg_pad[i] = pad; skip[i] = 0;
+		atomicAdd(totals, (unsigned long long)n_seed); atomicAdd(totals + 1, (unsigned long long)n);
+	}
+}
+
+// anchors of the round: the previous chunk's chains re-injected (rmap.cpp:343-357) + one per seed hit (:383-390), as packed
+// keys in the read's (power-of-two padded) segment.  Reads that skipped chaining carry their chains' anchors into the new
+// arena unchanged.
+__global__ void __launch_bounds__(32)
+k_fill_anchors(ReadState *__restrict__ st, const uint32_t *__restrict__ act, uint32_t n_act, const uint64_t *__restrict__ evoff, Params P,
+               ChainRec *__restrict__ chains, const ra_anchor_t *__restrict__ anc_prev0, const ra_anchor_t *__restrict__ anc_prev1,
+               ra_anchor_t *__restrict__ anc_cur, uint32_t cur_arena, const uint32_t *__restrict__ seeds_p, const uint32_t *__restrict__ seed_cnt,
+               const uint64_t *__restrict__ seed_off, const uint64_t *__restrict__ vals, const uint32_t *__restrict__ n_seed_in,
+               const uint32_t *__restrict__ seg_n, const uint32_t *__restrict__ seg_pad, const uint64_t *__restrict__ seg_base,
+               const uint32_t *__restrict__ skip, uint64_t *__restrict__ keys)
+{
+	const uint32_t i = blockIdx.x;
+	const int lane = threadIdx.x;
+	if (i >= n_act) return;
+	const uint32_t r = act[i];
+	const uint64_t base = seg_base[i];
+	const ReadState s = st[r];
+	const ra_anchor_t *__restrict__ prev = s.arena ? anc_prev1 : anc_prev0;
+	ChainRec *rc = chains + (size_t)r * P.cap_chains;
+	if (skip[i]) {
+		uint64_t o = base;
+		for (uint32_t c = 0; c < s.n_chains; ++c) {
+			const ChainRec ch = rc[c];
+			for (uint32_t k = lane; k < ch.n_anchors; k += 32) anc_cur[o + k] = prev[ch.anchor_off + k];
+			__syncwarp();
+			if (lane == 0) rc[c].anchor_off = o;
+			o += ch.n_anchors;
+		}
+		if (lane == 0) st[r].arena = cur_arena;
+		return;
+	}
+	uint64_t o = base;
+	for (uint32_t c = 0; c < s.n_chains; ++c) {
+		const ChainRec ch = rc[c];
+		for (uint32_t k = lane; k < ch.n_anchors; k += 32) {
+			const ra_anchor_t an = prev[ch.anchor_off + k];
+			keys[o + k] = pack_key(ch.ref, ch.strand, an.target_position, an.query_position);
+		}
+		o += ch.n_anchors;
+	}
+	const uint64_t a = evoff[i];
+	const uint32_t n_seed = n_seed_in[i];
+	const uint32_t chunk_start = s.offset;                                                          // gen_chains(..., reg->offset, ...) :574
+	for (uint32_t b = 0; b < n_seed; b += 32) {
+		const uint32_t sd = b + lane;
+		const uint32_t c = sd < n_seed ? seed_cnt[a + sd] : 0u;
+		uint32_t inc = c;
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += y; }
+		const uint64_t mine = o + inc - c;
+		if (c) {
+			const uint64_t vo = seed_off[a + sd];
+			const uint32_t q = seeds_p[a + sd] + chunk_start;                                         // pi + chunk_start, :387
+			for (uint32_t t = 0; t < c; ++t) {
+				const uint64_t kv = vals[vo + t];
+				keys[mine + t] = pack_key((uint32_t)(kv >> 32), (uint32_t)(kv & 1), (uint32_t)(kv >> 1) & 0x7fffffffu, q);   // :385-387
+			}
+		}
+		o += __shfl_sync(0xffffffffu, inc, 31);
+	}
+	for (uint64_t k = base + seg_n[i] + lane; k < base + seg_pad[i]; k += 32) keys[k] = kPadKey;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// anchor sort (rmap.cpp:396-401): one CTA per read, bitonic network over the padded segment
+// ---------------------------------------------------------------------------------------------------------------
+constexpr uint32_t kSortSmem = 4096;                               // keys staged in shared memory
+__global__ void __launch_bounds__(256)
+k_sort_segments(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_base, const uint32_t *__restrict__ seg_pad,
+                const uint32_t *__restrict__ skip, uint32_t n_act)
+{
+	__shared__ uint64_t sk[kSortSmem];
+	const uint32_t i = blockIdx.x;
+	if (i >= n_act || skip[i]) return;
+	const uint32_t n = seg_pad[i];
+	if (n < 2) return;
+	uint64_t *g = keys + seg_base[i];
+	const int tid = threadIdx.x;
+	if (n <= kSortSmem) {
+		for (uint32_t k = tid; k < n; k += 256) sk[k] = g[k];
+		__syncthreads();
+		for (uint32_t size = 2; size <= n; size <<= 1)
+			for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+				for (uint32_t t = tid; t < (n >> 1); t += 256) {
+					const uint32_t lo = 2 * t - (t & (stride - 1));
+					const uint32_t hi = lo + stride;
+					const bool up = (lo & size) == 0;
+					const uint64_t x = sk[lo], y = sk[hi];
+					if ((x > y) == up) { sk[lo] = y; sk[hi] = x; }
+				}
+				__syncthreads();
+			}
+		for (uint32_t k = tid; k < n; k += 256) g[k] = sk[k];
+		return;
+	}
+	for (uint32_t size = 2; size <= n; size <<= 1)
+		for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+			for (uint32_t t = tid; t < (n >> 1); t += 256) {
+				const uint32_t lo = 2 * t - (t & (stride - 1));
+				const uint32_t hi = lo + stride;
+				const bool up = (lo & size) == 0;
+				const uint64_t x = g[lo], y = g[hi];
+				if ((x > y) == up) { g[lo] = y; g[hi] = x; }
+			}
+			__syncthreads();
+		}
+}
+
+} // namespace mapk
