@@ -112,6 +112,7 @@ const char *ra_last_error(void);
 /* ri_mapopt_init, roptions.c:5-61 (hot-path subset) */
 void        ra_mapopt_init(ra_mapopt_t *opt);
 int         ra_set_opt(ra_ctx *ctx, const ra_mapopt_t *opt);
+int         ra_get_opt(const ra_ctx *ctx, ra_mapopt_t *opt);
 /* number of kernels this context has launched since creation (bench.py's gpu_launches) */
 uint64_t    ra_launch_count(const ra_ctx *ctx);
 /* Device time of the most recent event-detection and DTW batches, measured with CUDA events on the

@@ -712,3 +712,38 @@ def build_flat_index(seqs, pore_vals, preset="sensitive", k=6, contract=1, names
     return dict(w=w, e=e, n=n, q=q, lq=lq, k=k, flag=0, n_seq=len(seqs), names=names or [f"ref{i}" for i in range(len(seqs))],
                 seq_len=np.array([len(s) for s in seqs], np.uint32), fwd=fwd, rev=rev, keys=np.ascontiguousarray(keys), key_off=key_off,
                 vals=np.ascontiguousarray(y))
+
+
+def write_index_file(path: str, ix: dict, names=None) -> None:
+    """Writes a flat table in the reference's index file format (ri_idx_dump, rawindex.cpp:275-315), so that index loaders
+    (the reference's ri_idx_load, the product's ra_index_load_file) can be driven where the reference build is absent."""
+    b = 14
+    keys = ix["keys"]; off = ix["key_off"].astype(np.int64); vals = ix["vals"]
+    bucket = (keys & np.uint64((1 << b) - 1)).astype(np.int64)
+    order = np.argsort(bucket, kind="stable")
+    bstart = np.searchsorted(bucket[order], np.arange((1 << b) + 1))
+    with open(path, "wb") as f:
+        f.write(b"RI")
+        f.write(np.array([ix["w"], ix["e"], ix["n"], ix["q"], ix["lq"], ix["k"], ix["n_seq"], ix.get("flag", 0)], np.uint32).tobytes())
+        nm = names or ix.get("names") or [f"ref{i}" for i in range(ix["n_seq"])]
+        for i in range(ix["n_seq"]):
+            f.write(bytes([len(nm[i])])); f.write(nm[i].encode())
+            f.write(np.uint32(ix["seq_len"][i]).tobytes())
+            f.write(np.ascontiguousarray(ix["fwd"][i], np.float32).tobytes()); f.write(np.ascontiguousarray(ix["rev"][i], np.float32).tobytes())
+        for i in range(1 << b):
+            sel = order[bstart[i]:bstart[i + 1]]
+            cnt = (off[sel + 1] - off[sel])
+            multi = cnt > 1
+            p = np.concatenate([vals[off[j]:off[j + 1]] for j in sel[multi]]) if multi.any() else np.zeros(0, np.uint64)
+            f.write(np.int32(len(p)).tobytes()); f.write(p.tobytes())
+            f.write(np.uint32(len(sel)).tobytes())
+            if len(sel) == 0:
+                continue
+            kv = np.zeros((len(sel), 2), np.uint64)
+            kv[:, 0] = ((keys[sel] >> np.uint64(b)) << np.uint64(1)) | (~multi).astype(np.uint64)
+            pstart = np.concatenate(([0], np.cumsum(cnt[multi])))[:-1]
+            v = np.zeros(len(sel), np.uint64)
+            v[~multi] = vals[off[sel[~multi]]]
+            v[multi] = (pstart.astype(np.uint64) << np.uint64(32)) | cnt[multi].astype(np.uint64)
+            kv[:, 1] = v
+            f.write(kv.tobytes())

@@ -9,3 +9,5 @@ from .api import (  # noqa: F401
     RI_M_DTW_BORDER_CONSTRAINT_GLOBAL, RI_M_DTW_BORDER_CONSTRAINT_LOCAL, RI_M_DTW_BORDER_CONSTRAINT_SPARSE,
     RI_M_DTW_FILL_METHOD_BANDED, RI_M_DTW_FILL_METHOD_FULL, Context, make_items, ri_mapopt_init,
 )
+from ._lib import PAF_DTYPE, MapStats, RiMapOpt  # noqa: F401,E402
+from .mapper import RI_M_DTW_EVALUATE_CHAINS, RI_M_DTW_OUTPUT_CIGAR, Index, ri_mapopt_full  # noqa: F401,E402

@@ -646,6 +646,17 @@ int ra_set_opt(ra_ctx *ctx, const ra_mapopt_t *opt)
 }
 
 uint64_t ra_launch_count(const ra_ctx *ctx) { return ctx ? ctx->launches : 0; }
+int ra_get_opt(const ra_ctx *ctx, ra_mapopt_t *opt) { if (!ctx || !opt) return fail(RA_EINVAL, "NULL argument"); *opt = ctx->opt; return RA_OK; }
+// internal (map.cu): kernels launched outside this file count too; errors raised there go through ra_last_error()
+void ra__add_launches(ra_ctx *ctx, uint64_t n) { if (ctx) ctx->launches += n; }
+int ra__device(const ra_ctx *ctx) { return ctx ? ctx->device : 0; }
+int ra__fail(int code, const char *fmt, ...)
+{
+	va_list ap; va_start(ap, fmt);
+	vsnprintf(g_err, sizeof(g_err), fmt, ap);
+	va_end(ap);
+	return code;
+}
 
 int ra_last_timing(ra_ctx *ctx, float *events_scan_ms, float *events_total_ms, float *dtw_ms)
 {

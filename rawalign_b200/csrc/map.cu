@@ -24,6 +24,7 @@
 
 extern "C" void ra__add_launches(ra_ctx *ctx, uint64_t n);        // api.cu
 extern "C" int ra__fail(int code, const char *fmt, ...);            // api.cu: sets ra_last_error()
+extern "C" int ra__device(const ra_ctx *ctx);
 
 namespace {
 
@@ -254,4 +255,5 @@ int ra_index_info(const ra_index *ix, int32_t *out, uint32_t *seq_len_out)
 } // extern "C"
 
 #include "map_kernels.cuh"
+#include "map_chain.cuh"
 #include "map_batch.cuh"

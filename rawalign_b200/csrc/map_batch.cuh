@@ -1,0 +1,222 @@
+// map_batch.cuh -- host orchestration of ra_map_batch (included by map.cu only).
+#pragma once
+#include <chrono>
+
+namespace mapk {
+
+__global__ void k_init_state(ReadState *__restrict__ st, uint32_t n_reads, const uint32_t *__restrict__ l_sig_dev, ra_paf_t *__restrict__ paf)
+{
+	const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= n_reads) return;
+	ReadState s = st[r];
+	if (l_sig_dev) s.l_sig = l_sig_dev[r];
+	s.active = s.l_sig > 0; s.done = s.l_sig == 0;
+	ra_paf_t o; memset(&o, 0, sizeof(o));
+	if (s.l_sig == 0) { o.ci = 1; o.sl = 0; }                      // the loop of rmap.cpp:685 does not run: an unmapped line with ci:i:1
+	paf[r] = o;
+	st[r] = s;
+}
+
+} // namespace mapk
+
+namespace {
+
+struct StageClock {
+	std::chrono::steady_clock::time_point t;
+	void start() { t = std::chrono::steady_clock::now(); }
+	float lap() { auto n = std::chrono::steady_clock::now(); float ms = std::chrono::duration<float, std::milli>(n - t).count(); t = n; return ms; }
+};
+
+inline uint32_t events_bound(uint32_t len, uint32_t w1, uint32_t w2) { return len / (w1 / 2 + 2) + len / (w2 / 2 + 2) + 4; }
+
+} // namespace
+
+extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt,
+                            const int16_t *raw, const uint64_t *raw_off, const uint32_t *raw_len, const float *offset, const float *scale,
+                            const float *sig, const uint64_t *sig_off, const uint32_t *sig_len,
+                            uint32_t n_reads, ra_paf_t *out, ra_map_stats_t *stats)
+{
+	using namespace mapk;
+	if (!ctx || !ix || !opt || !out) return ra__fail(RA_EINVAL, "NULL argument");
+	if (ix->ctx != ctx) return ra__fail(RA_EINVAL, "the index was loaded for another context");
+	const bool from_raw = raw != nullptr;
+	if (from_raw ? (!raw_off || !raw_len || !offset || !scale) : (!sig || !sig_off || !sig_len)) return ra__fail(RA_EINVAL, "NULL signal table");
+	if (ix->w != 0 || ix->n != 0) return ra__fail(RA_EUNSUP, "minimizer (w=%d) / BLEND (n=%d) seeding is not implemented on the device", ix->w, ix->n);
+	if (opt->num_best_chains < 1 || opt->num_best_chains > (uint32_t)kMaxBest) return ra__fail(RA_EUNSUP, "num_best_chains %u (supported: 1..%d)", opt->num_best_chains, kMaxBest);
+	if (opt->chunk_size == 0 || opt->max_num_chunk == 0) return ra__fail(RA_EINVAL, "chunk_size / max_num_chunk must be positive");
+	if ((uint64_t)events_bound(opt->chunk_size, opt->window_length1, opt->window_length2) * opt->max_num_chunk >= (1ull << kQueryBits))
+		return ra__fail(RA_EUNSUP, "more than %u events per read possible (chunk_size x max_num_chunk too large)", 1u << kQueryBits);
+	const uint64_t cap_chains64 = (uint64_t)opt->num_best_chains * 2 * ix->n_seq;
+	if (cap_chains64 > 8192) return ra__fail(RA_EUNSUP, "%u reference sequences x %u best chains exceed the per-read chain table", ix->n_seq, opt->num_best_chains);
+	if (stats) memset(stats, 0, sizeof(*stats));
+	if (n_reads == 0) return RA_OK;
+	int rc;
+	{   // hot-path options of the context follow the map options; fp_contract / test hooks stay as the context has them
+		ra_mapopt_t o; if ((rc = ra_get_opt(ctx, &o))) return rc;
+		o.window_length1 = opt->window_length1; o.window_length2 = opt->window_length2; o.threshold1 = opt->threshold1; o.threshold2 = opt->threshold2;
+		o.peak_height = opt->peak_height; o.dtw_border_constraint = opt->dtw_border_constraint; o.dtw_fill_method = opt->dtw_fill_method;
+		o.dtw_band_radius_frac = opt->dtw_band_radius_frac; o.dtw_match_bonus = opt->dtw_match_bonus; o.dtw_min_score = opt->dtw_min_score;
+		if ((rc = ra_set_opt(ctx, &o))) return rc;
+	}
+	float *ref_dev = nullptr; uint64_t ref_n = 0;
+	if ((rc = ra_ref_device(ctx, &ref_dev, &ref_n))) return rc;
+	MAP_CUDA(cudaSetDevice(ra__device(ctx)));
+	cudaStream_t S = ix->stream;
+	StageClock clk, total; total.start(); clk.start();
+	ra_map_stats_t stt; memset(&stt, 0, sizeof(stt));
+	uint64_t launches = 0, lib_launches = 0;       // kernels launched here / by the K1 and DTW entry points (those count themselves)
+
+	Params P; memset(&P, 0, sizeof(P));
+	P.chunk_size = opt->chunk_size; P.max_num_chunk = opt->max_num_chunk; P.min_events = opt->min_events;
+	P.max_gap_length = (int32_t)opt->max_gap_length; P.max_target_gap_length = (int32_t)opt->max_target_gap_length;
+	P.chaining_band_length = (int32_t)opt->chaining_band_length; P.max_num_skips = (int32_t)opt->max_num_skips;
+	P.min_num_anchors = (int32_t)opt->min_num_anchors; P.num_best_chains = (int32_t)opt->num_best_chains;
+	P.min_chaining_score = opt->min_chaining_score; P.min_chain_anchor = opt->min_chain_anchor;
+	P.min_bestmap_ratio = opt->min_bestmap_ratio; P.min_meanmap_ratio = opt->min_meanmap_ratio; P.dtw_min_score = opt->dtw_min_score;
+	P.sample_rate = opt->sample_rate; P.bp_per_sec = opt->bp_per_sec;
+	P.dtw = (opt->flag & RA_M_DTW_EVALUATE_CHAINS) ? 1u : 0u; P.no_filter = (opt->flag & RA_M_DISABLE_CHAININGSCORE_FILTERING) ? 1u : 0u;
+	P.e = ix->e; P.q = ix->q; P.lq = ix->lq; P.n_seq = ix->n_seq; P.cap_chains = (uint32_t)cap_chains64; P.slot_bits = ix->slot_bits;
+
+	// ---- signal to the device, read table ------------------------------------------------------------------------------
+	const uint64_t *in_off = from_raw ? raw_off : sig_off;
+	const uint32_t *in_len = from_raw ? raw_len : sig_len;
+	uint64_t n_samples = 0;
+	for (uint32_t r = 0; r < n_reads; ++r) n_samples = std::max<uint64_t>(n_samples, in_off[r] + in_len[r]);
+	std::vector<ReadState> hst(n_reads);
+	uint64_t ev_cap = 0;
+	const uint64_t max_read = (uint64_t)opt->chunk_size * opt->max_num_chunk;
+	for (uint32_t r = 0; r < n_reads; ++r) {
+		ReadState s; memset(&s, 0, sizeof(s));
+		s.sig_off = in_off[r]; s.l_sig = in_len[r]; s.ev_base = ev_cap;
+		const uint64_t used = std::min<uint64_t>(in_len[r], max_read);
+		const uint64_t nch = (used + opt->chunk_size - 1) / opt->chunk_size;
+		ev_cap += used / (opt->window_length1 / 2 + 2) + used / (opt->window_length2 / 2 + 2) + 4 * nch + 4;
+		hst[r] = s;
+	}
+	if ((rc = ix->sig.reserve(std::max<uint64_t>(n_samples, 1) * 4 + 64))) return rc;
+	if ((rc = ix->state.reserve((size_t)n_reads * sizeof(ReadState)))) return rc;
+	if ((rc = ix->chains.reserve((size_t)n_reads * P.cap_chains * sizeof(ChainRec)))) return rc;
+	if ((rc = ix->paf.reserve((size_t)n_reads * sizeof(ra_paf_t)))) return rc;
+	if ((rc = ix->ev.reserve(std::max<uint64_t>(ev_cap, 1) * 4))) return rc;
+	if ((rc = ix->act.reserve((size_t)n_reads * 4)) || (rc = ix->coff.reserve((size_t)n_reads * 8)) || (rc = ix->clen.reserve((size_t)n_reads * 4))) return rc;
+	if ((rc = ix->counters.reserve(256))) return rc;
+	if ((rc = ix->evoff_round.reserve(((size_t)n_reads + 1) * 8))) return rc;
+	if ((rc = ix->n_seed.reserve((size_t)n_reads * 4)) || (rc = ix->seg_n.reserve((size_t)n_reads * 4)) || (rc = ix->n_hits.reserve((size_t)n_reads * 4)) ||
+	    (rc = ix->scan_tmp.reserve((size_t)n_reads * 4)) || (rc = ix->seg_base.reserve(((size_t)n_reads + 1) * 8)) ||
+	    (rc = ix->n_cand.reserve((size_t)n_reads * 4)) || (rc = ix->cand_base.reserve(((size_t)n_reads + 1) * 8)) ||
+	    (rc = ix->group_first.reserve(((size_t)n_reads + 1) * 4)) || (rc = ix->cand.reserve((size_t)n_reads * P.cap_chains * sizeof(ChainRec)))) return rc;
+	if (!ix->pin) { MAP_CUDA(cudaMallocHost(&ix->pin, 4096)); ix->pin_cap = 4096; }
+	MAP_CUDA(cudaMemcpyAsync(ix->state.p, hst.data(), (size_t)n_reads * sizeof(ReadState), cudaMemcpyHostToDevice, S));
+	const uint32_t *l_sig_dev = nullptr;
+	if (from_raw) {
+		if ((rc = ix->raw16.reserve(std::max<uint64_t>(n_samples, 1) * 2 + 64)) || (rc = ix->rd_off.reserve((size_t)n_reads * 8)) || (rc = ix->rd_len.reserve((size_t)n_reads * 4)) ||
+		    (rc = ix->rd_offset.reserve((size_t)n_reads * 4)) || (rc = ix->rd_scale.reserve((size_t)n_reads * 4)) || (rc = ix->seed_cnt.reserve((size_t)n_reads * 4))) return rc;
+		MAP_CUDA(cudaMemcpyAsync(ix->raw16.p, raw, n_samples * 2, cudaMemcpyHostToDevice, S));
+		MAP_CUDA(cudaMemcpyAsync(ix->rd_off.p, raw_off, (size_t)n_reads * 8, cudaMemcpyHostToDevice, S));
+		MAP_CUDA(cudaMemcpyAsync(ix->rd_len.p, raw_len, (size_t)n_reads * 4, cudaMemcpyHostToDevice, S));
+		MAP_CUDA(cudaMemcpyAsync(ix->rd_offset.p, offset, (size_t)n_reads * 4, cudaMemcpyHostToDevice, S));
+		MAP_CUDA(cudaMemcpyAsync(ix->rd_scale.p, scale, (size_t)n_reads * 4, cudaMemcpyHostToDevice, S));
+		uint32_t *lsd = ix->n_hits.as<uint32_t>();                 // per-read l_sig of the decode (n_hits is free until the first round)
+		MAP_CUDA(ra::launch_decode_raw(ix->raw16.as<int16_t>(), ix->rd_off.as<uint64_t>(), ix->rd_len.as<uint32_t>(), ix->rd_offset.as<float>(),
+		                               ix->rd_scale.as<float>(), n_reads, ix->sig.as<float>(), lsd, S));
+		l_sig_dev = lsd; ++launches;
+	} else MAP_CUDA(cudaMemcpyAsync(ix->sig.p, sig, n_samples * 4, cudaMemcpyHostToDevice, S));
+	k_init_state<<<(n_reads + 255) / 256, 256, 0, S>>>(ix->state.as<ReadState>(), n_reads, l_sig_dev, ix->paf.as<ra_paf_t>()); ++launches;
+	MAP_CUDA(cudaStreamSynchronize(S));
+	stt.decode_ms = clk.lap();
+
+	ReadState *st = ix->state.as<ReadState>();
+	uint32_t *counters = ix->counters.as<uint32_t>();
+	unsigned long long *totals = reinterpret_cast<unsigned long long *>(counters + 8);
+	uint32_t *hc = reinterpret_cast<uint32_t *>(ix->pin);
+	const uint32_t w1 = opt->window_length1, w2 = opt->window_length2;
+	for (uint32_t round = 0; round < opt->max_num_chunk; ++round) {
+		const uint32_t cur = round & 1u;
+		MAP_CUDA(cudaMemsetAsync(counters, 0, 64, S));
+		k_round_setup<<<1, 1024, 0, S>>>(st, n_reads, P, ix->act.as<uint32_t>(), ix->coff.as<uint64_t>(), ix->clen.as<uint32_t>(), counters); ++launches;
+		MAP_CUDA(cudaMemcpyAsync(hc, counters, 8, cudaMemcpyDeviceToHost, S));
+		MAP_CUDA(cudaStreamSynchronize(S));
+		const uint32_t n_act = hc[0], max_len = hc[1];
+		if (n_act == 0) break;
+		stt.rounds = round + 1; stt.chunks += n_act;
+		stt.select_ms += clk.lap();
+		// ---- K1 over the round's chunks, appended to the reads' event arrays ------------------------------------------
+		const uint64_t round_cap = (uint64_t)n_act * events_bound(max_len, w1, w2);
+		if ((rc = ix->ev_round.reserve(round_cap * 4)) || (rc = ix->seeds_h.reserve(round_cap * 4)) || (rc = ix->seeds_p.reserve(round_cap * 4)) ||
+		    (rc = ix->seed_cnt.reserve(round_cap * 4)) || (rc = ix->seed_off.reserve(round_cap * 8))) return rc;
+		uint64_t tot_ev = 0;
+		const uint64_t l0 = ra_launch_count(ctx);
+		if ((rc = ra_detect_events_batch_dev(ctx, ix->sig.as<float>(), ix->coff.as<uint64_t>(), ix->clen.as<uint32_t>(), n_act, max_len,
+		                                     ix->ev_round.as<float>(), round_cap, ix->evoff_round.as<uint64_t>(), &tot_ev))) return rc;
+		stt.events += tot_ev;
+		k_append_events<<<(n_act * 32 + 127) / 128, 128, 0, S>>>(st, ix->act.as<uint32_t>(), n_act, ix->ev_round.as<float>(), ix->evoff_round.as<uint64_t>(),
+		                                                      ix->ev.as<float>()); ++launches;
+		MAP_CUDA(cudaStreamSynchronize(S));
+		stt.events_ms += clk.lap();
+		// ---- seeds, index lookups, anchor counts ------------------------------------------------------------------------
+		uint32_t *skip = ix->scan_tmp.as<uint32_t>();
+		uint32_t *seg_pad = ix->n_hits.as<uint32_t>();
+		const size_t sym_bytes = (events_bound(max_len, w1, w2) + 63u) & ~63u;
+		if (sym_bytes > 48 * 1024) return ra__fail(RA_EUNSUP, "chunk_size %u needs %zu bytes of symbols per warp", opt->chunk_size, sym_bytes);
+		k_seed<<<n_act, 32, sym_bytes, S>>>(st, ix->act.as<uint32_t>(), n_act, ix->ev_round.as<float>(), ix->evoff_round.as<uint64_t>(), P, ix->slots.as<Slot>(),
+		                                    ix->chains.as<ChainRec>(), ix->seeds_h.as<uint32_t>(), ix->seeds_p.as<uint32_t>(), ix->seed_cnt.as<uint32_t>(),
+		                                    ix->seed_off.as<uint64_t>(), ix->n_seed.as<uint32_t>(), ix->seg_n.as<uint32_t>(), seg_pad, skip, totals); ++launches;
+		MAP_CUDA(ra::launch_exclusive_scan_u32(seg_pad, ix->seg_base.as<uint64_t>(), n_act, S)); ++launches;
+		uint64_t *h64 = reinterpret_cast<uint64_t *>(hc + 16);
+		MAP_CUDA(cudaMemcpyAsync(h64, ix->seg_base.as<uint64_t>() + n_act, 8, cudaMemcpyDeviceToHost, S));
+		MAP_CUDA(cudaMemcpyAsync(h64 + 1, totals, 16, cudaMemcpyDeviceToHost, S));
+		MAP_CUDA(cudaStreamSynchronize(S));
+		const uint64_t total_pad = h64[0];
+		stt.seeds += h64[1]; stt.anchors += h64[2];
+		stt.seed_ms += clk.lap();
+		// ---- anchors, sort, chaining -------------------------------------------------------------------------------------
+		const uint64_t an = std::max<uint64_t>(total_pad, 1);
+		if ((rc = ix->keys.reserve(an * 8)) || (rc = ix->score.reserve(an * 4)) || (rc = ix->pred.reserve(an * 4)) || (rc = ix->used.reserve(an)) ||
+		    (rc = ix->anc[cur].reserve(an * sizeof(ra_anchor_t)))) return rc;
+		k_fill_anchors<<<n_act, 32, 0, S>>>(st, ix->act.as<uint32_t>(), n_act, ix->evoff_round.as<uint64_t>(), P, ix->chains.as<ChainRec>(),
+		                                    ix->anc[0].as<ra_anchor_t>(), ix->anc[1].as<ra_anchor_t>(), ix->anc[cur].as<ra_anchor_t>(), cur,
+		                                    ix->seeds_p.as<uint32_t>(), ix->seed_cnt.as<uint32_t>(), ix->seed_off.as<uint64_t>(), ix->vals.as<uint64_t>(),
+		                                    ix->n_seed.as<uint32_t>(), ix->seg_n.as<uint32_t>(), seg_pad, ix->seg_base.as<uint64_t>(), skip, ix->keys.as<uint64_t>());
+		k_advance_offset<<<(n_act + 127) / 128, 128, 0, S>>>(st, ix->act.as<uint32_t>(), n_act, ix->evoff_round.as<uint64_t>(), skip);
+		k_sort_segments<<<n_act, 256, 0, S>>>(ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), seg_pad, skip, n_act);
+		launches += 3;
+		MAP_CUDA(cudaStreamSynchronize(S));
+		stt.sort_ms += clk.lap();
+		k_chain<<<(n_act * 32 + 127) / 128, 128, 0, S>>>(ix->act.as<uint32_t>(), n_act, P, ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), ix->seg_n.as<uint32_t>(), skip,
+		                                                 ix->score.as<float>(), ix->pred.as<uint32_t>(), ix->used.as<uint8_t>(), ix->anc[cur].as<ra_anchor_t>(),
+		                                                 ix->cand.as<ChainRec>(), ix->n_cand.as<uint32_t>());
+		MAP_CUDA(ra::launch_exclusive_scan_u32(ix->n_cand.as<uint32_t>(), ix->cand_base.as<uint64_t>(), n_act, S));
+		launches += 2;
+		MAP_CUDA(cudaMemcpyAsync(h64, ix->cand_base.as<uint64_t>() + n_act, 8, cudaMemcpyDeviceToHost, S));
+		MAP_CUDA(cudaStreamSynchronize(S));
+		const uint64_t n_cand_total = h64[0];
+		stt.chain_ms += clk.lap();
+		// ---- DTW evaluation of the candidates (the hot path) -------------------------------------------------------------
+		if (P.dtw && n_cand_total) {
+			if (n_cand_total >= 0xffffffffull) return ra__fail(RA_EINVAL, "too many candidate chains in one round");
+			if ((rc = ix->dtw_chains.reserve(n_cand_total * sizeof(ra_chain_t))) || (rc = ix->dscore.reserve(n_cand_total * 4)) || (rc = ix->dkeep.reserve(n_cand_total))) return rc;
+			k_emit_dtw_chains<<<(n_act + 1 + 127) / 128, 128, 0, S>>>(st, ix->act.as<uint32_t>(), n_act, P, ix->cand.as<ChainRec>(), ix->n_cand.as<uint32_t>(),
+			                                                          ix->cand_base.as<uint64_t>(), ix->seq_tab.as<uint64_t>(), ix->dtw_chains.as<ra_chain_t>(),
+			                                                          ix->group_first.as<uint32_t>()); ++launches;
+			MAP_CUDA(cudaStreamSynchronize(S));
+			if ((rc = ra_align_chains_batch_dev(ctx, ix->ev.as<float>(), nullptr, ix->anc[cur].as<ra_anchor_t>(), an, ix->dtw_chains.as<ra_chain_t>(),
+			                                    (uint32_t)n_cand_total, ix->group_first.as<uint32_t>(), n_act, 1, nullptr, ix->dscore.as<float>(),
+			                                    ix->dkeep.as<uint8_t>(), nullptr, nullptr))) return rc;
+			stt.chains_evaluated += n_cand_total;
+		}
+		lib_launches += ra_launch_count(ctx) - l0;
+		stt.dtw_ms += clk.lap();
+		k_select<<<(n_act + 63) / 64, 64, 0, S>>>(st, ix->act.as<uint32_t>(), n_act, P, ix->cand.as<ChainRec>(), ix->n_cand.as<uint32_t>(), ix->cand_base.as<uint64_t>(),
+		                                         ix->dscore.as<float>(), ix->dkeep.as<uint8_t>(), skip, ix->chains.as<ChainRec>(), ix->anc[cur].as<ra_anchor_t>(), cur,
+		                                         ix->seq_tab.as<uint64_t>(), ix->paf.as<ra_paf_t>(), counters); ++launches;
+		MAP_CUDA(cudaGetLastError());
+	}
+	MAP_CUDA(cudaMemcpyAsync(out, ix->paf.p, (size_t)n_reads * sizeof(ra_paf_t), cudaMemcpyDeviceToHost, S));
+	MAP_CUDA(cudaStreamSynchronize(S));
+	stt.select_ms += clk.lap();
+	stt.total_ms = total.lap();
+	stt.launches = launches + lib_launches;
+	ra__add_launches(ctx, launches);
+	if (stats) *stats = stt;
+	return RA_OK;
+}

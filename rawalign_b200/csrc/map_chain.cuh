@@ -226,7 +226,6 @@ k_select(ReadState *__restrict__ st, const uint32_t *__restrict__ act, uint32_t 
 			}
 		}
 		s.n_chains = np; s.arena = cur_arena;
-		s.offset += (uint32_t)0;                                   // reg->offset is advanced by the caller-side bookkeeping below
 	}
 	const bool mapped = is_mapped(rc, s.n_chains, P);
 	bool leave = mapped;

@@ -1,0 +1,123 @@
+"""Host-side mirror of the reference's map loop on top of the C ABI (ra_index_*, ra_map_batch).
+
+``Index`` = ri_idx_t on the device (loaded from the reference's unchanged index file, or from a flat table);
+``map_reads`` = kt_for(n_threads, map_worker_for, ...) over a batch of reads (rmap.cpp:916), returning the numbers of
+every PAF line; ``paf_lines`` formats them exactly as rmap.cpp:730-758 / :954-972 do (minus the per-read wall time mt:f:).
+Nothing here computes on the CPU beyond formatting.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+from ._lib import PAF_DTYPE, MapStats, RiMapOpt, check
+
+RI_M_DTW_EVALUATE_CHAINS = 0x2     # roptions.h:12
+RI_M_DTW_OUTPUT_CIGAR = 0x4
+
+
+def ri_mapopt_full(**kw) -> RiMapOpt:
+    """ri_mapopt_init (roptions.c:5-61), then keyword overrides."""
+    o = RiMapOpt()
+    _lib.load().ra_ri_mapopt_init(C.byref(o))
+    for k, v in kw.items():
+        setattr(o, k, v)
+    return o
+
+
+class Index:
+    """ra_index: the seed table and the reference signals on the device, bound to one Context."""
+
+    def __init__(self, ctx, handle, names=None):
+        self._L = _lib.load(); self.ctx = ctx; self._h = handle
+        info = (C.c_int32 * 9)()
+        check(self._L.ra_index_info(self._h, info, None))
+        self.w, self.e, self.n, self.q, self.lq, self.k, self.n_seq = [int(x) for x in info[:7]]
+        self.seq_len = np.zeros(self.n_seq, np.uint32)
+        check(self._L.ra_index_info(self._h, info, self.seq_len.ctypes.data))
+        self.names = list(names) if names is not None else [f"ref{i}" for i in range(self.n_seq)]
+
+    @classmethod
+    def load_file(cls, ctx, path: str, names=None) -> "Index":
+        """ri_idx_load (rawindex.cpp:317-377) straight to the device."""
+        h = C.c_void_p()
+        check(_lib.load().ra_index_load_file(ctx._h, path.encode(), C.byref(h)))
+        if names is None:
+            names = _names_from_index_file(path)
+        return cls(ctx, h, names)
+
+    @classmethod
+    def load_flat(cls, ctx, tab: dict) -> "Index":
+        fwd = [np.ascontiguousarray(a, np.float32) for a in tab["fwd"]]; rev = [np.ascontiguousarray(a, np.float32) for a in tab["rev"]]
+        n_seq = len(fwd)
+        fp = (C.c_void_p * n_seq)(*[a.ctypes.data for a in fwd]); rp = (C.c_void_p * n_seq)(*[a.ctypes.data for a in rev])
+        keys = np.ascontiguousarray(tab["keys"], np.uint64); ko = np.ascontiguousarray(tab["key_off"], np.uint64); vals = np.ascontiguousarray(tab["vals"], np.uint64)
+        sl = np.ascontiguousarray(tab["seq_len"], np.uint32)
+        h = C.c_void_p()
+        check(_lib.load().ra_index_load_flat(ctx._h, tab["w"], tab["e"], tab["n"], tab["q"], tab["lq"], tab["k"], n_seq, sl.ctypes.data,
+                                             C.cast(fp, C.c_void_p), C.cast(rp, C.c_void_p), len(keys), keys.ctypes.data, ko.ctypes.data, vals.ctypes.data, C.byref(h)))
+        return cls(ctx, h, tab.get("names"))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.ra_index_destroy(self._h); self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def map_reads(self, opt: RiMapOpt, *, raw=None, raw_off=None, raw_len=None, offset=None, scale=None, sig=None, sig_off=None, sig_len=None):
+        """One batch through ra_map_batch.  Either int16 DAC samples (raw, raw_off, raw_len, offset, scale) or float pA
+        (sig, sig_off, sig_len).  Returns (records: PAF_DTYPE[n_reads], stats: dict)."""
+        st = MapStats()
+        if raw is not None:
+            raw = np.ascontiguousarray(raw, np.int16); ro = np.ascontiguousarray(raw_off, np.uint64); rl = np.ascontiguousarray(raw_len, np.uint32)
+            of = np.ascontiguousarray(offset, np.float32); sc = np.ascontiguousarray(scale, np.float32)
+            n = len(rl); out = np.zeros(n, PAF_DTYPE)
+            check(self._L.ra_map_batch(self.ctx._h, self._h, C.byref(opt), raw.ctypes.data, ro.ctypes.data, rl.ctypes.data, of.ctypes.data, sc.ctypes.data,
+                                       None, None, None, n, out.ctypes.data, C.byref(st)))
+        else:
+            sig = np.ascontiguousarray(sig, np.float32); so = np.ascontiguousarray(sig_off, np.uint64); sl = np.ascontiguousarray(sig_len, np.uint32)
+            n = len(sl); out = np.zeros(n, PAF_DTYPE)
+            check(self._L.ra_map_batch(self.ctx._h, self._h, C.byref(opt), None, None, None, None, None, sig.ctypes.data, so.ctypes.data, sl.ctypes.data,
+                                       n, out.ctypes.data, C.byref(st)))
+        return out, st.as_dict()
+
+    def paf_lines(self, rec: np.ndarray, read_names: Optional[Sequence[str]] = None):
+        """The PAF lines of rmap.cpp:954-972 with the tags of :730-758 / :764-790, minus mt:f: (std::to_string(float) = %f)."""
+        out = []
+        for r, o in enumerate(rec):
+            nm = read_names[r] if read_names is not None else f"read_{r}"
+            if o["mapped"]:
+                tags = (f"ci:i:{o['ci']}\tsl:i:{o['sl']}\tcm:i:{o['cm']}\tnc:i:{o['nc']}\ts1:f:{o['s1']:f}\ts2:f:{o['s2']:f}\tsm:f:{o['sm']:f}"
+                        f"\tat:f:{o['at']:f}\taq:f:{o['aq']:f}")
+                fs = int(o["fragment_start_position"]); fl = int(o["fragment_length"])
+                rs = int(o["read_start_position"]); re_ = int(o["read_end_position"])
+                out.append(f"{nm}\t{o['read_length']}\t{rs}\t{re_}\t{'-' if o['rev'] else '+'}\t{self.names[int(o['ref_id'])]}\t{self.seq_len[int(o['ref_id'])]}"
+                           f"\t{fs}\t{(fs + fl) & 0xFFFFFFFF}\t{(re_ - rs - 1) & 0xFFFFFFFF}\t{fl}\t{o['mapq']}\t{tags}")
+            elif o["nc"] >= 1:
+                tags = (f"ci:i:{o['ci']}\tsl:i:{o['sl']}\tcm:i:{o['cm']}\tnc:i:{o['nc']}\ts1:f:{o['s1']:f}\ts2:f:{o['s2']:f}\tsm:f:{o['sm']:f}"
+                        f"\tat:f:{o['at']:f}\taq:f:{o['aq']:f}")
+                out.append(f"{nm}\t{o['read_length']}\t*\t*\t*\t*\t*\t*\t*\t*\t*\t{o['mapq']}\t{tags}")
+            else:
+                out.append(f"{nm}\t{o['read_length']}\t*\t*\t*\t*\t*\t*\t*\t*\t*\t{o['mapq']}\tci:i:{o['ci']}\tsl:i:{o['sl']}\tcm:i:0\tnc:i:0\ts1:f:0\ts2:f:0\tsm:f:0\tat:f:0\taq:f:0")
+        return out
+
+
+def _names_from_index_file(path: str):
+    """Sequence names from the header of the reference's index file (rawindex.cpp:283-296)."""
+    names = []
+    with open(path, "rb") as f:
+        assert f.read(2) == b"RI"
+        pars = np.frombuffer(f.read(32), np.uint32)
+        for _ in range(int(pars[6])):
+            l = f.read(1)[0]
+            names.append(f.read(l).decode())
+            ln = int(np.frombuffer(f.read(4), np.uint32)[0])
+            f.seek(8 * ln, 1)
+    return names

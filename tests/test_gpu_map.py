@@ -1,0 +1,99 @@
+"""-m gpu: the map loop on the device (ra_index_load_*, ra_map_batch: seeding, index lookup, anchor sort, chaining DP,
+DTW evaluation, primary chains, MAPQ, chunk loop, PAF fields) through the C ABI against
+  * the PAF lines the reference's own map_worker_for printed (tests/golden/map_cases.npz, oracle/gen_golden_map.py), and
+  * the pinned CPU restatement (oracle/ra_oracle_map.c) on fresh random data, field by field."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, bits
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def mg():
+    g = np.load(os.path.join(GOLDEN, "map_cases.npz"))
+    return {k: g[k] for k in g.files}
+
+
+@pytest.fixture(scope="module")
+def flat(mg):
+    from oracle import build_flat_index
+    return {p: build_flat_index([mg["seq0"], mg["seq1"]], mg["pore_vals"], p) for p in ("sensitive", "viral", "fast")}
+
+
+def _opt(kw):
+    import rawalign_b200 as ra
+    return ra.ri_mapopt_full(**kw)
+
+
+def _dac(n):
+    from workload import synth
+    return (np.full(n, np.float32(synth.DAC_OFFSET)), np.full(n, np.float32(np.float32(synth.DAC_RANGE) / np.float32(synth.DAC_DIGITISATION))))
+
+
+@pytest.mark.parametrize("ci", range(6))
+def test_map_batch_paf_vs_reference_golden(mg, flat, ci):
+    import rawalign_b200 as ra
+    from oracle.gen_golden_map import CONFIGS
+    preset, kw = CONFIGS[ci]
+    off, sc = _dac(len(mg["raw_len"]))
+    with ra.Context(0) as ctx, ra.Index.load_flat(ctx, flat[preset]) as ix:
+        rec, st = ix.map_reads(_opt(kw), raw=mg["raw"], raw_off=mg["raw_off"], raw_len=mg["raw_len"], offset=off, scale=sc)
+        got = ix.paf_lines(rec)
+    want = str(mg["paf"][ci]).split("\n")
+    assert len(got) == len(want)
+    for r, (a, b) in enumerate(zip(got, want)):
+        assert a == b, (r, a, b)
+    assert st["rounds"] == 30 and st["launches"] > 0
+
+
+def test_index_file_loader_and_float_input(mg, flat, tmp_path):
+    """ra_index_load_file on a file in the reference's format; float pA input instead of DAC samples; same PAF."""
+    import rawalign_b200 as ra
+    from oracle import write_index_file
+    from oracle.gen_golden_map import CONFIGS
+    from workload import synth
+    p = str(tmp_path / "ref.ind")
+    write_index_file(p, flat["sensitive"])
+    sig = ((mg["raw"].astype(np.float32) + np.float32(synth.DAC_OFFSET)) * (np.float32(synth.DAC_RANGE) / np.float32(synth.DAC_DIGITISATION))).astype(np.float32)
+    with ra.Context(0) as ctx, ra.Index.load_file(ctx, p) as ix:
+        assert ix.n_seq == 2 and ix.e == 6 and ix.names == ["ref0", "ref1"]
+        rec, _ = ix.map_reads(_opt(CONFIGS[0][1]), sig=sig, sig_off=mg["raw_off"], sig_len=mg["raw_len"])
+        got = ix.paf_lines(rec)
+    assert got == str(mg["paf"][0]).split("\n")
+
+
+@pytest.mark.parametrize("preset,kw,n_seq", [("sensitive", dict(flag=2), 1), ("fast", dict(flag=2, dtw_border_constraint=0, dtw_fill_method=1), 3),
+                                             ("viral", dict(flag=0, max_num_chunk=6), 2), ("sensitive", dict(flag=2, min_events=600, num_best_chains=5), 1)])
+def test_map_batch_vs_oracle_random(preset, kw, n_seq):
+    """Fresh data: clean, noisy and junk reads over 1-3 sequences; every PAF field equals the pinned restatement's."""
+    import rawalign_b200 as ra
+    from oracle import MapOracle, build_flat_index
+    from workload import synth
+    rng = np.random.default_rng(1000 + n_seq)
+    seqs = [synth.random_reference(int(n), seed=50 + i) for i, n in enumerate([400_000, 120_000, 60_000][:n_seq])]
+    tab = build_flat_index(seqs, synth.pore_model_as_loaded(), preset)
+    rd = synth.simulate_reads(seqs[0], 96, seed=9, max_chunks=30)
+    sig = rd.sig.copy()
+    for r in range(0, 96, 8):                                      # junk
+        a = int(rd.read_off[r]); n = int(rd.read_len[r]); sig[a:a + n] = np.clip(np.repeat(rng.normal(90, 13, n // 8 + 1), 8)[:n] + rng.normal(0, 2, n), 31, 199)
+    for r in range(3, 96, 5):                                      # noisy
+        a = int(rd.read_off[r]); n = int(rd.read_len[r]); sig[a:a + n] = np.clip(sig[a:a + n] + rng.normal(0, 5.0, n), 31, 199)
+    sig = sig.astype(np.float32)
+    mo = MapOracle(tab)
+    want = mo.map_reads(mo.mapopt(**kw), sig, rd.read_off[:-1], rd.read_len)
+    with ra.Context(0) as ctx, ra.Index.load_flat(ctx, tab) as ix:
+        rec, st = ix.map_reads(_opt(kw), sig=sig, sig_off=rd.read_off[:-1], sig_len=rd.read_len)
+        got_lines = ix.paf_lines(rec)
+    for f in ("mapped", "ref_id", "read_length", "read_start_position", "read_end_position", "fragment_start_position", "fragment_length", "mapq",
+              "rev", "ci", "sl", "cm", "nc", "n_events"):
+        assert np.array_equal(rec[f], want[f]), (f, np.nonzero(rec[f] != want[f])[0][:8])
+    for f in ("s1", "s2", "sm", "at", "aq"):
+        assert np.array_equal(bits(rec[f]), bits(want[f])), f
+    m = want["mapped"].astype(bool)
+    assert np.array_equal(bits(rec["alns"][m]), bits(want["alns"][m]))
+    assert got_lines == mo.paf_lines(want)
+    assert want["mapped"].sum() >= 40 and (want["ci"] > 1).sum() >= 5
