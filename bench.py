@@ -308,37 +308,67 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="C2", choices=["C1", "C2", "C3", "C4", "C5", "C2hot"],
+                    help="BASELINE.json configs through the whole map loop (ra_map_batch); C2hot = only the dense hot-path step "
+                         "(K1 + chain DTW on synthetic chains) that also supplies the roofline numbers of the default line")
     ap.add_argument("--reads-per-gpu", type=int, default=int(os.environ.get("RA_BENCH_READS", 4096)))
+    ap.add_argument("--map-reads-per-gpu", type=int, default=int(os.environ.get("RA_BENCH_MAP_READS", 8192)))
     ap.add_argument("--cpu-sample-reads", type=int, default=32)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-hot-path", action="store_true", help="skip the dense hot-path step in a map-loop run (no roofline numbers)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1)); local = int(os.environ.get("LOCAL_RANK", 0))
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = max(args.warmup, 3)
-    config = {"workload": "C2: 5 Mb synthetic reference, simulated R9.4 reads, sparse border, banded=0.1",
-              "reads_per_gpu": args.reads_per_gpu, "batch_note": "one batch ~ the reference's default mini-batch (-K 500M of signal, roptions.c:34)",
-              "max_chunks_per_read": MAX_CHUNKS, "chains_per_round": CHAINS_PER_ROUND, "batches_in_flight_per_gpu": max(1, PIPELINE_DEPTH),
-              "l2_policy": "inputs larger than L2 (signal batch >> 126 MB)"}
+    hot_config = {"workload": "C2 hot path: 5 Mb synthetic reference, simulated R9.4 reads, sparse border, banded=0.1; K1 over every chunk + chain DTW of every chunk round on synthetic chains",
+                  "reads_per_gpu": args.reads_per_gpu, "batch_note": "one batch ~ the reference's default mini-batch (-K 500M of signal, roptions.c:34)",
+                  "max_chunks_per_read": MAX_CHUNKS, "chains_per_round": CHAINS_PER_ROUND, "batches_in_flight_per_gpu": max(1, PIPELINE_DEPTH),
+                  "l2_policy": "inputs larger than L2 (signal batch >> 126 MB)"}
 
     if args.impl == "reference":
         if rank != 0:
             return 0
-        return run_reference_arm(args, config)
+        if args.config == "C2hot":
+            return run_reference_arm(args, hot_config)
+        return run_reference_map_arm(args)
 
     # exactly one line on stdout: anything a C library prints (e.g. the NCCL version banner) goes to stderr instead
     sys.stdout.flush()
     json_fd = os.dup(1); os.dup2(2, 1)
-    config["cpu_binding"] = bind_to_gpu_numa_node(local)
+    binding = bind_to_gpu_numa_node(local)
+    hot_config["cpu_binding"] = binding
     import torch
     import torch.distributed as dist
-    import rawalign_b200 as ra
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback in the product path); use --impl reference for the CPU arm")
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
+    if args.config == "C2hot":
+        out = hot_path(args, hot_config, rank, world, local, torch, dist, dev)
+    else:
+        out = map_path(args, rank, world, local, torch, dist, dev, binding)
+        if not args.no_hot_path:
+            hot = hot_path(args, hot_config, rank, world, local, torch, dist, dev, with_cpu=False)
+            if rank == 0:
+                out["roofline"] = hot["roofline"]; out["roofline_dtw"] = hot["roofline_dtw"]
+                out["hot_path"] = {k: hot[k] for k in ("value", "unit", "ms_per_step", "dtw_gcups", "hot_path_gcups", "cells_per_step", "stages_ms", "e2e", "gpu_launches", "config")}
+                out["hot_path"]["what"] = ("the dense form of the same path (--config C2hot): K1 over every chunk of 4096 reads x 8 chunks and the chain DTW of every "
+                                           "chunk round on synthetic chains, no early stop -- the step the roofline numbers are measured on")
+                out["gpu_launches"] += hot["gpu_launches"]
+    if rank == 0:
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(out) + "\n").encode())
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
 
+
+def hot_path(args, config, rank, world, local, torch, dist, dev, with_cpu=True):
+    """The dense hot-path step (K1 + chain DTW, synthetic chains); returns the JSON dict on rank 0."""
+    import rawalign_b200 as ra
+    out = None
     t_setup = time.time()
     ref_seq, ref_arena = build_reference()
     reads, coff, clen, crid = build_reads(ref_seq, args.reads_per_gpu, seed=2 + rank)
@@ -521,7 +551,7 @@ def main():
                              "unit": "GCUPS", "frac": cells_issued / (k2_ms * 1e-3) / 1e9 / alu_peak_gcups,
                              "peak_source": "148 SMs x 128 fp32 lanes x 1.965 GHz / 4 lane-ops per cell (SURVEY 8d)"},
         }
-        if not args.no_cpu_baseline:
+        if with_cpu and not args.no_cpu_baseline:
             be, kind = cpu_backend()
             n_thr = os.cpu_count() or 1
             nsub = min(args.reads_per_gpu, max(args.cpu_sample_reads, 8 * n_thr))
@@ -543,12 +573,179 @@ def main():
                                    "dtw_gcups": cells_ref / max(t_cpu - t_ev, 1e-9) / 1e9,
                                    "scores_bit_equal_gpu": bool(np.array_equal(sc_cpu.view(np.uint32), gpu_sc.view(np.uint32)))}
             out["cpu_baseline"]["parity_bit_exact"] = out["cpu_baseline"]["scores_bit_equal_gpu"]
-        sys.stdout.flush()
-        os.write(json_fd, (json.dumps(out) + "\n").encode())
     for c in ctxs:
         c.close()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------------
+# the whole map loop (ra_map_batch) on the datasets of BASELINE.json's configs
+# ------------------------------------------------------------------------------------------------------
+def map_opt_kwargs(name):
+    from workload.mapbench import CONFIGS
+    return dict(CONFIGS[name]["opt"])
+
+
+def map_path(args, rank, world, local, torch, dist, dev, binding):
+    """One step = one batch of reads through the whole map loop on the device: int16 DAC samples in, one PAF record per read out
+    (decode, K1, seeding, index lookup, anchor sort, chaining, chain DTW, primary chains / MAPQ / stop test for every chunk
+    round).  `value`: the batch already resident in HBM; `e2e`: ra_map_batch from pinned host buffers, copies inside."""
+    import rawalign_b200 as ra
+    from workload.mapbench import CONFIGS, Dataset, digest
+    name = args.config
+    cfg = CONFIGS[name]
+    ds = Dataset(name, log=log)
+    n_reads = args.map_reads_per_gpu
+    t0 = time.time()
+    raw, off, ln, dac_off, dac_scale = ds.reads(n_reads, seed=2 + rank)
+    log(f"[rank {rank}] {n_reads} reads simulated in {time.time() - t0:.1f}s: {len(raw) * 2 / 1e6:.0f} MB of int16 signal")
+    raw_p = torch.from_numpy(raw).pin_memory().numpy()            # the e2e path copies from pinned host memory every step
+    ctx = ra.Context(local)
+    t0 = time.time()
+    ix = ra.Index.load_file(ctx, ds.index_path)
+    t_index = time.time() - t0
+    opt = ra.ri_mapopt_full(**cfg["opt"])
+    if opt.flag & 0x4:
+        raise SystemExit("C3 (--dtw-output-cigar) is not wired into ra_map_batch yet; the traceback kernels are measured by tools/microbench_dtw.py")
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def step_e2e():
+        return ix.map_reads(opt, raw=raw_p, raw_off=off, raw_len=ln, offset=dac_off, scale=dac_scale)
+
+    def step_res(count=False):
+        return ix.map_reads(opt, resident_reads=n_reads, count_cells=count)
+
+    rec0, st0 = step_e2e()
+    recc, stc = step_res(True)                                    # one counted pass (cell counting is instrumentation)
+    for _ in range(max(args.warmup - 2, 1)):
+        step_res()
+    barrier()
+    sampler = ClockSampler(local); sampler.start()
+    l0 = ctx.launch_count
+    stage_acc = {}
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        rec, st = step_res()
+        for k, v in st.items():
+            if k.endswith("_ms"):
+                stage_acc[k] = stage_acc.get(k, 0.0) + v
+    barrier()
+    dt = time.perf_counter() - t0
+    launches = ctx.launch_count - l0
+    step_e2e(); barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        rec_e, st_e = step_e2e()
+    barrier()
+    dt_e2e = time.perf_counter() - t0
+    clocks = sampler.stop()
+    tt = torch.tensor([dt, dt_e2e], dtype=torch.float64, device=dev)
     if world > 1:
-        dist.destroy_process_group()
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    dt, dt_e2e = float(tt[0]), float(tt[1])
+    tot = torch.tensor([n_reads, stc["cells_useful"], stc["cells_issued"], int(rec0["mapped"].sum())], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tot)
+    reads_all, cells_all, issued_all, mapped_all = [float(x) for x in tot]
+    out = None
+    if rank == 0:
+        lines = ix.paf_lines(rec0)
+        out = {"metric": "reads_per_s", "value": reads_all * args.steps / dt, "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+               "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+               "config": {"workload": cfg["desc"] + "; the whole map loop per read batch (ra_map_batch: decode, event detection, seeding, index lookup, "
+                                      "chaining, chain DTW, primary chains, MAPQ, early stop), one step = one batch",
+                          "reads_per_gpu": n_reads, "reference_bases": int(sum(cfg["ref"])), "n_sequences": len(cfg["ref"]), "preset": cfg["preset"],
+                          "note": cfg.get("note", ""), "index": f"reference index file format, built by {ds.index_by}, loaded by ra_index_load_file in {t_index:.2f}s",
+                          "l2_policy": "inputs larger than L2 (signal batch >> 126 MB)", "cpu_binding": binding},
+               "reads_mapped_frac": mapped_all / reads_all,
+               "dtw_cells_per_step": {"useful": cells_all, "issued": issued_all},
+               "hot_path_gcups": cells_all * args.steps / dt / 1e9,
+               "map_stages_ms": {k: v / args.steps for k, v in sorted(stage_acc.items())},
+               "map_counts_per_step": {k: stc[k] for k in ("rounds", "chunks", "events", "seeds", "anchors", "chains_evaluated", "launches")},
+               "e2e": {"value": reads_all * args.steps / dt_e2e, "unit": "reads/s", "ms_per_step": dt_e2e / args.steps * 1e3,
+                       "h2d_bytes_per_step": int(raw.nbytes + off.nbytes + ln.nbytes + dac_off.nbytes + dac_scale.nbytes), "d2h_bytes_per_step": int(rec0.nbytes),
+                       "input": "int16 DAC samples of the whole reads in pinned host memory -> ra_map_batch -> one 88-byte record per read",
+                       "records_equal_resident_path": bool(rec_e.tobytes() == rec.tobytes() == rec0.tobytes())},
+               "gpu_launches": int(launches), "clocks": clocks, "paf_digest": digest(lines)}
+        if not args.no_cpu_baseline:
+            out["cpu_baseline"] = reference_map_sample(ds, cfg, raw, off, ln, lines, max(args.cpu_sample_reads, 256), n_reads)
+    ix.close(); ctx.close()
+    return out
+
+
+def reference_map_sample(ds, cfg, raw, off, ln, gpu_lines, nsub, n_reads, steps=1):
+    """The reference's own map loop -- kt_for(n_threads, map_worker_for, ...) through oracle/_ref/libra_refmap.so -- on the
+    first nsub reads of the batch with every host thread; its PAF lines (minus mt:f:) are diffed against the GPU's."""
+    import re
+    from oracle import RefMap
+    n_thr = os.cpu_count() or 1
+    nsub = min(nsub, n_reads)
+    if not RefMap.available():
+        return {"value": None, "unit": "reads/s", "cores": n_thr, "kind": "reference", "sample": "unavailable: oracle/_ref/libra_refmap.so was not built"}
+    rm = RefMap()
+    idx = rm.index_load(ds.index_path)
+    opt = rm.mapopt(**cfg["opt"])
+    end = int(off[nsub - 1]) + int(ln[nsub - 1])
+    sig = ds.decode(raw[:end])
+    rm.map_reads(idx, opt, sig, off[:min(nsub, 32)], ln[:min(nsub, 32)], n_threads=n_thr)      # warm-up
+    best = None
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        paf, mapped, chunks = rm.map_reads(idx, opt, sig, off[:nsub], ln[:nsub], n_threads=n_thr)
+        t = time.perf_counter() - t0
+        best = t if best is None else min(best, t)
+    n1 = max(1, nsub // n_thr)
+    t0 = time.perf_counter(); rm.map_reads(idx, opt, sig, off[:n1], ln[:n1], n_threads=1); t1 = time.perf_counter() - t0
+    strip = lambda l: re.sub(r"mt:f:[0-9.eE+-]+\t", "", l)
+    same = [strip(a) == b for a, b in zip(paf, gpu_lines[:nsub])]
+    rm.index_free(idx)
+    return {"value": nsub / best, "unit": "reads/s", "cores": n_thr, "kind": "reference",
+            "sample": f"first {nsub} reads of the batch through the reference's own map loop (kt_for + map_worker_for, rmap.cpp:667-822, {n_thr} threads): "
+                      "event detection, seeding, chaining and DTW as the reference does them; signal already decoded to float",
+            "seconds": best, "one_thread_reads_per_s": n1 / t1, "thread_scaling": (nsub / best) / (n1 / t1),
+            "mapped_frac": float(mapped.mean()), "mean_chunks": float(chunks.mean()),
+            "paf_lines_equal_gpu": int(sum(same)), "paf_lines_compared": len(same), "parity_bit_exact": bool(all(same))}
+
+
+def run_reference_map_arm(args):
+    """--impl reference for the map-loop configs: the reference's map loop on all host threads, each step a bounded sample."""
+    from workload.mapbench import CONFIGS, Dataset
+    name = args.config
+    cfg = CONFIGS[name]
+    ds = Dataset(name, log=log)
+    n_thr = os.cpu_count() or 1
+    nsub = int(os.environ.get("RA_REF_SAMPLE_READS", 64 * n_thr))
+    raw, off, ln, _, _ = ds.reads(nsub, seed=2)
+    from oracle import RefMap
+    if not RefMap.available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libra_refmap.so (the reference's compiled map loop) was not built in this checkout"}), flush=True)
+        return 0
+    rm = RefMap(); idx = rm.index_load(ds.index_path); opt = rm.mapopt(**cfg["opt"])
+    sig = ds.decode(raw)
+    for _ in range(max(1, min(args.warmup, 2))):
+        rm.map_reads(idx, opt, sig, off[:min(nsub, 4 * n_thr)], ln[:min(nsub, 4 * n_thr)], n_threads=n_thr)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        paf, mapped, chunks = rm.map_reads(idx, opt, sig, off, ln, n_threads=n_thr)
+    dt = time.perf_counter() - t0
+    n1 = max(1, nsub // n_thr)
+    t1 = time.perf_counter(); rm.map_reads(idx, opt, sig, off[:n1], ln[:n1], n_threads=1); t1 = time.perf_counter() - t1
+    val = nsub * args.steps / dt
+    out = {"impl": "reference", "metric": "reads_per_s", "value": val, "unit": "reads/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": cfg["desc"] + "; the whole map loop per read batch", "reads_per_step": nsub, "reference_bases": int(sum(cfg["ref"])),
+                      "n_sequences": len(cfg["ref"]), "preset": cfg["preset"], "note": cfg.get("note", "")},
+           "cpu_baseline": {"value": val, "unit": "reads/s", "cores": n_thr, "kind": "reference",
+                            "sample": f"{nsub} reads per step (same generator as the GPU arm) through the reference's own map loop: kt_for(n_threads, map_worker_for) "
+                                      f"(rmap.cpp:916, :667-822) on {n_thr} threads, index loaded by the reference's ri_idx_load; signal already decoded to float",
+                            "one_thread_reads_per_s": n1 / t1, "thread_scaling": val / (n1 / t1), "mapped_frac": float(mapped.mean()), "mean_chunks": float(chunks.mean())},
+           "e2e": {"value": val, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out), flush=True)
     return 0
 
 

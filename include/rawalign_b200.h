@@ -113,6 +113,10 @@ const char *ra_last_error(void);
 void        ra_mapopt_init(ra_mapopt_t *opt);
 int         ra_set_opt(ra_ctx *ctx, const ra_mapopt_t *opt);
 int         ra_get_opt(const ra_ctx *ctx, ra_mapopt_t *opt);
+/* Performance knobs that do not change results (defaults in parentheses): "chain_slice_min_anchors" (2097152: anchors per
+ * upload slice of ra_align_chains_batch, at most 8 slices), "k1_groups" (8: chunk groups of the resident event detection that run
+ * on concurrent streams), "k1_priority_stream" (1: the latency-bound K1 kernels on a high-priority stream). */
+int         ra_set_tuning(ra_ctx *ctx, const char *name, int64_t value);
 /* number of kernels this context has launched since creation (bench.py's gpu_launches) */
 uint64_t    ra_launch_count(const ra_ctx *ctx);
 /* Device time of the most recent event-detection and DTW batches, measured with CUDA events on the
@@ -203,8 +207,14 @@ int ra_dtw_tb_batch(ra_ctx *ctx, const float *a_arena, uint64_t n_a, const float
  * alignment_score[k] receives chain.alignment_score; keep[k] (optional) receives
  * alignment_score >= dtw_min_score (rmap.cpp:518). cells_issued / cells_useful (optional) receive
  * the DP cells the GPU evaluated and the cells the reference would have evaluated.
- * The slicing, the DTW and the replay all run in one kernel (csrc/chains.cu); 8 bytes per anchor and
- * 32 per chain go to the device, 5 bytes per chain come back. */
+ * Sparse border: a plan kernel, a flat part-cost kernel over all anchor-to-anchor parts and a replay kernel
+ * (csrc/chains_sparse.cu); global border: one item per chain through the wavefront kernels with the replay on the host.
+ * 8 bytes per anchor and 32 per chain go to the device, 5 bytes per chain come back.
+ * Preconditions, checked (RA_EINVAL): chain records inside the anchor array; every chain's anchors monotonic (anchors[0] =
+ * chain end, neither coordinate increases along the array -- the reference's chainer makes them strictly decreasing,
+ * rmap.cpp:456-465); the chain end inside the read / reference arenas.  The interior anchors are checked on the device
+ * (k_validate_chains) before any kernel indexes with them.  For the _dev form with caller-owned arenas the arena sizes are
+ * unknown to the library: monotonicity is checked, the bounds of ra_chain_t::read_off / ref_off are the caller's. */
 int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
                           const float *ref_arena, uint64_t n_ref,
                           const ra_anchor_t *anchors, uint64_t n_anchors,
@@ -293,12 +303,14 @@ typedef struct ra_map_stats_s {
 	float    decode_ms, events_ms, seed_ms, sort_ms, chain_ms, dtw_ms, select_ms, total_ms;
 	uint32_t rounds; uint32_t reserved;
 	uint64_t chunks, events, seeds, anchors, chains_evaluated, launches;
+	uint64_t cells_issued, cells_useful;   /* DP cells of the chain evaluations; counted only when reserved == 1 on entry */
 } ra_map_stats_t;
 
 /* Maps a batch of reads.  Signal either as int16 DAC samples (raw != NULL: read r is raw[raw_off[r] .. +raw_len[r]),
  * offset[r] / scale[r] as in ra_detect_events_raw_batch; decoded on the device, rsig.cpp:213-222) or as float pA
  * (raw == NULL: sig[sig_off[r] .. +sig_len[r]) = ri_sig_t::sig).  All pointers are host pointers.  out: n_reads records in
- * input order.  Minimizer (w > 0) and BLEND (n > 0) indexes return RA_EUNSUP. */
+ * input order.  raw == NULL and sig == NULL maps again the batch the previous call left on the device (no upload, no decode:
+ * the device-resident form).  Minimizer (w > 0) and BLEND (n > 0) indexes return RA_EUNSUP. */
 int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt,
                  const int16_t *raw, const uint64_t *raw_off, const uint32_t *raw_len, const float *offset, const float *scale,
                  const float *sig, const uint64_t *sig_off, const uint32_t *sig_len,

@@ -53,7 +53,7 @@ class MapStats(C.Structure):
     """ra_map_stats_t"""
     _fields_ = [(n, C.c_float) for n in ("decode_ms", "events_ms", "seed_ms", "sort_ms", "chain_ms", "dtw_ms", "select_ms", "total_ms")] + \
                [("rounds", C.c_uint32), ("reserved", C.c_uint32)] + \
-               [(n, C.c_uint64) for n in ("chunks", "events", "seeds", "anchors", "chains_evaluated", "launches")]
+               [(n, C.c_uint64) for n in ("chunks", "events", "seeds", "anchors", "chains_evaluated", "launches", "cells_issued", "cells_useful")]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}
@@ -106,6 +106,7 @@ def load() -> C.CDLL:
     L.ra_align_chains_batch_dev.argtypes = [vp, vp, vp, vp, u64, vp, u32, vp, u32, i32, vp, vp, vp, C.POINTER(u64), C.POINTER(u64)]
     L.ra_align_chains_cigar_batch.argtypes = [vp, vp, u64, vp, u64, vp, u64, vp, u32, vp, vp, vp, vp, vp, u64, vp]
     L.ra_get_opt.argtypes = [vp, C.POINTER(MapOpt)]
+    L.ra_set_tuning.argtypes = [vp, C.c_char_p, C.c_int64]; L.ra_set_tuning.restype = C.c_int
     L.ra_ri_mapopt_init.argtypes = [C.POINTER(RiMapOpt)]; L.ra_ri_mapopt_init.restype = None
     L.ra_index_load_file.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
     L.ra_index_load_flat.argtypes = [vp] + [C.c_int32] * 6 + [u32, vp, vp, vp, u64, vp, vp, vp, C.POINTER(vp)]
@@ -133,5 +134,5 @@ EXPORTED_SYMBOLS = [
     "ra_detect_events_batch", "ra_detect_events_batch_dev", "ra_detect_events_raw_batch", "ra_last_event_positions",
     "ra_dtw_batch", "ra_dtw_batch_dev", "ra_dtw_cells", "ra_dtw_tb_batch",
     "ra_align_chains_batch", "ra_align_chains_batch_dev", "ra_align_chains_cigar_batch",
-    "ra_get_opt", "ra_ri_mapopt_init", "ra_index_load_file", "ra_index_load_flat", "ra_index_destroy", "ra_index_info", "ra_map_batch",
+    "ra_get_opt", "ra_set_tuning", "ra_ri_mapopt_init", "ra_index_load_file", "ra_index_load_flat", "ra_index_destroy", "ra_index_info", "ra_map_batch",
 ]

@@ -75,6 +75,10 @@ class Context:
         self.close()
 
     # ---- options / reference mirror ------------------------------------------------------------
+    def set_tuning(self, name: str, value: int):
+        """ra_set_tuning: performance knobs that do not change results."""
+        check(self._L.ra_set_tuning(self._h, name.encode(), int(value)))
+
     def set_opt(self, opt: MapOpt):
         check(self._L.ra_set_opt(self._h, C.byref(opt)))
         self.opt = opt

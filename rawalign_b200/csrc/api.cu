@@ -114,6 +114,7 @@ struct ra_ctx {
 	bool force_generic_dtw = false;    // test hook (reserved bit 2): every item through the generic shared-memory DTW kernel
 	bool legacy_sparse_tiles = false;  // test hook (reserved bit 3): sparse parts through the CTA-wide tiles of k_sp_parts instead of k_sp_parts2
 	bool want_ev_pos = true;           // keep the event start samples of the last K1 call (ra_last_event_positions)
+	uint64_t chain_slice_min_anchors = 2u << 20;   // ra_set_tuning("chain_slice_min_anchors"): anchors per upload slice of ra_align_chains_batch
 	// traceback
 	DevBuf dirs, dir_off, slot_off, slot_i, slot_j, slot_d, path_len, path_off, out_i, out_j, out_d;
 };
@@ -474,7 +475,7 @@ int sparse_pipeline(ra_ctx *ctx, const ra::ChainLaunch &L, uint32_t n_chains, ui
 int chains_dev(ra_ctx *ctx, const float *read_dev, const float *ref_dev, const ra_anchor_t *anchors_dev,
                const ra_chain_t *chains_dev_p, const uint32_t *group_first_dev, uint32_t n_groups, int min_score_mode,
                const float *min_score_dev, float *score_dev, uint8_t *keep_dev, uint64_t *cells_host /* [2] or null */,
-               uint32_t n_chains, uint64_t n_anchors)
+               uint32_t n_chains, uint64_t n_anchors, uint64_t n_read = 0, uint64_t n_ref = 0)
 {
 	if (n_groups == 0) { if (cells_host) cells_host[0] = cells_host[1] = 0; return RA_OK; }
 	const ra_mapopt_t &o = ctx->opt;
@@ -494,9 +495,15 @@ int chains_dev(ra_ctx *ctx, const float *read_dev, const float *ref_dev, const r
 		L.band_frac = o.dtw_band_radius_frac; L.match_bonus = o.dtw_match_bonus; L.min_dtw_score = o.dtw_min_score;
 		L.min_score_mode = min_score_mode; L.min_score = min_score_dev; L.score = score_dev; L.keep = keep_dev;
 		L.work_counter = ctx->counter.as<uint32_t>(); L.need_cap = ctx->counter.as<uint32_t>() + 4;
+		L.error = ctx->counter.as<uint32_t>() + 8; L.n_read = n_read; L.n_ref = n_ref;
 		L.cells = cells_host ? ctx->cells.as<uint64_t>() : nullptr;      // cell counting is instrumentation: off unless asked for
 		L.ring_scratch = ring_cap ? ctx->chain_ring.as<float>() : nullptr; L.ring_cap = ring_cap;
 		RA_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
+		// every anchor of every chain is checked on the device before anything indexes with it (the kernels pack anchor
+		// distances into narrow descriptor fields and index the arenas with them)
+		RA_CUDA(cudaMemsetAsync(L.error, 0, sizeof(uint32_t), ctx->stream));
+		RA_CUDA(ra::launch_validate_chains(L, 0, n_chains, ctx->stream));
+		ctx->launches += 1;
 		if (o.dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_SPARSE) {
 			if ((rc = sparse_pipeline(ctx, L, n_chains, n_anchors))) return rc;
 		} else {
@@ -505,11 +512,13 @@ int chains_dev(ra_ctx *ctx, const float *read_dev, const float *ref_dev, const r
 		}
 		RA_CUDA(cudaEventRecord(ctx->ev[4], ctx->stream));
 		ctx->timed_dtw = true;
-		uint32_t need = 0;
+		uint32_t need = 0, bad = 0;
 		RA_CUDA(cudaMemcpyAsync(&need, L.need_cap, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+		RA_CUDA(cudaMemcpyAsync(&bad, L.error, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
 		uint64_t cells[2] = {0, 0};
 		if (L.cells) RA_CUDA(cudaMemcpyAsync(cells, L.cells, sizeof(cells), cudaMemcpyDeviceToHost, ctx->stream));
 		RA_CUDA(cudaStreamSynchronize(ctx->stream));
+		if (bad) return fail(RA_EINVAL, "a chain's anchors are not monotonic (anchors[0] must be the chain end, positions non-increasing) or leave the arenas");
 		if (need == 0) { if (cells_host) { cells_host[0] = cells[0]; cells_host[1] = cells[1]; } return RA_OK; }
 		if (attempt == 1) break;
 		if ((rc = ctx->chain_ring.reserve(warps * 3 * (size_t)need * sizeof(float)))) return rc;
@@ -647,6 +656,14 @@ int ra_set_opt(ra_ctx *ctx, const ra_mapopt_t *opt)
 
 uint64_t ra_launch_count(const ra_ctx *ctx) { return ctx ? ctx->launches : 0; }
 int ra_get_opt(const ra_ctx *ctx, ra_mapopt_t *opt) { if (!ctx || !opt) return fail(RA_EINVAL, "NULL argument"); *opt = ctx->opt; return RA_OK; }
+int ra_set_tuning(ra_ctx *ctx, const char *name, int64_t value)
+{
+	if (!ctx || !name) return fail(RA_EINVAL, "NULL argument");
+	if (!strcmp(name, "chain_slice_min_anchors")) { if (value < 1) return fail(RA_EINVAL, "chain_slice_min_anchors must be >= 1"); ctx->chain_slice_min_anchors = (uint64_t)value; return RA_OK; }
+	if (!strcmp(name, "k1_groups")) { if (value < 1 || value > kSliceStreams) return fail(RA_EINVAL, "k1_groups must be 1..%d", kSliceStreams); ctx->k1_groups = (int)value; return RA_OK; }
+	if (!strcmp(name, "k1_priority_stream")) { ctx->k1_prio = value != 0; return RA_OK; }
+	return fail(RA_EINVAL, "unknown tuning parameter %s", name);
+}
 // internal (map.cu): kernels launched outside this file count too; errors raised there go through ra_last_error()
 void ra__add_launches(ra_ctx *ctx, uint64_t n) { if (ctx) ctx->launches += n; }
 int ra__device(const ra_ctx *ctx) { return ctx ? ctx->device : 0; }
@@ -745,7 +762,8 @@ int ra_detect_events_batch(ra_ctx *ctx, const float *sig, uint64_t n_sig, const 
 	if ((rc = ctx->chunk_off.reserve((size_t)(n_chunks + 1) * sizeof(uint64_t)))) return rc;
 	if ((rc = ctx->chunk_len.reserve((size_t)(n_chunks + 1) * sizeof(uint32_t)))) return rc;
 	if ((rc = ctx->ev_off.reserve((size_t)(n_chunks + 1) * sizeof(uint64_t)))) return rc;
-	const uint64_t dev_cap = std::min<uint64_t>(ev_cap, sum_len / 2 + n_chunks + 16);   // peaks are >= 3 samples apart per detector: < 0.54 events per sample
+	// the same bound events_pipe_layout sizes the peak lists with: emissions of one detector are >= w/2 + 2 samples apart
+	const uint64_t dev_cap = std::min<uint64_t>(ev_cap, sum_len / (ctx->opt.window_length1 / 2 + 2) + sum_len / (ctx->opt.window_length2 / 2 + 2) + 4ull * n_chunks + 16);
 	if ((rc = ctx->ev_out.reserve((size_t)std::max<uint64_t>(dev_cap, 1) * sizeof(float)))) return rc;
 	if (n_chunks == 0) { ev_off[0] = 0; ctx->last_events = ctx->resident_events = 0; return RA_OK; }
 	// Slices of chunks; slice k may start once sig[0 .. need[k]) is on the device (need = running max of chunk ends).
@@ -803,7 +821,7 @@ int ra_detect_events_raw_batch(ra_ctx *ctx, const int16_t *raw, uint64_t n_raw, 
 	if ((rc = ctx->chunk_off.reserve((size_t)(max_chunks_total + 1) * sizeof(uint64_t)))) return rc;
 	if ((rc = ctx->chunk_len.reserve((size_t)(max_chunks_total + 1) * sizeof(uint32_t)))) return rc;
 	if ((rc = ctx->ev_off.reserve((size_t)(max_chunks_total + 1) * sizeof(uint64_t)))) return rc;
-	const uint64_t dev_cap = std::min<uint64_t>(ev_cap, max_samples / 2 + max_chunks_total + 16);
+	const uint64_t dev_cap = std::min<uint64_t>(ev_cap, max_samples / (ctx->opt.window_length1 / 2 + 2) + max_samples / (ctx->opt.window_length2 / 2 + 2) + 4ull * max_chunks_total + 16);
 	if ((rc = ctx->ev_out.reserve((size_t)std::max<uint64_t>(dev_cap, 1) * sizeof(float)))) return rc;
 	if ((rc = ctx->pin_lsig.reserve((size_t)(n_reads + 1) * 4))) return rc;
 	chunk_first[0] = 0;
@@ -1066,6 +1084,9 @@ static int chain_items(const ra_mapopt_t &o, const ra_anchor_t *anc, const ra_ch
 {
 	if (ch.n_anchors == 0) return fail(RA_EINVAL, "chain without anchors");
 	const bool banded = (o.dtw_fill_method == RA_DTW_FILL_METHOD_BANDED);
+	for (uint32_t p = 1; p < ch.n_anchors; ++p)                    // anchors[0] is the chain end; positions never increase along the array
+		if (anc[p].query_position > anc[p - 1].query_position || anc[p].target_position > anc[p - 1].target_position)
+			return fail(RA_EINVAL, "chain anchors are not monotonic (anchor %u)", p);
 	auto push = [&](const ra_anchor_t &s, const ra_anchor_t &e, bool excl) {
 		ra_dtw_item_t it;
 		it.a_off = ch.read_off + s.query_position;                  // rmap.cpp:201, :259
@@ -1160,7 +1181,7 @@ int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
 	// Sparse border with chains laid out in order: anchors and chain records go up in slices (h2d stream) and every slice is
 	// evaluated as soon as it has arrived; anything else takes the one-shot path.
 	const bool in_order = laid_in_order && ctx->opt.dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_SPARSE;
-	const int n_slices = in_order ? (int)std::min<uint64_t>(kMaxSlices, std::max<uint64_t>(1, n_anchors / (2u << 20))) : 1;   // >= 16 MB of anchors per slice
+	const int n_slices = in_order ? (int)std::min<uint64_t>(kMaxSlices, std::max<uint64_t>(1, n_anchors / ctx->chain_slice_min_anchors)) : 1;   // >= 16 MB of anchors per slice by default
 	if (n_slices > 1) {
 		if ((rc = ctx->counter.reserve(64))) return rc;
 		if ((rc = ctx->cells.reserve(64))) return rc;
@@ -1195,6 +1216,8 @@ int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
 		L.band_frac = o.dtw_band_radius_frac; L.match_bonus = o.dtw_match_bonus; L.min_dtw_score = o.dtw_min_score;
 		L.min_score_mode = min_score_mode; L.min_score = ms_dev; L.score = ctx->score.as<float>(); L.keep = ctx->keep.as<uint8_t>();
 		L.work_counter = ctx->counter.as<uint32_t>(); L.need_cap = ctx->counter.as<uint32_t>() + 4;
+		L.error = ctx->counter.as<uint32_t>() + 8; L.n_read = nr; L.n_ref = nf;
+		RA_CUDA(cudaMemsetAsync(L.error, 0, sizeof(uint32_t), ctx->stream));
 		L.cells = want_cells ? ctx->cells.as<uint64_t>() : nullptr;
 		const size_t warps = (size_t)ctx->n_sm * ra::kChainCtasPerSm * 4;
 		uint32_t ring_cap = ctx->chain_ring.cap ? (uint32_t)(ctx->chain_ring.cap / (warps * 3 * sizeof(float))) : 0;
@@ -1211,19 +1234,23 @@ int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
 			const uint32_t k0 = gf[g0], k1 = gf[g1];
 			const uint64_t a0 = chains[k0].anchor_off, a1 = chains[k1 - 1].anchor_off + chains[k1 - 1].n_anchors;
 			(void)a0; (void)a1;
+			RA_CUDA(ra::launch_validate_chains(Ls, k0, k1, ctx->stream));       // interior anchors of the slice, before anything indexes with them
+			ctx->launches += 1;
 			if ((rc = sparse_pipeline(ctx, Ls, n_chains, n_anchors, k == 0))) return rc;
 		}
 		RA_CUDA(cudaEventRecord(ctx->ev[4], ctx->stream));
 		ctx->timed_dtw = true;
 		tr.mark("chains: kernels queued");
 		if (tr.on) { cudaStreamSynchronize(ctx->h2d); tr.mark("chains: h2d done"); cudaStreamSynchronize(ctx->stream); tr.mark("chains: kernels done"); }
-		uint32_t need = 0;
+		uint32_t need = 0, bad = 0;
 		RA_CUDA(cudaMemcpyAsync(&need, L.need_cap, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+		RA_CUDA(cudaMemcpyAsync(&bad, L.error, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
 		if (L.cells) RA_CUDA(cudaMemcpyAsync(cells, L.cells, sizeof(cells), cudaMemcpyDeviceToHost, ctx->stream));
 		RA_CUDA(cudaMemcpyAsync(alignment_score, ctx->score.p, (size_t)n_chains * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
 		if (keep) RA_CUDA(cudaMemcpyAsync(keep, ctx->keep.p, (size_t)n_chains, cudaMemcpyDeviceToHost, ctx->stream));
 		RA_CUDA(cudaStreamSynchronize(ctx->stream));
 		tr.mark("chains: results back");
+		if (bad) return fail(RA_EINVAL, "a chain's anchors are not monotonic (anchors[0] must be the chain end, positions non-increasing) or leave the arenas");
 		if (need == 0) {
 			if (cells_issued) *cells_issued = cells[0];
 			if (cells_useful) *cells_useful = cells[1];
@@ -1277,7 +1304,7 @@ int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
 		RA_CUDA(cudaMemcpyAsync(ctx->group_first.p, gf.data(), gf.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
 	}
 	if ((rc = chains_dev(ctx, read_dev, ref_dev, ctx->anchors.as<ra_anchor_t>(), ctx->chains.as<ra_chain_t>(), ctx->group_first.as<uint32_t>(),
-	                     n_groups, min_score_mode, ms_dev, ctx->score.as<float>(), ctx->keep.as<uint8_t>(), want_cells ? cells : nullptr, n_chains, n_anchors))) return rc;
+	                     n_groups, min_score_mode, ms_dev, ctx->score.as<float>(), ctx->keep.as<uint8_t>(), want_cells ? cells : nullptr, n_chains, n_anchors, nr, nf))) return rc;
 	RA_CUDA(cudaMemcpyAsync(alignment_score, ctx->score.p, (size_t)n_chains * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
 	if (keep) RA_CUDA(cudaMemcpyAsync(keep, ctx->keep.p, (size_t)n_chains, cudaMemcpyDeviceToHost, ctx->stream));
 	RA_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -1298,7 +1325,8 @@ int ra_align_chains_batch_dev(ra_ctx *ctx, const float *read_arena_dev, const fl
 	if (n_groups && (!read_dev || !ref_dev)) return fail(RA_EINVAL, "no read or reference arena on the device");
 	uint64_t cells[2] = {0, 0};
 	int rc = chains_dev(ctx, read_dev, ref_dev, anchors_dev, chains_dev_p, group_first_dev, n_groups, min_score_mode, min_score_dev,
-	                    alignment_score_dev, keep_dev, (cells_issued || cells_useful) ? cells : nullptr, n_chains, n_anchors);
+	                    alignment_score_dev, keep_dev, (cells_issued || cells_useful) ? cells : nullptr, n_chains, n_anchors,
+	                    read_arena_dev ? 0 : ctx->resident_events, ref_arena_dev ? 0 : ctx->ref_n);   // caller-owned arenas: sizes unknown here
 	if (rc) return rc;
 	if (cells_issued) *cells_issued = cells[0];
 	if (cells_useful) *cells_useful = cells[1];

@@ -57,6 +57,7 @@ k_chain_eval(ChainLaunch L)
 	float *my_gring = L.ring_scratch ? L.ring_scratch + (size_t)gwarp * 3 * L.ring_cap : nullptr;
 	uint64_t cells_issued = 0, cells_useful = 0;
 
+	if (*reinterpret_cast<volatile uint32_t *>(L.error)) return;             // a chain failed validation: nothing is evaluated
 	for (;;) {
 		uint32_t g = 0;
 		if (lane == 0) g = atomicAdd(L.work_counter, 1u);
@@ -164,6 +165,34 @@ k_chain_eval(ChainLaunch L)
 			atomicAdd(reinterpret_cast<unsigned long long *>(L.cells + 1), (unsigned long long)cells_useful);
 		}
 	}
+}
+
+__global__ void __launch_bounds__(128)
+k_validate_chains(ChainLaunch L, uint32_t k0, uint32_t k1)
+{
+	const uint32_t k = k0 + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+	const int lane = threadIdx.x & 31;
+	if (k >= k1) return;
+	const ra_chain_t ch = L.chains[k];
+	const ra_anchor_t *__restrict__ anc = L.anchors + ch.anchor_off;
+	bool bad = ch.n_anchors == 0;
+	for (uint32_t p = 1 + lane; p < ch.n_anchors; p += 32) {
+		const ra_anchor_t a = anc[p - 1], b = anc[p];
+		bad |= (b.query_position > a.query_position) | (b.target_position > a.target_position);
+	}
+	if (lane == 0 && ch.n_anchors) {
+		const ra_anchor_t e = anc[0];
+		if (L.n_read && ch.read_off + e.query_position >= L.n_read) bad = true;
+		if (L.n_ref && ch.ref_off + e.target_position >= L.n_ref) bad = true;
+	}
+	if (__any_sync(0xffffffffu, bad) && lane == 0) atomicOr(L.error, 1u);
+}
+
+cudaError_t launch_validate_chains(const ChainLaunch &L, uint32_t k0, uint32_t k1, cudaStream_t s)
+{
+	if (k1 <= k0) return cudaSuccess;
+	k_validate_chains<<<(uint32_t)(((uint64_t)(k1 - k0) * 32 + 127) / 128), 128, 0, s>>>(L, k0, k1);
+	return cudaGetLastError();
 }
 
 cudaError_t launch_chain_eval(const ChainLaunch &L, int n_sm, cudaStream_t s)

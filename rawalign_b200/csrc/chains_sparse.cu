@@ -67,10 +67,11 @@ k_sp_prep(ChainLaunch L, SparsePlan P, int phase)
 	const int lane = threadIdx.x & 31;
 	uint32_t k0 = 0, k1 = 0;
 	if (g < L.n_groups) { k0 = L.group_first[g]; k1 = L.group_first[g + 1]; }
+	const bool invalid = *reinterpret_cast<volatile uint32_t *>(L.error) != 0;   // k_validate_chains found a malformed chain: plan no parts at all
 	uint32_t my_parts = 0, my_tiles = 0;
 	for (uint32_t k = k0; k < k1; ++k) {
 		const ra_chain_t ch = L.chains[k];
-		if (chain_active(L, P, phase, g, k, k0, ch)) { my_parts += ch.n_anchors - 1u; my_tiles += (ch.n_anchors - 1u + P.tile_parts - 1) / P.tile_parts; }
+		if (!invalid && chain_active(L, P, phase, g, k, k0, ch)) { my_parts += ch.n_anchors - 1u; my_tiles += (ch.n_anchors - 1u + P.tile_parts - 1) / P.tile_parts; }
 	}
 	uint32_t ip = my_parts, it = my_tiles;                                    // inclusive warp scans
 #pragma unroll
@@ -84,7 +85,7 @@ k_sp_prep(ChainLaunch L, SparsePlan P, int phase)
 	uint64_t pb = bp + ip - my_parts, tb = bt + it - my_tiles;
 	for (uint32_t k = k0; k < k1; ++k) {
 		const ra_chain_t ch = L.chains[k];
-		const bool active = chain_active(L, P, phase, g, k, k0, ch);
+		const bool active = !invalid && chain_active(L, P, phase, g, k, k0, ch);
 		const uint32_t parts = active ? ch.n_anchors - 1u : 0u;
 		P.n_parts[k] = parts;
 		P.part_base[k] = pb;
@@ -537,7 +538,9 @@ k_sp_replay(ChainLaunch L, SparsePlan P, int phase)
 	const uint32_t kb = (phase == 2) ? k0 + 1 : k0, ke = (phase == 1) ? min(k0 + 1, k1) : k1;
 	float best = (phase == 2) ? P.best[g] : 0.0f;                               // rmap.cpp:515
 	uint64_t useful = 0;
+	const bool invalid = *reinterpret_cast<volatile uint32_t *>(L.error) != 0;
 	for (uint32_t k = kb; k < ke; ++k) {
+		if (invalid) { if (lane == 0) { L.score[k] = RA_SCORE_DROPPED; if (L.keep) L.keep[k] = 0; } continue; }   // nothing was evaluated; the entry point reports RA_EINVAL
 		const ra_chain_t ch = L.chains[k];
 		const uint32_t parts = ch.n_anchors - 1u;
 		const float ms = (L.min_score_mode == 1) ? best : (L.min_score ? L.min_score[k] : RA_SCORE_DROPPED);

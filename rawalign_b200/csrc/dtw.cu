@@ -199,11 +199,14 @@ cudaError_t launch_dtw_generic(const DtwLaunch &L, bool traceback, int n_sm, cud
 	cudaError_t e = cudaMemsetAsync(L.work_counter, 0, sizeof(uint32_t), s);
 	if (e != cudaSuccess) return e;
 	const size_t smem = (size_t)kWarpsPerCta * 3 * kSmemRingCap * sizeof(float);
-	static bool attr_done = false;
-	if (!attr_done) {
-		cudaFuncSetAttribute(k_dtw_generic<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-		cudaFuncSetAttribute(k_dtw_generic<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-		attr_done = true;
+	static unsigned long long attr_devices = 0;                       // the opt-in is per function AND per device
+	int dev = 0;
+	cudaGetDevice(&dev);
+	if (!((attr_devices >> (dev & 63)) & 1ull)) {
+		e = cudaFuncSetAttribute(k_dtw_generic<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		if (e == cudaSuccess) e = cudaFuncSetAttribute(k_dtw_generic<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+		if (e != cudaSuccess) return e;
+		__atomic_fetch_or(&attr_devices, 1ull << (dev & 63), __ATOMIC_RELAXED);
 	}
 	// persistent grid: 4 CTAs of 4 warps per SM (shared-memory bound), never more warps than problems
 	uint32_t ctas = (uint32_t)n_sm * 4u;

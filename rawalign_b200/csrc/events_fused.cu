@@ -326,11 +326,14 @@ cudaError_t launch_events_fused(const float *sig, const uint64_t *chunk_off, con
 	k = k < 1 ? 1 : (k > kFusedMaxK ? kFusedMaxK : k);
 	A.k = k;
 	const size_t smem = events_fused_smem(k);
-	static bool attr_done = false;
-	if (!attr_done) {
-		cudaFuncSetAttribute(k_events_fused<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)events_fused_smem(kFusedMaxK));
-		cudaFuncSetAttribute(k_events_fused<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)events_fused_smem(kFusedMaxK));
-		attr_done = true;
+	static unsigned long long attr_devices = 0;                       // the opt-in is per function AND per device
+	int dev = 0;
+	cudaGetDevice(&dev);
+	if (!((attr_devices >> (dev & 63)) & 1ull)) {
+		cudaError_t ae = cudaFuncSetAttribute(k_events_fused<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)events_fused_smem(kFusedMaxK));
+		if (ae == cudaSuccess) ae = cudaFuncSetAttribute(k_events_fused<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)events_fused_smem(kFusedMaxK));
+		if (ae != cudaSuccess) return ae;
+		__atomic_fetch_or(&attr_devices, 1ull << (dev & 63), __ATOMIC_RELAXED);
 	}
 	const uint32_t per_cta = (uint32_t)k * kFusedWarps;
 	const uint32_t ctas = (n_chunks + per_cta - 1) / per_cta;

@@ -40,7 +40,11 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 	if (!ctx || !ix || !opt || !out) return ra__fail(RA_EINVAL, "NULL argument");
 	if (ix->ctx != ctx) return ra__fail(RA_EINVAL, "the index was loaded for another context");
 	const bool from_raw = raw != nullptr;
-	if (from_raw ? (!raw_off || !raw_len || !offset || !scale) : (!sig || !sig_off || !sig_len)) return ra__fail(RA_EINVAL, "NULL signal table");
+	const bool resident = !raw && !sig;                            // map again the signal the previous call left on the device
+	if (resident) {
+		if (ix->last_len.size() != n_reads || n_reads == 0) return ra__fail(RA_EINVAL, "no resident batch of %u reads on the device", n_reads);
+	} else if (from_raw ? (!raw_off || !raw_len || !offset || !scale) : (!sig || !sig_off || !sig_len)) return ra__fail(RA_EINVAL, "NULL signal table");
+	const bool count_cells = stats && stats->reserved == 1;        // instrumentation: DP cells of the chain evaluations (costs a counter pass)
 	if (ix->w != 0 || ix->n != 0) return ra__fail(RA_EUNSUP, "minimizer (w=%d) / BLEND (n=%d) seeding is not implemented on the device", ix->w, ix->n);
 	if (opt->num_best_chains < 1 || opt->num_best_chains > (uint32_t)kMaxBest) return ra__fail(RA_EUNSUP, "num_best_chains %u (supported: 1..%d)", opt->num_best_chains, kMaxBest);
 	if (opt->chunk_size == 0 || opt->max_num_chunk == 0) return ra__fail(RA_EINVAL, "chunk_size / max_num_chunk must be positive");
@@ -50,6 +54,7 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 	if (cap_chains64 > 8192) return ra__fail(RA_EUNSUP, "%u reference sequences x %u best chains exceed the per-read chain table", ix->n_seq, opt->num_best_chains);
 	if (stats) memset(stats, 0, sizeof(*stats));
 	if (n_reads == 0) return RA_OK;
+	uint64_t cells_acc[2] = {0, 0};
 	int rc;
 	{   // hot-path options of the context follow the map options; fp_contract / test hooks stay as the context has them
 		ra_mapopt_t o; if ((rc = ra_get_opt(ctx, &o))) return rc;
@@ -78,8 +83,13 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 	P.e = ix->e; P.q = ix->q; P.lq = ix->lq; P.n_seq = ix->n_seq; P.cap_chains = (uint32_t)cap_chains64; P.slot_bits = ix->slot_bits;
 
 	// ---- signal to the device, read table ------------------------------------------------------------------------------
-	const uint64_t *in_off = from_raw ? raw_off : sig_off;
-	const uint32_t *in_len = from_raw ? raw_len : sig_len;
+	if (!resident) {
+		ix->last_off.assign(from_raw ? raw_off : sig_off, (from_raw ? raw_off : sig_off) + n_reads);
+		ix->last_len.assign(from_raw ? raw_len : sig_len, (from_raw ? raw_len : sig_len) + n_reads);
+		ix->last_raw = from_raw;
+	}
+	const uint64_t *in_off = ix->last_off.data();
+	const uint32_t *in_len = ix->last_len.data();
 	uint64_t n_samples = 0;
 	for (uint32_t r = 0; r < n_reads; ++r) n_samples = std::max<uint64_t>(n_samples, in_off[r] + in_len[r]);
 	std::vector<ReadState> hst(n_reads);
@@ -108,7 +118,9 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 	if (!ix->pin) { MAP_CUDA(cudaMallocHost(&ix->pin, 4096)); ix->pin_cap = 4096; }
 	MAP_CUDA(cudaMemcpyAsync(ix->state.p, hst.data(), (size_t)n_reads * sizeof(ReadState), cudaMemcpyHostToDevice, S));
 	const uint32_t *l_sig_dev = nullptr;
-	if (from_raw) {
+	if (resident) {
+		if (ix->last_raw) l_sig_dev = ix->lsig_keep.as<uint32_t>();
+	} else if (from_raw) {
 		if ((rc = ix->raw16.reserve(std::max<uint64_t>(n_samples, 1) * 2 + 64)) || (rc = ix->rd_off.reserve((size_t)n_reads * 8)) || (rc = ix->rd_len.reserve((size_t)n_reads * 4)) ||
 		    (rc = ix->rd_offset.reserve((size_t)n_reads * 4)) || (rc = ix->rd_scale.reserve((size_t)n_reads * 4)) || (rc = ix->seed_cnt.reserve((size_t)n_reads * 4))) return rc;
 		MAP_CUDA(cudaMemcpyAsync(ix->raw16.p, raw, n_samples * 2, cudaMemcpyHostToDevice, S));
@@ -116,7 +128,8 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 		MAP_CUDA(cudaMemcpyAsync(ix->rd_len.p, raw_len, (size_t)n_reads * 4, cudaMemcpyHostToDevice, S));
 		MAP_CUDA(cudaMemcpyAsync(ix->rd_offset.p, offset, (size_t)n_reads * 4, cudaMemcpyHostToDevice, S));
 		MAP_CUDA(cudaMemcpyAsync(ix->rd_scale.p, scale, (size_t)n_reads * 4, cudaMemcpyHostToDevice, S));
-		uint32_t *lsd = ix->n_hits.as<uint32_t>();                 // per-read l_sig of the decode (n_hits is free until the first round)
+		if ((rc = ix->lsig_keep.reserve((size_t)n_reads * 4))) return rc;
+		uint32_t *lsd = ix->lsig_keep.as<uint32_t>();              // per-read l_sig of the decode (kept for resident re-runs)
 		MAP_CUDA(ra::launch_decode_raw(ix->raw16.as<int16_t>(), ix->rd_off.as<uint64_t>(), ix->rd_len.as<uint32_t>(), ix->rd_offset.as<float>(),
 		                               ix->rd_scale.as<float>(), n_reads, ix->sig.as<float>(), lsd, S));
 		l_sig_dev = lsd; ++launches;
@@ -201,7 +214,8 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 			MAP_CUDA(cudaStreamSynchronize(S));
 			if ((rc = ra_align_chains_batch_dev(ctx, ix->ev.as<float>(), nullptr, ix->anc[cur].as<ra_anchor_t>(), an, ix->dtw_chains.as<ra_chain_t>(),
 			                                    (uint32_t)n_cand_total, ix->group_first.as<uint32_t>(), n_act, 1, nullptr, ix->dscore.as<float>(),
-			                                    ix->dkeep.as<uint8_t>(), nullptr, nullptr))) return rc;
+			                                    ix->dkeep.as<uint8_t>(), count_cells ? &cells_acc[0] : nullptr, count_cells ? &cells_acc[1] : nullptr))) return rc;
+			stt.cells_issued += cells_acc[0]; stt.cells_useful += cells_acc[1];
 			stt.chains_evaluated += n_cand_total;
 		}
 		lib_launches += ra_launch_count(ctx) - l0;

@@ -107,7 +107,13 @@ struct ChainLaunch {
 	uint32_t ring_cap;
 	uint64_t *cells;                 // [issued, useful]; may be null
 	uint32_t *need_cap;              // receives the ring capacity a skipped part needed (0 = none skipped)
+	uint32_t *error;                 // set by k_validate_chains when a chain's anchors are not monotonic / out of the arenas; the
+	                                 // evaluation kernels do nothing once it is set (the entry point returns RA_EINVAL)
+	uint64_t n_read, n_ref;          // arena sizes in floats for the bounds check (0 = unknown: only monotonicity is checked)
 };
+// every anchor of every chain: anchors[0] is the chain end, positions do not increase along the array (rmap.cpp:456-465 makes
+// them strictly monotonic), the chain end stays inside the arenas.  One warp per chain.
+cudaError_t launch_validate_chains(const ChainLaunch &L, uint32_t k0, uint32_t k1, cudaStream_t s);
 constexpr int kChainCtasPerSm = 6;
 cudaError_t launch_chain_eval(const ChainLaunch &L, int n_sm, cudaStream_t s);
 // sparse border (chains_sparse.cu): flat part-cost kernel over tiles of 256 parts + replay kernel

@@ -71,11 +71,17 @@ class Index:
     def __exit__(self, *a):
         self.close()
 
-    def map_reads(self, opt: RiMapOpt, *, raw=None, raw_off=None, raw_len=None, offset=None, scale=None, sig=None, sig_off=None, sig_len=None):
+    def map_reads(self, opt: RiMapOpt, *, raw=None, raw_off=None, raw_len=None, offset=None, scale=None, sig=None, sig_off=None, sig_len=None,
+                  resident_reads: int = 0, count_cells: bool = False):
         """One batch through ra_map_batch.  Either int16 DAC samples (raw, raw_off, raw_len, offset, scale) or float pA
-        (sig, sig_off, sig_len).  Returns (records: PAF_DTYPE[n_reads], stats: dict)."""
-        st = MapStats()
-        if raw is not None:
+        (sig, sig_off, sig_len), or resident_reads = n to map again the batch the previous call left on the device.
+        Returns (records: PAF_DTYPE[n_reads], stats: dict)."""
+        st = MapStats(); st.reserved = 1 if count_cells else 0
+        if resident_reads:
+            out = np.zeros(resident_reads, PAF_DTYPE)
+            check(self._L.ra_map_batch(self.ctx._h, self._h, C.byref(opt), None, None, None, None, None, None, None, None,
+                                       resident_reads, out.ctypes.data, C.byref(st)))
+        elif raw is not None:
             raw = np.ascontiguousarray(raw, np.int16); ro = np.ascontiguousarray(raw_off, np.uint64); rl = np.ascontiguousarray(raw_len, np.uint32)
             of = np.ascontiguousarray(offset, np.float32); sc = np.ascontiguousarray(scale, np.float32)
             n = len(rl); out = np.zeros(n, PAF_DTYPE)

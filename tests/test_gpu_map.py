@@ -43,11 +43,14 @@ def test_map_batch_paf_vs_reference_golden(mg, flat, ci):
     with ra.Context(0) as ctx, ra.Index.load_flat(ctx, flat[preset]) as ix:
         rec, st = ix.map_reads(_opt(kw), raw=mg["raw"], raw_off=mg["raw_off"], raw_len=mg["raw_len"], offset=off, scale=sc)
         got = ix.paf_lines(rec)
+        rec2, st2 = ix.map_reads(_opt(kw), resident_reads=len(mg["raw_len"]), count_cells=True)      # device-resident re-run
     want = str(mg["paf"][ci]).split("\n")
     assert len(got) == len(want)
     for r, (a, b) in enumerate(zip(got, want)):
         assert a == b, (r, a, b)
-    assert st["rounds"] == 30 and st["launches"] > 0
+    assert 1 <= st["rounds"] <= 30 and st["launches"] > 0
+    assert rec2.tobytes() == rec.tobytes() and st2["chunks"] == st["chunks"]
+    assert (st2["cells_useful"] > 0) == bool(kw.get("flag", 0) & 2)
 
 
 def test_index_file_loader_and_float_input(mg, flat, tmp_path):

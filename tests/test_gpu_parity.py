@@ -457,3 +457,56 @@ def test_events_sliced_copies_large_batch(ctx, oracle):
     ev2, off2, lsig, first = ctx.detect_events_raw_batch(rd.raw, rd.read_off[:-1], rd.read_len, rd.dac_offset, rd.dac_scale, 4000, 8)
     assert np.array_equal(lsig, rd.read_len) and int(first[-1]) == len(coff)
     assert np.array_equal(off2, off_o) and np.array_equal(bits(ev2), bits(ev_o))
+
+
+# ---- sliced chain upload and anchor validation ------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("slice_anchors", [200, 1500, 1 << 30])
+def test_align_chains_sliced_upload_vs_oracle(oracle, slice_anchors):
+    """The sliced upload path of ra_align_chains_batch (h2d stream, per-slice group cuts and pipelines) with 8 slices, a few
+    slices (some empty) and the one-shot path give the oracle's scores bit for bit."""
+    import rawalign_b200 as ra
+    from oracle import DtwOpt
+    read, ref, anchors, chains = _workload(n_reads=30, seed=91)
+    oo = DtwOpt(1, 1, 0.10, 0.4, 20.0)
+    want = np.zeros(len(chains), np.float32)
+    best, grp = 0.0, None
+    for k, ch in enumerate(chains):
+        if grp != ch["group"]:
+            best, grp = 0.0, ch["group"]
+        a = anchors[int(ch["anchor_off"]):int(ch["anchor_off"]) + int(ch["n_anchors"])]
+        s = oracle.align_chain(a, read[int(ch["read_off"]):], ref, oo, min_score=best, score_fma=1)
+        want[k] = s
+        if s >= np.float32(20.0) and s > best:
+            best = float(s)
+    with ra.Context(0) as c:
+        c.set_tuning("chain_slice_min_anchors", slice_anchors)
+        score, keep, issued, useful = c.align_chains_batch(read, ref, anchors, chains, min_score_mode=1)
+        assert np.array_equal(bits(score), bits(want))
+        assert np.array_equal(keep.astype(bool), want >= np.float32(20.0))
+        # a second call on the same context (counters and staging reused)
+        score2, _, _, _ = c.align_chains_batch(read, ref, anchors, chains, min_score_mode=1, count_cells=False)
+        assert np.array_equal(bits(score2), bits(want))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("slice_anchors", [300, 1 << 30])
+def test_align_chains_rejects_malformed_anchors(slice_anchors):
+    """A non-monotonic interior anchor or a chain end outside the arenas is RA_EINVAL, not an out-of-bounds access."""
+    import rawalign_b200 as ra
+    read, ref, anchors, chains = _workload(n_reads=12, seed=92)
+    with ra.Context(0) as c:
+        c.set_tuning("chain_slice_min_anchors", slice_anchors)
+        bad = anchors.copy()
+        ch = chains[len(chains) // 2]
+        bad["query_position"][int(ch["anchor_off"]) + int(ch["n_anchors"]) // 2] += 100000       # interior anchor jumps ahead of its neighbours
+        with pytest.raises(ra.RawAlignError) as e:
+            c.align_chains_batch(read, ref, bad, chains, min_score_mode=1)
+        assert e.value.code == -3
+        bad = anchors.copy()
+        bad["target_position"][int(ch["anchor_off"]) + 1] = 0xFFFFFFF0
+        with pytest.raises(ra.RawAlignError) as e:
+            c.align_chains_batch(read, ref, bad, chains, min_score_mode=1)
+        assert e.value.code == -3
+        score, _, _, _ = c.align_chains_batch(read, ref, anchors, chains, min_score_mode=1)       # the context still works
+        assert np.isfinite(score).all()
