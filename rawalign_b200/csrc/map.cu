@@ -91,6 +91,7 @@ struct ra_index {
 	Buf lsig_keep;
 	std::vector<uint64_t> last_off; std::vector<uint32_t> last_len; bool last_raw = false;   // the batch left on the device by the last ra_map_batch
 	void *pin = nullptr; size_t pin_cap = 0;
+	bool sort_attr = false;                                        // the sort kernel's > 48 KB shared memory opt-in (one index = one device)
 	cudaStream_t stream = nullptr;
 	cudaEvent_t ev_t[16] = {};
 };

@@ -191,7 +191,8 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 		                                    ix->seeds_p.as<uint32_t>(), ix->seed_cnt.as<uint32_t>(), ix->seed_off.as<uint64_t>(), ix->vals.as<uint64_t>(),
 		                                    ix->n_seed.as<uint32_t>(), ix->seg_n.as<uint32_t>(), seg_pad, ix->seg_base.as<uint64_t>(), skip, ix->keys.as<uint64_t>());
 		k_advance_offset<<<(n_act + 127) / 128, 128, 0, S>>>(st, ix->act.as<uint32_t>(), n_act, ix->evoff_round.as<uint64_t>(), skip);
-		k_sort_segments<<<n_act, 256, 0, S>>>(ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), seg_pad, skip, n_act);
+		if (!ix->sort_attr) { MAP_CUDA(cudaFuncSetAttribute(k_sort_segments, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kSortSmem * 8))); ix->sort_attr = true; }
+		k_sort_segments<<<n_act, kSortThreads, kSortSmem * 8, S>>>(ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), seg_pad, skip, n_act);
 		launches += 3;
 		MAP_CUDA(cudaStreamSynchronize(S));
 		stt.sort_ms += clk.lap();

@@ -33,10 +33,19 @@ __device__ __forceinline__ bool traceback(const uint64_t *__restrict__ keys, con
 }
 
 // Chaining DP of gen_chains (rmap.cpp:427-507) for every (ref, strand) list of one read, in the reference's list order,
-// with the running max_chaining_score shared by the lists (:428).  One warp per read; the recurrences (the predecessor scan
-// with its skip counter, the running maximum, the used flags of the tracebacks) are sequential, so lane 0 walks them.
-// Candidate chains go to cand[i * cap + k] in generation order, or sorted by chaining score (stable, :512) when they are to
-// be evaluated by DTW.
+// with the running max_chaining_score shared by the lists (:428).  One warp per read.  The anchors of a list are walked in
+// order (score[ai] needs the scores before it), but the predecessor scan of one anchor (:452-484) is done 32 predecessors at
+// a time: lane l looks at anchor ai-1-l (one coalesced load), and the loop's sequential semantics are rebuilt from warp
+// prefix operations --
+//   * the target-gap break (:458) is monotonic along the lanes (the list is sorted by target): the first lane that hits it,
+//     or that leaves the chaining band / the list, ends the scan;
+//   * score[ai] only ever grows, so a predecessor improves it iff its candidate score beats the seed value and every
+//     candidate before it: an exclusive prefix maximum;
+//   * the skip counter (:479-482) is a prefix sum of -1 (improved) / +1 (did not) over the lanes that reach the comparison;
+//     the first non-improving lane that takes it past max_num_skips is the last one the reference looks at.
+// All lanes carry the same running state (score, predecessor, skip count, best-candidate list), lane 0 writes and does the
+// tracebacks.  Candidate chains go to cand[i * cap + k] in generation order, or sorted by chaining score (stable, :512) when
+// they are to be evaluated by DTW.
 __global__ void __launch_bounds__(128)
 k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_base,
         const uint32_t *__restrict__ seg_n, const uint32_t *__restrict__ skip, float *__restrict__ score, uint32_t *__restrict__ pred,
@@ -49,15 +58,14 @@ k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64
 	const uint64_t base = seg_base[i];
 	const uint32_t n = seg_n[i];
 	const uint64_t *__restrict__ K = keys + base;
-	float *__restrict__ S = score + base;
+	float *S = score + base;
 	uint32_t *__restrict__ Pd = pred + base;
 	uint8_t *__restrict__ U = used + base;
 	for (uint32_t k = lane; k < n; k += 32) U[k] = 0;
 	__syncwarp();
-	if (lane != 0) return;
 	ChainRec *out = cand + (size_t)i * P.cap_chains;
-	uint32_t nc = 0;
-	uint64_t wo = base;                                            // next free chain-anchor slot of this read
+	uint32_t nc = 0;                                               // lane 0 only
+	uint64_t wo = base;                                            // next free chain-anchor slot of this read (lane 0 only)
 	float max_chaining_score = 0.0f;                               // :428
 	const float fe = (float)P.e;
 	uint32_t ls = 0;
@@ -73,23 +81,46 @@ k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64
 			uint32_t start = ls;
 			if (ai - ls > (uint32_t)P.chaining_band_length) start = ai - (uint32_t)P.chaining_band_length;   // :448
 			int32_t num_skips = 0;
-			for (uint32_t pi = ai; pi-- > start;) {                // :452
+			bool done = false;
+			for (uint32_t top = ai; top > start && !done; top = top >= 32 ? top - 32 : 0) {
+				const bool inrange = top >= start + 1u + (uint32_t)lane;          // predecessor top-1-lane is still >= start
+				const uint32_t pi = inrange ? top - 1u - (uint32_t)lane : start;
 				const uint64_t kp = K[pi];
 				const int32_t pt = (int32_t)key_target(kp), pq = (int32_t)key_query(kp);
-				if (pq == cq) continue;
-				if (pt == ct) continue;
-				if (pt + P.max_target_gap_length < ct) break;      // :458
+				const bool brk_t = inrange && (pt + P.max_target_gap_length < ct);              // :458
+				const uint32_t dead_mask = __ballot_sync(0xffffffffu, brk_t || !inrange);
+				const int first_dead = dead_mask ? __ffs(dead_mask) - 1 : 32;
 				const int32_t td = ct - pt, qd = cq - pq;
-				if (qd < 0) continue;                              // :465
+				const bool valid = lane < first_dead && pq != cq && pt != ct && qd >= 0;     // :455-457, :465
 				float cur = 0.0f;
-				const int32_t md = min(min(td, qd), P.e);
-				const int32_t gap = abs(td - qd);
-				const float gap_scale = td > 0 ? __fdiv_rn((float)qd, (float)td) : 1.0f;   // :469
-				if (gap < P.max_gap_length && gap_scale < 5.0f && gap_scale > 0.75f) cur = __fadd_rn(S[pi], (float)md);   // :472-474
-				if (cur > sc) { sc = cur; pr = pi; --num_skips; }
-				else { ++num_skips; if (num_skips > P.max_num_skips) break; }
+				if (valid) {
+					const int32_t md = min(min(td, qd), P.e);
+					const int32_t gap = abs(td - qd);
+					const float gap_scale = td > 0 ? __fdiv_rn((float)qd, (float)td) : 1.0f;   // :469
+					if (gap < P.max_gap_length && gap_scale < 5.0f && gap_scale > 0.75f) cur = __fadd_rn(__ldcg(S + pi), (float)md);   // :472-474
+				}
+				float pm = cur;                                    // inclusive prefix maximum (0 for the lanes that do not count)
+#pragma unroll
+				for (int d = 1; d < 32; d <<= 1) { const float y = __shfl_up_sync(0xffffffffu, pm, d); if (lane >= d) pm = fmaxf(pm, y); }
+				float before = __shfl_up_sync(0xffffffffu, pm, 1);
+				before = fmaxf(lane ? before : 0.0f, sc);
+				const bool improve = valid && cur > before;        // :476
+				int32_t ps = valid ? (improve ? -1 : 1) : 0;       // :479-481
+#pragma unroll
+				for (int d = 1; d < 32; d <<= 1) { const int32_t y = __shfl_up_sync(0xffffffffu, ps, d); if (lane >= d) ps += y; }
+				ps += num_skips;
+				const uint32_t brk_mask = __ballot_sync(0xffffffffu, valid && !improve && ps > P.max_num_skips);   // :482
+				const int last = brk_mask ? __ffs(brk_mask) - 1 : 31;
+				const uint32_t imp_mask = __ballot_sync(0xffffffffu, improve && lane <= last);
+				if (imp_mask) {
+					const int t = 31 - __clz(imp_mask);            // improvements grow along the lanes: the last one holds the maximum
+					sc = __shfl_sync(0xffffffffu, cur, t); pr = __shfl_sync(0xffffffffu, pi, t);
+				}
+				num_skips = __shfl_sync(0xffffffffu, ps, last);
+				done = brk_mask != 0 || first_dead < 32;
 			}
-			S[ai] = sc; Pd[ai] = pr;
+			if (lane == 0) { S[ai] = sc; Pd[ai] = pr; }
+			__syncwarp();
 			if (sc > max_chaining_score) max_chaining_score = sc;  // :485-487
 			if (P.no_filter || (sc >= P.min_chaining_score && sc > max_chaining_score / 2)) {   // :488-492
 				// keep the num_best_chains best by (score desc, index desc) (compare(), :175-179): ai only grows, so a tie goes in front
@@ -103,17 +134,20 @@ k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64
 				}
 			}
 		}
-		for (int k = 0; k < ncand; ++k) {                          // :498-505
-			ChainRec rec;
-			if (nc < P.cap_chains && traceback(K, S, Pd, U, ci[k], P.min_num_anchors, anc_cur + wo, &rec)) {
-				rec.ref = list >> 1; rec.strand = list & 1u; rec.anchor_off = wo;
-				wo += rec.n_anchors;
-				out[nc++] = rec;
+		if (lane == 0)
+			for (int k = 0; k < ncand; ++k) {                      // :498-505
+				ChainRec rec;
+				if (nc < P.cap_chains && traceback(K, S, Pd, U, ci[k], P.min_num_anchors, anc_cur + wo, &rec)) {
+					rec.ref = list >> 1; rec.strand = list & 1u; rec.anchor_off = wo;
+					wo += rec.n_anchors;
+					out[nc++] = rec;
+				}
+				if (!P.no_filter && S[ci[k]] < max_chaining_score / 2) break;
 			}
-			if (!P.no_filter && S[ci[k]] < max_chaining_score / 2) break;
-		}
+		__syncwarp();
 		ls = ai;
 	}
+	if (lane != 0) return;
 	if (P.dtw)                                                     // :512, insertion sort = libstdc++'s std::sort for <= 16 elements
 		for (uint32_t a = 1; a < nc; ++a) {
 			const ChainRec x = out[a];

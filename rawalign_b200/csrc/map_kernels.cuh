@@ -248,46 +248,38 @@ k_fill_anchors(ReadState *__restrict__ st, const uint32_t *__restrict__ act, uin
 // ---------------------------------------------------------------------------------------------------------------
 // anchor sort (rmap.cpp:396-401): one CTA per read, bitonic network over the padded segment
 // ---------------------------------------------------------------------------------------------------------------
-constexpr uint32_t kSortSmem = 4096;                               // keys staged in shared memory
-__global__ void __launch_bounds__(256)
+constexpr uint32_t kSortSmem = 16384;                              // keys staged in shared memory (128 KB, opt-in)
+constexpr int kSortThreads = 512;
+__global__ void __launch_bounds__(kSortThreads)
 k_sort_segments(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_base, const uint32_t *__restrict__ seg_pad,
                 const uint32_t *__restrict__ skip, uint32_t n_act)
 {
-	__shared__ uint64_t sk[kSortSmem];
+	extern __shared__ uint64_t sk[];
 	const uint32_t i = blockIdx.x;
 	if (i >= n_act || skip[i]) return;
 	const uint32_t n = seg_pad[i];
 	if (n < 2) return;
 	uint64_t *g = keys + seg_base[i];
 	const int tid = threadIdx.x;
-	if (n <= kSortSmem) {
-		for (uint32_t k = tid; k < n; k += 256) sk[k] = g[k];
+	const bool in_smem = n <= kSortSmem;
+	uint64_t *w = in_smem ? sk : g;                                // longer segments are sorted in place in global memory
+	if (in_smem) {
+		for (uint32_t k = tid; k < n; k += kSortThreads) sk[k] = g[k];
 		__syncthreads();
-		for (uint32_t size = 2; size <= n; size <<= 1)
-			for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
-				for (uint32_t t = tid; t < (n >> 1); t += 256) {
-					const uint32_t lo = 2 * t - (t & (stride - 1));
-					const uint32_t hi = lo + stride;
-					const bool up = (lo & size) == 0;
-					const uint64_t x = sk[lo], y = sk[hi];
-					if ((x > y) == up) { sk[lo] = y; sk[hi] = x; }
-				}
-				__syncthreads();
-			}
-		for (uint32_t k = tid; k < n; k += 256) g[k] = sk[k];
-		return;
 	}
 	for (uint32_t size = 2; size <= n; size <<= 1)
 		for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
-			for (uint32_t t = tid; t < (n >> 1); t += 256) {
+			for (uint32_t t = tid; t < (n >> 1); t += kSortThreads) {
 				const uint32_t lo = 2 * t - (t & (stride - 1));
 				const uint32_t hi = lo + stride;
 				const bool up = (lo & size) == 0;
-				const uint64_t x = g[lo], y = g[hi];
-				if ((x > y) == up) { g[lo] = y; g[hi] = x; }
+				const uint64_t x = w[lo], y = w[hi];
+				if ((x > y) == up) { w[lo] = y; w[hi] = x; }
 			}
 			__syncthreads();
 		}
+	if (in_smem)
+		for (uint32_t k = tid; k < n; k += kSortThreads) g[k] = sk[k];
 }
 
 } // namespace mapk
