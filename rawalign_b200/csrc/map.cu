@@ -88,7 +88,7 @@ struct ra_index {
 	Buf raw16, rd_off, rd_len, rd_offset, rd_scale, sig, state, chains, chains_tmp, paf;
 	Buf act, coff, clen, ev_round, evoff_round, ev, seeds_h, seeds_p, seed_cnt, seed_off, n_seed, n_hits, seg_n, seg_base, counters;
 	Buf keys, score, pred, used, anc[2], cand, n_cand, cand_base, dtw_chains, group_first, dscore, dkeep, scan_tmp;
-	Buf lsig_keep;
+	Buf lsig_keep, nt, n_nt;
 	std::vector<uint64_t> last_off; std::vector<uint32_t> last_len; bool last_raw = false;   // the batch left on the device by the last ra_map_batch
 	void *pin = nullptr; size_t pin_cap = 0;
 	bool sort_attr = false;                                        // the sort kernel's > 48 KB shared memory opt-in (one index = one device)
@@ -238,7 +238,7 @@ void ra_index_destroy(ra_index *ix)
 	               &ix->chains_tmp, &ix->paf, &ix->act, &ix->coff, &ix->clen, &ix->ev_round, &ix->evoff_round, &ix->ev, &ix->seeds_h, &ix->seeds_p,
 	               &ix->seed_cnt, &ix->seed_off, &ix->n_seed, &ix->n_hits, &ix->seg_n, &ix->seg_base, &ix->counters, &ix->keys, &ix->score, &ix->pred,
 	               &ix->used, &ix->anc[0], &ix->anc[1], &ix->cand, &ix->n_cand, &ix->cand_base, &ix->dtw_chains, &ix->group_first, &ix->dscore,
-	               &ix->dkeep, &ix->scan_tmp, &ix->lsig_keep };
+	               &ix->dkeep, &ix->scan_tmp, &ix->lsig_keep, &ix->nt, &ix->n_nt };
 	for (Buf *b : all) b->release();
 	if (ix->pin) cudaFreeHost(ix->pin);
 	if (ix->stream) cudaStreamDestroy(ix->stream);

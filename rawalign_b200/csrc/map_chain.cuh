@@ -32,11 +32,67 @@ __device__ __forceinline__ bool traceback(const uint64_t *__restrict__ keys, con
 	return true;
 }
 
+__device__ __forceinline__ bool linkable(int32_t ct, int32_t cq, int32_t pt, int32_t pq, const Params &P)   // rmap.cpp:455-474
+{
+	const int32_t td = ct - pt, qd = cq - pq;
+	if (pq == cq || pt == ct || qd < 0) return false;
+	const float gap_scale = td > 0 ? __fdiv_rn((float)qd, (float)td) : 1.0f;
+	return abs(td - qd) < P.max_gap_length && gap_scale < 5.0f && gap_scale > 0.75f;
+}
+
+// Pre-pass of the chaining DP, one lane per anchor.  Most anchors are isolated seed hits: no predecessor the reference's scan
+// would look at (:452-484: up to the target-gap break, the chaining band, or max_num_skips + 1 comparisons that cannot
+// improve) satisfies the gap conditions of :472, so their score stays the seed value e and they are their own predecessor --
+// decided here, in parallel, without the recurrence.  The anchors that do have a linkable predecessor in reach are listed in
+// order (nt) for the sequential pass.  Every anchor gets score = e, pred = self, used = 0.
+__global__ void __launch_bounds__(128)
+k_chain_pre(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_base,
+            const uint32_t *__restrict__ seg_n, const uint32_t *__restrict__ skip, float *__restrict__ score, uint32_t *__restrict__ pred,
+            uint8_t *__restrict__ used, uint32_t *__restrict__ nt, uint32_t *__restrict__ n_nt)
+{
+	const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const int lane = threadIdx.x & 31;
+	if (i >= n_act) return;
+	if (skip[i]) { if (lane == 0) n_nt[i] = 0; return; }
+	const uint64_t base = seg_base[i];
+	const uint32_t n = seg_n[i];
+	const uint64_t *__restrict__ K = keys + base;
+	const float fe = (float)P.e;
+	const bool all = P.no_filter || fe >= P.min_chaining_score;    // an isolated anchor could itself be a chain end: no shortcut
+	uint32_t cnt = 0;
+	for (uint32_t a0 = 0; a0 < n; a0 += 32) {
+		const uint32_t a = a0 + lane;
+		bool hit = false;
+		if (a < n) {
+			const uint64_t kc = K[a];
+			const uint32_t list = key_list(kc);
+			const int32_t ct = (int32_t)key_target(kc), cq = (int32_t)key_query(kc);
+			score[base + a] = fe; pred[base + a] = a; used[base + a] = 0;
+			hit = all;
+			int32_t looked = 0;
+			for (uint32_t pi = a; !hit && pi-- > 0;) {
+				const uint64_t kp = K[pi];
+				if (key_list(kp) != list || a - pi > (uint32_t)P.chaining_band_length) break;
+				const int32_t pt = (int32_t)key_target(kp), pq = (int32_t)key_query(kp);
+				if (pq == cq || pt == ct) continue;
+				if (pt + P.max_target_gap_length < ct) break;
+				if (cq - pq < 0) continue;
+				if (linkable(ct, cq, pt, pq, P)) hit = true;
+				else if (++looked > P.max_num_skips) break;            // the reference's scan has given up by now (:482)
+			}
+		}
+		const uint32_t m = __ballot_sync(0xffffffffu, hit);
+		if (hit) nt[base + cnt + __popc(m & ((1u << lane) - 1u))] = a;
+		cnt += __popc(m);
+	}
+	if (lane == 0) n_nt[i] = cnt;
+}
+
 // Chaining DP of gen_chains (rmap.cpp:427-507) for every (ref, strand) list of one read, in the reference's list order,
-// with the running max_chaining_score shared by the lists (:428).  One warp per read.  The anchors of a list are walked in
-// order (score[ai] needs the scores before it), but the predecessor scan of one anchor (:452-484) is done 32 predecessors at
-// a time: lane l looks at anchor ai-1-l (one coalesced load), and the loop's sequential semantics are rebuilt from warp
-// prefix operations --
+// with the running max_chaining_score shared by the lists (:428).  One warp per read, over the anchors k_chain_pre listed.
+// The anchors of a list are walked in order (score[ai] needs the scores before it), but the predecessor scan of one anchor
+// (:452-484) is done 32 predecessors at a time: lane l looks at anchor ai-1-l (one coalesced load), and the loop's sequential
+// semantics are rebuilt from warp prefix operations --
 //   * the target-gap break (:458) is monotonic along the lanes (the list is sorted by target): the first lane that hits it,
 //     or that leaves the chaining band / the list, ends the scan;
 //   * score[ai] only ever grows, so a predecessor improves it iff its candidate score beats the seed value and every
@@ -44,12 +100,14 @@ __device__ __forceinline__ bool traceback(const uint64_t *__restrict__ keys, con
 //   * the skip counter (:479-482) is a prefix sum of -1 (improved) / +1 (did not) over the lanes that reach the comparison;
 //     the first non-improving lane that takes it past max_num_skips is the last one the reference looks at.
 // All lanes carry the same running state (score, predecessor, skip count, best-candidate list), lane 0 writes and does the
-// tracebacks.  Candidate chains go to cand[i * cap + k] in generation order, or sorted by chaining score (stable, :512) when
-// they are to be evaluated by DTW.
+// tracebacks.  The running maximum only needs the listed anchors: every score is >= e, and the filter of :488-492 is applied
+// after the anchor's own score has entered the maximum.  Candidate chains go to cand[i * cap + k] in generation order, or
+// sorted by chaining score (stable, :512) when they are to be evaluated by DTW.
 __global__ void __launch_bounds__(128)
 k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_base,
         const uint32_t *__restrict__ seg_n, const uint32_t *__restrict__ skip, float *__restrict__ score, uint32_t *__restrict__ pred,
-        uint8_t *__restrict__ used, ra_anchor_t *__restrict__ anc_cur, ChainRec *__restrict__ cand, uint32_t *__restrict__ n_cand)
+        uint8_t *__restrict__ used, const uint32_t *__restrict__ nt, const uint32_t *__restrict__ n_nt, ra_anchor_t *__restrict__ anc_cur,
+        ChainRec *__restrict__ cand, uint32_t *__restrict__ n_cand)
 {
 	const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
 	const int lane = threadIdx.x & 31;
@@ -61,19 +119,26 @@ k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64
 	float *S = score + base;
 	uint32_t *__restrict__ Pd = pred + base;
 	uint8_t *__restrict__ U = used + base;
-	for (uint32_t k = lane; k < n; k += 32) U[k] = 0;
-	__syncwarp();
+	const uint32_t *__restrict__ NT = nt + base;
+	const uint32_t m_nt = n_nt[i];
 	ChainRec *out = cand + (size_t)i * P.cap_chains;
 	uint32_t nc = 0;                                               // lane 0 only
 	uint64_t wo = base;                                            // next free chain-anchor slot of this read (lane 0 only)
 	float max_chaining_score = 0.0f;                               // :428
 	const float fe = (float)P.e;
-	uint32_t ls = 0;
-	while (ls < n) {
-		const uint32_t list = key_list(K[ls]);
+	uint32_t j = 0;
+	while (j < m_nt) {
+		const uint32_t first = NT[j];
+		const uint32_t list = key_list(K[first]);
+		uint32_t ls;                                               // first anchor of this (ref, strand) list: lower bound of the list id
+		{
+			uint32_t lo = 0, hi = first;
+			while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (key_list(K[mid]) < list) lo = mid + 1; else hi = mid; }
+			ls = lo;
+		}
 		float cs[kMaxBest]; uint32_t ci[kMaxBest]; int ncand = 0;
-		uint32_t ai = ls;
-		for (; ai < n; ++ai) {
+		for (; j < m_nt; ++j) {
+			const uint32_t ai = NT[j];
 			const uint64_t kc = K[ai];
 			if (key_list(kc) != list) break;
 			float sc = fe; uint32_t pr = ai;                       // :442-443
@@ -93,11 +158,15 @@ k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64
 				const int32_t td = ct - pt, qd = cq - pq;
 				const bool valid = lane < first_dead && pq != cq && pt != ct && qd >= 0;     // :455-457, :465
 				float cur = 0.0f;
-				if (valid) {
-					const int32_t md = min(min(td, qd), P.e);
-					const int32_t gap = abs(td - qd);
-					const float gap_scale = td > 0 ? __fdiv_rn((float)qd, (float)td) : 1.0f;   // :469
-					if (gap < P.max_gap_length && gap_scale < 5.0f && gap_scale > 0.75f) cur = __fadd_rn(__ldcg(S + pi), (float)md);   // :472-474
+				if (valid && linkable(ct, cq, pt, pq, P)) cur = __fadd_rn(__ldcg(S + pi), (float)min(min(td, qd), P.e));   // :467-474
+				const uint32_t valid_mask = __ballot_sync(0xffffffffu, valid);
+				if (__ballot_sync(0xffffffffu, cur > sc) == 0) {
+					// nothing here beats the score so far: every lane that counts is a skip (:479-482)
+					const int room = P.max_num_skips + 1 - num_skips;             // the room-th skip from here ends the scan
+					const int have = __popc(valid_mask);
+					if (have >= room) done = true; else num_skips += have;
+					if (first_dead < 32) done = true;
+					continue;
 				}
 				float pm = cur;                                    // inclusive prefix maximum (0 for the lanes that do not count)
 #pragma unroll
@@ -145,8 +214,8 @@ k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64
 				if (!P.no_filter && S[ci[k]] < max_chaining_score / 2) break;
 			}
 		__syncwarp();
-		ls = ai;
 	}
+	(void)n;
 	if (lane != 0) return;
 	if (P.dtw)                                                     // :512, insertion sort = libstdc++'s std::sort for <= 16 elements
 		for (uint32_t a = 1; a < nc; ++a) {
