@@ -600,13 +600,19 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
     raw, off, ln, dac_off, dac_scale = ds.reads(n_reads, seed=2 + rank)
     log(f"[rank {rank}] {n_reads} reads simulated in {time.time() - t0:.1f}s: {len(raw) * 2 / 1e6:.0f} MB of int16 signal")
     raw_p = torch.from_numpy(raw).pin_memory().numpy()            # the e2e path copies from pinned host memory every step
-    ctx = ra.Context(local)
-    t0 = time.time()
-    ix = ra.Index.load_file(ctx, ds.index_path)
-    t_index = time.time() - t0
+    # MAP_DEPTH batches in flight per GPU (one context + index each, one host thread each), as a map loop with double-buffered
+    # mini-batches runs: one batch's uploads and host round trips overlap the other's kernels.  Every step does all of its work.
+    depth = max(1, int(os.environ.get("RA_BENCH_MAP_DEPTH", 2)))
     opt = ra.ri_mapopt_full(**cfg["opt"])
     if opt.flag & 0x4:
         raise SystemExit("C3 (--dtw-output-cigar) is not wired into ra_map_batch yet; the traceback kernels are measured by tools/microbench_dtw.py")
+    pipes = []
+    t0 = time.time()
+    for w in range(depth):
+        c = ra.Context(local)
+        pipes.append((c, ra.Index.load_file(c, ds.index_path)))
+    t_index = (time.time() - t0) / depth
+    ctx, ix = pipes[0]
 
     def barrier():
         torch.cuda.synchronize()
@@ -614,35 +620,54 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
             dist.barrier()
             torch.cuda.synchronize()
 
-    def step_e2e():
-        return ix.map_reads(opt, raw=raw_p, raw_off=off, raw_len=ln, offset=dac_off, scale=dac_scale)
+    def step_e2e(w=0):
+        return pipes[w][1].map_reads(opt, raw=raw_p, raw_off=off, raw_len=ln, offset=dac_off, scale=dac_scale)
 
-    def step_res(count=False):
-        return ix.map_reads(opt, resident_reads=n_reads, count_cells=count)
+    def step_res(w=0, count=False):
+        return pipes[w][1].map_reads(opt, resident_reads=n_reads, count_cells=count)
 
-    rec0, st0 = step_e2e()
-    recc, stc = step_res(True)                                    # one counted pass (cell counting is instrumentation)
-    for _ in range(max(args.warmup - 2, 1)):
-        step_res()
+    last = {}
+
+    def run_steps(fn, n_steps):
+        errs = []
+
+        def worker(w):
+            try:
+                for _ in range(w, n_steps, depth):
+                    last[w] = fn(w)
+            except Exception as e:      # noqa: BLE001
+                errs.append(e)
+        ths = [threading.Thread(target=worker, args=(w,)) for w in range(depth)]
+        for t in ths:
+            t.start()
+        for t in ths:
+            t.join()
+        if errs:
+            raise errs[0]
+
+    for w in range(depth):
+        rec0, st0 = step_e2e(w)                                   # every pipeline holds the batch; also the first parity sample
+    recc, stc = step_res(0, True)                                 # one counted pass (cell counting is instrumentation)
+    run_steps(step_res, max(args.warmup, depth))
+    barrier()
+    # per-stage times of one un-pipelined step
+    rec, st_alone = step_res(0)
     barrier()
     sampler = ClockSampler(local); sampler.start()
-    l0 = ctx.launch_count
-    stage_acc = {}
+    l0 = sum(p[0].launch_count for p in pipes)
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        rec, st = step_res()
-        for k, v in st.items():
-            if k.endswith("_ms"):
-                stage_acc[k] = stage_acc.get(k, 0.0) + v
+    run_steps(step_res, args.steps)
     barrier()
     dt = time.perf_counter() - t0
-    launches = ctx.launch_count - l0
-    step_e2e(); barrier()
+    launches = sum(p[0].launch_count for p in pipes) - l0
+    rec = last[0][0]
+    run_steps(step_e2e, depth); barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        rec_e, st_e = step_e2e()
+    run_steps(step_e2e, args.steps)
     barrier()
     dt_e2e = time.perf_counter() - t0
+    rec_e = last[(args.steps - 1) % depth][0] if (args.steps - 1) % depth in last else last[0][0]
+    stage_acc = {k: v * args.steps for k, v in st_alone.items() if k.endswith("_ms")}
     clocks = sampler.stop()
     tt = torch.tensor([dt, dt_e2e], dtype=torch.float64, device=dev)
     if world > 1:
@@ -665,7 +690,8 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
                "reads_mapped_frac": mapped_all / reads_all,
                "dtw_cells_per_step": {"useful": cells_all, "issued": issued_all},
                "hot_path_gcups": cells_all * args.steps / dt / 1e9,
-               "map_stages_ms": {k: v / args.steps for k, v in sorted(stage_acc.items())},
+               "map_stages_ms": dict({k: v / args.steps for k, v in sorted(stage_acc.items())}, note="one step run alone (host-observed, between synchronisations); the timed steps overlap two batches"),
+               "batches_in_flight_per_gpu": depth,
                "map_counts_per_step": {k: stc[k] for k in ("rounds", "chunks", "events", "seeds", "anchors", "chains_evaluated", "launches")},
                "e2e": {"value": reads_all * args.steps / dt_e2e, "unit": "reads/s", "ms_per_step": dt_e2e / args.steps * 1e3,
                        "h2d_bytes_per_step": int(raw.nbytes + off.nbytes + ln.nbytes + dac_off.nbytes + dac_scale.nbytes), "d2h_bytes_per_step": int(rec0.nbytes),
@@ -674,7 +700,8 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
                "gpu_launches": int(launches), "clocks": clocks, "paf_digest": digest(lines)}
         if not args.no_cpu_baseline:
             out["cpu_baseline"] = reference_map_sample(ds, cfg, raw, off, ln, lines, max(args.cpu_sample_reads, 256), n_reads)
-    ix.close(); ctx.close()
+    for c, x in pipes:
+        x.close(); c.close()
     return out
 
 

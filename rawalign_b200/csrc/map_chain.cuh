@@ -62,24 +62,30 @@ k_chain_pre(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const ui
 	uint32_t cnt = 0;
 	for (uint32_t a0 = 0; a0 < n; a0 += 32) {
 		const uint32_t a = a0 + lane;
-		bool hit = false;
-		if (a < n) {
-			const uint64_t kc = K[a];
-			const uint32_t list = key_list(kc);
-			const int32_t ct = (int32_t)key_target(kc), cq = (int32_t)key_query(kc);
-			score[base + a] = fe; pred[base + a] = a; used[base + a] = 0;
-			hit = all;
-			int32_t looked = 0;
-			for (uint32_t pi = a; !hit && pi-- > 0;) {
-				const uint64_t kp = K[pi];
-				if (key_list(kp) != list || a - pi > (uint32_t)P.chaining_band_length) break;
-				const int32_t pt = (int32_t)key_target(kp), pq = (int32_t)key_query(kp);
-				if (pq == cq || pt == ct) continue;
-				if (pt + P.max_target_gap_length < ct) break;
-				if (cq - pq < 0) continue;
-				if (linkable(ct, cq, pt, pq, P)) hit = true;
-				else if (++looked > P.max_num_skips) break;            // the reference's scan has given up by now (:482)
-			}
+		const bool mine = a < n;
+		const uint64_t kc = mine ? K[a] : 0ull;
+		const uint32_t list = key_list(kc);
+		const int32_t ct = (int32_t)key_target(kc), cq = (int32_t)key_query(kc);
+		if (mine) { score[base + a] = fe; pred[base + a] = a; used[base + a] = 0; }
+		bool hit = mine && all;
+		bool active = mine && !all && a > 0;
+		uint32_t pi = a;
+		int32_t looked = 0;
+		// the lanes walk their predecessors in lock-step (a warp-uniform loop with predicated bodies: per-lane break / continue
+		// would leave the lanes diverged, 32 times the latency)
+		while (__any_sync(0xffffffffu, active)) {
+			const uint32_t pj = active ? pi - 1u : 0u;
+			const uint64_t kp = K[pj];
+			const int32_t pt = (int32_t)key_target(kp), pq = (int32_t)key_query(kp);
+			const bool same = key_list(kp) == list && a - pj <= (uint32_t)P.chaining_band_length;
+			const bool skipc = pq == cq || pt == ct;                                          // :455-456
+			const bool brk = !skipc && (pt + P.max_target_gap_length < ct);                   // :458
+			const bool consider = active && same && !skipc && !brk && (cq - pq) >= 0;         // :465
+			const bool link = consider && linkable(ct, cq, pt, pq, P);
+			hit |= link;
+			looked += (consider && !link) ? 1 : 0;
+			active = active && same && !brk && !link && looked <= P.max_num_skips && pj > 0;  // :482: the reference's scan has given up by then
+			pi = pj;
 		}
 		const uint32_t m = __ballot_sync(0xffffffffu, hit);
 		if (hit) nt[base + cnt + __popc(m & ((1u << lane) - 1u))] = a;
@@ -127,8 +133,17 @@ k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64
 	float max_chaining_score = 0.0f;                               // :428
 	const float fe = (float)P.e;
 	uint32_t j = 0;
+	// software pipeline over the listed anchors: the key of the next anchor and the keys of its first 32 predecessors are
+	// requested one anchor ahead, so that their (L2 / HBM) latency overlaps the prefix operations of the current anchor
+	uint32_t nt_reg = lane < m_nt ? NT[lane] : 0u;                 // NT[jb + lane] for the block of 32 list entries at jb
+	uint32_t jb = 0;
+	auto nt_at = [&](uint32_t jj) -> uint32_t {                    // jj in [jb, jb + 32)
+		return __shfl_sync(0xffffffffu, nt_reg, (int)(jj - jb));
+	};
+	uint64_t kc_pre = 0, kp_pre = 0;
+	if (m_nt) { const uint32_t a0 = nt_at(0); kc_pre = K[a0]; kp_pre = K[a0 > (uint32_t)lane ? a0 - 1u - (uint32_t)lane : 0u]; }
 	while (j < m_nt) {
-		const uint32_t first = NT[j];
+		const uint32_t first = nt_at(j);
 		const uint32_t list = key_list(K[first]);
 		uint32_t ls;                                               // first anchor of this (ref, strand) list: lower bound of the list id
 		{
@@ -138,9 +153,18 @@ k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64
 		}
 		float cs[kMaxBest]; uint32_t ci[kMaxBest]; int ncand = 0;
 		for (; j < m_nt; ++j) {
-			const uint32_t ai = NT[j];
-			const uint64_t kc = K[ai];
+			const uint32_t ai = nt_at(j);
+			const uint64_t kc = kc_pre;
 			if (key_list(kc) != list) break;
+			const uint64_t kp_first = kp_pre;
+			{   // request the next listed anchor's keys now
+				const uint32_t jn = j + 1;
+				if (jn < m_nt) {
+					if (jn - jb >= 32u) { jb = jn; nt_reg = jb + lane < m_nt ? NT[jb + lane] : 0u; }
+					const uint32_t an = nt_at(jn);
+					kc_pre = K[an]; kp_pre = K[an > (uint32_t)lane ? an - 1u - (uint32_t)lane : 0u];
+				}
+			}
 			float sc = fe; uint32_t pr = ai;                       // :442-443
 			const int32_t ct = (int32_t)key_target(kc), cq = (int32_t)key_query(kc);
 			uint32_t start = ls;
@@ -150,7 +174,7 @@ k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64
 			for (uint32_t top = ai; top > start && !done; top = top >= 32 ? top - 32 : 0) {
 				const bool inrange = top >= start + 1u + (uint32_t)lane;          // predecessor top-1-lane is still >= start
 				const uint32_t pi = inrange ? top - 1u - (uint32_t)lane : start;
-				const uint64_t kp = K[pi];
+				const uint64_t kp = (top == ai && inrange) ? kp_first : K[pi];
 				const int32_t pt = (int32_t)key_target(kp), pq = (int32_t)key_query(kp);
 				const bool brk_t = inrange && (pt + P.max_target_gap_length < ct);              // :458
 				const uint32_t dead_mask = __ballot_sync(0xffffffffu, brk_t || !inrange);
@@ -158,7 +182,7 @@ k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64
 				const int32_t td = ct - pt, qd = cq - pq;
 				const bool valid = lane < first_dead && pq != cq && pt != ct && qd >= 0;     // :455-457, :465
 				float cur = 0.0f;
-				if (valid && linkable(ct, cq, pt, pq, P)) cur = __fadd_rn(__ldcg(S + pi), (float)min(min(td, qd), P.e));   // :467-474
+				if (valid && linkable(ct, cq, pt, pq, P)) cur = __fadd_rn(S[pi], (float)min(min(td, qd), P.e));   // :467-474 (S[pi] was stored by lane 0 before a __syncwarp)
 				const uint32_t valid_mask = __ballot_sync(0xffffffffu, valid);
 				if (__ballot_sync(0xffffffffu, cur > sc) == 0) {
 					// nothing here beats the score so far: every lane that counts is a skip (:479-482)

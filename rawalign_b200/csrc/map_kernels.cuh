@@ -225,22 +225,30 @@ k_fill_anchors(ReadState *__restrict__ st, const uint32_t *__restrict__ act, uin
 	const uint64_t a = evoff[i];
 	const uint32_t n_seed = n_seed_in[i];
 	const uint32_t chunk_start = s.offset;                                                          // gen_chains(..., reg->offset, ...) :574
+	// hits of 32 seeds at a time, spread evenly over the lanes (the hit counts are heavy-tailed: a lane that owned one
+	// frequent seed would hold the warp): hit h of the tile belongs to the seed whose exclusive offset is the last one <= h
+	__shared__ uint32_t s_excl[32], s_q[32];
+	__shared__ uint64_t s_vo[32];
 	for (uint32_t b = 0; b < n_seed; b += 32) {
 		const uint32_t sd = b + lane;
 		const uint32_t c = sd < n_seed ? seed_cnt[a + sd] : 0u;
 		uint32_t inc = c;
 #pragma unroll
 		for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += y; }
-		const uint64_t mine = o + inc - c;
-		if (c) {
-			const uint64_t vo = seed_off[a + sd];
-			const uint32_t q = seeds_p[a + sd] + chunk_start;                                         // pi + chunk_start, :387
-			for (uint32_t t = 0; t < c; ++t) {
-				const uint64_t kv = vals[vo + t];
-				keys[mine + t] = pack_key((uint32_t)(kv >> 32), (uint32_t)(kv & 1), (uint32_t)(kv >> 1) & 0x7fffffffu, q);   // :385-387
-			}
+		const uint32_t total = __shfl_sync(0xffffffffu, inc, 31);
+		s_excl[lane] = inc - c;
+		s_vo[lane] = sd < n_seed ? seed_off[a + sd] : 0ull;
+		s_q[lane] = sd < n_seed ? seeds_p[a + sd] + chunk_start : 0u;                                  // pi + chunk_start, :387
+		__syncwarp();
+		for (uint32_t h = lane; h < total; h += 32) {
+			int lo = 0;
+#pragma unroll
+			for (int step = 16; step > 0; step >>= 1) if (s_excl[lo + step] <= h) lo += step;      // seeds without hits share an offset: the last one wins
+			const uint64_t kv = vals[s_vo[lo] + (h - s_excl[lo])];
+			keys[o + h] = pack_key((uint32_t)(kv >> 32), (uint32_t)(kv & 1), (uint32_t)(kv >> 1) & 0x7fffffffu, s_q[lo]);   // :385-387
 		}
-		o += __shfl_sync(0xffffffffu, inc, 31);
+		__syncwarp();
+		o += total;
 	}
 	for (uint64_t k = base + seg_n[i] + lane; k < base + seg_pad[i]; k += 32) keys[k] = kPadKey;
 }
@@ -249,7 +257,7 @@ k_fill_anchors(ReadState *__restrict__ st, const uint32_t *__restrict__ act, uin
 // anchor sort (rmap.cpp:396-401): one CTA per read, bitonic network over the padded segment
 // ---------------------------------------------------------------------------------------------------------------
 constexpr uint32_t kSortSmem = 16384;                              // keys staged in shared memory (128 KB, opt-in)
-constexpr int kSortThreads = 512;
+constexpr int kSortThreads = 1024;
 __global__ void __launch_bounds__(kSortThreads)
 k_sort_segments(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_base, const uint32_t *__restrict__ seg_pad,
                 const uint32_t *__restrict__ skip, uint32_t n_act)
@@ -274,7 +282,8 @@ k_sort_segments(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_ba
 				const uint32_t hi = lo + stride;
 				const bool up = (lo & size) == 0;
 				const uint64_t x = w[lo], y = w[hi];
-				if ((x > y) == up) { w[lo] = y; w[hi] = x; }
+				const bool sw = (x > y) == up;
+				w[lo] = sw ? y : x; w[hi] = sw ? x : y;
 			}
 			__syncthreads();
 		}
