@@ -88,7 +88,8 @@ struct ra_index {
 	Buf raw16, rd_off, rd_len, rd_offset, rd_scale, sig, state, chains, chains_tmp, paf;
 	Buf act, coff, clen, ev_round, evoff_round, ev, seeds_h, seeds_p, seed_cnt, seed_off, n_seed, n_hits, seg_n, seg_base, counters;
 	Buf keys, score, pred, used, anc[2], cand, n_cand, cand_base, dtw_chains, group_first, dscore, dkeep, scan_tmp;
-	Buf lsig_keep, nt, n_nt;
+	Buf lsig_keep, nt, n_nt, bin_base;
+	uint32_t tshift = 0, n_bins = 0;                               // bin function of the bucket sort: bin_base[ref << 1 | strand] + (target >> tshift)
 	std::vector<uint64_t> last_off; std::vector<uint32_t> last_len; bool last_raw = false;   // the batch left on the device by the last ra_map_batch
 	void *pin = nullptr; size_t pin_cap = 0;
 	bool sort_attr = false;                                        // the sort kernel's > 48 KB shared memory opt-in (one index = one device)
@@ -129,6 +130,21 @@ int build_device_index(ra_ctx *ctx, ra_index *ix, const float *const *fwd, const
 	MAP_CUDA(cudaMemcpy(ix->slots.p, slots.data(), n_slots * sizeof(Slot), cudaMemcpyHostToDevice));
 	if ((rc = ix->vals.reserve(std::max<uint64_t>(ix->n_vals, 1) * 8))) return rc;
 	if (ix->n_vals) MAP_CUDA(cudaMemcpy(ix->vals.p, vals, ix->n_vals * 8, cudaMemcpyHostToDevice));
+	if (2ull * ix->n_seq <= 4096) {                                // bins of the anchor bucket sort (map_kernels.cuh, kBins): uniform over the concatenated reference
+		uint32_t ts = 0;
+		for (;; ++ts) {
+			uint64_t tot = 0;
+			for (uint32_t i = 0; i < ix->n_seq; ++i) tot += 2ull * (((uint64_t)ix->seq_len[i] >> ts) + 1);
+			if (tot <= 4096) break;
+		}
+		std::vector<uint32_t> bb(2 * (size_t)ix->n_seq);
+		uint32_t acc = 0;
+		for (uint32_t i = 0; i < ix->n_seq; ++i)
+			for (int st = 0; st < 2; ++st) { bb[2 * i + st] = acc; acc += (uint32_t)(((uint64_t)ix->seq_len[i] >> ts) + 1); }
+		if ((rc = ix->bin_base.reserve(bb.size() * 4))) return rc;
+		MAP_CUDA(cudaMemcpy(ix->bin_base.p, bb.data(), bb.size() * 4, cudaMemcpyHostToDevice));
+		ix->tshift = ts; ix->n_bins = acc;
+	}
 	MAP_CUDA(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
 	for (auto &e : ix->ev_t) MAP_CUDA(cudaEventCreate(&e));
 	return RA_OK;
@@ -238,7 +254,7 @@ void ra_index_destroy(ra_index *ix)
 	               &ix->chains_tmp, &ix->paf, &ix->act, &ix->coff, &ix->clen, &ix->ev_round, &ix->evoff_round, &ix->ev, &ix->seeds_h, &ix->seeds_p,
 	               &ix->seed_cnt, &ix->seed_off, &ix->n_seed, &ix->n_hits, &ix->seg_n, &ix->seg_base, &ix->counters, &ix->keys, &ix->score, &ix->pred,
 	               &ix->used, &ix->anc[0], &ix->anc[1], &ix->cand, &ix->n_cand, &ix->cand_base, &ix->dtw_chains, &ix->group_first, &ix->dscore,
-	               &ix->dkeep, &ix->scan_tmp, &ix->lsig_keep, &ix->nt, &ix->n_nt };
+	               &ix->dkeep, &ix->scan_tmp, &ix->lsig_keep, &ix->nt, &ix->n_nt, &ix->bin_base };
 	for (Buf *b : all) b->release();
 	if (ix->pin) cudaFreeHost(ix->pin);
 	if (ix->stream) cudaStreamDestroy(ix->stream);

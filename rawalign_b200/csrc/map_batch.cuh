@@ -191,12 +191,22 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 		                                    ix->seeds_p.as<uint32_t>(), ix->seed_cnt.as<uint32_t>(), ix->seed_off.as<uint64_t>(), ix->vals.as<uint64_t>(),
 		                                    ix->n_seed.as<uint32_t>(), ix->seg_n.as<uint32_t>(), seg_pad, ix->seg_base.as<uint64_t>(), skip, ix->keys.as<uint64_t>());
 		k_advance_offset<<<(n_act + 127) / 128, 128, 0, S>>>(st, ix->act.as<uint32_t>(), n_act, ix->evoff_round.as<uint64_t>(), skip);
-		if (!ix->sort_attr) { MAP_CUDA(cudaFuncSetAttribute(k_sort_segments, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kSortSmem * 8))); ix->sort_attr = true; }
-		k_sort_segments<<<n_act, kSortThreads, kSortSmem * 8, S>>>(ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), seg_pad, skip, n_act);
+		if (!ix->sort_attr) {
+			MAP_CUDA(cudaFuncSetAttribute(k_sort_segments, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kSortSmem * 8)));
+			MAP_CUDA(cudaFuncSetAttribute(k_sort_buckets, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BucketSmem)));
+			ix->sort_attr = true;
+		}
+		uint32_t done_upto = 0;
+		if (ix->n_bins && !getenv("RA_MAP_BITONIC_ONLY")) {            // bucket form for segments that fit shared memory, the bitonic network for the rest
+			k_sort_buckets<<<n_act, kBucketThreads, sizeof(BucketSmem), S>>>(ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), ix->seg_n.as<uint32_t>(), seg_pad, skip, n_act,
+			                                                              ix->bin_base.as<uint32_t>(), ix->tshift, ix->n_bins);
+			done_upto = kBucketMaxKeys; ++launches;
+		}
+		k_sort_segments<<<n_act, kSortThreads, kSortSmem * 8, S>>>(ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), seg_pad, skip, n_act, done_upto);
 		launches += 3;
 		MAP_CUDA(cudaStreamSynchronize(S));
 		stt.sort_ms += clk.lap();
-		k_chain_pre<<<(n_act * 32 + 127) / 128, 128, 0, S>>>(ix->act.as<uint32_t>(), n_act, P, ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), ix->seg_n.as<uint32_t>(), skip,
+		k_chain_pre<<<n_act, kPreThreads, 0, S>>>(ix->act.as<uint32_t>(), n_act, P, ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), ix->seg_n.as<uint32_t>(), skip,
 		                                                     ix->score.as<float>(), ix->pred.as<uint32_t>(), ix->used.as<uint8_t>(), ix->nt.as<uint32_t>(), ix->n_nt.as<uint32_t>());
 		k_chain<<<(n_act * 32 + 127) / 128, 128, 0, S>>>(ix->act.as<uint32_t>(), n_act, P, ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), ix->seg_n.as<uint32_t>(), skip,
 		                                                 ix->score.as<float>(), ix->pred.as<uint32_t>(), ix->used.as<uint8_t>(), ix->nt.as<uint32_t>(), ix->n_nt.as<uint32_t>(),

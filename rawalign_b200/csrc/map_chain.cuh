@@ -45,23 +45,25 @@ __device__ __forceinline__ bool linkable(int32_t ct, int32_t cq, int32_t pt, int
 // improve) satisfies the gap conditions of :472, so their score stays the seed value e and they are their own predecessor --
 // decided here, in parallel, without the recurrence.  The anchors that do have a linkable predecessor in reach are listed in
 // order (nt) for the sequential pass.  Every anchor gets score = e, pred = self, used = 0.
-__global__ void __launch_bounds__(128)
+constexpr int kPreThreads = 256;
+__global__ void __launch_bounds__(kPreThreads)
 k_chain_pre(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_base,
             const uint32_t *__restrict__ seg_n, const uint32_t *__restrict__ skip, float *__restrict__ score, uint32_t *__restrict__ pred,
             uint8_t *__restrict__ used, uint32_t *__restrict__ nt, uint32_t *__restrict__ n_nt)
 {
-	const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-	const int lane = threadIdx.x & 31;
+	__shared__ uint32_t warp_cnt[kPreThreads / 32];
+	const uint32_t i = blockIdx.x;                                 // one CTA per read: 8 warps keep 8 scans in flight per read
+	const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
 	if (i >= n_act) return;
-	if (skip[i]) { if (lane == 0) n_nt[i] = 0; return; }
+	if (skip[i]) { if (tid == 0) n_nt[i] = 0; return; }
 	const uint64_t base = seg_base[i];
 	const uint32_t n = seg_n[i];
 	const uint64_t *__restrict__ K = keys + base;
 	const float fe = (float)P.e;
 	const bool all = P.no_filter || fe >= P.min_chaining_score;    // an isolated anchor could itself be a chain end: no shortcut
 	uint32_t cnt = 0;
-	for (uint32_t a0 = 0; a0 < n; a0 += 32) {
-		const uint32_t a = a0 + lane;
+	for (uint32_t a0 = 0; a0 < n; a0 += kPreThreads) {
+		const uint32_t a = a0 + tid;
 		const bool mine = a < n;
 		const uint64_t kc = mine ? K[a] : 0ull;
 		const uint32_t list = key_list(kc);
@@ -87,11 +89,17 @@ k_chain_pre(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const ui
 			active = active && same && !brk && !link && looked <= P.max_num_skips && pj > 0;  // :482: the reference's scan has given up by then
 			pi = pj;
 		}
-		const uint32_t m = __ballot_sync(0xffffffffu, hit);
-		if (hit) nt[base + cnt + __popc(m & ((1u << lane) - 1u))] = a;
-		cnt += __popc(m);
+		const uint32_t m = __ballot_sync(0xffffffffu, hit);        // ordered compaction of the tile's listed anchors
+		if (lane == 0) warp_cnt[wid] = __popc(m);
+		__syncthreads();
+		uint32_t before = 0, total = 0;
+#pragma unroll
+		for (int w = 0; w < kPreThreads / 32; ++w) { const uint32_t t = warp_cnt[w]; if (w < wid) before += t; total += t; }
+		if (hit) nt[base + cnt + before + __popc(m & ((1u << lane) - 1u))] = a;
+		cnt += total;
+		__syncthreads();
 	}
-	if (lane == 0) n_nt[i] = cnt;
+	if (tid == 0) n_nt[i] = cnt;
 }
 
 // Chaining DP of gen_chains (rmap.cpp:427-507) for every (ref, strand) list of one read, in the reference's list order,
@@ -152,6 +160,8 @@ k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64
 			ls = lo;
 		}
 		float cs[kMaxBest]; uint32_t ci[kMaxBest]; int ncand = 0;
+#pragma unroll
+		for (int t = 0; t < kMaxBest; ++t) { cs[t] = 0.0f; ci[t] = 0u; }
 		for (; j < m_nt; ++j) {
 			const uint32_t ai = nt_at(j);
 			const uint64_t kc = kc_pre;
@@ -217,26 +227,33 @@ k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64
 			if (sc > max_chaining_score) max_chaining_score = sc;  // :485-487
 			if (P.no_filter || (sc >= P.min_chaining_score && sc > max_chaining_score / 2)) {   // :488-492
 				// keep the num_best_chains best by (score desc, index desc) (compare(), :175-179): ai only grows, so a tie goes in front
-				int p = 0;
-				while (p < ncand && !(sc >= cs[p])) ++p;
+				int p = 0;                                         // fully unrolled with selects: the list stays in registers
+#pragma unroll
+				for (int t = 0; t < kMaxBest; ++t) p += (t < ncand && cs[t] > sc) ? 1 : 0;
 				if (p < P.num_best_chains) {
 					const int lastp = min(ncand, P.num_best_chains - 1);
-					for (int t = lastp; t > p; --t) { cs[t] = cs[t - 1]; ci[t] = ci[t - 1]; }
-					cs[p] = sc; ci[p] = ai;
+#pragma unroll
+					for (int t = kMaxBest - 1; t > 0; --t) { const bool sh = t > p && t <= lastp; cs[t] = sh ? cs[t - 1] : cs[t]; ci[t] = sh ? ci[t - 1] : ci[t]; }
+#pragma unroll
+					for (int t = 0; t < kMaxBest; ++t) { const bool here = t == p; cs[t] = here ? sc : cs[t]; ci[t] = here ? ai : ci[t]; }
 					if (ncand < P.num_best_chains) ++ncand;
 				}
 			}
 		}
-		if (lane == 0)
-			for (int k = 0; k < ncand; ++k) {                      // :498-505
+		if (lane == 0) {
+			bool stop = false;
+#pragma unroll
+			for (int k = 0; k < kMaxBest; ++k) {                   // :498-505
+				if (k >= ncand || stop) continue;
 				ChainRec rec;
 				if (nc < P.cap_chains && traceback(K, S, Pd, U, ci[k], P.min_num_anchors, anc_cur + wo, &rec)) {
 					rec.ref = list >> 1; rec.strand = list & 1u; rec.anchor_off = wo;
 					wo += rec.n_anchors;
 					out[nc++] = rec;
 				}
-				if (!P.no_filter && S[ci[k]] < max_chaining_score / 2) break;
+				if (!P.no_filter && S[ci[k]] < max_chaining_score / 2) stop = true;
 			}
+		}
 		__syncwarp();
 	}
 	(void)n;

@@ -260,13 +260,13 @@ constexpr uint32_t kSortSmem = 16384;                              // keys stage
 constexpr int kSortThreads = 1024;
 __global__ void __launch_bounds__(kSortThreads)
 k_sort_segments(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_base, const uint32_t *__restrict__ seg_pad,
-                const uint32_t *__restrict__ skip, uint32_t n_act)
+                const uint32_t *__restrict__ skip, uint32_t n_act, uint32_t done_upto /* segments up to this padded size were sorted by k_sort_buckets */)
 {
 	extern __shared__ uint64_t sk[];
 	const uint32_t i = blockIdx.x;
 	if (i >= n_act || skip[i]) return;
 	const uint32_t n = seg_pad[i];
-	if (n < 2) return;
+	if (n < 2 || n <= done_upto) return;
 	uint64_t *g = keys + seg_base[i];
 	const int tid = threadIdx.x;
 	const bool in_smem = n <= kSortSmem;
@@ -289,6 +289,108 @@ k_sort_segments(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_ba
 		}
 	if (in_smem)
 		for (uint32_t k = tid; k < n; k += kSortThreads) g[k] = sk[k];
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// anchor sort, bucket form: one CTA per read, everything in shared memory
+// ---------------------------------------------------------------------------------------------------------------
+// The packed keys are uniformly spread over the reference (seed hits are), so one counting pass over a monotone bin function
+// -- bin = bin_base[ref << 1 | strand] + (target >> tshift), at most kBins bins over the whole index -- leaves a handful of
+// keys per bin; the bins are then finished independently (insertion sort by one thread, or a warp-wide bitonic pass for the
+// rare crowded bin, e.g. the read's true locus).  O(n) work per read instead of the bitonic network's n log^2 n.
+constexpr uint32_t kBins = 4096;
+constexpr uint32_t kBucketMaxKeys = 8192;
+constexpr int kBucketThreads = 512;
+struct BucketSmem {
+	uint64_t keys[kBucketMaxKeys];
+	uint32_t count[kBins + 1];
+	uint32_t cursor[kBins];
+	uint32_t warp_tot[kBucketThreads / 32];
+};
+
+__device__ __forceinline__ uint32_t key_bin(uint64_t k, const uint32_t *__restrict__ bin_base, uint32_t tshift)
+{
+	return bin_base[key_list(k)] + (key_target(k) >> tshift);
+}
+
+__global__ void __launch_bounds__(kBucketThreads)
+k_sort_buckets(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_base, const uint32_t *__restrict__ seg_n, const uint32_t *__restrict__ seg_pad,
+               const uint32_t *__restrict__ skip, uint32_t n_act, const uint32_t *__restrict__ bin_base, uint32_t tshift, uint32_t n_bins)
+{
+	extern __shared__ __align__(16) unsigned char bsm_raw[];
+	BucketSmem &sm = *reinterpret_cast<BucketSmem *>(bsm_raw);
+	const uint32_t i = blockIdx.x;
+	if (i >= n_act || skip[i]) return;
+	const uint32_t n = seg_n[i];
+	if (n < 2 || seg_pad[i] > kBucketMaxKeys) return;             // long segments are left to k_sort_segments
+	uint64_t *g = keys + seg_base[i];
+	const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+	for (uint32_t b = tid; b <= n_bins; b += kBucketThreads) sm.count[b] = 0;
+	__syncthreads();
+	for (uint32_t k = tid; k < n; k += kBucketThreads) atomicAdd(&sm.count[key_bin(g[k], bin_base, tshift)], 1u);
+	__syncthreads();
+	// exclusive scan of count[0 .. n_bins) -> cursor / count (count[b] becomes the start of bin b, count[n_bins] = n)
+	uint32_t carry = 0;
+	for (uint32_t b0 = 0; b0 < n_bins; b0 += kBucketThreads) {
+		const uint32_t b = b0 + tid;
+		const uint32_t v = b < n_bins ? sm.count[b] : 0u;
+		uint32_t inc = v;
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += y; }
+		if (lane == 31) sm.warp_tot[wid] = inc;
+		__syncthreads();
+		uint32_t before = 0, total = 0;
+		for (int w = 0; w < kBucketThreads / 32; ++w) { const uint32_t t = sm.warp_tot[w]; if (w < wid) before += t; total += t; }
+		if (b < n_bins) { const uint32_t ex = carry + before + inc - v; sm.count[b] = ex; sm.cursor[b] = ex; }
+		carry += total;
+		__syncthreads();
+	}
+	if (tid == 0) sm.count[n_bins] = n;
+	__syncthreads();
+	for (uint32_t k = tid; k < n; k += kBucketThreads) {
+		const uint64_t key = g[k];
+		sm.keys[atomicAdd(&sm.cursor[key_bin(key, bin_base, tshift)], 1u)] = key;
+	}
+	__syncthreads();
+	// finish the bins: small ones by one thread each, crowded ones by a whole warp afterwards
+	constexpr uint32_t kSmall = 24;
+	for (uint32_t b = tid; b < n_bins; b += kBucketThreads) {
+		const uint32_t lo = sm.count[b], hi = sm.count[b + 1];
+		if (hi - lo < 2 || hi - lo > kSmall) continue;
+		for (uint32_t a = lo + 1; a < hi; ++a) {
+			const uint64_t x = sm.keys[a];
+			uint32_t c = a;
+			while (c > lo && sm.keys[c - 1] > x) { sm.keys[c] = sm.keys[c - 1]; --c; }
+			sm.keys[c] = x;
+		}
+	}
+	for (uint32_t b = wid; b < n_bins; b += kBucketThreads / 32) {   // warp-uniform loop
+		const uint32_t lo = sm.count[b], m = sm.count[b + 1] - lo;
+		if (m <= kSmall) continue;
+		uint32_t pad = 32; while (pad < m) pad <<= 1;
+		uint64_t *w = sm.keys + lo;
+		// bitonic network in its all-ascending form (first step of every merge compares mirrored positions), over a virtual
+		// power-of-two range whose slots >= m hold +inf: every comparator moves the minimum to the lower index, so the
+		// virtual keys never move and only pairs of real keys are touched
+		for (uint32_t size = 2; size <= pad; size <<= 1) {
+			const uint32_t half = size >> 1;
+			for (uint32_t t = lane; t < (pad >> 1); t += 32) {
+				const uint32_t blk = t / half, off = t - blk * half;
+				const uint32_t l0 = blk * size + off, h0 = blk * size + size - 1u - off;
+				if (h0 < m) { const uint64_t x = w[l0], y = w[h0]; if (x > y) { w[l0] = y; w[h0] = x; } }
+			}
+			__syncwarp();
+			for (uint32_t stride = half >> 1; stride > 0; stride >>= 1) {
+				for (uint32_t t = lane; t < (pad >> 1); t += 32) {
+					const uint32_t l0 = 2 * t - (t & (stride - 1)), h0 = l0 + stride;
+					if (h0 < m) { const uint64_t x = w[l0], y = w[h0]; if (x > y) { w[l0] = y; w[h0] = x; } }
+				}
+				__syncwarp();
+			}
+		}
+	}
+	__syncthreads();
+	for (uint32_t k = tid; k < n; k += kBucketThreads) g[k] = sm.keys[k];
 }
 
 } // namespace mapk
