@@ -316,6 +316,14 @@ int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt,
                  const float *sig, const uint64_t *sig_off, const uint32_t *sig_len,
                  uint32_t n_reads, ra_paf_t *out, ra_map_stats_t *stats);
 
+/* With RA_M_DTW_OUTPUT_CIGAR in opt->flag, ra_map_batch also runs align_chain(chains[0], cigar=true) for every mapped read
+ * (rmap.cpp:715-717; full matrix + traceback per anchor-to-anchor part, the quirks of SURVEY.md A.4 included) and
+ * ra_paf_t::alns is the score that call leaves in chains[0].alignment_score (what the alns:f: tag prints, :741).  The
+ * alignments of the last such call, CSR by read: elements [path_off[r], path_off[r+1]) of path_i (read event), path_j
+ * (reference position), path_diff -- the triples of the aln:s: tag (:580-592).  Call with path_i == NULL to size (path_off is
+ * filled, n_reads+1 entries). */
+int ra_map_last_cigar(ra_index *ix, uint32_t n_reads, uint64_t *path_off, uint64_t *path_i, uint64_t *path_j, float *path_diff, uint64_t cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -107,6 +107,13 @@ def main():
                 out["chunk_nchains"] = np.array(NCH, np.int32)
             rm.index_free(idx)
         out["paf"] = np.array(lines)
+        # --dtw-output-cigar (rmap.cpp:715-717, :741-744): alns:f: and the aln:s: triples of chains[0] of every mapped read
+        from oracle import RI_M_DTW_OUTPUT_CIGAR
+        idx = rm.index_build(d + "/ref.fa", d + "/model.txt", "sensitive")
+        paf, mapped, chunks = rm.map_reads(idx, rm.mapopt(flag=RI_M_DTW_EVALUATE_CHAINS | RI_M_DTW_OUTPUT_CIGAR), sig, raw_off, raw_len, n_threads=4)
+        out["paf_cigar"] = np.array("\n".join(strip_mt(l) for l in paf))
+        print("cigar lines", len(paf), "bytes", sum(len(l) for l in paf))
+        rm.index_free(idx)
         # a sketch of real events (ri_sketch, the call of rmap.cpp:367)
         from oracle import Oracle
         ev = Oracle().detect_events(sig[:4000])

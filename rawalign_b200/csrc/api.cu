@@ -667,6 +667,12 @@ int ra_set_tuning(ra_ctx *ctx, const char *name, int64_t value)
 // internal (map.cu): kernels launched outside this file count too; errors raised there go through ra_last_error()
 void ra__add_launches(ra_ctx *ctx, uint64_t n) { if (ctx) ctx->launches += n; }
 int ra__device(const ra_ctx *ctx) { return ctx ? ctx->device : 0; }
+// internal (map.cu): lets the entry points that read "the events resident on the device" read the map loop's event arena
+void ra__swap_resident(ra_ctx *ctx, void **dev_ptr, uint64_t *n_floats)
+{
+	std::swap(ctx->ev_out.p, *dev_ptr);
+	std::swap(ctx->resident_events, *n_floats);
+}
 int ra__fail(int code, const char *fmt, ...)
 {
 	va_list ap; va_start(ap, fmt);
@@ -997,10 +1003,12 @@ int ra_dtw_tb_batch(ra_ctx *ctx, const float *a_arena, uint64_t n_a, const float
                     const ra_dtw_item_t *items, uint32_t n_items, float *cost_out, uint32_t *path_i, uint32_t *path_j,
                     float *path_diff, uint64_t path_cap, uint64_t *path_off)
 {
-	if (!ctx || !path_off || (n_items && (!a_arena || !items || !cost_out || !path_i || !path_j))) return fail(RA_EINVAL, "NULL argument");
+	if (!ctx || !path_off || (n_items && (!items || !cost_out || !path_i || !path_j))) return fail(RA_EINVAL, "NULL argument");
 	RA_CUDA(cudaSetDevice(ctx->device));
 	path_off[0] = 0;
 	if (n_items == 0) return RA_OK;
+	if (!a_arena && !ctx->resident_events) return fail(RA_EINVAL, "a_arena is NULL and no events are resident on the device");
+	if (!a_arena) n_a = ctx->resident_events;                     // a_arena == NULL: the events the last event-detection call left on the device
 	if (!b_arena && !ctx->ref.p) return fail(RA_EINVAL, "no reference arena: pass b_arena or call ra_ref_load first");
 	int rc = check_items(items, n_items, n_a, b_arena ? n_b : ctx->ref_n);
 	if (rc) return rc;
@@ -1016,7 +1024,7 @@ int ra_dtw_tb_batch(ra_ctx *ctx, const float *a_arena, uint64_t n_a, const float
 		maxw = std::max(maxw, it.b_len);
 	}
 	dir_off[n_items] = dwords; slot_off[n_items] = slots;
-	if ((rc = ctx->a_arena.reserve((size_t)n_a * sizeof(float)))) return rc;
+	if (a_arena && (rc = ctx->a_arena.reserve((size_t)n_a * sizeof(float)))) return rc;
 	if ((rc = ctx->items.reserve((size_t)n_items * sizeof(ra_dtw_item_t)))) return rc;
 	if ((rc = ctx->cost.reserve((size_t)n_items * sizeof(float)))) return rc;
 	if ((rc = ctx->dirs.reserve((size_t)dwords * 4))) return rc;
@@ -1031,7 +1039,8 @@ int ra_dtw_tb_batch(ra_ctx *ctx, const float *a_arena, uint64_t n_a, const float
 	if ((rc = ctx->out_j.reserve((size_t)slots * 4))) return rc;
 	if (path_diff && (rc = ctx->out_d.reserve((size_t)slots * 4))) return rc;
 	if ((rc = ctx->counter.reserve(64))) return rc;
-	RA_CUDA(cudaMemcpyAsync(ctx->a_arena.p, a_arena, (size_t)n_a * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	if (a_arena) RA_CUDA(cudaMemcpyAsync(ctx->a_arena.p, a_arena, (size_t)n_a * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	const float *a_dev = a_arena ? ctx->a_arena.as<float>() : ctx->ev_out.as<float>();
 	const float *b_dev = ctx->ref.as<float>();
 	if (b_arena) {
 		if ((rc = ctx->b_arena.reserve((size_t)n_b * sizeof(float)))) return rc;
@@ -1043,7 +1052,7 @@ int ra_dtw_tb_batch(ra_ctx *ctx, const float *a_arena, uint64_t n_a, const float
 	RA_CUDA(cudaMemcpyAsync(ctx->slot_off.p, slot_off.data(), (size_t)(n_items + 1) * 8, cudaMemcpyHostToDevice, ctx->stream));
 
 	ra::DtwLaunch L; memset(&L, 0, sizeof(L));
-	L.a_arena = ctx->a_arena.as<float>(); L.b_arena = b_dev; L.items = ctx->items.as<ra_dtw_item_t>(); L.n_items = n_items;
+	L.a_arena = a_dev; L.b_arena = b_dev; L.items = ctx->items.as<ra_dtw_item_t>(); L.n_items = n_items;
 	L.cost = ctx->cost.as<float>(); L.work_counter = ctx->counter.as<uint32_t>();
 	if (maxw > ra::dtw_generic_smem_ring_cap()) {
 		uint32_t cap = 1; while (cap < maxw) cap <<= 1;
@@ -1338,8 +1347,8 @@ int ra_align_chains_cigar_batch(ra_ctx *ctx, const float *read_arena, uint64_t n
                                 float *alignment_score, float *dtw_cost_out, uint64_t *path_i, uint64_t *path_j, float *path_diff,
                                 uint64_t path_cap, uint64_t *path_off)
 {
-	if (!ctx || !path_off || (n_chains && (!read_arena || !anchors || !chains || !alignment_score || !path_i || !path_j)))
-		return fail(RA_EINVAL, "NULL argument");
+	if (!ctx || !path_off || (n_chains && (!anchors || !chains || !alignment_score || !path_i || !path_j)))
+		return fail(RA_EINVAL, "NULL argument");                   // read_arena == NULL: the events resident on the device
 	const ra_mapopt_t &o = ctx->opt;
 	std::vector<ra_dtw_item_t> items;
 	std::vector<uint64_t> first(n_chains + 1);

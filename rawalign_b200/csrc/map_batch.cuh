@@ -55,6 +55,11 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 	if (stats) memset(stats, 0, sizeof(*stats));
 	if (n_reads == 0) return RA_OK;
 	uint64_t cells_acc[2] = {0, 0};
+	const bool cigar = (opt->flag & RA_M_DTW_OUTPUT_CIGAR) != 0;
+	if (cigar && opt->dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_GLOBAL && opt->dtw_fill_method == RA_DTW_FILL_METHOD_BANDED)
+		return ra__fail(RA_EUNSUP, "global border + banded fill + cigar is not implemented by the reference (rmap.cpp:223-225 asserts)");
+	std::vector<std::pair<uint32_t, float>> cig_alns;
+	ix->cig_start.assign(n_reads, 0); ix->cig_len.assign(n_reads, 0); ix->cig_i.clear(); ix->cig_j.clear(); ix->cig_d.clear();
 	int rc;
 	{   // hot-path options of the context follow the map options; fp_contract / test hooks stay as the context has them
 		ra_mapopt_t o; if ((rc = ra_get_opt(ctx, &o))) return rc;
@@ -177,10 +182,11 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 		MAP_CUDA(ra::launch_exclusive_scan_u32(seg_pad, ix->seg_base.as<uint64_t>(), n_act, S)); ++launches;
 		uint64_t *h64 = reinterpret_cast<uint64_t *>(hc + 16);
 		MAP_CUDA(cudaMemcpyAsync(h64, ix->seg_base.as<uint64_t>() + n_act, 8, cudaMemcpyDeviceToHost, S));
-		MAP_CUDA(cudaMemcpyAsync(h64 + 1, totals, 16, cudaMemcpyDeviceToHost, S));
+		MAP_CUDA(cudaMemcpyAsync(h64 + 1, totals, 24, cudaMemcpyDeviceToHost, S));
 		MAP_CUDA(cudaStreamSynchronize(S));
 		const uint64_t total_pad = h64[0];
 		stt.seeds += h64[1]; stt.anchors += h64[2];
+		const uint64_t max_pad = h64[3];
 		stt.seed_ms += clk.lap();
 		// ---- anchors, sort, chaining -------------------------------------------------------------------------------------
 		const uint64_t an = std::max<uint64_t>(total_pad, 1);
@@ -202,7 +208,8 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 			                                                              ix->bin_base.as<uint32_t>(), ix->tshift, ix->n_bins);
 			done_upto = kBucketMaxKeys; ++launches;
 		}
-		k_sort_segments<<<n_act, kSortThreads, kSortSmem * 8, S>>>(ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), seg_pad, skip, n_act, done_upto);
+		if (max_pad > done_upto)
+			k_sort_segments<<<n_act, kSortThreads, kSortSmem * 8, S>>>(ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), seg_pad, skip, n_act, done_upto);
 		launches += 3;
 		MAP_CUDA(cudaStreamSynchronize(S));
 		stt.sort_ms += clk.lap();
@@ -238,13 +245,74 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 		                                         ix->dscore.as<float>(), ix->dkeep.as<uint8_t>(), skip, ix->chains.as<ChainRec>(), ix->anc[cur].as<ra_anchor_t>(), cur,
 		                                         ix->seq_tab.as<uint64_t>(), ix->paf.as<ra_paf_t>(), counters); ++launches;
 		MAP_CUDA(cudaGetLastError());
+		if (cigar) {                                                // rmap.cpp:715-717 for the reads that left the loop mapped in this round
+			if ((rc = ix->fin_r.reserve((size_t)n_act * 4)) || (rc = ix->fin_aoff.reserve((size_t)n_act * 8)) || (rc = ix->fin_chain.reserve((size_t)n_act * sizeof(ra_chain_t))) ||
+			    (rc = ix->fin_anc.reserve(an * sizeof(ra_anchor_t)))) return rc;
+			k_cigar_list<<<1, 1024, 0, S>>>(st, ix->act.as<uint32_t>(), n_act, P, ix->chains.as<ChainRec>(), ix->paf.as<ra_paf_t>(), ix->fin_r.as<uint32_t>(),
+			                                ix->fin_aoff.as<uint64_t>(), counters); ++launches;
+			MAP_CUDA(cudaMemcpyAsync(hc + 4, counters + 4, 8, cudaMemcpyDeviceToHost, S));
+			MAP_CUDA(cudaStreamSynchronize(S));
+			const uint32_t n_fin = hc[4], n_fa = hc[5];
+			if (n_fin) {
+				k_cigar_pack<<<(n_fin * 32 + 127) / 128, 128, 0, S>>>(st, P, ix->chains.as<ChainRec>(), ix->anc[cur].as<ra_anchor_t>(), ix->seq_tab.as<uint64_t>(),
+				                                                      ix->fin_r.as<uint32_t>(), ix->fin_aoff.as<uint64_t>(), n_fin, ix->fin_chain.as<ra_chain_t>(),
+				                                                      ix->fin_anc.as<ra_anchor_t>()); ++launches;
+				std::vector<uint32_t> fr(n_fin); std::vector<ra_chain_t> fc(n_fin); std::vector<ra_anchor_t> fa(n_fa);
+				MAP_CUDA(cudaMemcpyAsync(fr.data(), ix->fin_r.p, (size_t)n_fin * 4, cudaMemcpyDeviceToHost, S));
+				MAP_CUDA(cudaMemcpyAsync(fc.data(), ix->fin_chain.p, (size_t)n_fin * sizeof(ra_chain_t), cudaMemcpyDeviceToHost, S));
+				MAP_CUDA(cudaMemcpyAsync(fa.data(), ix->fin_anc.p, (size_t)n_fa * sizeof(ra_anchor_t), cudaMemcpyDeviceToHost, S));
+				MAP_CUDA(cudaStreamSynchronize(S));
+				uint64_t pcap = 0;
+				for (uint32_t k = 0; k < n_fin; ++k) {
+					const ra_anchor_t *a = fa.data() + fc[k].anchor_off;
+					pcap += (uint64_t)(a[0].query_position - a[fc[k].n_anchors - 1].query_position) + (a[0].target_position - a[fc[k].n_anchors - 1].target_position) + 2ull * fc[k].n_anchors + 2;
+				}
+				std::vector<float> sc(n_fin), cost(n_fin), pd(pcap);
+				std::vector<uint64_t> pi(pcap), pj(pcap), poff(n_fin + 1);
+				void *evp = ix->ev.p; uint64_t evn = ev_cap;
+				ra__swap_resident(ctx, &evp, &evn);                   // the cigar entry point reads "the events resident on the device"
+				const uint64_t lc = ra_launch_count(ctx);
+				rc = ra_align_chains_cigar_batch(ctx, nullptr, 0, nullptr, 0, fa.data(), n_fa, fc.data(), n_fin, sc.data(), cost.data(), pi.data(), pj.data(), pd.data(), pcap, poff.data());
+				lib_launches += ra_launch_count(ctx) - lc;
+				ra__swap_resident(ctx, &evp, &evn);
+				if (rc) return rc;
+				for (uint32_t k = 0; k < n_fin; ++k) {
+					const uint32_t r = fr[k];
+					ix->cig_start[r] = ix->cig_i.size(); ix->cig_len[r] = poff[k + 1] - poff[k];
+					ix->cig_i.insert(ix->cig_i.end(), pi.begin() + poff[k], pi.begin() + poff[k + 1]);
+					ix->cig_j.insert(ix->cig_j.end(), pj.begin() + poff[k], pj.begin() + poff[k + 1]);
+					ix->cig_d.insert(ix->cig_d.end(), pd.begin() + poff[k], pd.begin() + poff[k + 1]);
+					cig_alns.push_back({r, sc[k]});
+				}
+			}
+			stt.select_ms += clk.lap();
+		}
 	}
 	MAP_CUDA(cudaMemcpyAsync(out, ix->paf.p, (size_t)n_reads * sizeof(ra_paf_t), cudaMemcpyDeviceToHost, S));
 	MAP_CUDA(cudaStreamSynchronize(S));
+	for (auto &x : cig_alns) out[x.first].alns = x.second;          // alns:f: prints chains[0].alignment_score after align_chain(cigar=true) has rewritten it (:306, :741)
 	stt.select_ms += clk.lap();
 	stt.total_ms = total.lap();
 	stt.launches = launches + lib_launches;
 	ra__add_launches(ctx, launches);
 	if (stats) *stats = stt;
+	return RA_OK;
+}
+
+// The alignments of the last ra_map_batch run with RA_M_DTW_OUTPUT_CIGAR, CSR by read (see the header).
+extern "C" int ra_map_last_cigar(ra_index *ix, uint32_t n_reads, uint64_t *path_off, uint64_t *path_i, uint64_t *path_j, float *path_diff, uint64_t cap)
+{
+	if (!ix || !path_off) return ra__fail(RA_EINVAL, "NULL argument");
+	if (ix->cig_len.size() != n_reads) return ra__fail(RA_EINVAL, "the last ra_map_batch mapped %zu reads, not %u", ix->cig_len.size(), n_reads);
+	uint64_t w = 0;
+	for (uint32_t r = 0; r < n_reads; ++r) { path_off[r] = w; w += ix->cig_len[r]; }
+	path_off[n_reads] = w;
+	if (!path_i) return RA_OK;                                      // sizing call
+	if (w > cap) return ra__fail(RA_EINVAL, "path capacity %llu < %llu", (unsigned long long)cap, (unsigned long long)w);
+	for (uint32_t r = 0; r < n_reads; ++r)
+		for (uint64_t t = 0; t < ix->cig_len[r]; ++t) {
+			path_i[path_off[r] + t] = ix->cig_i[ix->cig_start[r] + t]; path_j[path_off[r] + t] = ix->cig_j[ix->cig_start[r] + t];
+			if (path_diff) path_diff[path_off[r] + t] = ix->cig_d[ix->cig_start[r] + t];
+		}
 	return RA_OK;
 }

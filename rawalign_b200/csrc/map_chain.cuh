@@ -36,8 +36,14 @@ __device__ __forceinline__ bool linkable(int32_t ct, int32_t cq, int32_t pt, int
 {
 	const int32_t td = ct - pt, qd = cq - pq;
 	if (pq == cq || pt == ct || qd < 0) return false;
-	const float gap_scale = td > 0 ? __fdiv_rn((float)qd, (float)td) : 1.0f;
-	return abs(td - qd) < P.max_gap_length && gap_scale < 5.0f && gap_scale > 0.75f;
+	if (abs(td - qd) >= P.max_gap_length) return false;
+	if (td <= 0) return true;                                      // gap_scale = 1 (:469)
+	// gap_scale = RN((float)qd / td) against 0.75 and 5 (:472).  Both operands below 2^22 convert exactly and the quotient of
+	// two such integers cannot lie within half an ulp of 3/4 or of 5 without being equal to it (|qd/td - 3/4| >= 1/(4 td)), so
+	// the correctly rounded comparison is the integer one; larger operands take the division
+	if ((uint32_t)td < (1u << 22) && (uint32_t)qd < (1u << 22)) return 4 * (int64_t)qd > 3 * (int64_t)td && (int64_t)qd < 5 * (int64_t)td;
+	const float gap_scale = __fdiv_rn((float)qd, (float)td);
+	return gap_scale < 5.0f && gap_scale > 0.75f;
 }
 
 // Pre-pass of the chaining DP, one lane per anchor.  Most anchors are isolated seed hits: no predecessor the reference's scan
@@ -428,6 +434,62 @@ __global__ void k_advance_offset(ReadState *__restrict__ st, const uint32_t *__r
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n_act || skip[i]) return;
 	st[act[i]].offset += (uint32_t)(evoff[i + 1] - evoff[i]);
+}
+
+// ---- --dtw-output-cigar (rmap.cpp:715-717): chains[0] of the reads that left the loop mapped in this round -------------
+// ordered list of those reads + exclusive scan of their chain-0 anchor counts; one CTA
+__global__ void __launch_bounds__(1024)
+k_cigar_list(const ReadState *__restrict__ st, const uint32_t *__restrict__ act, uint32_t n_act, Params P, const ChainRec *__restrict__ chains,
+             const ra_paf_t *__restrict__ paf, uint32_t *__restrict__ fin_r, uint64_t *__restrict__ fin_aoff, uint32_t *__restrict__ counters /* [4] n_fin, [5] anchors */)
+{
+	__shared__ uint32_t wc[32], wa[32];
+	__shared__ uint32_t base_c, base_a;
+	const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+	if (tid == 0) { base_c = 0; base_a = 0; }
+	__syncthreads();
+	for (uint32_t i0 = 0; i0 < n_act; i0 += 1024) {
+		const uint32_t i = i0 + tid;
+		uint32_t r = 0, na = 0; bool fin = false;
+		if (i < n_act) { r = act[i]; fin = !st[r].active && paf[r].mapped; if (fin) na = chains[(size_t)r * P.cap_chains].n_anchors; }
+		const uint32_t m = __ballot_sync(0xffffffffu, fin);
+		uint32_t inc = na;
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += y; }
+		if (lane == 31) wa[wid] = inc;
+		if (lane == 0) wc[wid] = __popc(m);
+		__syncthreads();
+		uint32_t bc = 0, ba = 0, tc = 0, ta = 0;
+		for (int w = 0; w < 32; ++w) { if (w < wid) { bc += wc[w]; ba += wa[w]; } tc += wc[w]; ta += wa[w]; }
+		if (fin) {
+			const uint32_t k = base_c + bc + __popc(m & ((1u << lane) - 1u));
+			fin_r[k] = r; fin_aoff[k] = base_a + ba + inc - na;
+		}
+		__syncthreads();
+		if (tid == 0) { base_c += tc; base_a += ta; }
+		__syncthreads();
+	}
+	if (tid == 0) { counters[4] = base_c; counters[5] = base_a; }
+}
+
+// the listed chains as ra_chain_t + their anchors, contiguous; one warp per chain
+__global__ void __launch_bounds__(128)
+k_cigar_pack(const ReadState *__restrict__ st, Params P, const ChainRec *__restrict__ chains, const ra_anchor_t *__restrict__ anc_cur,
+             const uint64_t *__restrict__ seq_tab, const uint32_t *__restrict__ fin_r, const uint64_t *__restrict__ fin_aoff, uint32_t n_fin,
+             ra_chain_t *__restrict__ out_chain, ra_anchor_t *__restrict__ out_anc)
+{
+	const uint32_t k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+	const int lane = threadIdx.x & 31;
+	if (k >= n_fin) return;
+	const uint32_t r = fin_r[k];
+	const ChainRec c = chains[(size_t)r * P.cap_chains];
+	const uint64_t o = fin_aoff[k];
+	for (uint32_t a = lane; a < c.n_anchors; a += 32) out_anc[o + a] = anc_cur[c.anchor_off + a];
+	if (lane == 0) {
+		ra_chain_t ch;
+		ch.anchor_off = o; ch.n_anchors = c.n_anchors; ch.group = k; ch.read_off = st[r].ev_base;
+		ch.ref_off = seq_tab[3 * (size_t)c.ref + (c.strand == 1 ? 0 : 1)];
+		out_chain[k] = ch;
+	}
 }
 
 } // namespace mapk

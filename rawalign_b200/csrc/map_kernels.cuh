@@ -99,7 +99,7 @@ k_seed(const ReadState *__restrict__ st, const uint32_t *__restrict__ act, uint3
        const uint64_t *__restrict__ evoff, Params P, const Slot *__restrict__ slots, const ChainRec *__restrict__ chains,
        uint32_t *__restrict__ seeds_h, uint32_t *__restrict__ seeds_p, uint32_t *__restrict__ seed_cnt, uint64_t *__restrict__ seed_off,
        uint32_t *__restrict__ n_seed_out, uint32_t *__restrict__ seg_n /* anchors of the read this round */, uint32_t *__restrict__ seg_pad,
-       uint32_t *__restrict__ skip, unsigned long long *__restrict__ totals /* [0] seeds, [1] anchors */)
+       uint32_t *__restrict__ skip, unsigned long long *__restrict__ totals /* [0] seeds, [1] anchors, [2] longest padded segment */)
 {
 	extern __shared__ uint8_t sym[];                               // quantised symbols of the accepted events
 	const uint32_t i = blockIdx.x;
@@ -178,7 +178,7 @@ k_seed(const ReadState *__restrict__ st, const uint32_t *__restrict__ act, uint3
 		uint32_t pad = 1; while (pad < n) pad <<= 1;
 		if (n == 0) pad = 0;
 		n_seed_out[i] = n_seed; seg_n[i] = n; seg_pad[i] = pad; skip[i] = 0;
-		atomicAdd(totals, (unsigned long long)n_seed); atomicAdd(totals + 1, (unsigned long long)n);
+		atomicAdd(totals, (unsigned long long)n_seed); atomicAdd(totals + 1, (unsigned long long)n); atomicMax(totals + 2, (unsigned long long)pad);
 	}
 }
 

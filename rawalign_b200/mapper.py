@@ -94,7 +94,21 @@ class Index:
                                        n, out.ctypes.data, C.byref(st)))
         return out, st.as_dict()
 
-    def paf_lines(self, rec: np.ndarray, read_names: Optional[Sequence[str]] = None):
+    def last_cigar(self, n_reads: int):
+        """ra_map_last_cigar: (path_off[n_reads+1], path_i, path_j, path_diff) of the last map_reads call with RI_M_DTW_OUTPUT_CIGAR."""
+        off = np.zeros(n_reads + 1, np.uint64)
+        check(self._L.ra_map_last_cigar(self._h, n_reads, off.ctypes.data, None, None, None, 0))
+        tot = int(off[-1])
+        pi = np.zeros(max(tot, 1), np.uint64); pj = np.zeros(max(tot, 1), np.uint64); pd = np.zeros(max(tot, 1), np.float32)
+        check(self._L.ra_map_last_cigar(self._h, n_reads, off.ctypes.data, pi.ctypes.data, pj.ctypes.data, pd.ctypes.data, tot))
+        return off, pi[:tot], pj[:tot], pd[:tot]
+
+    @staticmethod
+    def aln_string(pi, pj, pd) -> str:
+        """dtwresult_to_string (rmap.cpp:580-592): operator<< of size_t, size_t, float (6 significant digits)."""
+        return "".join(f"({int(i)},{int(j)},{float(d):.6g})" for i, j, d in zip(pi, pj, pd))
+
+    def paf_lines(self, rec: np.ndarray, read_names: Optional[Sequence[str]] = None, cigar=None):
         """The PAF lines of rmap.cpp:954-972 with the tags of :730-758 / :764-790, minus mt:f: (std::to_string(float) = %f)."""
         out = []
         for r, o in enumerate(rec):
@@ -102,6 +116,10 @@ class Index:
             if o["mapped"]:
                 tags = (f"ci:i:{o['ci']}\tsl:i:{o['sl']}\tcm:i:{o['cm']}\tnc:i:{o['nc']}\ts1:f:{o['s1']:f}\ts2:f:{o['s2']:f}\tsm:f:{o['sm']:f}"
                         f"\tat:f:{o['at']:f}\taq:f:{o['aq']:f}")
+                if cigar is not None:                                  # rmap.cpp:741-744
+                    off, pi, pj, pd = cigar
+                    a, b = int(off[r]), int(off[r + 1])
+                    tags += f"\talns:f:{o['alns']:f}\taln:s:" + self.aln_string(pi[a:b], pj[a:b], pd[a:b])
                 fs = int(o["fragment_start_position"]); fl = int(o["fragment_length"])
                 rs = int(o["read_start_position"]); re_ = int(o["read_end_position"])
                 out.append(f"{nm}\t{o['read_length']}\t{rs}\t{re_}\t{'-' if o['rev'] else '+'}\t{self.names[int(o['ref_id'])]}\t{self.seq_len[int(o['ref_id'])]}"

@@ -127,3 +127,19 @@ def test_compiled_cpp_consumer_prints_the_reference_paf(mg, flat, tmp_path, ci, 
     assert r.returncode == 0, r.stderr[-2000:]
     got = [re.sub(r"mt:f:[0-9.eE+-]+\t", "", l) for l in r.stdout.splitlines()]
     assert got == str(mg["paf"][ci]).split("\n")
+
+
+def test_map_batch_cigar_vs_reference_golden(mg, flat):
+    """--dtw-output-cigar through the map loop: alns:f: and every (i,j,diff) triple of aln:s: equal the reference's."""
+    import rawalign_b200 as ra
+    off, sc = _dac(len(mg["raw_len"]))
+    n = len(mg["raw_len"])
+    with ra.Context(0) as ctx, ra.Index.load_flat(ctx, flat["sensitive"]) as ix:
+        rec, st = ix.map_reads(_opt(dict(flag=ra.RI_M_DTW_EVALUATE_CHAINS | ra.RI_M_DTW_OUTPUT_CIGAR)), raw=mg["raw"], raw_off=mg["raw_off"], raw_len=mg["raw_len"], offset=off, scale=sc)
+        cig = ix.last_cigar(n)
+        got = ix.paf_lines(rec, cigar=cig)
+    want = str(mg["paf_cigar"]).split("\n")
+    assert len(got) == len(want)
+    for r, (a, b) in enumerate(zip(got, want)):
+        assert a == b, (r, a[:300], b[:300])
+    assert int(cig[0][-1]) > 10000
