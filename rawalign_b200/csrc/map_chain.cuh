@@ -123,7 +123,7 @@ k_chain_pre(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const ui
 // tracebacks.  The running maximum only needs the listed anchors: every score is >= e, and the filter of :488-492 is applied
 // after the anchor's own score has entered the maximum.  Candidate chains go to cand[i * cap + k] in generation order, or
 // sorted by chaining score (stable, :512) when they are to be evaluated by DTW.
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 4)
 k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_base,
         const uint32_t *__restrict__ seg_n, const uint32_t *__restrict__ skip, float *__restrict__ score, uint32_t *__restrict__ pred,
         uint8_t *__restrict__ used, const uint32_t *__restrict__ nt, const uint32_t *__restrict__ n_nt, ra_anchor_t *__restrict__ anc_cur,
@@ -200,7 +200,21 @@ k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64
 				float cur = 0.0f;
 				if (valid && linkable(ct, cq, pt, pq, P)) cur = __fadd_rn(S[pi], (float)min(min(td, qd), P.e));   // :467-474 (S[pi] was stored by lane 0 before a __syncwarp)
 				const uint32_t valid_mask = __ballot_sync(0xffffffffu, valid);
-				if (__ballot_sync(0xffffffffu, cur > sc) == 0) {
+				const uint32_t beat_mask = __ballot_sync(0xffffffffu, cur > sc);
+				if (beat_mask != 0 && (beat_mask & (beat_mask - 1)) == 0) {
+					// exactly one lane t beats the score so far: it is the only improvement (-1), every other counting lane a skip (+1)
+					const int t = __ffs(beat_mask) - 1;
+					const int room = P.max_num_skips + 1 - num_skips;
+					const int before_t = __popc(valid_mask & ((1u << t) - 1u));
+					if (before_t >= room) { done = true; continue; }              // the scan ends before it reaches lane t (:482)
+					sc = __shfl_sync(0xffffffffu, cur, t); pr = __shfl_sync(0xffffffffu, pi, t);
+					num_skips += before_t - 1;
+					const int after_t = __popc(valid_mask >> t >> 1);
+					if (after_t >= P.max_num_skips + 1 - num_skips) done = true; else num_skips += after_t;
+					if (first_dead < 32) done = true;
+					continue;
+				}
+				if (beat_mask == 0) {
 					// nothing here beats the score so far: every lane that counts is a skip (:479-482)
 					const int room = P.max_num_skips + 1 - num_skips;             // the room-th skip from here ends the scan
 					const int have = __popc(valid_mask);
