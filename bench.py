@@ -604,8 +604,7 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
     # mini-batches runs: one batch's uploads and host round trips overlap the other's kernels.  Every step does all of its work.
     depth = max(1, int(os.environ.get("RA_BENCH_MAP_DEPTH", 2)))
     opt = ra.ri_mapopt_full(**cfg["opt"])
-    if opt.flag & 0x4:
-        raise SystemExit("C3 (--dtw-output-cigar) is not wired into ra_map_batch yet; the traceback kernels are measured by tools/microbench_dtw.py")
+    want_cigar = bool(opt.flag & 0x4)
     pipes = []
     t0 = time.time()
     for w in range(depth):
@@ -620,11 +619,19 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
             dist.barrier()
             torch.cuda.synchronize()
 
+    cig = {}
+
     def step_e2e(w=0):
-        return pipes[w][1].map_reads(opt, raw=raw_p, raw_off=off, raw_len=ln, offset=dac_off, scale=dac_scale)
+        r = pipes[w][1].map_reads(opt, raw=raw_p, raw_off=off, raw_len=ln, offset=dac_off, scale=dac_scale)
+        if want_cigar:
+            cig[w] = pipes[w][1].last_cigar(n_reads)             # the aln:s: triples come back to the host inside the timed region
+        return r
 
     def step_res(w=0, count=False):
-        return pipes[w][1].map_reads(opt, resident_reads=n_reads, count_cells=count)
+        r = pipes[w][1].map_reads(opt, resident_reads=n_reads, count_cells=count)
+        if want_cigar:
+            cig[w] = pipes[w][1].last_cigar(n_reads)
+        return r
 
     last = {}
 
@@ -679,7 +686,7 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
     reads_all, cells_all, issued_all, mapped_all = [float(x) for x in tot]
     out = None
     if rank == 0:
-        lines = ix.paf_lines(rec0)
+        lines = ix.paf_lines(rec0, cigar=cig.get(0) if want_cigar else None)
         out = {"metric": "reads_per_s", "value": reads_all * args.steps / dt, "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                "config": {"workload": cfg["desc"] + "; the whole map loop per read batch (ra_map_batch: decode, event detection, seeding, index lookup, "
@@ -694,7 +701,8 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
                "batches_in_flight_per_gpu": depth,
                "map_counts_per_step": {k: stc[k] for k in ("rounds", "chunks", "events", "seeds", "anchors", "chains_evaluated", "launches")},
                "e2e": {"value": reads_all * args.steps / dt_e2e, "unit": "reads/s", "ms_per_step": dt_e2e / args.steps * 1e3,
-                       "h2d_bytes_per_step": int(raw.nbytes + off.nbytes + ln.nbytes + dac_off.nbytes + dac_scale.nbytes), "d2h_bytes_per_step": int(rec0.nbytes),
+                       "h2d_bytes_per_step": int(raw.nbytes + off.nbytes + ln.nbytes + dac_off.nbytes + dac_scale.nbytes),
+                       "d2h_bytes_per_step": int(rec0.nbytes + (20 * len(cig[0][1]) + cig[0][0].nbytes if want_cigar else 0)),
                        "input": "int16 DAC samples of the whole reads in pinned host memory -> ra_map_batch -> one 88-byte record per read",
                        "records_equal_resident_path": bool(rec_e.tobytes() == rec.tobytes() == rec0.tobytes())},
                "gpu_launches": int(launches), "clocks": clocks, "paf_digest": digest(lines)}

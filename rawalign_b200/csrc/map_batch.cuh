@@ -186,7 +186,7 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 		MAP_CUDA(cudaStreamSynchronize(S));
 		const uint64_t total_pad = h64[0];
 		stt.seeds += h64[1]; stt.anchors += h64[2];
-		const uint64_t max_pad = h64[3];
+		const uint64_t max_n = h64[3];                                 // longest anchor segment of the round
 		stt.seed_ms += clk.lap();
 		// ---- anchors, sort, chaining -------------------------------------------------------------------------------------
 		const uint64_t an = std::max<uint64_t>(total_pad, 1);
@@ -199,17 +199,23 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 		k_advance_offset<<<(n_act + 127) / 128, 128, 0, S>>>(st, ix->act.as<uint32_t>(), n_act, ix->evoff_round.as<uint64_t>(), skip);
 		if (!ix->sort_attr) {
 			MAP_CUDA(cudaFuncSetAttribute(k_sort_segments, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kSortSmem * 8)));
-			MAP_CUDA(cudaFuncSetAttribute(k_sort_buckets, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BucketSmem)));
+			MAP_CUDA(cudaFuncSetAttribute(k_sort_buckets<kBucketMaxKeys, 0u>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BucketSmemT<kBucketMaxKeys>)));
+			MAP_CUDA(cudaFuncSetAttribute(k_sort_buckets<kBucketMaxKeysL, kBucketMaxKeys>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BucketSmemT<kBucketMaxKeysL>)));
 			ix->sort_attr = true;
 		}
-		uint32_t done_upto = 0;
+		uint32_t done_n = 0;
 		if (ix->n_bins && !getenv("RA_MAP_BITONIC_ONLY")) {            // bucket form for segments that fit shared memory, the bitonic network for the rest
-			k_sort_buckets<<<n_act, kBucketThreads, sizeof(BucketSmem), S>>>(ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), ix->seg_n.as<uint32_t>(), seg_pad, skip, n_act,
-			                                                              ix->bin_base.as<uint32_t>(), ix->tshift, ix->n_bins);
-			done_upto = kBucketMaxKeys; ++launches;
+			k_sort_buckets<kBucketMaxKeys, 0u><<<n_act, kBucketThreads, sizeof(BucketSmemT<kBucketMaxKeys>), S>>>(
+			    ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), ix->seg_n.as<uint32_t>(), seg_pad, skip, n_act, ix->bin_base.as<uint32_t>(), ix->tshift, ix->n_bins);
+			done_n = kBucketMaxKeys; ++launches;
+			if (max_n > kBucketMaxKeys) {                           // segments of 8193 .. 20480 anchors: same algorithm, one CTA per SM
+				k_sort_buckets<kBucketMaxKeysL, kBucketMaxKeys><<<n_act, kBucketThreads, sizeof(BucketSmemT<kBucketMaxKeysL>), S>>>(
+				    ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), ix->seg_n.as<uint32_t>(), seg_pad, skip, n_act, ix->bin_base.as<uint32_t>(), ix->tshift, ix->n_bins);
+				done_n = kBucketMaxKeysL; ++launches;
+			}
 		}
-		if (max_pad > done_upto)
-			k_sort_segments<<<n_act, kSortThreads, kSortSmem * 8, S>>>(ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), seg_pad, skip, n_act, done_upto);
+		if (max_n > done_n)
+			k_sort_segments<<<n_act, kSortThreads, kSortSmem * 8, S>>>(ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), seg_pad, skip, n_act, ix->seg_n.as<uint32_t>(), done_n);
 		launches += 3;
 		MAP_CUDA(cudaStreamSynchronize(S));
 		stt.sort_ms += clk.lap();

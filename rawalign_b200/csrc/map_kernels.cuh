@@ -99,7 +99,7 @@ k_seed(const ReadState *__restrict__ st, const uint32_t *__restrict__ act, uint3
        const uint64_t *__restrict__ evoff, Params P, const Slot *__restrict__ slots, const ChainRec *__restrict__ chains,
        uint32_t *__restrict__ seeds_h, uint32_t *__restrict__ seeds_p, uint32_t *__restrict__ seed_cnt, uint64_t *__restrict__ seed_off,
        uint32_t *__restrict__ n_seed_out, uint32_t *__restrict__ seg_n /* anchors of the read this round */, uint32_t *__restrict__ seg_pad,
-       uint32_t *__restrict__ skip, unsigned long long *__restrict__ totals /* [0] seeds, [1] anchors, [2] longest padded segment */)
+       uint32_t *__restrict__ skip, unsigned long long *__restrict__ totals /* [0] seeds, [1] anchors, [2] longest segment */)
 {
 	extern __shared__ uint8_t sym[];                               // quantised symbols of the accepted events
 	const uint32_t i = blockIdx.x;
@@ -178,7 +178,7 @@ k_seed(const ReadState *__restrict__ st, const uint32_t *__restrict__ act, uint3
 		uint32_t pad = 1; while (pad < n) pad <<= 1;
 		if (n == 0) pad = 0;
 		n_seed_out[i] = n_seed; seg_n[i] = n; seg_pad[i] = pad; skip[i] = 0;
-		atomicAdd(totals, (unsigned long long)n_seed); atomicAdd(totals + 1, (unsigned long long)n); atomicMax(totals + 2, (unsigned long long)pad);
+		atomicAdd(totals, (unsigned long long)n_seed); atomicAdd(totals + 1, (unsigned long long)n); atomicMax(totals + 2, (unsigned long long)n);
 	}
 }
 
@@ -260,13 +260,13 @@ constexpr uint32_t kSortSmem = 16384;                              // keys stage
 constexpr int kSortThreads = 1024;
 __global__ void __launch_bounds__(kSortThreads)
 k_sort_segments(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_base, const uint32_t *__restrict__ seg_pad,
-                const uint32_t *__restrict__ skip, uint32_t n_act, uint32_t done_upto /* segments up to this padded size were sorted by k_sort_buckets */)
+                const uint32_t *__restrict__ skip, uint32_t n_act, const uint32_t *__restrict__ seg_n, uint32_t done_n /* segments of up to this many anchors were sorted by k_sort_buckets */)
 {
 	extern __shared__ uint64_t sk[];
 	const uint32_t i = blockIdx.x;
 	if (i >= n_act || skip[i]) return;
 	const uint32_t n = seg_pad[i];
-	if (n < 2 || n <= done_upto) return;
+	if (n < 2 || seg_n[i] <= done_n) return;
 	uint64_t *g = keys + seg_base[i];
 	const int tid = threadIdx.x;
 	const bool in_smem = n <= kSortSmem;
@@ -299,30 +299,34 @@ k_sort_segments(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_ba
 // keys per bin; the bins are then finished independently (insertion sort by one thread, or a warp-wide bitonic pass for the
 // rare crowded bin, e.g. the read's true locus).  O(n) work per read instead of the bitonic network's n log^2 n.
 constexpr uint32_t kBins = 4096;
-constexpr uint32_t kBucketMaxKeys = 8192;
+constexpr uint32_t kBucketMaxKeys = 8192;                          // the common size class: three CTAs per SM
+constexpr uint32_t kBucketMaxKeysL = 20480;                        // long segments (reads with several chunks of anchors): one CTA per SM
 constexpr int kBucketThreads = 512;
-struct BucketSmem {
-	uint64_t keys[kBucketMaxKeys];
+template <uint32_t MAXK>
+struct BucketSmemT {
+	uint64_t keys[MAXK];
 	uint32_t count[kBins + 1];
 	uint32_t cursor[kBins];
 	uint32_t warp_tot[kBucketThreads / 32];
 };
+using BucketSmem = BucketSmemT<kBucketMaxKeys>;
 
 __device__ __forceinline__ uint32_t key_bin(uint64_t k, const uint32_t *__restrict__ bin_base, uint32_t tshift)
 {
 	return bin_base[key_list(k)] + (key_target(k) >> tshift);
 }
 
+template <uint32_t MAXK, uint32_t MINPAD>
 __global__ void __launch_bounds__(kBucketThreads)
 k_sort_buckets(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_base, const uint32_t *__restrict__ seg_n, const uint32_t *__restrict__ seg_pad,
                const uint32_t *__restrict__ skip, uint32_t n_act, const uint32_t *__restrict__ bin_base, uint32_t tshift, uint32_t n_bins)
 {
 	extern __shared__ __align__(16) unsigned char bsm_raw[];
-	BucketSmem &sm = *reinterpret_cast<BucketSmem *>(bsm_raw);
+	BucketSmemT<MAXK> &sm = *reinterpret_cast<BucketSmemT<MAXK> *>(bsm_raw);
 	const uint32_t i = blockIdx.x;
 	if (i >= n_act || skip[i]) return;
 	const uint32_t n = seg_n[i];
-	if (n < 2 || seg_pad[i] > kBucketMaxKeys) return;             // long segments are left to k_sort_segments
+	if (n < 2 || n > MAXK || seg_pad[i] <= MINPAD) return;        // this instantiation's size class only; longer segments are left to k_sort_segments
 	uint64_t *g = keys + seg_base[i];
 	const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
 	for (uint32_t b = tid; b <= n_bins; b += kBucketThreads) sm.count[b] = 0;
