@@ -725,7 +725,7 @@ def reference_map_sample(ds, cfg, raw, off, ln, gpu_lines, nsub, n_reads, steps=
     rm = RefMap()
     idx = rm.index_load(ds.index_path)
     opt = rm.mapopt(**cfg["opt"])
-    end = int(off[nsub - 1]) + int(ln[nsub - 1])
+    end = int((off[:nsub].astype(np.int64) + ln[:nsub].astype(np.int64)).max())      # reads need not be laid out in order (C4 mixes sources)
     sig = ds.decode(raw[:end])
     rm.map_reads(idx, opt, sig, off[:min(nsub, 32)], ln[:min(nsub, 32)], n_threads=n_thr)      # warm-up
     best = None

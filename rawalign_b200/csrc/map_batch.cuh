@@ -206,13 +206,21 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 		uint32_t done_n = 0;
 		if (ix->n_bins && !getenv("RA_MAP_BITONIC_ONLY")) {            // bucket form for segments that fit shared memory, the bitonic network for the rest
 			k_sort_buckets<kBucketMaxKeys, 0u><<<n_act, kBucketThreads, sizeof(BucketSmemT<kBucketMaxKeys>), S>>>(
-			    ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), ix->seg_n.as<uint32_t>(), seg_pad, skip, n_act, ix->bin_base.as<uint32_t>(), ix->tshift, ix->n_bins);
-			done_n = kBucketMaxKeys; ++launches;
+			    ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), ix->seg_n.as<uint32_t>(), seg_pad, skip, n_act, ix->bin_base.as<uint32_t>(), ix->tshift, ix->n_bins, nullptr);
+			++launches;
 			if (max_n > kBucketMaxKeys) {                           // segments of 8193 .. 20480 anchors: same algorithm, one CTA per SM
 				k_sort_buckets<kBucketMaxKeysL, kBucketMaxKeys><<<n_act, kBucketThreads, sizeof(BucketSmemT<kBucketMaxKeysL>), S>>>(
-				    ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), ix->seg_n.as<uint32_t>(), seg_pad, skip, n_act, ix->bin_base.as<uint32_t>(), ix->tshift, ix->n_bins);
-				done_n = kBucketMaxKeysL; ++launches;
+				    ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), ix->seg_n.as<uint32_t>(), seg_pad, skip, n_act, ix->bin_base.as<uint32_t>(), ix->tshift, ix->n_bins, nullptr);
+				++launches;
 			}
+			if (max_n > kBucketMaxKeysL) {                          // longer still: the binned keys are staged in global memory
+				if ((rc = ix->stage.reserve(an * 8))) return rc;
+				k_sort_buckets<0u, kBucketMaxKeysL><<<n_act, kBucketThreads, sizeof(BucketSmemT<0u>), S>>>(
+				    ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), ix->seg_n.as<uint32_t>(), seg_pad, skip, n_act, ix->bin_base.as<uint32_t>(), ix->tshift, ix->n_bins,
+				    ix->stage.as<uint64_t>());
+				++launches;
+			}
+			done_n = 0xffffffffu;
 		}
 		if (max_n > done_n)
 			k_sort_segments<<<n_act, kSortThreads, kSortSmem * 8, S>>>(ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), seg_pad, skip, n_act, ix->seg_n.as<uint32_t>(), done_n);

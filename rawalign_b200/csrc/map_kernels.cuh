@@ -304,7 +304,7 @@ constexpr uint32_t kBucketMaxKeysL = 20480;                        // long segme
 constexpr int kBucketThreads = 512;
 template <uint32_t MAXK>
 struct BucketSmemT {
-	uint64_t keys[MAXK];
+	uint64_t keys[MAXK ? MAXK : 1];                                // MAXK == 0: the keys are staged in a global-memory arena instead
 	uint32_t count[kBins + 1];
 	uint32_t cursor[kBins];
 	uint32_t warp_tot[kBucketThreads / 32];
@@ -319,15 +319,17 @@ __device__ __forceinline__ uint32_t key_bin(uint64_t k, const uint32_t *__restri
 template <uint32_t MAXK, uint32_t MINPAD>
 __global__ void __launch_bounds__(kBucketThreads)
 k_sort_buckets(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_base, const uint32_t *__restrict__ seg_n, const uint32_t *__restrict__ seg_pad,
-               const uint32_t *__restrict__ skip, uint32_t n_act, const uint32_t *__restrict__ bin_base, uint32_t tshift, uint32_t n_bins)
+               const uint32_t *__restrict__ skip, uint32_t n_act, const uint32_t *__restrict__ bin_base, uint32_t tshift, uint32_t n_bins,
+               uint64_t *__restrict__ stage /* MAXK == 0 only: arena parallel to keys */)
 {
 	extern __shared__ __align__(16) unsigned char bsm_raw[];
 	BucketSmemT<MAXK> &sm = *reinterpret_cast<BucketSmemT<MAXK> *>(bsm_raw);
 	const uint32_t i = blockIdx.x;
 	if (i >= n_act || skip[i]) return;
 	const uint32_t n = seg_n[i];
-	if (n < 2 || n > MAXK || seg_pad[i] <= MINPAD) return;        // this instantiation's size class only; longer segments are left to k_sort_segments
+	if (n < 2 || (MAXK && n > MAXK) || n <= MINPAD) return;       // this instantiation's size class only (MINPAD < n <= MAXK; MAXK == 0: no upper limit)
 	uint64_t *g = keys + seg_base[i];
+	uint64_t *const wk = MAXK ? sm.keys : stage + seg_base[i];    // where the binned keys live while the bins are finished
 	const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
 	for (uint32_t b = tid; b <= n_bins; b += kBucketThreads) sm.count[b] = 0;
 	__syncthreads();
@@ -353,7 +355,7 @@ k_sort_buckets(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_bas
 	__syncthreads();
 	for (uint32_t k = tid; k < n; k += kBucketThreads) {
 		const uint64_t key = g[k];
-		sm.keys[atomicAdd(&sm.cursor[key_bin(key, bin_base, tshift)], 1u)] = key;
+		wk[atomicAdd(&sm.cursor[key_bin(key, bin_base, tshift)], 1u)] = key;
 	}
 	__syncthreads();
 	// finish the bins: small ones by one thread each, crowded ones by a whole warp afterwards
@@ -362,17 +364,17 @@ k_sort_buckets(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_bas
 		const uint32_t lo = sm.count[b], hi = sm.count[b + 1];
 		if (hi - lo < 2 || hi - lo > kSmall) continue;
 		for (uint32_t a = lo + 1; a < hi; ++a) {
-			const uint64_t x = sm.keys[a];
+			const uint64_t x = wk[a];
 			uint32_t c = a;
-			while (c > lo && sm.keys[c - 1] > x) { sm.keys[c] = sm.keys[c - 1]; --c; }
-			sm.keys[c] = x;
+			while (c > lo && wk[c - 1] > x) { wk[c] = wk[c - 1]; --c; }
+			wk[c] = x;
 		}
 	}
 	for (uint32_t b = wid; b < n_bins; b += kBucketThreads / 32) {   // warp-uniform loop
 		const uint32_t lo = sm.count[b], m = sm.count[b + 1] - lo;
 		if (m <= kSmall) continue;
 		uint32_t pad = 32; while (pad < m) pad <<= 1;
-		uint64_t *w = sm.keys + lo;
+		uint64_t *w = wk + lo;
 		// bitonic network in its all-ascending form (first step of every merge compares mirrored positions), over a virtual
 		// power-of-two range whose slots >= m hold +inf: every comparator moves the minimum to the lower index, so the
 		// virtual keys never move and only pairs of real keys are touched
@@ -394,7 +396,7 @@ k_sort_buckets(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_bas
 		}
 	}
 	__syncthreads();
-	for (uint32_t k = tid; k < n; k += kBucketThreads) g[k] = sm.keys[k];
+	for (uint32_t k = tid; k < n; k += kBucketThreads) g[k] = wk[k];
 }
 
 } // namespace mapk
