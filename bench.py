@@ -707,7 +707,7 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
                        "records_equal_resident_path": bool(rec_e.tobytes() == rec.tobytes() == rec0.tobytes())},
                "gpu_launches": int(launches), "clocks": clocks, "paf_digest": digest(lines)}
         if not args.no_cpu_baseline:
-            out["cpu_baseline"] = reference_map_sample(ds, cfg, raw, off, ln, lines, max(args.cpu_sample_reads, 256), n_reads)
+            out["cpu_baseline"] = reference_map_sample(ds, cfg, raw, off, ln, lines, max(args.cpu_sample_reads, 64 * (os.cpu_count() or 1)), n_reads, steps=2)
     for c, x in pipes:
         x.close(); c.close()
     return out
