@@ -594,7 +594,14 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
     from workload.mapbench import CONFIGS, Dataset, digest
     name = args.config
     cfg = CONFIGS[name]
-    ds = Dataset(name, log=log)
+    if world > 1:                                                 # rank 0 builds the reference and its index file, the others wait and find it cached
+        if rank == 0:
+            ds = Dataset(name, log=log)
+        dist.barrier()
+        if rank != 0:
+            ds = Dataset(name, log=log)
+    else:
+        ds = Dataset(name, log=log)
     n_reads = args.map_reads_per_gpu
     t0 = time.time()
     raw, off, ln, dac_off, dac_scale = ds.reads(n_reads, seed=2 + rank)

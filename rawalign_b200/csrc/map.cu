@@ -89,7 +89,7 @@ struct ra_index {
 	Buf raw16, rd_off, rd_len, rd_offset, rd_scale, sig, state, chains, chains_tmp, paf;
 	Buf act, coff, clen, ev_round, evoff_round, ev, seeds_h, seeds_p, seed_cnt, seed_off, n_seed, n_hits, seg_n, seg_base, counters;
 	Buf keys, score, pred, used, anc[2], cand, n_cand, cand_base, dtw_chains, group_first, dscore, dkeep, scan_tmp;
-	Buf lsig_keep, nt, n_nt, bin_base, stage, fin_r, fin_aoff, fin_chain, fin_anc;
+	Buf lsig_keep, nt, n_nt, ntf, cxf, bin_base, stage, fin_r, fin_aoff, fin_chain, fin_anc;
 	// --dtw-output-cigar results of the last ra_map_batch, host side: per read the range of its alignment in cig_i/j/d
 	std::vector<uint64_t> cig_start, cig_len, cig_i, cig_j; std::vector<float> cig_d;
 	uint32_t tshift = 0, n_bins = 0;                               // bin function of the bucket sort: bin_base[ref << 1 | strand] + (target >> tshift)
@@ -257,7 +257,7 @@ void ra_index_destroy(ra_index *ix)
 	               &ix->chains_tmp, &ix->paf, &ix->act, &ix->coff, &ix->clen, &ix->ev_round, &ix->evoff_round, &ix->ev, &ix->seeds_h, &ix->seeds_p,
 	               &ix->seed_cnt, &ix->seed_off, &ix->n_seed, &ix->n_hits, &ix->seg_n, &ix->seg_base, &ix->counters, &ix->keys, &ix->score, &ix->pred,
 	               &ix->used, &ix->anc[0], &ix->anc[1], &ix->cand, &ix->n_cand, &ix->cand_base, &ix->dtw_chains, &ix->group_first, &ix->dscore,
-	               &ix->dkeep, &ix->scan_tmp, &ix->lsig_keep, &ix->nt, &ix->n_nt, &ix->bin_base, &ix->stage, &ix->fin_r, &ix->fin_aoff, &ix->fin_chain, &ix->fin_anc };
+	               &ix->dkeep, &ix->scan_tmp, &ix->lsig_keep, &ix->nt, &ix->n_nt, &ix->ntf, &ix->cxf, &ix->bin_base, &ix->stage, &ix->fin_r, &ix->fin_aoff, &ix->fin_chain, &ix->fin_anc };
 	for (Buf *b : all) b->release();
 	if (ix->pin) cudaFreeHost(ix->pin);
 	if (ix->stream) cudaStreamDestroy(ix->stream);

@@ -190,7 +190,7 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 		stt.seed_ms += clk.lap();
 		// ---- anchors, sort, chaining -------------------------------------------------------------------------------------
 		const uint64_t an = std::max<uint64_t>(total_pad, 1);
-		if ((rc = ix->keys.reserve(an * 8)) || (rc = ix->score.reserve(an * 4)) || (rc = ix->pred.reserve(an * 4)) || (rc = ix->used.reserve(an)) || (rc = ix->nt.reserve(an * 4)) ||
+		if ((rc = ix->keys.reserve(an * 8)) || (rc = ix->score.reserve(an * 4)) || (rc = ix->pred.reserve(an * 4)) || (rc = ix->used.reserve(an)) || (rc = ix->nt.reserve(an * 4)) || (rc = ix->ntf.reserve(an)) || (rc = ix->cxf.reserve(an)) ||
 		    (rc = ix->anc[cur].reserve(an * sizeof(ra_anchor_t)))) return rc;
 		k_fill_anchors<<<n_act, 32, 0, S>>>(st, ix->act.as<uint32_t>(), n_act, ix->evoff_round.as<uint64_t>(), P, ix->chains.as<ChainRec>(),
 		                                    ix->anc[0].as<ra_anchor_t>(), ix->anc[1].as<ra_anchor_t>(), ix->anc[cur].as<ra_anchor_t>(), cur,
@@ -228,11 +228,14 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 		MAP_CUDA(cudaStreamSynchronize(S));
 		stt.sort_ms += clk.lap();
 		k_chain_pre<<<n_act, kPreThreads, 0, S>>>(ix->act.as<uint32_t>(), n_act, P, ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), ix->seg_n.as<uint32_t>(), skip,
-		                                                     ix->score.as<float>(), ix->pred.as<uint32_t>(), ix->used.as<uint8_t>(), ix->nt.as<uint32_t>(), ix->n_nt.as<uint32_t>());
+		                                                     ix->score.as<float>(), ix->pred.as<uint32_t>(), ix->used.as<uint8_t>(), ix->nt.as<uint32_t>(), ix->n_nt.as<uint32_t>(),
+		                                                     ix->ntf.as<uint8_t>());
+		k_chain_simple<<<n_act, kPreThreads, 0, S>>>(ix->act.as<uint32_t>(), n_act, P, ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), skip, ix->score.as<float>(),
+		                                             ix->pred.as<uint32_t>(), ix->nt.as<uint32_t>(), ix->n_nt.as<uint32_t>(), ix->ntf.as<uint8_t>(), ix->cxf.as<uint8_t>());
 		k_chain<<<(n_act * 32 + 127) / 128, 128, 0, S>>>(ix->act.as<uint32_t>(), n_act, P, ix->keys.as<uint64_t>(), ix->seg_base.as<uint64_t>(), ix->seg_n.as<uint32_t>(), skip,
 		                                                 ix->score.as<float>(), ix->pred.as<uint32_t>(), ix->used.as<uint8_t>(), ix->nt.as<uint32_t>(), ix->n_nt.as<uint32_t>(),
-		                                                 ix->anc[cur].as<ra_anchor_t>(), ix->cand.as<ChainRec>(), ix->n_cand.as<uint32_t>());
-		++launches;
+		                                                 ix->cxf.as<uint8_t>(), ix->anc[cur].as<ra_anchor_t>(), ix->cand.as<ChainRec>(), ix->n_cand.as<uint32_t>());
+		launches += 2;
 		MAP_CUDA(ra::launch_exclusive_scan_u32(ix->n_cand.as<uint32_t>(), ix->cand_base.as<uint64_t>(), n_act, S));
 		launches += 2;
 		MAP_CUDA(cudaMemcpyAsync(h64, ix->cand_base.as<uint64_t>() + n_act, 8, cudaMemcpyDeviceToHost, S));

@@ -55,7 +55,7 @@ constexpr int kPreThreads = 256;
 __global__ void __launch_bounds__(kPreThreads)
 k_chain_pre(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_base,
             const uint32_t *__restrict__ seg_n, const uint32_t *__restrict__ skip, float *__restrict__ score, uint32_t *__restrict__ pred,
-            uint8_t *__restrict__ used, uint32_t *__restrict__ nt, uint32_t *__restrict__ n_nt)
+            uint8_t *__restrict__ used, uint32_t *__restrict__ nt, uint32_t *__restrict__ n_nt, uint8_t *__restrict__ ntf)
 {
 	__shared__ uint32_t warp_cnt[kPreThreads / 32];
 	const uint32_t i = blockIdx.x;                                 // one CTA per read: 8 warps keep 8 scans in flight per read
@@ -95,6 +95,7 @@ k_chain_pre(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const ui
 			active = active && same && !brk && !link && looked <= P.max_num_skips && pj > 0;  // :482: the reference's scan has given up by then
 			pi = pj;
 		}
+		if (mine) ntf[base + a] = hit ? 1 : 0;
 		const uint32_t m = __ballot_sync(0xffffffffu, hit);        // ordered compaction of the tile's listed anchors
 		if (lane == 0) warp_cnt[wid] = __popc(m);
 		__syncthreads();
@@ -106,6 +107,60 @@ k_chain_pre(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const ui
 		__syncthreads();
 	}
 	if (tid == 0) n_nt[i] = cnt;
+}
+
+// Second parallel pass, one lane per LISTED anchor.  Most listed anchors are chance pairs: every linkable predecessor the
+// reference's scan reaches is itself an isolated anchor, whose score is known to be e.  For those the whole scan of
+// :452-484 -- strict-improvement rule, skip counter, cut-off -- is replayed here by the lane on its own (lock-step
+// predicated loop), and score / predecessor are final.  An anchor whose scan touches a linkable predecessor that is itself
+// listed depends on a score not known yet: it is marked complex (cx = 1) and left to the sequential pass.
+__global__ void __launch_bounds__(kPreThreads)
+k_chain_simple(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_base,
+               const uint32_t *__restrict__ skip, float *__restrict__ score, uint32_t *__restrict__ pred, const uint32_t *__restrict__ nt,
+               const uint32_t *__restrict__ n_nt, const uint8_t *__restrict__ ntf, uint8_t *__restrict__ cx)
+{
+	const uint32_t i = blockIdx.x;
+	const int tid = threadIdx.x;
+	if (i >= n_act || skip[i]) return;
+	const uint64_t base = seg_base[i];
+	const uint64_t *__restrict__ K = keys + base;
+	const uint8_t *__restrict__ F = ntf + base;
+	const uint32_t m_nt = n_nt[i];
+	const float fe = (float)P.e;
+	for (uint32_t j0 = 0; j0 < m_nt; j0 += kPreThreads) {
+		const uint32_t j = j0 + tid;
+		const bool mine = j < m_nt;
+		const uint32_t a = mine ? nt[base + j] : 0u;
+		const uint64_t kc = K[a];
+		const uint32_t list = key_list(kc);
+		const int32_t ct = (int32_t)key_target(kc), cq = (int32_t)key_query(kc);
+		float sc = fe; uint32_t pr = a;
+		int32_t skips = 0;
+		bool complex_ = false;
+		bool active = mine && a > 0;
+		uint32_t pi = a;
+		while (__any_sync(0xffffffffu, active)) {
+			const uint32_t pj = active ? pi - 1u : 0u;
+			const uint64_t kp = K[pj];
+			const int32_t pt = (int32_t)key_target(kp), pq = (int32_t)key_query(kp);
+			const bool same = key_list(kp) == list && a - pj <= (uint32_t)P.chaining_band_length;    // :446-448
+			const bool skipc = pq == cq || pt == ct;                                          // :455-456
+			const bool brk = !skipc && (pt + P.max_target_gap_length < ct);                   // :458
+			const bool consider = active && same && !skipc && !brk && (cq - pq) >= 0;         // :465
+			const bool link = consider && linkable(ct, cq, pt, pq, P);
+			if (link && F[pj]) complex_ = true;                                                // its score is not e and not known yet
+			const float cur = link ? __fadd_rn(fe, (float)min(min(ct - pt, cq - pq), P.e)) : 0.0f;   // :467-474 with score[pj] = e
+			const bool better = consider && cur > sc;                                          // :476
+			if (better) { sc = cur; pr = pj; }
+			skips += consider ? (better ? -1 : 1) : 0;                                         // :479-481
+			active = active && same && !brk && !complex_ && !(consider && !better && skips > P.max_num_skips) && pj > 0;   // :482
+			pi = pj;
+		}
+		if (mine) {
+			cx[base + j] = complex_ ? 1 : 0;
+			if (!complex_) { score[base + a] = sc; pred[base + a] = pr; }
+		}
+	}
 }
 
 // Chaining DP of gen_chains (rmap.cpp:427-507) for every (ref, strand) list of one read, in the reference's list order,
@@ -126,39 +181,41 @@ k_chain_pre(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const ui
 __global__ void __launch_bounds__(128, 4)
 k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_base,
         const uint32_t *__restrict__ seg_n, const uint32_t *__restrict__ skip, float *__restrict__ score, uint32_t *__restrict__ pred,
-        uint8_t *__restrict__ used, const uint32_t *__restrict__ nt, const uint32_t *__restrict__ n_nt, ra_anchor_t *__restrict__ anc_cur,
-        ChainRec *__restrict__ cand, uint32_t *__restrict__ n_cand)
+        uint8_t *__restrict__ used, const uint32_t *__restrict__ nt, const uint32_t *__restrict__ n_nt, const uint8_t *__restrict__ cx,
+        ra_anchor_t *__restrict__ anc_cur, ChainRec *__restrict__ cand, uint32_t *__restrict__ n_cand)
 {
 	const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
 	const int lane = threadIdx.x & 31;
 	if (i >= n_act) return;
 	if (skip[i]) { if (lane == 0) n_cand[i] = 0; return; }
 	const uint64_t base = seg_base[i];
-	const uint32_t n = seg_n[i];
 	const uint64_t *__restrict__ K = keys + base;
 	float *S = score + base;
 	uint32_t *__restrict__ Pd = pred + base;
 	uint8_t *__restrict__ U = used + base;
 	const uint32_t *__restrict__ NT = nt + base;
+	const uint8_t *__restrict__ CX = cx + base;
 	const uint32_t m_nt = n_nt[i];
 	ChainRec *out = cand + (size_t)i * P.cap_chains;
 	uint32_t nc = 0;                                               // lane 0 only
 	uint64_t wo = base;                                            // next free chain-anchor slot of this read (lane 0 only)
 	float max_chaining_score = 0.0f;                               // :428
 	const float fe = (float)P.e;
-	uint32_t j = 0;
-	// software pipeline over the listed anchors: the key of the next anchor and the keys of its first 32 predecessors are
-	// requested one anchor ahead, so that their (L2 / HBM) latency overlaps the prefix operations of the current anchor
-	uint32_t nt_reg = lane < m_nt ? NT[lane] : 0u;                 // NT[jb + lane] for the block of 32 list entries at jb
-	uint32_t jb = 0;
-	auto nt_at = [&](uint32_t jj) -> uint32_t {                    // jj in [jb, jb + 32)
-		return __shfl_sync(0xffffffffu, nt_reg, (int)(jj - jb));
+	// the listed anchors are taken 32 at a time: lane l holds entry jb + l (index, key, complex flag, and -- for the anchors
+	// k_chain_simple finished -- the final score); the walk below reads them with shuffles
+	uint32_t jb = 0, nt_reg = 0, cx_reg = 0; float s_reg = 0.0f; uint64_t k_reg = 0;
+	auto load_block = [&](uint32_t j0) {
+		jb = j0;
+		const bool in = jb + lane < m_nt;
+		nt_reg = in ? NT[jb + lane] : 0u; cx_reg = in ? (uint32_t)CX[jb + lane] : 0u;
+		k_reg = in ? K[nt_reg] : 0ull; s_reg = in ? S[nt_reg] : 0.0f;
 	};
-	uint64_t kc_pre = 0, kp_pre = 0;
-	if (m_nt) { const uint32_t a0 = nt_at(0); kc_pre = K[a0]; kp_pre = K[a0 > (uint32_t)lane ? a0 - 1u - (uint32_t)lane : 0u]; }
+	if (m_nt) load_block(0);
+	uint32_t j = 0;
 	while (j < m_nt) {
-		const uint32_t first = nt_at(j);
-		const uint32_t list = key_list(K[first]);
+		if (j - jb >= 32u) load_block(j);
+		const uint32_t first = __shfl_sync(0xffffffffu, nt_reg, (int)(j - jb));
+		const uint32_t list = key_list(__shfl_sync(0xffffffffu, k_reg, (int)(j - jb)));
 		uint32_t ls;                                               // first anchor of this (ref, strand) list: lower bound of the list id
 		{
 			uint32_t lo = 0, hi = first;
@@ -169,81 +226,78 @@ k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64
 #pragma unroll
 		for (int t = 0; t < kMaxBest; ++t) { cs[t] = 0.0f; ci[t] = 0u; }
 		for (; j < m_nt; ++j) {
-			const uint32_t ai = nt_at(j);
-			const uint64_t kc = kc_pre;
+			if (j - jb >= 32u) load_block(j);
+			const int sl = (int)(j - jb);
+			const uint32_t ai = __shfl_sync(0xffffffffu, nt_reg, sl);
+			const uint64_t kc = __shfl_sync(0xffffffffu, k_reg, sl);
 			if (key_list(kc) != list) break;
-			const uint64_t kp_first = kp_pre;
-			{   // request the next listed anchor's keys now
-				const uint32_t jn = j + 1;
-				if (jn < m_nt) {
-					if (jn - jb >= 32u) { jb = jn; nt_reg = jb + lane < m_nt ? NT[jb + lane] : 0u; }
-					const uint32_t an = nt_at(jn);
-					kc_pre = K[an]; kp_pre = K[an > (uint32_t)lane ? an - 1u - (uint32_t)lane : 0u];
-				}
-			}
-			float sc = fe; uint32_t pr = ai;                       // :442-443
-			const int32_t ct = (int32_t)key_target(kc), cq = (int32_t)key_query(kc);
-			uint32_t start = ls;
-			if (ai - ls > (uint32_t)P.chaining_band_length) start = ai - (uint32_t)P.chaining_band_length;   // :448
-			int32_t num_skips = 0;
-			bool done = false;
-			for (uint32_t top = ai; top > start && !done; top = top >= 32 ? top - 32 : 0) {
-				const bool inrange = top >= start + 1u + (uint32_t)lane;          // predecessor top-1-lane is still >= start
-				const uint32_t pi = inrange ? top - 1u - (uint32_t)lane : start;
-				const uint64_t kp = (top == ai && inrange) ? kp_first : K[pi];
-				const int32_t pt = (int32_t)key_target(kp), pq = (int32_t)key_query(kp);
-				const bool brk_t = inrange && (pt + P.max_target_gap_length < ct);              // :458
-				const uint32_t dead_mask = __ballot_sync(0xffffffffu, brk_t || !inrange);
-				const int first_dead = dead_mask ? __ffs(dead_mask) - 1 : 32;
-				const int32_t td = ct - pt, qd = cq - pq;
-				const bool valid = lane < first_dead && pq != cq && pt != ct && qd >= 0;     // :455-457, :465
-				float cur = 0.0f;
-				if (valid && linkable(ct, cq, pt, pq, P)) cur = __fadd_rn(S[pi], (float)min(min(td, qd), P.e));   // :467-474 (S[pi] was stored by lane 0 before a __syncwarp)
-				const uint32_t valid_mask = __ballot_sync(0xffffffffu, valid);
-				const uint32_t beat_mask = __ballot_sync(0xffffffffu, cur > sc);
-				if (beat_mask != 0 && (beat_mask & (beat_mask - 1)) == 0) {
-					// exactly one lane t beats the score so far: it is the only improvement (-1), every other counting lane a skip (+1)
-					const int t = __ffs(beat_mask) - 1;
-					const int room = P.max_num_skips + 1 - num_skips;
-					const int before_t = __popc(valid_mask & ((1u << t) - 1u));
-					if (before_t >= room) { done = true; continue; }              // the scan ends before it reaches lane t (:482)
-					sc = __shfl_sync(0xffffffffu, cur, t); pr = __shfl_sync(0xffffffffu, pi, t);
-					num_skips += before_t - 1;
-					const int after_t = __popc(valid_mask >> t >> 1);
-					if (after_t >= P.max_num_skips + 1 - num_skips) done = true; else num_skips += after_t;
-					if (first_dead < 32) done = true;
-					continue;
-				}
-				if (beat_mask == 0) {
-					// nothing here beats the score so far: every lane that counts is a skip (:479-482)
-					const int room = P.max_num_skips + 1 - num_skips;             // the room-th skip from here ends the scan
-					const int have = __popc(valid_mask);
-					if (have >= room) done = true; else num_skips += have;
-					if (first_dead < 32) done = true;
-					continue;
-				}
-				float pm = cur;                                    // inclusive prefix maximum (0 for the lanes that do not count)
+			float sc;
+			if (!__shfl_sync(0xffffffffu, cx_reg, sl)) sc = __shfl_sync(0xffffffffu, s_reg, sl);   // finished by k_chain_simple
+			else {
+				sc = fe; uint32_t pr = ai;                         // :442-443
+				const int32_t ct = (int32_t)key_target(kc), cq = (int32_t)key_query(kc);
+				uint32_t start = ls;
+				if (ai - ls > (uint32_t)P.chaining_band_length) start = ai - (uint32_t)P.chaining_band_length;   // :448
+				int32_t num_skips = 0;
+				bool done = false;
+				for (uint32_t top = ai; top > start && !done; top = top >= 32 ? top - 32 : 0) {
+					const bool inrange = top >= start + 1u + (uint32_t)lane;          // predecessor top-1-lane is still >= start
+					const uint32_t pi = inrange ? top - 1u - (uint32_t)lane : start;
+					const uint64_t kp = K[pi];
+					const int32_t pt = (int32_t)key_target(kp), pq = (int32_t)key_query(kp);
+					const bool brk_t = inrange && (pt + P.max_target_gap_length < ct);              // :458
+					const uint32_t dead_mask = __ballot_sync(0xffffffffu, brk_t || !inrange);
+					const int first_dead = dead_mask ? __ffs(dead_mask) - 1 : 32;
+					const int32_t td = ct - pt, qd = cq - pq;
+					const bool valid = lane < first_dead && pq != cq && pt != ct && qd >= 0;     // :455-457, :465
+					float cur = 0.0f;
+					if (valid && linkable(ct, cq, pt, pq, P)) cur = __fadd_rn(S[pi], (float)min(min(td, qd), P.e));   // :467-474 (stored by an earlier kernel, or by lane 0 before a __syncwarp)
+					const uint32_t valid_mask = __ballot_sync(0xffffffffu, valid);
+					const uint32_t beat_mask = __ballot_sync(0xffffffffu, cur > sc);
+					if (beat_mask != 0 && (beat_mask & (beat_mask - 1)) == 0) {
+						// exactly one lane t beats the score so far: it is the only improvement (-1), every other counting lane a skip (+1)
+						const int t = __ffs(beat_mask) - 1;
+						const int room = P.max_num_skips + 1 - num_skips;
+						const int before_t = __popc(valid_mask & ((1u << t) - 1u));
+						if (before_t >= room) { done = true; continue; }              // the scan ends before it reaches lane t (:482)
+						sc = __shfl_sync(0xffffffffu, cur, t); pr = __shfl_sync(0xffffffffu, pi, t);
+						num_skips += before_t - 1;
+						const int after_t = __popc(valid_mask >> t >> 1);
+						if (after_t >= P.max_num_skips + 1 - num_skips) done = true; else num_skips += after_t;
+						if (first_dead < 32) done = true;
+						continue;
+					}
+					if (beat_mask == 0) {
+						// nothing here beats the score so far: every lane that counts is a skip (:479-482)
+						const int room = P.max_num_skips + 1 - num_skips;             // the room-th skip from here ends the scan
+						const int have = __popc(valid_mask);
+						if (have >= room) done = true; else num_skips += have;
+						if (first_dead < 32) done = true;
+						continue;
+					}
+					float pm = cur;                                    // inclusive prefix maximum (0 for the lanes that do not count)
 #pragma unroll
-				for (int d = 1; d < 32; d <<= 1) { const float y = __shfl_up_sync(0xffffffffu, pm, d); if (lane >= d) pm = fmaxf(pm, y); }
-				float before = __shfl_up_sync(0xffffffffu, pm, 1);
-				before = fmaxf(lane ? before : 0.0f, sc);
-				const bool improve = valid && cur > before;        // :476
-				int32_t ps = valid ? (improve ? -1 : 1) : 0;       // :479-481
+					for (int d = 1; d < 32; d <<= 1) { const float y = __shfl_up_sync(0xffffffffu, pm, d); if (lane >= d) pm = fmaxf(pm, y); }
+					float before = __shfl_up_sync(0xffffffffu, pm, 1);
+					before = fmaxf(lane ? before : 0.0f, sc);
+					const bool improve = valid && cur > before;        // :476
+					int32_t ps = valid ? (improve ? -1 : 1) : 0;       // :479-481
 #pragma unroll
-				for (int d = 1; d < 32; d <<= 1) { const int32_t y = __shfl_up_sync(0xffffffffu, ps, d); if (lane >= d) ps += y; }
-				ps += num_skips;
-				const uint32_t brk_mask = __ballot_sync(0xffffffffu, valid && !improve && ps > P.max_num_skips);   // :482
-				const int last = brk_mask ? __ffs(brk_mask) - 1 : 31;
-				const uint32_t imp_mask = __ballot_sync(0xffffffffu, improve && lane <= last);
-				if (imp_mask) {
-					const int t = 31 - __clz(imp_mask);            // improvements grow along the lanes: the last one holds the maximum
-					sc = __shfl_sync(0xffffffffu, cur, t); pr = __shfl_sync(0xffffffffu, pi, t);
+					for (int d = 1; d < 32; d <<= 1) { const int32_t y = __shfl_up_sync(0xffffffffu, ps, d); if (lane >= d) ps += y; }
+					ps += num_skips;
+					const uint32_t brk_mask = __ballot_sync(0xffffffffu, valid && !improve && ps > P.max_num_skips);   // :482
+					const int last = brk_mask ? __ffs(brk_mask) - 1 : 31;
+					const uint32_t imp_mask = __ballot_sync(0xffffffffu, improve && lane <= last);
+					if (imp_mask) {
+						const int t = 31 - __clz(imp_mask);            // improvements grow along the lanes: the last one holds the maximum
+						sc = __shfl_sync(0xffffffffu, cur, t); pr = __shfl_sync(0xffffffffu, pi, t);
+					}
+					num_skips = __shfl_sync(0xffffffffu, ps, last);
+					done = brk_mask != 0 || first_dead < 32;
 				}
-				num_skips = __shfl_sync(0xffffffffu, ps, last);
-				done = brk_mask != 0 || first_dead < 32;
+				if (lane == 0) { S[ai] = sc; Pd[ai] = pr; }
+				__syncwarp();
 			}
-			if (lane == 0) { S[ai] = sc; Pd[ai] = pr; }
-			__syncwarp();
 			if (sc > max_chaining_score) max_chaining_score = sc;  // :485-487
 			if (P.no_filter || (sc >= P.min_chaining_score && sc > max_chaining_score / 2)) {   // :488-492
 				// keep the num_best_chains best by (score desc, index desc) (compare(), :175-179): ai only grows, so a tie goes in front
@@ -276,7 +330,6 @@ k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64
 		}
 		__syncwarp();
 	}
-	(void)n;
 	if (lane != 0) return;
 	if (P.dtw)                                                     // :512, insertion sort = libstdc++'s std::sort for <= 16 elements
 		for (uint32_t a = 1; a < nc; ++a) {

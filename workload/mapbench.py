@@ -59,16 +59,18 @@ class Dataset:
         if not os.path.exists(self.index_path):
             synth.write_fasta(self.fasta, self.seqs); synth.write_pore_model(self.model)
             rb = _ref_binary()
+            tmp_ind = self.index_path + f".{os.getpid()}.tmp"
             ok = False
             if rb:
-                r = subprocess.run([rb, "-x", cfg["preset"], "-t", str(os.cpu_count() or 4), "-p", self.model, "-d", self.index_path + ".tmp", self.fasta],
+                r = subprocess.run([rb, "-x", cfg["preset"], "-t", str(os.cpu_count() or 4), "-p", self.model, "-d", tmp_ind, self.fasta],
                                    capture_output=True, text=True)
-                ok = r.returncode == 0 and os.path.exists(self.index_path + ".tmp")
+                ok = r.returncode == 0 and os.path.exists(tmp_ind)
                 if ok:
-                    os.replace(self.index_path + ".tmp", self.index_path); self.index_by = "the reference's indexer (oracle/_ref/rawalign -d)"
+                    os.replace(tmp_ind, self.index_path); self.index_by = "the reference's indexer (oracle/_ref/rawalign -d)"
             if not ok:
                 from oracle import build_flat_index, write_index_file
-                write_index_file(self.index_path, build_flat_index(self.seqs, synth.pore_model_as_loaded(), cfg["preset"]))
+                write_index_file(tmp_ind, build_flat_index(self.seqs, synth.pore_model_as_loaded(), cfg["preset"]))
+                os.replace(tmp_ind, self.index_path)
                 self.index_by = "the pinned CPU restatement (oracle.build_flat_index)"
         log(f"[{name}] reference {sum(cfg['ref']) / 1e6:.1f} Mb in {len(self.seqs)} sequence(s); index {os.path.getsize(self.index_path) >> 20} MiB by {self.index_by} ({time.time() - t0:.1f}s)")
 
