@@ -107,6 +107,7 @@ struct ra_ctx {
 	DevBuf a_arena, b_arena, items, cost, counter, ring, order;
 	// chains
 	DevBuf anchors, chains, group_first, min_score, score, keep, cells, chain_ring;
+	DevBuf gl_chain_item, gl_item_cells;                           // global-border plan (chains_global.cu)
 	DevBuf sp_nparts, sp_ntiles, sp_pbase, sp_tbase, sp_tchain, sp_cost, sp_pcells, sp_best, sp_rest;   // sparse-border plan (chains_sparse.cu)
 	uint64_t resident_events = 0;      // events left on the device by the last ra_detect_events_batch
 	bool force_unfused_events = false; // test hook: run the five-kernel K1 v2 (also the path for windows > kFusedMaxWindow)
@@ -393,7 +394,7 @@ int dtw_dev(ra_ctx *ctx, const float *a_dev, const float *b_dev, const ra_dtw_it
 	std::vector<uint32_t> order(n_items);
 	for (uint32_t k = 0; k < n_items; ++k) order[start[slot[k]]++] = k;     // stable: input order within a class
 	if ((rc = ctx->order.reserve((size_t)n_items * sizeof(uint32_t)))) return rc;
-	if ((rc = ctx->counter.reserve(64))) return rc;
+	if ((rc = ctx->counter.reserve(256))) return rc;
 	RA_CUDA(cudaMemcpyAsync(ctx->order.p, order.data(), (size_t)n_items * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
 	ra::DtwLaunch L; memset(&L, 0, sizeof(L));
 	L.a_arena = a_dev; L.b_arena = b_dev; L.items = items_dev; L.cost = cost_dev;
@@ -470,6 +471,51 @@ int sparse_pipeline(ra_ctx *ctx, const ra::ChainLaunch &L, uint32_t n_chains, ui
 	return RA_OK;
 }
 
+// Global border on device-resident chains: per phase, the chains whose budget passes become DTW items (k_glob_prep), the items
+// visit the host only to be sorted into wavefront classes (dtw_dev), and k_glob_replay does the reference's serial arithmetic.
+int global_pipeline(ra_ctx *ctx, const ra::ChainLaunch &L, uint32_t n_chains)
+{
+	int rc;
+	if (n_chains == 0) return RA_OK;
+	if ((rc = ctx->items.reserve((size_t)n_chains * sizeof(ra_dtw_item_t)))) return rc;
+	if ((rc = ctx->cost.reserve((size_t)n_chains * sizeof(float)))) return rc;
+	if ((rc = ctx->gl_chain_item.reserve((size_t)n_chains * sizeof(int32_t)))) return rc;
+	if ((rc = ctx->sp_best.reserve((size_t)L.n_groups * sizeof(float)))) return rc;
+	if (L.cells && (rc = ctx->gl_item_cells.reserve((size_t)n_chains * 8))) return rc;
+	if (L.cells) RA_CUDA(cudaMemsetAsync(L.cells, 0, 2 * sizeof(uint64_t), ctx->stream));
+	RA_CUDA(cudaMemsetAsync(L.need_cap, 0, sizeof(uint32_t), ctx->stream));
+	uint32_t *n_items_dev = ctx->counter.as<uint32_t>() + 21;
+	uint64_t issued = 0;
+	const int first = (L.min_score_mode == 1) ? 1 : 0, last = (L.min_score_mode == 1) ? 2 : 0;
+	std::vector<ra_dtw_item_t> items;
+	std::vector<uint64_t> cells;
+	for (int phase = first; phase <= last; ++phase) {
+		RA_CUDA(ra::launch_glob_prep(L, phase, ctx->sp_best.as<float>(), ctx->items.as<ra_dtw_item_t>(), ctx->gl_chain_item.as<int32_t>(), n_items_dev, ctx->stream));
+		uint32_t n_items = 0;
+		RA_CUDA(cudaMemcpyAsync(&n_items, n_items_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+		RA_CUDA(cudaStreamSynchronize(ctx->stream));
+		ctx->launches += 1;
+		if (n_items) {
+			items.resize(n_items);
+			RA_CUDA(cudaMemcpyAsync(items.data(), ctx->items.p, (size_t)n_items * sizeof(ra_dtw_item_t), cudaMemcpyDeviceToHost, ctx->stream));
+			RA_CUDA(cudaStreamSynchronize(ctx->stream));
+			if (L.cells) {
+				cells.resize(n_items);
+				for (uint32_t k = 0; k < n_items; ++k) { cells[k] = ra_dtw_cells(items[k].a_len, items[k].b_len, items[k].band_radius); issued += cells[k]; }
+				RA_CUDA(cudaMemcpyAsync(ctx->gl_item_cells.p, cells.data(), (size_t)n_items * 8, cudaMemcpyHostToDevice, ctx->stream));
+			}
+			if ((rc = dtw_dev(ctx, L.read_arena, L.ref_arena, ctx->items.as<ra_dtw_item_t>(), items.data(), n_items, ctx->cost.as<float>()))) return rc;
+		}
+		RA_CUDA(ra::launch_glob_replay(L, phase, ctx->sp_best.as<float>(), ctx->gl_chain_item.as<int32_t>(), ctx->cost.as<float>(),
+		                               L.cells ? ctx->gl_item_cells.as<unsigned long long>() : nullptr, ctx->stream));
+		ctx->launches += 1;
+		RA_CUDA(cudaStreamSynchronize(ctx->stream));              // the next phase's items overwrite ctx->items / ctx->cost
+	}
+	if (L.cells) RA_CUDA(cudaMemcpyAsync(L.cells, &issued, sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
+	RA_CUDA(cudaStreamSynchronize(ctx->stream));
+	return RA_OK;
+}
+
 // Runs the chain kernel on device-resident inputs; retries once with a larger HBM ring when a part
 // was wider than the rings available.
 int chains_dev(ra_ctx *ctx, const float *read_dev, const float *ref_dev, const ra_anchor_t *anchors_dev,
@@ -482,7 +528,7 @@ int chains_dev(ra_ctx *ctx, const float *read_dev, const float *ref_dev, const r
 	if (o.dtw_border_constraint != RA_DTW_BORDER_CONSTRAINT_GLOBAL && o.dtw_border_constraint != RA_DTW_BORDER_CONSTRAINT_SPARSE)
 		return fail(RA_EUNSUP, "invalid border constraint (the reference exits at rmap.cpp:301-304)");
 	int rc;
-	if ((rc = ctx->counter.reserve(64))) return rc;
+	if ((rc = ctx->counter.reserve(256))) return rc;
 	if ((rc = ctx->cells.reserve(64))) return rc;
 	const size_t warps = (size_t)ctx->n_sm * ra::kChainCtasPerSm * 4;
 	uint32_t ring_cap = ctx->chain_ring.cap ? (uint32_t)(ctx->chain_ring.cap / (warps * 3 * sizeof(float))) : 0;
@@ -495,7 +541,7 @@ int chains_dev(ra_ctx *ctx, const float *read_dev, const float *ref_dev, const r
 		L.band_frac = o.dtw_band_radius_frac; L.match_bonus = o.dtw_match_bonus; L.min_dtw_score = o.dtw_min_score;
 		L.min_score_mode = min_score_mode; L.min_score = min_score_dev; L.score = score_dev; L.keep = keep_dev;
 		L.work_counter = ctx->counter.as<uint32_t>(); L.need_cap = ctx->counter.as<uint32_t>() + 4;
-		L.error = ctx->counter.as<uint32_t>() + 8; L.n_read = n_read; L.n_ref = n_ref;
+		L.error = ctx->counter.as<uint32_t>() + 20; L.n_read = n_read; L.n_ref = n_ref;
 		L.cells = cells_host ? ctx->cells.as<uint64_t>() : nullptr;      // cell counting is instrumentation: off unless asked for
 		L.ring_scratch = ring_cap ? ctx->chain_ring.as<float>() : nullptr; L.ring_cap = ring_cap;
 		RA_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
@@ -506,6 +552,8 @@ int chains_dev(ra_ctx *ctx, const float *read_dev, const float *ref_dev, const r
 		ctx->launches += 1;
 		if (o.dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_SPARSE) {
 			if ((rc = sparse_pipeline(ctx, L, n_chains, n_anchors))) return rc;
+		} else if (!ctx->force_generic_dtw) {
+			if ((rc = global_pipeline(ctx, L, n_chains))) return rc;
 		} else {
 			RA_CUDA(ra::launch_chain_eval(L, ctx->n_sm, ctx->stream));
 			ctx->launches += 1;
@@ -1038,7 +1086,7 @@ int ra_dtw_tb_batch(ra_ctx *ctx, const float *a_arena, uint64_t n_a, const float
 	if ((rc = ctx->out_i.reserve((size_t)slots * 4))) return rc;
 	if ((rc = ctx->out_j.reserve((size_t)slots * 4))) return rc;
 	if (path_diff && (rc = ctx->out_d.reserve((size_t)slots * 4))) return rc;
-	if ((rc = ctx->counter.reserve(64))) return rc;
+	if ((rc = ctx->counter.reserve(256))) return rc;
 	if (a_arena) RA_CUDA(cudaMemcpyAsync(ctx->a_arena.p, a_arena, (size_t)n_a * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
 	const float *a_dev = a_arena ? ctx->a_arena.as<float>() : ctx->ev_out.as<float>();
 	const float *b_dev = ctx->ref.as<float>();
@@ -1192,7 +1240,7 @@ int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
 	const bool in_order = laid_in_order && ctx->opt.dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_SPARSE;
 	const int n_slices = in_order ? (int)std::min<uint64_t>(kMaxSlices, std::max<uint64_t>(1, n_anchors / ctx->chain_slice_min_anchors)) : 1;   // >= 16 MB of anchors per slice by default
 	if (n_slices > 1) {
-		if ((rc = ctx->counter.reserve(64))) return rc;
+		if ((rc = ctx->counter.reserve(256))) return rc;
 		if ((rc = ctx->cells.reserve(64))) return rc;
 		if ((rc = ctx->pin_gf.reserve(gf.size() * sizeof(uint32_t)))) return rc;
 		memcpy(ctx->pin_gf.p, gf.data(), gf.size() * sizeof(uint32_t));
@@ -1225,7 +1273,7 @@ int ra_align_chains_batch(ra_ctx *ctx, const float *read_arena, uint64_t n_read,
 		L.band_frac = o.dtw_band_radius_frac; L.match_bonus = o.dtw_match_bonus; L.min_dtw_score = o.dtw_min_score;
 		L.min_score_mode = min_score_mode; L.min_score = ms_dev; L.score = ctx->score.as<float>(); L.keep = ctx->keep.as<uint8_t>();
 		L.work_counter = ctx->counter.as<uint32_t>(); L.need_cap = ctx->counter.as<uint32_t>() + 4;
-		L.error = ctx->counter.as<uint32_t>() + 8; L.n_read = nr; L.n_ref = nf;
+		L.error = ctx->counter.as<uint32_t>() + 20; L.n_read = nr; L.n_ref = nf;
 		RA_CUDA(cudaMemsetAsync(L.error, 0, sizeof(uint32_t), ctx->stream));
 		L.cells = want_cells ? ctx->cells.as<uint64_t>() : nullptr;
 		const size_t warps = (size_t)ctx->n_sm * ra::kChainCtasPerSm * 4;

@@ -114,6 +114,9 @@ struct ChainLaunch {
 // every anchor of every chain: anchors[0] is the chain end, positions do not increase along the array (rmap.cpp:456-465 makes
 // them strictly monotonic), the chain end stays inside the arenas.  One warp per chain.
 cudaError_t launch_validate_chains(const ChainLaunch &L, uint32_t k0, uint32_t k1, cudaStream_t s);
+// global border through the wavefront item kernels (chains_global.cu)
+cudaError_t launch_glob_prep(const ChainLaunch &L, int phase, const float *best, ra_dtw_item_t *items, int32_t *chain_item, uint32_t *n_items, cudaStream_t s);
+cudaError_t launch_glob_replay(const ChainLaunch &L, int phase, float *best, const int32_t *chain_item, const float *cost, const unsigned long long *item_cells, cudaStream_t s);
 constexpr int kChainCtasPerSm = 6;
 cudaError_t launch_chain_eval(const ChainLaunch &L, int n_sm, cudaStream_t s);
 // sparse border (chains_sparse.cu): flat part-cost kernel over tiles of 256 parts + replay kernel
