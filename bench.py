@@ -532,7 +532,8 @@ def hot_path(args, config, rank, world, local, torch, dist, dev, with_cpu=True):
                     "h2d_bytes_per_step": int(reads.raw.nbytes + 20 * args.reads_per_gpu + coff.nbytes + clen.nbytes + anchors.nbytes + chains.nbytes + gfirst.nbytes),
                     "d2h_bytes_per_step": int(4 * n_events + 8 * (n_chunks + 1) + 4 * args.reads_per_gpu + 5 * len(chains)),
                     "input": "int16 DAC samples, decoded on the device (ra_detect_events_raw_batch); copies sliced to overlap the kernels",
-                    "events_equal_resident_path": bool(e2e_out["n_ev"] == n_events and np.array_equal(e2e_out["ev"][:4096], ev_d[:4096].cpu().numpy()))},
+                    "events_equal_resident_path": bool(e2e_out["n_ev"] == n_events and np.array_equal(e2e_out["ev"][:n_events].view(np.uint32), ev_d[:n_events].cpu().numpy().view(np.uint32))),
+                    "scores_equal_resident_path": bool(np.array_equal(np.asarray(e2e_out["score"]).view(np.uint32), score_d.cpu().numpy().view(np.uint32)))},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"kernel": "K1 event detection (k_prefix_pipe + k_tstat_pipe + k_fsm_pipe + k_exclusive_scan_u32 + k_finish_pipe, eight chunk groups on concurrent streams)",

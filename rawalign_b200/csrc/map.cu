@@ -91,7 +91,9 @@ struct ra_index {
 	Buf keys, score, pred, used, anc[2], cand, n_cand, cand_base, dtw_chains, group_first, dscore, dkeep, scan_tmp;
 	Buf lsig_keep, nt, n_nt, ntf, cxf, bin_base, stage, fin_r, fin_aoff, fin_chain, fin_anc;
 	// --dtw-output-cigar results of the last ra_map_batch, host side: per read the range of its alignment in cig_i/j/d
-	std::vector<uint64_t> cig_start, cig_len, cig_i, cig_j; std::vector<float> cig_d;
+	struct CigRound { std::vector<uint64_t> pi, pj; std::vector<float> pd; };
+	std::vector<CigRound> cig_rounds;                              // one per chunk round that finished mapped reads (moved in, not copied)
+	std::vector<uint64_t> cig_start, cig_len; std::vector<uint32_t> cig_round;
 	uint32_t tshift = 0, n_bins = 0;                               // bin function of the bucket sort: bin_base[ref << 1 | strand] + (target >> tshift)
 	std::vector<uint64_t> last_off; std::vector<uint32_t> last_len; bool last_raw = false;   // the batch left on the device by the last ra_map_batch
 	void *pin = nullptr; size_t pin_cap = 0;

@@ -59,7 +59,7 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 	if (cigar && opt->dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_GLOBAL && opt->dtw_fill_method == RA_DTW_FILL_METHOD_BANDED)
 		return ra__fail(RA_EUNSUP, "global border + banded fill + cigar is not implemented by the reference (rmap.cpp:223-225 asserts)");
 	std::vector<std::pair<uint32_t, float>> cig_alns;
-	ix->cig_start.assign(n_reads, 0); ix->cig_len.assign(n_reads, 0); ix->cig_i.clear(); ix->cig_j.clear(); ix->cig_d.clear();
+	ix->cig_start.assign(n_reads, 0); ix->cig_len.assign(n_reads, 0); ix->cig_round.assign(n_reads, 0); ix->cig_rounds.clear();
 	int rc;
 	{   // hot-path options of the context follow the map options; fp_contract / test hooks stay as the context has them
 		ra_mapopt_t o; if ((rc = ra_get_opt(ctx, &o))) return rc;
@@ -293,14 +293,14 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 				lib_launches += ra_launch_count(ctx) - lc;
 				ra__swap_resident(ctx, &evp, &evn);
 				if (rc) return rc;
+				const uint32_t round_slot = (uint32_t)ix->cig_rounds.size();
 				for (uint32_t k = 0; k < n_fin; ++k) {
 					const uint32_t r = fr[k];
-					ix->cig_start[r] = ix->cig_i.size(); ix->cig_len[r] = poff[k + 1] - poff[k];
-					ix->cig_i.insert(ix->cig_i.end(), pi.begin() + poff[k], pi.begin() + poff[k + 1]);
-					ix->cig_j.insert(ix->cig_j.end(), pj.begin() + poff[k], pj.begin() + poff[k + 1]);
-					ix->cig_d.insert(ix->cig_d.end(), pd.begin() + poff[k], pd.begin() + poff[k + 1]);
+					ix->cig_round[r] = round_slot; ix->cig_start[r] = poff[k]; ix->cig_len[r] = poff[k + 1] - poff[k];
 					cig_alns.push_back({r, sc[k]});
 				}
+				ix->cig_rounds.emplace_back();
+				ix->cig_rounds.back().pi = std::move(pi); ix->cig_rounds.back().pj = std::move(pj); ix->cig_rounds.back().pd = std::move(pd);
 			}
 			stt.select_ms += clk.lap();
 		}
@@ -326,10 +326,13 @@ extern "C" int ra_map_last_cigar(ra_index *ix, uint32_t n_reads, uint64_t *path_
 	path_off[n_reads] = w;
 	if (!path_i) return RA_OK;                                      // sizing call
 	if (w > cap) return ra__fail(RA_EINVAL, "path capacity %llu < %llu", (unsigned long long)cap, (unsigned long long)w);
-	for (uint32_t r = 0; r < n_reads; ++r)
-		for (uint64_t t = 0; t < ix->cig_len[r]; ++t) {
-			path_i[path_off[r] + t] = ix->cig_i[ix->cig_start[r] + t]; path_j[path_off[r] + t] = ix->cig_j[ix->cig_start[r] + t];
-			if (path_diff) path_diff[path_off[r] + t] = ix->cig_d[ix->cig_start[r] + t];
-		}
+	for (uint32_t r = 0; r < n_reads; ++r) {
+		const uint64_t len = ix->cig_len[r];
+		if (!len) continue;
+		const ra_index::CigRound &c = ix->cig_rounds[ix->cig_round[r]];
+		memcpy(path_i + path_off[r], c.pi.data() + ix->cig_start[r], len * 8);
+		memcpy(path_j + path_off[r], c.pj.data() + ix->cig_start[r], len * 8);
+		if (path_diff) memcpy(path_diff + path_off[r], c.pd.data() + ix->cig_start[r], len * 4);
+	}
 	return RA_OK;
 }

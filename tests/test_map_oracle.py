@@ -114,3 +114,20 @@ def test_map_loop_live_differential(tmp_path):
         for a, b in zip(got, paf):
             assert a == strip_mt(b)
         rm.index_free(idx)
+
+
+def test_mapbench_dataset_index_matches_the_restatement(tmp_path):
+    """workload/mapbench.py (bench.py's dataset builder): the index file it leaves -- written by the reference's own indexer where
+    oracle/_ref/rawalign exists, else from the restatement -- parses to the table oracle.build_flat_index gives for the same
+    sequences, and the simulated reads are laid out as the C ABI expects."""
+    from oracle import parse_index_file
+    from workload import synth
+    from workload.mapbench import CONFIGS, Dataset
+    ds = Dataset("C1", workdir=str(tmp_path))
+    ix = parse_index_file(ds.index_path)
+    flat = build_flat_index(ds.seqs, synth.pore_model_as_loaded(), CONFIGS["C1"]["preset"])
+    assert np.array_equal(ix["keys"], flat["keys"]) and np.array_equal(ix["key_off"], flat["key_off"]) and np.array_equal(ix["vals"], flat["vals"])
+    raw, off, ln, dac_off, dac_scale = ds.reads(16, seed=3)
+    assert raw.dtype == np.int16 and len(off) == len(ln) == 16 and int((off.astype(np.int64) + ln).max()) <= len(raw)
+    sig = ds.decode(raw)
+    assert sig[int(off[0]):int(off[0]) + int(ln[0])].min() > 30.0 and sig[int(off[0]):int(off[0]) + int(ln[0])].max() < 200.0
