@@ -610,7 +610,7 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
     raw_p = torch.from_numpy(raw).pin_memory().numpy()            # the e2e path copies from pinned host memory every step
     # MAP_DEPTH batches in flight per GPU (one context + index each, one host thread each), as a map loop with double-buffered
     # mini-batches runs: one batch's uploads and host round trips overlap the other's kernels.  Every step does all of its work.
-    depth = max(1, int(os.environ.get("RA_BENCH_MAP_DEPTH", 2)))
+    depth = max(1, int(os.environ.get("RA_BENCH_MAP_DEPTH", 3)))
     opt = ra.ri_mapopt_full(**cfg["opt"])
     want_cigar = bool(opt.flag & 0x4)
     pipes = []
@@ -705,7 +705,7 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
                "reads_mapped_frac": mapped_all / reads_all,
                "dtw_cells_per_step": {"useful": cells_all, "issued": issued_all},
                "hot_path_gcups": cells_all * args.steps / dt / 1e9,
-               "map_stages_ms": dict({k: v / args.steps for k, v in sorted(stage_acc.items())}, note="one step run alone (host-observed, between synchronisations); the timed steps overlap two batches"),
+               "map_stages_ms": dict({k: v / args.steps for k, v in sorted(stage_acc.items())}, note="one step run alone (host-observed, between synchronisations); the timed steps overlap the batches in flight"),
                "batches_in_flight_per_gpu": depth,
                "map_counts_per_step": {k: stc[k] for k in ("rounds", "chunks", "events", "seeds", "anchors", "chains_evaluated", "launches")},
                "e2e": {"value": reads_all * args.steps / dt_e2e, "unit": "reads/s", "ms_per_step": dt_e2e / args.steps * 1e3,
