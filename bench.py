@@ -615,9 +615,12 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
     want_cigar = bool(opt.flag & 0x4)
     pipes = []
     t0 = time.time()
+    from rawalign_b200.shard import broadcast_index
     for w in range(depth):
         c = ra.Context(local)
-        pipes.append((c, ra.Index.load_file(c, ds.index_path)))
+        # rank 0 parses the reference's index file; the other ranks receive the device tables (hash slots, positions, reference
+        # signals) by NCCL broadcast -- the one collective of the path, at load
+        pipes.append((c, broadcast_index(c, ds.index_path, rank, dev)))
     t_index = (time.time() - t0) / depth
     ctx, ix = pipes[0]
 
@@ -700,7 +703,7 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
                "config": {"workload": cfg["desc"] + "; the whole map loop per read batch (ra_map_batch: decode, event detection, seeding, index lookup, "
                                       "chaining, chain DTW, primary chains, MAPQ, early stop), one step = one batch",
                           "reads_per_gpu": n_reads, "reference_bases": int(sum(cfg["ref"])), "n_sequences": len(cfg["ref"]), "preset": cfg["preset"],
-                          "note": cfg.get("note", ""), "index": f"reference index file format, built by {ds.index_by}, loaded by ra_index_load_file in {t_index:.2f}s",
+                          "note": cfg.get("note", ""), "index": f"reference index file format, built by {ds.index_by}, loaded by ra_index_load_file on rank 0" + (" and replicated by NCCL broadcast" if world > 1 else "") + f" in {t_index:.2f}s per context",
                           "l2_policy": "inputs larger than L2 (signal batch >> 126 MB)", "cpu_binding": binding},
                "reads_mapped_frac": mapped_all / reads_all,
                "dtw_cells_per_step": {"useful": cells_all, "issued": issued_all},

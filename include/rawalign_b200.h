@@ -288,6 +288,13 @@ void ra_index_destroy(ra_index *ix);
 /* out[0..8] = w, e, n, q, lq, k, n_seq, n_keys (low 32 bits), n_vals (low 32 bits); seq_len_out (optional) n_seq entries */
 int ra_index_info(const ra_index *ix, int32_t *out, uint32_t *seq_len_out);
 
+/* Replication across the GPUs of a box (index and reference signals replicated, one broadcast at load): rank 0
+ * loads the index; ra_index_tables gives the device pointers / byte sizes of its three tables {hash slots, positions, reference
+ * mirror}; the other ranks call ra_index_alloc with rank 0's ra_index_info values, key / position counts and sequence lengths,
+ * and receive the three tables into their own ra_index_tables pointers (ncclBroadcast; rawalign_b200/shard.py does it). */
+int ra_index_tables(ra_index *ix, void **ptrs /* 3 */, uint64_t *bytes /* 3 */);
+int ra_index_alloc(ra_ctx *ctx, const int32_t *info /* 9, as ra_index_info */, uint64_t n_keys, uint64_t n_vals, const uint32_t *seq_len, ra_index **out);
+
 /* The numbers behind one PAF line (rmap.cpp:730-758, :954-972); the caller formats them (mt:f:, the per-read wall time, has no
  * per-read meaning in a batch). */
 typedef struct ra_paf_s {

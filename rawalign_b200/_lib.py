@@ -114,6 +114,8 @@ def load() -> C.CDLL:
     L.ra_index_info.argtypes = [vp, C.POINTER(C.c_int32), vp]
     L.ra_map_batch.argtypes = [vp, vp, C.POINTER(RiMapOpt), vp, vp, vp, vp, vp, vp, vp, vp, u32, vp, C.POINTER(MapStats)]
     L.ra_map_last_cigar.argtypes = [vp, u32, vp, vp, vp, vp, u64]
+    L.ra_index_tables.argtypes = [vp, vp, vp]; L.ra_index_tables.restype = C.c_int
+    L.ra_index_alloc.argtypes = [vp, C.POINTER(C.c_int32), u64, u64, vp, C.POINTER(vp)]; L.ra_index_alloc.restype = C.c_int
     for name in ("ra_get_opt", "ra_index_load_file", "ra_index_load_flat", "ra_index_info", "ra_map_batch", "ra_map_last_cigar"):
         getattr(L, name).restype = C.c_int
     for name in ("ra_init", "ra_set_opt", "ra_last_timing", "ra_ref_load", "ra_ref_load_flat", "ra_ref_device", "ra_ref_alloc",
@@ -135,5 +137,5 @@ EXPORTED_SYMBOLS = [
     "ra_detect_events_batch", "ra_detect_events_batch_dev", "ra_detect_events_raw_batch", "ra_last_event_positions",
     "ra_dtw_batch", "ra_dtw_batch_dev", "ra_dtw_cells", "ra_dtw_tb_batch",
     "ra_align_chains_batch", "ra_align_chains_batch_dev", "ra_align_chains_cigar_batch",
-    "ra_get_opt", "ra_set_tuning", "ra_ri_mapopt_init", "ra_index_load_file", "ra_index_load_flat", "ra_index_destroy", "ra_index_info", "ra_map_batch", "ra_map_last_cigar",
+    "ra_get_opt", "ra_set_tuning", "ra_ri_mapopt_init", "ra_index_load_file", "ra_index_load_flat", "ra_index_destroy", "ra_index_info", "ra_map_batch", "ra_map_last_cigar", "ra_index_tables", "ra_index_alloc",
 ]

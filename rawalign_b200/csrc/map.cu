@@ -112,8 +112,13 @@ int build_device_index(ra_ctx *ctx, ra_index *ix, const float *const *fwd, const
 {
 	if (ix->n_seq == 0 || ix->n_seq > kMaxSeq) return ra__fail(RA_EUNSUP, "%u reference sequences (supported: 1..%u)", ix->n_seq, kMaxSeq);
 	std::vector<uint64_t> arena_off(2 * (size_t)ix->n_seq);
-	int rc = ra_ref_load(ctx, ix->n_seq, fwd, rev, ix->seq_len.data(), arena_off.data());
-	if (rc) return rc;
+	int rc;
+	if (fwd) { if ((rc = ra_ref_load(ctx, ix->n_seq, fwd, rev, ix->seq_len.data(), arena_off.data()))) return rc; }
+	else {                                                         // replica: the same arena layout as ra_ref_load ([fwd(0) | rev(0) | fwd(1) | ...]), filled by broadcast
+		uint64_t o = 0;
+		for (uint32_t i = 0; i < ix->n_seq; ++i) { arena_off[2 * i] = o; o += ix->seq_len[i]; arena_off[2 * i + 1] = o; o += ix->seq_len[i]; }
+		if ((rc = ra_ref_alloc(ctx, o))) return rc;
+	}
 	std::vector<uint64_t> tab(3 * (size_t)ix->n_seq);
 	for (uint32_t i = 0; i < ix->n_seq; ++i) { tab[3 * i] = arena_off[2 * i]; tab[3 * i + 1] = arena_off[2 * i + 1]; tab[3 * i + 2] = ix->seq_len[i]; }
 	if ((rc = ix->seq_tab.reserve(tab.size() * 8))) return rc;
@@ -123,8 +128,8 @@ int build_device_index(ra_ctx *ctx, ra_index *ix, const float *const *fwd, const
 	if (bits > 31) return ra__fail(RA_EUNSUP, "index has too many distinct seeds (%llu)", (unsigned long long)ix->n_keys);
 	ix->slot_bits = bits;
 	const uint64_t n_slots = 1ull << bits;
-	std::vector<Slot> slots(n_slots, Slot{0, 0, 0});
-	for (uint64_t i = 0; i < ix->n_keys; ++i) {
+	std::vector<Slot> slots(keys ? n_slots : 0, Slot{0, 0, 0});
+	for (uint64_t i = 0; keys && i < ix->n_keys; ++i) {
 		if (keys[i] >> 32) return ra__fail(RA_EINVAL, "seed hash %llu does not fit 32 bits (rsketch.c masks hash64 to 32 bits)", (unsigned long long)keys[i]);
 		const uint32_t key = (uint32_t)keys[i];
 		uint64_t h = ((uint32_t)(key * 0x9E3779B1u)) >> (32 - bits);
@@ -132,9 +137,9 @@ int build_device_index(ra_ctx *ctx, ra_index *ix, const float *const *fwd, const
 		slots[h].key = key; slots[h].cnt = (uint32_t)(key_off[i + 1] - key_off[i]); slots[h].off = key_off[i];
 	}
 	if ((rc = ix->slots.reserve(n_slots * sizeof(Slot)))) return rc;
-	MAP_CUDA(cudaMemcpy(ix->slots.p, slots.data(), n_slots * sizeof(Slot), cudaMemcpyHostToDevice));
+	if (keys) MAP_CUDA(cudaMemcpy(ix->slots.p, slots.data(), n_slots * sizeof(Slot), cudaMemcpyHostToDevice));
 	if ((rc = ix->vals.reserve(std::max<uint64_t>(ix->n_vals, 1) * 8))) return rc;
-	if (ix->n_vals) MAP_CUDA(cudaMemcpy(ix->vals.p, vals, ix->n_vals * 8, cudaMemcpyHostToDevice));
+	if (vals && ix->n_vals) MAP_CUDA(cudaMemcpy(ix->vals.p, vals, ix->n_vals * 8, cudaMemcpyHostToDevice));
 	if (2ull * ix->n_seq <= 4096) {                                // bins of the anchor bucket sort (map_kernels.cuh, kBins): uniform over the concatenated reference
 		uint32_t ts = 0;
 		for (;; ++ts) {
@@ -265,6 +270,32 @@ void ra_index_destroy(ra_index *ix)
 	if (ix->stream) cudaStreamDestroy(ix->stream);
 	for (auto &e : ix->ev_t) if (e) cudaEventDestroy(e);
 	delete ix;
+}
+
+/* ---- replication across GPUs: rank 0 loads the index, the others allocate one of the same geometry and receive the tables --- */
+int ra_index_tables(ra_index *ix, void **ptrs, uint64_t *bytes)
+{
+	if (!ix || !ptrs || !bytes) return ra__fail(RA_EINVAL, "NULL argument");
+	float *ref = nullptr; uint64_t ref_n = 0;
+	int rc = ra_ref_device(ix->ctx, &ref, &ref_n);
+	if (rc) return rc;
+	ptrs[0] = ix->slots.p; bytes[0] = (1ull << ix->slot_bits) * sizeof(Slot);
+	ptrs[1] = ix->vals.p;  bytes[1] = ix->n_vals * 8;
+	ptrs[2] = ref;         bytes[2] = ref_n * 4;
+	return RA_OK;
+}
+
+int ra_index_alloc(ra_ctx *ctx, const int32_t *info /* the 9 values of ra_index_info */, uint64_t n_keys, uint64_t n_vals, const uint32_t *seq_len, ra_index **out)
+{
+	if (!ctx || !info || !seq_len || !out) return ra__fail(RA_EINVAL, "NULL argument");
+	ra_index *ix = new ra_index();
+	ix->ctx = ctx; ix->w = info[0]; ix->e = info[1]; ix->n = info[2]; ix->q = info[3]; ix->lq = info[4]; ix->k = info[5]; ix->n_seq = (uint32_t)info[6];
+	ix->n_keys = n_keys; ix->n_vals = n_vals;
+	ix->seq_len.assign(seq_len, seq_len + ix->n_seq);
+	int rc = build_device_index(ctx, ix, nullptr, nullptr, nullptr, nullptr, nullptr);     // geometry and tables of the right size, contents by broadcast
+	if (rc) { ra_index_destroy(ix); return rc; }
+	*out = ix;
+	return RA_OK;
 }
 
 int ra_index_info(const ra_index *ix, int32_t *out, uint32_t *seq_len_out)

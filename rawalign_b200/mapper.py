@@ -61,6 +61,26 @@ class Index:
                                              C.cast(fp, C.c_void_p), C.cast(rp, C.c_void_p), len(keys), keys.ctypes.data, ko.ctypes.data, vals.ctypes.data, C.byref(h)))
         return cls(ctx, h, tab.get("names"))
 
+    def tables(self):
+        """[(device pointer, bytes)] of the hash slots, the position array and the reference mirror (ra_index_tables)."""
+        ptrs = (C.c_void_p * 3)(); nb = (C.c_uint64 * 3)()
+        check(self._L.ra_index_tables(self._h, ptrs, nb))
+        return [(int(ptrs[i] or 0), int(nb[i])) for i in range(3)]
+
+    def counts(self):
+        info = (C.c_int32 * 9)()
+        check(self._L.ra_index_info(self._h, info, None))
+        return [int(x) for x in info]
+
+    @classmethod
+    def alloc_like(cls, ctx, info, n_keys, n_vals, seq_len, names=None) -> "Index":
+        """ra_index_alloc: an index of the same geometry whose tables are to be received by broadcast."""
+        h = C.c_void_p()
+        ia = (C.c_int32 * 9)(*info)
+        sl = np.ascontiguousarray(seq_len, np.uint32)
+        check(_lib.load().ra_index_alloc(ctx._h, ia, int(n_keys), int(n_vals), sl.ctypes.data, C.byref(h)))
+        return cls(ctx, h, names)
+
     def close(self):
         if getattr(self, "_h", None):
             self._L.ra_index_destroy(self._h); self._h = None

@@ -56,6 +56,41 @@ def broadcast_reference(ctx, ref_arena, rank: int, device=None) -> None:
     torch.cuda.synchronize(device)
 
 
+def broadcast_index(ctx, index_path, rank: int, device=None):
+    """Replicates the index: rank 0 parses the reference's index file (ra_index_load_file), every other rank allocates an index
+    of the same geometry and receives the three device tables -- hash slots, positions, reference signals -- by one broadcast
+    each over NCCL (NVLink / NVSwitch).  Returns the rank's Index.  World size 1 is a plain load."""
+    import torch
+    import torch.distributed as dist
+    from .mapper import Index
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    if world == 1:
+        return Index.load_file(ctx, index_path)
+    meta = [None]
+    ix = None
+    if rank == 0:
+        ix = Index.load_file(ctx, index_path)
+        meta = [dict(info=ix.counts(), seq_len=ix.seq_len.tolist(), names=ix.names, bytes=[b for _, b in ix.tables()])]
+    dist.broadcast_object_list(meta, 0)
+    m = meta[0]
+    if rank != 0:
+        # the replica needs the table geometry, not the exact key count: 16-byte slots, 2^bits >= 2 * n_keys + 16 of them
+        n_vals = m["bytes"][1] // 8
+        n_keys = (m["bytes"][0] // 16 - 16) // 2
+        ix = Index.alloc_like(ctx, m["info"], n_keys, n_vals, np.array(m["seq_len"], np.uint32), m["names"])
+        assert [b for _, b in ix.tables()] == m["bytes"], "replica geometry differs from rank 0's"
+    for ptr, nbytes in ix.tables():
+        if nbytes == 0:
+            continue
+
+        class _T:
+            __cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+        t = torch.as_tensor(_T(), device=device)
+        dist.broadcast(t, 0)
+    torch.cuda.synchronize(device)
+    return ix
+
+
 def merge_in_order(local_rows: list, my_range: Tuple[int, int], n_reads: int, dst: int = 0):
     """Gathers per-read results (any picklable rows, one per read of ``my_range``) on rank ``dst`` and returns the
     list of all ``n_reads`` rows in input order there (None elsewhere).  Host-side, after the GPU work."""

@@ -143,3 +143,40 @@ def test_map_batch_cigar_vs_reference_golden(mg, flat):
     for r, (a, b) in enumerate(zip(got, want)):
         assert a == b, (r, a[:300], b[:300])
     assert int(cig[0][-1]) > 10000
+
+
+def test_bitonic_sort_fallback_gives_the_same_paf():
+    """The anchor sort has two forms (bucket sort in shared memory; the bitonic network for segments beyond it, or when the
+    index has too many sequences for the bin table).  RA_MAP_BITONIC_ONLY=1 sends every segment through the network: the golden
+    PAF tests are re-run that way in a child process."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    e = dict(os.environ); e["RA_MAP_BITONIC_ONLY"] = "1"
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_gpu_map.py"), "-q", "-x", "-m", "gpu", "-k", "paf_vs_reference_golden",
+                        "-p", "no:cacheprovider"], env=e, cwd=root, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+def test_index_replica_by_copy(mg, flat, tmp_path):
+    """ra_index_alloc + ra_index_tables: a replica allocated from rank 0's geometry and filled by device-to-device copies of the
+    three tables (what the NCCL broadcast does across GPUs) maps to the same PAF."""
+    import torch
+    import rawalign_b200 as ra
+    from oracle.gen_golden_map import CONFIGS
+    off, sc = _dac(len(mg["raw_len"]))
+    with ra.Context(0) as c0, ra.Context(0) as c1, ra.Index.load_flat(c0, flat["sensitive"]) as ix0:
+        info = ix0.counts(); tabs = ix0.tables()
+        rep = ra.Index.alloc_like(c1, info, (tabs[0][1] // 16 - 16) // 2, tabs[1][1] // 8, ix0.seq_len, ix0.names)
+        try:
+            assert [b for _, b in rep.tables()] == [b for _, b in tabs]
+            for (src, n), (dst, _) in zip(tabs, rep.tables()):
+                class _V:
+                    def __init__(self, p):
+                        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "|u1", "data": (p, False), "version": 2}
+                torch.as_tensor(_V(dst), device="cuda:0").copy_(torch.as_tensor(_V(src), device="cuda:0"))
+            torch.cuda.synchronize()
+            rec, _ = rep.map_reads(_opt(CONFIGS[0][1]), raw=mg["raw"], raw_off=mg["raw_off"], raw_len=mg["raw_len"], offset=off, scale=sc)
+            assert rep.paf_lines(rec) == str(mg["paf"][0]).split("\n")
+        finally:
+            rep.close()

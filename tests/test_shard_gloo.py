@@ -66,3 +66,13 @@ def test_sharded_equals_unsharded_world2(tmp_path):
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
     mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     assert (tmp_path / "ok").exists()
+
+
+def test_broadcast_index_world1_is_a_plain_load_signature():
+    """broadcast_index / Index.alloc_like / Index.tables exist with the documented signatures (the collective itself needs GPUs:
+    it is exercised by bench.py under torchrun and by tests/test_gpu_map.py::test_index_replica_by_copy on one GPU)."""
+    import inspect
+    from rawalign_b200 import shard
+    from rawalign_b200.mapper import Index
+    assert list(inspect.signature(shard.broadcast_index).parameters) == ["ctx", "index_path", "rank", "device"]
+    assert hasattr(Index, "alloc_like") and hasattr(Index, "tables") and hasattr(Index, "counts")
