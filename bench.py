@@ -610,7 +610,8 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
     raw_p = torch.from_numpy(raw).pin_memory().numpy()            # the e2e path copies from pinned host memory every step
     # MAP_DEPTH batches in flight per GPU (one context + index each, one host thread each), as a map loop with double-buffered
     # mini-batches runs: one batch's uploads and host round trips overlap the other's kernels.  Every step does all of its work.
-    depth = max(1, int(os.environ.get("RA_BENCH_MAP_DEPTH", 3)))
+    # (a 250 Mb index is 23 GB and its rounds hold ~0.8 G anchors: two batches in flight fit 180 GB, three do not)
+    depth = max(1, int(os.environ.get("RA_BENCH_MAP_DEPTH", 2 if sum(cfg["ref"]) >= 200_000_000 else 3)))
     opt = ra.ri_mapopt_full(**cfg["opt"])
     want_cigar = bool(opt.flag & 0x4)
     pipes = []
@@ -620,8 +621,9 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
         c = ra.Context(local)
         # rank 0 parses the reference's index file; the other ranks receive the device tables (hash slots, positions, reference
         # signals) by NCCL broadcast -- the one collective of the path, at load
-        pipes.append((c, broadcast_index(c, ds.index_path, rank, dev)))
-    t_index = (time.time() - t0) / depth
+        pipes.append((c, broadcast_index(c, ds.index_path, rank, dev) if w == 0 else pipes[0][1].clone(c)))
+        if w == 0:
+            t_index = time.time() - t0
     ctx, ix = pipes[0]
 
     def barrier():
@@ -632,10 +634,18 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
 
     cig = {}
 
-    def step_e2e(w=0):
+    sig_p = torch.from_numpy(ds.decode(raw)).pin_memory().numpy()   # ri_sig_t::sig as the reference's reader hands it to the map loop (rsig.cpp:213-222)
+
+    def step_raw(w=0):
         r = pipes[w][1].map_reads(opt, raw=raw_p, raw_off=off, raw_len=ln, offset=dac_off, scale=dac_scale)
         if want_cigar:
             cig[w] = pipes[w][1].last_cigar(n_reads)             # the aln:s: triples come back to the host inside the timed region
+        return r
+
+    def step_e2e(w=0):
+        r = pipes[w][1].map_reads(opt, sig=sig_p, sig_off=off, sig_len=ln)
+        if want_cigar:
+            cig[w] = pipes[w][1].last_cigar(n_reads)
         return r
 
     def step_res(w=0, count=False):
@@ -664,7 +674,7 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
             raise errs[0]
 
     for w in range(depth):
-        rec0, st0 = step_e2e(w)                                   # every pipeline holds the batch; also the first parity sample
+        rec0, st0 = step_raw(w)                                   # every pipeline holds the batch; also the first parity sample
     recc, stc = step_res(0, True)                                 # one counted pass (cell counting is instrumentation)
     run_steps(step_res, max(args.warmup, depth))
     barrier()
@@ -679,18 +689,24 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
     dt = time.perf_counter() - t0
     launches = sum(p[0].launch_count for p in pipes) - l0
     rec = last[0][0]
-    run_steps(step_e2e, depth); barrier()
+    run_steps(step_raw, depth); barrier()
+    t0 = time.perf_counter()
+    run_steps(step_raw, args.steps)
+    barrier()
+    dt_raw = time.perf_counter() - t0
+    rec_r, st_r = last[0]
+    run_steps(step_e2e, depth); barrier()                         # (the float form leaves nothing resident: it runs last)
     t0 = time.perf_counter()
     run_steps(step_e2e, args.steps)
     barrier()
     dt_e2e = time.perf_counter() - t0
-    rec_e = last[(args.steps - 1) % depth][0] if (args.steps - 1) % depth in last else last[0][0]
+    rec_e, st_e = last[0]
     stage_acc = {k: v * args.steps for k, v in st_alone.items() if k.endswith("_ms")}
     clocks = sampler.stop()
-    tt = torch.tensor([dt, dt_e2e], dtype=torch.float64, device=dev)
+    tt = torch.tensor([dt, dt_e2e, dt_raw], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    dt, dt_e2e = float(tt[0]), float(tt[1])
+    dt, dt_e2e, dt_raw = float(tt[0]), float(tt[1]), float(tt[2])
     tot = torch.tensor([n_reads, stc["cells_useful"], stc["cells_issued"], int(rec0["mapped"].sum())], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tot)
@@ -703,7 +719,7 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
                "config": {"workload": cfg["desc"] + "; the whole map loop per read batch (ra_map_batch: decode, event detection, seeding, index lookup, "
                                       "chaining, chain DTW, primary chains, MAPQ, early stop), one step = one batch",
                           "reads_per_gpu": n_reads, "reference_bases": int(sum(cfg["ref"])), "n_sequences": len(cfg["ref"]), "preset": cfg["preset"],
-                          "note": cfg.get("note", ""), "index": f"reference index file format, built by {ds.index_by}, loaded by ra_index_load_file on rank 0" + (" and replicated by NCCL broadcast" if world > 1 else "") + f" in {t_index:.2f}s per context",
+                          "note": cfg.get("note", ""), "index": f"reference index file format, built by {ds.index_by}, loaded by ra_index_load_file on rank 0" + (" and replicated by NCCL broadcast" if world > 1 else "") + f" in {t_index:.2f}s; the other batches in flight use device-to-device copies (ra_index_clone)",
                           "l2_policy": "inputs larger than L2 (signal batch >> 126 MB)", "cpu_binding": binding},
                "reads_mapped_frac": mapped_all / reads_all,
                "dtw_cells_per_step": {"useful": cells_all, "issued": issued_all},
@@ -712,10 +728,18 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
                "batches_in_flight_per_gpu": depth,
                "map_counts_per_step": {k: stc[k] for k in ("rounds", "chunks", "events", "seeds", "anchors", "chains_evaluated", "launches")},
                "e2e": {"value": reads_all * args.steps / dt_e2e, "unit": "reads/s", "ms_per_step": dt_e2e / args.steps * 1e3,
-                       "h2d_bytes_per_step": int(raw.nbytes + off.nbytes + ln.nbytes + dac_off.nbytes + dac_scale.nbytes),
-                       "d2h_bytes_per_step": int(rec0.nbytes + (20 * len(cig[0][1]) + cig[0][0].nbytes if want_cigar else 0)),
-                       "input": "int16 DAC samples of the whole reads in pinned host memory -> ra_map_batch -> one 88-byte record per read",
+                       "h2d_bytes_per_step": int(st_e["h2d_bytes"]),
+                       "d2h_bytes_per_step": int(st_e["d2h_bytes"] + (20 * len(cig[0][1]) + cig[0][0].nbytes if want_cigar else 0)),
+                       "input": "ri_sig_t of every read (float pA, l_sig) in pinned host memory -- what the reference's reader hands map_worker_for and what "
+                                "the reference arm is timed on -> ra_map_batch -> one 88-byte record per read; per chunk round the GPU fetches only the chunk "
+                                "each still-active read is at (bytes counted by the library), as the reference's loop touches only those (rmap.cpp:685-712)",
+                       "host_buffer_bytes": int(sig_p.nbytes),
                        "records_equal_resident_path": bool(rec_e.tobytes() == rec.tobytes() == rec0.tobytes())},
+               "e2e_int16": {"value": reads_all * args.steps / dt_raw, "unit": "reads/s", "ms_per_step": dt_raw / args.steps * 1e3,
+                             "h2d_bytes_per_step": int(st_r["h2d_bytes"]), "d2h_bytes_per_step": int(st_r["d2h_bytes"]),
+                             "input": "int16 DAC samples of the whole reads in pinned host memory (decode and the (30,200) pA filter on the device, row f3): "
+                                      "l_sig is only known after the whole read has been decoded, so the whole read goes up",
+                             "records_equal_resident_path": bool(rec_r.tobytes() == rec0.tobytes())},
                "gpu_launches": int(launches), "clocks": clocks, "paf_digest": digest(lines)}
         if not args.no_cpu_baseline:
             out["cpu_baseline"] = reference_map_sample(ds, cfg, raw, off, ln, lines, max(args.cpu_sample_reads, 64 * (os.cpu_count() or 1)), n_reads, steps=2)

@@ -115,7 +115,9 @@ int         ra_set_opt(ra_ctx *ctx, const ra_mapopt_t *opt);
 int         ra_get_opt(const ra_ctx *ctx, ra_mapopt_t *opt);
 /* Performance knobs that do not change results (defaults in parentheses): "chain_slice_min_anchors" (2097152: anchors per
  * upload slice of ra_align_chains_batch, at most 8 slices), "k1_groups" (8: chunk groups of the resident event detection that run
- * on concurrent streams), "k1_priority_stream" (1: the latency-bound K1 kernels on a high-priority stream). */
+ * on concurrent streams), "k1_priority_stream" (1: the latency-bound K1 kernels on a high-priority stream), "map_sig_whole"
+ * (0: the float form of ra_map_batch uploads per chunk round only the chunk each still-active read is at; 1: the whole batch
+ * up front, which also leaves it resident for the device-resident form). */
 int         ra_set_tuning(ra_ctx *ctx, const char *name, int64_t value);
 /* number of kernels this context has launched since creation (bench.py's gpu_launches) */
 uint64_t    ra_launch_count(const ra_ctx *ctx);
@@ -284,6 +286,19 @@ int ra_index_load_file(ra_ctx *ctx, const char *path, ra_index **out);
 int ra_index_load_flat(ra_ctx *ctx, int32_t w, int32_t e, int32_t n, int32_t q, int32_t lq, int32_t k, uint32_t n_seq, const uint32_t *seq_len,
                        const float *const *fwd, const float *const *rev, uint64_t n_keys, const uint64_t *keys, const uint64_t *key_off,
                        const uint64_t *vals, ra_index **out);
+/* Index construction on the device: what ri_idx_gen computes per sequence (rawindex.cpp:127-153:
+ * ri_seq_to_sig for strand flag 1 then 0, rsig.cpp:7-41 -- fp64 mean / standard deviation summed in sequence order -- and
+ * ri_sketch of both signals) and worker_post's grouping by seed (:194-247), as the device table ra_map_batch reads; the
+ * expected signals become the context's reference mirror.  seq[i]: seq_len[i] base codes 0..3 = ACGT, 4 = ambiguous
+ * (seq_nt4_table); pore_vals: 4^k level means (main.cpp:345-347).  The contraction mode follows the context's fp_contract.
+ * Regular seeding only (w = n = 0).  ra_index_export returns the result as the flat table of ra_index_load_flat (positions in
+ * ri_idx_get's order) -- bit-identical to the table parsed from an index file the reference built; keys == NULL sizes. */
+int ra_index_build(ra_ctx *ctx, int32_t e, int32_t q, int32_t lq, int32_t k, uint32_t n_seq, const uint8_t *const *seq, const uint32_t *seq_len,
+                   const float *pore_vals, ra_index **out);
+int ra_index_export(ra_index *ix, uint64_t *n_keys, uint64_t *n_vals, uint64_t *keys, uint64_t *key_off, uint64_t *vals);
+/* A copy of an index for another context -- a second batch in flight on the same GPU, or a peer GPU of the same process: the
+ * three tables go device to device, the file is not parsed again. */
+int ra_index_clone(ra_index *src, ra_ctx *ctx, ra_index **out);
 void ra_index_destroy(ra_index *ix);
 /* out[0..8] = w, e, n, q, lq, k, n_seq, n_keys (low 32 bits), n_vals (low 32 bits); seq_len_out (optional) n_seq entries */
 int ra_index_info(const ra_index *ix, int32_t *out, uint32_t *seq_len_out);
@@ -311,13 +326,17 @@ typedef struct ra_map_stats_s {
 	uint32_t rounds; uint32_t reserved;
 	uint64_t chunks, events, seeds, anchors, chains_evaluated, launches;
 	uint64_t cells_issued, cells_useful;   /* DP cells of the chain evaluations; counted only when reserved == 1 on entry */
+	uint64_t h2d_bytes, d2h_bytes;         /* bytes the call moved over PCIe (signal, tables, control words, records) */
 } ra_map_stats_t;
 
 /* Maps a batch of reads.  Signal either as int16 DAC samples (raw != NULL: read r is raw[raw_off[r] .. +raw_len[r]),
  * offset[r] / scale[r] as in ra_detect_events_raw_batch; decoded on the device, rsig.cpp:213-222) or as float pA
  * (raw == NULL: sig[sig_off[r] .. +sig_len[r]) = ri_sig_t::sig).  All pointers are host pointers.  out: n_reads records in
- * input order.  raw == NULL and sig == NULL maps again the batch the previous call left on the device (no upload, no decode:
- * the device-resident form).  Minimizer (w > 0) and BLEND (n > 0) indexes return RA_EUNSUP. */
+ * input order.  The float form moves, per chunk round, only the chunk each still-active read is at (sig_len[r] is l_sig, so
+ * nothing else of a read that maps early is needed, rmap.cpp:685-712): read by the GPU straight from sig when that is
+ * page-locked memory, else gathered into a page-locked staging buffer first; sig must stay valid and unchanged during the call.
+ * raw == NULL and sig == NULL maps again the batch the previous raw-form (or "map_sig_whole") call left on the device (no
+ * upload, no decode: the device-resident form).  Minimizer (w > 0) and BLEND (n > 0) indexes return RA_EUNSUP. */
 int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt,
                  const int16_t *raw, const uint64_t *raw_off, const uint32_t *raw_len, const float *offset, const float *scale,
                  const float *sig, const uint64_t *sig_off, const uint32_t *sig_len,

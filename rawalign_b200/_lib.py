@@ -53,7 +53,7 @@ class MapStats(C.Structure):
     """ra_map_stats_t"""
     _fields_ = [(n, C.c_float) for n in ("decode_ms", "events_ms", "seed_ms", "sort_ms", "chain_ms", "dtw_ms", "select_ms", "total_ms")] + \
                [("rounds", C.c_uint32), ("reserved", C.c_uint32)] + \
-               [(n, C.c_uint64) for n in ("chunks", "events", "seeds", "anchors", "chains_evaluated", "launches", "cells_issued", "cells_useful")]
+               [(n, C.c_uint64) for n in ("chunks", "events", "seeds", "anchors", "chains_evaluated", "launches", "cells_issued", "cells_useful", "h2d_bytes", "d2h_bytes")]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}
@@ -116,6 +116,9 @@ def load() -> C.CDLL:
     L.ra_map_last_cigar.argtypes = [vp, u32, vp, vp, vp, vp, u64]
     L.ra_index_tables.argtypes = [vp, vp, vp]; L.ra_index_tables.restype = C.c_int
     L.ra_index_alloc.argtypes = [vp, C.POINTER(C.c_int32), u64, u64, vp, C.POINTER(vp)]; L.ra_index_alloc.restype = C.c_int
+    L.ra_index_clone.argtypes = [vp, vp, C.POINTER(vp)]; L.ra_index_clone.restype = C.c_int
+    L.ra_index_build.argtypes = [vp] + [C.c_int32] * 4 + [u32, vp, vp, vp, C.POINTER(vp)]; L.ra_index_build.restype = C.c_int
+    L.ra_index_export.argtypes = [vp, C.POINTER(u64), C.POINTER(u64), vp, vp, vp]; L.ra_index_export.restype = C.c_int
     for name in ("ra_get_opt", "ra_index_load_file", "ra_index_load_flat", "ra_index_info", "ra_map_batch", "ra_map_last_cigar"):
         getattr(L, name).restype = C.c_int
     for name in ("ra_init", "ra_set_opt", "ra_last_timing", "ra_ref_load", "ra_ref_load_flat", "ra_ref_device", "ra_ref_alloc",
@@ -138,4 +141,5 @@ EXPORTED_SYMBOLS = [
     "ra_dtw_batch", "ra_dtw_batch_dev", "ra_dtw_cells", "ra_dtw_tb_batch",
     "ra_align_chains_batch", "ra_align_chains_batch_dev", "ra_align_chains_cigar_batch",
     "ra_get_opt", "ra_set_tuning", "ra_ri_mapopt_init", "ra_index_load_file", "ra_index_load_flat", "ra_index_destroy", "ra_index_info", "ra_map_batch", "ra_map_last_cigar", "ra_index_tables", "ra_index_alloc",
+    "ra_index_build", "ra_index_export", "ra_index_clone",
 ]

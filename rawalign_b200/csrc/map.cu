@@ -25,6 +25,7 @@
 extern "C" void ra__add_launches(ra_ctx *ctx, uint64_t n);        // api.cu
 extern "C" int ra__fail(int code, const char *fmt, ...);            // api.cu: sets ra_last_error()
 extern "C" int ra__device(const ra_ctx *ctx);
+extern "C" int ra__map_sig_whole(const ra_ctx *ctx);
 extern "C" void ra__swap_resident(ra_ctx *ctx, void **dev_ptr, uint64_t *n_floats);
 
 namespace {
@@ -97,6 +98,7 @@ struct ra_index {
 	uint32_t tshift = 0, n_bins = 0;                               // bin function of the bucket sort: bin_base[ref << 1 | strand] + (target >> tshift)
 	std::vector<uint64_t> last_off; std::vector<uint32_t> last_len; bool last_raw = false;   // the batch left on the device by the last ra_map_batch
 	void *pin = nullptr; size_t pin_cap = 0;
+	void *pin_sig = nullptr; size_t pin_sig_cap = 0;               // staging of the per-round signal upload from pageable caller memory
 	bool sort_attr = false;                                        // the sort kernel's > 48 KB shared memory opt-in (one index = one device)
 	cudaStream_t stream = nullptr;
 	cudaEvent_t ev_t[16] = {};
@@ -107,39 +109,14 @@ namespace {
 // ---------------------------------------------------------------------------------------------------------------
 // host: index file -> flat table -> device open-addressing table
 // ---------------------------------------------------------------------------------------------------------------
-int build_device_index(ra_ctx *ctx, ra_index *ix, const float *const *fwd, const float *const *rev, const uint64_t *keys, const uint64_t *key_off,
-                       const uint64_t *vals)
+// sequence table, bin table of the anchor sort, stream and events: everything of an index that follows from the sequence lengths
+int finish_index_geometry(ra_ctx *ctx, ra_index *ix, const std::vector<uint64_t> &arena_off)
 {
-	if (ix->n_seq == 0 || ix->n_seq > kMaxSeq) return ra__fail(RA_EUNSUP, "%u reference sequences (supported: 1..%u)", ix->n_seq, kMaxSeq);
-	std::vector<uint64_t> arena_off(2 * (size_t)ix->n_seq);
 	int rc;
-	if (fwd) { if ((rc = ra_ref_load(ctx, ix->n_seq, fwd, rev, ix->seq_len.data(), arena_off.data()))) return rc; }
-	else {                                                         // replica: the same arena layout as ra_ref_load ([fwd(0) | rev(0) | fwd(1) | ...]), filled by broadcast
-		uint64_t o = 0;
-		for (uint32_t i = 0; i < ix->n_seq; ++i) { arena_off[2 * i] = o; o += ix->seq_len[i]; arena_off[2 * i + 1] = o; o += ix->seq_len[i]; }
-		if ((rc = ra_ref_alloc(ctx, o))) return rc;
-	}
 	std::vector<uint64_t> tab(3 * (size_t)ix->n_seq);
 	for (uint32_t i = 0; i < ix->n_seq; ++i) { tab[3 * i] = arena_off[2 * i]; tab[3 * i + 1] = arena_off[2 * i + 1]; tab[3 * i + 2] = ix->seq_len[i]; }
 	if ((rc = ix->seq_tab.reserve(tab.size() * 8))) return rc;
 	MAP_CUDA(cudaMemcpy(ix->seq_tab.p, tab.data(), tab.size() * 8, cudaMemcpyHostToDevice));
-	uint32_t bits = 4;
-	while ((1ull << bits) < 2 * ix->n_keys + 16) ++bits;
-	if (bits > 31) return ra__fail(RA_EUNSUP, "index has too many distinct seeds (%llu)", (unsigned long long)ix->n_keys);
-	ix->slot_bits = bits;
-	const uint64_t n_slots = 1ull << bits;
-	std::vector<Slot> slots(keys ? n_slots : 0, Slot{0, 0, 0});
-	for (uint64_t i = 0; keys && i < ix->n_keys; ++i) {
-		if (keys[i] >> 32) return ra__fail(RA_EINVAL, "seed hash %llu does not fit 32 bits (rsketch.c masks hash64 to 32 bits)", (unsigned long long)keys[i]);
-		const uint32_t key = (uint32_t)keys[i];
-		uint64_t h = ((uint32_t)(key * 0x9E3779B1u)) >> (32 - bits);
-		while (slots[h].cnt) h = (h + 1) & (n_slots - 1);
-		slots[h].key = key; slots[h].cnt = (uint32_t)(key_off[i + 1] - key_off[i]); slots[h].off = key_off[i];
-	}
-	if ((rc = ix->slots.reserve(n_slots * sizeof(Slot)))) return rc;
-	if (keys) MAP_CUDA(cudaMemcpy(ix->slots.p, slots.data(), n_slots * sizeof(Slot), cudaMemcpyHostToDevice));
-	if ((rc = ix->vals.reserve(std::max<uint64_t>(ix->n_vals, 1) * 8))) return rc;
-	if (vals && ix->n_vals) MAP_CUDA(cudaMemcpy(ix->vals.p, vals, ix->n_vals * 8, cudaMemcpyHostToDevice));
 	if (2ull * ix->n_seq <= 4096) {                                // bins of the anchor bucket sort (map_kernels.cuh, kBins): uniform over the concatenated reference
 		uint32_t ts = 0;
 		for (;; ++ts) {
@@ -158,6 +135,78 @@ int build_device_index(ra_ctx *ctx, ra_index *ix, const float *const *fwd, const
 	MAP_CUDA(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
 	for (auto &e : ix->ev_t) MAP_CUDA(cudaEventCreate(&e));
 	return RA_OK;
+}
+
+// arena layout of ra_ref_load: [fwd(0) | rev(0) | fwd(1) | ...], each seq.len floats
+std::vector<uint64_t> arena_layout(const ra_index *ix, uint64_t *total)
+{
+	std::vector<uint64_t> arena_off(2 * (size_t)ix->n_seq);
+	uint64_t o = 0;
+	for (uint32_t i = 0; i < ix->n_seq; ++i) { arena_off[2 * i] = o; o += ix->seq_len[i]; arena_off[2 * i + 1] = o; o += ix->seq_len[i]; }
+	if (total) *total = o;
+	return arena_off;
+}
+
+// table insertion on the device: one thread per key claims a slot by compare-and-swap on the (key | count << 32) word, linear probing;
+// the insertion order (and so the slot a key ends up in) is irrelevant to lookups.  A key seen twice raises *dup.
+__global__ void __launch_bounds__(256)
+k_ix_insert(const uint32_t *__restrict__ key, const uint32_t *__restrict__ cnt, const uint64_t *__restrict__ off, uint64_t n, Slot *__restrict__ slots,
+            uint32_t slot_bits, uint32_t *__restrict__ dup)
+{
+	const uint32_t m = (1u << slot_bits) - 1u;
+	unsigned long long *w = reinterpret_cast<unsigned long long *>(slots);   // 16-byte slots: words 2h (key, cnt) and 2h + 1 (off)
+	for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+		const uint32_t k = key[i];
+		const unsigned long long word = (unsigned long long)k | ((unsigned long long)cnt[i] << 32);
+		uint32_t h = (uint32_t)(k * 0x9E3779B1u) >> (32 - slot_bits);
+		for (;;) {
+			const unsigned long long prev = atomicCAS(&w[2ull * h], 0ull, word);
+			if (prev == 0ull) { w[2ull * h + 1] = off[i]; break; }
+			if ((uint32_t)prev == k) { atomicExch(dup, 1u); break; }
+			h = (h + 1u) & m;
+		}
+	}
+}
+
+// fwd == NULL: replica (tables of the right size, contents by broadcast).  key / cnt / off: one entry per distinct seed hash,
+// off into vals[]; any order.
+int build_device_index(ra_ctx *ctx, ra_index *ix, const float *const *fwd, const float *const *rev, const uint32_t *key, const uint32_t *cnt,
+                       const uint64_t *off, const uint64_t *vals)
+{
+	if (ix->n_seq == 0 || ix->n_seq > kMaxSeq) return ra__fail(RA_EUNSUP, "%u reference sequences (supported: 1..%u)", ix->n_seq, kMaxSeq);
+	uint64_t total = 0;
+	std::vector<uint64_t> arena_off = arena_layout(ix, &total);
+	int rc;
+	if (fwd) { if ((rc = ra_ref_load(ctx, ix->n_seq, fwd, rev, ix->seq_len.data(), arena_off.data()))) return rc; }
+	else if ((rc = ra_ref_alloc(ctx, total))) return rc;
+	uint32_t bits = 4;
+	while ((1ull << bits) < 2 * ix->n_keys + 16) ++bits;
+	if (bits > 31) return ra__fail(RA_EUNSUP, "index has too many distinct seeds (%llu)", (unsigned long long)ix->n_keys);
+	ix->slot_bits = bits;
+	const uint64_t n_slots = 1ull << bits;
+	if ((rc = ix->slots.reserve(n_slots * sizeof(Slot)))) return rc;
+	if ((rc = ix->vals.reserve(std::max<uint64_t>(ix->n_vals, 1) * 8))) return rc;
+	if (fwd) {
+		MAP_CUDA(cudaMemset(ix->slots.p, 0, n_slots * sizeof(Slot)));
+		if (ix->n_vals) MAP_CUDA(cudaMemcpy(ix->vals.p, vals, ix->n_vals * 8, cudaMemcpyHostToDevice));
+		if (ix->n_keys) {
+			Buf dk, dc, dof, dd;
+			auto done = [&](int code) { dk.release(); dc.release(); dof.release(); dd.release(); return code; };
+			if ((rc = dk.reserve(ix->n_keys * 4)) || (rc = dc.reserve(ix->n_keys * 4)) || (rc = dof.reserve(ix->n_keys * 8)) || (rc = dd.reserve(64))) return done(rc);
+			cudaError_t ce;
+			if ((ce = cudaMemcpy(dk.p, key, ix->n_keys * 4, cudaMemcpyHostToDevice)) || (ce = cudaMemcpy(dc.p, cnt, ix->n_keys * 4, cudaMemcpyHostToDevice)) ||
+			    (ce = cudaMemcpy(dof.p, off, ix->n_keys * 8, cudaMemcpyHostToDevice)) || (ce = cudaMemset(dd.p, 0, 4)))
+				return done(ra__fail(RA_ECUDA, "index upload: %s", cudaGetErrorString(ce)));
+			k_ix_insert<<<(unsigned)std::min<uint64_t>(148 * 16, (ix->n_keys + 255) / 256), 256>>>(dk.as<uint32_t>(), dc.as<uint32_t>(), dof.as<uint64_t>(), ix->n_keys,
+			                                                                                    ix->slots.as<Slot>(), bits, dd.as<uint32_t>());
+			uint32_t dup = 0;
+			if ((ce = cudaMemcpy(&dup, dd.p, 4, cudaMemcpyDeviceToHost)) || (ce = cudaGetLastError())) return done(ra__fail(RA_ECUDA, "index insert: %s", cudaGetErrorString(ce)));
+			done(0);
+			if (dup) return ra__fail(RA_EINVAL, "index table holds a seed hash twice");
+			ra__add_launches(ctx, 1);
+		}
+	}
+	return finish_index_geometry(ctx, ix, arena_off);
 }
 
 } // namespace
@@ -189,7 +238,18 @@ int ra_index_load_flat(ra_ctx *ctx, int32_t w, int32_t e, int32_t n, int32_t q, 
 	ix->ctx = ctx; ix->w = w; ix->e = e; ix->n = n; ix->q = q; ix->lq = lq; ix->k = k; ix->n_seq = n_seq; ix->n_keys = n_keys;
 	ix->n_vals = n_keys ? key_off[n_keys] : 0;
 	ix->seq_len.assign(seq_len, seq_len + n_seq);
-	int rc = build_device_index(ctx, ix, fwd, rev, keys, key_off, vals);
+	std::vector<uint32_t> k32(n_keys), c32(n_keys);
+	for (uint64_t i = 0; i < n_keys; ++i) {
+		const uint64_t c = key_off[i + 1] - key_off[i];
+		if (keys[i] >> 32 || c == 0 || c >> 32 || key_off[i + 1] > ix->n_vals) {
+			const uint64_t bad_key = keys[i];
+			ra_index_destroy(ix);
+			return ra__fail(RA_EINVAL, "index table entry %llu: hash %llu must fit 32 bits (rsketch.c masks hash64 to 32 bits) and own 1..2^32-1 in-range positions",
+			                (unsigned long long)i, (unsigned long long)bad_key);
+		}
+		k32[i] = (uint32_t)keys[i]; c32[i] = (uint32_t)c;
+	}
+	int rc = build_device_index(ctx, ix, fwd, rev, k32.data(), c32.data(), key_off, vals);
 	if (rc) { ra_index_destroy(ix); return rc; }
 	*out = ix;
 	return RA_OK;
@@ -220,12 +280,12 @@ int ra_index_load_file(ra_ctx *ctx, const char *path, ra_index **out)
 		if (fread(fw[i].data(), 4, seq_len[i], f) != seq_len[i] || fread(rv[i].data(), 4, seq_len[i], f) != seq_len[i]) return bad("truncated signal");
 	}
 	const int b = 14;                                              // ri_idx_load: ri_idx_init(14, ...), rawindex.cpp:330
-	struct KV { uint64_t hash, start, cnt; };
-	std::vector<KV> kv;
+	std::vector<uint32_t> k32, c32;                               // one entry per distinct seed hash, in file order
+	std::vector<uint64_t> koff;
 	std::vector<uint64_t> pool;                                    // every bucket's p[] and the single positions, in file order
 	for (uint32_t i = 0; i < (1u << b); ++i) {
 		int32_t nb; uint32_t size;
-		if (fread(&nb, 4, 1, f) != 1) return bad("truncated bucket");
+		if (fread(&nb, 4, 1, f) != 1 || nb < 0) return bad("truncated bucket");
 		const uint64_t pbase = pool.size();
 		pool.resize(pbase + (size_t)nb);
 		if (nb && fread(pool.data() + pbase, 8, (size_t)nb, f) != (size_t)nb) return bad("truncated bucket positions");
@@ -234,27 +294,29 @@ int ra_index_load_file(ra_ctx *ctx, const char *path, ra_index **out)
 			uint64_t x[2];
 			if (fread(x, 8, 2, f) != 2) return bad("truncated hash table");
 			const uint64_t hash = ((x[0] >> 1) << b) | i;          // key = hash >> b << 1 | single (rawindex.cpp:222-226)
-			if (x[0] & 1) { pool.push_back(x[1]); kv.push_back({hash, pool.size() - 1, 1}); }
-			else kv.push_back({hash, pbase + (x[1] >> 32), (uint32_t)x[1]});
+			if (hash >> 32) return bad("seed hash does not fit 32 bits (rsketch.c masks hash64 to 32 bits)");
+			k32.push_back((uint32_t)hash);
+			if (x[0] & 1) { pool.push_back(x[1]); koff.push_back(pool.size() - 1); c32.push_back(1); }
+			else {
+				const uint64_t st = x[1] >> 32, c = (uint32_t)x[1];
+				if (c == 0 || st + c > (uint64_t)nb) return bad("hash table entry points outside its bucket");
+				koff.push_back(pbase + st); c32.push_back((uint32_t)c);
+			}
 		}
 	}
 	fclose(f);
-	std::sort(kv.begin(), kv.end(), [](const KV &a, const KV &c) { return a.hash < c.hash; });
-	std::vector<uint64_t> keys(kv.size()), key_off(kv.size() + 1), vals;
-	uint64_t tot = 0;
-	for (auto &x : kv) tot += x.cnt;
-	vals.reserve(tot);
-	for (size_t i = 0; i < kv.size(); ++i) {
-		keys[i] = kv[i].hash; key_off[i] = vals.size();
-		vals.insert(vals.end(), pool.begin() + kv[i].start, pool.begin() + kv[i].start + kv[i].cnt);
-	}
-	key_off[kv.size()] = vals.size();
+	const uint32_t e = pars[1], q = pars[3], lq = pars[4];
+	if (e < 2 || e > 9 || (lq + 2) * e > 63 || q < 1 || q > 32 || lq > q) return ra__fail(RA_EINVAL, "index file %s: bad sketch parameters e=%u q=%u lq=%u", path, e, q, lq);
 	std::vector<const float *> fp(n_seq), rp(n_seq);
 	for (uint32_t i = 0; i < n_seq; ++i) { fp[i] = fw[i].data(); rp[i] = rv[i].data(); }
-	int rc = ra_index_load_flat(ctx, (int32_t)pars[0], (int32_t)pars[1], (int32_t)pars[2], (int32_t)pars[3], (int32_t)pars[4], (int32_t)pars[5], n_seq,
-	                            seq_len.data(), fp.data(), rp.data(), keys.size(), keys.data(), key_off.data(), vals.data(), out);
-	if (rc == RA_OK) (*out)->names = names;
-	return rc;
+	ra_index *ix = new ra_index();
+	ix->ctx = ctx; ix->w = (int32_t)pars[0]; ix->e = (int32_t)e; ix->n = (int32_t)pars[2]; ix->q = (int32_t)q; ix->lq = (int32_t)lq; ix->k = (int32_t)pars[5];
+	ix->n_seq = n_seq; ix->n_keys = k32.size(); ix->n_vals = pool.size(); ix->seq_len = seq_len; ix->names = names;
+	// the table is keyed by hash and the positions of a key are contiguous in pool[] (ascending, rawindex.cpp:232): no sorting needed
+	int rc = build_device_index(ctx, ix, fp.data(), rp.data(), k32.data(), c32.data(), koff.data(), pool.data());
+	if (rc) { ra_index_destroy(ix); return rc; }
+	*out = ix;
+	return RA_OK;
 }
 
 void ra_index_destroy(ra_index *ix)
@@ -267,6 +329,7 @@ void ra_index_destroy(ra_index *ix)
 	               &ix->dkeep, &ix->scan_tmp, &ix->lsig_keep, &ix->nt, &ix->n_nt, &ix->ntf, &ix->cxf, &ix->bin_base, &ix->stage, &ix->fin_r, &ix->fin_aoff, &ix->fin_chain, &ix->fin_anc };
 	for (Buf *b : all) b->release();
 	if (ix->pin) cudaFreeHost(ix->pin);
+	if (ix->pin_sig) cudaFreeHost(ix->pin_sig);
 	if (ix->stream) cudaStreamDestroy(ix->stream);
 	for (auto &e : ix->ev_t) if (e) cudaEventDestroy(e);
 	delete ix;
@@ -292,8 +355,35 @@ int ra_index_alloc(ra_ctx *ctx, const int32_t *info /* the 9 values of ra_index_
 	ix->ctx = ctx; ix->w = info[0]; ix->e = info[1]; ix->n = info[2]; ix->q = info[3]; ix->lq = info[4]; ix->k = info[5]; ix->n_seq = (uint32_t)info[6];
 	ix->n_keys = n_keys; ix->n_vals = n_vals;
 	ix->seq_len.assign(seq_len, seq_len + ix->n_seq);
-	int rc = build_device_index(ctx, ix, nullptr, nullptr, nullptr, nullptr, nullptr);     // geometry and tables of the right size, contents by broadcast
+	int rc = build_device_index(ctx, ix, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);     // geometry and tables of the right size, contents by broadcast
 	if (rc) { ra_index_destroy(ix); return rc; }
+	*out = ix;
+	return RA_OK;
+}
+
+// A second index with the same contents for another context (another batch in flight on the same GPU, or a peer GPU of the same
+// process): tables copied device to device, no host parse.
+int ra_index_clone(ra_index *src, ra_ctx *ctx, ra_index **out)
+{
+	if (!src || !ctx || !out) return ra__fail(RA_EINVAL, "NULL argument");
+	ra_index *ix = new ra_index();
+	ix->ctx = ctx; ix->w = src->w; ix->e = src->e; ix->n = src->n; ix->q = src->q; ix->lq = src->lq; ix->k = src->k; ix->n_seq = src->n_seq;
+	ix->seq_len = src->seq_len; ix->names = src->names; ix->n_vals = src->n_vals;
+	ix->n_keys = ((1ull << src->slot_bits) - 16) / 2;               // the key count that sizes the same table; the true count is set below
+	MAP_CUDA(cudaSetDevice(ra__device(ctx)));
+	int rc = build_device_index(ctx, ix, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+	if (rc) { ra_index_destroy(ix); return rc; }
+	ix->n_keys = src->n_keys;
+	void *sp[3], *dp[3]; uint64_t sb[3], db[3];
+	if ((rc = ra_index_tables(src, sp, sb)) || (rc = ra_index_tables(ix, dp, db))) { ra_index_destroy(ix); return rc; }
+	for (int i = 0; i < 3; ++i) {
+		if (sb[i] != db[i]) { ra_index_destroy(ix); return ra__fail(RA_EINVAL, "clone geometry differs (table %d: %llu vs %llu bytes)", i, (unsigned long long)sb[i], (unsigned long long)db[i]); }
+		if (sb[i]) {
+			cudaError_t ce = cudaMemcpyPeer(dp[i], ra__device(ctx), sp[i], ra__device(src->ctx), sb[i]);
+			if (ce != cudaSuccess) { ra_index_destroy(ix); return ra__fail(RA_ECUDA, "index clone: %s", cudaGetErrorString(ce)); }
+		}
+	}
+	MAP_CUDA(cudaDeviceSynchronize());
 	*out = ix;
 	return RA_OK;
 }
@@ -312,3 +402,5 @@ int ra_index_info(const ra_index *ix, int32_t *out, uint32_t *seq_len_out)
 #include "map_kernels.cuh"
 #include "map_chain.cuh"
 #include "map_batch.cuh"
+#include "map_index_build.cuh"
+#include "map_index_host.cuh"

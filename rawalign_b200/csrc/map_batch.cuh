@@ -17,6 +17,37 @@ __global__ void k_init_state(ReadState *__restrict__ st, uint32_t n_reads, const
 	st[r] = s;
 }
 
+// Float-signal form, per-round upload: the round's chunk of every active read is fetched straight from the caller's buffer when
+// that is page-locked (mapped host memory read over PCIe, 128-byte coalesced) into a dense round arena, chunk i at i * stride.
+__global__ void __launch_bounds__(256)
+k_gather_chunks(const float *__restrict__ hsig, uint64_t *__restrict__ coff, const uint32_t *__restrict__ clen, uint32_t n_act, float *__restrict__ dst, uint32_t stride)
+{
+	const uint32_t i = blockIdx.x;
+	if (i >= n_act) return;
+	const float *__restrict__ src = hsig + coff[i];
+	const uint32_t n = clen[i];
+	float *__restrict__ d = dst + (size_t)i * stride;
+	const uint32_t head = min(n, (uint32_t)(((16u - (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15u)) & 15u) >> 2));
+	if (threadIdx.x < head) d[threadIdx.x] = src[threadIdx.x];
+	const float4 *__restrict__ s4 = reinterpret_cast<const float4 *>(src + head);
+	const uint32_t n4 = (n - head) >> 2;
+	for (uint32_t k = threadIdx.x; k < n4; k += 256) {
+		const float4 v = s4[k];
+		float *o = d + head + 4u * k;
+		o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w;
+	}
+	const uint32_t tail0 = head + 4u * n4;
+	if (tail0 + threadIdx.x < n) d[tail0 + threadIdx.x] = src[tail0 + threadIdx.x];
+	__syncthreads();
+	if (threadIdx.x == 0) coff[i] = (uint64_t)i * stride;
+}
+
+__global__ void k_dense_coff(uint64_t *__restrict__ coff, uint32_t n_act, uint32_t stride)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n_act) coff[i] = (uint64_t)i * stride;
+}
+
 } // namespace mapk
 
 namespace {
@@ -44,6 +75,9 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 	if (resident) {
 		if (ix->last_len.size() != n_reads || n_reads == 0) return ra__fail(RA_EINVAL, "no resident batch of %u reads on the device", n_reads);
 	} else if (from_raw ? (!raw_off || !raw_len || !offset || !scale) : (!sig || !sig_off || !sig_len)) return ra__fail(RA_EINVAL, "NULL signal table");
+	// float form: per round only the chunk each active read is at goes up (sig_len[r] IS l_sig, rsig.cpp:213-222 ran in the caller's
+	// reader), so a read that maps in its first chunk costs 16 KB of PCIe instead of its whole signal; nothing stays resident
+	const bool lazy = !from_raw && !resident && !ra__map_sig_whole(ctx);
 	const bool count_cells = stats && stats->reserved == 1;        // instrumentation: DP cells of the chain evaluations (costs a counter pass)
 	if (ix->w != 0 || ix->n != 0) return ra__fail(RA_EUNSUP, "minimizer (w=%d) / BLEND (n=%d) seeding is not implemented on the device", ix->w, ix->n);
 	if (opt->num_best_chains < 1 || opt->num_best_chains > (uint32_t)kMaxBest) return ra__fail(RA_EUNSUP, "num_best_chains %u (supported: 1..%d)", opt->num_best_chains, kMaxBest);
@@ -108,7 +142,7 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 		ev_cap += used / (opt->window_length1 / 2 + 2) + used / (opt->window_length2 / 2 + 2) + 4 * nch + 4;
 		hst[r] = s;
 	}
-	if ((rc = ix->sig.reserve(std::max<uint64_t>(n_samples, 1) * 4 + 64))) return rc;
+	if (!lazy && (rc = ix->sig.reserve(std::max<uint64_t>(n_samples, 1) * 4 + 64))) return rc;
 	if ((rc = ix->state.reserve((size_t)n_reads * sizeof(ReadState)))) return rc;
 	if ((rc = ix->chains.reserve((size_t)n_reads * P.cap_chains * sizeof(ChainRec)))) return rc;
 	if ((rc = ix->paf.reserve((size_t)n_reads * sizeof(ra_paf_t)))) return rc;
@@ -138,7 +172,20 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 		MAP_CUDA(ra::launch_decode_raw(ix->raw16.as<int16_t>(), ix->rd_off.as<uint64_t>(), ix->rd_len.as<uint32_t>(), ix->rd_offset.as<float>(),
 		                               ix->rd_scale.as<float>(), n_reads, ix->sig.as<float>(), lsd, S));
 		l_sig_dev = lsd; ++launches;
-	} else MAP_CUDA(cudaMemcpyAsync(ix->sig.p, sig, n_samples * 4, cudaMemcpyHostToDevice, S));
+		stt.h2d_bytes += n_samples * 2 + (uint64_t)n_reads * 20;
+	} else if (!lazy) { MAP_CUDA(cudaMemcpyAsync(ix->sig.p, sig, n_samples * 4, cudaMemcpyHostToDevice, S)); stt.h2d_bytes += n_samples * 4; }
+	const float *hsig_dev = nullptr;                               // the caller's buffer as the device sees it (page-locked, mapped), else NULL
+	if (lazy && n_samples) {
+		cudaPointerAttributes pa0, pa1;
+		if (cudaPointerGetAttributes(&pa0, sig) == cudaSuccess && cudaPointerGetAttributes(&pa1, sig + n_samples - 1) == cudaSuccess &&
+		    pa0.type == cudaMemoryTypeHost && pa1.type == cudaMemoryTypeHost && pa0.devicePointer &&
+		    (const char *)pa1.devicePointer - (const char *)pa0.devicePointer == (const char *)(sig + n_samples - 1) - (const char *)sig)
+			hsig_dev = static_cast<const float *>(pa0.devicePointer);
+		(void)cudaGetLastError();
+	}
+	const uint32_t lazy_stride = (opt->chunk_size + 3u) & ~3u;
+	std::vector<uint64_t> h_coff; std::vector<uint32_t> h_clen;
+	if (!resident) stt.h2d_bytes += (uint64_t)n_reads * sizeof(ReadState);
 	k_init_state<<<(n_reads + 255) / 256, 256, 0, S>>>(ix->state.as<ReadState>(), n_reads, l_sig_dev, ix->paf.as<ra_paf_t>()); ++launches;
 	MAP_CUDA(cudaStreamSynchronize(S));
 	stt.decode_ms = clk.lap();
@@ -152,12 +199,39 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 		const uint32_t cur = round & 1u;
 		MAP_CUDA(cudaMemsetAsync(counters, 0, 64, S));
 		k_round_setup<<<1, 1024, 0, S>>>(st, n_reads, P, ix->act.as<uint32_t>(), ix->coff.as<uint64_t>(), ix->clen.as<uint32_t>(), counters); ++launches;
-		MAP_CUDA(cudaMemcpyAsync(hc, counters, 8, cudaMemcpyDeviceToHost, S));
+		MAP_CUDA(cudaMemcpyAsync(hc, counters, 64, cudaMemcpyDeviceToHost, S));   // [0] active reads, [1] longest chunk, [14..15] samples of the round
 		MAP_CUDA(cudaStreamSynchronize(S));
 		const uint32_t n_act = hc[0], max_len = hc[1];
 		if (n_act == 0) break;
 		stt.rounds = round + 1; stt.chunks += n_act;
 		stt.select_ms += clk.lap();
+		if (lazy) {
+			if ((rc = ix->sig.reserve((uint64_t)n_act * lazy_stride * 4 + 64))) return rc;
+			if (hsig_dev) {
+				k_gather_chunks<<<n_act, 256, 0, S>>>(hsig_dev, ix->coff.as<uint64_t>(), ix->clen.as<uint32_t>(), n_act, ix->sig.as<float>(), lazy_stride); ++launches;
+				stt.h2d_bytes += 4ull * *reinterpret_cast<const uint64_t *>(hc + 14);
+			} else {                                                // pageable caller memory: gather on the host into a page-locked staging buffer
+				h_coff.resize(n_act); h_clen.resize(n_act);
+				MAP_CUDA(cudaMemcpyAsync(h_coff.data(), ix->coff.p, (size_t)n_act * 8, cudaMemcpyDeviceToHost, S));
+				MAP_CUDA(cudaMemcpyAsync(h_clen.data(), ix->clen.p, (size_t)n_act * 4, cudaMemcpyDeviceToHost, S));
+				MAP_CUDA(cudaStreamSynchronize(S));
+				const size_t need = (size_t)n_act * lazy_stride * 4;
+				if (ix->pin_sig_cap < need) {
+					if (ix->pin_sig) cudaFreeHost(ix->pin_sig);
+					ix->pin_sig = nullptr; ix->pin_sig_cap = 0;
+					MAP_CUDA(cudaMallocHost(&ix->pin_sig, need)); ix->pin_sig_cap = need;
+				}
+				float *stg = static_cast<float *>(ix->pin_sig);
+				uint64_t moved = 0;
+				for (uint32_t i = 0; i < n_act; ++i) { memcpy(stg + (size_t)i * lazy_stride, sig + h_coff[i], (size_t)h_clen[i] * 4); moved += h_clen[i]; }
+				MAP_CUDA(cudaMemcpyAsync(ix->sig.p, stg, need, cudaMemcpyHostToDevice, S));
+				k_dense_coff<<<(n_act + 255) / 256, 256, 0, S>>>(ix->coff.as<uint64_t>(), n_act, lazy_stride); ++launches;
+				stt.h2d_bytes += 4 * moved;
+				stt.d2h_bytes += (uint64_t)n_act * 12;
+			}
+			MAP_CUDA(cudaStreamSynchronize(S));                     // K1 runs on the context's streams: the round arena must be complete
+			stt.decode_ms += clk.lap();
+		}
 		// ---- K1 over the round's chunks, appended to the reads' event arrays ------------------------------------------
 		const uint64_t round_cap = (uint64_t)n_act * events_bound(max_len, w1, w2);
 		if ((rc = ix->ev_round.reserve(round_cap * 4)) || (rc = ix->seeds_h.reserve(round_cap * 4)) || (rc = ix->seeds_p.reserve(round_cap * 4)) ||
@@ -307,6 +381,8 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 	}
 	MAP_CUDA(cudaMemcpyAsync(out, ix->paf.p, (size_t)n_reads * sizeof(ra_paf_t), cudaMemcpyDeviceToHost, S));
 	MAP_CUDA(cudaStreamSynchronize(S));
+	stt.d2h_bytes += (uint64_t)n_reads * sizeof(ra_paf_t) + 64ull * stt.rounds;
+	if (lazy) { ix->last_off.clear(); ix->last_len.clear(); }       // nothing resident to map again
 	for (auto &x : cig_alns) out[x.first].alns = x.second;          // alns:f: prints chains[0].alignment_score after align_chain(cigar=true) has rewritten it (:306, :741)
 	stt.select_ms += clk.lap();
 	stt.total_ms = total.lap();

@@ -62,6 +62,7 @@ k_round_setup(ReadState *__restrict__ st, uint32_t n_reads, Params P, uint32_t *
 			const uint32_t len = min(P.chunk_size, s.l_sig - s.chunk_start);                      // rmap.cpp:686-687
 			act[i] = r; coff[i] = s.sig_off + s.chunk_start; clen[i] = len;
 			atomicMax(&maxlen_s, len);
+			atomicAdd(reinterpret_cast<unsigned long long *>(counters + 14), (unsigned long long)len);   // [14..15]: samples of the round
 		}
 		__syncthreads();
 		if (tid == 0) base_s = base + total;

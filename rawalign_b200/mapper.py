@@ -61,6 +61,35 @@ class Index:
                                              C.cast(fp, C.c_void_p), C.cast(rp, C.c_void_p), len(keys), keys.ctypes.data, ko.ctypes.data, vals.ctypes.data, C.byref(h)))
         return cls(ctx, h, tab.get("names"))
 
+    @classmethod
+    def build(cls, ctx, seqs, pore_vals, *, e: int, q: int, lq: int, k: int = 6, names=None) -> "Index":
+        """ri_idx_gen on the device (ra_index_build): seqs = uint8 arrays of base codes 0..3 (ACGT), 4 = ambiguous; pore_vals =
+        the 4^k level means of the pore model.  Parameters as ri_idx_init stores them (rawindex.cpp:9-24); w = n = 0."""
+        ss = [np.ascontiguousarray(s, np.uint8) for s in seqs]
+        n_seq = len(ss)
+        sp = (C.c_void_p * n_seq)(*[a.ctypes.data for a in ss])
+        sl = np.array([len(a) for a in ss], np.uint32)
+        pv = np.ascontiguousarray(pore_vals, np.float32)
+        if pv.size != 4 ** k:
+            raise ValueError(f"pore model has {pv.size} levels, 4^{k} expected")
+        h = C.c_void_p()
+        check(_lib.load().ra_index_build(ctx._h, e, q, lq, k, n_seq, C.cast(sp, C.c_void_p), sl.ctypes.data, pv.ctypes.data, C.byref(h)))
+        return cls(ctx, h, names)
+
+    def clone(self, ctx) -> "Index":
+        """ra_index_clone: the same index for another context, copied device to device."""
+        h = C.c_void_p()
+        check(self._L.ra_index_clone(self._h, ctx._h, C.byref(h)))
+        return Index(ctx, h, self.names)
+
+    def export(self) -> dict:
+        """ra_index_export: the seed table as (keys ascending, key_off, positions ascending per key) -- parse_index_file's form."""
+        nk = C.c_uint64(); nv = C.c_uint64()
+        check(self._L.ra_index_export(self._h, C.byref(nk), C.byref(nv), None, None, None))
+        keys = np.zeros(nk.value, np.uint64); ko = np.zeros(nk.value + 1, np.uint64); vals = np.zeros(max(nv.value, 1), np.uint64)
+        check(self._L.ra_index_export(self._h, C.byref(nk), C.byref(nv), keys.ctypes.data, ko.ctypes.data, vals.ctypes.data))
+        return dict(keys=keys, key_off=ko, vals=vals[:nv.value])
+
     def tables(self):
         """[(device pointer, bytes)] of the hash slots, the position array and the reference mirror (ra_index_tables)."""
         ptrs = (C.c_void_p * 3)(); nb = (C.c_uint64 * 3)()

@@ -180,3 +180,110 @@ def test_index_replica_by_copy(mg, flat, tmp_path):
             assert rep.paf_lines(rec) == str(mg["paf"][0]).split("\n")
         finally:
             rep.close()
+
+
+def _dev_f32(ptr, n):
+    import torch
+
+    class _V:
+        __cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (ptr, False), "version": 2}
+    return torch.as_tensor(_V(), device="cuda:0").cpu().numpy()
+
+
+@pytest.mark.parametrize("preset,lens,contract", [("sensitive", [300_000], 1), ("fast", [150_000, 9, 40_000, 777], 1), ("viral", [29_903, 5_000], 0)])
+def test_index_build_on_device_equals_the_reference_table(preset, lens, contract):
+    """f4: ra_index_build (ri_idx_gen on the device) -- the exported seed table, the expected signals in the mirror and the PAF
+    mapped through the built index equal those of the pinned restatement of rawindex.cpp / rsig.cpp (which test_map_oracle pins
+    against index files the reference wrote).  Ambiguous bases, a sequence of exactly k bases, both contraction modes."""
+    import rawalign_b200 as ra
+    from oracle import PRESETS, build_flat_index
+    from oracle.gen_golden_map import CONFIGS
+    from workload import synth
+    rng = np.random.default_rng(77)
+    seqs = [synth.random_reference(int(n), seed=300 + i) for i, n in enumerate(lens)]
+    for s in seqs:
+        if len(s) > 1000:
+            s[rng.integers(0, len(s), 40)] = 4                       # N bases (seq_nt4_table -> 4)
+            s[500:530] = 4
+    pore = synth.pore_model_as_loaded()
+    tab = build_flat_index(seqs, pore, preset, contract=contract)
+    e, q, lq, w, n = PRESETS[preset]
+    rd = synth.simulate_reads(np.where(seqs[0] < 4, seqs[0], 0).astype(np.uint8), 48, seed=21, max_chunks=6)
+    sig = rd.sig.astype(np.float32)
+    kw = CONFIGS[0][1]
+    with ra.Context(0) as ctx:
+        o = ctx.opt; o.fp_contract = contract; ctx.set_opt(o)
+        with ra.Index.build(ctx, seqs, pore, e=e, q=q, lq=lq, k=6) as ix:      # (one index per context at a time: the mirror is the context's)
+            got = ix.export()
+            assert np.array_equal(got["keys"], tab["keys"]) and np.array_equal(got["key_off"], tab["key_off"]) and np.array_equal(got["vals"], tab["vals"])
+            assert ix.counts()[6:] == [len(seqs), len(tab["keys"]), len(tab["vals"])]
+            ptr, nbytes = ix.tables()[2]
+            mirror = _dev_f32(ptr, nbytes // 4)
+            want = np.concatenate([np.concatenate((f, r)) for f, r in zip(tab["fwd"], tab["rev"])])
+            assert mirror.shape == want.shape and np.array_equal(bits(mirror), bits(want))
+            rec, _ = ix.map_reads(_opt(kw), sig=sig, sig_off=rd.read_off[:-1], sig_len=rd.read_len)
+            got_paf = ix.paf_lines(rec)
+        with ra.Index.load_flat(ctx, tab) as ref_ix:
+            rec2, _ = ref_ix.map_reads(_opt(kw), sig=sig, sig_off=rd.read_off[:-1], sig_len=rd.read_len)
+            assert got_paf == ref_ix.paf_lines(rec2)
+            assert rec2["mapped"].sum() >= 20
+
+
+def test_index_build_rejects_bad_input():
+    import rawalign_b200 as ra
+    from workload import synth
+    pore = synth.pore_model_as_loaded()
+    with ra.Context(0) as ctx:
+        with pytest.raises(ra.RawAlignError):
+            ra.Index.build(ctx, [np.zeros(5, np.uint8)], pore, e=6, q=9, lq=3, k=6)          # shorter than k
+        with pytest.raises(ra.RawAlignError):
+            ra.Index.build(ctx, [np.zeros(500, np.uint8)], pore, e=12, q=9, lq=3, k=6)        # e out of range
+        with pytest.raises(ValueError):
+            ra.Index.build(ctx, [np.zeros(500, np.uint8)], pore[:100], e=6, q=9, lq=3, k=6)
+        with ra.Index.build(ctx, [np.arange(6, dtype=np.uint8) % 4, np.arange(40, dtype=np.uint8) % 4], pore, e=6, q=9, lq=3, k=6) as ix:
+            assert ix.counts()[6] == 2                                                        # one k-mer: no seeds, no crash
+
+
+def test_index_clone_for_a_second_context(mg, flat):
+    """ra_index_clone: the batches in flight on one GPU share one parse of the index file."""
+    import rawalign_b200 as ra
+    from oracle.gen_golden_map import CONFIGS
+    off, sc = _dac(len(mg["raw_len"]))
+    with ra.Context(0) as c0, ra.Context(0) as c1, ra.Index.load_flat(c0, flat["sensitive"]) as ix0, ix0.clone(c1) as ix1:
+        assert ix1.counts() == ix0.counts() and ix1.names == ix0.names
+        rec, _ = ix1.map_reads(_opt(CONFIGS[0][1]), raw=mg["raw"], raw_off=mg["raw_off"], raw_len=mg["raw_len"], offset=off, scale=sc)
+        assert ix1.paf_lines(rec) == str(mg["paf"][0]).split("\n")
+        a, b = ix0.export(), ix1.export()
+        assert all(np.array_equal(a[k], b[k]) for k in a)
+
+
+def test_float_form_uploads_per_round_from_pinned_and_pageable_memory(mg, flat):
+    """The float form moves only the chunk each active read is at: straight from page-locked caller memory (mapped reads by the
+    GPU, any alignment), through a staging buffer from pageable memory; "map_sig_whole" uploads everything and leaves the batch
+    resident.  Same records every way, and the bytes moved are the chunks consumed."""
+    import torch
+    import rawalign_b200 as ra
+    from oracle.gen_golden_map import CONFIGS
+    from workload import synth
+    sig = ((mg["raw"].astype(np.float32) + np.float32(synth.DAC_OFFSET)) * (np.float32(synth.DAC_RANGE) / np.float32(synth.DAC_DIGITISATION))).astype(np.float32)
+    pinned = torch.from_numpy(sig).pin_memory().numpy()
+    shifted = torch.from_numpy(np.concatenate((np.zeros(1, np.float32), sig))).pin_memory().numpy()      # every chunk starts 4 bytes off a 16-byte line
+    n = len(mg["raw_len"])
+    off, ln = mg["raw_off"], mg["raw_len"]
+    opt = _opt(CONFIGS[0][1])
+    with ra.Context(0) as ctx, ra.Index.load_flat(ctx, flat["sensitive"]) as ix:
+        rec_a, st_a = ix.map_reads(opt, sig=sig, sig_off=off, sig_len=ln)
+        rec_b, st_b = ix.map_reads(opt, sig=pinned, sig_off=off, sig_len=ln)
+        rec_s, st_s = ix.map_reads(opt, sig=shifted, sig_off=off + np.uint64(1), sig_len=ln)
+        with pytest.raises(ra.RawAlignError):
+            ix.map_reads(opt, resident_reads=n)                     # nothing was left on the device
+        ctx.set_tuning("map_sig_whole", 1)
+        rec_c, st_c = ix.map_reads(opt, sig=pinned, sig_off=off, sig_len=ln)
+        rec_d, _ = ix.map_reads(opt, resident_reads=n)
+        got = ix.paf_lines(rec_b)
+    assert got == str(mg["paf"][0]).split("\n")
+    assert rec_a.tobytes() == rec_b.tobytes() == rec_s.tobytes() == rec_c.tobytes() == rec_d.tobytes()
+    consumed = 4 * sum(int(min(4000, max(0, int(l) - 4000 * c))) for l, ci in zip(ln, rec_b["ci"]) for c in range(int(ci)))
+    for st in (st_a, st_b, st_s):
+        assert 0 <= st["h2d_bytes"] - consumed < 64 * n + 4096
+    assert st_c["h2d_bytes"] >= int(ln.sum()) * 4 > st_b["h2d_bytes"]

@@ -30,13 +30,12 @@ CONFIGS = {
     "C3": dict(desc="C3: C2 + --dtw-output-cigar", ref=[5_000_000], preset="sensitive",
                opt=dict(flag=RI_M_DTW_EVALUATE_CHAINS | RI_M_DTW_OUTPUT_CIGAR, dtw_border_constraint=1, dtw_fill_method=1, dtw_band_radius_frac=0.10)),
     "C4": dict(desc="C4: multi-genome synthetic index (20 genomes + one 30 kb viral target, contamination-style), -x fast, global border, full matrix",
-               ref=[2_000_000, 500_000, 4_000_000, 1_000_000, 3_000_000, 700_000, 1_500_000, 2_500_000, 600_000, 900_000,
-                    1_200_000, 800_000, 3_500_000, 1_100_000, 650_000, 1_800_000, 2_200_000, 550_000, 1_300_000, 950_000, 30_000],
+               ref=[6_500_000, 1_625_000, 13_000_000, 3_250_000, 9_750_000, 2_275_000, 4_875_000, 8_125_000, 1_950_000, 2_925_000,
+                    3_900_000, 2_600_000, 11_375_000, 3_575_000, 2_112_500, 5_850_000, 7_150_000, 1_787_500, 4_225_000, 3_087_500, 30_000],
                preset="fast", opt=dict(flag=RI_M_DTW_EVALUATE_CHAINS, dtw_border_constraint=0, dtw_fill_method=0),
-               viral_frac=0.10, note="30.7 Mb of genomes instead of ~100 Mb: the index builder on this path is the CPU reference's"),
+               viral_frac=0.10),
     "C5": dict(desc="C5: chromosome-scale synthetic reference, -x fast --dtw-evaluate-chains, banded=0.15",
-               ref=[50_000_000], preset="fast", opt=dict(flag=RI_M_DTW_EVALUATE_CHAINS, dtw_band_radius_frac=0.15),
-               note="50 Mb instead of ~250 Mb (index construction time on the host); seed-hit density per read scales with the reference"),
+               ref=[250_000_000], preset="fast", opt=dict(flag=RI_M_DTW_EVALUATE_CHAINS, dtw_band_radius_frac=0.15)),
 }
 
 

@@ -73,8 +73,6 @@ def simulate_reads(ref: np.ndarray, n_reads: int, seed: int = 2, mean_len: float
     mm, ms = model or pore_model()
     rng = np.random.default_rng(seed)
     L = len(ref)
-    fwd_rank = kmer_ranks(ref)
-    rev_rank = kmer_ranks(3 - ref[::-1])
     nb = np.clip(rng.lognormal(np.log(mean_len), 0.5, n_reads), 1000, min(50000, L - K)).astype(np.int64)
     max_bases = int(max_chunks * CHUNK_SIZE / SAMPLES_PER_BASE * 1.3) + 64
     nb = np.minimum(nb, max_bases)
@@ -82,7 +80,8 @@ def simulate_reads(ref: np.ndarray, n_reads: int, seed: int = 2, mean_len: float
     start = (rng.random(n_reads) * (L - K + 1 - nb)).astype(np.int64)
     sigs, lens, bstarts = [], [], []
     for r in range(n_reads):
-        ranks = (fwd_rank if strand[r] == 0 else rev_rank)[start[r]:start[r] + nb[r]]
+        a, b = int(start[r]), int(start[r] + nb[r]) + K - 1        # k-mer ranks of the read's bases only (the reference can be 250 Mb)
+        ranks = kmer_ranks(ref[a:b] if strand[r] == 0 else (3 - ref[L - b:L - a][::-1]))
         dwell = 1 + rng.poisson(7.9, nb[r])
         lv = np.repeat(mm[ranks], dwell); sd = np.repeat(ms[ranks], dwell)
         s = lv + rng.normal(0.0, 1.0, len(lv)) * sd
