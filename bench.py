@@ -611,7 +611,8 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
     # MAP_DEPTH batches in flight per GPU (one context + index each, one host thread each), as a map loop with double-buffered
     # mini-batches runs: one batch's uploads and host round trips overlap the other's kernels.  Every step does all of its work.
     # (a 250 Mb index is 23 GB and its rounds hold ~0.8 G anchors: two batches in flight fit 180 GB, three do not)
-    depth = max(1, int(os.environ.get("RA_BENCH_MAP_DEPTH", 2 if sum(cfg["ref"]) >= 200_000_000 else 3)))
+    ref_bases = sum(cfg["ref"])
+    depth = max(1, int(os.environ.get("RA_BENCH_MAP_DEPTH", 2 if ref_bases >= 200_000_000 else 3 if ref_bases >= 50_000_000 else 4)))
     opt = ra.ri_mapopt_full(**cfg["opt"])
     want_cigar = bool(opt.flag & 0x4)
     pipes = []

@@ -22,24 +22,37 @@ __global__ void k_init_state(ReadState *__restrict__ st, uint32_t n_reads, const
 __global__ void __launch_bounds__(256)
 k_gather_chunks(const float *__restrict__ hsig, uint64_t *__restrict__ coff, const uint32_t *__restrict__ clen, uint32_t n_act, float *__restrict__ dst, uint32_t stride)
 {
-	const uint32_t i = blockIdx.x;
-	if (i >= n_act) return;
-	const float *__restrict__ src = hsig + coff[i];
-	const uint32_t n = clen[i];
-	float *__restrict__ d = dst + (size_t)i * stride;
-	const uint32_t head = min(n, (uint32_t)(((16u - (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15u)) & 15u) >> 2));
-	if (threadIdx.x < head) d[threadIdx.x] = src[threadIdx.x];
-	const float4 *__restrict__ s4 = reinterpret_cast<const float4 *>(src + head);
-	const uint32_t n4 = (n - head) >> 2;
-	for (uint32_t k = threadIdx.x; k < n4; k += 256) {
-		const float4 v = s4[k];
-		float *o = d + head + 4u * k;
-		o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w;
+	// a small persistent grid (PCIe needs ~100 KB in flight, not the whole machine: the other batches' kernels keep their SM slots),
+	// one warp per chunk at a time, four 16-byte loads in flight per lane
+	const int lane = threadIdx.x & 31;
+	const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+	for (uint32_t i = warp; i < n_act; i += n_warps) {
+		const float *__restrict__ src = hsig + coff[i];
+		const uint32_t n = clen[i];
+		float *__restrict__ d = dst + (size_t)i * stride;
+		const uint32_t head = min(n, (uint32_t)(((16u - (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15u)) & 15u) >> 2));
+		if ((uint32_t)lane < head) d[lane] = src[lane];
+		const float4 *__restrict__ s4 = reinterpret_cast<const float4 *>(src + head);
+		const uint32_t n4 = (n - head) >> 2;
+		uint32_t k = lane;
+		for (; k + 96 < n4; k += 128) {
+			const float4 v0 = s4[k], v1 = s4[k + 32], v2 = s4[k + 64], v3 = s4[k + 96];
+			float *o = d + head + 4u * k;
+			o[0] = v0.x; o[1] = v0.y; o[2] = v0.z; o[3] = v0.w;
+			o[128] = v1.x; o[129] = v1.y; o[130] = v1.z; o[131] = v1.w;
+			o[256] = v2.x; o[257] = v2.y; o[258] = v2.z; o[259] = v2.w;
+			o[384] = v3.x; o[385] = v3.y; o[386] = v3.z; o[387] = v3.w;
+		}
+		for (; k < n4; k += 32) {
+			const float4 v = s4[k];
+			float *o = d + head + 4u * k;
+			o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w;
+		}
+		const uint32_t tail0 = head + 4u * n4;
+		if (tail0 + (uint32_t)lane < n) d[tail0 + lane] = src[tail0 + lane];
+		__syncwarp();
+		if (lane == 0) coff[i] = (uint64_t)i * stride;
 	}
-	const uint32_t tail0 = head + 4u * n4;
-	if (tail0 + threadIdx.x < n) d[tail0 + threadIdx.x] = src[tail0 + threadIdx.x];
-	__syncthreads();
-	if (threadIdx.x == 0) coff[i] = (uint64_t)i * stride;
 }
 
 __global__ void k_dense_coff(uint64_t *__restrict__ coff, uint32_t n_act, uint32_t stride)
@@ -208,7 +221,7 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 		if (lazy) {
 			if ((rc = ix->sig.reserve((uint64_t)n_act * lazy_stride * 4 + 64))) return rc;
 			if (hsig_dev) {
-				k_gather_chunks<<<n_act, 256, 0, S>>>(hsig_dev, ix->coff.as<uint64_t>(), ix->clen.as<uint32_t>(), n_act, ix->sig.as<float>(), lazy_stride); ++launches;
+				k_gather_chunks<<<std::min<uint32_t>((n_act + 7) / 8, 148), 256, 0, S>>>(hsig_dev, ix->coff.as<uint64_t>(), ix->clen.as<uint32_t>(), n_act, ix->sig.as<float>(), lazy_stride); ++launches;
 				stt.h2d_bytes += 4ull * *reinterpret_cast<const uint64_t *>(hc + 14);
 			} else {                                                // pageable caller memory: gather on the host into a page-locked staging buffer
 				h_coff.resize(n_act); h_clen.resize(n_act);
@@ -275,6 +288,7 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 			MAP_CUDA(cudaFuncSetAttribute(k_sort_segments, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kSortSmem * 8)));
 			MAP_CUDA(cudaFuncSetAttribute(k_sort_buckets<kBucketMaxKeys, 0u>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BucketSmemT<kBucketMaxKeys>)));
 			MAP_CUDA(cudaFuncSetAttribute(k_sort_buckets<kBucketMaxKeysL, kBucketMaxKeys>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BucketSmemT<kBucketMaxKeysL>)));
+			MAP_CUDA(cudaFuncSetAttribute(k_sort_buckets<0u, kBucketMaxKeysL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BucketSmemT<0u>)));
 			ix->sort_attr = true;
 		}
 		uint32_t done_n = 0;

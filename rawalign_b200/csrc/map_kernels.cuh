@@ -303,14 +303,58 @@ constexpr uint32_t kBins = 4096;
 constexpr uint32_t kBucketMaxKeys = 8192;                          // the common size class: three CTAs per SM
 constexpr uint32_t kBucketMaxKeysL = 20480;                        // long segments (reads with several chunks of anchors): one CTA per SM
 constexpr int kBucketThreads = 512;
+constexpr uint32_t kGroupKeys = 8192;                              // MAXK == 0: keys of one run of bins finished in shared memory
 template <uint32_t MAXK>
 struct BucketSmemT {
-	uint64_t keys[MAXK ? MAXK : 1];                                // MAXK == 0: the keys are staged in a global-memory arena instead
+	uint64_t keys[MAXK ? MAXK : kGroupKeys];                       // MAXK == 0: the binned keys are staged in a global-memory arena; keys[] holds one run of bins at a time
 	uint32_t count[kBins + 1];
 	uint32_t cursor[kBins];
 	uint32_t warp_tot[kBucketThreads / 32];
 };
 using BucketSmem = BucketSmemT<kBucketMaxKeys>;
+
+// finishes bins [b0, b1) of a binned key array (wk[0] is the key at position base, count[b] = start of bin b): small bins by one
+// thread each (insertion sort), crowded ones by a whole warp afterwards
+__device__ __forceinline__ void finish_bins(uint64_t *wk, uint32_t base, const uint32_t *count, uint32_t b0, uint32_t b1, int tid, int lane, int wid)
+{
+	constexpr uint32_t kSmall = 24;
+	for (uint32_t b = b0 + tid; b < b1; b += kBucketThreads) {
+		const uint32_t lo = count[b], m = count[b + 1] - lo;
+		if (m < 2 || m > kSmall) continue;
+		uint64_t *w = wk + (lo - base);
+		for (uint32_t a = 1; a < m; ++a) {
+			const uint64_t x = w[a];
+			uint32_t c = a;
+			while (c > 0 && w[c - 1] > x) { w[c] = w[c - 1]; --c; }
+			w[c] = x;
+		}
+	}
+	for (uint32_t b = b0 + wid; b < b1; b += kBucketThreads / 32) {   // warp-uniform loop
+		const uint32_t lo = count[b], m = count[b + 1] - lo;
+		if (m <= kSmall) continue;
+		uint32_t pad = 32; while (pad < m) pad <<= 1;
+		uint64_t *w = wk + (lo - base);
+		// bitonic network in its all-ascending form (first step of every merge compares mirrored positions), over a virtual
+		// power-of-two range whose slots >= m hold +inf: every comparator moves the minimum to the lower index, so the
+		// virtual keys never move and only pairs of real keys are touched
+		for (uint32_t size = 2; size <= pad; size <<= 1) {
+			const uint32_t half = size >> 1;
+			for (uint32_t t = lane; t < (pad >> 1); t += 32) {
+				const uint32_t blk = t / half, off = t - blk * half;
+				const uint32_t l0 = blk * size + off, h0 = blk * size + size - 1u - off;
+				if (h0 < m) { const uint64_t x = w[l0], y = w[h0]; if (x > y) { w[l0] = y; w[h0] = x; } }
+			}
+			__syncwarp();
+			for (uint32_t stride = half >> 1; stride > 0; stride >>= 1) {
+				for (uint32_t t = lane; t < (pad >> 1); t += 32) {
+					const uint32_t l0 = 2 * t - (t & (stride - 1)), h0 = l0 + stride;
+					if (h0 < m) { const uint64_t x = w[l0], y = w[h0]; if (x > y) { w[l0] = y; w[h0] = x; } }
+				}
+				__syncwarp();
+			}
+		}
+	}
+}
 
 __device__ __forceinline__ uint32_t key_bin(uint64_t k, const uint32_t *__restrict__ bin_base, uint32_t tshift)
 {
@@ -359,45 +403,36 @@ k_sort_buckets(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_bas
 		wk[atomicAdd(&sm.cursor[key_bin(key, bin_base, tshift)], 1u)] = key;
 	}
 	__syncthreads();
-	// finish the bins: small ones by one thread each, crowded ones by a whole warp afterwards
-	constexpr uint32_t kSmall = 24;
-	for (uint32_t b = tid; b < n_bins; b += kBucketThreads) {
-		const uint32_t lo = sm.count[b], hi = sm.count[b + 1];
-		if (hi - lo < 2 || hi - lo > kSmall) continue;
-		for (uint32_t a = lo + 1; a < hi; ++a) {
-			const uint64_t x = wk[a];
-			uint32_t c = a;
-			while (c > lo && wk[c - 1] > x) { wk[c] = wk[c - 1]; --c; }
-			wk[c] = x;
-		}
+	if (MAXK) {
+		finish_bins(wk, 0, sm.count, 0, n_bins, tid, lane, wid);
+		__syncthreads();
+		for (uint32_t k = tid; k < n; k += kBucketThreads) g[k] = wk[k];
+		return;
 	}
-	for (uint32_t b = wid; b < n_bins; b += kBucketThreads / 32) {   // warp-uniform loop
-		const uint32_t lo = sm.count[b], m = sm.count[b + 1] - lo;
-		if (m <= kSmall) continue;
-		uint32_t pad = 32; while (pad < m) pad <<= 1;
-		uint64_t *w = wk + lo;
-		// bitonic network in its all-ascending form (first step of every merge compares mirrored positions), over a virtual
-		// power-of-two range whose slots >= m hold +inf: every comparator moves the minimum to the lower index, so the
-		// virtual keys never move and only pairs of real keys are touched
-		for (uint32_t size = 2; size <= pad; size <<= 1) {
-			const uint32_t half = size >> 1;
-			for (uint32_t t = lane; t < (pad >> 1); t += 32) {
-				const uint32_t blk = t / half, off = t - blk * half;
-				const uint32_t l0 = blk * size + off, h0 = blk * size + size - 1u - off;
-				if (h0 < m) { const uint64_t x = w[l0], y = w[h0]; if (x > y) { w[l0] = y; w[h0] = x; } }
-			}
-			__syncwarp();
-			for (uint32_t stride = half >> 1; stride > 0; stride >>= 1) {
-				for (uint32_t t = lane; t < (pad >> 1); t += 32) {
-					const uint32_t l0 = 2 * t - (t & (stride - 1)), h0 = l0 + stride;
-					if (h0 < m) { const uint64_t x = w[l0], y = w[h0]; if (x > y) { w[l0] = y; w[h0] = x; } }
-				}
-				__syncwarp();
-			}
+	// MAXK == 0: the binned keys sit in global memory; runs of consecutive bins that fit the group buffer are finished in shared
+	// memory and written straight to their final place (a single bin larger than the buffer is finished where it is)
+	uint32_t b0 = 0;
+	while (b0 < n_bins) {                                          // CTA-uniform
+		const uint32_t lo = sm.count[b0];
+		uint32_t b1 = b0, step = 1;
+		while (b1 + step <= n_bins && sm.count[b1 + step] - lo <= kGroupKeys) { b1 += step; step <<= 1; }   // gallop, then bisect
+		for (step >>= 1; step > 0; step >>= 1) if (b1 + step <= n_bins && sm.count[b1 + step] - lo <= kGroupKeys) b1 += step;
+		if (b1 == b0) {                                             // one crowded bin beyond the buffer
+			b1 = b0 + 1;
+			finish_bins(wk, 0, sm.count, b0, b1, tid, lane, wid);
+			__syncthreads();
+			for (uint32_t k = lo + tid; k < sm.count[b1]; k += kBucketThreads) g[k] = wk[k];
+		} else {
+			const uint32_t m = sm.count[b1] - lo;
+			for (uint32_t k = tid; k < m; k += kBucketThreads) sm.keys[k] = wk[lo + k];
+			__syncthreads();
+			finish_bins(sm.keys, lo, sm.count, b0, b1, tid, lane, wid);
+			__syncthreads();
+			for (uint32_t k = tid; k < m; k += kBucketThreads) g[lo + k] = sm.keys[k];
 		}
+		__syncthreads();
+		b0 = b1;
 	}
-	__syncthreads();
-	for (uint32_t k = tid; k < n; k += kBucketThreads) g[k] = wk[k];
 }
 
 } // namespace mapk

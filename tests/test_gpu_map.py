@@ -287,3 +287,27 @@ def test_float_form_uploads_per_round_from_pinned_and_pageable_memory(mg, flat):
     for st in (st_a, st_b, st_s):
         assert 0 <= st["h2d_bytes"] - consumed < 64 * n + 4096
     assert st_c["h2d_bytes"] >= int(ln.sum()) * 4 > st_b["h2d_bytes"]
+
+
+def test_repetitive_reference_long_anchor_segments():
+    """A tandem-repeat reference (500 copies of a 600-base unit) gives every chunk tens of thousands of anchors: the anchor sort's largest size class
+    (binned keys staged in global memory, runs of bins finished in shared memory) and long chaining lists; all PAF fields equal
+    the pinned restatement's."""
+    import rawalign_b200 as ra
+    from oracle import MapOracle, build_flat_index
+    from workload import synth
+    unit = synth.random_reference(600, seed=71)
+    ref = np.concatenate([synth.random_reference(20_000, seed=72)] + [unit] * 500 + [synth.random_reference(20_000, seed=73)])
+    tab = build_flat_index([ref], synth.pore_model_as_loaded(), "sensitive")
+    rd = synth.simulate_reads(ref[20_000:20_000 + 300_000], 12, seed=5, max_chunks=3)
+    sig = rd.sig.astype(np.float32)
+    kw = dict(flag=2, max_num_chunk=3)
+    mo = MapOracle(tab)
+    want = mo.map_reads(mo.mapopt(**kw), sig, rd.read_off[:-1], rd.read_len)
+    with ra.Context(0) as ctx, ra.Index.load_flat(ctx, tab) as ix:
+        rec, st = ix.map_reads(_opt(kw), sig=sig, sig_off=rd.read_off[:-1], sig_len=rd.read_len)
+        got_lines = ix.paf_lines(rec)
+    assert st["anchors"] > 12 * 20480
+    assert got_lines == mo.paf_lines(want)
+    for f in ("s1", "s2", "sm", "at", "aq"):
+        assert np.array_equal(bits(rec[f]), bits(want[f])), f
