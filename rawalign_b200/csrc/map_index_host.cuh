@@ -106,13 +106,14 @@ extern "C" int ra_index_export(ra_index *ix, uint64_t *n_keys, uint64_t *n_vals,
 	std::vector<uint64_t> v(ix->n_vals);
 	MAP_CUDA(cudaMemcpy(slots.data(), ix->slots.p, n_slots * sizeof(Slot), cudaMemcpyDeviceToHost));
 	if (ix->n_vals) MAP_CUDA(cudaMemcpy(v.data(), ix->vals.p, ix->n_vals * 8, cudaMemcpyDeviceToHost));
-	std::vector<uint32_t> used;
-	for (uint64_t h = 0; h < n_slots; ++h) if (slots[h].cnt) used.push_back((uint32_t)h);
+	std::vector<uint64_t> used;                                    // key << 32 | slot: sorts by key without touching the table
+	used.reserve(ix->n_keys);
+	for (uint64_t h = 0; h < n_slots; ++h) if (slots[h].cnt) used.push_back(((uint64_t)slots[h].key << 32) | h);
 	if (used.size() != ix->n_keys) return ra__fail(RA_EINVAL, "index table holds %zu keys, %llu expected", used.size(), (unsigned long long)ix->n_keys);
-	std::sort(used.begin(), used.end(), [&](uint32_t a, uint32_t b) { return slots[a].key < slots[b].key; });
+	std::sort(used.begin(), used.end());
 	uint64_t w = 0;
 	for (size_t i = 0; i < used.size(); ++i) {
-		const Slot &s = slots[used[i]];
+		const Slot &s = slots[(uint32_t)used[i]];
 		keys[i] = s.key; key_off[i] = w;
 		std::copy(v.begin() + s.off, v.begin() + s.off + s.cnt, vals + w);
 		std::sort(vals + w, vals + w + s.cnt);

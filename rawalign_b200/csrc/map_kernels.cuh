@@ -303,14 +303,37 @@ constexpr uint32_t kBins = 4096;
 constexpr uint32_t kBucketMaxKeys = 8192;                          // the common size class: three CTAs per SM
 constexpr uint32_t kBucketMaxKeysL = 20480;                        // long segments (reads with several chunks of anchors): one CTA per SM
 constexpr int kBucketThreads = 512;
-constexpr uint32_t kGroupKeys = 8192;                              // MAXK == 0: keys of one run of bins finished in shared memory
+constexpr uint32_t kGroupKeys = 4096;                              // MAXK == 0: keys of one run of bins finished in shared memory
+constexpr uint32_t kFineBins = 2048;                               // MAXK == 0: the run is binned again, up to 2^F times finer
 template <uint32_t MAXK>
 struct BucketSmemT {
 	uint64_t keys[MAXK ? MAXK : kGroupKeys];                       // MAXK == 0: the binned keys are staged in a global-memory arena; keys[] holds one run of bins at a time
+	uint64_t keys2[MAXK ? 1 : kGroupKeys];                         // MAXK == 0: the run after the second binning
+	uint32_t fine[MAXK ? 1 : kFineBins + 1];
 	uint32_t count[kBins + 1];
 	uint32_t cursor[kBins];
 	uint32_t warp_tot[kBucketThreads / 32];
 };
+
+// exclusive scan of a[0 .. n) in place by the whole CTA (a[n] is not written); cur[] receives a copy
+__device__ __forceinline__ void cta_exclusive_scan(uint32_t *a, uint32_t *cur, uint32_t n, uint32_t *warp_tot, int tid, int lane, int wid)
+{
+	uint32_t carry = 0;
+	for (uint32_t b0 = 0; b0 < n; b0 += kBucketThreads) {
+		const uint32_t b = b0 + tid;
+		const uint32_t v = b < n ? a[b] : 0u;
+		uint32_t inc = v;
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += y; }
+		if (lane == 31) warp_tot[wid] = inc;
+		__syncthreads();
+		uint32_t before = 0, total = 0;
+		for (int w = 0; w < kBucketThreads / 32; ++w) { const uint32_t t = warp_tot[w]; if (w < wid) before += t; total += t; }
+		if (b < n) { const uint32_t ex = carry + before + inc - v; a[b] = ex; cur[b] = ex; }
+		carry += total;
+		__syncthreads();
+	}
+}
 using BucketSmem = BucketSmemT<kBucketMaxKeys>;
 
 // finishes bins [b0, b1) of a binned key array (wk[0] is the key at position base, count[b] = start of bin b): small bins by one
@@ -381,21 +404,7 @@ k_sort_buckets(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_bas
 	for (uint32_t k = tid; k < n; k += kBucketThreads) atomicAdd(&sm.count[key_bin(g[k], bin_base, tshift)], 1u);
 	__syncthreads();
 	// exclusive scan of count[0 .. n_bins) -> cursor / count (count[b] becomes the start of bin b, count[n_bins] = n)
-	uint32_t carry = 0;
-	for (uint32_t b0 = 0; b0 < n_bins; b0 += kBucketThreads) {
-		const uint32_t b = b0 + tid;
-		const uint32_t v = b < n_bins ? sm.count[b] : 0u;
-		uint32_t inc = v;
-#pragma unroll
-		for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += y; }
-		if (lane == 31) sm.warp_tot[wid] = inc;
-		__syncthreads();
-		uint32_t before = 0, total = 0;
-		for (int w = 0; w < kBucketThreads / 32; ++w) { const uint32_t t = sm.warp_tot[w]; if (w < wid) before += t; total += t; }
-		if (b < n_bins) { const uint32_t ex = carry + before + inc - v; sm.count[b] = ex; sm.cursor[b] = ex; }
-		carry += total;
-		__syncthreads();
-	}
+	cta_exclusive_scan(sm.count, sm.cursor, n_bins, sm.warp_tot, tid, lane, wid);
 	if (tid == 0) sm.count[n_bins] = n;
 	__syncthreads();
 	for (uint32_t k = tid; k < n; k += kBucketThreads) {
@@ -409,26 +418,52 @@ k_sort_buckets(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_bas
 		for (uint32_t k = tid; k < n; k += kBucketThreads) g[k] = wk[k];
 		return;
 	}
-	// MAXK == 0: the binned keys sit in global memory; runs of consecutive bins that fit the group buffer are finished in shared
-	// memory and written straight to their final place (a single bin larger than the buffer is finished where it is)
+	// MAXK == 0: the binned keys sit in global memory.  Runs of consecutive bins that fit the group buffer are loaded into shared
+	// memory, binned a second time 2^F times finer (a long segment leaves tens of keys per first-level bin), finished there and
+	// written straight to their final place; a single bin larger than the buffer is finished where it is.
 	uint32_t b0 = 0;
 	while (b0 < n_bins) {                                          // CTA-uniform
 		const uint32_t lo = sm.count[b0];
 		uint32_t b1 = b0, step = 1;
-		while (b1 + step <= n_bins && sm.count[b1 + step] - lo <= kGroupKeys) { b1 += step; step <<= 1; }   // gallop, then bisect
-		for (step >>= 1; step > 0; step >>= 1) if (b1 + step <= n_bins && sm.count[b1 + step] - lo <= kGroupKeys) b1 += step;
+		auto fits = [&](uint32_t b) { return b <= n_bins && b - b0 <= kFineBins && sm.count[b] - lo <= kGroupKeys; };
+		while (fits(b1 + step)) { b1 += step; step <<= 1; }        // gallop, then bisect
+		for (step >>= 1; step > 0; step >>= 1) if (fits(b1 + step)) b1 += step;
 		if (b1 == b0) {                                             // one crowded bin beyond the buffer
 			b1 = b0 + 1;
 			finish_bins(wk, 0, sm.count, b0, b1, tid, lane, wid);
 			__syncthreads();
 			for (uint32_t k = lo + tid; k < sm.count[b1]; k += kBucketThreads) g[k] = wk[k];
 		} else {
-			const uint32_t m = sm.count[b1] - lo;
+			const uint32_t m = sm.count[b1] - lo, nb = b1 - b0;
+			uint32_t F = 0;
+			while (F < tshift && (nb << (F + 1)) <= kFineBins && (m >> F) > 2u * nb) ++F;   // until ~2 keys per fine bin
 			for (uint32_t k = tid; k < m; k += kBucketThreads) sm.keys[k] = wk[lo + k];
-			__syncthreads();
-			finish_bins(sm.keys, lo, sm.count, b0, b1, tid, lane, wid);
-			__syncthreads();
-			for (uint32_t k = tid; k < m; k += kBucketThreads) g[lo + k] = sm.keys[k];
+			if (F == 0) {
+				__syncthreads();
+				finish_bins(sm.keys, lo, sm.count, b0, b1, tid, lane, wid);
+				__syncthreads();
+				for (uint32_t k = tid; k < m; k += kBucketThreads) g[lo + k] = sm.keys[k];
+			} else {
+				const uint32_t nf = nb << F, fmask = (1u << F) - 1u, fsh = tshift - F;
+				for (uint32_t b = tid; b <= nf; b += kBucketThreads) sm.fine[b] = 0;
+				__syncthreads();
+				for (uint32_t k = tid; k < m; k += kBucketThreads) {
+					const uint64_t key = sm.keys[k];
+					atomicAdd(&sm.fine[((key_bin(key, bin_base, tshift) - b0) << F) | ((key_target(key) >> fsh) & fmask)], 1u);
+				}
+				__syncthreads();
+				cta_exclusive_scan(sm.fine, sm.cursor, nf, sm.warp_tot, tid, lane, wid);   // (cursor[] is free once the first-level scatter is done)
+				if (tid == 0) sm.fine[nf] = m;
+				__syncthreads();
+				for (uint32_t k = tid; k < m; k += kBucketThreads) {
+					const uint64_t key = sm.keys[k];
+					sm.keys2[atomicAdd(&sm.cursor[((key_bin(key, bin_base, tshift) - b0) << F) | ((key_target(key) >> fsh) & fmask)], 1u)] = key;
+				}
+				__syncthreads();
+				finish_bins(sm.keys2, 0, sm.fine, 0, nf, tid, lane, wid);
+				__syncthreads();
+				for (uint32_t k = tid; k < m; k += kBucketThreads) g[lo + k] = sm.keys2[k];
+			}
 		}
 		__syncthreads();
 		b0 = b1;

@@ -311,3 +311,31 @@ def test_repetitive_reference_long_anchor_segments():
     assert got_lines == mo.paf_lines(want)
     for f in ("s1", "s2", "sm", "at", "aq"):
         assert np.array_equal(bits(rec[f]), bits(want[f])), f
+
+
+def test_index_build_on_device_equals_the_reference_indexer_output(tmp_path):
+    """f4 pinned directly: the reference's unmodified indexer (oracle/_ref/rawalign -d) writes an index file for a FASTA; the table
+    and signals ra_index_build makes from the same bases are identical to the parsed file."""
+    import subprocess
+    import rawalign_b200 as ra
+    from oracle import PRESETS, parse_index_file
+    from workload import synth
+    from workload.mapbench import _ref_binary
+    rb = _ref_binary()
+    if rb is None:
+        pytest.skip("oracle/_ref/rawalign was not built in this checkout")
+    seqs = [synth.random_reference(n, seed=400 + i) for i, n in enumerate([250_000, 31_000, 4_321])]
+    fa, model, ind = str(tmp_path / "r.fa"), str(tmp_path / "m.txt"), str(tmp_path / "r.ind")
+    synth.write_fasta(fa, seqs); synth.write_pore_model(model)
+    r = subprocess.run([rb, "-x", "fast", "-t", "4", "-p", model, "-d", ind, fa], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
+    tab = parse_index_file(ind)
+    e, q, lq, w, n = PRESETS["fast"]
+    assert (tab["e"], tab["q"], tab["lq"]) == (e, q, lq)
+    with ra.Context(0) as ctx, ra.Index.build(ctx, seqs, synth.pore_model_as_loaded(), e=e, q=q, lq=lq, k=6) as ix:
+        got = ix.export()
+        ptr, nbytes = ix.tables()[2]
+        mirror = _dev_f32(ptr, nbytes // 4)
+    assert np.array_equal(got["keys"], tab["keys"]) and np.array_equal(got["key_off"], tab["key_off"]) and np.array_equal(got["vals"], tab["vals"])
+    want = np.concatenate([np.concatenate((f, r_)) for f, r_ in zip(tab["fwd"], tab["rev"])])
+    assert np.array_equal(bits(mirror), bits(want))
