@@ -730,7 +730,7 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
                "map_counts_per_step": {k: stc[k] for k in ("rounds", "chunks", "events", "seeds", "anchors", "chains_evaluated", "launches")},
                "e2e": {"value": reads_all * args.steps / dt_e2e, "unit": "reads/s", "ms_per_step": dt_e2e / args.steps * 1e3,
                        "h2d_bytes_per_step": int(st_e["h2d_bytes"]),
-                       "d2h_bytes_per_step": int(st_e["d2h_bytes"] + (20 * len(cig[0][1]) + cig[0][0].nbytes if want_cigar else 0)),
+                       "d2h_bytes_per_step": int(st_e["d2h_bytes"]),   # records + control words + (cigar) 12 B per path element, counted by the library
                        "input": "ri_sig_t of every read (float pA, l_sig) in pinned host memory -- what the reference's reader hands map_worker_for and what "
                                 "the reference arm is timed on -> ra_map_batch -> one 88-byte record per read; per chunk round the GPU fetches only the chunk "
                                 "each still-active read is at (bytes counted by the library), as the reference's loop touches only those (rmap.cpp:685-712)",
@@ -742,6 +742,24 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
                                       "l_sig is only known after the whole read has been decoded, so the whole read goes up",
                              "records_equal_resident_path": bool(rec_r.tobytes() == rec0.tobytes())},
                "gpu_launches": int(launches), "clocks": clocks, "paf_digest": digest(lines)}
+        # the integer stages that dominate the map step, against the HBM roofline: algorithmic bytes of the stage / its time in the step run
+        # alone (host-observed between synchronisations: includes the launch gaps of the stage's kernels)
+        try:
+            hbm_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0)); psrc = "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            hbm_peak, psrc = 6650.0, "fallback"
+        n_anc = float(stc["anchors"])
+        out["roofline_map"] = {
+            "anchor_fill_and_sort": {"kernels": "k_fill_anchors + k_sort_buckets<*>", "bound": "hbm", "unit": "GB/s", "peak": hbm_peak, "peak_source": psrc,
+                                     "algorithmic_bytes": "per anchor: 8 B position gathered from the index + 8 B key written (fill); 8 B read + 8 B written (sort) = 32 B",
+                                     "achieved": 32.0 * n_anc / (st_alone["sort_ms"] * 1e-3) / 1e9, "frac": 32.0 * n_anc / (st_alone["sort_ms"] * 1e-3) / 1e9 / hbm_peak,
+                                     "traffic": "profiles/r02_map_kernels.md: k_sort_buckets<8192> 361 MB read + 301 MB written for 59 M keys (= algorithmic)"},
+            "chaining": {"kernels": "k_chain_pre + k_chain_simple + k_chain", "bound": "hbm", "unit": "GB/s", "peak": hbm_peak, "peak_source": psrc,
+                         "algorithmic_bytes": "per anchor: 8 B key read, 4 B score + 4 B predecessor + 1 B used flag written = 17 B",
+                         "achieved": 17.0 * n_anc / (st_alone["chain_ms"] * 1e-3) / 1e9, "frac": 17.0 * n_anc / (st_alone["chain_ms"] * 1e-3) / 1e9 / hbm_peak,
+                         "traffic": "profiles/r02_map_kernels.md: k_chain_pre 0.47 GB read + 0.52 GB written, k_chain 1.24 GB per launch (keys re-read by each of the three passes)",
+                         "note": "latency / issue-bound integer recurrences (the chaining DP is sequential per read), not bandwidth-bound: the fraction is reported for "
+                                 "completeness, the lever is the dependent-instruction chain per anchor (profiles/r02_map_kernels.md)"}}
         if not args.no_cpu_baseline:
             out["cpu_baseline"] = reference_map_sample(ds, cfg, raw, off, ln, lines, max(args.cpu_sample_reads, 64 * (os.cpu_count() or 1)), n_reads, steps=2)
     for c, x in pipes:

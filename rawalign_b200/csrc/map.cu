@@ -56,6 +56,22 @@ struct Buf {                                                       // grow-only 
 	template <class T> T *as() const { return reinterpret_cast<T *>(p); }
 };
 
+struct PinBuf {                                                    // grow-only page-locked host buffer; reserve() keeps the first `keep` bytes
+	void *p = nullptr; size_t cap = 0;
+	int reserve(size_t bytes, size_t keep = 0)
+	{
+		if (bytes <= cap) return RA_OK;
+		size_t want = std::max(bytes, cap + cap / 2);
+		void *q = nullptr;
+		if (cudaMallocHost(&q, want) != cudaSuccess) { (void)cudaGetLastError(); return ra__fail(RA_ECUDA, "cudaMallocHost(%zu) failed", want); }
+		if (p && keep) memcpy(q, p, keep);
+		if (p) cudaFreeHost(p);
+		p = q; cap = want;
+		return RA_OK;
+	}
+	void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
 struct Slot { uint32_t key, cnt; uint64_t off; };                  // cnt == 0: empty
 
 struct ChainRec {                                                  // ri_chain_t (rmap.h:30-46) with the anchors as an arena offset
@@ -92,9 +108,11 @@ struct ra_index {
 	Buf keys, score, pred, used, anc[2], cand, n_cand, cand_base, dtw_chains, group_first, dscore, dkeep, scan_tmp;
 	Buf lsig_keep, nt, n_nt, ntf, cxf, bin_base, stage, fin_r, fin_aoff, fin_chain, fin_anc;
 	// --dtw-output-cigar results of the last ra_map_batch, host side: per read the range of its alignment in cig_i/j/d
-	struct CigRound { std::vector<uint64_t> pi, pj; std::vector<float> pd; };
-	std::vector<CigRound> cig_rounds;                              // one per chunk round that finished mapped reads (moved in, not copied)
-	std::vector<uint64_t> cig_start, cig_len; std::vector<uint32_t> cig_round;
+	struct CigDev { Buf parts, first, items, slot_sz, dir_sz, slot_off, dir_off, dirs, si, sj, sd, plen, poff, oi, oj, od, cost, alns, coff, clen, add, ring, cnt; } cg;
+	PinBuf cig_i, cig_j, cig_d;                                    // path elements (u32 i, u32 j, f32 diff) of every finished read, in finishing order
+	uint64_t cig_total = 0;
+	std::vector<uint64_t> cig_start, cig_len, cig_add_i, cig_add_j;   // per read: its range in cig_*; the addend of its last element (global border)
+	int n_sm = 0;
 	uint32_t tshift = 0, n_bins = 0;                               // bin function of the bucket sort: bin_base[ref << 1 | strand] + (target >> tshift)
 	std::vector<uint64_t> last_off; std::vector<uint32_t> last_len; bool last_raw = false;   // the batch left on the device by the last ra_map_batch
 	void *pin = nullptr; size_t pin_cap = 0;
@@ -330,6 +348,8 @@ void ra_index_destroy(ra_index *ix)
 	for (Buf *b : all) b->release();
 	if (ix->pin) cudaFreeHost(ix->pin);
 	if (ix->pin_sig) cudaFreeHost(ix->pin_sig);
+	ix->cig_i.release(); ix->cig_j.release(); ix->cig_d.release();
+	{ ra_index::CigDev &G = ix->cg; Buf *cg[] = { &G.parts, &G.first, &G.items, &G.slot_sz, &G.dir_sz, &G.slot_off, &G.dir_off, &G.dirs, &G.si, &G.sj, &G.sd, &G.plen, &G.poff, &G.oi, &G.oj, &G.od, &G.cost, &G.alns, &G.coff, &G.clen, &G.add, &G.ring, &G.cnt }; for (Buf *b : cg) b->release(); }
 	if (ix->stream) cudaStreamDestroy(ix->stream);
 	for (auto &e : ix->ev_t) if (e) cudaEventDestroy(e);
 	delete ix;
@@ -401,6 +421,7 @@ int ra_index_info(const ra_index *ix, int32_t *out, uint32_t *seq_len_out)
 
 #include "map_kernels.cuh"
 #include "map_chain.cuh"
+#include "map_cigar.cuh"
 #include "map_batch.cuh"
 #include "map_index_build.cuh"
 #include "map_index_host.cuh"

@@ -106,7 +106,7 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 	if (cigar && opt->dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_GLOBAL && opt->dtw_fill_method == RA_DTW_FILL_METHOD_BANDED)
 		return ra__fail(RA_EUNSUP, "global border + banded fill + cigar is not implemented by the reference (rmap.cpp:223-225 asserts)");
 	std::vector<std::pair<uint32_t, float>> cig_alns;
-	ix->cig_start.assign(n_reads, 0); ix->cig_len.assign(n_reads, 0); ix->cig_round.assign(n_reads, 0); ix->cig_rounds.clear();
+	ix->cig_start.assign(n_reads, 0); ix->cig_len.assign(n_reads, 0); ix->cig_add_i.assign(n_reads, 0); ix->cig_add_j.assign(n_reads, 0); ix->cig_total = 0;
 	int rc;
 	{   // hot-path options of the context follow the map options; fp_contract / test hooks stay as the context has them
 		ra_mapopt_t o; if ((rc = ra_get_opt(ctx, &o))) return rc;
@@ -357,38 +357,89 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 			                                ix->fin_aoff.as<uint64_t>(), counters); ++launches;
 			MAP_CUDA(cudaMemcpyAsync(hc + 4, counters + 4, 8, cudaMemcpyDeviceToHost, S));
 			MAP_CUDA(cudaStreamSynchronize(S));
-			const uint32_t n_fin = hc[4], n_fa = hc[5];
+			const uint32_t n_fin = hc[4];                           // (hc[5]: anchors of those chains, sized fin_anc already)
 			if (n_fin) {
 				k_cigar_pack<<<(n_fin * 32 + 127) / 128, 128, 0, S>>>(st, P, ix->chains.as<ChainRec>(), ix->anc[cur].as<ra_anchor_t>(), ix->seq_tab.as<uint64_t>(),
 				                                                      ix->fin_r.as<uint32_t>(), ix->fin_aoff.as<uint64_t>(), n_fin, ix->fin_chain.as<ra_chain_t>(),
 				                                                      ix->fin_anc.as<ra_anchor_t>()); ++launches;
-				std::vector<uint32_t> fr(n_fin); std::vector<ra_chain_t> fc(n_fin); std::vector<ra_anchor_t> fa(n_fa);
-				MAP_CUDA(cudaMemcpyAsync(fr.data(), ix->fin_r.p, (size_t)n_fin * 4, cudaMemcpyDeviceToHost, S));
-				MAP_CUDA(cudaMemcpyAsync(fc.data(), ix->fin_chain.p, (size_t)n_fin * sizeof(ra_chain_t), cudaMemcpyDeviceToHost, S));
-				MAP_CUDA(cudaMemcpyAsync(fa.data(), ix->fin_anc.p, (size_t)n_fa * sizeof(ra_anchor_t), cudaMemcpyDeviceToHost, S));
+				// align_chain(cigar = true) for the n_fin winning chains, all on the device (map_cigar.cuh)
+				const int sparse = opt->dtw_border_constraint == RA_DTW_BORDER_CONSTRAINT_SPARSE;
+				ra_index::CigDev &G = ix->cg;
+				if ((rc = G.parts.reserve((size_t)n_fin * 4)) || (rc = G.first.reserve(((size_t)n_fin + 1) * 8)) || (rc = G.alns.reserve((size_t)n_fin * 4)) ||
+				    (rc = G.coff.reserve((size_t)n_fin * 8)) || (rc = G.clen.reserve((size_t)n_fin * 4)) || (rc = G.add.reserve((size_t)n_fin * 16)) || (rc = G.cnt.reserve(64))) return rc;
+				const ra_chain_t *fch = ix->fin_chain.as<ra_chain_t>(); const ra_anchor_t *fan = ix->fin_anc.as<ra_anchor_t>();
+				k_cig_count<<<(n_fin + 255) / 256, 256, 0, S>>>(fch, n_fin, sparse, G.parts.as<uint32_t>()); ++launches;
+				MAP_CUDA(ra::launch_exclusive_scan_u32(G.parts.as<uint32_t>(), G.first.as<uint64_t>(), n_fin, S)); ++launches;
+				MAP_CUDA(cudaMemcpyAsync(h64, G.first.as<uint64_t>() + n_fin, 8, cudaMemcpyDeviceToHost, S));
 				MAP_CUDA(cudaStreamSynchronize(S));
-				uint64_t pcap = 0;
-				for (uint32_t k = 0; k < n_fin; ++k) {
-					const ra_anchor_t *a = fa.data() + fc[k].anchor_off;
-					pcap += (uint64_t)(a[0].query_position - a[fc[k].n_anchors - 1].query_position) + (a[0].target_position - a[fc[k].n_anchors - 1].target_position) + 2ull * fc[k].n_anchors + 2;
+				const uint64_t n_items64 = h64[0];
+				if (n_items64 >= 0xffffffffull) return ra__fail(RA_EINVAL, "too many alignment parts in one round");
+				const uint32_t n_items = (uint32_t)n_items64;
+				if ((rc = G.poff.reserve(((size_t)n_items + 1) * 8)) || (rc = G.items.reserve(std::max<size_t>(n_items, 1) * sizeof(ra_dtw_item_t))) ||
+				    (rc = G.cost.reserve(std::max<size_t>(n_items, 1) * 4))) return rc;
+				uint64_t total = 0;
+				if (n_items) {
+					if ((rc = G.slot_sz.reserve((size_t)n_items * 4)) || (rc = G.dir_sz.reserve((size_t)n_items * 4)) || (rc = G.slot_off.reserve(((size_t)n_items + 1) * 8)) ||
+					    (rc = G.dir_off.reserve(((size_t)n_items + 1) * 8)) || (rc = G.plen.reserve((size_t)n_items * 4))) return rc;
+					MAP_CUDA(cudaMemsetAsync(G.cnt.p, 0, 64, S));
+					k_cig_items<<<(n_fin * 32 + 127) / 128, 128, 0, S>>>(fch, fan, n_fin, sparse, G.first.as<uint64_t>(), G.items.as<ra_dtw_item_t>(), G.slot_sz.as<uint32_t>(),
+					                                                  G.dir_sz.as<uint32_t>(), G.cnt.as<uint32_t>() + 8); ++launches;
+					MAP_CUDA(ra::launch_exclusive_scan_u32(G.slot_sz.as<uint32_t>(), G.slot_off.as<uint64_t>(), n_items, S));
+					MAP_CUDA(ra::launch_exclusive_scan_u32(G.dir_sz.as<uint32_t>(), G.dir_off.as<uint64_t>(), n_items, S)); launches += 2;
+					MAP_CUDA(cudaMemcpyAsync(h64, G.slot_off.as<uint64_t>() + n_items, 8, cudaMemcpyDeviceToHost, S));
+					MAP_CUDA(cudaMemcpyAsync(h64 + 1, G.dir_off.as<uint64_t>() + n_items, 8, cudaMemcpyDeviceToHost, S));
+					MAP_CUDA(cudaMemcpyAsync(h64 + 2, G.cnt.as<uint32_t>() + 8, 4, cudaMemcpyDeviceToHost, S));
+					MAP_CUDA(cudaStreamSynchronize(S));
+					const uint64_t slots = h64[0], dwords = h64[1]; const uint32_t maxw = (uint32_t)h64[2];
+					if ((rc = G.dirs.reserve(std::max<uint64_t>(dwords, 1) * 4)) || (rc = G.si.reserve(slots * 4)) || (rc = G.sj.reserve(slots * 4)) || (rc = G.sd.reserve(slots * 4)) ||
+					    (rc = G.oi.reserve(slots * 4)) || (rc = G.oj.reserve(slots * 4)) || (rc = G.od.reserve(slots * 4))) return rc;
+					ra::DtwLaunch L; memset(&L, 0, sizeof(L));
+					L.a_arena = ix->ev.as<float>(); L.b_arena = ref_dev; L.items = G.items.as<ra_dtw_item_t>(); L.n_items = n_items;
+					L.cost = G.cost.as<float>(); L.work_counter = G.cnt.as<uint32_t>();
+					if (!ix->n_sm) MAP_CUDA(cudaDeviceGetAttribute(&ix->n_sm, cudaDevAttrMultiProcessorCount, ra__device(ctx)));
+					if (maxw > ra::dtw_generic_smem_ring_cap()) {
+						uint32_t cap = 1; while (cap < maxw) cap <<= 1;
+						if ((rc = G.ring.reserve((size_t)ix->n_sm * 16 * 3 * cap * sizeof(float)))) return rc;
+						L.ring_scratch = G.ring.as<float>(); L.ring_cap = cap;
+					}
+					L.dirs = G.dirs.as<uint32_t>(); L.dir_off = G.dir_off.as<uint64_t>();
+					L.path_i = G.si.as<uint32_t>(); L.path_j = G.sj.as<uint32_t>(); L.path_diff = G.sd.as<float>();
+					L.slot_off = G.slot_off.as<uint64_t>(); L.path_len = G.plen.as<uint32_t>();
+					int nl = 0;
+					MAP_CUDA(ra::launch_dtw_generic(L, true, ix->n_sm, S, &nl));
+					MAP_CUDA(ra::launch_exclusive_scan_u32(G.plen.as<uint32_t>(), G.poff.as<uint64_t>(), n_items, S));
+					MAP_CUDA(ra::launch_path_compact(G.si.as<uint32_t>(), G.sj.as<uint32_t>(), G.sd.as<float>(), G.slot_off.as<uint64_t>(), G.items.as<ra_dtw_item_t>(),
+					                                 G.plen.as<uint32_t>(), G.poff.as<uint64_t>(), n_items, G.oi.as<uint32_t>(), G.oj.as<uint32_t>(), G.od.as<float>(), S));
+					launches += nl + 2;
+				} else MAP_CUDA(cudaMemsetAsync(G.poff.p, 0, 8, S));
+				ra_mapopt_t co; if ((rc = ra_get_opt(ctx, &co))) return rc;
+				k_cig_finish<<<(n_fin * 32 + 127) / 128, 128, 0, S>>>(fch, fan, n_fin, sparse, G.first.as<uint64_t>(), G.items.as<ra_dtw_item_t>(), G.cost.as<float>(),
+				                                                   G.poff.as<uint64_t>(), G.oi.as<uint32_t>(), G.oj.as<uint32_t>(), opt->dtw_match_bonus, (int)co.fp_contract,
+				                                                   G.alns.as<float>(), G.coff.as<uint64_t>(), G.clen.as<uint32_t>(), G.add.as<uint64_t>()); ++launches;
+				std::vector<uint32_t> fr(n_fin), clen(n_fin); std::vector<float> al(n_fin); std::vector<uint64_t> coff(n_fin), add(2 * (size_t)n_fin);
+				MAP_CUDA(cudaMemcpyAsync(fr.data(), ix->fin_r.p, (size_t)n_fin * 4, cudaMemcpyDeviceToHost, S));
+				MAP_CUDA(cudaMemcpyAsync(al.data(), G.alns.p, (size_t)n_fin * 4, cudaMemcpyDeviceToHost, S));
+				MAP_CUDA(cudaMemcpyAsync(coff.data(), G.coff.p, (size_t)n_fin * 8, cudaMemcpyDeviceToHost, S));
+				MAP_CUDA(cudaMemcpyAsync(clen.data(), G.clen.p, (size_t)n_fin * 4, cudaMemcpyDeviceToHost, S));
+				MAP_CUDA(cudaMemcpyAsync(add.data(), G.add.p, (size_t)n_fin * 16, cudaMemcpyDeviceToHost, S));
+				MAP_CUDA(cudaMemcpyAsync(h64, G.poff.as<uint64_t>() + n_items, 8, cudaMemcpyDeviceToHost, S));
+				MAP_CUDA(cudaStreamSynchronize(S));
+				total = h64[0];
+				if ((rc = ix->cig_i.reserve((ix->cig_total + total) * 4, ix->cig_total * 4)) || (rc = ix->cig_j.reserve((ix->cig_total + total) * 4, ix->cig_total * 4)) ||
+				    (rc = ix->cig_d.reserve((ix->cig_total + total) * 4, ix->cig_total * 4))) return rc;
+				if (total) {                                            // the finished paths: 12 bytes per element into page-locked host arrays
+					MAP_CUDA(cudaMemcpyAsync(static_cast<uint32_t *>(ix->cig_i.p) + ix->cig_total, G.oi.p, total * 4, cudaMemcpyDeviceToHost, S));
+					MAP_CUDA(cudaMemcpyAsync(static_cast<uint32_t *>(ix->cig_j.p) + ix->cig_total, G.oj.p, total * 4, cudaMemcpyDeviceToHost, S));
+					MAP_CUDA(cudaMemcpyAsync(static_cast<float *>(ix->cig_d.p) + ix->cig_total, G.od.p, total * 4, cudaMemcpyDeviceToHost, S));
+					MAP_CUDA(cudaStreamSynchronize(S));
 				}
-				std::vector<float> sc(n_fin), cost(n_fin), pd(pcap);
-				std::vector<uint64_t> pi(pcap), pj(pcap), poff(n_fin + 1);
-				void *evp = ix->ev.p; uint64_t evn = ev_cap;
-				ra__swap_resident(ctx, &evp, &evn);                   // the cigar entry point reads "the events resident on the device"
-				const uint64_t lc = ra_launch_count(ctx);
-				rc = ra_align_chains_cigar_batch(ctx, nullptr, 0, nullptr, 0, fa.data(), n_fa, fc.data(), n_fin, sc.data(), cost.data(), pi.data(), pj.data(), pd.data(), pcap, poff.data());
-				lib_launches += ra_launch_count(ctx) - lc;
-				ra__swap_resident(ctx, &evp, &evn);
-				if (rc) return rc;
-				const uint32_t round_slot = (uint32_t)ix->cig_rounds.size();
+				stt.d2h_bytes += total * 12 + (uint64_t)n_fin * 36;
 				for (uint32_t k = 0; k < n_fin; ++k) {
 					const uint32_t r = fr[k];
-					ix->cig_round[r] = round_slot; ix->cig_start[r] = poff[k]; ix->cig_len[r] = poff[k + 1] - poff[k];
-					cig_alns.push_back({r, sc[k]});
+					ix->cig_start[r] = ix->cig_total + coff[k]; ix->cig_len[r] = clen[k]; ix->cig_add_i[r] = add[2 * (size_t)k]; ix->cig_add_j[r] = add[2 * (size_t)k + 1];
+					cig_alns.push_back({r, al[k]});
 				}
-				ix->cig_rounds.emplace_back();
-				ix->cig_rounds.back().pi = std::move(pi); ix->cig_rounds.back().pj = std::move(pj); ix->cig_rounds.back().pd = std::move(pd);
+				ix->cig_total += total;
 			}
 			stt.select_ms += clk.lap();
 		}
@@ -416,13 +467,16 @@ extern "C" int ra_map_last_cigar(ra_index *ix, uint32_t n_reads, uint64_t *path_
 	path_off[n_reads] = w;
 	if (!path_i) return RA_OK;                                      // sizing call
 	if (w > cap) return ra__fail(RA_EINVAL, "path capacity %llu < %llu", (unsigned long long)cap, (unsigned long long)w);
+	const uint32_t *ci = static_cast<const uint32_t *>(ix->cig_i.p), *cj = static_cast<const uint32_t *>(ix->cig_j.p);
+	const float *cd = static_cast<const float *>(ix->cig_d.p);
 	for (uint32_t r = 0; r < n_reads; ++r) {
 		const uint64_t len = ix->cig_len[r];
 		if (!len) continue;
-		const ra_index::CigRound &c = ix->cig_rounds[ix->cig_round[r]];
-		memcpy(path_i + path_off[r], c.pi.data() + ix->cig_start[r], len * 8);
-		memcpy(path_j + path_off[r], c.pj.data() + ix->cig_start[r], len * 8);
-		if (path_diff) memcpy(path_diff + path_off[r], c.pd.data() + ix->cig_start[r], len * 4);
+		const uint64_t a = ix->cig_start[r];
+		uint64_t *pi = path_i + path_off[r], *pj = path_j + path_off[r];
+		for (uint64_t t = 0; t < len; ++t) { pi[t] = ci[a + t]; pj[t] = cj[a + t]; }
+		pi[len - 1] += ix->cig_add_i[r]; pj[len - 1] += ix->cig_add_j[r];      // global border: rmap.cpp:230-233
+		if (path_diff) memcpy(path_diff + path_off[r], cd + a, len * 4);
 	}
 	return RA_OK;
 }

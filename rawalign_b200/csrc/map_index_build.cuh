@@ -53,14 +53,30 @@ k_ib_sums(const StrandJob *__restrict__ jobs, uint32_t n_jobs, const float *__re
 	const StrandJob J = jobs[jb];
 	const float *__restrict__ x = arena + J.sig_off;
 	double sum = 0.0, sum2 = 0.0;
+	// the dependent chain is one DADD and one DFMA per value; everything else (load of the next block, shuffles, conversions) is
+	// hoisted off it: full blocks run fully unrolled on 32 converted values held in registers
+	float v = lane < J.n_sig ? x[lane] : 0.0f;
 	for (uint32_t b = 0; b < J.n_sig; b += 32) {
-		const float v = b + lane < J.n_sig ? x[b + lane] : 0.0f;
+		const uint32_t nb = b + 32;
+		const float vn = nb + lane < J.n_sig ? x[nb + lane] : 0.0f;
 		const uint32_t cnt = min(32u, J.n_sig - b);
-		for (uint32_t t = 0; t < cnt; ++t) {
-			const double c = (double)__shfl_sync(0xffffffffu, v, (int)t);
-			sum = __dadd_rn(sum, c);                                                    // rsig.cpp:30
-			sum2 = CONTRACT ? __fma_rn(c, c, sum2) : __dadd_rn(sum2, __dmul_rn(c, c));  // :31
+		if (cnt == 32u) {
+			double c[32];
+#pragma unroll
+			for (int t = 0; t < 32; ++t) c[t] = (double)__shfl_sync(0xffffffffu, v, t);
+#pragma unroll
+			for (int t = 0; t < 32; ++t) {
+				sum = __dadd_rn(sum, c[t]);                                                          // rsig.cpp:30
+				sum2 = CONTRACT ? __fma_rn(c[t], c[t], sum2) : __dadd_rn(sum2, __dmul_rn(c[t], c[t]));   // :31
+			}
+		} else {
+			for (uint32_t t = 0; t < cnt; ++t) {
+				const double c = (double)__shfl_sync(0xffffffffu, v, (int)t);
+				sum = __dadd_rn(sum, c);
+				sum2 = CONTRACT ? __fma_rn(c, c, sum2) : __dadd_rn(sum2, __dmul_rn(c, c));
+			}
 		}
+		v = vn;
 	}
 	if (lane == 0) {
 		const double n = (double)J.n_sig;
@@ -98,15 +114,28 @@ k_ib_sketch(const StrandJob *__restrict__ jobs, uint32_t n_jobs, const float *__
 	const uint64_t id_shift = (uint64_t)J.seq << 32;
 	float last = 0.0f;
 	uint32_t n_acc = 0;
+	float v = (uint32_t)lane < J.n_sig ? ev[lane] : 0.0f;
 	for (uint32_t b = 0; b < J.n_sig; b += 32) {
 		const uint32_t idx = b + lane;
-		const float v = idx < J.n_sig ? ev[idx] : 0.0f;
+		const float vn = idx + 32 < J.n_sig ? ev[idx + 32] : 0.0f;  // next block's load is in flight during this block's chain
 		const uint32_t cnt = min(32u, J.n_sig - b);
 		uint32_t accmask = 0;
-		for (uint32_t t = 0; t < cnt; ++t) {
-			const float x = __shfl_sync(0xffffffffu, v, (int)t);
-			const bool rej = ((b + t) > 0 && fabsf(__fsub_rn(x, last)) < 0.3f) || x == 3.402823466e+32f;   // rsketch.c:243
-			if (!rej) { last = x; accmask |= 1u << t; }
+		if (cnt == 32u && b > 0) {                                  // full block: shuffles hoisted, the chain is subtract / compare / select
+			float xs[32];
+#pragma unroll
+			for (int t = 0; t < 32; ++t) xs[t] = __shfl_sync(0xffffffffu, v, t);
+#pragma unroll
+			for (int t = 0; t < 32; ++t) {
+				const bool rej = fabsf(__fsub_rn(xs[t], last)) < 0.3f || xs[t] == 3.402823466e+32f;            // rsketch.c:243
+				last = rej ? last : xs[t];
+				accmask |= rej ? 0u : (1u << t);
+			}
+		} else {
+			for (uint32_t t = 0; t < cnt; ++t) {
+				const float x = __shfl_sync(0xffffffffu, v, (int)t);
+				const bool rej = ((b + t) > 0 && fabsf(__fsub_rn(x, last)) < 0.3f) || x == 3.402823466e+32f;   // rsketch.c:243
+				if (!rej) { last = x; accmask |= 1u << t; }
+			}
 		}
 		const bool mine = (accmask >> lane) & 1u;
 		const uint32_t rank = n_acc + __popc(accmask & ((1u << lane) - 1u));
@@ -127,6 +156,7 @@ k_ib_sketch(const StrandJob *__restrict__ jobs, uint32_t n_jobs, const float *__
 		}
 		n_acc += __popc(accmask);
 		__syncwarp();
+		v = vn;
 	}
 	if (lane == 0) n_seeds[jb] = n_acc + 1u >= (uint32_t)e ? n_acc + 1u - (uint32_t)e : 0u;
 }
