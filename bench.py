@@ -735,6 +735,7 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
                                 "the reference arm is timed on -> ra_map_batch -> one 88-byte record per read; per chunk round the GPU fetches only the chunk "
                                 "each still-active read is at (bytes counted by the library), as the reference's loop touches only those (rmap.cpp:685-712)",
                        "host_buffer_bytes": int(sig_p.nbytes),
+                       "stages_ms_last_step": {k: round(float(v), 3) for k, v in st_e.items() if k.endswith("_ms")},
                        "records_equal_resident_path": bool(rec_e.tobytes() == rec.tobytes() == rec0.tobytes())},
                "e2e_int16": {"value": reads_all * args.steps / dt_raw, "unit": "reads/s", "ms_per_step": dt_raw / args.steps * 1e3,
                              "h2d_bytes_per_step": int(st_r["h2d_bytes"]), "d2h_bytes_per_step": int(st_r["d2h_bytes"]),

@@ -339,3 +339,35 @@ def test_index_build_on_device_equals_the_reference_indexer_output(tmp_path):
     assert np.array_equal(got["keys"], tab["keys"]) and np.array_equal(got["key_off"], tab["key_off"]) and np.array_equal(got["vals"], tab["vals"])
     want = np.concatenate([np.concatenate((f, r_)) for f, r_ in zip(tab["fwd"], tab["rev"])])
     assert np.array_equal(bits(mirror), bits(want))
+
+
+@pytest.mark.parametrize("border,fill", [(0, 0), (1, 0), (1, 1)])
+def test_cigar_stage_vs_live_reference(tmp_path, border, fill):
+    """--dtw-output-cigar under global border + full matrix (the last-element quirk of rmap.cpp:230-233), sparse + full and sparse +
+    banded, against the reference's own map loop run live (oracle/_ref/libra_refmap.so), on an index built on the device."""
+    import re
+    import rawalign_b200 as ra
+    from oracle import PRESETS, RefMap
+    from workload import synth
+    if not RefMap.available():
+        pytest.skip("oracle/_ref/libra_refmap.so was not built in this checkout")
+    seqs = [synth.random_reference(n, seed=500 + i) for i, n in enumerate([200_000, 50_000])]
+    fa, model = str(tmp_path / "r.fa"), str(tmp_path / "m.txt")
+    synth.write_fasta(fa, seqs); synth.write_pore_model(model)
+    rd = synth.simulate_reads(seqs[0], 40, seed=31, max_chunks=4)
+    sig = rd.sig.astype(np.float32)
+    off, ln = rd.read_off[:-1].astype(np.uint64), rd.read_len.astype(np.uint32)
+    kw = dict(flag=ra.RI_M_DTW_EVALUATE_CHAINS | ra.RI_M_DTW_OUTPUT_CIGAR, dtw_border_constraint=border, dtw_fill_method=fill)
+    rm = RefMap()
+    idx = rm.index_build(fa, model, "sensitive")
+    paf, mapped, _ = rm.map_reads(idx, rm.mapopt(**kw), sig, off, ln, n_threads=4)
+    rm.index_free(idx)
+    want = [re.sub(r"mt:f:[0-9.eE+-]+\t", "", l) for l in paf]
+    e, q, lq, w, n = PRESETS["sensitive"]
+    with ra.Context(0) as ctx, ra.Index.build(ctx, seqs, synth.pore_model_as_loaded(), e=e, q=q, lq=lq, k=6) as ix:
+        rec, _ = ix.map_reads(_opt(kw), sig=sig, sig_off=off, sig_len=ln)
+        got = ix.paf_lines(rec, cigar=ix.last_cigar(len(ln)))
+    assert mapped.sum() >= 20
+    assert len(got) == len(want)
+    for r, (a, b) in enumerate(zip(got, want)):
+        assert a == b, (r, a[:300], b[:300])
