@@ -119,6 +119,7 @@ struct ra_index {
 	void *pin_sig = nullptr; size_t pin_sig_cap = 0;               // staging of the per-round signal upload from pageable caller memory
 	bool sort_attr = false;                                        // the sort kernel's > 48 KB shared memory opt-in (one index = one device)
 	cudaStream_t stream = nullptr;
+	cudaStream_t stream_hi = nullptr;                              // highest priority: the PCIe gather of a round must not queue behind other batches' kernels
 	cudaEvent_t ev_t[16] = {};
 };
 
@@ -151,6 +152,7 @@ int finish_index_geometry(ra_ctx *ctx, ra_index *ix, const std::vector<uint64_t>
 		ix->tshift = ts; ix->n_bins = acc;
 	}
 	MAP_CUDA(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
+	{ int lo = 0, hi = 0; MAP_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi)); MAP_CUDA(cudaStreamCreateWithPriority(&ix->stream_hi, cudaStreamNonBlocking, hi)); }
 	for (auto &e : ix->ev_t) MAP_CUDA(cudaEventCreate(&e));
 	return RA_OK;
 }
@@ -351,6 +353,7 @@ void ra_index_destroy(ra_index *ix)
 	ix->cig_i.release(); ix->cig_j.release(); ix->cig_d.release();
 	{ ra_index::CigDev &G = ix->cg; Buf *cg[] = { &G.parts, &G.first, &G.items, &G.slot_sz, &G.dir_sz, &G.slot_off, &G.dir_off, &G.dirs, &G.si, &G.sj, &G.sd, &G.plen, &G.poff, &G.oi, &G.oj, &G.od, &G.cost, &G.alns, &G.coff, &G.clen, &G.add, &G.ring, &G.cnt }; for (Buf *b : cg) b->release(); }
 	if (ix->stream) cudaStreamDestroy(ix->stream);
+	if (ix->stream_hi) cudaStreamDestroy(ix->stream_hi);
 	for (auto &e : ix->ev_t) if (e) cudaEventDestroy(e);
 	delete ix;
 }

@@ -221,7 +221,9 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 		if (lazy) {
 			if ((rc = ix->sig.reserve((uint64_t)n_act * lazy_stride * 4 + 64))) return rc;
 			if (hsig_dev) {
-				k_gather_chunks<<<std::min<uint32_t>((n_act + 7) / 8, 148), 256, 0, S>>>(hsig_dev, ix->coff.as<uint64_t>(), ix->clen.as<uint32_t>(), n_act, ix->sig.as<float>(), lazy_stride); ++launches;
+				MAP_CUDA(cudaEventRecord(ix->ev_t[0], ix->stream_hi));
+				k_gather_chunks<<<std::min<uint32_t>((n_act + 7) / 8, 148), 256, 0, ix->stream_hi>>>(hsig_dev, ix->coff.as<uint64_t>(), ix->clen.as<uint32_t>(), n_act, ix->sig.as<float>(), lazy_stride); ++launches;
+				MAP_CUDA(cudaEventRecord(ix->ev_t[1], ix->stream_hi));
 				stt.h2d_bytes += 4ull * *reinterpret_cast<const uint64_t *>(hc + 14);
 			} else {                                                // pageable caller memory: gather on the host into a page-locked staging buffer
 				h_coff.resize(n_act); h_clen.resize(n_act);
@@ -242,8 +244,9 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 				stt.h2d_bytes += 4 * moved;
 				stt.d2h_bytes += (uint64_t)n_act * 12;
 			}
-			MAP_CUDA(cudaStreamSynchronize(S));                     // K1 runs on the context's streams: the round arena must be complete
+			MAP_CUDA(cudaStreamSynchronize(hsig_dev ? ix->stream_hi : S));   // K1 runs on the context's streams: the round arena must be complete (S is idle here: the round's counters were just read)
 			stt.decode_ms += clk.lap();
+			if (hsig_dev && getenv("RA_MAP_TRACE")) { float gms = 0; cudaEventElapsedTime(&gms, ix->ev_t[0], ix->ev_t[1]); fprintf(stderr, "[map] round %u: gather of %u chunks %.3f ms on the device\n", round, n_act, gms); }
 		}
 		// ---- K1 over the round's chunks, appended to the reads' event arrays ------------------------------------------
 		const uint64_t round_cap = (uint64_t)n_act * events_bound(max_len, w1, w2);
