@@ -225,15 +225,52 @@ k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64
 		float cs[kMaxBest]; uint32_t ci[kMaxBest]; int ncand = 0;
 #pragma unroll
 		for (int t = 0; t < kMaxBest; ++t) { cs[t] = 0.0f; ci[t] = 0u; }
-		for (; j < m_nt; ++j) {
+		// inserts (sc, ai) into the num_best_chains best by (score desc, index desc) (compare(), :175-179): ai only grows, so a tie goes
+		// in front; fully unrolled with selects: the list stays in registers
+		auto keep_best = [&](float sc, uint32_t ai) {
+			int p = 0;
+#pragma unroll
+			for (int t = 0; t < kMaxBest; ++t) p += (t < ncand && cs[t] > sc) ? 1 : 0;
+			if (p < P.num_best_chains) {
+				const int lastp = min(ncand, P.num_best_chains - 1);
+#pragma unroll
+				for (int t = kMaxBest - 1; t > 0; --t) { const bool sh = t > p && t <= lastp; cs[t] = sh ? cs[t - 1] : cs[t]; ci[t] = sh ? ci[t - 1] : ci[t]; }
+#pragma unroll
+				for (int t = 0; t < kMaxBest; ++t) { const bool here = t == p; cs[t] = here ? sc : cs[t]; ci[t] = here ? ai : ci[t]; }
+				if (ncand < P.num_best_chains) ++ncand;
+			}
+		};
+		while (j < m_nt) {
 			if (j - jb >= 32u) load_block(j);
 			const int sl = (int)(j - jb);
+			// a run of listed anchors of this list that k_chain_simple finished is taken in one step: their scores are final, the
+			// running maximum after each of them is a prefix maximum, and the filter of :488-492 lets through a handful at most
+			{
+				const bool in_list = jb + (uint32_t)lane < m_nt && key_list(k_reg) == list;
+				const uint32_t stop = __ballot_sync(0xffffffffu, !in_list || cx_reg != 0u) & ~((1u << sl) - 1u);
+				const int run_end = stop ? __ffs(stop) - 1 : 32;
+				if (run_end > sl) {
+					const bool in_run = lane >= sl && lane < run_end;
+					float pm = in_run ? s_reg : 0.0f;                  // scores are >= e > 0
+#pragma unroll
+					for (int d = 1; d < 32; d <<= 1) { const float y = __shfl_up_sync(0xffffffffu, pm, d); if (lane >= d) pm = fmaxf(pm, y); }
+					pm = fmaxf(pm, max_chaining_score);                // the maximum once this lane's score has entered it (:485-487)
+					const bool pass = in_run && (P.no_filter || (s_reg >= P.min_chaining_score && s_reg > pm / 2));   // :488-492
+					uint32_t pass_mask = __ballot_sync(0xffffffffu, pass);
+					max_chaining_score = __shfl_sync(0xffffffffu, pm, run_end - 1);
+					while (pass_mask) {
+						const int t = __ffs(pass_mask) - 1; pass_mask &= pass_mask - 1;
+						keep_best(__shfl_sync(0xffffffffu, s_reg, t), __shfl_sync(0xffffffffu, nt_reg, t));
+					}
+					j += (uint32_t)(run_end - sl);
+					continue;
+				}
+			}
 			const uint32_t ai = __shfl_sync(0xffffffffu, nt_reg, sl);
 			const uint64_t kc = __shfl_sync(0xffffffffu, k_reg, sl);
 			if (key_list(kc) != list) break;
 			float sc;
-			if (!__shfl_sync(0xffffffffu, cx_reg, sl)) sc = __shfl_sync(0xffffffffu, s_reg, sl);   // finished by k_chain_simple
-			else {
+			{                                                      // a complex anchor: the scan of :452-484, 32 predecessors at a time
 				sc = fe; uint32_t pr = ai;                         // :442-443
 				const int32_t ct = (int32_t)key_target(kc), cq = (int32_t)key_query(kc);
 				uint32_t start = ls;
@@ -299,20 +336,8 @@ k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64
 				__syncwarp();
 			}
 			if (sc > max_chaining_score) max_chaining_score = sc;  // :485-487
-			if (P.no_filter || (sc >= P.min_chaining_score && sc > max_chaining_score / 2)) {   // :488-492
-				// keep the num_best_chains best by (score desc, index desc) (compare(), :175-179): ai only grows, so a tie goes in front
-				int p = 0;                                         // fully unrolled with selects: the list stays in registers
-#pragma unroll
-				for (int t = 0; t < kMaxBest; ++t) p += (t < ncand && cs[t] > sc) ? 1 : 0;
-				if (p < P.num_best_chains) {
-					const int lastp = min(ncand, P.num_best_chains - 1);
-#pragma unroll
-					for (int t = kMaxBest - 1; t > 0; --t) { const bool sh = t > p && t <= lastp; cs[t] = sh ? cs[t - 1] : cs[t]; ci[t] = sh ? ci[t - 1] : ci[t]; }
-#pragma unroll
-					for (int t = 0; t < kMaxBest; ++t) { const bool here = t == p; cs[t] = here ? sc : cs[t]; ci[t] = here ? ai : ci[t]; }
-					if (ncand < P.num_best_chains) ++ncand;
-				}
-			}
+			if (P.no_filter || (sc >= P.min_chaining_score && sc > max_chaining_score / 2)) keep_best(sc, ai);   // :488-492
+			++j;
 		}
 		if (lane == 0) {
 			bool stop = false;
