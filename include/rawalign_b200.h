@@ -154,6 +154,19 @@ int ra_detect_events_batch_dev(ra_ctx *ctx, const float *sig_dev,
                                uint32_t n_chunks, uint32_t max_chunk_len,
                                float *ev_out_dev, uint64_t ev_cap, uint64_t *ev_off_dev,
                                uint64_t *total_events);
+/* No-allocation form of ra_detect_events_batch_dev.  It has no counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same inputs, outputs and results (bit-identical) as ra_detect_events_batch_dev, every pointer a device pointer, but
+ * the pipeline's scratch is a file-scope device array of 8 MiB that every GPU which loads the library holds until exit, and the
+ * call makes no cudaMalloc / cudaFree or allocating library call.  It enqueues its kernels on `stream` (a cudaStream_t; NULL =
+ * the default stream) and returns WITHOUT synchronising: ev_out_dev / ev_off_dev are valid once the stream reaches that point
+ * (read ev_off_dev[n_chunks] for the event count).  Limit: n_chunks x scratch-per-chunk must fit the 8 MiB -- with the default
+ * detector windows (3, 6) 100 chunks of up to 4096 samples, 399 of up to 1024; larger requests return RA_EINVAL with the
+ * numbers in ra_last_error().  Windows above 14 return RA_EUNSUP.  Every call on a GPU shares the one array: calls that
+ * overlap on the GPU (other streams, threads or contexts) race; serialise them. */
+int ra_detect_events_noalloc(ra_ctx *ctx, const float *sig_dev, const uint64_t *chunk_off_dev, const uint32_t *chunk_len_dev,
+                             uint32_t n_chunks, uint32_t max_chunk_len, float *ev_out_dev, uint64_t ev_cap, uint64_t *ev_off_dev,
+                             void *stream);
 
 /* Raw-signal form: the conversion loop of ri_read_sig (src/rsig.cpp:213-222) and the chunk loop of
  * map_worker_for (src/rmap.cpp:684-689) moved to the device, so that the DAC samples cross the bus as int16.

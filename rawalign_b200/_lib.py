@@ -117,6 +117,7 @@ def load() -> C.CDLL:
     L.ra_index_tables.argtypes = [vp, vp, vp]; L.ra_index_tables.restype = C.c_int
     L.ra_index_alloc.argtypes = [vp, C.POINTER(C.c_int32), u64, u64, vp, C.POINTER(vp)]; L.ra_index_alloc.restype = C.c_int
     L.ra_index_clone.argtypes = [vp, vp, C.POINTER(vp)]; L.ra_index_clone.restype = C.c_int
+    L.ra_detect_events_noalloc.argtypes = [vp, vp, vp, vp, u32, u32, vp, u64, vp, vp]; L.ra_detect_events_noalloc.restype = C.c_int
     L.ra_index_build.argtypes = [vp] + [C.c_int32] * 4 + [u32, vp, vp, vp, C.POINTER(vp)]; L.ra_index_build.restype = C.c_int
     L.ra_index_export.argtypes = [vp, C.POINTER(u64), C.POINTER(u64), vp, vp, vp]; L.ra_index_export.restype = C.c_int
     for name in ("ra_get_opt", "ra_index_load_file", "ra_index_load_flat", "ra_index_info", "ra_map_batch", "ra_map_last_cigar"):
@@ -141,5 +142,5 @@ EXPORTED_SYMBOLS = [
     "ra_dtw_batch", "ra_dtw_batch_dev", "ra_dtw_cells", "ra_dtw_tb_batch",
     "ra_align_chains_batch", "ra_align_chains_batch_dev", "ra_align_chains_cigar_batch",
     "ra_get_opt", "ra_set_tuning", "ra_ri_mapopt_init", "ra_index_load_file", "ra_index_load_flat", "ra_index_destroy", "ra_index_info", "ra_map_batch", "ra_map_last_cigar", "ra_index_tables", "ra_index_alloc",
-    "ra_index_build", "ra_index_export", "ra_index_clone",
+    "ra_index_build", "ra_index_export", "ra_index_clone", "ra_detect_events_noalloc",
 ]
