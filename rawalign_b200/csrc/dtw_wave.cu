@@ -59,7 +59,9 @@ struct BandTrack {
 // One problem swept by T = 32*WARPS threads (thread index t).  The value a group's first row needs from the row above it
 // travels lane to lane by shuffle; between warps (WARPS > 1) through a double-buffered shared-memory mailbox, one barrier per
 // step.  Returns dp(n-1, m-1) in the thread that owns it (*owner = true there).
-template <int H, int WARPS>
+// FULL (the whole matrix, DTW_global): no band to track and no cell to mask -- rows j >= m of the last group hold garbage that
+// only flows downwards (a row reads the row above it, never the one below) and is never read by dp(n-1, m-1).
+template <int H, int WARPS, bool FULL = false>
 __device__ __forceinline__ float wave_cost(const float *__restrict__ A, int n, const float *__restrict__ B, int m, int band, int t,
                                            float (*mbox)[WARPS], bool *owner)
 {
@@ -83,7 +85,9 @@ __device__ __forceinline__ float wave_cost(const float *__restrict__ A, int n, c
 		for (int attempt = 0; attempt < 2; ++attempt) {
 			if (g * H >= m || i < 0) break;                  // no group left, or this group has not reached column 0 yet
 			bool finished = (i >= n);
-			if (!finished) {
+			if (FULL) {
+				if (!finished) { act = true; break; }
+			} else if (!finished) {
 				if (need_init) {
 					if (i > 0) { tr.init(i - 1); jlo_p = tr.jlo(); jhi_p = tr.jhi(); tr.step(); }
 					else { tr.init(0); jlo_p = 0; jhi_p = -1; }
@@ -101,8 +105,8 @@ __device__ __forceinline__ float wave_cost(const float *__restrict__ A, int n, c
 		float send = kInf;
 		if (act) {
 			const int jt = g * H - 1;                        // the row above this group's first row (owned by the neighbouring thread)
-			float up = (g > 0 && jt >= jlo && jt <= jhi) ? recv : kInf;                     // dp(i, jt)
-			float diag = (g > 0 && i > 0 && jt >= jlo_p && jt <= jhi_p) ? recv_prev : kInf;   // dp(i-1, jt)
+			float up = (g > 0 && (FULL || (jt >= jlo && jt <= jhi))) ? recv : kInf;                     // dp(i, jt)
+			float diag = (g > 0 && i > 0 && (FULL || (jt >= jlo_p && jt <= jhi_p))) ? recv_prev : kInf;   // dp(i-1, jt)
 			if (g == 0 && i == 0) diag = 0.0f;               // virtual dp(-1,-1) = 0 so that dp(0,0) = |A0 - B0|
 			const float a_i = __ldg(A + i);
 			const unsigned base = (unsigned)(g * H - jlo), wdt = (unsigned)(jhi - jlo);
@@ -110,7 +114,7 @@ __device__ __forceinline__ float wave_cost(const float *__restrict__ A, int n, c
 			for (int r = 0; r < H; ++r) {
 				const float left = prev[r];
 				float v = fminf(fminf(up, left), diag) + fabsf(a_i - bv[r]);
-				v = (base + (unsigned)r <= wdt) ? v : kInf;   // rows outside [jlo, jhi] are outside the cell set
+				if (!FULL) v = (base + (unsigned)r <= wdt) ? v : kInf;   // rows outside [jlo, jhi] are outside the cell set
 				diag = left; up = v; prev[r] = v;
 			}
 			send = up;
@@ -152,7 +156,8 @@ k_dtw_wave(DtwLaunch L, const uint32_t *__restrict__ order, uint32_t n_order, ui
 		int n = (int)it.a_len, m = (int)it.b_len;
 		if (n < m) { const float *t = A; A = B; B = t; const int tl = n; n = m; m = tl; }      // dtw.cpp:284-292; a full matrix is symmetric
 		bool owner;
-		float res = wave_cost<H, 1>(A, n, B, m, it.band_radius, lane, nullptr, &owner);
+		float res = it.band_radius < 0 ? wave_cost<H, 1, true>(A, n, B, m, -1, lane, nullptr, &owner)
+		                               : wave_cost<H, 1, false>(A, n, B, m, it.band_radius, lane, nullptr, &owner);
 		if (owner) {
 			if (it.exclude_last) res -= fabsf(__ldg(A + n - 1) - __ldg(B + m - 1));               // dtw.cpp:514-516 / :60-62
 			L.cost[k] = res;
@@ -181,7 +186,8 @@ k_dtw_wave_cta(DtwLaunch L, const uint32_t *__restrict__ order, uint32_t n_order
 		int n = (int)it.a_len, m = (int)it.b_len;
 		if (n < m) { const float *t = A; A = B; B = t; const int tl = n; n = m; m = tl; }
 		bool owner;
-		float res = wave_cost<H, kWideWarps>(A, n, B, m, it.band_radius, (int)threadIdx.x, mbox, &owner);
+		float res = it.band_radius < 0 ? wave_cost<H, kWideWarps, true>(A, n, B, m, -1, (int)threadIdx.x, mbox, &owner)
+		                               : wave_cost<H, kWideWarps, false>(A, n, B, m, it.band_radius, (int)threadIdx.x, mbox, &owner);
 		if (owner) {
 			if (it.exclude_last) res -= fabsf(__ldg(A + n - 1) - __ldg(B + m - 1));
 			L.cost[k] = res;

@@ -21,10 +21,11 @@ for name, al, bl, R, n in shapes:
     a_d = torch.from_numpy(a.reshape(-1)).to(dev); b_d = torch.from_numpy(b.reshape(-1)).to(dev)
     it_d = torch.from_numpy(items.view(np.uint8).reshape(-1)).to(dev); c_d = torch.empty(n, dtype=torch.float32, device=dev)
     cells = ra.Context.dtw_cells(al, bl, R) * n
-    for _ in range(2):
+    REPS = int(os.environ.get("RA_MB_REPS", 5))                    # RA_MB_REPS=1: one warm-up + one timed launch per shape (for ncu)
+    for _ in range(2 if REPS > 1 else 1):
         ctx.dtw_batch_dev(a_d.data_ptr(), b_d.data_ptr(), it_d.data_ptr(), items, c_d.data_ptr())
     ts = []
-    for _ in range(5):
+    for _ in range(REPS):
         ctx.dtw_batch_dev(a_d.data_ptr(), b_d.data_ptr(), it_d.data_ptr(), items, c_d.data_ptr())
         ts.append(ctx.last_timing()[2])
     ms = float(np.median(ts))
@@ -47,7 +48,7 @@ for hook, label in ((0, "sparse-like stream, R=1 (one item per thread)"), (4, "s
     c2 = ra.Context(0, opt)
     nn = n if hook == 0 else n // 8
     ts = []
-    for rep in range(4):
+    for rep in range(4 if int(os.environ.get("RA_MB_REPS", 5)) > 1 else 2):
         t0 = time.perf_counter()
         c2.dtw_batch_dev(a_d.data_ptr(), b_d.data_ptr(), it_d.data_ptr(), items[:nn], c_d.data_ptr())
         wall = (time.perf_counter() - t0) * 1e3
