@@ -46,6 +46,13 @@ __device__ __forceinline__ bool linkable(int32_t ct, int32_t cq, int32_t pt, int
 	return gap_scale < 5.0f && gap_scale > 0.75f;
 }
 
+// A predecessor can only be linked when 4 qd > 3 td (gap_scale > 0.75, :472) and qd = cq - pq <= cq, i.e. when 3 td < 4 cq.  The
+// lists are sorted by target, so from the first predecessor with 3 td >= 4 cq on nothing can be linked any more: whatever the
+// reference's scan still does there (count skips until the target-gap break or the cut-off) cannot change the anchor's score or
+// predecessor.  The scans below stop there -- for the anchors of a first chunk (cq < ~500 events) a window of < 670 target
+// positions instead of max_target_gap_length = 5000.
+__device__ __forceinline__ bool beyond_link_reach(int32_t ct, int32_t cq, int32_t pt) { return 3ll * ((long long)ct - pt) >= 4ll * cq; }
+
 // Pre-pass of the chaining DP, one lane per anchor.  Most anchors are isolated seed hits: no predecessor the reference's scan
 // would look at (:452-484: up to the target-gap break, the chaining band, or max_num_skips + 1 comparisons that cannot
 // improve) satisfies the gap conditions of :472, so their score stays the seed value e and they are their own predecessor --
@@ -87,7 +94,7 @@ k_chain_pre(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const ui
 			const int32_t pt = (int32_t)key_target(kp), pq = (int32_t)key_query(kp);
 			const bool same = key_list(kp) == list && a - pj <= (uint32_t)P.chaining_band_length;
 			const bool skipc = pq == cq || pt == ct;                                          // :455-456
-			const bool brk = !skipc && (pt + P.max_target_gap_length < ct);                   // :458
+			const bool brk = (!skipc && (pt + P.max_target_gap_length < ct)) || beyond_link_reach(ct, cq, pt);   // :458
 			const bool consider = active && same && !skipc && !brk && (cq - pq) >= 0;         // :465
 			const bool link = consider && linkable(ct, cq, pt, pq, P);
 			hit |= link;
@@ -145,7 +152,7 @@ k_chain_simple(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const
 			const int32_t pt = (int32_t)key_target(kp), pq = (int32_t)key_query(kp);
 			const bool same = key_list(kp) == list && a - pj <= (uint32_t)P.chaining_band_length;    // :446-448
 			const bool skipc = pq == cq || pt == ct;                                          // :455-456
-			const bool brk = !skipc && (pt + P.max_target_gap_length < ct);                   // :458
+			const bool brk = (!skipc && (pt + P.max_target_gap_length < ct)) || beyond_link_reach(ct, cq, pt);   // :458
 			const bool consider = active && same && !skipc && !brk && (cq - pq) >= 0;         // :465
 			const bool link = consider && linkable(ct, cq, pt, pq, P);
 			if (link && F[pj]) complex_ = true;                                                // its score is not e and not known yet
@@ -282,7 +289,7 @@ k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64
 					const uint32_t pi = inrange ? top - 1u - (uint32_t)lane : start;
 					const uint64_t kp = K[pi];
 					const int32_t pt = (int32_t)key_target(kp), pq = (int32_t)key_query(kp);
-					const bool brk_t = inrange && (pt + P.max_target_gap_length < ct);              // :458
+					const bool brk_t = inrange && ((pt + P.max_target_gap_length < ct) || beyond_link_reach(ct, cq, pt));   // :458
 					const uint32_t dead_mask = __ballot_sync(0xffffffffu, brk_t || !inrange);
 					const int first_dead = dead_mask ? __ffs(dead_mask) - 1 : 32;
 					const int32_t td = ct - pt, qd = cq - pq;
