@@ -253,7 +253,7 @@ k_sp_parts(ChainLaunch L, SparsePlan P)
 // parts of a tile -- 2 % of the parts -- cost 30 % of the warp instructions because they ran 1-3 lanes wide).  Here a
 // warp owns a tile of up to 128 consecutive parts of one chain, synchronises only with itself, and moves on to its next
 // tile as soon as it is done:
-//   * the tile is cut into batches whose read / reference spans fit the warp's staging window (1024 floats each);
+//   * the tile is cut into batches whose read / reference spans fit the warp's staging window (kSp2Stage floats each);
 //   * R' <= 2 parts (98 % at banded=0.1: band 1 -> R' = 1 when square, 2 otherwise) are counting-sorted by height and
 //     run 32 at a time through ONE register evaluator (R' = 1 embedded in the R' = 2 schedule, dtw_core.cuh), so a round
 //     has no class divergence; a round of only R' = 1 parts takes the smaller R' = 1 evaluator;
@@ -283,7 +283,11 @@ __device__ __forceinline__ uint32_t diag_cells(int n, int m, int rp)
 constexpr int kSp2Warps = 4;
 constexpr int kSp2Tile = kSparseTileParts2;       // parts per warp tile
 constexpr int kSp2Per = kSp2Tile / 32;
-constexpr int kSp2Stage = 1024;
+#ifndef RA_SP2_STAGE
+#define RA_SP2_STAGE 480
+#endif
+constexpr int kSp2Stage = RA_SP2_STAGE;            // floats of read span / reference span staged per warp batch (<= 1024: 10-bit offsets in desc)
+static_assert(kSp2Stage <= 1024 && kSp2Stage % 32 == 0, "staging window");
 constexpr int kSp2Bins = 64;                      // class (0: R' <= 2, 1: other narrow) x height (32 bins)
 constexpr uint32_t kSp2DeferBelow = 16;           // a remainder of fewer other-narrow parts goes to k_sp_rest
 

@@ -134,7 +134,7 @@ struct SparsePlan {
 };
 constexpr int kSparseCtasPerSm = 6;
 #ifndef RA_SP2_CTAS
-#define RA_SP2_CTAS 4
+#define RA_SP2_CTAS 6                // with a staging window of 480 floats per span: 38 KB per CTA (profiles/r02_ab_sp2_stage_ctas.txt)
 #endif
 constexpr int kSparse2CtasPerSm = RA_SP2_CTAS;
 constexpr int kSparseTileParts = 256;
