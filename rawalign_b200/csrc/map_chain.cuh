@@ -3,6 +3,9 @@
 
 namespace mapk {
 
+#ifndef RA_CHAIN_MIN_CTAS
+#define RA_CHAIN_MIN_CTAS 8              // 60 registers, 32 warps per SM: +3.4 % on the C2 map loop (profiles/r02_ab_chain_ctas.txt)
+#endif
 constexpr int kMaxBest = 8;                                        // num_best_chains supported (default 3, roptions.c:18)
 
 // traceback_chains, rmap.cpp:130-173.  score / pred / used are indexed like the keys of the segment (pred = segment index).
@@ -185,7 +188,7 @@ k_chain_simple(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const
 // tracebacks.  The running maximum only needs the listed anchors: every score is >= e, and the filter of :488-492 is applied
 // after the anchor's own score has entered the maximum.  Candidate chains go to cand[i * cap + k] in generation order, or
 // sorted by chaining score (stable, :512) when they are to be evaluated by DTW.
-__global__ void __launch_bounds__(128, 4)
+__global__ void __launch_bounds__(128, RA_CHAIN_MIN_CTAS)
 k_chain(const uint32_t *__restrict__ act, uint32_t n_act, Params P, const uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_base,
         const uint32_t *__restrict__ seg_n, const uint32_t *__restrict__ skip, float *__restrict__ score, uint32_t *__restrict__ pred,
         uint8_t *__restrict__ used, const uint32_t *__restrict__ nt, const uint32_t *__restrict__ n_nt, const uint8_t *__restrict__ cx,
