@@ -304,7 +304,10 @@ constexpr uint32_t kBucketMaxKeys = 8192;                          // the common
 constexpr uint32_t kBucketMaxKeysL = 20480;                        // long segments (reads with several chunks of anchors): one CTA per SM
 constexpr int kBucketThreads = 512;
 constexpr uint32_t kGroupKeys = 4096;                              // MAXK == 0: keys of one run of bins finished in shared memory
-constexpr uint32_t kFineBins = 2048;                               // MAXK == 0: the run is binned again, up to 2^F times finer
+constexpr uint32_t kFineBins = 2048;
+constexpr int kScanIters = (int)(kBins / kBucketThreads);         // bins per thread in the CTA-wide scan
+constexpr uint32_t kMaxCrowded = 63;
+constexpr uint32_t kSmallBin = 24;                                 // bins up to this size are finished by one thread                               // MAXK == 0: the run is binned again, up to 2^F times finer
 template <uint32_t MAXK>
 struct BucketSmemT {
 	uint64_t keys[MAXK ? MAXK : kGroupKeys];                       // MAXK == 0: the binned keys are staged in a global-memory arena; keys[] holds one run of bins at a time
@@ -312,38 +315,83 @@ struct BucketSmemT {
 	uint32_t fine[MAXK ? 1 : kFineBins + 1];
 	uint32_t count[kBins + 1];
 	uint32_t cursor[kBins];
-	uint32_t warp_tot[kBucketThreads / 32];
+	uint32_t warp_tot[kScanIters * (kBucketThreads / 32)];
+	uint32_t crowd[1 + kMaxCrowded];                               // [0]: number of bins with more than kSmallBin keys, then their indices
 };
 
-// exclusive scan of a[0 .. n) in place by the whole CTA (a[n] is not written); cur[] receives a copy
+// exclusive scan of a[0 .. n), n <= kBins, in place by the whole CTA (a[n] is not written); cur[] receives a copy.  Thread t holds
+// bins t, t + 512, ...: warp-inclusive scans in registers, one pass of warp 0 over the 128 warp totals, three barriers in all.
 __device__ __forceinline__ void cta_exclusive_scan(uint32_t *a, uint32_t *cur, uint32_t n, uint32_t *warp_tot, int tid, int lane, int wid)
 {
-	uint32_t carry = 0;
-	for (uint32_t b0 = 0; b0 < n; b0 += kBucketThreads) {
-		const uint32_t b = b0 + tid;
-		const uint32_t v = b < n ? a[b] : 0u;
-		uint32_t inc = v;
+	constexpr int W = kBucketThreads / 32;
+	uint32_t v[kScanIters], inc[kScanIters];
 #pragma unroll
-		for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += y; }
-		if (lane == 31) warp_tot[wid] = inc;
-		__syncthreads();
-		uint32_t before = 0, total = 0;
-		for (int w = 0; w < kBucketThreads / 32; ++w) { const uint32_t t = warp_tot[w]; if (w < wid) before += t; total += t; }
-		if (b < n) { const uint32_t ex = carry + before + inc - v; a[b] = ex; cur[b] = ex; }
-		carry += total;
-		__syncthreads();
+	for (int i = 0; i < kScanIters; ++i) {
+		const uint32_t b = (uint32_t)(i * kBucketThreads + tid);
+		v[i] = b < n ? a[b] : 0u;
+		uint32_t x = v[i];
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, d); if (lane >= d) x += y; }
+		inc[i] = x;
+		if (lane == 31) warp_tot[i * W + wid] = x;                 // entry i * W + wid covers bins i * 512 + wid * 32 + [0, 32): bin order
 	}
+	__syncthreads();
+	if (wid == 0) {                                                // exclusive scan of the kScanIters * W totals, (kScanIters * W / 32) per lane
+		constexpr int PER = kScanIters * W / 32;
+		uint32_t t[PER], sum = 0;
+#pragma unroll
+		for (int k = 0; k < PER; ++k) { t[k] = warp_tot[PER * lane + k]; sum += t[k]; }
+		uint32_t x = sum;
+#pragma unroll
+		for (int d = 1; d < 32; d <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, d); if (lane >= d) x += y; }
+		uint32_t ex = x - sum;
+#pragma unroll
+		for (int k = 0; k < PER; ++k) { warp_tot[PER * lane + k] = ex; ex += t[k]; }
+	}
+	__syncthreads();
+#pragma unroll
+	for (int i = 0; i < kScanIters; ++i) {
+		const uint32_t b = (uint32_t)(i * kBucketThreads + tid);
+		if (b < n) { const uint32_t ex = warp_tot[i * W + wid] + inc[i] - v[i]; a[b] = ex; cur[b] = ex; }
+	}
+	__syncthreads();
 }
-using BucketSmem = BucketSmemT<kBucketMaxKeys>;
 
 // finishes bins [b0, b1) of a binned key array (wk[0] is the key at position base, count[b] = start of bin b): small bins by one
-// thread each (insertion sort), crowded ones by a whole warp afterwards
-__device__ __forceinline__ void finish_bins(uint64_t *wk, uint32_t base, const uint32_t *count, uint32_t b0, uint32_t b1, int tid, int lane, int wid)
+// thread each (insertion sort), crowded ones (listed in crowd[] on the way) by a whole warp afterwards.  Called by the whole CTA.
+__device__ __forceinline__ void warp_sort_bin(uint64_t *w, uint32_t m, int lane)
 {
-	constexpr uint32_t kSmall = 24;
+	uint32_t pad = 32; while (pad < m) pad <<= 1;
+	// bitonic network in its all-ascending form (first step of every merge compares mirrored positions), over a virtual
+	// power-of-two range whose slots >= m hold +inf: every comparator moves the minimum to the lower index, so the
+	// virtual keys never move and only pairs of real keys are touched
+	for (uint32_t size = 2; size <= pad; size <<= 1) {
+		const uint32_t half = size >> 1;
+		for (uint32_t t = lane; t < (pad >> 1); t += 32) {
+			const uint32_t blk = t / half, off = t - blk * half;
+			const uint32_t l0 = blk * size + off, h0 = blk * size + size - 1u - off;
+			if (h0 < m) { const uint64_t x = w[l0], y = w[h0]; if (x > y) { w[l0] = y; w[h0] = x; } }
+		}
+		__syncwarp();
+		for (uint32_t stride = half >> 1; stride > 0; stride >>= 1) {
+			for (uint32_t t = lane; t < (pad >> 1); t += 32) {
+				const uint32_t l0 = 2 * t - (t & (stride - 1)), h0 = l0 + stride;
+				if (h0 < m) { const uint64_t x = w[l0], y = w[h0]; if (x > y) { w[l0] = y; w[h0] = x; } }
+			}
+			__syncwarp();
+		}
+	}
+}
+
+__device__ __forceinline__ void finish_bins(uint64_t *wk, uint32_t base, const uint32_t *count, uint32_t b0, uint32_t b1, int tid, int lane, int wid,
+                                            uint32_t *crowd)
+{
+	if (tid == 0) crowd[0] = 0;
+	__syncthreads();
 	for (uint32_t b = b0 + tid; b < b1; b += kBucketThreads) {
 		const uint32_t lo = count[b], m = count[b + 1] - lo;
-		if (m < 2 || m > kSmall) continue;
+		if (m < 2) continue;
+		if (m > kSmallBin) { const uint32_t k = atomicAdd(&crowd[0], 1u); if (k < kMaxCrowded) crowd[1 + k] = b; continue; }
 		uint64_t *w = wk + (lo - base);
 		for (uint32_t a = 1; a < m; ++a) {
 			const uint64_t x = w[a];
@@ -352,29 +400,17 @@ __device__ __forceinline__ void finish_bins(uint64_t *wk, uint32_t base, const u
 			w[c] = x;
 		}
 	}
-	for (uint32_t b = b0 + wid; b < b1; b += kBucketThreads / 32) {   // warp-uniform loop
-		const uint32_t lo = count[b], m = count[b + 1] - lo;
-		if (m <= kSmall) continue;
-		uint32_t pad = 32; while (pad < m) pad <<= 1;
-		uint64_t *w = wk + (lo - base);
-		// bitonic network in its all-ascending form (first step of every merge compares mirrored positions), over a virtual
-		// power-of-two range whose slots >= m hold +inf: every comparator moves the minimum to the lower index, so the
-		// virtual keys never move and only pairs of real keys are touched
-		for (uint32_t size = 2; size <= pad; size <<= 1) {
-			const uint32_t half = size >> 1;
-			for (uint32_t t = lane; t < (pad >> 1); t += 32) {
-				const uint32_t blk = t / half, off = t - blk * half;
-				const uint32_t l0 = blk * size + off, h0 = blk * size + size - 1u - off;
-				if (h0 < m) { const uint64_t x = w[l0], y = w[h0]; if (x > y) { w[l0] = y; w[h0] = x; } }
-			}
-			__syncwarp();
-			for (uint32_t stride = half >> 1; stride > 0; stride >>= 1) {
-				for (uint32_t t = lane; t < (pad >> 1); t += 32) {
-					const uint32_t l0 = 2 * t - (t & (stride - 1)), h0 = l0 + stride;
-					if (h0 < m) { const uint64_t x = w[l0], y = w[h0]; if (x > y) { w[l0] = y; w[h0] = x; } }
-				}
-				__syncwarp();
-			}
+	__syncthreads();
+	const uint32_t nc = crowd[0];
+	if (nc <= kMaxCrowded) {
+		for (uint32_t k = wid; k < nc; k += kBucketThreads / 32) {  // warp-uniform loop
+			const uint32_t b = crowd[1 + k], lo = count[b];
+			warp_sort_bin(wk + (lo - base), count[b + 1] - lo, lane);
+		}
+	} else {                                                       // more crowded bins than the list holds: look at every bin
+		for (uint32_t b = b0 + wid; b < b1; b += kBucketThreads / 32) {
+			const uint32_t lo = count[b], m = count[b + 1] - lo;
+			if (m > kSmallBin) warp_sort_bin(wk + (lo - base), m, lane);
 		}
 	}
 }
@@ -413,7 +449,7 @@ k_sort_buckets(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_bas
 	}
 	__syncthreads();
 	if (MAXK) {
-		finish_bins(wk, 0, sm.count, 0, n_bins, tid, lane, wid);
+		finish_bins(wk, 0, sm.count, 0, n_bins, tid, lane, wid, sm.crowd);
 		__syncthreads();
 		for (uint32_t k = tid; k < n; k += kBucketThreads) g[k] = wk[k];
 		return;
@@ -430,7 +466,7 @@ k_sort_buckets(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_bas
 		for (step >>= 1; step > 0; step >>= 1) if (fits(b1 + step)) b1 += step;
 		if (b1 == b0) {                                             // one crowded bin beyond the buffer
 			b1 = b0 + 1;
-			finish_bins(wk, 0, sm.count, b0, b1, tid, lane, wid);
+			finish_bins(wk, 0, sm.count, b0, b1, tid, lane, wid, sm.crowd);
 			__syncthreads();
 			for (uint32_t k = lo + tid; k < sm.count[b1]; k += kBucketThreads) g[k] = wk[k];
 		} else {
@@ -440,7 +476,7 @@ k_sort_buckets(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_bas
 			for (uint32_t k = tid; k < m; k += kBucketThreads) sm.keys[k] = wk[lo + k];
 			if (F == 0) {
 				__syncthreads();
-				finish_bins(sm.keys, lo, sm.count, b0, b1, tid, lane, wid);
+				finish_bins(sm.keys, lo, sm.count, b0, b1, tid, lane, wid, sm.crowd);
 				__syncthreads();
 				for (uint32_t k = tid; k < m; k += kBucketThreads) g[lo + k] = sm.keys[k];
 			} else {
@@ -460,7 +496,7 @@ k_sort_buckets(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_bas
 					sm.keys2[atomicAdd(&sm.cursor[((key_bin(key, bin_base, tshift) - b0) << F) | ((key_target(key) >> fsh) & fmask)], 1u)] = key;
 				}
 				__syncthreads();
-				finish_bins(sm.keys2, 0, sm.fine, 0, nf, tid, lane, wid);
+				finish_bins(sm.keys2, 0, sm.fine, 0, nf, tid, lane, wid, sm.crowd);
 				__syncthreads();
 				for (uint32_t k = tid; k < m; k += kBucketThreads) g[lo + k] = sm.keys2[k];
 			}
