@@ -321,7 +321,8 @@ struct BucketSmemT {
 
 // exclusive scan of a[0 .. n), n <= kBins, in place by the whole CTA (a[n] is not written); cur[] receives a copy.  Thread t holds
 // bins t, t + 512, ...: warp-inclusive scans in registers, one pass of warp 0 over the 128 warp totals, three barriers in all.
-__device__ __forceinline__ void cta_exclusive_scan(uint32_t *a, uint32_t *cur, uint32_t n, uint32_t *warp_tot, int tid, int lane, int wid)
+__device__ __forceinline__ void cta_exclusive_scan(uint32_t *a, uint32_t *cur, uint32_t n, uint32_t *warp_tot, int tid, int lane, int wid,
+                                                   uint32_t *crowd = nullptr /* bins of more than kSmallBin keys are appended (crowd[0] zeroed by the caller) */)
 {
 	constexpr int W = kBucketThreads / 32;
 	uint32_t v[kScanIters], inc[kScanIters];
@@ -353,6 +354,7 @@ __device__ __forceinline__ void cta_exclusive_scan(uint32_t *a, uint32_t *cur, u
 	for (int i = 0; i < kScanIters; ++i) {
 		const uint32_t b = (uint32_t)(i * kBucketThreads + tid);
 		if (b < n) { const uint32_t ex = warp_tot[i * W + wid] + inc[i] - v[i]; a[b] = ex; cur[b] = ex; }
+		if (crowd && v[i] > kSmallBin) { const uint32_t k = atomicAdd(&crowd[0], 1u); if (k < kMaxCrowded) crowd[1 + k] = b; }
 	}
 	__syncthreads();
 }
@@ -415,6 +417,43 @@ __device__ __forceinline__ void finish_bins(uint64_t *wk, uint32_t base, const u
 	}
 }
 
+// The bins of a binned key array straight to their sorted place in global memory: one thread per KEY -- its rank among the keys of
+// its bin (ties by position, so the result is a permutation) is its offset in the bin.  src[0] is the key at position `base`,
+// count[b] the start of bin b, bin_of(key) the key's bin; positions [p0, p1); dst is indexed by position.  Adjacent threads hold
+// keys of the same or neighbouring bins, so the rank loops of a warp are about equally long (the one-thread-per-bin insertion
+// sort this replaces ran 4 of 32 lanes wide).  Bins of more than kSmallBin keys are left to crowded_write.
+template <class BinOf>
+__device__ __forceinline__ void rank_write(const uint64_t *src, uint32_t base, const uint32_t *count, uint32_t p0, uint32_t p1, BinOf bin_of,
+                                           uint64_t *__restrict__ dst, int tid)
+{
+	for (uint32_t p = p0 + tid; p < p1; p += kBucketThreads) {
+		const uint64_t x = src[p - base];
+		const uint32_t b = bin_of(x);
+		const uint32_t lo = count[b], m = count[b + 1] - lo;
+		if (m > kSmallBin) continue;
+		const uint64_t *w = src + (lo - base);
+		uint32_t r = 0;
+		for (uint32_t q = 0; q < m; ++q) { const uint64_t y = w[q]; r += (y < x || (y == x && lo + q < p)) ? 1u : 0u; }
+		dst[lo + r] = x;
+	}
+}
+
+// the crowded bins: sorted in place by a whole warp each, then copied out.  crowd == nullptr or an overflowed list: every bin of
+// [b0, b1) is looked at.  Warp-uniform.
+__device__ __forceinline__ void crowded_write(uint64_t *src, uint32_t base, const uint32_t *count, uint32_t b0, uint32_t b1, const uint32_t *crowd,
+                                              uint64_t *__restrict__ dst, int lane, int wid)
+{
+	auto one = [&](uint32_t b) {
+		const uint32_t lo = count[b], m = count[b + 1] - lo;
+		uint64_t *w = src + (lo - base);
+		warp_sort_bin(w, m, lane);
+		for (uint32_t t = lane; t < m; t += 32) dst[lo + t] = w[t];
+	};
+	const uint32_t nc = crowd ? crowd[0] : 0xffffffffu;
+	if (nc <= kMaxCrowded) { for (uint32_t k = wid; k < nc; k += kBucketThreads / 32) one(crowd[1 + k]); }
+	else for (uint32_t b = b0 + wid; b < b1; b += kBucketThreads / 32) if (count[b + 1] - count[b] > kSmallBin) one(b);
+}
+
 __device__ __forceinline__ uint32_t key_bin(uint64_t k, const uint32_t *__restrict__ bin_base, uint32_t tshift)
 {
 	return bin_base[key_list(k)] + (key_target(k) >> tshift);
@@ -436,11 +475,12 @@ k_sort_buckets(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_bas
 	uint64_t *const wk = MAXK ? sm.keys : stage + seg_base[i];    // where the binned keys live while the bins are finished
 	const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
 	for (uint32_t b = tid; b <= n_bins; b += kBucketThreads) sm.count[b] = 0;
+	if (tid == 0) sm.crowd[0] = 0;
 	__syncthreads();
 	for (uint32_t k = tid; k < n; k += kBucketThreads) atomicAdd(&sm.count[key_bin(g[k], bin_base, tshift)], 1u);
 	__syncthreads();
 	// exclusive scan of count[0 .. n_bins) -> cursor / count (count[b] becomes the start of bin b, count[n_bins] = n)
-	cta_exclusive_scan(sm.count, sm.cursor, n_bins, sm.warp_tot, tid, lane, wid);
+	cta_exclusive_scan(sm.count, sm.cursor, n_bins, sm.warp_tot, tid, lane, wid, MAXK ? sm.crowd : nullptr);
 	if (tid == 0) sm.count[n_bins] = n;
 	__syncthreads();
 	for (uint32_t k = tid; k < n; k += kBucketThreads) {
@@ -448,10 +488,11 @@ k_sort_buckets(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_bas
 		wk[atomicAdd(&sm.cursor[key_bin(key, bin_base, tshift)], 1u)] = key;
 	}
 	__syncthreads();
-	if (MAXK) {
-		finish_bins(wk, 0, sm.count, 0, n_bins, tid, lane, wid, sm.crowd);
+	const auto bin1 = [&](uint64_t key) { return key_bin(key, bin_base, tshift); };
+	if (MAXK) {                                                   // binned keys in shared memory -> sorted keys in global memory
+		rank_write(wk, 0, sm.count, 0, n, bin1, g, tid);
 		__syncthreads();
-		for (uint32_t k = tid; k < n; k += kBucketThreads) g[k] = wk[k];
+		crowded_write(wk, 0, sm.count, 0, n_bins, sm.crowd, g, lane, wid);
 		return;
 	}
 	// MAXK == 0: the binned keys sit in global memory.  Runs of consecutive bins that fit the group buffer are loaded into shared
@@ -476,29 +517,31 @@ k_sort_buckets(uint64_t *__restrict__ keys, const uint64_t *__restrict__ seg_bas
 			for (uint32_t k = tid; k < m; k += kBucketThreads) sm.keys[k] = wk[lo + k];
 			if (F == 0) {
 				__syncthreads();
-				finish_bins(sm.keys, lo, sm.count, b0, b1, tid, lane, wid, sm.crowd);
+				rank_write(sm.keys, lo, sm.count, lo, lo + m, bin1, g, tid);
 				__syncthreads();
-				for (uint32_t k = tid; k < m; k += kBucketThreads) g[lo + k] = sm.keys[k];
+				crowded_write(sm.keys, lo, sm.count, b0, b1, nullptr, g, lane, wid);
 			} else {
 				const uint32_t nf = nb << F, fmask = (1u << F) - 1u, fsh = tshift - F;
+				const auto bin2 = [&](uint64_t key) { return ((key_bin(key, bin_base, tshift) - b0) << F) | ((key_target(key) >> fsh) & fmask); };
 				for (uint32_t b = tid; b <= nf; b += kBucketThreads) sm.fine[b] = 0;
+				if (tid == 0) sm.crowd[0] = 0;
 				__syncthreads();
 				for (uint32_t k = tid; k < m; k += kBucketThreads) {
 					const uint64_t key = sm.keys[k];
-					atomicAdd(&sm.fine[((key_bin(key, bin_base, tshift) - b0) << F) | ((key_target(key) >> fsh) & fmask)], 1u);
+					atomicAdd(&sm.fine[bin2(key)], 1u);
 				}
 				__syncthreads();
-				cta_exclusive_scan(sm.fine, sm.cursor, nf, sm.warp_tot, tid, lane, wid);   // (cursor[] is free once the first-level scatter is done)
+				cta_exclusive_scan(sm.fine, sm.cursor, nf, sm.warp_tot, tid, lane, wid, sm.crowd);   // (cursor[] is free once the first-level scatter is done)
 				if (tid == 0) sm.fine[nf] = m;
 				__syncthreads();
 				for (uint32_t k = tid; k < m; k += kBucketThreads) {
 					const uint64_t key = sm.keys[k];
-					sm.keys2[atomicAdd(&sm.cursor[((key_bin(key, bin_base, tshift) - b0) << F) | ((key_target(key) >> fsh) & fmask)], 1u)] = key;
+					sm.keys2[atomicAdd(&sm.cursor[bin2(key)], 1u)] = key;
 				}
 				__syncthreads();
-				finish_bins(sm.keys2, 0, sm.fine, 0, nf, tid, lane, wid, sm.crowd);
+				rank_write(sm.keys2, 0, sm.fine, 0, m, bin2, g + lo, tid);
 				__syncthreads();
-				for (uint32_t k = tid; k < m; k += kBucketThreads) g[lo + k] = sm.keys2[k];
+				crowded_write(sm.keys2, 0, sm.fine, 0, nf, sm.crowd, g + lo, lane, wid);
 			}
 		}
 		__syncthreads();
