@@ -620,6 +620,8 @@ def map_path(args, rank, world, local, torch, dist, dev, binding):
     from rawalign_b200.shard import broadcast_index
     for w in range(depth):
         c = ra.Context(local)
+        if os.environ.get("RA_BENCH_HOST_GATHER"):
+            c.set_tuning("map_host_gather", int(os.environ["RA_BENCH_HOST_GATHER"]))
         # rank 0 parses the reference's index file; the other ranks receive the device tables (hash slots, positions, reference
         # signals) by NCCL broadcast -- the one collective of the path, at load
         pipes.append((c, broadcast_index(c, ds.index_path, rank, dev) if w == 0 else pipes[0][1].clone(c)))

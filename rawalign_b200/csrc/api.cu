@@ -115,6 +115,7 @@ struct ra_ctx {
 	bool force_generic_dtw = false;    // test hook (reserved bit 2): every item through the generic shared-memory DTW kernel
 	bool legacy_sparse_tiles = false;  // test hook (reserved bit 3): sparse parts through the CTA-wide tiles of k_sp_parts instead of k_sp_parts2
 	bool want_ev_pos = true;           // keep the event start samples of the last K1 call (ra_last_event_positions)
+	int map_host_gather = 0;           // ra_set_tuning("map_host_gather"): float-form ra_map_batch gathers the round's chunks on the host (N threads) and uploads them by DMA
 	bool map_sig_whole = false;        // ra_set_tuning("map_sig_whole"): float-form ra_map_batch uploads the whole batch up front
 	uint64_t chain_slice_min_anchors = 2u << 20;   // ra_set_tuning("chain_slice_min_anchors"): anchors per upload slice of ra_align_chains_batch
 	// traceback
@@ -712,12 +713,14 @@ int ra_set_tuning(ra_ctx *ctx, const char *name, int64_t value)
 	if (!strcmp(name, "k1_groups")) { if (value < 1 || value > kSliceStreams) return fail(RA_EINVAL, "k1_groups must be 1..%d", kSliceStreams); ctx->k1_groups = (int)value; return RA_OK; }
 	if (!strcmp(name, "k1_priority_stream")) { ctx->k1_prio = value != 0; return RA_OK; }
 	if (!strcmp(name, "map_sig_whole")) { ctx->map_sig_whole = value != 0; return RA_OK; }
+	if (!strcmp(name, "map_host_gather")) { if (value < 0 || value > 16) return fail(RA_EINVAL, "map_host_gather must be 0..16 (threads)"); ctx->map_host_gather = (int)value; return RA_OK; }
 	return fail(RA_EINVAL, "unknown tuning parameter %s", name);
 }
 // internal (map.cu): kernels launched outside this file count too; errors raised there go through ra_last_error()
 void ra__add_launches(ra_ctx *ctx, uint64_t n) { if (ctx) ctx->launches += n; }
 int ra__device(const ra_ctx *ctx) { return ctx ? ctx->device : 0; }
 int ra__map_sig_whole(const ra_ctx *ctx) { return ctx && ctx->map_sig_whole; }
+int ra__map_host_gather(const ra_ctx *ctx) { return ctx ? ctx->map_host_gather : 0; }
 // internal (map.cu): lets the entry points that read "the events resident on the device" read the map loop's event arena
 void ra__swap_resident(ra_ctx *ctx, void **dev_ptr, uint64_t *n_floats)
 {

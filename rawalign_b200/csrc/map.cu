@@ -21,11 +21,13 @@
 #include <cstdlib>
 #include <string>
 #include <vector>
+#include <thread>
 
 extern "C" void ra__add_launches(ra_ctx *ctx, uint64_t n);        // api.cu
 extern "C" int ra__fail(int code, const char *fmt, ...);            // api.cu: sets ra_last_error()
 extern "C" int ra__device(const ra_ctx *ctx);
 extern "C" int ra__map_sig_whole(const ra_ctx *ctx);
+extern "C" int ra__map_host_gather(const ra_ctx *ctx);
 extern "C" void ra__swap_resident(ra_ctx *ctx, void **dev_ptr, uint64_t *n_floats);
 
 namespace {

@@ -188,7 +188,8 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 		stt.h2d_bytes += n_samples * 2 + (uint64_t)n_reads * 20;
 	} else if (!lazy) { MAP_CUDA(cudaMemcpyAsync(ix->sig.p, sig, n_samples * 4, cudaMemcpyHostToDevice, S)); stt.h2d_bytes += n_samples * 4; }
 	const float *hsig_dev = nullptr;                               // the caller's buffer as the device sees it (page-locked, mapped), else NULL
-	if (lazy && n_samples) {
+	const int host_gather = ra__map_host_gather(ctx);
+	if (lazy && n_samples && !host_gather) {
 		cudaPointerAttributes pa0, pa1;
 		if (cudaPointerGetAttributes(&pa0, sig) == cudaSuccess && cudaPointerGetAttributes(&pa1, sig + n_samples - 1) == cudaSuccess &&
 		    pa0.type == cudaMemoryTypeHost && pa1.type == cudaMemoryTypeHost && pa0.devicePointer &&
@@ -238,7 +239,15 @@ extern "C" int ra_map_batch(ra_ctx *ctx, ra_index *ix, const ra_ri_mapopt_t *opt
 				}
 				float *stg = static_cast<float *>(ix->pin_sig);
 				uint64_t moved = 0;
-				for (uint32_t i = 0; i < n_act; ++i) { memcpy(stg + (size_t)i * lazy_stride, sig + h_coff[i], (size_t)h_clen[i] * 4); moved += h_clen[i]; }
+				const int nthr = std::max(1, std::min(host_gather, (int)(n_act / 256)));
+				auto gather = [&](uint32_t i0, uint32_t i1) { for (uint32_t i = i0; i < i1; ++i) memcpy(stg + (size_t)i * lazy_stride, sig + h_coff[i], (size_t)h_clen[i] * 4); };
+				if (nthr > 1) {
+					std::vector<std::thread> th;
+					for (int t = 1; t < nthr; ++t) th.emplace_back(gather, (uint32_t)((uint64_t)n_act * t / nthr), (uint32_t)((uint64_t)n_act * (t + 1) / nthr));
+					gather(0, (uint32_t)((uint64_t)n_act / nthr));
+					for (auto &t : th) t.join();
+				} else gather(0, n_act);
+				for (uint32_t i = 0; i < n_act; ++i) moved += h_clen[i];
 				MAP_CUDA(cudaMemcpyAsync(ix->sig.p, stg, need, cudaMemcpyHostToDevice, S));
 				k_dense_coff<<<(n_act + 255) / 256, 256, 0, S>>>(ix->coff.as<uint64_t>(), n_act, lazy_stride); ++launches;
 				stt.h2d_bytes += 4 * moved;
